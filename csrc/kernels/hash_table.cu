@@ -1,0 +1,358 @@
+// K6 + C2 (hash aggregate, fused reduce-scatter of partials), K8 (hash join), K10 (hash sets).
+//
+// Reference counterparts: AccumulateDictionary — a chained table with seed/accumulate in place
+// (LinqToDryad/DryadLinqCollection.cs:519-722) driven by ParallelHashGroupByPartialAccumulate /
+// FullAccumulate (LinqToDryad/DryadLinqVertex.cs:5718-6416); the partial → HashPartition → Merge →
+// final GroupBy plan (LinqToDryad/DryadLinqQueryGen.cs:2179-2296); ParallelHashJoin
+// (DryadLinqVertex.cs:6703-7315); hash-set Distinct/Union/Intersect/Except (DryadLinqVertex.cs:
+// 1239-1660).
+//
+// Design: one open-addressing table per GPU in HBM (keys[cap] + SoA value lanes), claimed with a
+// 64-bit CAS and updated with fire-and-forget reductions (RED).  The decomposable combine across
+// GPUs is NOT a separate shuffle: `agg_merge_peers` walks the local partial table and applies
+// each partial directly to the key-owner's final table in the owner's HBM with system-scope
+// atomics over NVLink — the reduce-scatter and the final accumulate are the same instruction.
+#include "common.cuh"
+#include "../../include/dryad_b200.h"
+
+namespace dryad { namespace ht {
+
+constexpr uint64_t EMPTY = ~0ull;  // reserved key; the engine remaps a genuine ~0 key on ingest
+
+struct Lanes {
+  int nlanes;
+  int op[DRYAD_MAX_LANES];
+  int64_t* tbl[DRYAD_MAX_LANES];       // table lanes (local)
+  const int64_t* in[DRYAD_MAX_LANES];  // input columns (may be null for COUNT)
+};
+
+struct PeerTables {
+  int world;
+  uint64_t* keys[DRYAD_MAX_PEERS];
+  int64_t* lanes[DRYAD_MAX_PEERS][DRYAD_MAX_LANES];
+  uint64_t cap;
+};
+
+__device__ __forceinline__ int64_t identity_of(int op) {
+  switch (op) {
+    case DRYAD_AGG_MIN_I64: return INT64_MAX;
+    case DRYAD_AGG_MAX_I64: return INT64_MIN;
+    case DRYAD_AGG_MIN_F64: return __double_as_longlong(__longlong_as_double(0x7ff0000000000000ll));
+    case DRYAD_AGG_MAX_F64: return __double_as_longlong(__longlong_as_double(0xfff0000000000000ll));
+    default: return 0;  // sums and counts (0.0 is all-zero bits)
+  }
+}
+
+__device__ __forceinline__ void atomic_min_f64(double* addr, double v) {
+  unsigned long long* a = (unsigned long long*)addr;
+  unsigned long long old = *a, assumed;
+  do {
+    assumed = old;
+    if (__longlong_as_double(assumed) <= v) break;
+    old = atomicCAS(a, assumed, (unsigned long long)__double_as_longlong(v));
+  } while (assumed != old);
+}
+__device__ __forceinline__ void atomic_max_f64(double* addr, double v) {
+  unsigned long long* a = (unsigned long long*)addr;
+  unsigned long long old = *a, assumed;
+  do {
+    assumed = old;
+    if (__longlong_as_double(assumed) >= v) break;
+    old = atomicCAS(a, assumed, (unsigned long long)__double_as_longlong(v));
+  } while (assumed != old);
+}
+
+// `combine`: true when folding partial aggregates (COUNT partials add instead of counting rows).
+template <bool SYSTEM>
+__device__ __forceinline__ void apply(int op, int64_t* slot, int64_t v, bool combine,
+                                      int32_t* status) {
+  switch (op) {
+    case DRYAD_AGG_COUNT:
+      if (SYSTEM) atomicAdd_system((unsigned long long*)slot, (unsigned long long)(combine ? v : 1));
+      else atomicAdd((unsigned long long*)slot, (unsigned long long)(combine ? v : 1));
+      break;
+    case DRYAD_AGG_SUM_I64:
+      if (SYSTEM) atomicAdd_system((unsigned long long*)slot, (unsigned long long)v);
+      else atomicAdd((unsigned long long*)slot, (unsigned long long)v);
+      break;
+    case DRYAD_AGG_SUM_I64_CHECKED: {
+      long long old = (long long)(SYSTEM ? atomicAdd_system((unsigned long long*)slot, (unsigned long long)v)
+                                         : atomicAdd((unsigned long long*)slot, (unsigned long long)v));
+      long long nw = (long long)((unsigned long long)old + (unsigned long long)v);
+      if (((old ^ nw) & (v ^ nw)) < 0) atomicMax(status, 3);  // AddChecked overflow
+      break;
+    }
+    case DRYAD_AGG_SUM_F64:
+      if (SYSTEM) atomicAdd_system((double*)slot, __longlong_as_double(v));
+      else atomicAdd((double*)slot, __longlong_as_double(v));
+      break;
+    case DRYAD_AGG_MIN_I64:
+      if (SYSTEM) atomicMin_system((long long*)slot, (long long)v); else atomicMin((long long*)slot, (long long)v);
+      break;
+    case DRYAD_AGG_MAX_I64:
+      if (SYSTEM) atomicMax_system((long long*)slot, (long long)v); else atomicMax((long long*)slot, (long long)v);
+      break;
+    case DRYAD_AGG_MIN_F64: atomic_min_f64((double*)slot, __longlong_as_double(v)); break;
+    case DRYAD_AGG_MAX_F64: atomic_max_f64((double*)slot, __longlong_as_double(v)); break;
+  }
+}
+
+// Find-or-claim the slot of `key`.  Returns cap on a full table.
+template <bool SYSTEM>
+__device__ __forceinline__ uint64_t find_or_insert(uint64_t* keys, uint64_t cap, uint64_t key) {
+  uint64_t mask = cap - 1;
+  uint64_t s = mix64(key) & mask;
+  for (uint64_t probes = 0; probes < cap; ++probes) {
+    uint64_t k = *reinterpret_cast<volatile uint64_t*>(keys + s);
+    if (k == key) return s;
+    if (k == EMPTY) {
+      unsigned long long old = SYSTEM
+          ? atomicCAS_system((unsigned long long*)(keys + s), (unsigned long long)EMPTY, (unsigned long long)key)
+          : atomicCAS((unsigned long long*)(keys + s), (unsigned long long)EMPTY, (unsigned long long)key);
+      if (old == EMPTY || old == key) return s;
+    }
+    s = (s + 1) & mask;
+  }
+  return cap;
+}
+
+__device__ __forceinline__ uint64_t find_slot(const uint64_t* keys, uint64_t cap, uint64_t key) {
+  uint64_t mask = cap - 1;
+  uint64_t s = mix64(key) & mask;
+  for (uint64_t probes = 0; probes < cap; ++probes) {
+    uint64_t k = keys[s];
+    if (k == key) return s;
+    if (k == EMPTY) return cap;
+    s = (s + 1) & mask;
+  }
+  return cap;
+}
+
+__global__ void agg_init_kernel(uint64_t* keys, uint64_t cap, Lanes L) {
+  uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  uint64_t stride = (uint64_t)gridDim.x * blockDim.x;
+  for (; i < cap; i += stride) {
+    keys[i] = EMPTY;
+    for (int l = 0; l < L.nlanes; ++l) L.tbl[l][i] = identity_of(L.op[l]);
+  }
+}
+
+__global__ void __launch_bounds__(256) agg_update_kernel(uint64_t* keys, uint64_t cap, Lanes L,
+                                                         const uint64_t* __restrict__ in_keys,
+                                                         int64_t n, int combine, int32_t* status) {
+  int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  int64_t stride = (int64_t)gridDim.x * blockDim.x;
+  for (; i < n; i += stride) {
+    uint64_t key = in_keys[i];
+    uint64_t s = find_or_insert<false>(keys, cap, key);
+    if (s == cap) { atomicMax(status, 1); continue; }
+    for (int l = 0; l < L.nlanes; ++l) {
+      int64_t v = L.in[l] ? L.in[l][i] : 1;
+      apply<false>(L.op[l], L.tbl[l] + s, v, combine != 0, status);
+    }
+  }
+}
+
+// K6+C2 fused: fold every local partial into the owner rank's table over NVLink.
+__global__ void __launch_bounds__(256) agg_merge_peers_kernel(const uint64_t* __restrict__ keys,
+                                                              uint64_t cap, Lanes L, PeerTables T,
+                                                              int32_t* status) {
+  uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  uint64_t stride = (uint64_t)gridDim.x * blockDim.x;
+  for (; i < cap; i += stride) {
+    uint64_t key = keys[i];
+    if (key == EMPTY) continue;
+    int owner = (int)hash_bucket(key, (uint32_t)T.world);
+    uint64_t s = find_or_insert<true>(T.keys[owner], T.cap, key);
+    if (s == T.cap) { atomicMax(status, 1); continue; }
+    for (int l = 0; l < L.nlanes; ++l)
+      apply<true>(L.op[l], T.lanes[owner][l] + s, L.tbl[l][i], true, status);
+  }
+}
+
+__global__ void __launch_bounds__(256) agg_extract_kernel(const uint64_t* __restrict__ keys,
+                                                          uint64_t cap, Lanes L,
+                                                          uint64_t* __restrict__ out_keys,
+                                                          int64_t* const* __restrict__ out_lanes,
+                                                          unsigned long long* __restrict__ out_count,
+                                                          int64_t out_cap) {
+  uint64_t base0 = ((uint64_t)blockIdx.x * blockDim.x + threadIdx.x) & ~31ull;
+  uint64_t stride = (uint64_t)gridDim.x * blockDim.x;
+  for (uint64_t base = base0; base < cap; base += stride) {
+    uint64_t i = base + lane_id();
+    uint64_t key = (i < cap) ? keys[i] : EMPTY;
+    bool occ = key != EMPTY;
+    uint32_t m = __ballot_sync(0xffffffffu, occ);
+    if (!m) continue;
+    unsigned long long pos = 0;
+    if (lane_id() == 0) pos = atomicAdd(out_count, (unsigned long long)__popc(m));
+    pos = __shfl_sync(0xffffffffu, pos, 0);
+    if (occ) {
+      int64_t o = (int64_t)pos + __popc(m & lanemask_lt());
+      if (o < out_cap) {
+        out_keys[o] = key;
+        for (int l = 0; l < L.nlanes; ++l) out_lanes[l][o] = L.tbl[l][i];
+      }
+    }
+  }
+}
+
+// ---- K8 hash join (multimap: head[slot] -> row chain) ---------------------------------------
+__global__ void join_init_kernel(uint64_t* keys, int32_t* head, uint64_t cap) {
+  uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  uint64_t stride = (uint64_t)gridDim.x * blockDim.x;
+  for (; i < cap; i += stride) { keys[i] = EMPTY; head[i] = -1; }
+}
+
+__global__ void join_build_kernel(uint64_t* keys, int32_t* head, uint64_t cap,
+                                  const uint64_t* __restrict__ build_keys, int32_t* next, int64_t n,
+                                  int32_t* status) {
+  int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  int64_t stride = (int64_t)gridDim.x * blockDim.x;
+  for (; i < n; i += stride) {
+    uint64_t s = find_or_insert<false>(keys, cap, build_keys[i]);
+    if (s == cap) { atomicMax(status, 1); continue; }
+    next[i] = atomicExch(&head[s], (int32_t)i);
+  }
+}
+
+// mode 0: count matches per probe row; mode 1: emit (probe, build) index pairs at offsets[i].
+__global__ void join_probe_kernel(const uint64_t* __restrict__ keys, const int32_t* __restrict__ head,
+                                  uint64_t cap, const int32_t* __restrict__ next,
+                                  const uint64_t* __restrict__ probe_keys, int64_t n, int mode,
+                                  int64_t* __restrict__ counts_or_offsets,
+                                  int32_t* __restrict__ out_probe, int32_t* __restrict__ out_build) {
+  int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  int64_t stride = (int64_t)gridDim.x * blockDim.x;
+  for (; i < n; i += stride) {
+    uint64_t s = find_slot(keys, cap, probe_keys[i]);
+    if (mode == 0) {
+      int64_t c = 0;
+      if (s != cap) for (int32_t j = head[s]; j >= 0; j = next[j]) ++c;
+      counts_or_offsets[i] = c;
+    } else if (s != cap) {
+      int64_t o = counts_or_offsets[i];
+      for (int32_t j = head[s]; j >= 0; j = next[j]) { out_probe[o] = (int32_t)i; out_build[o] = j; ++o; }
+    }
+  }
+}
+
+// Set membership: out[i] = 1 if probe key is present.
+__global__ void set_contains_kernel(const uint64_t* __restrict__ keys, uint64_t cap,
+                                    const uint64_t* __restrict__ probe_keys, int64_t n,
+                                    uint8_t* __restrict__ out) {
+  int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  int64_t stride = (int64_t)gridDim.x * blockDim.x;
+  for (; i < n; i += stride) out[i] = find_slot(keys, cap, probe_keys[i]) != cap;
+}
+
+// Distinct that keeps the FIRST occurrence index per key (deterministic): lane 0 = MIN index.
+static inline int grid_for(int64_t n) {
+  int64_t g = (n + 256 * 4 - 1) / (256 * 4);
+  if (g < 1) g = 1;
+  if (g > 148 * 16) g = 148 * 16;
+  return (int)g;
+}
+
+static int fill_lanes(Lanes& L, int nlanes, const int* ops, int64_t* const* tbl,
+                      const int64_t* const* in) {
+  if (nlanes < 0 || nlanes > DRYAD_MAX_LANES) return DRYAD_ERR_BAD_ARG;
+  L.nlanes = nlanes;
+  for (int l = 0; l < nlanes; ++l) {
+    if (ops[l] < 0 || ops[l] > DRYAD_AGG_MAX_F64) return DRYAD_ERR_BAD_ARG;
+    L.op[l] = ops[l];
+    L.tbl[l] = tbl ? tbl[l] : nullptr;
+    L.in[l] = in ? in[l] : nullptr;
+  }
+  return DRYAD_OK;
+}
+
+static inline bool pow2(uint64_t x) { return x && !(x & (x - 1)); }
+
+}}  // namespace dryad::ht
+
+extern "C" {
+using namespace dryad::ht;
+
+int dryad_hash_agg_init(uint64_t* tbl_keys, uint64_t cap, int nlanes, const int* ops,
+                        int64_t* const* tbl_lanes, void* stream) {
+  if (!pow2(cap)) return DRYAD_ERR_BAD_ARG;
+  Lanes L; int rc = fill_lanes(L, nlanes, ops, tbl_lanes, nullptr); if (rc) return rc;
+  agg_init_kernel<<<grid_for((int64_t)cap), 256, 0, (cudaStream_t)stream>>>(tbl_keys, cap, L);
+  DRYAD_LAUNCH_CHECK();
+  return DRYAD_OK;
+}
+
+int dryad_hash_agg_update(uint64_t* tbl_keys, uint64_t cap, int nlanes, const int* ops,
+                          int64_t* const* tbl_lanes, const uint64_t* in_keys,
+                          const int64_t* const* in_lanes, int64_t n, int combine, int32_t* status,
+                          void* stream) {
+  if (!pow2(cap)) return DRYAD_ERR_BAD_ARG;
+  if (n <= 0) return DRYAD_OK;
+  Lanes L; int rc = fill_lanes(L, nlanes, ops, tbl_lanes, in_lanes); if (rc) return rc;
+  agg_update_kernel<<<grid_for(n), 256, 0, (cudaStream_t)stream>>>(tbl_keys, cap, L, in_keys, n, combine, status);
+  DRYAD_LAUNCH_CHECK();
+  return DRYAD_OK;
+}
+
+int dryad_hash_agg_merge_peers(const uint64_t* tbl_keys, uint64_t cap, int nlanes, const int* ops,
+                               int64_t* const* tbl_lanes, int world, uint64_t* const* peer_keys,
+                               int64_t* const* peer_lanes /* [world][nlanes] */, uint64_t peer_cap,
+                               int32_t* status, void* stream) {
+  if (!pow2(cap) || !pow2(peer_cap) || world < 1 || world > DRYAD_MAX_PEERS) return DRYAD_ERR_BAD_ARG;
+  Lanes L; int rc = fill_lanes(L, nlanes, ops, tbl_lanes, nullptr); if (rc) return rc;
+  PeerTables T; T.world = world; T.cap = peer_cap;
+  for (int r = 0; r < world; ++r) {
+    T.keys[r] = peer_keys[r];
+    for (int l = 0; l < nlanes; ++l) T.lanes[r][l] = peer_lanes[r * nlanes + l];
+  }
+  agg_merge_peers_kernel<<<grid_for((int64_t)cap), 256, 0, (cudaStream_t)stream>>>(tbl_keys, cap, L, T, status);
+  DRYAD_LAUNCH_CHECK();
+  return DRYAD_OK;
+}
+
+int dryad_hash_agg_extract(const uint64_t* tbl_keys, uint64_t cap, int nlanes, const int* ops,
+                           int64_t* const* tbl_lanes, uint64_t* out_keys,
+                           int64_t* const* out_lanes_dev, unsigned long long* out_count,
+                           int64_t out_cap, void* stream) {
+  if (!pow2(cap)) return DRYAD_ERR_BAD_ARG;
+  Lanes L; int rc = fill_lanes(L, nlanes, ops, tbl_lanes, nullptr); if (rc) return rc;
+  agg_extract_kernel<<<grid_for((int64_t)cap), 256, 0, (cudaStream_t)stream>>>(tbl_keys, cap, L, out_keys, out_lanes_dev, out_count, out_cap);
+  DRYAD_LAUNCH_CHECK();
+  return DRYAD_OK;
+}
+
+int dryad_join_build(uint64_t* tbl_keys, int32_t* head, uint64_t cap, const uint64_t* build_keys,
+                     int32_t* next, int64_t n, int32_t* status, void* stream) {
+  if (!pow2(cap) || n >= (1ll << 31)) return DRYAD_ERR_BAD_ARG;
+  cudaStream_t st = (cudaStream_t)stream;
+  join_init_kernel<<<grid_for((int64_t)cap), 256, 0, st>>>(tbl_keys, head, cap);
+  DRYAD_LAUNCH_CHECK();
+  if (n > 0) {
+    join_build_kernel<<<grid_for(n), 256, 0, st>>>(tbl_keys, head, cap, build_keys, next, n, status);
+    DRYAD_LAUNCH_CHECK();
+  }
+  return DRYAD_OK;
+}
+
+int dryad_join_probe(const uint64_t* tbl_keys, const int32_t* head, uint64_t cap,
+                     const int32_t* next, const uint64_t* probe_keys, int64_t n, int mode,
+                     int64_t* counts_or_offsets, int32_t* out_probe, int32_t* out_build,
+                     void* stream) {
+  if (!pow2(cap)) return DRYAD_ERR_BAD_ARG;
+  if (n <= 0) return DRYAD_OK;
+  join_probe_kernel<<<grid_for(n), 256, 0, (cudaStream_t)stream>>>(tbl_keys, head, cap, next, probe_keys, n, mode, counts_or_offsets, out_probe, out_build);
+  DRYAD_LAUNCH_CHECK();
+  return DRYAD_OK;
+}
+
+int dryad_set_contains(const uint64_t* tbl_keys, uint64_t cap, const uint64_t* probe_keys,
+                       int64_t n, uint8_t* out, void* stream) {
+  if (!pow2(cap)) return DRYAD_ERR_BAD_ARG;
+  if (n <= 0) return DRYAD_OK;
+  set_contains_kernel<<<grid_for(n), 256, 0, (cudaStream_t)stream>>>(tbl_keys, cap, probe_keys, n, out);
+  DRYAD_LAUNCH_CHECK();
+  return DRYAD_OK;
+}
+
+}  // extern "C"

@@ -1,0 +1,416 @@
+// K1 + K2 + C1: fused partition-and-scatter ("shuffle") over NVLink peer memory.
+//
+// Reference behaviour being replaced: every HashPartition / RangePartition vertex computes a
+// port per record — (hash & 0x7FFFFFFF) % nPorts (LinqToDryad/DryadLinqVertex.cs:4798-4907) or
+// a left-most binary search in the separator keys (DryadLinqVertex.cs:4911-5151,
+// DryadLinqUtil.cs:112-139) — and writes the record to one file per consumer; consumers fetch
+// P×Q files over HTTP after the producer finished (GraphBuilder.cs:481-504,
+// HttpScheduler.cs:65-91).  Here the bucket computation and the all-to-all are one kernel chain
+// with no NCCL call and no host round trip:
+//
+//   sh_count   : per-block histogram of destination partitions.
+//   sh_publish : scan over blocks; writes this rank's per-partition totals into EVERY rank's
+//                count matrix with P2P stores and raises a release.sys flag per peer.
+//   sh_scatter : waits (acquire.sys) for all ranks' totals, derives the exact, stable write
+//                offset of every record, groups each tile by destination in shared memory and
+//                stores contiguous, 16-byte aligned runs straight into the destination
+//                partition buffers — which live in peer GPUs' HBM.
+//   sh_barrier : epoch-numbered signal/wait across ranks so consumers may read.
+//
+// Offsets are exact (count → scan → write), so receive buffers are used densely, the result is
+// deterministic and stable (source rank, then source order), and skew can only fail loudly
+// (status = overflow) instead of corrupting memory.
+#include "common.cuh"
+#include "../../include/dryad_b200.h"
+
+namespace dryad { namespace sh {
+
+constexpr int THREADS = 256;
+constexpr int TILE = 256;
+constexpr int WARPS = THREADS / 32;
+constexpr int MAX_PARTS = 256;
+constexpr int MAX_COLS = 8;
+constexpr long long SPIN_CYCLES = 20000000000ll;  // ~10 s at 2 GHz: protocol failure, not a hang
+
+struct Params {
+  int ncols, nparts, mode, key_col, key_kind, key_off, emit_key, rank, world;
+  int nblocks, tiles_per_block;
+  int64_t n;
+  const unsigned char* src[MAX_COLS];
+  uint32_t width[MAX_COLS];
+  void* const* dst_table;
+  uint64_t* const* dst_key_table;
+  const uint64_t* separators;
+  const int64_t* capacity;
+  int64_t* counts_local;
+  int64_t* const* counts_peers;
+  uint64_t* flags_local;
+  uint64_t* const* flags_peers;
+  uint64_t epoch;
+  uint32_t* block_counts;  // [nparts][nblocks]
+  int32_t* status;
+  int max_width;
+};
+
+__device__ __forceinline__ uint64_t load_key(const Params& P, int64_t row) {
+  const unsigned char* base = P.src[P.key_col] + (size_t)row * P.width[P.key_col];
+  if (P.key_kind == 0) return *reinterpret_cast<const uint64_t*>(base);
+  const unsigned char* k = base + P.key_off;
+  uint64_t v = 0;
+#pragma unroll
+  for (int i = 0; i < 8; ++i) v = (v << 8) | (uint64_t)k[i];
+  return v;
+}
+
+__device__ __forceinline__ uint64_t key_from_smem(const Params& P, const unsigned char* row) {
+  if (P.key_kind == 0) return *reinterpret_cast<const uint64_t*>(row);
+  const unsigned char* k = row + P.key_off;
+  uint64_t v = 0;
+#pragma unroll
+  for (int i = 0; i < 8; ++i) v = (v << 8) | (uint64_t)k[i];
+  return v;
+}
+
+// Destination partition of a key.  `seps` points at shared memory (nparts-1 separators).
+__device__ __forceinline__ uint32_t part_of(uint64_t key, int mode, int nparts,
+                                            const uint64_t* seps) {
+  if (mode == DRYAD_PART_HASH) return hash_bucket(key, (uint32_t)nparts);
+  if (mode == DRYAD_PART_DIRECT) return (uint32_t)(key % (uint64_t)nparts);
+  // Left-most rule: ascending -> #separators strictly below key; descending -> strictly above.
+  int lo = 0, hi = nparts - 1;
+  const bool desc = (mode == DRYAD_PART_RANGE_DESC);
+  while (lo < hi) {
+    int mid = (lo + hi) >> 1;
+    uint64_t s = seps[mid];
+    bool go_right = desc ? (s > key) : (s < key);
+    if (go_right) lo = mid + 1; else hi = mid;
+  }
+  return (uint32_t)lo;
+}
+
+__global__ void __launch_bounds__(THREADS) sh_count(Params P) {
+  __shared__ uint32_t s_cnt[MAX_PARTS];
+  __shared__ uint64_t s_seps[MAX_PARTS];
+  const int tid = threadIdx.x;
+  for (int i = tid; i < P.nparts; i += THREADS) s_cnt[i] = 0;
+  if (P.mode == DRYAD_PART_RANGE_ASC || P.mode == DRYAD_PART_RANGE_DESC)
+    for (int i = tid; i < P.nparts - 1; i += THREADS) s_seps[i] = P.separators[i];
+  __syncthreads();
+  int64_t row0 = (int64_t)blockIdx.x * P.tiles_per_block * TILE;
+  int64_t row1 = min(P.n, row0 + (int64_t)P.tiles_per_block * TILE);
+  for (int64_t r0 = row0; r0 < row1; r0 += THREADS) {
+    const int64_t r = r0 + tid;
+    const bool in = r < row1;
+    const uint32_t amask = __ballot_sync(0xffffffffu, in);
+    if (in) {
+      uint32_t p = part_of(load_key(P, r), P.mode, P.nparts, s_seps);
+      uint32_t peers = __match_any_sync(amask, p);
+      if ((peers >> lane_id()) <= 1u) atomicAdd(&s_cnt[p], (uint32_t)__popc(peers));
+    }
+  }
+  __syncthreads();
+  for (int i = tid; i < P.nparts; i += THREADS)
+    P.block_counts[(size_t)i * P.nblocks + blockIdx.x] = s_cnt[i];
+}
+
+// One block.  Thread p scans partition p's counts over blocks, then publishes totals to peers.
+__global__ void __launch_bounds__(MAX_PARTS) sh_publish(Params P) {
+  const int p = threadIdx.x;
+  if (p < P.nparts) {
+    uint32_t* row = P.block_counts + (size_t)p * P.nblocks;
+    uint64_t sum = 0;
+    for (int b = 0; b < P.nblocks; ++b) { uint32_t c = row[b]; row[b] = (uint32_t)sum; sum += c; }
+    for (int r = 0; r < P.world; ++r)
+      P.counts_peers[r][(size_t)P.rank * P.nparts + p] = (int64_t)sum;
+  }
+  __threadfence_system();
+  __syncthreads();
+  if (p < P.world) st_release_sys(&P.flags_peers[p][P.rank], P.epoch);
+}
+
+__global__ void __launch_bounds__(THREADS) sh_scatter(Params P) {
+  extern __shared__ __align__(16) unsigned char smem[];
+  // layout: in[TILE*maxw] | out[TILE*maxw + 32*nparts + 16] | small arrays
+  const int maxw = P.max_width;
+  unsigned char* s_in = smem;
+  unsigned char* s_out = s_in + (size_t)TILE * maxw;
+  size_t out_bytes = (size_t)TILE * maxw + 32 * (size_t)P.nparts + 16;
+  uint64_t* s_seps = reinterpret_cast<uint64_t*>(s_out + out_bytes);        // [MAX_PARTS]
+  int64_t* s_gbase = reinterpret_cast<int64_t*>(s_seps + MAX_PARTS);        // [MAX_PARTS] rows
+  uint32_t* s_wcnt = reinterpret_cast<uint32_t*>(s_gbase + MAX_PARTS);      // [WARPS][MAX_PARTS]
+  uint32_t* s_tcnt = s_wcnt + WARPS * MAX_PARTS;                            // [MAX_PARTS]
+  uint32_t* s_tstart = s_tcnt + MAX_PARTS;                                  // [MAX_PARTS+1] rows
+  uint32_t* s_ustart = s_tstart + MAX_PARTS + 1;                            // [MAX_PARTS+1] 16B units
+  uint32_t* s_uoff = s_ustart + MAX_PARTS + 1;                              // [MAX_PARTS] byte offset of run in s_out
+  __shared__ int s_abort;
+
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const int np = P.nparts;
+
+  // Wait for every rank's totals, then derive this (rank, block)'s base row in each partition.
+  if (tid == 0) s_abort = 0;
+  __syncthreads();
+  if (tid < P.world) {
+    if (!spin_until_ge(&P.flags_local[tid], P.epoch, SPIN_CYCLES)) { s_abort = 2; }
+  }
+  __syncthreads();
+  if (s_abort) { if (tid == 0) atomicMax(P.status, 2); return; }
+  for (int p = tid; p < np; p += THREADS) {
+    int64_t before = 0, total = 0;
+    for (int r = 0; r < P.world; ++r) {
+      int64_t c = reinterpret_cast<const volatile int64_t*>(P.counts_local)[(size_t)r * np + p];
+      if (r < P.rank) before += c;
+      total += c;
+    }
+    if (total > P.capacity[p]) s_abort = 1;
+    s_gbase[p] = before + (int64_t)P.block_counts[(size_t)p * P.nblocks + blockIdx.x];
+  }
+  if (P.mode == DRYAD_PART_RANGE_ASC || P.mode == DRYAD_PART_RANGE_DESC)
+    for (int i = tid; i < np - 1; i += THREADS) s_seps[i] = P.separators[i];
+  __syncthreads();
+  if (s_abort) { if (tid == 0) atomicMax(P.status, 1); return; }
+
+  const int kc = P.key_col;
+  const uint32_t kw = P.width[kc];
+  const int total_cols = P.ncols + (P.emit_key ? 1 : 0);
+
+  for (int t = 0; t < P.tiles_per_block; ++t) {
+    int64_t row0 = ((int64_t)blockIdx.x * P.tiles_per_block + t) * TILE;
+    if (row0 >= P.n) break;
+    const int valid = (int)min((int64_t)TILE, P.n - row0);
+
+    // --- stage the key column, compute destination + stable rank ------------------------------
+    {
+      const unsigned char* g = P.src[kc] + (size_t)row0 * kw;
+      const int words = valid * (int)(kw / 4);
+      const uint32_t* g4 = reinterpret_cast<const uint32_t*>(g);
+      uint32_t* s4 = reinterpret_cast<uint32_t*>(s_in);
+      if ((reinterpret_cast<uintptr_t>(g) & 15) == 0) {
+        const int v16 = words / 4;
+        const uint4* g16 = reinterpret_cast<const uint4*>(g);
+        uint4* s16 = reinterpret_cast<uint4*>(s_in);
+        for (int i = tid; i < v16; i += THREADS) s16[i] = ld_stream_v4(g16 + i);
+        for (int i = v16 * 4 + tid; i < words; i += THREADS) s4[i] = g4[i];
+      } else {
+        for (int i = tid; i < words; i += THREADS) s4[i] = g4[i];
+      }
+    }
+    for (int i = tid; i < WARPS * np; i += THREADS) s_wcnt[i] = 0;
+    __syncthreads();
+
+    uint64_t key = 0; uint32_t part = 0, rank = 0;
+    const bool active = tid < valid;
+    if (active) {
+      key = key_from_smem(P, s_in + (size_t)tid * kw);
+      part = part_of(key, P.mode, np, s_seps);
+    }
+    {
+      uint32_t amask = __ballot_sync(0xffffffffu, active);
+      if (active) {
+        uint32_t peers = __match_any_sync(amask, part);
+        rank = __popc(peers & lanemask_lt());
+        if ((peers >> lane) <= 1u) s_wcnt[warp * np + part] = __popc(peers);
+      }
+    }
+    __syncthreads();
+    // per partition: exclusive scan over warps + tile count
+    for (int p = tid; p < np; p += THREADS) {
+      uint32_t sum = 0;
+#pragma unroll
+      for (int w = 0; w < WARPS; ++w) { uint32_t c = s_wcnt[w * np + p]; s_wcnt[w * np + p] = sum; sum += c; }
+      s_tcnt[p] = sum;
+    }
+    __syncthreads();
+    if (tid == 0) {  // np <= 256: a serial scan is cheap next to the tile's 25 KB of traffic
+      uint32_t acc = 0;
+      for (int p = 0; p < np; ++p) { s_tstart[p] = acc; acc += s_tcnt[p]; }
+      s_tstart[np] = acc;
+    }
+    __syncthreads();
+    if (active) rank += s_tstart[part] + s_wcnt[warp * np + part];  // tile-sorted row index
+    const uint32_t rank_in_part = active ? rank - s_tstart[part] : 0;
+
+    // --- per column: group by destination in shared memory, then aligned run stores ---------
+    for (int ci = 0; ci < total_cols; ++ci) {
+      // key column first (it is already staged), then the others, then the derived-key output
+      const bool is_key_out = (ci == P.ncols);
+      const int c = is_key_out ? P.ncols : (ci == 0 ? kc : (ci <= kc ? ci - 1 : ci));
+      const uint32_t w = is_key_out ? 8u : P.width[c];
+      if (ci > 0) __syncthreads();  // previous column's run stores are done with s_out/s_u*
+      // unit layout for this column: run p starts at a shared offset congruent to its global
+      // destination address mod 16, in its own 16-byte units.
+      if (tid == 0) {
+        uint32_t unit = 0;
+        for (int p = 0; p < np; ++p) {
+          s_ustart[p] = unit;
+          uint32_t cnt = s_tcnt[p];
+          if (cnt == 0) { s_uoff[p] = unit * 16; continue; }
+          unsigned char* dbase = is_key_out ? reinterpret_cast<unsigned char*>(P.dst_key_table[p])
+                                            : reinterpret_cast<unsigned char*>(P.dst_table[(size_t)c * np + p]);
+          uintptr_t a = reinterpret_cast<uintptr_t>(dbase) + (uintptr_t)s_gbase[p] * w;
+          uint32_t mis = (uint32_t)(a & 15);
+          s_uoff[p] = unit * 16 + mis;
+          unit += (mis + cnt * w + 15) / 16;
+        }
+        s_ustart[np] = unit;
+      }
+      if (!is_key_out && ci > 0) {
+        const unsigned char* g = P.src[c] + (size_t)row0 * w;
+        const int words = valid * (int)(w / 4);
+        const uint32_t* g4 = reinterpret_cast<const uint32_t*>(g);
+        uint32_t* s4 = reinterpret_cast<uint32_t*>(s_in);
+        if ((reinterpret_cast<uintptr_t>(g) & 15) == 0) {
+          const int v16 = words / 4;
+          const uint4* g16 = reinterpret_cast<const uint4*>(g);
+          uint4* s16 = reinterpret_cast<uint4*>(s_in);
+          for (int i = tid; i < v16; i += THREADS) s16[i] = ld_stream_v4(g16 + i);
+          for (int i = v16 * 4 + tid; i < words; i += THREADS) s4[i] = g4[i];
+        } else {
+          for (int i = tid; i < words; i += THREADS) s4[i] = g4[i];
+        }
+      }
+      __syncthreads();
+      // permute rows into destination-grouped order
+      if (active) {
+        uint32_t* d = reinterpret_cast<uint32_t*>(s_out + s_uoff[part] + (size_t)rank_in_part * w);
+        if (is_key_out) {
+          d[0] = (uint32_t)key; d[1] = (uint32_t)(key >> 32);
+        } else {
+          const uint32_t* s = reinterpret_cast<const uint32_t*>(s_in + (size_t)tid * w);
+          const int ww = (int)(w / 4);
+          for (int k = 0; k < ww; ++k) d[k] = s[k];
+        }
+      }
+      __syncthreads();
+      // write out: every 16-byte unit belongs to exactly one run
+      const uint32_t units = s_ustart[np];
+      for (uint32_t u = tid; u < units; u += THREADS) {
+        int lo = 0, hi = np - 1;  // last p with s_ustart[p] <= u and non-empty
+        while (lo < hi) { int mid = (lo + hi + 1) >> 1; if (s_ustart[mid] <= u) lo = mid; else hi = mid - 1; }
+        int p = lo;
+        // skip empty partitions sharing the same unit start
+        while (p > 0 && s_tcnt[p] == 0) --p;
+        if (s_tcnt[p] == 0) continue;
+        unsigned char* dbase = is_key_out ? reinterpret_cast<unsigned char*>(P.dst_key_table[p])
+                                          : reinterpret_cast<unsigned char*>(P.dst_table[(size_t)c * np + p]);
+        const uint32_t run_s = s_uoff[p];                    // shared byte offset of run start
+        const uint32_t run_e = run_s + s_tcnt[p] * w;        // exclusive
+        uintptr_t ga = reinterpret_cast<uintptr_t>(dbase) + (uintptr_t)s_gbase[p] * w;  // global addr of run start
+        const uint32_t ub = u * 16;                          // shared byte offset of this unit
+        uintptr_t gu = ga + (intptr_t)ub - (intptr_t)run_s;  // global addr matching the unit start
+        if (ub >= run_s && ub + 16 <= run_e) {
+          *reinterpret_cast<uint4*>(gu) = *reinterpret_cast<const uint4*>(s_out + ub);
+        } else {
+#pragma unroll
+          for (int k = 0; k < 4; ++k) {
+            uint32_t b = ub + 4 * k;
+            if (b >= run_s && b < run_e)
+              *reinterpret_cast<uint32_t*>(gu + 4 * k) = *reinterpret_cast<const uint32_t*>(s_out + b);
+          }
+        }
+      }
+    }
+    __syncthreads();
+    for (int p = tid; p < np; p += THREADS) s_gbase[p] += s_tcnt[p];
+    __syncthreads();
+  }
+  __threadfence_system();
+}
+
+// Epoch barrier across ranks: every rank's prior stream work is complete and visible.
+__global__ void sh_barrier(uint64_t* const* flags_peers, uint64_t* flags_local, int rank,
+                           int world, int slot, uint64_t epoch, int32_t* status) {
+  int t = threadIdx.x;
+  __threadfence_system();
+  if (t < world) {
+    st_release_sys(&flags_peers[t][(size_t)slot * DRYAD_MAX_PEERS + rank], epoch);
+    if (!spin_until_ge(&flags_local[(size_t)slot * DRYAD_MAX_PEERS + t], epoch, SPIN_CYCLES))
+      atomicMax(status, 2);
+  }
+}
+
+static size_t scatter_smem(int maxw, int nparts) {
+  size_t b = (size_t)TILE * maxw;                       // in
+  b += (size_t)TILE * maxw + 32 * (size_t)nparts + 16;  // out
+  b += 8 * MAX_PARTS + 8 * MAX_PARTS;                   // seps, gbase
+  b += 4 * (WARPS * MAX_PARTS + MAX_PARTS + (MAX_PARTS + 1) * 2 + MAX_PARTS);
+  return (b + 15) & ~(size_t)15;
+}
+
+static int pick_blocks(int64_t n, int* tiles_per_block) {
+  int64_t tiles = (n + TILE - 1) / TILE;
+  if (tiles < 1) tiles = 1;
+  int64_t nb = tiles < 148 * 8 ? tiles : 148 * 8;
+  int64_t tpb = (tiles + nb - 1) / nb;
+  nb = (tiles + tpb - 1) / tpb;
+  *tiles_per_block = (int)tpb;
+  return (int)nb;
+}
+
+}}  // namespace dryad::sh
+
+extern "C" {
+
+size_t dryad_shuffle_scratch_bytes(int64_t n, int nparts) {
+  int tpb;
+  int nb = dryad::sh::pick_blocks(n, &tpb);
+  return (((size_t)nparts * nb * 4) + 255) & ~(size_t)255;
+}
+
+int dryad_shuffle_run(const DryadShuffleDesc* d, void* stream) {
+  using namespace dryad::sh;
+  cudaStream_t st = (cudaStream_t)stream;
+  if (!d || d->ncols < 1 || d->ncols > MAX_COLS || d->nparts < 1 || d->nparts > MAX_PARTS ||
+      d->world < 1 || d->world > DRYAD_MAX_PEERS || d->rank < 0 || d->rank >= d->world || d->n < 0)
+    return DRYAD_ERR_BAD_ARG;
+  Params P;
+  P.ncols = d->ncols; P.nparts = d->nparts; P.mode = d->mode; P.key_col = d->key_col;
+  P.key_kind = d->key_kind; P.key_off = d->key_off; P.emit_key = d->emit_key;
+  P.rank = d->rank; P.world = d->world; P.n = d->n;
+  int maxw = d->emit_key ? 8 : 0;
+  for (int c = 0; c < d->ncols; ++c) {
+    if (d->width[c] == 0 || (d->width[c] & 3) || d->width[c] > 512) return DRYAD_ERR_BAD_ARG;
+    P.src[c] = (const unsigned char*)d->src[c];
+    P.width[c] = d->width[c];
+    if ((int)d->width[c] > maxw) maxw = (int)d->width[c];
+  }
+  if (d->key_col < 0 || d->key_col >= d->ncols) return DRYAD_ERR_BAD_ARG;
+  if (d->key_kind == 0 && d->width[d->key_col] != 8) return DRYAD_ERR_BAD_ARG;
+  if (d->key_kind == 1 && (d->key_off < 0 || d->key_off + 8 > (int)d->width[d->key_col]))
+    return DRYAD_ERR_BAD_ARG;
+  P.max_width = maxw;
+  P.dst_table = d->dst_table; P.dst_key_table = d->dst_key_table;
+  P.separators = d->separators; P.capacity = d->capacity;
+  P.counts_local = d->counts_local; P.counts_peers = d->counts_peers;
+  P.flags_local = d->flags_local; P.flags_peers = d->flags_peers; P.epoch = d->epoch;
+  P.status = d->status;
+  P.nblocks = pick_blocks(d->n, &P.tiles_per_block);
+  size_t need = (((size_t)P.nparts * P.nblocks * 4) + 255) & ~(size_t)255;
+  if (!d->scratch || d->scratch_bytes < need) return DRYAD_ERR_SCRATCH;
+  P.block_counts = (uint32_t*)d->scratch;
+
+  sh_count<<<P.nblocks, THREADS, 0, st>>>(P);
+  DRYAD_LAUNCH_CHECK();
+  sh_publish<<<1, MAX_PARTS, 0, st>>>(P);
+  DRYAD_LAUNCH_CHECK();
+  size_t smem = scatter_smem(maxw, P.nparts);
+  DRYAD_CUDA_TRY(cudaFuncSetAttribute(sh_scatter, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  sh_scatter<<<P.nblocks, THREADS, smem, st>>>(P);
+  DRYAD_LAUNCH_CHECK();
+  sh_barrier<<<1, 32, 0, st>>>(d->flags_peers, d->flags_local, d->rank, d->world, 1, d->epoch,
+                               d->status);
+  DRYAD_LAUNCH_CHECK();
+  return DRYAD_OK;
+}
+
+int dryad_signal_barrier(uint64_t* const* flags_peers, uint64_t* flags_local, int rank, int world,
+                         int slot, uint64_t epoch, int32_t* status, void* stream) {
+  if (world < 1 || world > DRYAD_MAX_PEERS || slot < 0 || slot >= DRYAD_FLAG_SLOTS)
+    return DRYAD_ERR_BAD_ARG;
+  dryad::sh::sh_barrier<<<1, 32, 0, (cudaStream_t)stream>>>(flags_peers, flags_local, rank, world,
+                                                            slot, epoch, status);
+  DRYAD_LAUNCH_CHECK();
+  return DRYAD_OK;
+}
+
+}  // extern "C"

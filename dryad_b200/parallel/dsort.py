@@ -1,0 +1,116 @@
+"""Distributed OrderBy over fixed-width rows: sample → separators → fused range shuffle → local
+radix sort → tie repair → payload gather.
+
+Mirrors the reference's OrderBy plan (LinqToDryad/DryadLinqQueryGen.cs:2362-2521): Phase1Sampling
+per partition, a single RangeSampler producing `pcount-1` separators that are broadcast to every
+distributor, RangePartition with CrossProduct edges into a Merge, then a per-partition Sort.
+Here the sampler output crosses GPUs as small P2P copies, the RangePartition+Merge is the fused
+shuffle kernel, and the sort is the one-sweep radix sort on (64-bit key prefix, row index) followed
+by one payload gather, so each 100-byte row crosses NVLink once and HBM three times.
+"""
+from __future__ import annotations
+
+from typing import Optional
+
+import torch
+
+from ..ops import core as K
+from .shuffle import ColSpec, FusedShuffle
+from .symm import SymmetricArena, tensor_from_ptr
+
+SAMPLE_RATE = 0.001          # DryadLinqSampler.SAMPLE_RATE (DryadLinqSampler.cs:38)
+MAX_SAMPLES = 1 << 20        # MAX_SECOND_PHASE_SAMPLES (DryadLinqSampler.cs:39)
+
+
+class RowSorter:
+    """Reusable distributed sorter for `[n, width]` uint8 rows keyed by `key_len` leading
+    big-endian bytes at `key_off` (key_len >= 8; bytes beyond 8 are resolved by tie repair)."""
+
+    def __init__(self, arena: SymmetricArena, max_rows: int, width: int, *, key_off: int = 0,
+                 key_len: int = 10, slack: float = 1.12, sample_rate: float = SAMPLE_RATE,
+                 descending: bool = False):
+        if key_len < 8:
+            raise ValueError("RowSorter needs at least 8 key bytes (pad shorter keys)")
+        self.arena, self.width, self.key_off, self.key_len = arena, width, key_off, key_len
+        self.descending = descending
+        self.world, self.rank = arena.world, arena.rank
+        self.max_rows = int(max_rows)
+        dev = arena.device
+        self.sample_rate = sample_rate
+        self.sample_cap = max(1024, min(MAX_SAMPLES // self.world, int(max_rows * sample_rate * 2) + 1024))
+        if self.world > 1:
+            self.cap_rows = int(max_rows * slack) + 4096
+            self.shuffle = FusedShuffle(arena, [ColSpec(width, torch.uint8, width)], self.cap_rows,
+                                        emit_key=True, max_rows_in=max_rows)
+            self.all_samples, self.all_samples_off = arena.alloc((self.world, self.sample_cap), torch.int64)
+            self.all_counts, self.all_counts_off = arena.alloc((self.world,), torch.int64)
+            self._peer_sample_views = []
+            self._peer_count_views = []
+            for r in range(self.world):
+                sp = tensor_from_ptr(arena.peer_ptr(r, self.all_samples_off + self.rank * self.sample_cap * 8),
+                                     self.sample_cap * 8, dev).view(torch.int64)
+                cp = tensor_from_ptr(arena.peer_ptr(r, self.all_counts_off + self.rank * 8), 8, dev).view(torch.int64)
+                self._peer_sample_views.append(sp)
+                self._peer_count_views.append(cp)
+        else:
+            self.cap_rows = self.max_rows
+            self.shuffle = None
+        n = self.cap_rows
+        self.keys_a = torch.empty(n, dtype=torch.int64, device=dev)
+        self.keys_b = torch.empty(n, dtype=torch.int64, device=dev)
+        self.idx_a = torch.empty(n, dtype=torch.int32, device=dev)
+        self.idx_b = torch.empty(n, dtype=torch.int32, device=dev)
+        self.out = torch.empty((n, width), dtype=torch.uint8, device=dev)
+        self.last_long_runs: Optional[torch.Tensor] = None
+
+    # -- separators ----------------------------------------------------------------------------
+    def _separators(self, rows: torch.Tensor) -> torch.Tensor:
+        samples, cnt = K.sample_rows(rows, self.key_off, seed=self.rank, rate=self.sample_rate,
+                                     cap=self.sample_cap)
+        cnt = torch.clamp(cnt, max=self.sample_cap)
+        # publish my samples + count into every rank's table (P2P copies), then barrier
+        for r in range(self.world):
+            self._peer_sample_views[r].copy_(samples, non_blocking=True)
+            self._peer_count_views[r].copy_(cnt, non_blocking=True)
+        self.arena.barrier(slot=2)
+        counts = self.all_counts.tolist()                      # host sync (tiny)
+        parts = [self.all_samples[r, :int(counts[r])] for r in range(self.world)]
+        allk = torch.cat(parts) if parts else samples[:0]
+        total = allk.numel()
+        skeys, _ = K.radix_sort_pairs(allk.contiguous(), None)   # ascending; the picker handles descending
+        return K.select_separators(skeys, total, self.world, self.descending)
+
+    # -- the sort ------------------------------------------------------------------------------
+    def sort(self, rows: torch.Tensor):
+        """rows: [n, width] uint8 on this rank.  Returns (sorted_rows_view, m): this rank's slice
+        of the global order (rank r holds keys between separators r-1 and r)."""
+        n = rows.shape[0]
+        if n > self.max_rows:
+            raise ValueError("RowSorter: more rows than the sorter was sized for")
+        if self.world > 1:
+            seps = self._separators(rows)
+            mode = "range_desc" if self.descending else "range_asc"
+            self.shuffle.run([rows], mode=mode, key_col=0, key_kind=1, key_off=self.key_off, separators=seps)
+            m = self.shuffle.received_rows()[0]               # host sync: sizes the local sort
+            src_rows = self.shuffle.recv[0][0]
+            keys = self.shuffle.recv_key[0][:m]
+            if self.descending:
+                keys = ~keys
+            # copy is avoided: the radix sort ping-pongs between the receive key buffer and keys_b
+            skeys, sidx = K.radix_sort_pairs(keys, self.idx_a[:m], iota=True, keys_alt=self.keys_b[:m],
+                                             vals_alt=self.idx_b[:m])
+        else:
+            m = n
+            src_rows = rows
+            K.extract_be64(rows, self.key_off, out=self.keys_a)
+            keys = self.keys_a[:m]
+            if self.descending:
+                keys = ~keys
+            skeys, sidx = K.radix_sort_pairs(keys, self.idx_a[:m], iota=True, keys_alt=self.keys_b[:m],
+                                             vals_alt=self.idx_b[:m])
+        if self.key_len > 8:
+            self.last_long_runs = K.fix_ties(skeys, sidx, src_rows, self.key_off + 8, self.key_len - 8,
+                                             descending=self.descending)
+        out = self.out[:m]
+        K.gather_rows(src_rows, sidx, out)
+        return out, m

@@ -1,0 +1,215 @@
+/* dryad_b200 — C ABI of the sm_100a kernel library (libdryad_kernels.so).
+ *
+ * Every entry point takes raw device pointers and a cudaStream_t (as void*), launches on that
+ * stream and returns 0 on success, a positive cudaError_t, or a negative DRYAD_ERR_* code.
+ * No entry point allocates device memory: callers pass outputs and, where a kernel needs
+ * working storage, a scratch buffer sized by the matching *_scratch_bytes() query.
+ *
+ * Each declaration cites the reference code whose behaviour it provides (paths relative to the
+ * Liuqin/Dryad tree).
+ */
+#ifndef DRYAD_B200_H
+#define DRYAD_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define DRYAD_MAX_PEERS_C 8
+#define DRYAD_FLAG_SLOTS 4      /* flags buffer = uint64[DRYAD_FLAG_SLOTS][8] per rank */
+#define DRYAD_MAX_LANES 8
+#define DRYAD_EXPR_MAX_INSTR 64
+#define DRYAD_EXPR_MAX_COLS 16
+
+enum {
+  DRYAD_OK = 0,
+  DRYAD_ERR_BAD_ARG = -1,
+  DRYAD_ERR_TOO_LARGE = -2,
+  DRYAD_ERR_OVERFLOW = -3,
+  DRYAD_ERR_SCRATCH = -4
+};
+
+/* ---- utility ------------------------------------------------------------------------------ */
+int dryad_device_count(void);
+const char* dryad_error_string(int code);
+int dryad_memcpy_async(void* dst, const void* src, size_t bytes, int kind, void* stream);
+int dryad_memset_async(void* dst, int value, size_t bytes, void* stream);
+
+/* ---- symmetric memory (peer-mapped HBM) ---------------------------------------------------
+ * Role of DryadVertex/VertexHost/system/channel (file/HTTP channels between vertices). */
+int dryad_symm_alloc(size_t bytes, void** out);
+int dryad_symm_free(void* p);
+int dryad_ipc_export(void* p, unsigned char handle64[64]);
+int dryad_ipc_open(const unsigned char handle64[64], void** out);
+int dryad_ipc_close(void* p);
+/* Epoch barrier over peer flags (slot < DRYAD_FLAG_SLOTS); status: 0 ok, 2 = peer timeout. */
+int dryad_signal_barrier(uint64_t* const* flags_peers, uint64_t* flags_local, int rank, int world,
+                         int slot, uint64_t epoch, int32_t* status, void* stream);
+
+/* ---- K14 key hashing: LinqToDryad/DryadLinqVertex.cs:4801, LinqToDryad/Hash64.cs ----------- */
+int dryad_hash_u64(const uint64_t* keys, uint64_t* out, int64_t n, void* stream);
+int dryad_hash_bytes(const uint8_t* bytes, const int64_t* offsets, uint64_t* out, int64_t n,
+                     void* stream);
+
+/* ---- K4 radix sort: LinqToDryad/DryadLinqVertex.cs:293-316, 9321-9818 ----------------------
+ * Sorts (key, u32 value) pairs on key bits [begin_bit, end_bit), ascending, stable.  Buffers
+ * ping-pong between x and x_alt; *result_in_alt tells where the result is.  vals may be NULL
+ * (keys only).  iota_vals != 0: values start as 0..n-1 and vals' initial content is ignored.
+ * n < 2^30. */
+size_t dryad_radix_sort_scratch_bytes(int64_t n, int begin_bit, int end_bit);
+int dryad_radix_sort_pairs_u64(uint64_t* keys, uint64_t* keys_alt, uint32_t* vals,
+                               uint32_t* vals_alt, int64_t n, int begin_bit, int end_bit,
+                               int iota_vals, void* scratch, size_t scratch_bytes,
+                               int* result_in_alt, void* stream);
+int dryad_radix_sort_pairs_u32(uint32_t* keys, uint32_t* keys_alt, uint32_t* vals,
+                               uint32_t* vals_alt, int64_t n, int begin_bit, int end_bit,
+                               int iota_vals, void* scratch, size_t scratch_bytes,
+                               int* result_in_alt, void* stream);
+
+/* ---- K1/K2 + C1 fused partition + all-to-all: LinqToDryad/DryadLinqVertex.cs:4788-5151,
+ *      DryadLinqGraphManager/GraphBuilder.cs:481-504 ------------------------------------------ */
+enum { DRYAD_PART_HASH = 0, DRYAD_PART_RANGE_ASC = 1, DRYAD_PART_RANGE_DESC = 2, DRYAD_PART_DIRECT = 3 };
+
+typedef struct DryadShuffleDesc {
+  int32_t ncols;           /* payload columns, 1..8 */
+  int32_t nparts;          /* destination partitions, 1..256 (each may live on any GPU) */
+  int32_t mode;            /* DRYAD_PART_* */
+  int32_t key_col;         /* column that carries the key */
+  int32_t key_kind;        /* 0: the column is a uint64 key; 1: 8 big-endian bytes at key_off */
+  int32_t key_off;
+  int32_t emit_key;        /* 1: also write the derived uint64 key to dst_key_table[part] */
+  int32_t rank, world;
+  int64_t n;               /* local rows */
+  const void* src[8];      /* local column bases (row-major, width[c] bytes per row) */
+  uint32_t width[8];       /* bytes per row, multiple of 4, <= 512 */
+  void* const* dst_table;          /* device array [ncols][nparts]: partition buffers (peer-mapped) */
+  uint64_t* const* dst_key_table;  /* device array [nparts] (emit_key) */
+  const uint64_t* separators;      /* device, nparts-1 keys (range modes) */
+  const int64_t* capacity;         /* device [nparts]: rows each partition buffer can hold */
+  int64_t* counts_local;           /* [world][nparts]: filled by all ranks; rows per (src, part) */
+  int64_t* const* counts_peers;    /* device array [world]: every rank's counts matrix */
+  uint64_t* flags_local;           /* uint64[DRYAD_FLAG_SLOTS][8] */
+  uint64_t* const* flags_peers;    /* device array [world] */
+  uint64_t epoch;                  /* strictly increasing per shuffle on this flag set */
+  void* scratch; size_t scratch_bytes;
+  int32_t* status;                 /* device: 0 ok, 1 capacity overflow, 2 peer timeout */
+} DryadShuffleDesc;
+
+size_t dryad_shuffle_scratch_bytes(int64_t n, int nparts);
+int dryad_shuffle_run(const DryadShuffleDesc* desc, void* stream);
+
+/* ---- K3 sampler + separators: LinqToDryad/DryadLinqSampler.cs:42-106, 139-246 -------------- */
+int dryad_sample_keys(const uint64_t* keys, int64_t n, uint64_t seed, double rate, uint64_t* out,
+                      unsigned long long* out_count, int64_t cap, void* stream);
+int dryad_sample_rows(const uint8_t* rows, int width, int key_off, int64_t n, uint64_t seed,
+                      double rate, uint64_t* out, unsigned long long* out_count, int64_t cap,
+                      void* stream);
+int dryad_select_separators(const uint64_t* sorted, int64_t cnt, int pcount, int descending,
+                            uint64_t* seps, void* stream);
+
+/* ---- row helpers for OrderBy on wide records ----------------------------------------------- */
+int dryad_extract_be64(const uint8_t* rows, int64_t n, int width, int key_off, uint64_t* out,
+                       void* stream);
+int dryad_fix_ties(const uint64_t* keys, uint32_t* idx, int64_t n, const uint8_t* rows, int width,
+                   int extra_off, int extra, int max_run, int descending, int32_t* long_runs,
+                   void* stream);
+int dryad_gather_rows(const void* in, const uint32_t* idx, void* out, int64_t n, int width,
+                      void* stream);
+int dryad_check_sorted_rows(const uint8_t* rows, int64_t n, int width, int key_off, int key_len,
+                            int descending, unsigned long long* result2, void* stream);
+
+/* ---- K6 + C2 hash aggregation: LinqToDryad/DryadLinqVertex.cs:5718-6416,
+ *      LinqToDryad/DryadLinqCollection.cs:519-722, LinqToDryad/DryadLinqQueryGen.cs:2179-2296 -- */
+enum {
+  DRYAD_AGG_COUNT = 0, DRYAD_AGG_SUM_I64 = 1, DRYAD_AGG_SUM_I64_CHECKED = 2, DRYAD_AGG_SUM_F64 = 3,
+  DRYAD_AGG_MIN_I64 = 4, DRYAD_AGG_MAX_I64 = 5, DRYAD_AGG_MIN_F64 = 6, DRYAD_AGG_MAX_F64 = 7
+};
+/* Table = keys[cap] (cap power of two; key ~0 is reserved) + nlanes int64/double lanes [cap].
+ * status: 1 table full, 3 checked-sum overflow. */
+int dryad_hash_agg_init(uint64_t* tbl_keys, uint64_t cap, int nlanes, const int* ops,
+                        int64_t* const* tbl_lanes, void* stream);
+int dryad_hash_agg_update(uint64_t* tbl_keys, uint64_t cap, int nlanes, const int* ops,
+                          int64_t* const* tbl_lanes, const uint64_t* in_keys,
+                          const int64_t* const* in_lanes, int64_t n, int combine, int32_t* status,
+                          void* stream);
+/* Fused reduce-scatter: fold local partials into the key owner's table (owner =
+ * hash_bucket(key, world)) with system-scope atomics on peer HBM. */
+int dryad_hash_agg_merge_peers(const uint64_t* tbl_keys, uint64_t cap, int nlanes, const int* ops,
+                               int64_t* const* tbl_lanes, int world, uint64_t* const* peer_keys,
+                               int64_t* const* peer_lanes, uint64_t peer_cap, int32_t* status,
+                               void* stream);
+int dryad_hash_agg_extract(const uint64_t* tbl_keys, uint64_t cap, int nlanes, const int* ops,
+                           int64_t* const* tbl_lanes, uint64_t* out_keys,
+                           int64_t* const* out_lanes_dev, unsigned long long* out_count,
+                           int64_t out_cap, void* stream);
+
+/* ---- K8 hash join / K10 hash sets: LinqToDryad/DryadLinqVertex.cs:775-1030, 6703-7315,
+ *      1239-1660 ----------------------------------------------------------------------------- */
+int dryad_join_build(uint64_t* tbl_keys, int32_t* head, uint64_t cap, const uint64_t* build_keys,
+                     int32_t* next, int64_t n, int32_t* status, void* stream);
+int dryad_join_probe(const uint64_t* tbl_keys, const int32_t* head, uint64_t cap,
+                     const int32_t* next, const uint64_t* probe_keys, int64_t n, int mode,
+                     int64_t* counts_or_offsets, int32_t* out_probe, int32_t* out_build,
+                     void* stream);
+int dryad_set_contains(const uint64_t* tbl_keys, uint64_t cap, const uint64_t* probe_keys,
+                       int64_t n, uint8_t* out, void* stream);
+
+/* ---- K12 fused elementwise programs + compaction: LinqToDryad/DryadLinqVertex.cs:74-198,
+ *      LinqToDryad/DryadLinqCodeGen.cs:2084-2138 ----------------------------------------------- */
+enum {
+  DRYAD_DT_I64 = 0, DRYAD_DT_F64 = 1, DRYAD_DT_I32 = 2, DRYAD_DT_F32 = 3, DRYAD_DT_U8 = 4,
+  DRYAD_DT_I16 = 5, DRYAD_DT_U32 = 6, DRYAD_DT_U16 = 7
+};
+enum {
+  DRYAD_OP_LOAD = 0, DRYAD_OP_CONST, DRYAD_OP_ROWID,
+  DRYAD_OP_ADD_I, DRYAD_OP_SUB_I, DRYAD_OP_MUL_I, DRYAD_OP_DIV_I, DRYAD_OP_MOD_I, DRYAD_OP_NEG_I,
+  DRYAD_OP_ADD_F, DRYAD_OP_SUB_F, DRYAD_OP_MUL_F, DRYAD_OP_DIV_F, DRYAD_OP_NEG_F,
+  DRYAD_OP_EQ_I, DRYAD_OP_NE_I, DRYAD_OP_LT_I, DRYAD_OP_LE_I, DRYAD_OP_GT_I, DRYAD_OP_GE_I,
+  DRYAD_OP_EQ_F, DRYAD_OP_NE_F, DRYAD_OP_LT_F, DRYAD_OP_LE_F, DRYAD_OP_GT_F, DRYAD_OP_GE_F,
+  DRYAD_OP_AND, DRYAD_OP_OR, DRYAD_OP_NOT, DRYAD_OP_BAND, DRYAD_OP_BOR, DRYAD_OP_BXOR,
+  DRYAD_OP_BNOT, DRYAD_OP_SHL, DRYAD_OP_SHR, DRYAD_OP_I2F, DRYAD_OP_F2I, DRYAD_OP_SELECT,
+  DRYAD_OP_HASH, DRYAD_OP_ABS_I, DRYAD_OP_ABS_F, DRYAD_OP_MIN_I, DRYAD_OP_MAX_I, DRYAD_OP_MIN_F,
+  DRYAD_OP_MAX_F, DRYAD_OP_SQRT_F, DRYAD_OP_FLOOR_F, DRYAD_OP_MOV, DRYAD_OP_STORE,
+  DRYAD_OP__COUNT
+};
+typedef struct DryadExprInstr { int32_t op, dst, a, b; int64_t imm; } DryadExprInstr;
+typedef struct DryadExprProgram {
+  int32_t ninstr, ncols_in, ncols_out, result_reg;
+  DryadExprInstr ins[DRYAD_EXPR_MAX_INSTR];
+  const void* in[DRYAD_EXPR_MAX_COLS];
+  int32_t in_dtype[DRYAD_EXPR_MAX_COLS];
+  void* out[DRYAD_EXPR_MAX_COLS];
+  int32_t out_dtype[DRYAD_EXPR_MAX_COLS];
+} DryadExprProgram;
+/* Runs the register program once per row; flags_out (optional) receives result_reg != 0. */
+int dryad_expr_run(const DryadExprProgram* prog, int64_t n, uint8_t* flags_out, void* stream);
+size_t dryad_compact_scratch_bytes(int64_t n);
+int dryad_compact_flags(const uint8_t* flags, int64_t n, uint32_t* out_idx, int64_t* count_dev,
+                        void* scratch, size_t scratch_bytes, void* stream);
+/* K16: exclusive scan of m counts into m+1 int64 offsets (LinqToDryad/DryadLinqEnumerable.cs:1131). */
+int dryad_exclusive_scan_u32(const uint32_t* in, int64_t m, int64_t* out_m_plus_1, void* stream);
+
+/* ---- K11 scalar aggregates: LinqToDryad/DryadLinqVertex.cs:1673-4704 ------------------------ */
+enum { DRYAD_RED_SUM = 0, DRYAD_RED_MIN = 1, DRYAD_RED_MAX = 2 };
+size_t dryad_reduce_scratch_bytes(void);
+int dryad_reduce(const void* col, int dtype, int64_t n, int op, void* out8, void* scratch,
+                 size_t scratch_bytes, void* stream);
+
+/* ---- K13 text tokenizer: LinqToDryad/DryadLinqTextReader.cs:36-280, samples/WordCount.cs.pp:72 */
+size_t dryad_tokenize_scratch_bytes(int64_t nbytes);
+int dryad_tokenize_count(const uint8_t* text, int64_t n, int delim, int keep_empty,
+                         int64_t* count_dev, void* scratch, size_t scratch_bytes, void* stream);
+int dryad_tokenize_write(const uint8_t* text, int64_t n, int delim, int keep_empty, int64_t* starts,
+                         int32_t* lens, uint64_t* hashes, void* scratch, size_t scratch_bytes,
+                         void* stream);
+int dryad_tokenize_verify(const uint8_t* text, const int64_t* starts, const int32_t* lens,
+                          const int64_t* rep_start, const int32_t* rep_len, int64_t ntok,
+                          unsigned long long* mismatches, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* DRYAD_B200_H */

@@ -1,0 +1,201 @@
+"""Numerics of every CUDA kernel against a plain PyTorch / Python reference of the same op."""
+import numpy as np
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def K():
+    from dryad_b200.ops import core
+    return core
+
+
+def _u64_sorted_ref(keys: torch.Tensor):
+    ku = keys.cpu().numpy().view(np.uint64)
+    order = np.argsort(ku, kind="stable")
+    return ku[order], order
+
+
+@pytest.mark.parametrize("n", [1, 1000, 6144, 6145, 200_000, 3_000_001])
+def test_radix_sort_u64_pairs(K, n):
+    g = torch.Generator(device="cuda").manual_seed(n)
+    keys = torch.randint(-2**63, 2**63 - 1, (n,), dtype=torch.int64, device="cuda", generator=g)
+    if n > 1000:
+        keys[::7] = keys[0]  # duplicates exercise stability
+    ref_k, ref_order = _u64_sorted_ref(keys)
+    sk, sv = K.radix_sort_pairs(keys.clone(), None, iota=True)
+    torch.cuda.synchronize()
+    assert np.array_equal(sk.cpu().numpy().view(np.uint64), ref_k)
+    assert np.array_equal(sv.cpu().numpy().view(np.uint32).astype(np.int64), ref_order)
+
+
+def test_radix_sort_u32_keys_only_and_bit_range(K):
+    n = 100_003
+    keys = torch.randint(0, 2**31 - 1, (n,), dtype=torch.int32, device="cuda")
+    sk, _ = K.radix_sort_pairs(keys.clone(), None)
+    assert torch.equal(sk, torch.sort(keys).values)
+    k64 = torch.randint(0, 2**40, (n,), dtype=torch.int64, device="cuda")
+    sk, sv = K.radix_sort_pairs(k64.clone(), None, iota=True, begin_bit=8, end_bit=24)
+    dig = (k64 >> 8) & 0xFFFF
+    ref = torch.sort(dig, stable=True)
+    assert torch.equal((sk >> 8) & 0xFFFF, ref.values)
+    assert torch.equal(sv.to(torch.int64), ref.indices)
+
+
+def test_hash_u64_matches_host(K):
+    from dryad_b200.utils.hashing import mix64_np
+    keys = torch.randint(-2**63, 2**63 - 1, (10_000,), dtype=torch.int64, device="cuda")
+    h = K.hash_u64(keys).cpu().numpy().view(np.uint64)
+    assert np.array_equal(h, mix64_np(keys.cpu().numpy().view(np.uint64)))
+
+
+def test_hash_bytes_matches_host(K):
+    from dryad_b200.utils.hashing import hash_bytes_py
+    words = [b"", b"a", b"hello", b"the quick brown fox", b"a" * 300]
+    data = torch.tensor(list(b"".join(words)), dtype=torch.uint8, device="cuda")
+    offs = torch.tensor(np.cumsum([0] + [len(w) for w in words]), dtype=torch.int64, device="cuda")
+    h = K.hash_bytes(data, offs).cpu().numpy().view(np.uint64)
+    assert [int(x) for x in h] == [hash_bytes_py(w) for w in words]
+
+
+@pytest.mark.parametrize("width", [4, 8, 12, 100, 256])
+def test_gather_rows(K, width):
+    n = 50_001
+    if width in (4, 8):
+        src = torch.randint(0, 2**31 - 1, (n,), dtype=torch.int32 if width == 4 else torch.int64, device="cuda")
+    else:
+        src = torch.randint(0, 256, (n, width), dtype=torch.uint8, device="cuda")
+    idx = torch.randperm(n, device="cuda").to(torch.int32)
+    out = K.gather_rows(src, idx)
+    assert torch.equal(out, src[idx.long()])
+
+
+def test_extract_and_check_sorted(K):
+    n = 20_000
+    rows = torch.randint(0, 256, (n, 100), dtype=torch.uint8, device="cuda")
+    k = K.extract_be64(rows, 0).cpu().numpy().view(np.uint64)
+    ref = rows[:, :8].cpu().numpy().astype(np.uint64)
+    want = np.zeros(n, dtype=np.uint64)
+    for b in range(8):
+        want = (want << np.uint64(8)) | ref[:, b]
+    assert np.array_equal(k, want)
+    res = K.check_sorted_rows(rows, 0, 10).cpu().numpy()
+    keys10 = [bytes(r) for r in rows[:, :10].cpu().numpy()]
+    bad = sum(1 for a, b in zip(keys10, keys10[1:]) if a > b)
+    assert int(res[0]) == bad
+    assert np.uint64(res.view(np.uint64)[1]) == np.sum(want, dtype=np.uint64)
+
+
+def test_sampler_is_deterministic_and_rate(K):
+    n = 2_000_000
+    keys = torch.arange(n, dtype=torch.int64, device="cuda")
+    s1, c1 = K.sample_keys(keys, seed=3, rate=0.001, cap=8192)
+    s2, c2 = K.sample_keys(keys, seed=3, rate=0.001, cap=8192)
+    m = int(c1.item())
+    assert m == int(c2.item()) and 1500 < m < 2500
+    assert torch.equal(torch.sort(s1[:m]).values, torch.sort(s2[:m]).values)
+    s3, c3 = K.sample_keys(keys, seed=4, rate=0.001, cap=8192)
+    assert not torch.equal(torch.sort(s1[:m]).values, torch.sort(s3[:int(c3.item())]).values[:m])
+
+
+def test_select_separators_matches_oracle(K):
+    from dryad_b200.oracle.sampler import select_separators
+    srt = torch.arange(0, 1000, 3, dtype=torch.int64, device="cuda")
+    for pc in (1, 2, 8, 400):
+        for desc in (False, True):
+            got = K.select_separators(srt, srt.numel(), pc, desc).cpu().tolist()
+            assert got == select_separators(srt.cpu().tolist(), pc, desc)
+
+
+def test_hash_aggregate_sum_count_min_max(K):
+    n, card = 400_000, 5000
+    keys = torch.randint(0, card, (n,), dtype=torch.int64, device="cuda")
+    v = torch.randint(-1000, 1000, (n,), dtype=torch.int64, device="cuda")
+    f = torch.rand(n, dtype=torch.float64, device="cuda")
+    t = K.HashAggTable(card * 2, ["sum_i64", "count", "min_i64", "max_i64", "sum_f64"], "cuda")
+    t.update(keys, [v, None, v, v, f.view(torch.int64)])
+    gk, gl = t.extract()
+    order = torch.argsort(gk)
+    gk, gl = gk[order], gl[:, order]
+    uk = torch.unique(keys)
+    assert torch.equal(gk, uk)
+    ref_sum = torch.zeros(card, dtype=torch.int64, device="cuda").index_add_(0, keys, v)[uk]
+    ref_cnt = torch.bincount(keys, minlength=card)[uk]
+    assert torch.equal(gl[0], ref_sum)
+    assert torch.equal(gl[1], ref_cnt)
+    ref_min = torch.full((card,), 2**62, dtype=torch.int64, device="cuda").scatter_reduce_(0, keys, v, "amin")[uk]
+    ref_max = torch.full((card,), -2**62, dtype=torch.int64, device="cuda").scatter_reduce_(0, keys, v, "amax")[uk]
+    assert torch.equal(gl[2], ref_min) and torch.equal(gl[3], ref_max)
+    ref_f = torch.zeros(card, dtype=torch.float64, device="cuda").index_add_(0, keys, f)[uk]
+    assert torch.allclose(gl[4].view(torch.float64), ref_f, rtol=1e-9, atol=1e-9)
+
+
+def test_hash_aggregate_checked_overflow(K):
+    keys = torch.zeros(4, dtype=torch.int64, device="cuda")
+    v = torch.full((4,), 2**62, dtype=torch.int64, device="cuda")
+    t = K.HashAggTable(64, ["sum_i64_checked"], "cuda")
+    t.update(keys, [v])
+    with pytest.raises(OverflowError):
+        t.extract()
+
+
+def test_hash_join_and_contains(K):
+    nb, npb = 5000, 20000
+    bk = torch.randint(0, 3000, (nb,), dtype=torch.int64, device="cuda")
+    pk = torch.randint(0, 4000, (npb,), dtype=torch.int64, device="cuda")
+    jt = K.JoinTable(bk)
+    op, ob = jt.probe(pk)
+    got = sorted(zip(op.cpu().tolist(), ob.cpu().tolist()))
+    bkc, pkc = bk.cpu().tolist(), pk.cpu().tolist()
+    by = {}
+    for j, k in enumerate(bkc):
+        by.setdefault(k, []).append(j)
+    want = sorted((i, j) for i, k in enumerate(pkc) for j in by.get(k, []))
+    assert got == want
+    c = jt.contains(pk).cpu().tolist()
+    assert c == [1 if k in by else 0 for k in pkc]
+
+
+def test_compact_and_reduce(K):
+    n = 123_457
+    x = torch.randint(-50, 50, (n,), dtype=torch.int64, device="cuda")
+    flags = (x > 10).to(torch.uint8)
+    idx, m = K.compact_flags(flags)
+    assert torch.equal(idx.long(), torch.nonzero(flags).flatten())
+    assert int(K.reduce(x, "sum").item()) == int(x.sum().item())
+    assert int(K.reduce(x, "min").item()) == int(x.min().item())
+    assert int(K.reduce(x, "max").item()) == int(x.max().item())
+    f = torch.rand(n, dtype=torch.float64, device="cuda")
+    assert abs(float(K.reduce(f, "sum").item()) - float(f.sum().item())) < 1e-6
+    a = K.reduce(f, "sum").item(); b = K.reduce(f, "sum").item()
+    assert a == b  # deterministic
+
+
+@pytest.mark.parametrize("keep_empty", [True, False])
+def test_tokenize(K, keep_empty):
+    from dryad_b200.oracle.text import split_tokens
+    txt = b"the quick  brown fox\n\njumps over the lazy dog \nthe end\n" * 57
+    t = torch.tensor(list(txt), dtype=torch.uint8, device="cuda")
+    starts, lens, hashes = K.tokenize(t, " ", keep_empty)
+    got = [txt[s:s + l] for s, l in zip(starts.cpu().tolist(), lens.cpu().tolist())]
+    assert got == split_tokens(txt, b" ", keep_empty)
+    from dryad_b200.utils.hashing import hash_bytes_py
+    assert [int(h) for h in hashes.cpu().numpy().view(np.uint64)[:20]] == [hash_bytes_py(w) for w in got[:20]]
+
+
+def test_expr_program_and_filter(K):
+    from dryad_b200.expr import col, lit
+    from dryad_b200.expr.compile import run_on_gpu
+    n = 70_001
+    a = torch.randint(-100, 100, (n,), dtype=torch.int64, device="cuda")
+    b = torch.rand(n, dtype=torch.float64, device="cuda")
+    cols = {"a": a, "b": b}
+    out, flags = run_on_gpu({"x": col("a") * 3 + 1, "y": col("b") * 2.0 + col("a")}, cols, n,
+                            predicate=(col("a") % 2 == 0) & (col("b") < 0.5))
+    assert torch.equal(out["x"], a * 3 + 1)
+    assert torch.allclose(out["y"], b * 2.0 + a.to(torch.float64))
+    ref = ((torch.remainder(a, 2) == 0) & (b < 0.5))
+    # C# % is a truncating remainder: even-ness is identical for negatives
+    assert torch.equal(flags.bool(), ref)
