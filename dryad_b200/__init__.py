@@ -1,0 +1,20 @@
+"""dryad_b200 — a B200-native dataflow engine with the capabilities of Dryad / DryadLINQ.
+
+Public API (see dryad_b200.api): DryadLinqContext, Query operators, Decomposable / Associative
+protocols, record types; column expressions in dryad_b200.expr.
+"""
+from .api.context import (CompressionScheme, DryadLinqContext, DryadLinqJobInfo, JobStatus, PlatformKind,
+                          QueryLoggingLevel, Table)
+from .api.decomposable import IAssociative, IDecomposable, associative, decomposable, resource
+from .api.errors import DryadLinqException, ErrorCategory, ErrorCode
+from .api.query import KeyedMultiQuery, MultiQuery, Query
+from .api.types import AggregateValue, ForkTuple, Grouping, LineRecord, Pair, Record
+from .expr import col, lit, where
+
+__version__ = "0.2.1b200"
+__all__ = [
+    "DryadLinqContext", "DryadLinqJobInfo", "JobStatus", "PlatformKind", "QueryLoggingLevel", "CompressionScheme",
+    "Table", "IDecomposable", "IAssociative", "decomposable", "associative", "resource", "DryadLinqException",
+    "ErrorCode", "ErrorCategory", "Query", "MultiQuery", "KeyedMultiQuery", "Record", "Pair", "LineRecord",
+    "ForkTuple", "Grouping", "AggregateValue", "col", "lit", "where",
+]

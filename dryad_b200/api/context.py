@@ -1,0 +1,364 @@
+"""DryadLinqContext: the entry point and all user-visible configuration.
+
+Reference: LinqToDryad/DryadLinqContext.cs:566-1309 (three constructors :642-672, properties
+:728-1119, FromStore :1176-1196, FromEnumerable :1210-1223, Equals over all settings :1283-1308),
+PlatformKind / cluster descriptors :44-547, job submission LinqToDryad/DryadLinqJobExecutor.cs and
+LocalJobSubmission.cs, job handle LinqToDryad/DryadLinqQueryRuntime.cs:34-110.
+
+Platforms here: LOCAL (all partitions in this process, host or single-GPU backend) and B200
+(one process per GPU under torch.distributed; partition p lives on rank p % world).
+"""
+from __future__ import annotations
+
+import os
+import tempfile
+import threading
+import time
+from enum import Enum
+from typing import Any, Callable, Dict, Iterable, List, Optional, Sequence
+
+from ..plan import static_config as SC
+from ..plan.dataset_info import DataSetInfo, RandomPartition
+from ..plan.logical import QExpr, infer_schema
+from .errors import DryadLinqException, ErrorCode
+from .query import Query
+
+VERSION = "0.2.1-b200"
+
+
+class PlatformKind(str, Enum):
+    LOCAL = "LOCAL"
+    B200 = "B200"            # one NVSwitch domain (replaces YARN_NATIVE / YARN_AZURE)
+
+
+class ExecutorKind(str, Enum):
+    DRYAD = "DRYAD"
+
+
+class CompressionScheme(str, Enum):
+    NoCompression = "None"
+    Gzip = "Gzip"
+
+
+class QueryLoggingLevel(str, Enum):
+    OFF, CRITICAL, ERROR, WARN, INFO, VERBOSE = "OFF", "CRITICAL", "ERROR", "WARN", "INFO", "VERBOSE"
+
+
+class JobStatus(str, Enum):
+    NotSubmitted, Waiting, Running, Success, Failure, Cancelled = (
+        "NotSubmitted", "Waiting", "Running", "Success", "Failure", "Cancelled")
+
+
+class Table:
+    """A materialised partitioned dataset (in memory and/or a partfile on disk)."""
+
+    def __init__(self, partitions: Optional[List[Any]], schema=None, info: Optional[DataSetInfo] = None,
+                 uri: Optional[str] = None, temporary: bool = False):
+        self.partitions = partitions
+        self.schema = schema
+        self.info = info
+        self.uri = uri
+        self.temporary = temporary
+        self.lease_expires = time.time() + SC.TEMP_LEASE_SECONDS if temporary else None
+
+    @property
+    def partition_count(self) -> int:
+        return len(self.partitions) if self.partitions is not None else 0
+
+
+class DryadLinqJobInfo:
+    """Job handle: ids, Wait() (raises on failure), CancelJob()."""
+
+    def __init__(self, context, queries: Sequence[Query]):
+        self.context, self.queries = context, list(queries)
+        self.job_ids: List[str] = []
+        self.status = JobStatus.NotSubmitted
+        self.error: Optional[BaseException] = None
+        self.results: List[Query] = []
+        self._thread: Optional[threading.Thread] = None
+        self._cancel = threading.Event()
+
+    def wait(self) -> List[Query]:
+        if self._thread is not None:
+            self._thread.join()
+        if self.status == JobStatus.Failure and self.error is not None:
+            raise self.error
+        if self.status == JobStatus.Cancelled:
+            raise DryadLinqException(ErrorCode.DidNotCompleteSuccessfully, "job was cancelled")
+        return self.results
+
+    def cancel_job(self) -> None:
+        self._cancel.set()
+        if self.status in (JobStatus.NotSubmitted, JobStatus.Waiting):
+            self.status = JobStatus.Cancelled
+
+    Wait, CancelJob = wait, cancel_job
+    JobIds = property(lambda s: s.job_ids)
+
+
+class DryadLinqContext:
+    _SETTINGS = ("platform", "num_partitions", "local_debug", "intermediate_data_compression_scheme",
+                 "output_data_compression_scheme", "compile_for_vertex_debugging", "job_friendly_name",
+                 "job_min_nodes", "job_max_nodes", "threads_per_worker", "application_master_mb_memory",
+                 "container_mb_memory", "queue", "node_group", "job_runtime_limit",
+                 "enable_speculative_duplication", "debug_break", "runtime_logging_level",
+                 "graph_manager_node", "select_order_preserving", "partition_unc_path", "device")
+
+    def __init__(self, num_partitions: Optional[int] = None, storage_scheme: str = "partfile", *,
+                 platform: PlatformKind = PlatformKind.LOCAL, device: str = "cpu", cluster_name: str = "localhost",
+                 local_debug: bool = False, work_dir: Optional[str] = None):
+        self.platform = PlatformKind(platform)
+        self.cluster_name = cluster_name
+        self.storage_scheme = storage_scheme
+        self.device = device
+        self.num_partitions = int(num_partitions) if num_partitions else SC.DEFAULT_PARTITION_COUNT
+        self.version = VERSION
+        # user-visible job properties (DryadLinqContext.cs:728-1119)
+        self.local_debug = local_debug
+        self.intermediate_data_compression_scheme = CompressionScheme.NoCompression.value
+        self.output_data_compression_scheme = CompressionScheme.NoCompression.value
+        self.compile_for_vertex_debugging = False
+        self.job_friendly_name = "DryadLINQ job"
+        self.job_min_nodes: Optional[int] = None
+        self.job_max_nodes: Optional[int] = None
+        self.threads_per_worker = int(os.environ.get("DRYAD_THREADS_PER_WORKER", "0")) or (os.cpu_count() or 1)
+        self.application_master_mb_memory: Optional[int] = None
+        self.container_mb_memory: Optional[int] = None
+        self.queue: Optional[str] = None
+        self.node_group: Optional[str] = None
+        self.job_runtime_limit: Optional[int] = None
+        self.enable_speculative_duplication = True
+        self.debug_break = False
+        self.runtime_logging_level = QueryLoggingLevel(os.environ.get("DRYAD_LOGGING_LEVEL", "ERROR"))
+        self.graph_manager_node: Optional[str] = None
+        self.select_order_preserving = False
+        self.partition_unc_path: Optional[str] = None
+        self.job_environment_variables: Dict[str, str] = {}
+        self.resources_to_add: List[str] = []
+        self.resources_to_remove: List[str] = []
+        self.exec_host_args: List[str] = []
+        # engine knobs (GraphManager/graph/DrGraphParameters.cpp:50-69)
+        self.max_failures_per_vertex = 6
+        self.fail_fast_on_deterministic_errors = False
+        self.retain_intermediate = True
+        self.sample_rate = SC.SAMPLE_RATE
+        self.broadcast_join_rows = 1 << 20     # planner rule: inner side at most this many rows -> broadcast join
+        self.fault_injector: Optional[Callable] = None
+        self.work_dir = work_dir or os.environ.get("DRYAD_HOME") or os.path.join(tempfile.gettempdir(), "DRYADLINQ",
+                                                                                f"app_{os.getpid()}")
+        self._disposed = False
+        self._frozen = False
+        self._tables: Dict[int, Table] = {}
+        self._job_counter = 0
+        self._lock = threading.RLock()
+        self.last_job_stats: List[dict] = []
+        self.last_plan = None
+
+    # ---- lifecycle ---------------------------------------------------------------------------
+    def dispose(self):
+        self._disposed = True
+        self._tables.clear()
+
+    Dispose = dispose
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *a):
+        self.dispose()
+
+    def _check_not_disposed(self):
+        if self._disposed:
+            raise DryadLinqException(ErrorCode.ContextDisposed, "the DryadLinqContext has been disposed")
+
+    def __setattr__(self, name, value):
+        # settings become read-only once a job has been submitted (BasicAPITests: context
+        # read-only after use; DryadLinqStringDictionary read-only-after-submit collections)
+        if getattr(self, "_frozen", False) and name in self._SETTINGS and getattr(self, name, None) != value:
+            raise DryadLinqException(ErrorCode.JobOptionNotImplemented,
+                                     f"context setting {name!r} cannot change after a job was submitted")
+        object.__setattr__(self, name, value)
+
+    def settings_equal(self, other: "DryadLinqContext") -> bool:
+        return all(getattr(self, k) == getattr(other, k) for k in self._SETTINGS)
+
+    Equals = settings_equal
+
+    # ---- data sources --------------------------------------------------------------------------
+    def from_enumerable(self, data: Iterable, num_partitions: Optional[int] = None) -> Query:
+        """Client data -> a dataset.  Like the reference (ingress through a temporary table,
+        DryadLinqContext.cs:1210-1223) the data lands in ONE partition unless a count is given."""
+        self._check_not_disposed()
+        rows = list(data)
+        n = int(num_partitions) if num_partitions else 1
+        parts: List[List] = [[] for _ in range(n)]
+        per = (len(rows) + n - 1) // n if rows else 0
+        for i in range(n):
+            parts[i] = rows[i * per:(i + 1) * per] if per else []
+        schema = infer_schema(rows[0]) if rows else None
+        return self._from_table(Table(parts, schema, None, None, True))
+
+    def from_partitions(self, parts: Sequence[Sequence], schema=None) -> Query:
+        self._check_not_disposed()
+        parts = [list(p) for p in parts]
+        if schema is None:
+            first = next((p[0] for p in parts if p), None)
+            schema = infer_schema(first) if first is not None else None
+        return self._from_table(Table(parts, schema, None, None, True))
+
+    def from_store(self, uri: str) -> Query:
+        """Open a stored partitioned table.  Loaded tables are RANDOM-partitioned, unordered and
+        not distinct whatever they were when written (DryadLinqQuery.cs:547-551)."""
+        self._check_not_disposed()
+        from ..channel import store
+        t = store.open_table(uri)
+        return self._from_table(Table(t.partitions, t.schema, None, uri, False), uri)
+
+    def from_columns(self, columns: Dict[str, Any], num_partitions: Optional[int] = None) -> Query:
+        """Columnar ingress: dict name -> 1-D numpy array / torch tensor (equal lengths)."""
+        self._check_not_disposed()
+        from ..runtime.columnar import ColumnBatch
+        batch = ColumnBatch.from_columns(columns)
+        n = int(num_partitions) if num_partitions else 1
+        parts = batch.split(n)
+        return self._from_table(Table(parts, batch.schema, None, None, True))
+
+    def _from_table(self, table: Table, uri: Optional[str] = None) -> Query:
+        pc = max(1, table.partition_count)
+        rows = None
+        if table.partitions is not None:
+            try:
+                rows = sum(len(p) for p in table.partitions)
+            except TypeError:
+                rows = None
+        e = QExpr("source", [], table.schema, table=table, partition_count=pc, uri=uri,
+                  info=table.info, row_estimate=rows)
+        self._tables[e.id] = table
+        return Query(self, e)
+
+    FromEnumerable, FromStore = from_enumerable, from_store
+
+    # ---- data access used by the runtimes ---------------------------------------------------
+    def _read_source_flat(self, e: QExpr) -> List:
+        t: Table = e.params["table"]
+        out: List = []
+        for i in range(t.partition_count):
+            out.extend(self._read_table_partition(t, i))
+        return out
+
+    def _read_table_partition(self, table: Table, i: int):
+        p = table.partitions[i]
+        if hasattr(p, "to_records"):
+            return p.to_records() if self._backend().wants_records else p
+        return p
+
+    def _check_store_target(self, uri: str, delete_if_exists: bool):
+        from ..channel import store
+        if store.exists(uri):
+            if not delete_if_exists:
+                raise DryadLinqException(ErrorCode.StreamAlreadyExists, f"{uri} already exists")
+
+    def _write_store(self, uri, parts, schema, compression):
+        from ..channel import store
+        store.write_table(uri, parts, schema, compression or self.output_data_compression_scheme)
+
+    def _commit_table(self, uri, parts, schema, info, compression, temporary) -> Table:
+        if uri:
+            self._write_store(uri, parts, schema, compression)
+        return Table(parts, schema, info, uri, temporary)
+
+    # ---- execution ----------------------------------------------------------------------------
+    def _backend(self):
+        from ..runtime.backends import get_backend
+        return get_backend(self)
+
+    def _make_reporter(self):
+        from ..sched.reporting import CalypsoReporter
+        self._job_counter += 1
+        job_dir = os.path.join(self.work_dir, "LocalJobs", str(self._job_counter))
+        return CalypsoReporter(job_dir, level=self.runtime_logging_level.value)
+
+    def submit(self, *queries: Query) -> DryadLinqJobInfo:
+        """Submit one or several queries as ONE job (DryadLinqQueryable.cs:4032-4252)."""
+        self._check_not_disposed()
+        qs = list(queries)
+        if not qs:
+            raise DryadLinqException(ErrorCode.UnhandledQuery, "nothing to submit")
+        if len({id(q) for q in qs}) != len(qs):
+            raise DryadLinqException(ErrorCode.UnhandledQuery, "the same query appears twice in one Submit")
+        for q in qs:
+            if q.context is not self:
+                raise DryadLinqException(ErrorCode.MustStartFromContext, "queries of one job must share one context")
+        job = DryadLinqJobInfo(self, qs)
+        object.__setattr__(self, "_frozen", True)
+        already = [q for q in qs if q._job is not None]
+        if len(already) == len(qs):          # re-submitting an executed query returns the existing job
+            return qs[0]._job
+        self._run_job(job)
+        return job
+
+    def submit_and_wait(self, *queries: Query) -> List[Query]:
+        return self.submit(*queries).wait()
+
+    Submit, SubmitAndWait = submit, submit_and_wait
+
+    def _run_job(self, job: DryadLinqJobInfo) -> None:
+        roots = [q.materialize_lazy() for q in job.queries]       # Query objects rooted at to_store
+        job.status = JobStatus.Running
+        job.job_ids = [f"job_{os.getpid()}_{self._job_counter + 1}"]
+        try:
+            if self.local_debug:
+                from ..oracle.interp import LocalDebugInterpreter
+                interp = LocalDebugInterpreter(self)
+                tables = {}
+                for r in roots:
+                    data = interp.run(r.expr)
+                    tables[r.expr.id] = Table([list(data)], r.expr.schema, None, r.expr.params.get("uri"),
+                                              r.expr.params.get("temporary", False))
+            else:
+                from ..plan.querygen import QueryGen
+                from ..runtime.executor import JobExecutor
+                plan = QueryGen(self, roots)
+                ex = JobExecutor(self, plan)
+                tables = ex.run()
+                self.last_job_stats = ex.stats
+                self.last_plan = plan
+            job.results = []
+            for q, r in zip(job.queries, roots):
+                t = tables[r.expr.id]
+                res = self._from_table(t, t.uri)
+                res._job = job
+                q._job = job
+                q._result = res
+                job.results.append(res)
+            job.status = JobStatus.Success
+        except BaseException as ex:  # noqa: BLE001
+            job.status = JobStatus.Failure
+            job.error = ex
+            raise
+
+    def _execute(self, q: Query) -> Query:
+        res = getattr(q, "_result", None)
+        if res is not None:
+            return res
+        if q.expr.op == "source":
+            return q
+        return self.submit(q).wait()[0]
+
+    def _execute_to_list(self, q: Query) -> List:
+        if self.local_debug and q.expr.op != "source":
+            from ..oracle.interp import LocalDebugInterpreter
+            self._check_not_disposed()
+            return list(LocalDebugInterpreter(self).run(q.expr))
+        res = self._execute(q)
+        t: Table = res.expr.params["table"]
+        out: List = []
+        for i in range(t.partition_count):
+            p = t.partitions[i]
+            out.extend(p.to_records() if hasattr(p, "to_records") else p)
+        return out
+
+    def _execute_to_partitions(self, q: Query) -> List[List]:
+        res = self._execute(q)
+        t: Table = res.expr.params["table"]
+        return [list(p.to_records() if hasattr(p, "to_records") else p) for p in t.partitions]

@@ -1,0 +1,449 @@
+"""The LINQ-style lazy query surface.
+
+Reference: the ~110 DryadLINQ-specific operators of LinqToDryad/DryadLinqQueryable.cs:54-4265 plus
+the standard System.Linq.Queryable operators the provider intercepts
+(LinqToDryad/DryadLinqQuery.cs:137-210, dispatcher DryadLinqQueryGen.cs:3439-4787).
+
+Operators only build `QExpr` nodes (lazy).  Execution is triggered by iteration, `submit()`,
+`submit_and_wait()`, `to_list()`, or a scalar aggregate (`count()`, `sum()` …) — the same
+triggers as the reference (DryadLinqQuery.cs:171-209, 563-596).  Every operator has a LocalDebug
+branch: with `context.local_debug` the query runs through the CPU oracle (LINQ-to-Objects).
+
+Method names are snake_case; PascalCase aliases (Select, Where, GroupBy, …) exist for users
+coming from the reference.
+"""
+from __future__ import annotations
+
+from typing import Any, Callable, Iterable, List, Optional, Sequence
+
+from ..expr import ir as X
+from ..plan.decomposition import try_decompose
+from ..plan.logical import Lam, QExpr, Schema
+from .errors import DryadLinqException, ErrorCode
+
+
+def _lam(fn, schema: Schema, nargs: int = 1) -> Lam:
+    if isinstance(fn, Lam):
+        return fn
+    if isinstance(fn, X.Expr) or isinstance(fn, dict):
+        # users may pass column expressions directly: q.select({"a": col("x") + 1})
+        ir = fn if isinstance(fn, X.Expr) else {k: X.wrap(v) for k, v in fn.items()}
+        return Lam(_fn_from_ir(ir), ir, 1)
+    if isinstance(fn, str):
+        kind = (schema or {}).get(fn, "o")
+        ir = X.col(fn, kind) if kind != "o" else None
+        return Lam(lambda r, _f=fn: r[_f] if isinstance(r, dict) else getattr(r, _f), ir, 1)
+    if not callable(fn):
+        raise DryadLinqException(ErrorCode.UnsupportedExpressionType, f"expected a function, got {fn!r}")
+    return Lam.traced(fn, schema, nargs)
+
+
+def _fn_from_ir(ir):
+    from .types import Record
+
+    def row_of(r):
+        return r if isinstance(r, dict) else {"value": r}
+    if isinstance(ir, X.Expr):
+        return lambda r: X.eval_row(ir, row_of(r))
+    if isinstance(ir, X.TupleFields):
+        return lambda r: tuple(X.eval_row(e, row_of(r)) for e in ir.values())
+    return lambda r: Record((k, X.eval_row(e, row_of(r))) for k, e in ir.items())
+
+
+class Query:
+    """IQueryable<T>: a lazy, partitioned dataset."""
+
+    def __init__(self, context, expr: QExpr):
+        self.context = context
+        self.expr = expr
+        self._job = None          # set once executed (data-backed afterwards)
+
+    # ---- plumbing --------------------------------------------------------------------------
+    @property
+    def schema(self) -> Schema:
+        return self.expr.schema
+
+    def _new(self, op: str, sources: Sequence["Query"] = (), schema: Schema = None, **params) -> "Query":
+        for s in sources:
+            if s.context is not self.context:
+                raise DryadLinqException(ErrorCode.MustStartFromContext,
+                                         "all inputs of a query must come from the same context")
+        self.context._check_not_disposed()
+        return Query(self.context, QExpr(op, [self.expr] + [s.expr for s in sources], schema, **params))
+
+    # ---- element-wise ----------------------------------------------------------------------
+    def select(self, fn) -> "Query":
+        if self.expr.op == "group_by" and "result" not in self.expr.params and "decomp" not in self.expr.params:
+            src = self.expr
+            dec = try_decompose(fn, src.params["elem_schema"], src.params["key"]) if callable(fn) else None
+            if dec is not None:
+                q = Query(self.context, QExpr("group_by", src.sources, dec.out_schema(), key=src.params["key"],
+                                              elem=src.params.get("elem"), elem_schema=src.params["elem_schema"],
+                                              comparer=src.params.get("comparer"), decomp=dec))
+                return q
+        lam = _lam(fn, self.schema)
+        return self._new("select", schema=lam.out_schema(), fn=lam, indexed=False)
+
+    def select_indexed(self, fn) -> "Query":
+        """Select((x, i) => …) with the GLOBAL record index."""
+        return self._new("select", schema=None, fn=Lam(fn, None, 2), indexed=True)
+
+    long_select = select_indexed
+
+    def where(self, pred) -> "Query":
+        return self._new("where", schema=self.schema, fn=_lam(pred, self.schema), indexed=False)
+
+    def where_indexed(self, pred) -> "Query":
+        return self._new("where", schema=self.schema, fn=Lam(pred, None, 2), indexed=True)
+
+    long_where = where_indexed
+
+    def select_many(self, fn, result: Optional[Callable] = None) -> "Query":
+        return self._new("select_many", schema=None, fn=Lam(fn, None, 1),
+                         result=Lam(result, None, 2) if result else None, indexed=False)
+
+    def select_many_indexed(self, fn, result: Optional[Callable] = None) -> "Query":
+        return self._new("select_many", schema=None, fn=Lam(fn, None, 2),
+                         result=Lam(result, None, 2) if result else None, indexed=True)
+
+    long_select_many = select_many_indexed
+
+    # ---- grouping / ordering ---------------------------------------------------------------
+    def group_by(self, key, elem=None, result=None, comparer=None) -> "Query":
+        klam = _lam(key, self.schema)
+        elam = _lam(elem, self.schema) if elem is not None else None
+        elem_schema = elam.out_schema() if elam is not None else self.schema
+        params = dict(key=klam, elem=elam, elem_schema=elem_schema, comparer=comparer)
+        if result is not None:
+            dec = try_decompose(result, elem_schema, klam, two_arg=True)
+            if dec is not None:
+                return self._new("group_by", schema=dec.out_schema(), decomp=dec, **params)
+            return self._new("group_by", schema=None, result=Lam(result, None, 2), **params)
+        return self._new("group_by", schema=None, **params)
+
+    def order_by(self, key, comparer=None, descending: bool = False) -> "Query":
+        return self._new("order_by", schema=self.schema, key=_lam(key, self.schema), comparer=comparer,
+                         descending=descending)
+
+    def order_by_descending(self, key, comparer=None) -> "Query":
+        return self.order_by(key, comparer, True)
+
+    def then_by(self, *_a, **_k):
+        raise DryadLinqException(ErrorCode.ThenByNotSupported,
+                                 "ThenBy is not supported; order by a composite key instead")
+
+    then_by_descending = then_by
+
+    def distinct(self, comparer=None) -> "Query":
+        return self._new("distinct", schema=self.schema, comparer=comparer)
+
+    def reverse(self) -> "Query":
+        return self._new("reverse", schema=self.schema)
+
+    # ---- binary ----------------------------------------------------------------------------
+    def join(self, inner: "Query", outer_key, inner_key, result, comparer=None) -> "Query":
+        ok, ik = _lam(outer_key, self.schema), _lam(inner_key, inner.schema)
+        rlam = _join_result_lam(result, self.schema, inner.schema)
+        return self._new("join", [inner], schema=rlam.out_schema(), outer_key=ok, inner_key=ik,
+                         result=rlam, comparer=comparer)
+
+    def group_join(self, inner: "Query", outer_key, inner_key, result, comparer=None) -> "Query":
+        return self._new("group_join", [inner], schema=None, outer_key=_lam(outer_key, self.schema),
+                         inner_key=_lam(inner_key, inner.schema), result=Lam(result, None, 2), comparer=comparer)
+
+    def concat(self, other: "Query") -> "Query":
+        return self._new("concat", [other], schema=self.schema if self.schema == other.schema else None)
+
+    def union(self, other: "Query", comparer=None) -> "Query":
+        return self._new("union", [other], schema=self.schema if self.schema == other.schema else None, comparer=comparer)
+
+    def intersect(self, other: "Query", comparer=None) -> "Query":
+        return self._new("intersect", [other], schema=self.schema, comparer=comparer)
+
+    def except_(self, other: "Query", comparer=None) -> "Query":
+        return self._new("except", [other], schema=self.schema, comparer=comparer)
+
+    def zip(self, other: "Query", fn) -> "Query":
+        return self._new("zip", [other], schema=None, fn=Lam(fn, None, 2))
+
+    # ---- prefix operators ------------------------------------------------------------------
+    def take(self, n: int) -> "Query":
+        return self._new("take", schema=self.schema, n=int(n))
+
+    def skip(self, n: int) -> "Query":
+        return self._new("skip", schema=self.schema, n=int(n))
+
+    def take_while(self, pred) -> "Query":
+        return self._new("take_while", schema=self.schema, fn=Lam(pred, None, 1), indexed=False)
+
+    def skip_while(self, pred) -> "Query":
+        return self._new("skip_while", schema=self.schema, fn=Lam(pred, None, 1), indexed=False)
+
+    def take_while_indexed(self, pred) -> "Query":
+        return self._new("take_while", schema=self.schema, fn=Lam(pred, None, 2), indexed=True)
+
+    def skip_while_indexed(self, pred) -> "Query":
+        return self._new("skip_while", schema=self.schema, fn=Lam(pred, None, 2), indexed=True)
+
+    long_take_while, long_skip_while = take_while_indexed, skip_while_indexed
+
+    # ---- partitioning (DryadLinqQueryable.cs:274-863, 3407-3677) ---------------------------
+    def hash_partition(self, key=None, count: Optional[int] = None, comparer=None) -> "Query":
+        klam = _lam(key, self.schema) if key is not None else _identity_lam(self.schema)
+        if count is not None and count < 1:
+            raise DryadLinqException(ErrorCode.IndexTooSmall, "partition count must be positive")
+        return self._new("hash_partition", schema=self.schema, key=klam, count=count, comparer=comparer)
+
+    def range_partition(self, key=None, count: Optional[int] = None, range_keys: Optional[Sequence] = None,
+                        comparer=None, descending: Optional[bool] = None) -> "Query":
+        klam = _lam(key, self.schema) if key is not None else _identity_lam(self.schema)
+        return self._new("range_partition", schema=self.schema, key=klam, count=count,
+                         range_keys=list(range_keys) if range_keys is not None else None,
+                         comparer=comparer, descending=descending)
+
+    def assume_hash_partition(self, key=None, comparer=None) -> "Query":
+        klam = _lam(key, self.schema) if key is not None else _identity_lam(self.schema)
+        return self._new("assume_hash_partition", schema=self.schema, key=klam, comparer=comparer)
+
+    def assume_range_partition(self, key=None, range_keys: Optional[Sequence] = None, comparer=None,
+                               descending: Optional[bool] = None) -> "Query":
+        klam = _lam(key, self.schema) if key is not None else _identity_lam(self.schema)
+        return self._new("assume_range_partition", schema=self.schema, key=klam,
+                         range_keys=list(range_keys) if range_keys is not None else None,
+                         comparer=comparer, descending=descending)
+
+    def assume_order_by(self, key=None, comparer=None, descending: bool = False) -> "Query":
+        klam = _lam(key, self.schema) if key is not None else _identity_lam(self.schema)
+        return self._new("assume_order_by", schema=self.schema, key=klam, comparer=comparer, descending=descending)
+
+    # ---- Apply / Fork (DryadLinqQueryable.cs:929-1208, 3716-3851) --------------------------
+    def apply(self, fn, other: Optional["Query"] = None) -> "Query":
+        """Non-homomorphic Apply: fn sees the WHOLE dataset (merged to one partition)."""
+        srcs = [other] if other is not None else []
+        return self._new("apply", srcs, schema=None, fn=Lam(fn, None, 1 + len(srcs)), per_partition=False,
+                         first_only=False)
+
+    def apply_per_partition(self, fn, other: Optional["Query"] = None, is_first_only: bool = False) -> "Query":
+        """Homomorphic Apply: fn runs once per partition.  Binary form: is_first_only=True
+        broadcasts `other` to every partition of self (left-homomorphic); False pairs partition i
+        with partition i (fully homomorphic; equal partition counts required)."""
+        srcs = [other] if other is not None else []
+        return self._new("apply", srcs, schema=None, fn=Lam(fn, None, 1 + len(srcs)), per_partition=True,
+                         first_only=is_first_only)
+
+    def apply_with_partition_index(self, fn) -> "Query":
+        return self._new("apply", schema=None, fn=Lam(fn, None, 2), per_partition=True, first_only=False,
+                         with_index=True)
+
+    def sliding_window(self, fn, window: int) -> "Query":
+        return self._new("sliding_window", schema=None, fn=Lam(fn, None, 1), window=int(window))
+
+    def fork(self, fn, n: int = 2) -> "MultiQuery":
+        """Mapper returns a tuple of n optional values; branch i receives the non-None i-th values.
+        `fn` may also be a per-partition function returning n sequences (fork_per_partition)."""
+        fk = self._new("fork", schema=None, fn=Lam(fn, None, 1), n=n, per_partition=False)
+        return MultiQuery(self.context, fk, n)
+
+    def fork_per_partition(self, fn, n: int = 2) -> "MultiQuery":
+        fk = self._new("fork", schema=None, fn=Lam(fn, None, 1), n=n, per_partition=True)
+        return MultiQuery(self.context, fk, n)
+
+    def fork_by_key(self, key_fn, keys: Sequence) -> "KeyedMultiQuery":
+        keys = list(keys)
+        idx = {k: i for i, k in enumerate(keys)}
+
+        def mapper(x, _idx=idx, _n=len(keys), _kf=key_fn):
+            out = [None] * _n
+            i = _idx.get(_kf(x))
+            if i is not None:
+                out[i] = x
+            return tuple(out)
+        fk = self._new("fork", schema=None, fn=Lam(mapper, None, 1), n=len(keys), per_partition=False)
+        return KeyedMultiQuery(self.context, fk, keys)
+
+    def broadcast(self, n: Optional[int] = None) -> "Query":
+        """BroadCast: every one of n partitions receives the whole dataset
+        (DryadLinqExtension.cs:264-281)."""
+        return self._new("broadcast", schema=self.schema, count=n)
+
+    def do_while(self, body: Callable[["Query"], "Query"], cond: Callable[["Query", "Query"], "Query"]) -> "Query":
+        """Client-side loop (DryadLinqQueryable.cs:1280-1306): each iteration submits body and
+        cond as one job; cond must produce a single bool."""
+        cur = self
+        while True:
+            nxt = body(cur)
+            c = cond(cur, nxt)
+            nxt_m, c_m = self.context.submit_and_wait(nxt.materialize_lazy(), c.materialize_lazy())
+            ok = bool(c_m.to_list()[0])
+            cur = nxt_m
+            if not ok:
+                return cur
+
+    # ---- scalar aggregates as datasets (*AsQuery, DryadLinqQueryable.cs:1384-3368) ---------
+    def _agg(self, kind: str, **params) -> "Query":
+        return self._new("aggregate", schema=None, kind=kind, **params)
+
+    def count_as_query(self, pred=None): return self._agg("count", fn=Lam(pred, None, 1) if pred else None)
+    def long_count_as_query(self, pred=None): return self.count_as_query(pred)
+    def sum_as_query(self, sel=None): return self._agg("sum", fn=_lam(sel, self.schema) if sel else None)
+    def min_as_query(self, sel=None): return self._agg("min", fn=_lam(sel, self.schema) if sel else None)
+    def max_as_query(self, sel=None): return self._agg("max", fn=_lam(sel, self.schema) if sel else None)
+    def average_as_query(self, sel=None): return self._agg("average", fn=_lam(sel, self.schema) if sel else None)
+    def any_as_query(self, pred=None): return self._agg("any", fn=Lam(pred, None, 1) if pred else None)
+    def all_as_query(self, pred): return self._agg("all", fn=Lam(pred, None, 1))
+    def contains_as_query(self, value): return self._agg("contains", value=value)
+    def first_as_query(self, pred=None): return self._agg("first", fn=Lam(pred, None, 1) if pred else None, default=False)
+    def first_or_default_as_query(self, pred=None): return self._agg("first", fn=Lam(pred, None, 1) if pred else None, default=True)
+    def last_as_query(self, pred=None): return self._agg("last", fn=Lam(pred, None, 1) if pred else None, default=False)
+    def last_or_default_as_query(self, pred=None): return self._agg("last", fn=Lam(pred, None, 1) if pred else None, default=True)
+    def single_as_query(self, pred=None): return self._agg("single", fn=Lam(pred, None, 1) if pred else None, default=False)
+    def single_or_default_as_query(self, pred=None): return self._agg("single", fn=Lam(pred, None, 1) if pred else None, default=True)
+
+    def sequence_equal_as_query(self, other: "Query"):
+        return self._new("aggregate", [other], schema=None, kind="sequence_equal")
+
+    def aggregate_as_query(self, func, seed=None, has_seed: Optional[bool] = None, result=None, seed_fn=None):
+        hs = has_seed if has_seed is not None else (seed is not None or seed_fn is not None)
+        return self._agg("aggregate", fn=Lam(func, None, 2), seed=seed, seed_fn=seed_fn, has_seed=hs,
+                         result=Lam(result, None, 1) if result else None)
+
+    # ---- scalar aggregates (execute immediately) --------------------------------------------
+    def _scalar(self, q: "Query"):
+        vals = q.to_list()
+        return vals[0] if vals else None
+
+    def count(self, pred=None): return self._scalar(self.count_as_query(pred))
+    long_count = count
+    def sum(self, sel=None): return self._scalar(self.sum_as_query(sel))
+    def min(self, sel=None): return self._scalar(self.min_as_query(sel))
+    def max(self, sel=None): return self._scalar(self.max_as_query(sel))
+    def average(self, sel=None): return self._scalar(self.average_as_query(sel))
+    def any(self, pred=None): return self._scalar(self.any_as_query(pred))
+    def all(self, pred): return self._scalar(self.all_as_query(pred))
+    def contains(self, value): return self._scalar(self.contains_as_query(value))
+    def first(self, pred=None): return self._scalar(self.first_as_query(pred))
+    def first_or_default(self, pred=None): return self._scalar(self.first_or_default_as_query(pred))
+    def last(self, pred=None): return self._scalar(self.last_as_query(pred))
+    def last_or_default(self, pred=None): return self._scalar(self.last_or_default_as_query(pred))
+    def single(self, pred=None): return self._scalar(self.single_as_query(pred))
+    def single_or_default(self, pred=None): return self._scalar(self.single_or_default_as_query(pred))
+    def sequence_equal(self, other): return self._scalar(self.sequence_equal_as_query(other))
+
+    def aggregate(self, func, seed=None, has_seed: Optional[bool] = None, result=None, seed_fn=None):
+        return self._scalar(self.aggregate_as_query(func, seed, has_seed, result, seed_fn))
+
+    def element_at(self, *_a):
+        raise DryadLinqException(ErrorCode.OperatorNotSupported, "ElementAt is not supported")
+
+    def default_if_empty(self, *_a):
+        raise DryadLinqException(ErrorCode.OperatorNotSupported, "DefaultIfEmpty is not supported")
+
+    def of_type(self, *_a):
+        raise DryadLinqException(ErrorCode.OperatorNotSupported, "OfType is not supported")
+
+    # ---- outputs / execution ---------------------------------------------------------------
+    def to_store(self, uri: str, delete_if_exists: bool = False, compression: Optional[str] = None) -> "Query":
+        """Lazy: names the output table; run it with submit()/submit_and_wait()."""
+        self.context._check_store_target(uri, delete_if_exists)
+        return self._new("to_store", schema=self.schema, uri=uri, compression=compression, temporary=False)
+
+    def materialize_lazy(self) -> "Query":
+        """A temporary output (ToTemporary role, DryadLinqQuery.cs:586-596)."""
+        if self.expr.op == "to_store":
+            return self
+        return self._new("to_store", schema=self.schema, uri=None, compression=None, temporary=True)
+
+    def submit(self):
+        return self.context.submit(self)
+
+    def submit_and_wait(self):
+        return self.context.submit_and_wait(self)[0]
+
+    def to_list(self) -> List:
+        return self.context._execute_to_list(self)
+
+    def __iter__(self):
+        return iter(self.to_list())
+
+    def partitions(self) -> List[List]:
+        """Materialised per-partition contents (structural partition checks in tests)."""
+        return self.context._execute_to_partitions(self)
+
+    def explain(self) -> str:
+        from ..plan.querygen import QueryGen
+        return QueryGen(self.context, [self.materialize_lazy()]).explain()
+
+    def to_xml(self) -> str:
+        from ..plan.querygen import QueryGen
+        return QueryGen(self.context, [self.materialize_lazy()]).to_xml()
+
+    # PascalCase aliases for users of the reference API
+    Select, Where, SelectMany, GroupBy, OrderBy, OrderByDescending = select, where, select_many, group_by, order_by, order_by_descending
+    Distinct, Reverse, Join, GroupJoin, Concat, Union, Intersect, Except, Zip = distinct, reverse, join, group_join, concat, union, intersect, except_, zip
+    Take, Skip, TakeWhile, SkipWhile = take, skip, take_while, skip_while
+    HashPartition, RangePartition, Apply, ApplyPerPartition, Fork, SlidingWindow = hash_partition, range_partition, apply, apply_per_partition, fork, sliding_window
+    AssumeHashPartition, AssumeRangePartition, AssumeOrderBy = assume_hash_partition, assume_range_partition, assume_order_by
+    LongSelect, LongWhere, LongSelectMany, LongTakeWhile, LongSkipWhile = select_indexed, where_indexed, select_many_indexed, take_while_indexed, skip_while_indexed
+    Count, LongCount, Sum, Min, Max, Average, Any, All, Contains = count, count, sum, min, max, average, any, all, contains
+    First, FirstOrDefault, Last, LastOrDefault, Single, SingleOrDefault = first, first_or_default, last, last_or_default, single, single_or_default
+    Aggregate, SequenceEqual, ToStore, Submit, SubmitAndWait, DoWhile, BroadCast = aggregate, sequence_equal, to_store, submit, submit_and_wait, do_while, broadcast
+    CountAsQuery, SumAsQuery, MinAsQuery, MaxAsQuery, AverageAsQuery = count_as_query, sum_as_query, min_as_query, max_as_query, average_as_query
+    AnyAsQuery, AllAsQuery, ContainsAsQuery, FirstAsQuery, LastAsQuery, SingleAsQuery, AggregateAsQuery = any_as_query, all_as_query, contains_as_query, first_as_query, last_as_query, single_as_query, aggregate_as_query
+
+
+def _identity_lam(schema: Schema) -> Lam:
+    ir = None
+    if schema is not None and list(schema) == ["value"] and schema["value"] != "o":
+        ir = X.col("value", schema["value"])
+    return Lam(lambda x: x, ir, 1, "identity")
+
+
+def _join_result_lam(result, outer_schema: Schema, inner_schema: Schema) -> Lam:
+    """Trace a (outer, inner) => record selector: outer columns are prefixed 'o.', inner 'i.'."""
+    if isinstance(result, Lam):
+        return result
+    ir = None
+    if outer_schema is not None and inner_schema is not None and \
+            all(k != "o" for k in list(outer_schema.values()) + list(inner_schema.values())):
+        try:
+            o = X.RowProxy(outer_schema, "o.") if list(outer_schema) != ["value"] else X.col("o.value", outer_schema["value"])
+            i = X.RowProxy(inner_schema, "i.") if list(inner_schema) != ["value"] else X.col("i.value", inner_schema["value"])
+            ir = X.normalise_traced(result(o, i))
+        except Exception:
+            ir = None
+    return Lam(result, ir, 2)
+
+
+class MultiQuery:
+    """IMultiQueryable: handles to the branches of a Fork (LinqToDryad/MultiQueryable.cs:38-389)."""
+
+    def __init__(self, context, fork_query: Query, n: int):
+        self.context, self._fork, self.n = context, fork_query, n
+        self._branches = [fork_query._new("fork_branch", schema=None, index=i) for i in range(n)]
+
+    def __getitem__(self, i: int) -> Query:
+        if not 0 <= i < self.n:
+            raise DryadLinqException(ErrorCode.IndexOutOfRange, f"fork branch {i} out of range")
+        return self._branches[i]
+
+    def __iter__(self):
+        return iter(self._branches)
+
+    first = property(lambda s: s[0])
+    second = property(lambda s: s[1])
+    third = property(lambda s: s[2])
+    First, Second, Third = first, second, third
+
+
+class KeyedMultiQuery(MultiQuery):
+    """IKeyedMultiQueryable: branches addressed by key."""
+
+    def __init__(self, context, fork_query: Query, keys: Sequence):
+        super().__init__(context, fork_query, len(keys))
+        self.keys = list(keys)
+
+    def by_key(self, key) -> Query:
+        try:
+            return self._branches[self.keys.index(key)]
+        except ValueError:
+            raise DryadLinqException(ErrorCode.MultiQueryableKeyOutOfRange, f"no fork branch for key {key!r}") from None

@@ -1,0 +1,181 @@
+"""Record (de)serialisation on the reference's wire primitives.
+
+Primitives (byte-exact with csrc/host/records.cpp and the reference
+LinqToDryad/DryadLinqBinaryWriter.cs:336-546): little-endian fixed-width numbers; compact int =
+1 byte below 0x80 else 4 bytes big-endian with the top bit set; string = compact(char count) +
+compact(UTF-8 byte count) + bytes.
+
+The reference generates one serializer class per record type (DryadLinqCodeGen.cs:496-1479).  The
+Python analog is a tagged self-describing encoding for arbitrary records plus a fixed-width fast
+path for numeric columnar schemas (rows of packed little-endian fields).
+"""
+from __future__ import annotations
+
+import struct
+from typing import Any, List, Tuple
+
+from ..api.types import ForkTuple, Grouping, LineRecord, Pair, Record
+
+T_NONE, T_FALSE, T_TRUE, T_INT, T_FLOAT, T_STR, T_BYTES, T_TUPLE, T_LIST, T_RECORD, T_PAIR, T_GROUP, T_LINE, T_BIGINT, T_DICT, T_FORK = range(16)
+
+
+def compact(v: int) -> bytes:
+    if 0 <= v < 0x80:
+        return bytes((v,))
+    if not 0 <= v < (1 << 31):
+        raise ValueError("compact int out of range")
+    return bytes(((v >> 24) | 0x80, (v >> 16) & 0xFF, (v >> 8) & 0xFF, v & 0xFF))
+
+
+def read_compact(buf: memoryview, pos: int) -> Tuple[int, int]:
+    b0 = buf[pos]
+    if b0 < 0x80:
+        return b0, pos + 1
+    return ((b0 & 0x7F) << 24) | (buf[pos + 1] << 16) | (buf[pos + 2] << 8) | buf[pos + 3], pos + 4
+
+
+def enc_string(s: str) -> bytes:
+    b = s.encode("utf-8")
+    return compact(len(s)) + compact(len(b)) + b
+
+
+def encode(obj: Any, out: List[bytes]) -> None:
+    if obj is None:
+        out.append(bytes((T_NONE,)))
+    elif obj is True:
+        out.append(bytes((T_TRUE,)))
+    elif obj is False:
+        out.append(bytes((T_FALSE,)))
+    elif isinstance(obj, int):
+        if -(1 << 63) <= obj < (1 << 63):
+            out.append(bytes((T_INT,)) + struct.pack("<q", obj))
+        else:
+            s = str(obj)
+            out.append(bytes((T_BIGINT,)) + enc_string(s))
+    elif isinstance(obj, float):
+        out.append(bytes((T_FLOAT,)) + struct.pack("<d", obj))
+    elif isinstance(obj, LineRecord):
+        out.append(bytes((T_LINE,)) + enc_string(str(obj)))
+    elif isinstance(obj, str):
+        out.append(bytes((T_STR,)) + enc_string(obj))
+    elif isinstance(obj, (bytes, bytearray)):
+        out.append(bytes((T_BYTES,)) + compact(len(obj)) + bytes(obj))
+    elif isinstance(obj, Grouping):
+        out.append(bytes((T_GROUP,)))
+        encode(obj.key, out)
+        out.append(compact(len(obj)))
+        for x in obj:
+            encode(x, out)
+    elif isinstance(obj, Pair):
+        out.append(bytes((T_PAIR,)))
+        encode(obj[0], out)
+        encode(obj[1], out)
+    elif isinstance(obj, ForkTuple):
+        out.append(bytes((T_FORK,)) + compact(len(obj)))
+        for x in obj:
+            encode(x, out)
+    elif isinstance(obj, Record):
+        out.append(bytes((T_RECORD,)) + compact(len(obj)))
+        for k, v in obj.items():
+            out.append(enc_string(k))
+            encode(v, out)
+    elif isinstance(obj, dict):
+        out.append(bytes((T_DICT,)) + compact(len(obj)))
+        for k, v in obj.items():
+            encode(k, out)
+            encode(v, out)
+    elif isinstance(obj, tuple):
+        out.append(bytes((T_TUPLE,)) + compact(len(obj)))
+        for x in obj:
+            encode(x, out)
+    elif isinstance(obj, list):
+        out.append(bytes((T_LIST,)) + compact(len(obj)))
+        for x in obj:
+            encode(x, out)
+    else:
+        import numpy as np
+        if isinstance(obj, np.integer):
+            encode(int(obj), out)
+        elif isinstance(obj, np.floating):
+            encode(float(obj), out)
+        elif isinstance(obj, np.bool_):
+            encode(bool(obj), out)
+        else:
+            from ..api.errors import DryadLinqException, ErrorCode
+            raise DryadLinqException(ErrorCode.TypeNotSerializable,
+                                     f"records of type {type(obj).__name__} cannot be serialised")
+
+
+def encode_record(obj: Any) -> bytes:
+    out: List[bytes] = []
+    encode(obj, out)
+    return b"".join(out)
+
+
+def _dec_string(buf: memoryview, pos: int) -> Tuple[str, int]:
+    _, pos = read_compact(buf, pos)
+    nb, pos = read_compact(buf, pos)
+    return bytes(buf[pos:pos + nb]).decode("utf-8"), pos + nb
+
+
+def decode(buf: memoryview, pos: int) -> Tuple[Any, int]:
+    t = buf[pos]
+    pos += 1
+    if t == T_NONE:
+        return None, pos
+    if t == T_TRUE:
+        return True, pos
+    if t == T_FALSE:
+        return False, pos
+    if t == T_INT:
+        return struct.unpack_from("<q", buf, pos)[0], pos + 8
+    if t == T_FLOAT:
+        return struct.unpack_from("<d", buf, pos)[0], pos + 8
+    if t == T_STR:
+        return _dec_string(buf, pos)
+    if t == T_LINE:
+        s, pos = _dec_string(buf, pos)
+        return LineRecord(s), pos
+    if t == T_BIGINT:
+        s, pos = _dec_string(buf, pos)
+        return int(s), pos
+    if t == T_BYTES:
+        n, pos = read_compact(buf, pos)
+        return bytes(buf[pos:pos + n]), pos + n
+    if t in (T_TUPLE, T_LIST, T_FORK):
+        n, pos = read_compact(buf, pos)
+        items = []
+        for _ in range(n):
+            v, pos = decode(buf, pos)
+            items.append(v)
+        return (tuple(items) if t == T_TUPLE else ForkTuple(*items) if t == T_FORK else items), pos
+    if t == T_PAIR:
+        a, pos = decode(buf, pos)
+        b, pos = decode(buf, pos)
+        return Pair(a, b), pos
+    if t == T_GROUP:
+        k, pos = decode(buf, pos)
+        n, pos = read_compact(buf, pos)
+        g = Grouping(k)
+        for _ in range(n):
+            v, pos = decode(buf, pos)
+            g.append(v)
+        return g, pos
+    if t == T_RECORD:
+        n, pos = read_compact(buf, pos)
+        r = Record()
+        for _ in range(n):
+            k, pos = _dec_string(buf, pos)
+            v, pos = decode(buf, pos)
+            r[k] = v
+        return r, pos
+    if t == T_DICT:
+        n, pos = read_compact(buf, pos)
+        d = {}
+        for _ in range(n):
+            k, pos = decode(buf, pos)
+            v, pos = decode(buf, pos)
+            d[k] = v
+        return d, pos
+    from ..api.errors import DryadLinqException, ErrorCode
+    raise DryadLinqException(ErrorCode.FailedToDeserialize, f"unknown record tag {t}")

@@ -1,0 +1,167 @@
+"""Partitioned tables on disk ("partfile" scheme) — the storage layer.
+
+Reference: PartitionedFileDataProvider (LinqToDryad/DataProvider.cs:378-538), DataPath URI schemes
+(LinqToDryad/DataPath.cs:36-124), GM-side partfile streams and commit
+(GraphManager/filesystem/DrPartitionFile.cpp:393-402, 561-597).  A table `partfile:///dir/name.pt`
+is a text metadata file (base path, partition count, `index,size` lines) plus one data file
+`<base>.%08X` per partition.  Data files are block streams written by the native writer
+(csrc/host/records.cpp); output is committed atomically: parts are written as `*.tmp`, renamed,
+and the `.pt` file is published last.  `file://...txt` sources read plain text lines as LineRecords.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import json
+import os
+from typing import Any, List, Optional, Sequence
+
+from .. import _native as N
+from ..api.errors import DryadLinqException, ErrorCode
+from ..api.types import LineRecord
+from . import records as R
+
+SCHEMES = ("partfile", "file", "hdfs", "wasb", "azureblob", "hpcdsc")
+
+
+class StoredTable:
+    def __init__(self, partitions: List[Any], schema):
+        self.partitions, self.schema = partitions, schema
+
+
+def parse_uri(uri: str):
+    if "://" not in uri:
+        return "partfile", uri
+    scheme, rest = uri.split("://", 1)
+    if scheme not in SCHEMES:
+        raise DryadLinqException(ErrorCode.UnrecognizedDataSource, f"unknown storage scheme {scheme!r}")
+    if scheme in ("hdfs", "wasb", "azureblob", "hpcdsc"):
+        raise DryadLinqException(ErrorCode.UnrecognizedDataSource,
+                                 f"{scheme}:// needs a cluster file system; this build has none (single box)")
+    path = "/" + rest.lstrip("/") if rest.startswith("/") else rest
+    return scheme, path
+
+
+def exists(uri: str) -> bool:
+    _, path = parse_uri(uri)
+    return os.path.exists(path)
+
+
+def delete(uri: str) -> None:
+    _, path = parse_uri(uri)
+    if not os.path.exists(path):
+        return
+    try:
+        base, n, _ = _read_meta(path)
+        for i in range(n):
+            p = _part_path(base, i)
+            if os.path.exists(p):
+                os.remove(p)
+    except Exception:
+        pass
+    os.remove(path)
+    if os.path.exists(path + ".schema"):
+        os.remove(path + ".schema")
+
+
+def _part_path(base: str, i: int) -> str:
+    buf = C.create_string_buffer(4096)
+    N.host().dh_partfile_part_path(base.encode(), i, buf, 4096)
+    return buf.value.decode()
+
+
+def _read_meta(path: str):
+    lib = N.host()
+    base = C.create_string_buffer(4096)
+    sizes = (C.c_int64 * 65536)()
+    n = lib.dh_partfile_read(path.encode(), base, 4096, sizes, 65536)
+    if n < 0:
+        raise DryadLinqException(ErrorCode.StreamDoesNotExist, f"cannot read partfile {path} ({n})")
+    return base.value.decode(), n, [sizes[i] for i in range(min(n, 65536))]
+
+
+def write_table(uri: str, parts: Sequence[Sequence], schema=None, compression: Optional[str] = None) -> None:
+    scheme, path = parse_uri(uri)
+    lib = N.host()
+    os.makedirs(os.path.dirname(os.path.abspath(path)) or ".", exist_ok=True)
+    base = os.path.splitext(path)[0]
+    comp = 1 if str(compression or "None").lower() in ("gzip", "1", "true") else 0
+    sizes = (C.c_int64 * max(len(parts), 1))()
+    tmp_paths = []
+    try:
+        for i, part in enumerate(parts):
+            final = _part_path(base, i)
+            tmp = final + ".v0.tmp"
+            tmp_paths.append((tmp, final))
+            w = lib.dh_writer_open(tmp.encode(), comp, 0)
+            if not w:
+                raise DryadLinqException(ErrorCode.FailedToCreateStream, f"cannot create {tmp}")
+            recs = part.to_records() if hasattr(part, "to_records") else part
+            for rec in recs:
+                b = R.encode_record(rec)
+                lib.dh_write_bytes(w, b, len(b))
+                rc = lib.dh_writer_end_record(w)
+                if rc:
+                    raise DryadLinqException(ErrorCode.WriteFileError, f"write failed ({rc})")
+            raw, stored, nrec = C.c_int64(), C.c_int64(), C.c_int64()
+            rc = lib.dh_writer_close(w, C.byref(raw), C.byref(stored), C.byref(nrec))
+            if rc:
+                raise DryadLinqException(ErrorCode.WriteFileError, f"close failed ({rc})")
+            sizes[i] = stored.value
+        for tmp, final in tmp_paths:                      # commit the successful part versions
+            if lib.dh_commit_part(tmp.encode(), final.encode()):
+                raise DryadLinqException(ErrorCode.WriteFileError, f"cannot commit {final}")
+        rc = lib.dh_partfile_write(path.encode(), base.encode(), len(parts), sizes, b"")
+        if rc:
+            raise DryadLinqException(ErrorCode.WriteFileError, f"cannot write {path} ({rc})")
+        with open(path + ".schema", "w") as f:
+            json.dump({"schema": schema, "compression": "Gzip" if comp else "None"}, f)
+    except BaseException:
+        for tmp, _ in tmp_paths:                          # failed jobs leave no partial outputs
+            if os.path.exists(tmp):
+                os.remove(tmp)
+        raise
+
+
+def read_partition_file(p: str) -> List:
+    lib = N.host()
+    r = lib.dh_reader_open(p.encode())
+    if not r:
+        raise DryadLinqException(ErrorCode.ReadFileError, f"cannot open {p}")
+    out: List = []
+    ptr = C.POINTER(C.c_uint8)()
+    avail = C.c_int64()
+    try:
+        while True:
+            rc = lib.dh_reader_peek(r, C.byref(ptr), C.byref(avail))
+            if rc < 0:
+                raise DryadLinqException(ErrorCode.FailedToReadFrom, f"corrupt block stream {p} ({rc})")
+            if avail.value == 0:
+                break
+            buf = memoryview(C.string_at(ptr, avail.value))   # whole records only (never straddle)
+            pos = 0
+            n = len(buf)
+            while pos < n:
+                obj, pos = R.decode(buf, pos)
+                out.append(obj)
+            lib.dh_reader_skip(r, avail.value)
+    finally:
+        lib.dh_reader_close(r)
+    return out
+
+
+def open_table(uri: str) -> StoredTable:
+    scheme, path = parse_uri(uri)
+    if not os.path.exists(path):
+        raise DryadLinqException(ErrorCode.StreamDoesNotExist, f"{uri} does not exist")
+    if scheme == "file" or not path.endswith(".pt"):
+        with open(path, "rb") as f:                       # plain text: one LineRecord per line
+            from ..oracle.text import split_lines
+            lines = [LineRecord(l.decode("utf-8")) for l in split_lines(f.read())]
+        return StoredTable([lines], None)
+    base, n, _ = _read_meta(path)
+    schema = None
+    if os.path.exists(path + ".schema"):
+        with open(path + ".schema") as f:
+            schema = json.load(f).get("schema")
+    parts = [read_partition_file(_part_path(base, i)) for i in range(n)]
+    return StoredTable(parts, schema)

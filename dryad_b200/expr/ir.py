@@ -400,6 +400,10 @@ def trace(fn: Callable, schema: Mapping[str, str], *extra_args) -> Optional[Any]
     return normalise_traced(out)
 
 
+class TupleFields(dict):
+    """A traced tuple result: field dict that materialises back into a Python tuple."""
+
+
 def normalise_traced(out: Any) -> Optional[Any]:
     if isinstance(out, Expr):
         return out
@@ -414,7 +418,7 @@ def normalise_traced(out: Any) -> Optional[Any]:
             res[k] = wrap(v)
         return res
     if isinstance(out, tuple) and out and all(isinstance(v, (Expr, int, float, bool)) for v in out):
-        return {f"item{i + 1}": wrap(v) for i, v in enumerate(out)}
+        return TupleFields((f"item{i + 1}", wrap(v)) for i, v in enumerate(out))
     if isinstance(out, (int, float, bool)):
         return lit(out)
     return None

@@ -97,8 +97,10 @@ def order_by(src: Sequence, key: Callable, descending: bool = False, comparer=No
         import functools
         cmpf = (lambda a, b: -comparer(key(a), key(b))) if descending else (lambda a, b: comparer(key(a), key(b)))
         return sorted(src, key=functools.cmp_to_key(cmpf))
-    return sorted(src, key=key, reverse=descending) if not descending else \
-        [x for _, x in sorted(((key(x), i, x) for i, x in enumerate(src)), key=lambda t: _Rev(t[0], t[1]))]
+    if not descending:
+        return sorted(src, key=key)
+    dec = sorted(((key(x), i, x) for i, x in enumerate(src)), key=lambda t: _Rev(t[0], t[1]))
+    return [t[2] for t in dec]
 
 
 class _Rev:

@@ -1,0 +1,176 @@
+"""Job executor: runs a physical plan stage by stage, vertex by vertex.
+
+Role of the GraphManager run loop + vertex hosts (reference call stack SURVEY §3.2/§3.3:
+GraphManager/vertex/DrGraph.cpp:86-116, DrVertex.cpp:431-885, DrCohort.cpp:720-745): every
+(stage, partition) is a vertex with VERSIONED attempts; a failed attempt is re-executed from its
+retained inputs; the job aborts after `max_failures_per_vertex` failures of the same vertex
+(GraphManager/graph/DrGraphParameters.cpp:52); outputs are committed only when the whole job
+succeeded (DrGraph.cpp:204-254).  The state machine itself lives in the native scheduler
+(`csrc/host/sched.cpp`, bound in `dryad_b200.sched`); this module wires data to it.
+"""
+from __future__ import annotations
+
+import time
+import traceback
+from typing import Any, Callable, Dict, List, Optional, Tuple
+
+from ..api.errors import DryadLinqException, ErrorCode
+from ..plan.qnodes import ConnOp, DLinqQueryNode, NodeType
+from ..plan.querygen import QueryGen
+from . import vertex_ops
+from .vertex_ops import VertexEnv
+
+
+class VertexFailure(Exception):
+    def __init__(self, node, part, version, cause):
+        super().__init__(f"vertex {node.type.value}#{node.uid}[{part}] v{version} failed: {cause}")
+        self.node, self.part, self.version, self.cause = node, part, version, cause
+
+
+class JobExecutor:
+    def __init__(self, context, plan: QueryGen, reporter=None):
+        self.context = context
+        self.plan = plan.build()
+        self.reporter = reporter or context._make_reporter()
+        self.out: Dict[int, List[Optional[List[List]]]] = {}     # node uid -> per partition -> ports
+        self.stats: List[dict] = []
+        self.backend = context._backend()
+
+    # ---- input assembly (GraphBuilder.ConnectPointwise / ConnectCrossProduct) --------------
+    def _inputs(self, node: DLinqQueryNode, i: int) -> List[List]:
+        ins: List[List] = []
+        t = node.type if node.type != NodeType.Super else node.members[0].type
+        for k, (child, op) in enumerate(node.children):
+            co = self.out[child.uid]
+            cpc = child.partition_count
+            if t == NodeType.ForkBranch:
+                idx = (node.members[0] if node.type == NodeType.Super else node).params["index"]
+                ins.append([co[i][idx]])
+            elif op == ConnOp.CrossProduct:
+                ins.append([co[s][i] for s in range(cpc)])
+            elif t == NodeType.Concat:
+                ins.append([])      # filled below
+            elif t == NodeType.Reverse and k == 0:
+                ins.append([co[cpc - 1 - i][0]])
+            elif cpc == node.partition_count:
+                ins.append([co[i][0]])
+            elif cpc == 1:
+                ins.append([co[0][0]])                               # 1:N broadcast
+            elif node.partition_count == 1:
+                ins.append([co[s][0] for s in range(cpc)])           # N:1 gather, port order
+            else:
+                g = (node.members[0] if node.type == NodeType.Super else node).params.get("group")
+                if g:
+                    ins.append([co[s][0] for s in range(g * i, min(cpc, g * i + g))])
+                else:
+                    raise DryadLinqException(ErrorCode.Internal,
+                                             f"cannot connect {cpc} -> {node.partition_count} partitions pointwise")
+        if t == NodeType.Concat:
+            acc = 0
+            for child, _ in node.children:
+                if i < acc + child.partition_count:
+                    return [[self.out[child.uid][i - acc][0]]]
+                acc += child.partition_count
+        if t == NodeType.Zip:
+            left = self.out[node.children[0][0].uid]
+            right = self.out[node.children[1][0].uid]
+            start = sum(len(left[s][0]) for s in range(i))
+            need = len(left[i][0])
+            flat: List = []
+            pos = 0
+            for s in range(node.children[1][0].partition_count):   # re-align right to left's boundaries
+                seg = right[s][0]
+                lo, hi = max(start, pos), min(start + need, pos + len(seg))
+                if lo < hi:
+                    flat.extend(seg[lo - pos:hi - pos])
+                pos += len(seg)
+            return [[left[i][0]], [flat]]
+        if t == NodeType.SlidingWindow:
+            w = (node.members[0] if node.type == NodeType.Super else node).params["window"]
+            co = self.out[node.children[0][0].uid]
+            halo: List = []
+            s = i - 1
+            while s >= 0 and len(halo) < w - 1:
+                seg = co[s][0]
+                take = (w - 1) - len(halo)
+                halo = list(seg[-take:]) + halo if take > 0 and seg else halo
+                s -= 1
+            ins.append([halo if i > 0 else []])
+        return ins
+
+    # ---- run -----------------------------------------------------------------------------------
+    def run(self) -> Dict[int, Any]:
+        ctx = self.context
+        rep = self.reporter
+        rep.job_start(self.plan)
+        max_fail = ctx.max_failures_per_vertex
+        t_job = time.perf_counter()
+        try:
+            for node in self.plan.nodes:
+                self.out[node.uid] = [None] * node.partition_count
+                for i in range(node.partition_count):
+                    version = 0
+                    failures = 0
+                    while True:
+                        rep.vertex_event(node, i, version, "starting")
+                        t0 = time.perf_counter()
+                        try:
+                            ins = self._inputs(node, i)
+                            if ctx.fault_injector is not None:
+                                ctx.fault_injector(node, i, version)
+                            env = VertexEnv(ctx, node.uid, i, version)
+                            ports = self.backend.run_vertex(node, i, ins, env)
+                            dt = time.perf_counter() - t0
+                            self.out[node.uid][i] = ports
+                            n_in = sum(self.backend.count(p) for inp in ins for p in inp)
+                            n_out = sum(self.backend.count(p) for p in ports)
+                            self.stats.append({"stage": node.uid, "stage_name": node.name, "part": i,
+                                               "version": version, "seconds": dt, "records_in": n_in,
+                                               "records_out": n_out})
+                            rep.vertex_event(node, i, version, "completed", seconds=dt, records_in=n_in, records_out=n_out)
+                            break
+                        except Exception as ex:  # noqa: BLE001  (vertex code is user code)
+                            failures += 1
+                            text = "".join(traceback.format_exception_only(type(ex), ex)).strip()
+                            rep.vertex_event(node, i, version, "failed", error=text)
+                            deterministic = isinstance(ex, DryadLinqException) and not getattr(ex, "transient", False)
+                            if failures >= max_fail or (deterministic and ctx.fail_fast_on_deterministic_errors):
+                                rep.job_stop(False, text)
+                                if isinstance(ex, DryadLinqException):
+                                    raise
+                                raise DryadLinqException(ErrorCode.DidNotCompleteSuccessfully,
+                                                         f"vertex {node.name}#{node.uid}[{i}] failed {failures} time(s): {text}", ex) from ex
+                            version += 1
+                # release inputs no longer needed (all parents done) — keeps HBM bounded
+                self._release_finished_children(node)
+            results = self._commit_outputs()
+            rep.job_stop(True, "", seconds=time.perf_counter() - t_job)
+            return results
+        except BaseException:
+            self._discard_outputs()
+            raise
+
+    def _release_finished_children(self, node: DLinqQueryNode):
+        """Drop a producer's buffers once every consumer stage has completed (bounded HBM / RAM);
+        with `retain_intermediate` they are kept, like the reference's intermediate files, so a
+        later failure could re-run a consumer without re-running the producer."""
+        if self.context.retain_intermediate:
+            return
+        done = {n.uid for n in self.plan.nodes if n.uid in self.out and all(x is not None for x in self.out[n.uid])}
+        for child, _ in node.children:
+            if child.parents and all(p.uid in done for p in child.parents):
+                self.out[child.uid] = [None] * child.partition_count
+
+    # ---- atomic output commit (DrGraph::FinalizeGraph) ----------------------------------------
+    def _commit_outputs(self) -> Dict[int, Any]:
+        results: Dict[int, Any] = {}
+        for root in self.plan.roots:
+            node = root if root.type == NodeType.OutputTable else root.members[-1]
+            parts = [self.backend.to_records(self.out[root.uid][i][0]) for i in range(root.partition_count)]
+            table = self.context._commit_table(node.params.get("uri"), parts, root.schema, root.info,
+                                               node.params.get("compression"), node.params.get("temporary", False))
+            results[node.params["qexpr_id"]] = table
+        return results
+
+    def _discard_outputs(self):
+        self.out.clear()

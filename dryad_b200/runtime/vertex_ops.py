@@ -1,0 +1,461 @@
+"""Host vertex runtime: the executable semantics of every physical operator over Python record
+lists — the role of the reference's operator library DryadLinqVertex
+(LinqToDryad/DryadLinqVertex.cs:51-5311) and helper bodies (LinqToDryad/DryadLinqHelper.cs:38-458).
+
+This is the general path (any Python record type, opaque lambdas).  Stages whose lambdas traced
+to column expressions over numeric columns run on the GPU through `runtime/gpu_ops.py` instead;
+both produce the same records, which is what the differential tests check.
+
+Contract: `run(node, part_index, inputs, env) -> [port0, port1, ...]` where `inputs[k]` is the
+list of channel payloads arriving on child edge k (one payload per producer for merging edges).
+"""
+from __future__ import annotations
+
+from typing import Any, Callable, Dict, List, Sequence
+
+from ..api.errors import DryadLinqException, ErrorCode
+from ..oracle import linq as L
+from ..oracle.sampler import phase1_sample, range_bucket, select_separators
+from ..plan.qnodes import DLinqQueryNode, NodeType
+from ..utils.hashing import hash_bucket
+
+
+def _cat(payloads: Sequence[Sequence]) -> List:
+    out: List = []
+    for p in payloads:
+        out.extend(p)
+    return out
+
+
+def _kfn(lam) -> Callable:
+    return lam.fn if lam is not None and lam.fn is not None else (lambda x: x)
+
+
+class VertexEnv:
+    """Per-vertex environment (LinqToDryad/VertexEnv.cs:34-367): ids, partition index, context."""
+
+    def __init__(self, context, vertex_id: int, part: int, version: int = 0):
+        self.context, self.vertex_id, self.part, self.version = context, vertex_id, part, version
+
+
+def run(node: DLinqQueryNode, part: int, inputs: List[List], env: VertexEnv) -> List[List]:
+    if node.type == NodeType.Super:
+        cur = inputs
+        out: List[List] = []
+        for m in node.members:
+            out = run(m, part, cur, env)
+            cur = [[out[0]]]
+        return out
+    fn = _DISPATCH.get(node.type)
+    if fn is None:
+        raise DryadLinqException(ErrorCode.OperatorNotSupported, f"no vertex code for {node.type}")
+    return fn(node, part, inputs, env)
+
+
+# ---- sources / sinks / plumbing ----------------------------------------------------------------
+def _input(node, part, inputs, env):
+    return [env.context._read_table_partition(node.params["table"], part)]
+
+
+def _output(node, part, inputs, env):
+    return [_cat(inputs[0])]
+
+
+def _identity(node, part, inputs, env):
+    return [_cat(inputs[0])]
+
+
+def _merge(node, part, inputs, env):
+    p = node.params
+    if p.get("sort_key") is not None:
+        import heapq
+        key = _kfn(p["sort_key"])
+        runs = [list(r) for r in inputs[0]]
+        return [list(heapq.merge(*runs, key=key, reverse=bool(p.get("descending"))))]
+    return [_cat(inputs[0])]           # port order is preserved (keepPortOrder)
+
+
+def _tee(node, part, inputs, env):
+    data = _cat(inputs[0])
+    if node.params.get("replicate"):
+        return [data for _ in range(node.n_out_ports)]
+    return [data]
+
+
+def _concat(node, part, inputs, env):
+    return [_cat(inputs[0])]
+
+
+def _fork_branch(node, part, inputs, env):
+    return [_cat(inputs[0])]
+
+
+# ---- element-wise ---------------------------------------------------------------------------------
+def _start_index(inputs) -> int:
+    side = _cat(inputs[1])
+    return int(side[0]) if side else 0
+
+
+def _select(node, part, inputs, env):
+    p = node.params
+    src = _cat(inputs[0])
+    if p.get("finalize") is not None:
+        dec = p["finalize"]
+        return [[dec.final(k, accs) for k, accs in src]]
+    if p["indexed"]:
+        s = _start_index(inputs)
+        f = p["fn"].fn
+        return [[f(x, s + i) for i, x in enumerate(src)]]
+    return [L.select(src, p["fn"].fn)]
+
+
+def _where(node, part, inputs, env):
+    p = node.params
+    src = _cat(inputs[0])
+    if p["indexed"]:
+        s = _start_index(inputs)
+        f = p["fn"].fn
+        return [[x for i, x in enumerate(src) if f(x, s + i)]]
+    return [L.where(src, p["fn"].fn)]
+
+
+def _select_many(node, part, inputs, env):
+    p = node.params
+    src = _cat(inputs[0])
+    res = p["result"].fn if p.get("result") else None
+    if p["indexed"]:
+        s = _start_index(inputs)
+        out = []
+        for i, x in enumerate(src):
+            for y in p["fn"].fn(x, s + i):
+                out.append(res(x, y) if res else y)
+        return [out]
+    return [L.select_many(src, p["fn"].fn, res)]
+
+
+# ---- distributors -----------------------------------------------------------------------------------
+def _hash_partition(node, part, inputs, env):
+    p = node.params
+    n = p["nports"]
+    key = _kfn(p["key"])
+    ports: List[List] = [[] for _ in range(n)]
+    for x in _cat(inputs[0]):
+        ports[hash_bucket(key(x), n)].append(x)       # (hash & 0x7FFFFFFF) % nPorts
+    return ports
+
+
+def _range_partition(node, part, inputs, env):
+    p = node.params
+    n = p["nports"]
+    key = _kfn(p["key"])
+    seps = p["range_keys"] if p.get("range_keys") is not None else _cat(inputs[1])
+    if len(seps) > n - 1:
+        raise DryadLinqException(ErrorCode.RangePartitionInputOutputMismatch,
+                                 f"{len(seps)} range keys for {n} ports")
+    desc = bool(p["descending"])
+    cmp = p.get("comparer")
+    ports: List[List] = [[] for _ in range(n)]
+    if cmp is None:
+        for x in _cat(inputs[0]):
+            ports[range_bucket(key(x), seps, desc)].append(x)
+    else:
+        for x in _cat(inputs[0]):
+            k = key(x)
+            lo, hi = 0, len(seps)
+            while lo < hi:
+                mid = (lo + hi) // 2
+                c = cmp(seps[mid], k)
+                if (c > 0) if desc else (c < 0):
+                    lo = mid + 1
+                else:
+                    hi = mid
+            ports[lo].append(x)
+    return ports
+
+
+def _sampler(node, part, inputs, env):
+    key = _kfn(node.params["key"])
+    return [phase1_sample([key(x) for x in _cat(inputs[0])], seed=env.vertex_id * 1000 + part,
+                          rate=env.context.sample_rate)]
+
+
+def _range_sampler(node, part, inputs, env):
+    p = node.params
+    samples = _cat(inputs[0])
+    cmp = p.get("comparer")
+    if cmp is not None:
+        import functools
+        samples = sorted(samples, key=functools.cmp_to_key(cmp))
+    else:
+        samples = sorted(samples)
+    return [select_separators(samples, p["pcount"], bool(p["descending"]))]
+
+
+def _offsets(node, part, inputs, env):
+    counts = _cat(inputs[0])
+    offs = L.offsets(counts)
+    n = node.params["nports"]
+    return [[offs[i]] if i < len(offs) else [0] for i in range(n)]
+
+
+# ---- stateful operators --------------------------------------------------------------------------------
+def _order_by(node, part, inputs, env):
+    p = node.params
+    return [L.order_by(_cat(inputs[0]), _kfn(p["key"]), bool(p["descending"]), p.get("comparer"))]
+
+
+def _group_by(node, part, inputs, env):
+    p = node.params
+    src = _cat(inputs[0])
+    mode = p["mode"]
+    key = _kfn(p["key"])
+    elem = p["elem"].fn if p.get("elem") is not None else None
+    if mode == "full":
+        groups = L.group_by(src, key, elem)
+        if p.get("result") is not None:
+            r = p["result"].fn
+            return [[r(g.key, g) for g in groups]]
+        return [groups]
+    dec = p["decomp"]
+    table: Dict[Any, list] = {}
+    keys: Dict[Any, Any] = {}
+    if mode in ("partial_acc", "full_acc"):
+        for x in src:
+            k = key(x)
+            hk = L._hashable(k)
+            v = elem(x) if elem else x
+            accs = table.get(hk)
+            if accs is None:
+                table[hk] = [a.seed(v) for a in dec.aggs]
+                keys[hk] = k
+            else:
+                for j, a in enumerate(dec.aggs):
+                    accs[j] = a.accumulate(accs[j], v)
+    else:  # final_acc: combine partial (key, accs) pairs
+        for k, paccs in src:
+            hk = L._hashable(k)
+            accs = table.get(hk)
+            if accs is None:
+                table[hk] = list(paccs)
+                keys[hk] = k
+            else:
+                for j, a in enumerate(dec.aggs):
+                    accs[j] = a.combine(accs[j], paccs[j])
+    return [[(keys[hk], accs) for hk, accs in table.items()]]
+
+
+def _join(node, part, inputs, env):
+    p = node.params
+    outer, inner = _cat(inputs[0]), _cat(inputs[1])
+    ok, ik, res = _kfn(p["outer_key"]), _kfn(p["inner_key"]), p["result"].fn
+    if node.type == NodeType.GroupJoin:
+        return [L.group_join(outer, inner, ok, ik, res)]
+    if p.get("algorithm") == "merge":
+        return [_merge_join(outer, inner, ok, ik, res, bool(p.get("descending")))]
+    return [L.join(outer, inner, ok, ik, res)]
+
+
+def _merge_join(outer, inner, ok, ik, res, desc):
+    """Co-iterate two key-sorted inputs (DryadLinqVertex.MergeJoin :898-1030)."""
+    out = []
+    i = j = 0
+    lt = (lambda a, b: a > b) if desc else (lambda a, b: a < b)
+    while i < len(outer) and j < len(inner):
+        ko, ki = ok(outer[i]), ik(inner[j])
+        if lt(ko, ki):
+            i += 1
+        elif lt(ki, ko):
+            j += 1
+        else:
+            j2 = j
+            while j2 < len(inner) and ik(inner[j2]) == ko:
+                j2 += 1
+            while i < len(outer) and ok(outer[i]) == ko:
+                for jj in range(j, j2):
+                    out.append(res(outer[i], inner[jj]))
+                i += 1
+            j = j2
+    return out
+
+
+def _distinct(node, part, inputs, env):
+    return [L.distinct(_cat(inputs[0]))]
+
+
+def _set_operation(node, part, inputs, env):
+    a, b = _cat(inputs[0]), _cat(inputs[1])
+    op = node.params["op"]
+    return [{"union": L.union, "intersect": L.intersect, "except": L.except_}[op](a, b)]
+
+
+def _partition_op(node, part, inputs, env):
+    p = node.params
+    src = _cat(inputs[0])
+    op = p["op"]
+    if op == "take":
+        return [L.take(src, p["n"])]
+    if op == "skip":
+        return [L.skip(src, p["n"])]
+    f = p["fn"].fn
+    if op == "take_while":
+        return [L.take_while(src, f, p.get("indexed", False))]
+    return [L.skip_while(src, f, p.get("indexed", False))]
+
+
+def _zip(node, part, inputs, env):
+    return [L.zip_(_cat(inputs[0]), _cat(inputs[1]), node.params["fn"].fn)]
+
+
+def _reverse(node, part, inputs, env):
+    return [L.reverse(_cat(inputs[0]))]
+
+
+def _sliding_window(node, part, inputs, env):
+    # inputs[1] = halo: the last w-1 records preceding this partition (neighbour exchange, C6)
+    p = node.params
+    w = p["window"]
+    halo = _cat(inputs[1]) if len(inputs) > 1 else []
+    data = halo + _cat(inputs[0])
+    f = p["fn"].fn
+    return [[f(list(data[i:i + w])) for i in range(0, len(data) - w + 1)]] if w > 0 else [[]]
+
+
+# ---- aggregates ---------------------------------------------------------------------------------------------
+_EMPTY = ("__empty__",)
+
+
+def _basic_aggregate(node, part, inputs, env):
+    p = node.params
+    kind, stage = p["kind"], p["stage"]
+    src = _cat(inputs[0])
+    fn = p["fn"].fn if p.get("fn") is not None else None
+    if kind == "sequence_equal":
+        return [[L.sequence_equal(src, _cat(inputs[1]))]]
+    if kind == "any_true":
+        return [[any(src)]]
+    if stage == 1:
+        vals = src
+        if kind == "count":
+            return [[L.count(vals, fn)]]
+        if kind in ("sum", "min", "max", "average"):
+            vals = [fn(x) for x in vals] if fn else vals
+            if kind == "sum":
+                return [[L.sum_(vals)]]
+            if not vals:
+                return [[]]
+            if kind == "min":
+                return [[min(vals)]]
+            if kind == "max":
+                return [[max(vals)]]
+            s = 0
+            for v in vals:
+                s = L.checked_add(s, v) if isinstance(v, int) else s + v
+            return [[(s, len(vals))]]
+        if kind == "any":
+            return [[L.any_(vals, fn)]]
+        if kind == "all":
+            return [[L.all_(vals, fn)]]
+        m = [x for x in vals if fn is None or fn(x)]
+        if kind == "first":
+            return [m[:1]]
+        if kind == "last":
+            return [m[-1:]]
+        if kind == "single":
+            return [m[:2]]
+        raise DryadLinqException(ErrorCode.AggregateOperatorNotSupported, kind)
+    # stage 2: combine partials (one value per non-empty partition, in port order)
+    if kind == "count" or kind == "sum":
+        return [[L.sum_(src)]]
+    if kind == "any":
+        return [[any(src)]]
+    if kind == "all":
+        return [[all(src)]]
+    try:
+        if kind == "min":
+            return [[L.min_(src)]]
+        if kind == "max":
+            return [[L.max_(src)]]
+        if kind == "average":
+            if not src:
+                raise ValueError("Sequence contains no elements (Average)")
+            s, c = 0, 0
+            for ps, pc in src:
+                s = L.checked_add(s, ps) if isinstance(ps, int) else s + ps
+                c += pc
+            return [[s / c]]
+        if kind == "first":
+            return [[L.first(src, None, p["default"])]]
+        if kind == "last":
+            return [[L.last(src, None, p["default"])]]
+        if kind == "single":
+            return [[L.single(src, None, p["default"])]]
+    except ValueError as ex:
+        code = {"min": ErrorCode.MinNoElements, "max": ErrorCode.MaxNoElements,
+                "average": ErrorCode.AverageNoElements, "first": ErrorCode.FirstNoElementsFirst,
+                "last": ErrorCode.LastNoElements, "single": ErrorCode.SingleNoElements}[kind]
+        if kind == "single" and "more than one" in str(ex):
+            code = ErrorCode.SingleMoreThanOneElement
+        raise DryadLinqException(code, str(ex)) from ex
+    raise DryadLinqException(ErrorCode.AggregateOperatorNotSupported, kind)
+
+
+def _contains(node, part, inputs, env):
+    return [[L.contains(_cat(inputs[0]), node.params["value"])]]
+
+
+def _aggregate(node, part, inputs, env):
+    p = node.params
+    src = _cat(inputs[0])
+    f = p["fn"].fn
+    stage = p["stage"]
+    if stage in (1, 2):
+        if not src:
+            if stage == 2:
+                raise DryadLinqException(ErrorCode.AggregateNoElements, "Sequence contains no elements (Aggregate)")
+            return [[]]
+        return [[L.aggregate(src, f)]]
+    seed = p["seed_fn"]() if p.get("seed_fn") else p.get("seed")
+    try:
+        return [[L.aggregate(src, f, seed, p["has_seed"], p["result"].fn if p.get("result") else None)]]
+    except ValueError as ex:
+        raise DryadLinqException(ErrorCode.AggregateNoElements, str(ex)) from ex
+
+
+# ---- apply / fork -------------------------------------------------------------------------------------------------
+def _apply(node, part, inputs, env):
+    p = node.params
+    f = p["fn"].fn
+    a = _cat(inputs[0])
+    try:
+        if p.get("with_index"):
+            return [list(f(a, part))]
+        if len(inputs) > 1:
+            return [list(f(a, _cat(inputs[1])))]
+        return [list(f(a))]
+    except DryadLinqException:
+        raise
+    except Exception as ex:
+        raise DryadLinqException(ErrorCode.FailureInUserApplyFunction, f"{type(ex).__name__}: {ex}", ex) from ex
+
+
+def _fork(node, part, inputs, env):
+    p = node.params
+    src = _cat(inputs[0])
+    if p["per_partition"]:
+        outs = p["fn"].fn(src)
+        return [list(o) for o in outs]
+    return [list(o) for o in L.fork(src, p["fn"].fn, p["n"])]
+
+
+_DISPATCH = {
+    NodeType.InputTable: _input, NodeType.OutputTable: _output, NodeType.Dummy: _identity,
+    NodeType.Merge: _merge, NodeType.Tee: _tee, NodeType.Concat: _concat, NodeType.ForkBranch: _fork_branch,
+    NodeType.Select: _select, NodeType.Where: _where, NodeType.SelectMany: _select_many,
+    NodeType.HashPartition: _hash_partition, NodeType.RangePartition: _range_partition,
+    NodeType.Sampler: _sampler, NodeType.RangeSampler: _range_sampler, NodeType.Offsets: _offsets,
+    NodeType.OrderBy: _order_by, NodeType.GroupBy: _group_by, NodeType.Join: _join, NodeType.GroupJoin: _join,
+    NodeType.Distinct: _distinct, NodeType.SetOperation: _set_operation, NodeType.PartitionOp: _partition_op,
+    NodeType.Zip: _zip, NodeType.Reverse: _reverse, NodeType.SlidingWindow: _sliding_window,
+    NodeType.BasicAggregate: _basic_aggregate, NodeType.Contains: _contains, NodeType.Aggregate: _aggregate,
+    NodeType.Apply: _apply, NodeType.Fork: _fork,
+}
