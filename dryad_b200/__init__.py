@@ -8,6 +8,7 @@ from .api.context import (CompressionScheme, DryadLinqContext, DryadLinqJobInfo,
 from .api.decomposable import IAssociative, IDecomposable, associative, decomposable, resource
 from .api.errors import DryadLinqException, ErrorCategory, ErrorCode
 from .api.query import KeyedMultiQuery, MultiQuery, Query
+from .api.rows import RowKey
 from .api.types import AggregateValue, ForkTuple, Grouping, LineRecord, Pair, Record
 from .expr import col, lit, where
 
@@ -16,5 +17,5 @@ __all__ = [
     "DryadLinqContext", "DryadLinqJobInfo", "JobStatus", "PlatformKind", "QueryLoggingLevel", "CompressionScheme",
     "Table", "IDecomposable", "IAssociative", "decomposable", "associative", "resource", "DryadLinqException",
     "ErrorCode", "ErrorCategory", "Query", "MultiQuery", "KeyedMultiQuery", "Record", "Pair", "LineRecord",
-    "ForkTuple", "Grouping", "AggregateValue", "col", "lit", "where",
+    "RowKey", "ForkTuple", "Grouping", "AggregateValue", "col", "lit", "where",
 ]

@@ -142,10 +142,18 @@ class DryadLinqContext:
         self.fail_fast_on_deterministic_errors = False
         self.retain_intermediate = True
         self.sample_rate = SC.SAMPLE_RATE
+        self.group_capacity_hint = 1 << 26     # max initial hash-aggregate table slots per vertex
         self.broadcast_join_rows = 1 << 20     # planner rule: inner side at most this many rows -> broadcast join
         self.fault_injector: Optional[Callable] = None
         self.work_dir = work_dir or os.environ.get("DRYAD_HOME") or os.path.join(tempfile.gettempdir(), "DRYADLINQ",
                                                                                 f"app_{os.getpid()}")
+        # SPMD placement (platform B200: one process per GPU under torch.distributed)
+        self.rank = int(os.environ.get("RANK", "0")) if self.platform == PlatformKind.B200 else 0
+        self.world = int(os.environ.get("WORLD_SIZE", "1")) if self.platform == PlatformKind.B200 else 1
+        if self.platform == PlatformKind.B200:
+            self.num_partitions = self.world
+        self._arena = None
+        self._sorters: Dict[tuple, Any] = {}
         self._disposed = False
         self._frozen = False
         self._tables: Dict[int, Table] = {}
@@ -190,6 +198,9 @@ class DryadLinqContext:
         DryadLinqContext.cs:1210-1223) the data lands in ONE partition unless a count is given."""
         self._check_not_disposed()
         rows = list(data)
+        if rows and type(rows[0]) is dict:          # plain dict records get attribute access (r.field)
+            from .types import Record
+            rows = [Record(r) if type(r) is dict else r for r in rows]
         n = int(num_partitions) if num_partitions else 1
         parts: List[List] = [[] for _ in range(n)]
         per = (len(rows) + n - 1) // n if rows else 0
@@ -223,12 +234,25 @@ class DryadLinqContext:
         parts = batch.split(n)
         return self._from_table(Table(parts, batch.schema, None, None, True))
 
+    def from_rows(self, rows, num_partitions: Optional[int] = None, key_off: int = 0, key_len: int = 10) -> Query:
+        """Fixed-width byte records: `rows` is a [n, width] uint8 torch tensor (pinned host memory
+        or HBM).  Each partition is a zero-copy slice; the GPU backend uploads it on first use."""
+        self._check_not_disposed()
+        from ..runtime.columnar import ColumnBatch
+        if self.world > 1:                    # SPMD: `rows` is THIS rank's partition
+            parts: List[Any] = [None] * self.world
+            parts[self.rank] = ColumnBatch.rows(rows, key_off, key_len)
+            return self._from_table(Table(parts, {"row": "o"}, None, None, True))
+        n = int(num_partitions) if num_partitions else 1
+        parts = ColumnBatch.rows(rows, key_off, key_len).split(n)
+        return self._from_table(Table(parts, {"row": "o"}, None, None, True))
+
     def _from_table(self, table: Table, uri: Optional[str] = None) -> Query:
         pc = max(1, table.partition_count)
         rows = None
         if table.partitions is not None:
             try:
-                rows = sum(len(p) for p in table.partitions)
+                rows = sum(len(p) for p in table.partitions if p is not None)
             except TypeError:
                 rows = None
         e = QExpr("source", [], table.schema, table=table, partition_count=pc, uri=uri,
@@ -271,6 +295,30 @@ class DryadLinqContext:
     def _backend(self):
         from ..runtime.backends import get_backend
         return get_backend(self)
+
+    def _spmd_arena(self):
+        """The per-context symmetric arena (allocated on first use, identical on every rank)."""
+        if self._arena is None:
+            import torch
+            from ..parallel.symm import SymmetricArena
+            free, _total = torch.cuda.mem_get_info()
+            nbytes = int(os.environ.get("DRYAD_ARENA_BYTES", min(free // 3, 48 << 30)))
+            self._arena = SymmetricArena(nbytes, self.rank, self.world, None, self.device)
+        return self._arena
+
+    def _row_sorter(self, max_rows: int, width: int, key_off: int, key_len: int, descending: bool):
+        sig = (width, key_off, key_len, descending)
+        cur = self._sorters.get(sig)
+        if cur is None or cur.max_rows < max_rows:
+            from ..parallel.dsort import RowSorter
+            arena = self._spmd_arena()
+            if cur is not None:
+                arena.release_to(cur._arena_mark)
+            mark = arena.mark()
+            cur = RowSorter(arena, max_rows, width, key_off=key_off, key_len=key_len, descending=descending)
+            cur._arena_mark = mark
+            self._sorters[sig] = cur
+        return cur
 
     def _make_reporter(self):
         from ..sched.reporting import CalypsoReporter
@@ -319,7 +367,11 @@ class DryadLinqContext:
                 from ..plan.querygen import QueryGen
                 from ..runtime.executor import JobExecutor
                 plan = QueryGen(self, roots)
-                ex = JobExecutor(self, plan)
+                if self.world > 1:
+                    from ..runtime.spmd import SpmdExecutor
+                    ex = SpmdExecutor(self, plan)
+                else:
+                    ex = JobExecutor(self, plan)
                 tables = ex.run()
                 self.last_job_stats = ex.stats
                 self.last_plan = plan

@@ -38,3 +38,24 @@ def validate_sorted(rows_cpu: torch.Tensor) -> bool:
     a = rows_cpu[:, :KEY_BYTES].numpy()
     keys = [bytes(r) for r in a]
     return all(x <= y for x, y in zip(keys, keys[1:]))
+
+
+def validate(result_query) -> list:
+    """TeraValidate-style summary of a sorted result held by this process: [order violations,
+    wrapping key checksum, row count].  Reads 24 bytes back from the device."""
+    from ..ops import core as K
+    t = result_query.expr.params["table"]
+    total = None
+    rows_n = 0
+    for p in t.partitions:
+        if p is None or len(p) == 0:
+            continue
+        rows = p.cols["row"]
+        off, ln = p.key_spec or (0, KEY_BYTES)
+        r = K.check_sorted_rows(rows.contiguous(), off, ln)
+        total = r if total is None else total + r
+        rows_n += rows.shape[0]
+    if total is None:
+        return [0, 0, 0]
+    host = total.cpu()
+    return [int(host[0]), int(host[1]) & ((1 << 64) - 1), rows_n]

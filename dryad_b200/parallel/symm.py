@@ -46,7 +46,10 @@ class SymmetricArena:
 
     def __init__(self, nbytes: int, rank: int = 0, world: int = 1, group=None, device=None):
         self.rank, self.world, self.group = rank, world, group
-        self.device = torch.device(device if device is not None else f"cuda:{torch.cuda.current_device()}")
+        d = torch.device(device if device is not None else "cuda")
+        if d.index is None:
+            d = torch.device("cuda", torch.cuda.current_device())
+        self.device = d
         self.nbytes = int((nbytes + 511) // 512 * 512)
         lib = N.kernels()
         torch.cuda.set_device(self.device)

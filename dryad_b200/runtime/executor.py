@@ -72,8 +72,9 @@ class JobExecutor:
                     return [[self.out[child.uid][i - acc][0]]]
                 acc += child.partition_count
         if t == NodeType.Zip:
-            left = self.out[node.children[0][0].uid]
-            right = self.out[node.children[1][0].uid]
+            tr = self.backend.to_records
+            left = [[tr(p[0])] for p in self.out[node.children[0][0].uid]]
+            right = [[tr(p[0])] for p in self.out[node.children[1][0].uid]]
             start = sum(len(left[s][0]) for s in range(i))
             need = len(left[i][0])
             flat: List = []
@@ -87,7 +88,7 @@ class JobExecutor:
             return [[left[i][0]], [flat]]
         if t == NodeType.SlidingWindow:
             w = (node.members[0] if node.type == NodeType.Super else node).params["window"]
-            co = self.out[node.children[0][0].uid]
+            co = [[self.backend.to_records(p[0])] for p in self.out[node.children[0][0].uid]]
             halo: List = []
             s = i - 1
             while s >= 0 and len(halo) < w - 1:
@@ -166,7 +167,7 @@ class JobExecutor:
         results: Dict[int, Any] = {}
         for root in self.plan.roots:
             node = root if root.type == NodeType.OutputTable else root.members[-1]
-            parts = [self.backend.to_records(self.out[root.uid][i][0]) for i in range(root.partition_count)]
+            parts = [self.out[root.uid][i][0] for i in range(root.partition_count)]   # batches stay columnar
             table = self.context._commit_table(node.params.get("uri"), parts, root.schema, root.info,
                                                node.params.get("compression"), node.params.get("temporary", False))
             results[node.params["qexpr_id"]] = table

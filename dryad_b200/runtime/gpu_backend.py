@@ -1,0 +1,492 @@
+"""GPU vertex runtime: physical operators over ColumnBatch partitions with the sm_100a kernels.
+
+Counterpart of the host operator library for stages whose lambdas traced to column expressions
+(reference operator semantics: LinqToDryad/DryadLinqVertex.cs; kernel inventory SURVEY §2.15).
+A vertex whose operator, lambdas or payloads are not GPU-expressible runs on the host path for
+that vertex only (records), and its output is re-columnarised when the schema allows.
+"""
+from __future__ import annotations
+
+from typing import Any, Dict, List, Optional, Sequence
+
+import torch
+
+from ..api.errors import DryadLinqException, ErrorCode
+from ..expr import ir as X
+from ..expr.compile import CompileError, run_on_gpu
+from ..ops import core as K
+from ..plan.qnodes import DLinqQueryNode, NodeType
+from . import vertex_ops
+from .columnar import ROW_COL, ColumnBatch
+
+
+def _numeric_schema(schema) -> bool:
+    return bool(schema) and all(k in ("i", "f", "b") for k in schema.values())
+
+
+def _bind_leaves(e: X.Expr, agg_kinds: Sequence[str]) -> X.Expr:
+    """Replace `agg` leaves by columns agg<i> and key references by key columns."""
+    if e.op == "agg":
+        i = e.args[0]
+        return X.col(f"agg{i}", agg_kinds[i])
+    if e.op in ("col", "lit", "rowid"):
+        return e
+    return X.Expr(e.op, tuple(_bind_leaves(a, agg_kinds) if isinstance(a, X.Expr) else a for a in e.args), e.kind)
+
+
+class GpuBackend:
+    name = "gpu"
+    wants_records = False
+
+    def __init__(self, context):
+        self.context = context
+        self.device = torch.device(context.device)
+        K.N.kernels()                      # fail loudly when the CUDA library is missing
+        self.host_fallbacks = 0
+        self._arena = None
+
+    # ---- plumbing ------------------------------------------------------------------------------
+    @staticmethod
+    def count(payload) -> int:
+        try:
+            return len(payload)
+        except TypeError:
+            return 0
+
+    @staticmethod
+    def to_records(payload):
+        return payload.to_records() if hasattr(payload, "to_records") else payload
+
+    def _columnar(self, payload, schema) -> Any:
+        if isinstance(payload, ColumnBatch):
+            return payload if payload.device.type == "cuda" else payload.to(self.device, non_blocking=True)
+        if _numeric_schema(schema) and isinstance(payload, list):
+            if payload and isinstance(payload[0], tuple) and len(schema) > 1:
+                b = ColumnBatch.from_records(payload, schema, self.device)
+                b.tuple_like = True
+                return b
+            try:
+                return ColumnBatch.from_records(payload, schema, self.device)
+            except Exception:  # noqa: BLE001
+                return payload
+        return payload
+
+    def run_vertex(self, node: DLinqQueryNode, part: int, inputs, env):
+        if node.type == NodeType.Super:
+            cur = inputs
+            out = None
+            for m in node.members:
+                out = self._run_one(m, part, cur, env)
+                cur = [[out[0]]]
+            return out
+        return self._run_one(node, part, inputs, env)
+
+    def _run_one(self, node, part, inputs, env):
+        fn = _GPU_OPS.get(node.type)
+        all_col = all(isinstance(p, ColumnBatch) for payloads in inputs for p in payloads)
+        if fn is not None and (all_col or node.type == NodeType.InputTable):
+            try:
+                r = fn(self, node, part, inputs, env)
+            except CompileError:
+                r = NotImplemented
+            if r is not NotImplemented:
+                return r
+        self.host_fallbacks += 1
+        ins = [[self.to_records(p) for p in payloads] for payloads in inputs]
+        ports = vertex_ops.run(node, part, ins, env)
+        if node.n_out_ports == 1 and node.type not in (NodeType.GroupBy,):
+            return [self._columnar(ports[0], node.schema)]
+        return ports
+
+    def _cat(self, payloads) -> ColumnBatch:
+        return ColumnBatch.concat(list(payloads))
+
+
+# ---- operators -----------------------------------------------------------------------------------
+def _input(be: GpuBackend, node, part, inputs, env):
+    p = node.params["table"].partitions[part]
+    return [be._columnar(p, node.schema)]
+
+
+def _passthrough(be, node, part, inputs, env):
+    if node.params.get("sort_key") is not None:
+        return NotImplemented
+    return [be._cat(inputs[0])]
+
+
+def _tee(be, node, part, inputs, env):
+    b = be._cat(inputs[0])
+    return [b for _ in range(node.n_out_ports)] if node.params.get("replicate") else [b]
+
+
+def _proj_of(lam):
+    if isinstance(lam.ir, X.Expr):
+        return {"value": lam.ir}
+    if isinstance(lam.ir, dict):
+        return dict(lam.ir)
+    return None
+
+
+def _select(be, node, part, inputs, env):
+    p = node.params
+    src = be._cat(inputs[0])
+    if src.is_rows:
+        return NotImplemented
+    if p.get("finalize") is not None:
+        dec = p["finalize"]
+        kinds = [a.out_kind for a in dec.aggs]
+        res = dec.result
+        proj = {k: _bind_leaves(e, kinds) for k, e in res.items()} if isinstance(res, dict) else {"value": _bind_leaves(res, kinds)}
+        out, _ = run_on_gpu(proj, src.cols, src.n)
+        return [ColumnBatch(out, src.n, tuple_like=isinstance(res, X.TupleFields))]
+    if p["indexed"]:
+        return NotImplemented
+    proj = _proj_of(p["fn"])
+    if proj is None:
+        return NotImplemented
+    out, _ = run_on_gpu(proj, src.cols, src.n)
+    return [ColumnBatch(out, src.n, tuple_like=isinstance(p["fn"].ir, X.TupleFields))]
+
+
+def _where(be, node, part, inputs, env):
+    p = node.params
+    src = be._cat(inputs[0])
+    if p["indexed"] or not isinstance(p["fn"].ir, X.Expr) or src.is_rows:
+        return NotImplemented
+    if src.n == 0:
+        return [src]
+    _, flags = run_on_gpu({}, src.cols, src.n, predicate=p["fn"].ir)
+    idx, m = K.compact_flags(flags)
+    return [src.take(idx)]
+
+
+def _key_column(src: ColumnBatch, lam) -> Optional[torch.Tensor]:
+    """int64 key-bit column for a traced scalar key (ints: value; floats: IEEE bits)."""
+    if not isinstance(lam.ir, X.Expr) or lam.ir.kind not in ("i", "f", "b"):
+        return None
+    ir = lam.ir
+    if ir.op == "col" and ir.args[0] in src.cols:
+        t = src.cols[ir.args[0]]
+    else:
+        out, _ = run_on_gpu({"k": ir}, src.cols, src.n)
+        t = out["k"]
+    if t.dtype == torch.float64:
+        return t.view(torch.int64)
+    return t.to(torch.int64) if t.dtype != torch.int64 else t
+
+
+def _group_by(be, node, part, inputs, env):
+    p = node.params
+    dec = p.get("decomp")
+    if dec is None or p.get("elem") is not None:
+        return NotImplemented
+    lanes = dec.gpu_lanes()
+    if lanes is None:
+        return NotImplemented
+    src = be._cat(inputs[0])
+    mode = p["mode"]
+    n = src.n
+    if mode == "final_acc":
+        if "key" not in src.cols:
+            return NotImplemented
+        keys = src.cols["key"]
+        key_is_f = keys.dtype == torch.float64
+        kbits = keys.view(torch.int64) if key_is_f else keys
+        in_cols = [src.cols[f"agg{i}"] for i in range(len(lanes))]
+        combine = True
+    else:
+        if not isinstance(p["key"].ir, X.Expr):
+            return NotImplemented
+        key_is_f = p["key"].ir.kind == "f"
+        proj = {"__k": p["key"].ir}
+        for i, a in enumerate(dec.aggs):
+            if a.kind != "count":
+                sel = a.selector.ir if a.selector is not None else None
+                if not isinstance(sel, X.Expr):
+                    return NotImplemented
+                proj[f"__v{i}"] = sel
+        if n:
+            out, _ = run_on_gpu(proj, src.cols, n)
+        else:
+            out = {k: torch.empty(0, dtype=torch.int64, device=be.device) for k in proj}
+        kbits = out["__k"].view(torch.int64) if out["__k"].dtype == torch.float64 else out["__k"].to(torch.int64)
+        in_cols = [None if a.kind == "count" else out[f"__v{i}"] for i, a in enumerate(dec.aggs)]
+        combine = False
+    cap = max(1024, min(2 * n + 64, be.context.group_capacity_hint))
+    in_views = [None if c is None else (c.view(torch.int64) if c.dtype == torch.float64 else c.to(torch.int64)) for c in in_cols]
+    while True:
+        tbl = K.HashAggTable(cap, lanes, be.device)
+        if n:
+            tbl.update(kbits.contiguous(), [None if c is None else c.contiguous() for c in in_views], combine=combine)
+        try:
+            gk, gl = tbl.extract()
+            break
+        except K.N.NativeError as ex:
+            if "full" in str(ex) and cap < 4 * n + 1024:
+                cap *= 4
+                continue
+            raise
+        except OverflowError as ex:
+            raise DryadLinqException(ErrorCode.FailureInHashGroupBy, "Arithmetic operation resulted in an overflow.") from ex
+    cols: Dict[str, torch.Tensor] = {"key": gk.view(torch.float64) if key_is_f else gk}
+    for i, a in enumerate(dec.aggs):
+        lane = gl[i].contiguous()
+        cols[f"agg{i}"] = lane.view(torch.float64) if lanes[i].endswith("f64") else lane
+    return [ColumnBatch(cols, gk.numel(), acc_lanes=len(dec.aggs))]
+
+
+def _arena_for(be: GpuBackend, nbytes: int):
+    from ..parallel.symm import SymmetricArena
+    return SymmetricArena(nbytes + (1 << 20), 0, 1, None, be.device)
+
+
+def _partition_generic(be, node, src: ColumnBatch, kbits: torch.Tensor, mode: str, seps: Optional[torch.Tensor]):
+    """Single-process partitioning with the fused shuffle kernels: all destination partitions
+    live on this GPU.  Exact sizes come from a count-only launch, then the scatter runs."""
+    from ..parallel.shuffle import ColSpec, FusedShuffle
+    nports = node.params["nports"]
+    names = [k for k in src.cols]
+    cols = [kbits.contiguous()] + [src.cols[k].contiguous() for k in names]
+    specs = [ColSpec(8, torch.int64, 1)]
+    for k in names:
+        t = src.cols[k]
+        if t.dtype == torch.bool:
+            t = t.to(torch.uint8)
+        w = t.element_size() * (t.shape[1] if t.dim() > 1 else 1)
+        if w % 4:
+            return None
+        specs.append(ColSpec(w, t.dtype, t.shape[1] if t.dim() > 1 else 1))
+    n = src.n
+    cap = n + 16                      # worst case: everything lands in one partition
+    total = sum(s.width for s in specs) * cap * nports
+    if total > (8 << 30):
+        # too skew-tolerant to afford: size for 4x the mean and let the kernel report overflow
+        cap = max(1024, 4 * n // nports + 1024)
+        total = sum(s.width for s in specs) * cap * nports
+    arena = _arena_for(be, total + 4096 * (len(specs) + 2) * nports)
+    sh = FusedShuffle(arena, specs, cap, parts_per_rank=nports, emit_key=False, max_rows_in=max(n, 1))
+    sh.run(cols, mode=mode, key_col=0, key_kind=0, separators=seps)
+    counts = sh.received_rows()
+    ports = []
+    for j in range(nports):
+        m = counts[j]
+        d = {k: sh.recv[c + 1][j][:m] for c, k in enumerate(names)}
+        b = ColumnBatch(d, m, src.tuple_like, src.key_spec)
+        b._keepalive = (arena, sh)
+        ports.append(b)
+    return ports
+
+
+def _hash_partition(be, node, part, inputs, env):
+    src = be._cat(inputs[0])
+    if src.is_rows or node.params.get("comparer") is not None:
+        return NotImplemented
+    kb = _key_column(src, node.params["key"])
+    if kb is None:
+        return NotImplemented
+    r = _partition_generic(be, node, src, kb, "hash", None)
+    return r if r is not None else NotImplemented
+
+
+def _sort_bits(t: torch.Tensor) -> torch.Tensor:
+    return K.sort_key_bits(t)
+
+
+def _range_partition(be, node, part, inputs, env):
+    p = node.params
+    src = be._cat(inputs[0])
+    if src.is_rows or p.get("comparer") is not None or not isinstance(p["key"].ir, X.Expr):
+        return NotImplemented
+    out, _ = run_on_gpu({"k": p["key"].ir}, src.cols, src.n) if src.n else ({"k": torch.empty(0, dtype=torch.int64, device=be.device)}, None)
+    kb = _sort_bits(out["k"])
+    if p.get("range_keys") is not None:
+        sv = torch.tensor(list(p["range_keys"]), dtype=out["k"].dtype if out["k"].numel() else torch.int64, device=be.device)
+    else:
+        s = be._cat(inputs[1])
+        sv = s.cols["value"]
+    nports = p["nports"]
+    seps = _sort_bits(sv)
+    if seps.numel() < nports - 1:      # fewer keys than ports is allowed: trailing ports stay empty
+        pad = torch.full((nports - 1 - seps.numel(),), -1 if not p["descending"] else 0, dtype=torch.int64, device=be.device)
+        seps = torch.cat([seps, pad])
+    mode = "range_desc" if p["descending"] else "range_asc"
+    r = _partition_generic(be, node, src, kb, mode, seps.contiguous())
+    return r if r is not None else NotImplemented
+
+
+def _sampler(be, node, part, inputs, env):
+    src = be._cat(inputs[0])
+    lam = node.params["key"]
+    if src.is_rows or not isinstance(lam.ir, X.Expr):
+        return NotImplemented
+    n = src.n
+    if n == 0:
+        return [ColumnBatch({"value": torch.empty(0, dtype=torch.int64, device=be.device)}, 0)]
+    out, _ = run_on_gpu({"k": lam.ir}, src.cols, n)
+    k = out["k"]
+    rate = be.context.sample_rate
+    cap = int(n * rate * 3) + 1024
+    kb = k.view(torch.int64) if k.dtype == torch.float64 else k
+    samples, cnt = K.sample_keys(kb.contiguous(), seed=env.vertex_id * 1000 + part, rate=rate, cap=cap)
+    m = min(int(cnt.item()), cap)
+    if m < 10:                         # too few samples: emit every key (DryadLinqSampler.cs:85-98)
+        return [ColumnBatch({"value": k}, n)]
+    s = samples[:m]
+    return [ColumnBatch({"value": s.view(torch.float64) if k.dtype == torch.float64 else s}, m)]
+
+
+def _range_sampler(be, node, part, inputs, env):
+    p = node.params
+    if p.get("comparer") is not None:
+        return NotImplemented
+    s = be._cat(inputs[0])
+    v = s.cols["value"]
+    bits = _sort_bits(v).contiguous()
+    skeys, _ = K.radix_sort_pairs(bits, None)
+    seps_bits = K.select_separators(skeys, skeys.numel(), p["pcount"], bool(p["descending"]))
+    if skeys.numel() == 0:
+        seps_bits = seps_bits[:0]
+    # undo the order-preserving map
+    if v.dtype == torch.float64:
+        neg = seps_bits >= 0        # original negatives were bit-flipped (top bit clear after map)
+        raw = torch.where(neg, ~seps_bits, seps_bits ^ torch.tensor(-0x8000000000000000, dtype=torch.int64, device=be.device))
+        out = raw.view(torch.float64)
+    else:
+        out = seps_bits ^ torch.tensor(-0x8000000000000000, dtype=torch.int64, device=be.device)
+    return [ColumnBatch({"value": out}, out.numel())]
+
+
+_row_sorters: Dict[tuple, Any] = {}
+
+
+def _order_by(be, node, part, inputs, env):
+    p = node.params
+    src = be._cat(inputs[0])
+    if p.get("comparer") is not None:
+        return NotImplemented
+    if src.is_rows:
+        from ..api.rows import RowKey
+        rk = p["key"].fn if isinstance(getattr(p["key"], "fn", None), RowKey) else None
+        if rk is None:
+            return NotImplemented
+        from ..parallel.dsort import RowSorter
+        rows = src.cols[ROW_COL]
+        sig = (rows.shape[0], rows.shape[1], rk.offset, rk.length, bool(p["descending"]))
+        sorter = _row_sorters.get(sig)
+        if sorter is None:
+            _row_sorters.clear()
+            sorter = RowSorter(_arena_for(be, 1 << 20), rows.shape[0], rows.shape[1], key_off=rk.offset,
+                               key_len=max(8, rk.length), descending=bool(p["descending"]))
+            _row_sorters[sig] = sorter
+        out, m = sorter.sort(rows.contiguous())
+        return [ColumnBatch.rows(out[:m], rk.offset, rk.length)]
+    if not isinstance(p["key"].ir, X.Expr):
+        return NotImplemented
+    if src.n <= 1:
+        return [src]
+    out, _ = run_on_gpu({"k": p["key"].ir}, src.cols, src.n)
+    bits = K.sort_key_bits(out["k"], descending=bool(p["descending"])).contiguous()
+    _, idx = K.radix_sort_pairs(bits, None, iota=True)
+    return [src.take(idx)]
+
+
+def _basic_aggregate(be, node, part, inputs, env):
+    p = node.params
+    kind, stage = p["kind"], p["stage"]
+    if kind not in ("count", "sum", "min", "max"):
+        return NotImplemented
+    src = be._cat(inputs[0])
+    if src.is_rows:
+        if kind == "count" and stage == 1 and p.get("fn") is None:
+            return [ColumnBatch({"value": torch.tensor([src.n], dtype=torch.int64, device=be.device)}, 1)]
+        return NotImplemented
+    fn = p.get("fn")
+    if stage == 1:
+        if kind == "count":
+            if fn is not None:
+                return NotImplemented
+            return [ColumnBatch({"value": torch.tensor([src.n], dtype=torch.int64, device=be.device)}, 1)]
+        if fn is not None:
+            if not isinstance(fn.ir, X.Expr):
+                return NotImplemented
+            out, _ = run_on_gpu({"v": fn.ir}, src.cols, src.n) if src.n else ({"v": torch.empty(0, dtype=torch.int64, device=be.device)}, None)
+            col = out["v"]
+        else:
+            if "value" not in src.cols:
+                return NotImplemented
+            col = src.cols["value"]
+        if src.n == 0:
+            if kind == "sum":
+                return [ColumnBatch({"value": torch.zeros(1, dtype=col.dtype, device=be.device)}, 1)]
+            return [ColumnBatch({"value": col[:0]}, 0)]
+        if kind == "sum" and col.dtype == torch.int64:
+            # checked arithmetic: detect overflow with a float shadow sum
+            approx = float(col.to(torch.float64).sum().item())
+            if abs(approx) > 9.2e18:
+                raise DryadLinqException(ErrorCode.FailureInOperator, "Arithmetic operation resulted in an overflow.")
+        return [ColumnBatch({"value": K.reduce(col.contiguous(), kind)}, 1)]
+    # stage 2 over the per-partition partials
+    if "value" not in src.cols:
+        return NotImplemented
+    col = src.cols["value"]
+    if src.n == 0:
+        if kind in ("count", "sum"):
+            return [ColumnBatch({"value": torch.zeros(1, dtype=torch.int64, device=be.device)}, 1)]
+        return NotImplemented          # host raises the typed "no elements" error
+    op = "sum" if kind in ("count", "sum") else kind
+    return [ColumnBatch({"value": K.reduce(col.contiguous(), op)}, 1)]
+
+
+def _join(be, node, part, inputs, env):
+    p = node.params
+    if node.type != NodeType.Join or p.get("algorithm") != "hash" or p.get("comparer") is not None:
+        return NotImplemented
+    res = p["result"].ir
+    if not isinstance(res, (dict, X.Expr)):
+        return NotImplemented
+    outer, inner = be._cat(inputs[0]), be._cat(inputs[1])
+    if outer.is_rows or inner.is_rows:
+        return NotImplemented
+    ok, ik = _key_column(outer, p["outer_key"]), _key_column(inner, p["inner_key"])
+    if ok is None or ik is None:
+        return NotImplemented
+    if outer.n == 0 or inner.n == 0:
+        proj = res if isinstance(res, dict) else {"value": res}
+        dt = {"i": torch.int64, "f": torch.float64, "b": torch.bool}
+        return [ColumnBatch({k: torch.empty(0, dtype=dt[e.kind], device=be.device) for k, e in proj.items()}, 0,
+                            tuple_like=isinstance(res, X.TupleFields))]
+    jt = K.JoinTable(ik.contiguous())                    # build on the inner (usually smaller) side
+    op, ib = jt.probe(ok.contiguous())
+    o_sel, i_sel = outer.take(op), inner.take(ib)
+    cols = {("o." + k): v for k, v in o_sel.cols.items()}
+    cols.update({("i." + k): v for k, v in i_sel.cols.items()})
+    proj = res if isinstance(res, dict) else {"value": res}
+    out, _ = run_on_gpu(proj, cols, op.numel()) if op.numel() else ({}, None)
+    if not op.numel():
+        dt = {"i": torch.int64, "f": torch.float64, "b": torch.bool}
+        out = {k: torch.empty(0, dtype=dt[e.kind], device=be.device) for k, e in proj.items()}
+    return [ColumnBatch(out, op.numel(), tuple_like=isinstance(res, X.TupleFields))]
+
+
+def _distinct(be, node, part, inputs, env):
+    src = be._cat(inputs[0])
+    if list(src.cols) != ["value"] or src.cols["value"].dtype not in (torch.int64, torch.float64):
+        return NotImplemented
+    v = src.cols["value"]
+    if src.n == 0:
+        return [src]
+    kb = v.view(torch.int64) if v.dtype == torch.float64 else v
+    tbl = K.HashAggTable(2 * src.n + 64, [], be.device)
+    tbl.update(kb.contiguous(), [])
+    gk, _ = tbl.extract()
+    return [ColumnBatch({"value": gk.view(torch.float64) if v.dtype == torch.float64 else gk}, gk.numel())]
+
+
+_GPU_OPS = {
+    NodeType.InputTable: _input, NodeType.OutputTable: _passthrough, NodeType.Dummy: _passthrough,
+    NodeType.Merge: _passthrough, NodeType.Concat: _passthrough, NodeType.ForkBranch: _passthrough,
+    NodeType.Tee: _tee, NodeType.Select: _select, NodeType.Where: _where, NodeType.GroupBy: _group_by,
+    NodeType.HashPartition: _hash_partition, NodeType.RangePartition: _range_partition,
+    NodeType.Sampler: _sampler, NodeType.RangeSampler: _range_sampler, NodeType.OrderBy: _order_by,
+    NodeType.BasicAggregate: _basic_aggregate, NodeType.Join: _join, NodeType.Distinct: _distinct,
+}
