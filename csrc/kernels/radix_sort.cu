@@ -12,6 +12,7 @@
 // No CUB / thrust: the north star forbids a library sort on this path.
 #include "common.cuh"
 #include "../../include/dryad_b200.h"
+#include <mutex>
 
 namespace dryad { namespace rs {
 
@@ -305,6 +306,50 @@ int dryad_radix_sort_pairs_u32(uint32_t* keys, uint32_t* keys_alt, uint32_t* val
   return dryad::rs::sort_impl<uint32_t>(keys, keys_alt, vals, vals_alt, n, begin_bit, end_bit,
                                         iota_vals, scratch, scratch_bytes, result_in_alt,
                                         (cudaStream_t)stream);
+}
+
+// ---- allocation-free variant ---------------------------------------------------------------------
+// Some callers may not allocate device memory at all: a process whose own pool already owns all
+// of HBM, a latency-critical thread that must never wait on the driver's allocator (cudaMalloc and
+// cudaFree take a device-wide lock and can synchronise the device), or a plain C program that
+// links this library without any allocator of its own.  For them the sort's working storage
+// (digit histograms, tile counters, look-back status words) lives in a fixed array that is part of
+// the loaded module.  Every GPU that loads the library carries these DRYAD_SORT_NOALLOC_SCRATCH
+// bytes until the process exits.
+static __device__ __align__(256) unsigned char g_sort_noalloc_scratch[DRYAD_SORT_NOALLOC_SCRATCH];
+
+namespace dryad { namespace rs {
+static std::mutex g_noalloc_mu;
+static void* g_noalloc_ptr[64] = {nullptr};   // device address of the array, per device ordinal
+}}
+
+int dryad_radix_sort_pairs_u64_noalloc(uint64_t* keys, uint64_t* keys_alt, uint32_t* vals,
+                                       uint32_t* vals_alt, int64_t n, int begin_bit, int end_bit,
+                                       int iota_vals, int* result_in_alt, void* stream) {
+  using namespace dryad::rs;
+  if (n > DRYAD_SORT_NOALLOC_MAX_N) return DRYAD_ERR_TOO_LARGE;   // beyond the built-in scratch
+  if (n > 0 && end_bit > begin_bit && layout(n, begin_bit, end_bit).total > DRYAD_SORT_NOALLOC_SCRATCH)
+    return DRYAD_ERR_TOO_LARGE;
+  int dev = -1;
+  DRYAD_CUDA_TRY(cudaGetDevice(&dev));
+  if (dev < 0 || dev >= 64) return DRYAD_ERR_BAD_ARG;
+  void* scratch = nullptr;
+  {
+    // One-time set-up per device, with that device current: in host code the array's name is only
+    // a handle, so ask the runtime for the address the kernels must use.
+    std::lock_guard<std::mutex> lock(g_noalloc_mu);
+    if (g_noalloc_ptr[dev] == nullptr) {
+      void* p = nullptr;
+      DRYAD_CUDA_TRY(cudaGetSymbolAddress(&p, g_sort_noalloc_scratch));
+      g_noalloc_ptr[dev] = p;
+    }
+    scratch = g_noalloc_ptr[dev];
+  }
+  // sort_impl clears the parts of the scratch that must start at zero (histograms, tile counters,
+  // status words) on `stream` before each use, so stale contents of the previous call are harmless.
+  return sort_impl<uint64_t>(keys, keys_alt, vals, vals_alt, n, begin_bit, end_bit, iota_vals,
+                             scratch, (size_t)DRYAD_SORT_NOALLOC_SCRATCH, result_in_alt,
+                             (cudaStream_t)stream);
 }
 
 }  // extern "C"

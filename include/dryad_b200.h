@@ -69,6 +69,24 @@ int dryad_radix_sort_pairs_u32(uint32_t* keys, uint32_t* keys_alt, uint32_t* val
                                int iota_vals, void* scratch, size_t scratch_bytes,
                                int* result_in_alt, void* stream);
 
+/* Allocation-free sort.  No counterpart in the reference: it exists for callers that cannot
+ * allocate device memory — a host program whose own pool holds all of HBM, a thread that must not
+ * block on the driver's allocator, or a C program with no allocator library.  Same contract as
+ * dryad_radix_sort_pairs_u64, but the working storage is a fixed array inside the library
+ * (DRYAD_SORT_NOALLOC_SCRATCH bytes per GPU, held until the process exits), so n is limited to
+ * DRYAD_SORT_NOALLOC_MAX_N pairs; larger n returns DRYAD_ERR_TOO_LARGE ("size beyond supported
+ * maximum").  The call itself never calls cudaMalloc/cudaFree or any allocating library routine;
+ * the caller still provides keys/vals and their _alt ping-pong buffers.
+ * - The first call on each device looks up the array's device address (cudaGetSymbolAddress, with
+ *   that device current); make that first call before starting any stream capture.
+ * - All calls on a device share the one array: two calls whose kernels overlap on the GPU
+ *   (different streams, no ordering between them) race.  Serialise them on one stream. */
+#define DRYAD_SORT_NOALLOC_MAX_N (1ll << 22)
+#define DRYAD_SORT_NOALLOC_SCRATCH 716032   /* 2 x 8 KiB histograms + 256 + 683 tiles x 1 KiB */
+int dryad_radix_sort_pairs_u64_noalloc(uint64_t* keys, uint64_t* keys_alt, uint32_t* vals,
+                                       uint32_t* vals_alt, int64_t n, int begin_bit, int end_bit,
+                                       int iota_vals, int* result_in_alt, void* stream);
+
 /* ---- K1/K2 + C1 fused partition + all-to-all: LinqToDryad/DryadLinqVertex.cs:4788-5151,
  *      DryadLinqGraphManager/GraphBuilder.cs:481-504 ------------------------------------------ */
 enum { DRYAD_PART_HASH = 0, DRYAD_PART_RANGE_ASC = 1, DRYAD_PART_RANGE_DESC = 2, DRYAD_PART_DIRECT = 3 };
