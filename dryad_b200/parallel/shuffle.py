@@ -58,6 +58,7 @@ class FusedShuffle:
                 self.recv_key_off.append(off)
                 self.recv_key.append(arena.view(off, (self.cap_rows,), torch.int64))
         self.counts, self.counts_off = arena.alloc((W, self.nparts), torch.int64)
+        arena.check_symmetric("FusedShuffle receive buffers")
         # pointer tables (device)
         dst = []
         for c in range(len(self.cols)):

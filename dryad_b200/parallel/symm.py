@@ -86,6 +86,18 @@ class SymmetricArena:
         self._cursor = off + nbytes
         return off
 
+    def check_symmetric(self, what: str = "") -> None:
+        """Init-time guard: every rank must have made the same allocations (same cursor), or peer
+        addresses computed from local offsets would point at the wrong objects."""
+        if self.world == 1:
+            return
+        import torch.distributed as dist
+        cursors = [None] * self.world
+        dist.all_gather_object(cursors, self._cursor, group=self.group)
+        if len(set(cursors)) != 1:
+            raise RuntimeError(f"symmetric arena diverged across ranks {cursors} ({what}): "
+                               "allocate with identical sizes on every rank")
+
     def mark(self) -> int:
         return self._cursor
 

@@ -43,7 +43,7 @@ class SpmdExecutor(JobExecutor):
     def __init__(self, context, plan, reporter=None):
         super().__init__(context, plan, reporter)
         self.rank, self.world = context.rank, context.world
-        self.arena = context._spmd_arena()
+        self.arena = None                      # created lazily: host-backend SPMD needs no GPU arena
         self._skip: set = set()
         self._fused: Dict[int, Any] = {}
 

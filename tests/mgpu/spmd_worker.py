@@ -1,0 +1,140 @@
+"""Multi-rank worker (launched by torchrun / mp.spawn).  `--mode cpu` exercises the SPMD executor
+on the host backend over gloo; `--mode gpu` checks the fused multi-GPU kernels over NVLink."""
+import argparse
+import os
+import sys
+
+import torch
+import torch.distributed as dist
+
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__)))))
+import dryad_b200 as D  # noqa: E402
+
+
+def cpu_checks(rank, world):
+    ctx = D.DryadLinqContext(platform="B200", device="cpu")
+    assert ctx.world == world and ctx.rank == rank
+    data = list(range(200))
+    q = ctx.from_enumerable(data, world)
+    got = q.where(lambda x: x % 3 == 0).select(lambda x: x + 1).partitions()
+    mine = [x + 1 for x in data[rank * 100:(rank + 1) * 100] if x % 3 == 0] if world == 2 else None
+    if mine is not None:
+        assert got[0] == mine, (rank, got[0][:5], mine[:5])
+    words = ["a b c", "a b", "a", "c c c d"] * 5
+    wc = (ctx.from_enumerable(words, world).select_many(lambda l: l.split(" ")).group_by(lambda w: w)
+          .select(lambda g: (g.key, g.count())))
+    local = wc.partitions()[0]
+    allp = [None] * world
+    dist.all_gather_object(allp, local)
+    merged = sorted(sum(allp, []))
+    assert merged == [("a", 15), ("b", 10), ("c", 20), ("d", 5)], merged
+    # ordering: range partition + sort, globally ordered by rank
+    vals = [(i * 7919) % 1000 for i in range(400)]
+    srt = ctx.from_enumerable(vals, world).order_by(lambda x: x).partitions()[0]
+    allp = [None] * world
+    dist.all_gather_object(allp, srt)
+    assert sum(allp, []) == sorted(vals)
+    # scalar aggregate lands on rank 0
+    total = ctx.from_enumerable(vals, world).sum_as_query().partitions()[0]
+    if rank == 0:
+        assert total == [sum(vals)]
+
+
+def gpu_checks(rank, world):
+    from dryad_b200.models import terasort
+    from dryad_b200.ops import core as K
+    from dryad_b200.parallel.dagg import DistributedHashAggregate
+    from dryad_b200.parallel.dsort import RowSorter
+    from dryad_b200.parallel.shuffle import ColSpec, FusedShuffle
+    from dryad_b200.parallel.symm import SymmetricArena
+    from dryad_b200.utils.hashing import hash_bucket_np
+    dev = torch.device("cuda", int(os.environ.get("LOCAL_RANK", "0")))
+    torch.cuda.set_device(dev)
+    arena = SymmetricArena(2 << 30, rank, world, None, dev)
+    arena.barrier()
+    torch.cuda.synchronize()
+
+    # 1. fused hash shuffle of (key, value) columns: every key lands on its owner, nothing is lost
+    n = 1_000_003 + rank * 1000
+    g = torch.Generator(device=dev).manual_seed(100 + rank)
+    keys = torch.randint(-2**62, 2**62, (n,), dtype=torch.int64, device=dev, generator=g)
+    vals = torch.arange(n, dtype=torch.int64, device=dev) + rank * 10_000_000
+    sh = FusedShuffle(arena, [ColSpec(8, torch.int64), ColSpec(8, torch.int64)], int(1_010_000 * 1.3) + 4096, max_rows_in=1_010_000)   # same size on every rank
+    sh.run([keys, vals], mode="hash", key_col=0, key_kind=0)
+    m = sh.received_rows()[0]
+    rk, rv = sh.recv[0][0][:m], sh.recv[1][0][:m]
+    import numpy as np
+    owner = hash_bucket_np(rk.cpu().numpy().view(np.uint64), world)
+    assert (owner == rank).all()
+    tot = torch.tensor([m, int(rv.sum().item()), n, int(vals.sum().item())], dtype=torch.int64, device=dev)
+    dist.all_reduce(tot)
+    assert int(tot[0]) == int(tot[2]) and int(tot[1]) == int(tot[3]), tot
+    # stability: rows from one source keep their source order
+    src0 = rv[(rv >= 0) & (rv < 10_000_000)]
+    assert bool((src0[1:] > src0[:-1]).all())
+
+    # 2. distributed sort of 100-byte rows
+    nr = 500_000
+    rows = terasort.generate_rows(nr, seed=5, device=dev, rank=rank)
+    sorter = RowSorter(arena, nr, 100, key_len=10)
+    out, mm = sorter.sort(rows)
+    res = K.check_sorted_rows(out, 0, 10).cpu()
+    cs_in = K.check_sorted_rows(rows, 0, 10).cpu()[1]
+    assert int(res[0]) == 0
+    first = out[0, :10].cpu().numpy().tobytes() if mm else b""
+    last = out[mm - 1, :10].cpu().numpy().tobytes() if mm else b""
+    bounds = [None] * world
+    dist.all_gather_object(bounds, (first, last, mm, int(res[1]), int(cs_in)))
+    assert sum(b[2] for b in bounds) == nr * world
+    assert (sum(b[3] for b in bounds) - sum(b[4] for b in bounds)) % (1 << 64) == 0
+    ne = [b for b in bounds if b[2]]
+    assert all(a[1] <= b[0] for a, b in zip(ne, ne[1:])), "partitions are not globally ordered"
+
+    # 3. fused GroupBy reduce-scatter
+    nk = 50_000
+    gk = torch.randint(0, nk, (2_000_000,), dtype=torch.int64, device=dev, generator=g)
+    gv = torch.randint(0, 100, (2_000_000,), dtype=torch.int64, device=dev, generator=g)
+    agg = DistributedHashAggregate(arena, ["sum_i64", "count"], 2 * nk, 4 * nk)
+    for _ in range(2):
+        ok_, ol = agg.run(gk, [gv, None])
+    own = hash_bucket_np(ok_.cpu().numpy().view(np.uint64), world)
+    assert (own == rank).all()
+    full_k = [torch.zeros(nk, dtype=torch.int64, device=dev) for _ in range(2)]
+    full_k[0].index_add_(0, gk, gv)
+    full_k[1].index_add_(0, gk, torch.ones_like(gv))
+    dist.all_reduce(full_k[0]); dist.all_reduce(full_k[1])
+    assert torch.equal(ol[0], full_k[0][ok_]) and torch.equal(ol[1], full_k[1][ok_])
+
+    # 4. the same sort through the public API (SPMD executor -> RowSorter)
+    ctx = D.DryadLinqContext(platform="B200", device=str(dev))
+    host = rows.cpu().pin_memory()
+    res_q = ctx.from_rows(host, key_off=0, key_len=10).order_by(D.RowKey(0, 10)).submit_and_wait()
+    viol, cs, cnt = terasort.validate(res_q)
+    t = torch.tensor([viol, cnt], dtype=torch.int64, device=dev)
+    dist.all_reduce(t)
+    assert int(t[0]) == 0 and int(t[1]) == nr * world
+    torch.cuda.synchronize()
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--mode", default="cpu")
+    a = ap.parse_args()
+    rank, world = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"])
+    os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+    if a.mode == "cpu":
+        dist.init_process_group("gloo")
+        cpu_checks(rank, world)
+    else:
+        dev = torch.device("cuda", int(os.environ.get("LOCAL_RANK", "0")))
+        torch.cuda.set_device(dev)
+        dist.init_process_group("nccl", device_id=dev)
+        gpu_checks(rank, world)
+    dist.barrier()
+    if rank == 0:
+        print(f"SPMD {a.mode} checks passed on {world} ranks")
+    dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()
