@@ -56,6 +56,10 @@ __device__ __forceinline__ uint64_t load_key(const Params& P, int64_t row) {
   const unsigned char* base = P.src[P.key_col] + (size_t)row * P.width[P.key_col];
   if (P.key_kind == 0) return *reinterpret_cast<const uint64_t*>(base);
   const unsigned char* k = base + P.key_off;
+  if ((reinterpret_cast<uintptr_t>(k) & 3) == 0) {
+    const uint32_t* w = reinterpret_cast<const uint32_t*>(k);
+    return ((uint64_t)__byte_perm(__ldg(w), 0, 0x0123) << 32) | (uint64_t)__byte_perm(__ldg(w + 1), 0, 0x0123);
+  }
   uint64_t v = 0;
 #pragma unroll
   for (int i = 0; i < 8; ++i) v = (v << 8) | (uint64_t)k[i];
@@ -65,6 +69,10 @@ __device__ __forceinline__ uint64_t load_key(const Params& P, int64_t row) {
 __device__ __forceinline__ uint64_t key_from_smem(const Params& P, const unsigned char* row) {
   if (P.key_kind == 0) return *reinterpret_cast<const uint64_t*>(row);
   const unsigned char* k = row + P.key_off;
+  if ((reinterpret_cast<uintptr_t>(k) & 3) == 0) {   // two word loads + byte swaps
+    const uint32_t* w = reinterpret_cast<const uint32_t*>(k);
+    return ((uint64_t)__byte_perm(w[0], 0, 0x0123) << 32) | (uint64_t)__byte_perm(w[1], 0, 0x0123);
+  }
   uint64_t v = 0;
 #pragma unroll
   for (int i = 0; i < 8; ++i) v = (v << 8) | (uint64_t)k[i];
@@ -113,19 +121,46 @@ __global__ void __launch_bounds__(THREADS) sh_count(Params P) {
     P.block_counts[(size_t)i * P.nblocks + blockIdx.x] = s_cnt[i];
 }
 
-// One block.  Thread p scans partition p's counts over blocks, then publishes totals to peers.
-__global__ void __launch_bounds__(MAX_PARTS) sh_publish(Params P) {
-  const int p = threadIdx.x;
-  if (p < P.nparts) {
-    uint32_t* row = P.block_counts + (size_t)p * P.nblocks;
-    uint64_t sum = 0;
-    for (int b = 0; b < P.nblocks; ++b) { uint32_t c = row[b]; row[b] = (uint32_t)sum; sum += c; }
-    for (int r = 0; r < P.world; ++r)
-      P.counts_peers[r][(size_t)P.rank * P.nparts + p] = (int64_t)sum;
+// One block per partition: block p turns partition p's per-block counts into exclusive offsets
+// (chunked block scan), writes the total into EVERY rank's count matrix with P2P stores; the last
+// block to finish raises the release.sys flag on every peer.
+__global__ void __launch_bounds__(256) sh_publish(Params P, uint32_t* done_counter) {
+  __shared__ uint32_t s_warp[8];
+  __shared__ uint64_t s_carry;
+  __shared__ bool s_last;
+  const int p = blockIdx.x, t = threadIdx.x, lane = t & 31, warp = t >> 5;
+  uint32_t* row = P.block_counts + (size_t)p * P.nblocks;
+  if (t == 0) s_carry = 0;
+  __syncthreads();
+  for (int base = 0; base < P.nblocks; base += 256) {
+    const int i = base + t;
+    const uint32_t v = (i < P.nblocks) ? row[i] : 0u;
+    uint32_t incl = v;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      uint32_t a = __shfl_up_sync(0xffffffffu, incl, o);
+      if (lane >= o) incl += a;
+    }
+    if (lane == 31) s_warp[warp] = incl;
+    __syncthreads();
+    uint32_t before = 0;
+#pragma unroll
+    for (int w = 0; w < 8; ++w) before += (w < warp) ? s_warp[w] : 0u;
+    const uint64_t carry = s_carry;
+    if (i < P.nblocks) row[i] = (uint32_t)(carry + before + incl - v);
+    __syncthreads();
+    if (t == 255) s_carry = carry + before + incl;
+    __syncthreads();
   }
+  if (t < P.world) P.counts_peers[t][(size_t)P.rank * P.nparts + p] = (int64_t)s_carry;
   __threadfence_system();
   __syncthreads();
-  if (p < P.world) st_release_sys(&P.flags_peers[p][P.rank], P.epoch);
+  if (t == 0) s_last = atomicAdd(done_counter, 1u) == gridDim.x - 1;
+  __syncthreads();
+  if (s_last) {
+    __threadfence_system();
+    if (t < P.world) st_release_sys(&P.flags_peers[t][P.rank], P.epoch);
+  }
 }
 
 __global__ void __launch_bounds__(THREADS) sh_scatter(Params P) {
@@ -134,14 +169,15 @@ __global__ void __launch_bounds__(THREADS) sh_scatter(Params P) {
   const int maxw = P.max_width;
   unsigned char* s_in = smem;
   unsigned char* s_out = s_in + (size_t)TILE * maxw;
-  size_t out_bytes = (size_t)TILE * maxw + 32 * (size_t)P.nparts + 16;
-  uint64_t* s_seps = reinterpret_cast<uint64_t*>(s_out + out_bytes);        // [MAX_PARTS]
-  int64_t* s_gbase = reinterpret_cast<int64_t*>(s_seps + MAX_PARTS);        // [MAX_PARTS] rows
-  uint32_t* s_wcnt = reinterpret_cast<uint32_t*>(s_gbase + MAX_PARTS);      // [WARPS][MAX_PARTS]
-  uint32_t* s_tcnt = s_wcnt + WARPS * MAX_PARTS;                            // [MAX_PARTS]
-  uint32_t* s_tstart = s_tcnt + MAX_PARTS;                                  // [MAX_PARTS+1] rows
-  uint32_t* s_ustart = s_tstart + MAX_PARTS + 1;                            // [MAX_PARTS+1] 16B units
-  uint32_t* s_uoff = s_ustart + MAX_PARTS + 1;                              // [MAX_PARTS] byte offset of run in s_out
+  size_t out_bytes = ((size_t)TILE * maxw + 32 * (size_t)P.nparts + 16 + 15) & ~(size_t)15;
+  const int npa = (P.nparts + 3) & ~3;                                      // arrays sized by nparts
+  uint64_t* s_seps = reinterpret_cast<uint64_t*>(s_out + out_bytes);        // [npa]
+  int64_t* s_gbase = reinterpret_cast<int64_t*>(s_seps + npa);              // [npa] rows
+  uint32_t* s_wcnt = reinterpret_cast<uint32_t*>(s_gbase + npa);            // [WARPS][np]
+  uint32_t* s_tcnt = s_wcnt + WARPS * npa;                                  // [npa]
+  uint32_t* s_tstart = s_tcnt + npa;                                        // [npa+4] rows
+  uint32_t* s_ustart = s_tstart + npa + 4;                                  // [npa+4] 16B units
+  uint32_t* s_uoff = s_ustart + npa + 4;                                    // [npa] byte offset of run in s_out
   __shared__ int s_abort;
 
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
@@ -282,30 +318,28 @@ __global__ void __launch_bounds__(THREADS) sh_scatter(Params P) {
         }
       }
       __syncthreads();
-      // write out: every 16-byte unit belongs to exactly one run
-      const uint32_t units = s_ustart[np];
-      for (uint32_t u = tid; u < units; u += THREADS) {
-        int lo = 0, hi = np - 1;  // last p with s_ustart[p] <= u and non-empty
-        while (lo < hi) { int mid = (lo + hi + 1) >> 1; if (s_ustart[mid] <= u) lo = mid; else hi = mid - 1; }
-        int p = lo;
-        // skip empty partitions sharing the same unit start
-        while (p > 0 && s_tcnt[p] == 0) --p;
-        if (s_tcnt[p] == 0) continue;
+      // write out: warp w streams the runs of partitions w, w+8, ...  (16-byte aligned units)
+      for (int p = warp; p < np; p += WARPS) {
+        const uint32_t cnt = s_tcnt[p];
+        if (cnt == 0) continue;
         unsigned char* dbase = is_key_out ? reinterpret_cast<unsigned char*>(P.dst_key_table[p])
                                           : reinterpret_cast<unsigned char*>(P.dst_table[(size_t)c * np + p]);
         const uint32_t run_s = s_uoff[p];                    // shared byte offset of run start
-        const uint32_t run_e = run_s + s_tcnt[p] * w;        // exclusive
-        uintptr_t ga = reinterpret_cast<uintptr_t>(dbase) + (uintptr_t)s_gbase[p] * w;  // global addr of run start
-        const uint32_t ub = u * 16;                          // shared byte offset of this unit
-        uintptr_t gu = ga + (intptr_t)ub - (intptr_t)run_s;  // global addr matching the unit start
-        if (ub >= run_s && ub + 16 <= run_e) {
-          *reinterpret_cast<uint4*>(gu) = *reinterpret_cast<const uint4*>(s_out + ub);
-        } else {
+        const uint32_t run_e = run_s + cnt * w;              // exclusive
+        const uintptr_t ga = reinterpret_cast<uintptr_t>(dbase) + (uintptr_t)s_gbase[p] * w;
+        const uint32_t u0 = run_s >> 4, u1 = (run_e + 15) >> 4;
+        for (uint32_t u = u0 + lane; u < u1; u += 32) {
+          const uint32_t ub = u * 16;
+          const uintptr_t gu = ga + (intptr_t)ub - (intptr_t)run_s;
+          if (ub >= run_s && ub + 16 <= run_e) {
+            *reinterpret_cast<uint4*>(gu) = *reinterpret_cast<const uint4*>(s_out + ub);
+          } else {
 #pragma unroll
-          for (int k = 0; k < 4; ++k) {
-            uint32_t b = ub + 4 * k;
-            if (b >= run_s && b < run_e)
-              *reinterpret_cast<uint32_t*>(gu + 4 * k) = *reinterpret_cast<const uint32_t*>(s_out + b);
+            for (int k = 0; k < 4; ++k) {
+              uint32_t bb = ub + 4 * k;
+              if (bb >= run_s && bb < run_e)
+                *reinterpret_cast<uint32_t*>(gu + 4 * k) = *reinterpret_cast<const uint32_t*>(s_out + bb);
+            }
           }
         }
       }
@@ -331,9 +365,11 @@ __global__ void sh_barrier(uint64_t* const* flags_peers, uint64_t* flags_local, 
 
 static size_t scatter_smem(int maxw, int nparts) {
   size_t b = (size_t)TILE * maxw;                       // in
-  b += (size_t)TILE * maxw + 32 * (size_t)nparts + 16;  // out
-  b += 8 * MAX_PARTS + 8 * MAX_PARTS;                   // seps, gbase
-  b += 4 * (WARPS * MAX_PARTS + MAX_PARTS + (MAX_PARTS + 1) * 2 + MAX_PARTS);
+  b += ((size_t)TILE * maxw + 32 * (size_t)nparts + 16 + 15) & ~(size_t)15;  // out
+  const size_t npa = ((size_t)nparts + 3) & ~(size_t)3;
+  b = (b + 15) & ~(size_t)15;
+  b += 8 * npa + 8 * npa;                               // seps, gbase
+  b += 4 * (WARPS * npa + npa + (npa + 4) * 2 + npa);
   return (b + 15) & ~(size_t)15;
 }
 
@@ -354,7 +390,7 @@ extern "C" {
 size_t dryad_shuffle_scratch_bytes(int64_t n, int nparts) {
   int tpb;
   int nb = dryad::sh::pick_blocks(n, &tpb);
-  return (((size_t)nparts * nb * 4) + 255) & ~(size_t)255;
+  return ((((size_t)nparts * nb * 4) + 255) & ~(size_t)255) + 256;   // + done counter
 }
 
 int dryad_shuffle_run(const DryadShuffleDesc* d, void* stream) {
@@ -385,13 +421,15 @@ int dryad_shuffle_run(const DryadShuffleDesc* d, void* stream) {
   P.flags_local = d->flags_local; P.flags_peers = d->flags_peers; P.epoch = d->epoch;
   P.status = d->status;
   P.nblocks = pick_blocks(d->n, &P.tiles_per_block);
-  size_t need = (((size_t)P.nparts * P.nblocks * 4) + 255) & ~(size_t)255;
-  if (!d->scratch || d->scratch_bytes < need) return DRYAD_ERR_SCRATCH;
+  size_t counts_bytes = (((size_t)P.nparts * P.nblocks * 4) + 255) & ~(size_t)255;
+  if (!d->scratch || d->scratch_bytes < counts_bytes + 256) return DRYAD_ERR_SCRATCH;
   P.block_counts = (uint32_t*)d->scratch;
+  uint32_t* done_counter = (uint32_t*)((unsigned char*)d->scratch + counts_bytes);
+  DRYAD_CUDA_TRY(cudaMemsetAsync(done_counter, 0, 4, st));
 
   sh_count<<<P.nblocks, THREADS, 0, st>>>(P);
   DRYAD_LAUNCH_CHECK();
-  sh_publish<<<1, MAX_PARTS, 0, st>>>(P);
+  sh_publish<<<P.nparts, 256, 0, st>>>(P, done_counter);
   DRYAD_LAUNCH_CHECK();
   size_t smem = scatter_smem(maxw, P.nparts);
   DRYAD_CUDA_TRY(cudaFuncSetAttribute(sh_scatter, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));

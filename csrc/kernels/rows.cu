@@ -127,15 +127,15 @@ __global__ void select_separators_kernel(const uint64_t* __restrict__ sorted, in
 __global__ void fix_ties_kernel(const uint64_t* __restrict__ keys, uint32_t* __restrict__ idx,
                                 int64_t n, const unsigned char* __restrict__ rowsp, int width,
                                 int extra_off, int extra, int max_run, int descending,
-                                int32_t* __restrict__ long_runs) {
+                                uint64_t prefix_mask, int32_t* __restrict__ long_runs) {
   int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   int64_t stride = (int64_t)gridDim.x * blockDim.x;
   for (; i < n; i += stride) {
-    uint64_t k = keys[i];
-    if (i + 1 >= n || keys[i + 1] != k) continue;
-    if (i > 0 && keys[i - 1] == k) continue;
+    uint64_t k = keys[i] & prefix_mask;
+    if (i + 1 >= n || (keys[i + 1] & prefix_mask) != k) continue;
+    if (i > 0 && (keys[i - 1] & prefix_mask) == k) continue;
     int64_t e = i + 1;
-    while (e < n && keys[e] == k) ++e;
+    while (e < n && (keys[e] & prefix_mask) == k) ++e;
     int64_t len = e - i;
     if (len > max_run) { atomicAdd(long_runs, 1); continue; }
     // insertion sort on (extra bytes, idx)
@@ -289,11 +289,11 @@ int dryad_select_separators(const uint64_t* sorted, int64_t cnt, int pcount, int
 }
 
 int dryad_fix_ties(const uint64_t* keys, uint32_t* idx, int64_t n, const uint8_t* rowsp, int width,
-                   int extra_off, int extra, int max_run, int descending, int32_t* long_runs,
-                   void* stream) {
+                   int extra_off, int extra, int max_run, int descending, uint64_t prefix_mask,
+                   int32_t* long_runs, void* stream) {
   if (n <= 1 || extra <= 0) return DRYAD_OK;
   if (extra_off < 0 || extra_off + extra > width) return DRYAD_ERR_BAD_ARG;
-  fix_ties_kernel<<<grid_for(n, 256), 256, 0, (cudaStream_t)stream>>>(keys, idx, n, rowsp, width, extra_off, extra, max_run, descending, long_runs);
+  fix_ties_kernel<<<grid_for(n, 256), 256, 0, (cudaStream_t)stream>>>(keys, idx, n, rowsp, width, extra_off, extra, max_run, descending, prefix_mask, long_runs);
   DRYAD_LAUNCH_CHECK();
   return DRYAD_OK;
 }

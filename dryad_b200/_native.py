@@ -90,7 +90,7 @@ def _declare_kernels(lib):
                                            c_int64, P])
     _sig(lib, "dryad_select_separators", c_int, [P, c_int64, c_int, c_int, P, P])
     _sig(lib, "dryad_extract_be64", c_int, [P, c_int64, c_int, c_int, P, P])
-    _sig(lib, "dryad_fix_ties", c_int, [P, P, c_int64, P, c_int, c_int, c_int, c_int, c_int, P, P])
+    _sig(lib, "dryad_fix_ties", c_int, [P, P, c_int64, P, c_int, c_int, c_int, c_int, c_int, c_uint64, P, P])
     _sig(lib, "dryad_gather_rows", c_int, [P, P, P, c_int64, c_int, P])
     _sig(lib, "dryad_check_sorted_rows", c_int, [P, c_int64, c_int, c_int, c_int, c_int, P, P])
     _sig(lib, "dryad_hash_agg_init", c_int, [P, c_uint64, c_int, P, P, P])

@@ -161,14 +161,14 @@ def gather_rows(src: torch.Tensor, idx: torch.Tensor, out: Optional[torch.Tensor
 
 
 def fix_ties(keys: torch.Tensor, idx: torch.Tensor, rows: torch.Tensor, extra_off: int, extra: int,
-             *, max_run: int = 4096, descending: bool = False) -> torch.Tensor:
+             *, max_run: int = 4096, descending: bool = False, prefix_mask: int = (1 << 64) - 1) -> torch.Tensor:
     """Order runs of equal 64-bit prefixes by the next `extra` key bytes.  Returns a device int32
     counter of runs longer than max_run (left untouched)."""
     require_cuda(keys, idx, rows)
     long_runs = torch.zeros(1, dtype=torch.int32, device=keys.device)
     N.check(N.kernels().dryad_fix_ties(ptr(keys), ptr(idx), keys.numel(), ptr(rows), rows.shape[1],
-                                       extra_off, extra, max_run, int(descending), ptr(long_runs),
-                                       stream()), "fix_ties")
+                                       extra_off, extra, max_run, int(descending), prefix_mask,
+                                       ptr(long_runs), stream()), "fix_ties")
     _count()
     return long_runs
 

@@ -81,36 +81,74 @@ class RowSorter:
         return K.select_separators(skeys, total, self.world, self.descending)
 
     # -- the sort ------------------------------------------------------------------------------
+    WINDOW_BITS = 32          # radix passes cover this many key bits; ties are repaired from the rows
+    WINDOW_MAX_RUN = 64
+
+    @staticmethod
+    def _window(lo: int, hi: int):
+        """Bit window [b0, b1) of the 64-bit key prefix worth sorting when all keys lie in
+        [lo, hi]: leading bits common to lo and hi are skipped."""
+        top = max((lo ^ hi).bit_length(), RowSorter.WINDOW_BITS)
+        return top - RowSorter.WINDOW_BITS, top
+
+    def _local_sort(self, keys: torch.Tensor, m: int, src_rows: torch.Tensor, lo: int, hi: int):
+        """(64-bit prefix, row) -> sort permutation.  Fast path: 4 radix passes over a 32-bit window
+        + tie repair on the remaining key bytes; a partition with long runs of equal windows (not
+        TeraSort-like) falls back to all 8 passes."""
+        M64 = (1 << 64) - 1
+        b0, b1 = self._window(lo, hi)
+        if self.descending:
+            keys = ~keys
+        if b0 > 0:
+            skeys, sidx = K.radix_sort_pairs(keys, self.idx_a[:m], iota=True, begin_bit=b0, end_bit=b1,
+                                             keys_alt=self.keys_b[:m], vals_alt=self.idx_b[:m])
+            mask = (M64 << b0) & M64
+            first_byte = (64 - b0) // 8               # key bytes before this are equal inside a run
+            runs = K.fix_ties(skeys, sidx, src_rows, self.key_off + first_byte, self.key_len - first_byte,
+                              max_run=self.WINDOW_MAX_RUN, descending=self.descending, prefix_mask=mask)
+            if int(runs.item()) == 0:
+                self.last_long_runs = runs
+                return sidx
+            keys = K.extract_be64(src_rows[:m], self.key_off, out=self.keys_a)[:m]   # the sort clobbered them
+            if self.descending:
+                keys = ~keys
+        skeys, sidx = K.radix_sort_pairs(keys, self.idx_a[:m], iota=True, keys_alt=self.keys_b[:m],
+                                         vals_alt=self.idx_b[:m])
+        if self.key_len > 8:
+            self.last_long_runs = K.fix_ties(skeys, sidx, src_rows, self.key_off + 8, self.key_len - 8,
+                                             descending=self.descending)
+        return sidx
+
     def sort(self, rows: torch.Tensor):
         """rows: [n, width] uint8 on this rank.  Returns (sorted_rows_view, m): this rank's slice
         of the global order (rank r holds keys between separators r-1 and r)."""
         n = rows.shape[0]
         if n > self.max_rows:
             raise ValueError("RowSorter: more rows than the sorter was sized for")
+        M64 = (1 << 64) - 1
         if self.world > 1:
             seps = self._separators(rows)
             mode = "range_desc" if self.descending else "range_asc"
             self.shuffle.run([rows], mode=mode, key_col=0, key_kind=1, key_off=self.key_off, separators=seps)
+            sl = [x & M64 for x in seps.tolist()]              # host sync (tiny): this rank's key range
             m = self.shuffle.received_rows()[0]               # host sync: sizes the local sort
             src_rows = self.shuffle.recv[0][0]
             keys = self.shuffle.recv_key[0][:m]
+            r = self.rank
             if self.descending:
-                keys = ~keys
-            # copy is avoided: the radix sort ping-pongs between the receive key buffer and keys_b
-            skeys, sidx = K.radix_sort_pairs(keys, self.idx_a[:m], iota=True, keys_alt=self.keys_b[:m],
-                                             vals_alt=self.idx_b[:m])
+                lo = sl[r] if r < len(sl) else 0
+                hi = sl[r - 1] if r > 0 else M64
+                lo, hi = (~hi) & M64, (~lo) & M64              # keys are complemented before sorting
+            else:
+                lo = sl[r - 1] if r > 0 else 0
+                hi = sl[r] if r < len(sl) else M64
         else:
             m = n
             src_rows = rows
             K.extract_be64(rows, self.key_off, out=self.keys_a)
             keys = self.keys_a[:m]
-            if self.descending:
-                keys = ~keys
-            skeys, sidx = K.radix_sort_pairs(keys, self.idx_a[:m], iota=True, keys_alt=self.keys_b[:m],
-                                             vals_alt=self.idx_b[:m])
-        if self.key_len > 8:
-            self.last_long_runs = K.fix_ties(skeys, sidx, src_rows, self.key_off + 8, self.key_len - 8,
-                                             descending=self.descending)
+            lo, hi = 0, M64
+        sidx = self._local_sort(keys, m, src_rows, lo, hi)
         out = self.out[:m]
         K.gather_rows(src_rows, sidx, out)
         return out, m

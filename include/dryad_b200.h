@@ -131,9 +131,10 @@ int dryad_select_separators(const uint64_t* sorted, int64_t cnt, int pcount, int
 /* ---- row helpers for OrderBy on wide records ----------------------------------------------- */
 int dryad_extract_be64(const uint8_t* rows, int64_t n, int width, int key_off, uint64_t* out,
                        void* stream);
+/* Orders runs of equal (key & prefix_mask) by `extra` further key bytes read from the rows. */
 int dryad_fix_ties(const uint64_t* keys, uint32_t* idx, int64_t n, const uint8_t* rows, int width,
-                   int extra_off, int extra, int max_run, int descending, int32_t* long_runs,
-                   void* stream);
+                   int extra_off, int extra, int max_run, int descending, uint64_t prefix_mask,
+                   int32_t* long_runs, void* stream);
 int dryad_gather_rows(const void* in, const uint32_t* idx, void* out, int64_t n, int width,
                       void* stream);
 int dryad_check_sorted_rows(const uint8_t* rows, int64_t n, int width, int key_off, int key_len,

@@ -199,3 +199,22 @@ def test_expr_program_and_filter(K):
     ref = ((torch.remainder(a, 2) == 0) & (b < 0.5))
     # C# % is a truncating remainder: even-ness is identical for negatives
     assert torch.equal(flags.bool(), ref)
+
+
+def test_row_sorter_window_path_and_fallback(K):
+    """Random keys take the 4-pass window path; keys sharing long prefixes force the 8-pass
+    fallback; both must produce a fully ordered permutation of the input (10-byte keys)."""
+    from dryad_b200.parallel.dsort import RowSorter
+    from dryad_b200.parallel.symm import SymmetricArena
+    from dryad_b200.models import terasort
+    n = 300_000
+    rows = terasort.generate_rows(n, seed=9)
+    for variant in ("random", "shared_prefix", "descending"):
+        r = rows.clone()
+        if variant == "shared_prefix":
+            r[:, :6] = 7                      # only bytes 6..9 differ: every 32-bit window ties
+        s = RowSorter(SymmetricArena(1 << 20), n, 100, key_len=10, descending=(variant == "descending"))
+        out, m = s.sort(r)
+        res = K.check_sorted_rows(out, 0, 10, descending=(variant == "descending")).cpu()
+        assert m == n and int(res[0]) == 0, variant
+        assert (int(res[1]) & ((1 << 64) - 1)) == terasort.key_checksum(r), variant
