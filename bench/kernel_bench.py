@@ -109,6 +109,28 @@ def main():
         torch.bincount(gk, minlength=card)
     res["torch_index_add_bincount_ms"] = timeit(torch_agg)
 
+    # k-means iteration: tcgen05 kernel vs PyTorch (cuBLAS TF32 matmul + argmin + index_add)
+    try:
+        from dryad_b200.models import kmeans as KM
+        from dryad_b200.parallel.kmeans import KMeans
+        del rows, out, idx, keys, ka, kb, va, vb, gk, gv
+        torch.cuda.empty_cache()
+        npts, kk = min(n, 8_000_000), 1024
+        pts, centres = KM.generate(npts, kk, 5, dev)
+        km = KMeans(SymmetricArena(8 << 20), kk, npts)
+        km.set_centroids(centres + 0.05 * torch.randn_like(centres))
+        t = timeit(lambda: km.iterate(pts), iters=3, warmup=2)
+        res["kmeans_iter_ms"] = t
+        res["kmeans_points"] = npts
+        res["kmeans_Mpoints_s"] = npts / t / 1e3
+        res["kmeans_tflops_tf32"] = 2.0 * npts * kk * 128 / (t * 1e-3) / 1e12
+        res["kmeans_frac_of_measured_hbm"] = npts * 512 / (t * 1e-3) / 1e9 / hbm
+        torch.backends.cuda.matmul.allow_tf32 = True
+        c0 = km.centroids.clone()
+        res["kmeans_torch_cublas_tf32_ms"] = timeit(lambda: KM.reference_iteration(pts, c0), iters=2, warmup=1)
+    except Exception as ex:  # noqa: BLE001
+        res["kmeans_error"] = repr(ex)
+
     for k, v in res.items():
         print(f"{k}: {v:.4f}" if isinstance(v, float) else f"{k}: {v}")
     if a.json:

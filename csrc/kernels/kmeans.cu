@@ -1,0 +1,359 @@
+// K19 + C3: k-means assign + accumulate on the 5th-generation tensor cores.
+//
+// Not in the reference source: BASELINE.json config 5 builds k-means from DoWhile / Apply +
+// GroupBy-aggregate (LinqToDryad/DryadLinqQueryable.cs:1280-1306 is the client loop).  One
+// iteration = for every point the nearest centroid (argmin_j |c_j|^2 - 2 x.c_j), then per-centroid
+// sums and counts, then an all-reduce of those partials.
+//
+// km_assign is a persistent, warp-specialised kernel (one CTA per SM):
+//   warp 0      TMA producer: point tiles [128 x 128] fp32 (double buffered) and centroid k-blocks
+//               [128 x 32] fp32 through a 5-stage ring, all SWIZZLE_128B, mbarrier complete_tx.
+//   warp 1      tcgen05.mma issuer (one elected lane): kind::tf32, M=128 N=128 K=8, accumulating
+//               x.c_j for 128 points x 128 centroids into one of two TMEM accumulator buffers;
+//               tcgen05.commit releases ring slots and publishes accumulators.
+//   warps 2-5   epilogue: tcgen05.ld the accumulator rows (one point per thread), fused
+//               argmin with the fp32 centroid norms, then the point's exact fp32 coordinates are
+//               read back from the swizzled shared tile and added to the winner's sum with
+//               16-byte vector reductions (red.global.add.v4.f32) — sums stay fp32-exact, the
+//               TF32 product only decides near-ties.
+// km_update all-reduces sums/counts by loading every peer's partials over NVLink (peer-mapped
+// arena, fixed rank order => deterministic) and writes the new centroids and norms: no NCCL.
+#include "common.cuh"
+#include "../../include/dryad_b200.h"
+#include <cuda.h>
+#include <cudaTypedefs.h>
+
+namespace dryad { namespace km {
+
+constexpr int BM = 128, BN = 128, D = 128, KB = 32, NKB = D / KB;
+constexpr int B_STAGES = 5;
+constexpr int A_KB_BYTES = BM * KB * 4;          // 16 KiB
+constexpr int A_BYTES = A_KB_BYTES * NKB;        // 64 KiB
+constexpr int B_STAGE_BYTES = BN * KB * 4;       // 16 KiB
+constexpr int MAX_K = 2048;
+constexpr int THREADS = 192;
+constexpr int TMEM_COLS = 256;                   // two accumulator buffers of 128 fp32 columns
+
+constexpr size_t OFF_A = 0;
+constexpr size_t OFF_B = OFF_A + 2 * A_BYTES;
+constexpr size_t OFF_CN = OFF_B + (size_t)B_STAGES * B_STAGE_BYTES;
+constexpr size_t OFF_BAR = OFF_CN + MAX_K * 4;
+constexpr size_t SMEM_BYTES = OFF_BAR + 256 + 1024;   // + slack for 1024-byte alignment
+
+// ---- PTX wrappers ----------------------------------------------------------------------------
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+
+__device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count));
+}
+__device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive(uint64_t* bar) {
+  asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
+  const uint32_t addr = smem_u32(bar);
+  uint32_t done;
+  do {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+        "selp.u32 %0, 1, 0, p;\n\t}"
+        : "=r"(done) : "r"(addr), "r"(parity) : "memory");
+  } while (!done);
+}
+__device__ __forceinline__ void tma_load_2d(void* smem_dst, const CUtensorMap* map, int x, int y, uint64_t* bar) {
+  asm volatile(
+      "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];"
+      ::"r"(smem_u32(smem_dst)), "l"(map), "r"(smem_u32(bar)), "r"(x), "r"(y) : "memory");
+}
+__device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void tc_commit(uint64_t* bar) {
+  asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
+__device__ __forceinline__ void tc_mma_tf32(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t idesc, uint32_t accumulate) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "setp.ne.b32 p, %4, 0;\n\t"
+      "tcgen05.mma.cta_group::1.kind::tf32 [%0], %1, %2, %3, p;\n\t}"
+      ::"r"(tmem_d), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate) : "memory");
+}
+__device__ __forceinline__ void tc_ld_32x32(uint32_t taddr, float* v) {
+  uint32_t* r = reinterpret_cast<uint32_t*>(v);
+  asm volatile(
+      "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
+      "{%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15,%16,%17,%18,%19,%20,%21,%22,%23,%24,%25,%26,%27,%28,%29,%30,%31}, [%32];"
+      : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]),
+        "=r"(r[8]), "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15]),
+        "=r"(r[16]), "=r"(r[17]), "=r"(r[18]), "=r"(r[19]), "=r"(r[20]), "=r"(r[21]), "=r"(r[22]), "=r"(r[23]),
+        "=r"(r[24]), "=r"(r[25]), "=r"(r[26]), "=r"(r[27]), "=r"(r[28]), "=r"(r[29]), "=r"(r[30]), "=r"(r[31])
+      : "r"(taddr) : "memory");
+  asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+}
+__device__ __forceinline__ void red_add_v4(float* addr, float4 v) {
+  asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(addr), "f"(v.x), "f"(v.y), "f"(v.z), "f"(v.w) : "memory");
+}
+
+// K-major, SWIZZLE_128B shared-memory matrix descriptor: 8-row x 128-byte atoms stacked every
+// 1024 bytes (stride byte offset), descriptor version 1 (sm_100), layout type 2.
+__device__ __forceinline__ uint64_t make_desc(uint32_t saddr) {
+  uint64_t d = 0;
+  d |= (uint64_t)((saddr & 0x3FFFF) >> 4);             // start address
+  d |= (uint64_t)1 << 16;                              // leading byte offset (unused for swizzled K-major)
+  d |= (uint64_t)(1024 >> 4) << 32;                    // stride byte offset
+  d |= (uint64_t)1 << 46;                              // version
+  d |= (uint64_t)2 << 61;                              // SWIZZLE_128B
+  return d;
+}
+
+// c=F32 (1<<4), a=b=TF32 (2<<7, 2<<10), K-major both, N>>3 at bit 17, M>>4 at bit 24.
+constexpr uint32_t IDESC = (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(BN >> 3) << 17) | ((uint32_t)(BM >> 4) << 24);
+
+struct Bars {
+  uint64_t a_full[2], a_empty[2], b_full[B_STAGES], b_empty[B_STAGES], t_full[2], t_empty[2];
+  uint32_t tmem_base;
+};
+
+__global__ void __launch_bounds__(THREADS, 1)
+km_assign(const __grid_constant__ CUtensorMap map_x, const __grid_constant__ CUtensorMap map_c,
+          const float* __restrict__ cnorm, int64_t n, int k, int32_t* __restrict__ assign,
+          float* __restrict__ sums, unsigned long long* __restrict__ counts, float* __restrict__ inertia) {
+  extern __shared__ unsigned char smem_raw[];
+  unsigned char* smem = reinterpret_cast<unsigned char*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
+  unsigned char* sA = smem + OFF_A;
+  unsigned char* sB = smem + OFF_B;
+  float* s_cn = reinterpret_cast<float*>(smem + OFF_CN);
+  Bars* bars = reinterpret_cast<Bars*>(smem + OFF_BAR);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int nchunks = k / BN;
+  const int64_t ntiles = (n + BM - 1) / BM;
+
+  for (int i = threadIdx.x; i < k; i += THREADS) s_cn[i] = cnorm[i];
+  if (threadIdx.x == 0) {
+    for (int i = 0; i < 2; ++i) { mbar_init(&bars->a_full[i], 1); mbar_init(&bars->a_empty[i], 128);
+                                  mbar_init(&bars->t_full[i], 1); mbar_init(&bars->t_empty[i], 128); }
+    for (int i = 0; i < B_STAGES; ++i) { mbar_init(&bars->b_full[i], 1); mbar_init(&bars->b_empty[i], 1); }
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  if (warp == 1) {
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(&bars->tmem_base)), "n"(TMEM_COLS) : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = bars->tmem_base;
+
+  if (warp == 0) {
+    // ===== TMA producer =====
+    if (lane == 0) {
+      uint32_t it = 0, bs = 0, bphase = 0;
+      for (int64_t tile = blockIdx.x; tile < ntiles; tile += gridDim.x, ++it) {
+        const uint32_t ab = it & 1;
+        mbar_wait(&bars->a_empty[ab], ((it >> 1) & 1) ^ 1);
+        mbar_expect_tx(&bars->a_full[ab], A_BYTES);
+        for (int kb = 0; kb < NKB; ++kb)
+          tma_load_2d(sA + ab * A_BYTES + kb * A_KB_BYTES, &map_x, kb * KB, (int)(tile * BM), &bars->a_full[ab]);
+        for (int c = 0; c < nchunks; ++c)
+          for (int kb = 0; kb < NKB; ++kb) {
+            mbar_wait(&bars->b_empty[bs], bphase ^ 1);
+            mbar_expect_tx(&bars->b_full[bs], B_STAGE_BYTES);
+            tma_load_2d(sB + bs * B_STAGE_BYTES, &map_c, kb * KB, c * BN, &bars->b_full[bs]);
+            if (++bs == B_STAGES) { bs = 0; bphase ^= 1; }
+          }
+      }
+    }
+  } else if (warp == 1) {
+    // ===== MMA issuer =====
+    uint32_t it = 0, bs = 0, bphase = 0, cc = 0;
+    for (int64_t tile = blockIdx.x; tile < ntiles; tile += gridDim.x, ++it) {
+      const uint32_t ab = it & 1;
+      mbar_wait(&bars->a_full[ab], (it >> 1) & 1);
+      for (int c = 0; c < nchunks; ++c, ++cc) {
+        const uint32_t tb = cc & 1;
+        mbar_wait(&bars->t_empty[tb], ((cc >> 1) & 1) ^ 1);
+        tc_fence_after();
+        for (int kb = 0; kb < NKB; ++kb) {
+          mbar_wait(&bars->b_full[bs], bphase);
+          tc_fence_after();
+          if (lane == 0) {
+            const uint64_t ad = make_desc(smem_u32(sA + ab * A_BYTES + kb * A_KB_BYTES));
+            const uint64_t bd = make_desc(smem_u32(sB + bs * B_STAGE_BYTES));
+#pragma unroll
+            for (int kk = 0; kk < KB / 8; ++kk)   // K = 8 tf32 = 32 bytes per instruction
+              tc_mma_tf32(tmem_base + tb * BN, ad + (uint64_t)(kk * 2), bd + (uint64_t)(kk * 2), IDESC, (kb | kk) != 0);
+            tc_commit(&bars->b_empty[bs]);
+            if (kb == NKB - 1) tc_commit(&bars->t_full[tb]);
+          }
+          __syncwarp();
+          if (++bs == B_STAGES) { bs = 0; bphase ^= 1; }
+        }
+      }
+    }
+  } else {
+    // ===== epilogue: one point per thread =====
+    const int q = warp & 3;                         // TMEM lane quarter this warp may read
+    const int r = q * 32 + lane;                    // row inside the tile
+    uint32_t it = 0, cc = 0;
+    float local_inertia = 0.f;
+    for (int64_t tile = blockIdx.x; tile < ntiles; tile += gridDim.x, ++it) {
+      const uint32_t ab = it & 1;
+      float best = 3.4e38f;
+      int bi = 0;
+      for (int c = 0; c < nchunks; ++c, ++cc) {
+        const uint32_t tb = cc & 1;
+        mbar_wait(&bars->t_full[tb], (cc >> 1) & 1);
+        tc_fence_after();
+#pragma unroll 1
+        for (int sub = 0; sub < BN / 32; ++sub) {
+          float v[32];
+          tc_ld_32x32(tmem_base + ((uint32_t)(q * 32) << 16) + tb * BN + sub * 32, v);
+          const int j0 = c * BN + sub * 32;
+#pragma unroll
+          for (int j = 0; j < 32; ++j) {
+            float val = fmaf(-2.f, v[j], s_cn[j0 + j]);
+            if (val < best) { best = val; bi = j0 + j; }
+          }
+        }
+        tc_fence_before();
+        mbar_arrive(&bars->t_empty[tb]);
+      }
+      mbar_wait(&bars->a_full[ab], (it >> 1) & 1);  // TMA-written tile visible to this thread
+      const int64_t row = tile * BM + r;
+      if (row < n) {
+        assign[row] = bi;
+        atomicAdd(&counts[bi], 1ull);
+        float xn = 0.f;
+        float* dst = sums + (size_t)bi * D;
+        const unsigned char* base = sA + ab * A_BYTES + (r >> 3) * 1024 + (r & 7) * 128;
+#pragma unroll
+        for (int kb = 0; kb < NKB; ++kb)
+#pragma unroll
+          for (int ch = 0; ch < 8; ++ch) {
+            float4 x = *reinterpret_cast<const float4*>(base + kb * A_KB_BYTES + ((ch ^ (r & 7)) << 4));
+            xn += x.x * x.x + x.y * x.y + x.z * x.z + x.w * x.w;
+            red_add_v4(dst + kb * KB + ch * 4, x);
+          }
+        local_inertia += fmaxf(best + xn, 0.f);
+      }
+      mbar_arrive(&bars->a_empty[ab]);
+    }
+    local_inertia = warp_sum(local_inertia);
+    if (lane == 0 && inertia) atomicAdd(inertia, local_inertia);
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) {
+    tc_fence_after();
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "n"(TMEM_COLS) : "memory");
+  }
+}
+
+__global__ void km_norms(const float* __restrict__ c, int k, float* __restrict__ cnorm) {
+  int j = blockIdx.x * (blockDim.x / 32) + (threadIdx.x >> 5);
+  if (j >= k) return;
+  float s = 0.f;
+  for (int d = lane_id(); d < D; d += 32) { float v = c[(size_t)j * D + d]; s += v * v; }
+  s = warp_sum(s);
+  if (lane_id() == 0) cnorm[j] = s;
+}
+
+// All-reduce of (sums, counts) by peer loads + centroid update.  One thread per (centroid, dim).
+__global__ void km_update(float* const* __restrict__ peer_sums, unsigned long long* const* __restrict__ peer_counts,
+                          int world, int k, float* __restrict__ centroids, float* __restrict__ cnorm,
+                          unsigned long long* __restrict__ total_counts) {
+  int j = blockIdx.x;
+  int d = threadIdx.x;
+  unsigned long long cnt = 0;
+  float s = 0.f;
+  for (int r = 0; r < world; ++r) {            // fixed rank order: every rank computes identical bits
+    s += peer_sums[r][(size_t)j * D + d];
+    cnt += peer_counts[r][j];
+  }
+  float cval = cnt ? s / (float)cnt : centroids[(size_t)j * D + d];
+  centroids[(size_t)j * D + d] = cval;
+  float sq = warp_sum(cval * cval);
+  __shared__ float part[D / 32];
+  if ((d & 31) == 0) part[d >> 5] = sq;
+  __syncthreads();
+  if (d == 0) {
+    float t = 0.f;
+    for (int w = 0; w < D / 32; ++w) t += part[w];
+    cnorm[j] = t;
+    if (total_counts) total_counts[j] = cnt;
+  }
+}
+
+static PFN_cuTensorMapEncodeTiled_v12000 get_encode() {
+  static PFN_cuTensorMapEncodeTiled_v12000 fn = nullptr;
+  if (!fn) {
+    void* p = nullptr;
+    cudaDriverEntryPointQueryResult qres;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &qres) != cudaSuccess) return nullptr;
+    fn = (PFN_cuTensorMapEncodeTiled_v12000)p;
+  }
+  return fn;
+}
+
+static int make_map(CUtensorMap* m, const float* base, uint64_t rows) {
+  auto enc = get_encode();
+  if (!enc) return DRYAD_ERR_BAD_ARG;
+  cuuint64_t dims[2] = {(cuuint64_t)D, (cuuint64_t)rows};
+  cuuint64_t strides[1] = {(cuuint64_t)D * 4};
+  cuuint32_t box[2] = {(cuuint32_t)KB, (cuuint32_t)BM};
+  cuuint32_t estr[2] = {1, 1};
+  CUresult r = enc(m, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, (void*)base, dims, strides, box, estr,
+                   CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                   CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  return r == CUDA_SUCCESS ? DRYAD_OK : (int)(1000 + r);
+}
+
+}}  // namespace dryad::km
+
+extern "C" {
+using namespace dryad::km;
+
+int dryad_kmeans_norms(const float* centroids, int k, float* cnorm, void* stream) {
+  if (k <= 0) return DRYAD_ERR_BAD_ARG;
+  km_norms<<<(k + 7) / 8, 256, 0, (cudaStream_t)stream>>>(centroids, k, cnorm);
+  DRYAD_LAUNCH_CHECK();
+  return DRYAD_OK;
+}
+
+// points [n,128] fp32, centroids [k,128] fp32 (k multiple of 128, <= 2048), cnorm [k].
+// Outputs: assign[n] int32; sums[k,128] and counts[k] are ACCUMULATED into (zero them per
+// iteration); inertia (optional, 1 float) accumulates sum of squared distances.
+int dryad_kmeans_assign(const float* points, int64_t n, const float* centroids, const float* cnorm, int k,
+                        int32_t* assign, float* sums, unsigned long long* counts, float* inertia,
+                        int max_ctas, void* stream) {
+  if (n < 0 || k <= 0 || k % BN != 0 || k > MAX_K) return DRYAD_ERR_BAD_ARG;
+  if (n == 0) return DRYAD_OK;
+  if (((uintptr_t)points & 15) || ((uintptr_t)centroids & 15)) return DRYAD_ERR_BAD_ARG;
+  CUtensorMap mx, mc;
+  int rc = make_map(&mx, points, (uint64_t)n); if (rc) return rc;
+  rc = make_map(&mc, centroids, (uint64_t)k); if (rc) return rc;
+  DRYAD_CUDA_TRY(cudaFuncSetAttribute(km_assign, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SMEM_BYTES));
+  int dev = 0, sms = 148;
+  DRYAD_CUDA_TRY(cudaGetDevice(&dev));
+  DRYAD_CUDA_TRY(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
+  int64_t ntiles = (n + BM - 1) / BM;
+  int grid = (int)(ntiles < sms ? ntiles : sms);
+  if (max_ctas > 0 && grid > max_ctas) grid = max_ctas;
+  km_assign<<<grid, THREADS, SMEM_BYTES, (cudaStream_t)stream>>>(mx, mc, cnorm, n, k, assign, sums, counts, inertia);
+  DRYAD_LAUNCH_CHECK();
+  return DRYAD_OK;
+}
+
+int dryad_kmeans_update(float* const* peer_sums, unsigned long long* const* peer_counts, int world, int k,
+                        float* centroids, float* cnorm, unsigned long long* total_counts, void* stream) {
+  if (k <= 0 || world < 1 || world > DRYAD_MAX_PEERS) return DRYAD_ERR_BAD_ARG;
+  km_update<<<k, D, 0, (cudaStream_t)stream>>>(peer_sums, peer_counts, world, k, centroids, cnorm, total_counts);
+  DRYAD_LAUNCH_CHECK();
+  return DRYAD_OK;
+}
+
+}  // extern "C"

@@ -111,6 +111,11 @@ def _declare_kernels(lib):
     _sig(lib, "dryad_tokenize_count", c_int, [P, c_int64, c_int, c_int, P, P, c_size_t, P])
     _sig(lib, "dryad_tokenize_write", c_int, [P, c_int64, c_int, c_int, P, P, P, P, c_size_t, P])
     _sig(lib, "dryad_tokenize_verify", c_int, [P, P, P, P, P, c_int64, P, P])
+    _sig(lib, "dryad_kmeans_norms", c_int, [P, c_int, P, P])
+    _sig(lib, "dryad_kmeans_assign", c_int, [P, c_int64, P, P, c_int, P, P, P, P, c_int, P])
+    _sig(lib, "dryad_kmeans_update", c_int, [P, P, c_int, c_int, P, P, P, P])
+    _sig(lib, "dryad_radix_sort_pairs_u64_noalloc", c_int, [P, P, P, P, c_int64, c_int, c_int, c_int,
+                                                            C.POINTER(c_int), P])
     # optional symbols added by later kernels
     for nm, rt, at in _OPTIONAL:
         if hasattr(lib, nm):

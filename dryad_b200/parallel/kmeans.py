@@ -1,0 +1,61 @@
+"""Distributed k-means iteration (K19 + C3): tcgen05 assign/accumulate kernel per GPU, then an
+all-reduce of (sums, counts) by peer loads over NVLink and the centroid update — no NCCL.
+
+Points are sharded by rows (the DP partitioning of the dataset); centroids are replicated.
+"""
+from __future__ import annotations
+
+from typing import Optional
+
+import torch
+
+from .. import _native as N
+from ..ops import core as K
+from .symm import SymmetricArena
+
+D = 128
+
+
+class KMeans:
+    def __init__(self, arena: SymmetricArena, k: int, n_local_max: int):
+        if k % 128 or k > 2048:
+            raise ValueError("k must be a multiple of 128 and at most 2048")
+        self.arena, self.k = arena, k
+        self.world, self.rank = arena.world, arena.rank
+        dev = arena.device
+        self.sums, self.sums_off = arena.alloc((k, D), torch.float32)        # partials, peer-readable
+        self.counts, self.counts_off = arena.alloc((k,), torch.int64)
+        arena.check_symmetric("KMeans partials")
+        self.peer_sums = arena.peer_ptr_table(self.sums_off)
+        self.peer_counts = arena.peer_ptr_table(self.counts_off)
+        self.centroids = torch.empty((k, D), dtype=torch.float32, device=dev)
+        self.cnorm = torch.empty(k, dtype=torch.float32, device=dev)
+        self.total_counts = torch.zeros(k, dtype=torch.int64, device=dev)
+        self.assign = torch.empty(max(n_local_max, 1), dtype=torch.int32, device=dev)
+        self.inertia = torch.zeros(1, dtype=torch.float32, device=dev)
+
+    def set_centroids(self, c: torch.Tensor) -> None:
+        self.centroids.copy_(c)
+        N.check(N.kernels().dryad_kmeans_norms(K.ptr(self.centroids), self.k, K.ptr(self.cnorm), K.stream()), "kmeans_norms")
+        K._count()
+
+    def iterate(self, points: torch.Tensor, max_ctas: int = 0) -> None:
+        """One Lloyd iteration on this rank's shard ([n,128] fp32, contiguous).  Leaves the new
+        centroids in self.centroids (identical bits on every rank), assignments in self.assign."""
+        n = points.shape[0]
+        lib = N.kernels()
+        self.sums.zero_()
+        self.counts.zero_()
+        self.inertia.zero_()
+        if self.world > 1:
+            self.arena.barrier(slot=2)         # nobody is still reading last iteration's partials
+        N.check(lib.dryad_kmeans_assign(K.ptr(points), n, K.ptr(self.centroids), K.ptr(self.cnorm), self.k,
+                                        K.ptr(self.assign), K.ptr(self.sums), K.ptr(self.counts),
+                                        K.ptr(self.inertia), max_ctas, K.stream()), "kmeans_assign")
+        K._count()
+        if self.world > 1:
+            self.arena.barrier(slot=3)         # every rank's partials are complete and visible
+        N.check(lib.dryad_kmeans_update(K.ptr(self.peer_sums), K.ptr(self.peer_counts), self.world, self.k,
+                                        K.ptr(self.centroids), K.ptr(self.cnorm), K.ptr(self.total_counts),
+                                        K.stream()), "kmeans_update")
+        K._count()

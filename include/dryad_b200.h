@@ -228,6 +228,19 @@ int dryad_tokenize_verify(const uint8_t* text, const int64_t* starts, const int3
                           const int64_t* rep_start, const int32_t* rep_len, int64_t ntok,
                           unsigned long long* mismatches, void* stream);
 
+/* ---- K19 + C3 k-means on tcgen05/TMEM/TMA (BASELINE config 5; the client loop is
+ *      LinqToDryad/DryadLinqQueryable.cs:1280-1306 DoWhile) ------------------------------------
+ * points [n,128] fp32 and centroids [k,128] fp32 (k multiple of 128, k <= 2048), 16-byte aligned.
+ * dryad_kmeans_assign ACCUMULATES into sums[k,128], counts[k], inertia[1]: zero them per iteration. */
+int dryad_kmeans_norms(const float* centroids, int k, float* cnorm, void* stream);
+int dryad_kmeans_assign(const float* points, int64_t n, const float* centroids, const float* cnorm,
+                        int k, int32_t* assign, float* sums, unsigned long long* counts,
+                        float* inertia, int max_ctas, void* stream);
+/* All-reduce of the partials over peer-mapped memory + centroid update (no NCCL). */
+int dryad_kmeans_update(float* const* peer_sums, unsigned long long* const* peer_counts, int world,
+                        int k, float* centroids, float* cnorm, unsigned long long* total_counts,
+                        void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -218,3 +218,34 @@ def test_row_sorter_window_path_and_fallback(K):
         res = K.check_sorted_rows(out, 0, 10, descending=(variant == "descending")).cpu()
         assert m == n and int(res[0]) == 0, variant
         assert (int(res[1]) & ((1 << 64) - 1)) == terasort.key_checksum(r), variant
+
+
+@pytest.mark.parametrize("n,k", [(1000, 128), (70_001, 1024)])
+def test_kmeans_tcgen05_iteration(K, n, k):
+    """tcgen05/TMEM/TMA assign+accumulate vs an fp64 PyTorch reference of the same iteration."""
+    from dryad_b200.models import kmeans as KM
+    from dryad_b200.parallel.kmeans import KMeans
+    from dryad_b200.parallel.symm import SymmetricArena
+    pts, centres = KM.generate(n, k, seed=3, device="cuda")
+    init = centres + 0.05 * torch.randn_like(centres)
+    km = KMeans(SymmetricArena(8 << 20), k, n)
+    km.set_centroids(init)
+    km.iterate(pts)
+    torch.cuda.synchronize()
+    a = km.assign[:n].long()
+    p64, c64 = pts.double(), init.double()
+    d = (c64 * c64).sum(1)[None, :] - 2.0 * (p64 @ c64.T)
+    best = d.min(1).values
+    chosen = d.gather(1, a[:, None]).squeeze(1)
+    xn = (p64 * p64).sum(1)
+    # TF32 products may flip genuine near-ties only: the chosen centroid is (almost) the nearest
+    assert bool(((chosen + xn) <= (best + xn) * (1 + 2e-3) + 1e-3).all())
+    assert float((a == d.argmin(1)).float().mean()) > 0.999
+    # sums / counts are exact fp32 accumulations of the chosen assignment
+    ref_sums = torch.zeros((k, 128), dtype=torch.float64, device="cuda").index_add_(0, a, p64)
+    ref_cnt = torch.bincount(a, minlength=k)
+    assert torch.equal(km.total_counts, ref_cnt)
+    new_ref = torch.where(ref_cnt[:, None] > 0, ref_sums / ref_cnt.clamp(min=1)[:, None], c64)
+    assert torch.allclose(km.centroids.double(), new_ref, rtol=1e-4, atol=1e-4)
+    # the reported objective uses the TF32 distances (about 1e-3 of |c|^2 + 2|x.c| per point)
+    assert abs(float(km.inertia.item()) - float((chosen + xn).sum())) <= 3e-2 * float((chosen + xn).sum()) + 1.0
