@@ -27,6 +27,15 @@ class VertexFailure(Exception):
         self.node, self.part, self.version, self.cause = node, part, version, cause
 
 
+class InputReadError(Exception):
+    """A vertex could not read the output of (producer stage uid, partition): the graph manager
+    revokes that output and re-executes the producer (DrGraph::ReportFailure, DrGraph.cpp:392-415)."""
+
+    def __init__(self, producer_uid: int, producer_part: int, message: str = ""):
+        super().__init__(message or f"cannot read output of stage {producer_uid}[{producer_part}]")
+        self.producer_uid, self.producer_part = producer_uid, producer_part
+
+
 class JobExecutor:
     def __init__(self, context, plan: QueryGen, reporter=None):
         self.context = context
@@ -99,53 +108,105 @@ class JobExecutor:
             ins.append([halo if i > 0 else []])
         return ins
 
+    # ---- graph manager wiring -------------------------------------------------------------------
+    def _build_gm(self):
+        """Mirror the physical plan into the native graph manager: one GM stage per plan node, one
+        GM vertex per partition, edges expanded by the same connection rules the data follows."""
+        from ..sched.gm import CROSS_PRODUCT, POINTWISE, GraphManager
+        ctx = self.context
+        gm = GraphManager(max_failures=ctx.max_failures_per_vertex, speculative=ctx.enable_speculative_duplication)
+        sid = {}
+        self._gm_inputs: Dict[int, List[Tuple[int, int]]] = {}       # gm vertex -> [(producer uid, part)]
+        special = (NodeType.Concat, NodeType.Zip, NodeType.Reverse, NodeType.SlidingWindow)
+        for node in self.plan.nodes:
+            sid[node.uid] = gm.add_stage(f"{node.name}#{node.uid}", node.partition_count)
+        for node in self.plan.nodes:
+            head = node.members[0].type if node.type == NodeType.Super else node.type
+            first = gm.stage_first_vertex[sid[node.uid]]
+            for child, op in node.children:
+                cpc, pc = child.partition_count, node.partition_count
+                conservative = head in special or not (cpc == pc or cpc == 1 or pc == 1 or (pc and cpc % pc == 0))
+                kind = CROSS_PRODUCT if (op == ConnOp.CrossProduct or conservative) else POINTWISE
+                gm.connect(sid[child.uid], sid[node.uid], kind)
+                for d in range(pc):                      # same expansion order as gm_connect
+                    lst = self._gm_inputs.setdefault(first + d, [])
+                    if kind == CROSS_PRODUCT:
+                        srcs = range(cpc)
+                    elif cpc == pc:
+                        srcs = [d]
+                    elif cpc == 1:
+                        srcs = [0]
+                    elif pc == 1:
+                        srcs = range(cpc)
+                    else:
+                        g = cpc // pc
+                        srcs = range(d * g, d * g + g)
+                    lst.extend((child.uid, s) for s in srcs)
+        self._gm_stage_node = {sid[n.uid]: n for n in self.plan.nodes}
+        return gm
+
     # ---- run -----------------------------------------------------------------------------------
     def run(self) -> Dict[int, Any]:
+        """Drive the job: the native graph manager decides WHAT runs next (dependencies, versions,
+        retries, upstream invalidation, abort); this loop moves the data and runs the vertex code."""
         ctx = self.context
         rep = self.reporter
         rep.job_start(self.plan)
-        max_fail = ctx.max_failures_per_vertex
+        gm = self._build_gm()
+        self.gm = gm
+        for node in self.plan.nodes:
+            self.out[node.uid] = [None] * node.partition_count
         t_job = time.perf_counter()
+        gm.start()
         try:
-            for node in self.plan.nodes:
-                self.out[node.uid] = [None] * node.partition_count
-                for i in range(node.partition_count):
-                    version = 0
-                    failures = 0
-                    while True:
-                        rep.vertex_event(node, i, version, "starting")
-                        t0 = time.perf_counter()
-                        try:
-                            ins = self._inputs(node, i)
-                            if ctx.fault_injector is not None:
-                                ctx.fault_injector(node, i, version)
-                            env = VertexEnv(ctx, node.uid, i, version)
-                            ports = self.backend.run_vertex(node, i, ins, env)
-                            dt = time.perf_counter() - t0
-                            self.out[node.uid][i] = ports
-                            n_in = sum(self.backend.count(p) for inp in ins for p in inp)
-                            n_out = sum(self.backend.count(p) for p in ports)
-                            self.stats.append({"stage": node.uid, "stage_name": node.name, "part": i,
-                                               "version": version, "seconds": dt, "records_in": n_in,
-                                               "records_out": n_out})
-                            rep.vertex_event(node, i, version, "completed", seconds=dt, records_in=n_in, records_out=n_out)
-                            break
-                        except Exception as ex:  # noqa: BLE001  (vertex code is user code)
-                            failures += 1
-                            text = "".join(traceback.format_exception_only(type(ex), ex)).strip()
-                            rep.vertex_event(node, i, version, "failed", error=text)
-                            deterministic = isinstance(ex, DryadLinqException) and not getattr(ex, "transient", False)
-                            if failures >= max_fail or (deterministic and ctx.fail_fast_on_deterministic_errors):
-                                rep.job_stop(False, text)
-                                if isinstance(ex, DryadLinqException):
-                                    raise
-                                raise DryadLinqException(ErrorCode.DidNotCompleteSuccessfully,
-                                                         f"vertex {node.name}#{node.uid}[{i}] failed {failures} time(s): {text}", ex) from ex
-                            version += 1
-                # release inputs no longer needed (all parents done) — keeps HBM bounded
-                self._release_finished_children(node)
+            while True:
+                nxt = gm.next_ready(time.perf_counter() - t_job)
+                if nxt is None:
+                    break
+                v, version = nxt
+                info = gm.vertex(v)
+                node, i = self._gm_stage_node[info["stage"]], info["part"]
+                rep.vertex_event(node, i, version, "starting")
+                t0 = time.perf_counter()
+                try:
+                    ins = self._inputs(node, i)
+                    if ctx.fault_injector is not None:
+                        ctx.fault_injector(node, i, version)
+                    env = VertexEnv(ctx, node.uid, i, version)
+                    ports = self.backend.run_vertex(node, i, ins, env)
+                    dt = time.perf_counter() - t0
+                    self.out[node.uid][i] = ports
+                    n_in = sum(self.backend.count(p) for inp in ins for p in inp)
+                    n_out = sum(self.backend.count(p) for p in ports)
+                    self.stats.append({"stage": node.uid, "stage_name": node.name, "part": i, "version": version,
+                                       "seconds": dt, "records_in": n_in, "records_out": n_out})
+                    gm.completed(v, version, dt, float(n_in))
+                    rep.vertex_event(node, i, version, "completed", seconds=dt, records_in=n_in, records_out=n_out)
+                    self._release_finished_children(node)
+                except Exception as ex:  # noqa: BLE001  (vertex code is user code)
+                    text = "".join(traceback.format_exception_only(type(ex), ex)).strip()
+                    rep.vertex_event(node, i, version, "failed", error=text)
+                    bad = -1
+                    if isinstance(ex, InputReadError):
+                        want = (ex.producer_uid, ex.producer_part)
+                        edges = self._gm_inputs.get(v, [])
+                        bad = edges.index(want) if want in edges else -1
+                    rc = gm.failed(v, version, text, bad_input=bad)
+                    deterministic = isinstance(ex, DryadLinqException) and not getattr(ex, "transient", False)
+                    if rc == 2:                      # producer revoked: it will be re-executed
+                        self.out[ex.producer_uid][ex.producer_part] = None
+                        continue
+                    if rc == 1 or (deterministic and ctx.fail_fast_on_deterministic_errors):
+                        rep.job_stop(False, text)
+                        if isinstance(ex, DryadLinqException):
+                            raise
+                        raise DryadLinqException(ErrorCode.DidNotCompleteSuccessfully,
+                                                 f"{gm.error() or text}", ex) from ex
+            if gm.state != "Succeeded":
+                raise DryadLinqException(ErrorCode.DidNotCompleteSuccessfully,
+                                         f"job ended in state {gm.state}: {gm.error()}")
             results = self._commit_outputs()
-            rep.job_stop(True, "", seconds=time.perf_counter() - t_job)
+            rep.job_stop(True, "", seconds=time.perf_counter() - t_job, **gm.counters())
             return results
         except BaseException:
             self._discard_outputs()

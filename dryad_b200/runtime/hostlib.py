@@ -53,3 +53,55 @@ def declare(lib) -> None:
 def add(name, restype, argtypes):
     """Modules owning further host symbols (scheduler, mailbox, …) register them here."""
     _d(name, restype, argtypes)
+
+# ---- graph manager / dynamic managers -----------------------------------------------------------
+from ctypes import c_uint64  # noqa: E402
+
+_d("gm_create", P, [c_int, c_int])
+_d("gm_destroy", None, [P])
+_d("gm_set_outlier_params", None, [P, c_double, c_double, c_double])
+_d("gm_add_stage", c_int, [P, c_char_p, c_int])
+_d("gm_connect", c_int, [P, c_int, c_int, c_int])
+_d("gm_start", c_int, [P])
+_d("gm_next_ready", c_int, [P, c_double, C.POINTER(c_int), C.POINTER(c_int)])
+_d("gm_report_completed", c_int, [P, c_int, c_int, c_double, c_double])
+_d("gm_report_failed", c_int, [P, c_int, c_int, c_int, c_char_p])
+_d("gm_check_duplicates", c_int, [P, c_double])
+_d("gm_job_state", c_int, [P])
+_d("gm_vertex_count", c_int, [P])
+_d("gm_vertex_info", c_int, [P, c_int] + [C.POINTER(c_int)] * 5)
+_d("gm_counters", c_int, [P] + [C.POINTER(c_int)] * 4)
+_d("gm_error", c_int, [P, c_char_p, c_int])
+_d("gm_stage_model", c_int, [P, c_int] + [C.POINTER(c_double)] * 4 + [c_double])
+_d("dyn_aggregate_groups", c_int, [c_int, C.POINTER(c_int64), C.POINTER(c_int32), C.POINTER(c_int32), c_int, c_int64,
+                                   c_int64, C.POINTER(c_int32)])
+_d("dyn_consumer_count", c_int, [c_int64, c_int64, c_int, c_int])
+_d("dyn_broadcast_tree", c_int, [c_int, C.POINTER(c_int32)])
+PUMP_HANDLER = C.CFUNCTYPE(None, c_int64, c_int64, P)
+_d("pump_create", P, [c_int, PUMP_HANDLER, P])
+_d("pump_post", None, [P, c_int64, c_int64, c_double])
+_d("pump_wait_delivered", c_int64, [P, c_int64, c_double])
+_d("pump_destroy", None, [P])
+_d("mbox_create", P, [])
+_d("mbox_destroy", None, [P])
+_d("mbox_set", c_uint64, [P, c_char_p, c_char_p, c_char_p, c_int64])
+_d("mbox_block_on_status", c_uint64, [P, c_char_p, c_uint64, c_double, c_char_p, c_int32, c_char_p, c_int64,
+                                      C.POINTER(c_int64)])
+_d("ls_create", P, [c_int, C.POINTER(c_int32), c_double, c_double])
+_d("ls_destroy", None, [P])
+_d("ls_submit", None, [P, c_int64, C.POINTER(c_int32), c_int, c_int])
+_d("ls_computer_idle", c_int64, [P, c_int, c_double])
+_d("ls_waiting", c_int, [P])
+_d("fifo_create", P, [c_int])
+_d("fifo_destroy", None, [P])
+_d("fifo_write", c_int, [P, c_char_p, c_int64, c_double])
+_d("fifo_close_writer", None, [P])
+_d("fifo_abort", None, [P])
+_d("fifo_read", c_int64, [P, c_char_p, c_int64, c_double])
+_d("fifo_depth_now", c_int, [P])
+_d("cache_create", P, [c_char_p, c_int64, c_int64])
+_d("cache_destroy", None, [P])
+_d("cache_put", c_int, [P, c_char_p, c_char_p, c_int64])
+_d("cache_get", c_int64, [P, c_char_p, c_char_p, c_int64])
+_d("cache_stats", c_int, [P] + [C.POINTER(c_int64)] * 4)
+_d("fprint64", c_uint64, [c_uint64, c_char_p, c_int64])

@@ -1,0 +1,151 @@
+"""Headless job report: plan, per-stage statistics, schedule and automated failure diagnosis from a
+job directory (calypso.log + plan files).
+
+Reference: JobBrowser/JOM (job object model parsing `calypso.log`, JOM/jobinfo.cs, JOM/dryadlog.cs:32-345),
+the schedule (Gantt) view (JobBrowser/JobBrowser/jobschedule.cs) and the diagnosis engine
+(JobBrowser/JobBrowser/Diagnosis.cs: VertexFailureDiagnosis :311, JobFailureDiagnosis :594 with
+rules for serialization errors :545, failed-when-reading :573, plan parse errors :673, correlated
+machine failures :749, deterministic input failure :807).  The WinForms GUI itself is out of scope
+(no windowing here); this produces the same information as text / JSON.
+
+    python -m dryad_b200.tools.jobreport <job_dir> [--json]
+"""
+from __future__ import annotations
+
+import json
+import os
+import sys
+from collections import defaultdict
+from typing import Any, Dict, List
+
+
+def parse_calypso(path: str) -> List[Dict[str, Any]]:
+    events = []
+    with open(path) as f:
+        for line in f:
+            parts = line.rstrip("\n").split(",")
+            if len(parts) < 2:
+                continue
+            ev = {"ts": parts[0], "event": parts[1]}
+            for kv in parts[2:]:
+                if "=" in kv:
+                    k, v = kv.split("=", 1)
+                    ev[k] = v
+            events.append(ev)
+    return events
+
+
+def build_job(job_dir: str) -> Dict[str, Any]:
+    events = parse_calypso(os.path.join(job_dir, "calypso.log"))
+    stages: Dict[str, Dict[str, Any]] = {}
+    attempts: Dict[tuple, Dict[str, Any]] = {}
+    job: Dict[str, Any] = {"dir": job_dir, "success": None, "error": None, "seconds": None}
+    for e in events:
+        if e["event"] == "topology":
+            stages[e["stage"]] = {"id": int(e["stage"]), "name": e.get("stagename", ""), "type": e.get("type", ""),
+                                  "partitions": int(e.get("partitions", 0)), "children": e.get("children", "").split(),
+                                  "completed": 0, "failed": 0, "seconds": [], "records_in": 0, "records_out": 0}
+        elif e["event"] == "vertex":
+            key = (e["vertex"], e["version"])
+            a = attempts.setdefault(key, {"vertex": e["vertex"], "version": int(e["version"]), "stage": e.get("stage"),
+                                          "part": int(e.get("partInStage", 0)), "state": None, "start": None,
+                                          "end": None, "error": None})
+            a["state"] = e["state"]
+            if e["state"] == "starting":
+                a["start"] = e["ts"]
+            else:
+                a["end"] = e["ts"]
+            st = stages.get(e.get("stage"))
+            if e["state"] == "completed" and st is not None:
+                st["completed"] += 1
+                st["seconds"].append(float(e.get("seconds", 0)))
+                st["records_in"] += int(e.get("records_in", 0))
+                st["records_out"] += int(e.get("records_out", 0))
+            elif e["state"] == "failed":
+                a["error"] = e.get("error")
+                if st is not None:
+                    st["failed"] += 1
+        elif e["event"] == "stop":
+            job["success"] = e.get("success") == "True"
+            job["error"] = e.get("error")
+            job["seconds"] = float(e["seconds"]) if "seconds" in e else None
+            for k in ("completed", "failures", "duplicates", "invalidations"):
+                if k in e:
+                    job[k] = int(e[k])
+    job["stages"] = sorted(stages.values(), key=lambda s: s["id"])
+    job["attempts"] = sorted(attempts.values(), key=lambda a: (a["start"] or "", a["vertex"]))
+    job["diagnosis"] = diagnose(job)
+    return job
+
+
+def diagnose(job: Dict[str, Any]) -> List[str]:
+    """Post-mortem rules in the spirit of Diagnosis.cs."""
+    out: List[str] = []
+    failed = [a for a in job["attempts"] if a["state"] == "failed"]
+    if not failed and job.get("success"):
+        return ["job succeeded; no failed vertex attempts"]
+    by_vertex = defaultdict(list)
+    for a in failed:
+        by_vertex[a["vertex"]].append(a)
+    for v, atts in by_vertex.items():
+        errs = {(a["error"] or "").split(":")[0] for a in atts}
+        msg = (atts[-1]["error"] or "")
+        if len(atts) >= 2 and len(errs) == 1:
+            out.append(f"vertex {v} failed {len(atts)} times with the same error ({msg[:120]}): deterministic failure — "
+                       "most likely a bug in the user function or bad input records, not the cluster")
+        if "TypeNotSerializable" in msg or "FailedToDeserialize" in msg or "pickle" in msg.lower():
+            out.append(f"vertex {v}: serialization error — a record type cannot be (de)serialised")
+        if "cannot read" in msg.lower() or "ReadFileError" in msg or "StreamDoesNotExist" in msg:
+            out.append(f"vertex {v}: failed while READING its input — the producer's output was lost or is corrupt; "
+                       "the graph manager re-executes the producer")
+        if "overflow" in msg.lower():
+            out.append(f"vertex {v}: checked arithmetic overflow in an aggregate")
+        if "MemoryError" in msg or "out of memory" in msg.lower():
+            out.append(f"vertex {v}: ran out of memory — increase the partition count")
+    stages_failed = {a["stage"] for a in failed}
+    if len(by_vertex) >= 3 and len(stages_failed) == 1:
+        out.append(f"{len(by_vertex)} different vertices of stage {next(iter(stages_failed))} failed: the stage's "
+                   "operator fails independently of the partition")
+    if job.get("success") is False and job.get("error"):
+        out.append("job error: " + job["error"][:300])
+    if not out:
+        out.append("failed attempts were transient: every failed vertex succeeded on a later version")
+    return out
+
+
+def render(job: Dict[str, Any]) -> str:
+    lines = [f"Job {job['dir']}", f"  result: {'SUCCESS' if job['success'] else 'FAILURE' if job['success'] is False else 'unknown'}"
+             + (f" in {job['seconds']:.3f}s" if job.get("seconds") is not None else "")]
+    for k in ("completed", "failures", "duplicates", "invalidations"):
+        if k in job:
+            lines.append(f"  {k}: {job[k]}")
+    lines.append("Stages:")
+    lines.append(f"  {'id':>3} {'name':<38} {'parts':>5} {'done':>5} {'fail':>4} {'rec in':>10} {'rec out':>10} {'max s':>8} {'sum s':>8}")
+    for s in job["stages"]:
+        secs = s["seconds"] or [0.0]
+        lines.append(f"  {s['id']:>3} {s['name'][:38]:<38} {s['partitions']:>5} {s['completed']:>5} {s['failed']:>4} "
+                     f"{s['records_in']:>10} {s['records_out']:>10} {max(secs):>8.4f} {sum(secs):>8.4f}")
+    lines.append("Schedule (attempt order):")
+    for a in job["attempts"][:200]:
+        lines.append(f"  {a['start'] or '-':<28} v{a['vertex']:<8} ver {a['version']} -> {a['state']}")
+    lines.append("Diagnosis:")
+    lines += ["  - " + d for d in job["diagnosis"]]
+    plan = os.path.join(job["dir"], "QueryGraph__0.txt")
+    if os.path.exists(plan):
+        lines.append("Plan:")
+        lines += ["  " + l for l in open(plan).read().splitlines()]
+    return "\n".join(lines)
+
+
+def main(argv=None):
+    argv = argv or sys.argv[1:]
+    if not argv:
+        print(__doc__)
+        return 2
+    job = build_job(argv[0])
+    print(json.dumps(job, indent=1) if "--json" in argv else render(job))
+    return 0
+
+
+if __name__ == "__main__":
+    sys.exit(main())

@@ -44,6 +44,67 @@ int dh_partfile_read(const char* pt_path, char* base, int32_t cap, int64_t* size
 void dh_partfile_part_path(const char* base, int32_t index, char* out, int32_t cap);
 int dh_commit_part(const char* tmp_path, const char* final_path);
 
+/* ---- graph manager core: GraphManager/vertex/DrGraph.cpp, DrVertex.cpp, DrCohort.cpp,
+ *      stagemanager/DrStageStatistics.cpp, DrDefaultManager.cpp, DrDynamic*.{h,cpp} -------------- */
+void* gm_create(int max_failures, int speculative);
+void gm_destroy(void* h);
+void gm_set_outlier_params(void* h, double default_s, double min_s, double nonparam_fraction);
+int gm_add_stage(void* h, const char* name, int nparts);
+int gm_connect(void* h, int src_stage, int dst_stage, int kind);      /* 0 pointwise, 1 cross product */
+int gm_start(void* h);
+int gm_next_ready(void* h, double now, int* vertex, int* version);
+int gm_report_completed(void* h, int vertex, int version, double seconds, double bytes_in);
+int gm_report_failed(void* h, int vertex, int version, int bad_input, const char* message);
+int gm_check_duplicates(void* h, double now);
+int gm_job_state(void* h);                                            /* 0 not started,1 running,3 ok,4 failed */
+int gm_vertex_count(void* h);
+int gm_vertex_info(void* h, int vertex, int* stage, int* part, int* state, int* completed_version, int* failures);
+int gm_counters(void* h, int* completed, int* failures, int* duplicates, int* invalidations);
+int gm_error(void* h, char* buf, int cap);
+int gm_stage_model(void* h, int stage, double* startup, double* per_byte, double* sigma,
+                   double* threshold_for_bytes, double bytes);
+int dyn_aggregate_groups(int n, const int64_t* bytes, const int32_t* machine, const int32_t* pod,
+                         int max_inputs, int64_t max_bytes, int64_t skip_bytes, int32_t* group_out);
+int dyn_consumer_count(int64_t total_bytes, int64_t data_per_vertex, int min_count, int max_count);
+int dyn_broadcast_tree(int consumers, int32_t* copy_of);
+
+/* ---- message pump: GraphManager/kernel/DrMessagePump.h ------------------------------------------ */
+typedef void (*dh_pump_handler)(int64_t listener, int64_t message, void* user);
+void* pump_create(int threads, dh_pump_handler handler, void* user);
+void pump_post(void* h, int64_t listener, int64_t message, double delay_seconds);
+int64_t pump_wait_delivered(void* h, int64_t count, double timeout_seconds);
+void pump_destroy(void* h);
+
+/* ---- versioned mailbox: ProcessService/ProcessService.cs:674-746 ---------------------------------- */
+void* mbox_create(void);
+void mbox_destroy(void* h);
+uint64_t mbox_set(void* h, const char* key, const char* short_status, const void* data, int64_t n);
+uint64_t mbox_block_on_status(void* h, const char* key, uint64_t last_seen, double timeout_seconds,
+                              char* status_out, int32_t status_cap, void* data_out, int64_t cap, int64_t* n_out);
+
+/* ---- delay scheduler: LocalScheduler/LocalScheduler.cs, Queues.cs ---------------------------------- */
+void* ls_create(int ncomputers, const int32_t* rack_of, double rack_delay, double cluster_delay);
+void ls_destroy(void* h);
+void ls_submit(void* h, int64_t proc_id, const int32_t* computers, int n, int hard);
+int64_t ls_computer_idle(void* h, int computer, double age_bias);
+int ls_waiting(void* h);
+
+/* ---- FIFO channels, block cache + spill, Rabin fingerprint: channelfifo.cpp, ProcessService/Cache.cs,
+ *      SpillMachine.cs, classlib/DrFPrint.cpp, LinqToDryad/Hash64.cs ------------------------------- */
+void* fifo_create(int depth);
+void fifo_destroy(void* h);
+int fifo_write(void* h, const void* data, int64_t n, double timeout_seconds);
+void fifo_close_writer(void* h);
+void fifo_abort(void* h);
+int64_t fifo_read(void* h, void* out, int64_t cap, double timeout_seconds);
+int fifo_depth_now(void* h);
+void* cache_create(const char* spill_dir, int64_t low_water, int64_t high_water);
+void cache_destroy(void* h);
+int cache_put(void* h, const char* key, const void* data, int64_t n);
+int64_t cache_get(void* h, const char* key, void* out, int64_t cap);
+int cache_stats(void* h, int64_t* resident, int64_t* spills, int64_t* loads, int64_t* blocks);
+uint64_t fprint64(uint64_t seed, const void* data, int64_t n);
+
 #ifdef __cplusplus
 }
 #endif

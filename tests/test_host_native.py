@@ -1,0 +1,245 @@
+"""Native host runtime (libdryad_host.so): graph manager state machine, straggler model, dynamic
+managers, message pump, mailbox, delay scheduler, FIFO, cache/spill, fingerprint, record streams."""
+import os
+import threading
+import time
+
+import pytest
+
+from dryad_b200.channel import records as R
+from dryad_b200.channel.fifo import BlockCache, Fifo, fingerprint
+from dryad_b200.runtime.services import LocalScheduler, Mailbox, MessagePump
+from dryad_b200.sched import gm as G
+
+
+def _drain(gm, work=lambda v, ver: None, now=0.0):
+    order = []
+    while True:
+        nxt = gm.next_ready(now)
+        if nxt is None:
+            break
+        v, ver = nxt
+        work(v, ver)
+        order.append((v, ver))
+        gm.completed(v, ver, 0.01, 100.0)
+    return order
+
+
+def test_gm_runs_dag_in_dependency_order_and_finishes():
+    gm = G.GraphManager()
+    a = gm.add_stage("in", 3)
+    b = gm.add_stage("part", 3)
+    c = gm.add_stage("merge", 2)
+    d = gm.add_stage("out", 1)
+    gm.connect(a, b, G.POINTWISE)
+    gm.connect(b, c, G.CROSS_PRODUCT)
+    gm.connect(c, d, G.POINTWISE)
+    gm.start()
+    order = _drain(gm)
+    assert [v for v, _ in order] == list(range(9)) and all(ver == 0 for _, ver in order)
+    assert gm.state == "Succeeded" and gm.counters()["completed"] == 9
+
+
+def test_gm_retries_then_aborts_after_max_failures():
+    gm = G.GraphManager(max_failures=3)
+    s = gm.add_stage("s", 1)
+    gm.start()
+    for attempt in range(3):
+        v, ver = gm.next_ready(0.0)
+        assert ver == attempt                     # every attempt is a new version
+        rc = gm.failed(v, ver, "boom")
+        assert rc == (1 if attempt == 2 else 0)
+    assert gm.state == "Failed" and "failed 3 times" in gm.error()
+
+
+def test_gm_read_error_invalidates_and_reruns_the_producer():
+    gm = G.GraphManager()
+    p = gm.add_stage("producer", 1)
+    c = gm.add_stage("consumer", 1)
+    gm.connect(p, c)
+    gm.start()
+    v, ver = gm.next_ready(0.0)
+    gm.completed(v, ver, 0.1)
+    cv, cver = gm.next_ready(0.0)
+    assert gm.vertex(cv)["stage"] == c
+    assert gm.failed(cv, cver, "cannot read input", bad_input=0) == 2
+    v2, ver2 = gm.next_ready(0.0)                 # the producer runs again as version 1
+    assert v2 == v and ver2 == 1 and gm.counters()["invalidations"] == 1
+    gm.completed(v2, ver2, 0.1)
+    cv2, cver2 = gm.next_ready(0.0)
+    assert cv2 == cv and cver2 == 1
+    gm.completed(cv2, cver2, 0.1)
+    assert gm.state == "Succeeded"
+
+
+def test_gm_speculative_duplicate_first_finisher_wins():
+    gm = G.GraphManager()
+    gm.set_outlier_params(default_s=5.0, min_s=0.1)
+    s = gm.add_stage("s", 2)
+    gm.start()
+    v0, ver0 = gm.next_ready(0.0)
+    v1, ver1 = gm.next_ready(0.0)
+    gm.completed(v1, ver1, 1.0)
+    assert gm.check_duplicates(now=3.0) == 0      # below the threshold
+    assert gm.check_duplicates(now=6.0) == 1      # straggler: duplicate requested
+    dv, dver = gm.next_ready(6.0)
+    assert dv == v0 and dver == 1
+    assert gm.completed(dv, dver, 0.5) is True    # the duplicate wins...
+    assert gm.completed(v0, ver0, 9.0) is False   # ...and the original loses
+    assert gm.state == "Succeeded" and gm.counters()["duplicates"] == 1
+
+
+def test_stage_statistics_fit_and_outlier_threshold():
+    gm = G.GraphManager()
+    gm.set_outlier_params(default_s=600.0, min_s=0.5)
+    s = gm.add_stage("s", 40)
+    gm.start()
+    for i in range(30):
+        v, ver = gm.next_ready(0.0)
+        b = 1e6 * (1 + i % 5)
+        t = 2.0 + 3e-6 * b + (0.01 if i % 2 else -0.01)
+        if i == 7:
+            t = 500.0                              # one gross outlier must not wreck the fit
+        gm.completed(v, ver, t, b)
+    m = gm.stage_model(s, 3e6)
+    assert m["have_model"]
+    assert abs(m["startup"] - 2.0) < 0.5 and abs(m["per_byte"] - 3e-6) < 1e-6
+    assert m["outlier_threshold"] < 600.0
+
+
+def test_dynamic_managers():
+    groups = G.aggregate_groups([100] * 10, machine=[0, 0, 1, 1, 2, 2, 3, 3, 4, 4], pod=[0] * 5 + [1] * 5,
+                                max_inputs=4, max_bytes=10_000)
+    assert len(set(groups)) == 4                  # <=4 inputs per group, never across pods
+    assert groups[0] != groups[9]
+    big = G.aggregate_groups([10, 10**12, 10], [0, 0, 0], [0, 0, 0])
+    assert big[1] not in (big[0], big[2])         # oversize inputs are left alone
+    assert G.consumer_count(10 << 30, 1 << 30) == 10 and G.consumer_count(5, 1 << 30) == 1
+    copies, assign = G.broadcast_tree(16)
+    assert copies == 4 and sorted(set(assign)) == [0, 1, 2, 3]
+    assert G.broadcast_tree(4)[0] == 0
+
+
+def test_message_pump_delivers_under_listener_lock_and_delays():
+    seen, lock_violations, active = [], [], {}
+    mu = threading.Lock()
+
+    def handler(listener, message):
+        with mu:
+            if active.get(listener):
+                lock_violations.append(listener)
+            active[listener] = True
+        time.sleep(0.001)
+        with mu:
+            seen.append((listener, message, time.monotonic()))
+            active[listener] = False
+
+    pump = MessagePump(handler, threads=4)
+    t0 = time.monotonic()
+    for i in range(50):
+        pump.post(i % 3, i)
+    pump.post(7, 999, delay=0.2)
+    assert pump.wait_delivered(51, timeout=5.0) == 51
+    pump.close()
+    assert not lock_violations and len(seen) == 51
+    late = [t for l, m, t in seen if m == 999][0]
+    assert late - t0 >= 0.19
+
+
+def test_mailbox_versions_and_long_poll():
+    mb = Mailbox()
+    assert mb.block_on_status("cmd", 0, timeout=0.05) is None
+    v1 = mb.set("cmd", "start", b"payload-1")
+    got = mb.block_on_status("cmd", 0, timeout=0.1)
+    assert got == (v1, "start", b"payload-1")
+    assert mb.block_on_status("cmd", v1, timeout=0.05) is None      # nothing newer
+    threading.Timer(0.1, lambda: mb.set("cmd", "terminate", b"x")).start()
+    got = mb.block_on_status("cmd", v1, timeout=2.0)
+    assert got is not None and got[0] == v1 + 1 and got[1] == "terminate"
+    mb.close()
+
+
+def test_delay_scheduler_locality_then_rack_then_cluster():
+    ls = LocalScheduler(rack_of=[0, 0, 1, 1], rack_delay=1.0, cluster_delay=2.0)
+    ls.submit(1, [0])
+    ls.submit(2, [3], hard=True)
+    assert ls.computer_idle(2) is None                  # no affinity, nothing aged yet
+    assert ls.computer_idle(1, age_bias=1.5) == 1       # same rack as computer 0 after the rack delay
+    assert ls.computer_idle(0, age_bias=10.0) is None   # hard constraint never relaxes
+    assert ls.computer_idle(3) == 2
+    ls.submit(3, [0])
+    assert ls.computer_idle(2, age_bias=1.5) is None    # other rack: needs the cluster delay
+    assert ls.computer_idle(2, age_bias=2.5) == 3
+    assert ls.waiting == 0
+    ls.close()
+
+
+def test_fifo_blocking_depth_and_end_of_stream():
+    f = Fifo(depth=2)
+    assert f.write(b"a") and f.write(b"b")
+    assert f.write(b"c", timeout=0.05) is False         # full: blocking writer times out
+    got = []
+    t = threading.Thread(target=lambda: [got.append(f.read()) for _ in range(4)])
+    t.start()
+    assert f.write(b"c", timeout=2.0)
+    f.close_writer()
+    t.join()
+    assert got == [b"a", b"b", b"c", None]
+    f.close()
+
+
+def test_cache_spills_and_reloads(tmp_path):
+    c = BlockCache(str(tmp_path), low_water=3000, high_water=5000)
+    for i in range(8):
+        c.put(f"blk{i}", bytes([i]) * 1000)
+    st = c.stats()
+    assert st["spills"] >= 3 and st["resident"] <= 5000
+    for i in range(8):
+        assert c.get(f"blk{i}") == bytes([i]) * 1000
+    assert c.stats()["loads"] >= 3 and c.get("nope") is None
+    c.close()
+
+
+def test_fingerprint_properties():
+    a = fingerprint(b"hello world")
+    assert a == fingerprint(b"hello world") and a != fingerprint(b"hello worle") and a != fingerprint(b"hello worl")
+    assert fingerprint(b"") == 0 and fingerprint(b"abc", seed=5) != fingerprint(b"abc")
+
+
+def test_record_codec_primitives_and_roundtrip(tmp_path):
+    import ctypes as C
+    from dryad_b200 import _native as N
+    from dryad_b200.api.types import Grouping, LineRecord, Pair, Record
+    assert R.compact(0) == b"\x00" and R.compact(0x7F) == b"\x7f"
+    assert R.compact(0x80) == b"\x80\x00\x00\x80" and R.compact(0x12345678) == b"\x92\x34\x56\x78"
+    assert R.enc_string("hé") == b"\x02\x03h\xc3\xa9"
+    lib = N.host()
+    p = str(tmp_path / "prim.bin")
+    w = lib.dh_writer_open(p.encode(), 0, 0)
+    lib.dh_write_compact(w, 0x80)
+    lib.dh_write_i64(w, -2)
+    lib.dh_write_string(w, "hé".encode(), 3, 2)
+    lib.dh_writer_end_record(w)
+    lib.dh_writer_close(w, None, None, None)
+    raw = open(p, "rb").read()[16:]                       # skip the block header
+    assert raw == R.compact(0x80) + (-2).to_bytes(8, "little", signed=True) + R.enc_string("hé")
+    objs = [None, True, -5, 2**70, 1.5, "x", b"\x00\x01", (1, "a"), [1, [2]], Record(a=1, b="z"), Pair("k", 3),
+            Grouping("g", [1, 2]), LineRecord("line"), {"k": (1, 2)}]
+    for o in objs:
+        buf = memoryview(R.encode_record(o))
+        back, pos = R.decode(buf, 0)
+        assert back == o and pos == len(buf) and type(back) is type(o)
+
+
+def test_block_stream_never_splits_records_and_gzip(tmp_path):
+    from dryad_b200.channel import store
+    recs = [("r%d" % i, "x" * (i % 700)) for i in range(3000)]     # > one 256 KiB block
+    for comp in (None, "Gzip"):
+        uri = f"partfile://{tmp_path}/t_{comp}.pt"
+        store.write_table(uri, [recs[:1000], recs[1000:]], None, comp)
+        t = store.open_table(uri)
+        assert [len(p) for p in t.partitions] == [1000, 2000]
+        assert t.partitions[0] + t.partitions[1] == recs
+    raw = os.path.getsize(f"{tmp_path}/t_None.00000001")
+    gz = os.path.getsize(f"{tmp_path}/t_Gzip.00000001")
+    assert gz < raw / 5
