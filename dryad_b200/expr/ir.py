@@ -76,9 +76,8 @@ class Expr:
         if op in _BIT:
             return Expr(op, (a, b), "i")
         if a.kind == "o" or b.kind == "o":
-            if op == "add":
-                return Expr("concat", (a, b), "o")
-            raise TraceError(f"operator {op} on opaque values")
+            # opaque operands (strings, objects, untyped aggregates): host evaluation only
+            return Expr("truediv_o" if op == "truediv" else op, (a, b), "o")
         if op == "div":
             k = "f" if "f" in (a.kind, b.kind) else "i"   # C#: int / int truncates
         elif op == "truediv":
@@ -264,6 +263,7 @@ _PY = {
     "eq": operator.eq, "ne": operator.ne, "lt": operator.lt, "le": operator.le, "gt": operator.gt,
     "ge": operator.ge, "band": operator.and_, "bor": operator.or_, "bxor": operator.xor,
     "shl": operator.lshift, "shr": operator.rshift, "min": min, "max": max, "concat": operator.add,
+    "truediv_o": operator.truediv,
 }
 
 

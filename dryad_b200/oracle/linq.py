@@ -30,6 +30,47 @@ class Grouping(list):
     def __hash__(self):
         return hash((self.key, tuple(self)))
 
+    # LINQ-style aggregates over the group (so result selectors work on materialised groups too)
+    Key = property(lambda s: s.key)
+
+    def count(self, pred=None):
+        return sum(1 for x in self if pred is None or pred(x))
+
+    def sum(self, sel=None):
+        return sum_(list(self), sel)
+
+    def min(self, sel=None):
+        return min_(list(self), sel)
+
+    def max(self, sel=None):
+        return max_(list(self), sel)
+
+    def average(self, sel=None):
+        return average(list(self), sel)
+
+    def any(self, pred=None):
+        return any_(list(self), pred)
+
+    def all(self, pred):
+        return all_(list(self), pred)
+
+    def first(self):
+        return first(list(self))
+
+    def last(self):
+        return last(list(self))
+
+    def aggregate(self, decomposer, sel=None):
+        inst = decomposer() if isinstance(decomposer, type) else decomposer
+        inst.initialize(None)
+        acc = None
+        for i, x in enumerate(self):
+            v = sel(x) if sel else x
+            acc = inst.seed(v) if i == 0 else inst.accumulate(acc, v)
+        return inst.final_reduce(acc)
+
+    Count, Sum, Min, Max, Average, Any, All, First, Last, Aggregate = count, sum, min, max, average, any, all, first, last, aggregate
+
 
 def _hashable(k):
     if isinstance(k, dict):

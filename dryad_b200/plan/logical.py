@@ -94,4 +94,6 @@ def infer_schema(sample: Any) -> Schema:
         return {k: kind(v) for k, v in sample.items()}
     if hasattr(sample, "_fields"):
         return {k: kind(getattr(sample, k)) for k in sample._fields}
+    if type(sample) is tuple and sample and all(isinstance(v, (bool, numbers.Integral, numbers.Real)) for v in sample):
+        return {f"item{i + 1}": kind(v) for i, v in enumerate(sample)}
     return None

@@ -52,6 +52,8 @@ class QueryGen:
         self._check_output_rules()
         exprs = [simple_rewrite(e) for e in self.outputs]
         self.roots = [self.visit(e) for e in exprs]          # phase 1
+        for node, orig in zip(self.roots, self.outputs):     # results are keyed by the user's expression
+            node.params["qexpr_id"] = orig.id
         self._phase2()
         self._phase3()
         self._assign_unique_ids()
