@@ -212,6 +212,41 @@ def main():
         except Exception as ex:  # noqa: BLE001
             groupby = {"error": f"{type(ex).__name__}: {ex}"}
 
+    # ---- further BASELINE.json configs, short runs: broadcast join (4) and k-means (5) -------------
+    extra = {}
+    if not a.skip_groupby:
+        try:
+            from dryad_b200.models import joins
+            extra["broadcast_join"] = joins.bench(rank, world, dev, 50_000_000, 1 << 20, steps=a.steps, warmup=a.warmup,
+                                                  max_over_ranks=max_over_ranks, barrier=barrier)
+        except Exception as ex:  # noqa: BLE001
+            extra["broadcast_join"] = {"error": f"{type(ex).__name__}: {ex}"}
+        try:
+            from dryad_b200.models import kmeans as KM
+            from dryad_b200.parallel.kmeans import KMeans
+            torch.cuda.empty_cache()
+            npts, kk = 8_000_000, 1024
+            pts, centres = KM.generate(npts, kk, 5, dev, rank)
+            karena = SymmetricArena(16 << 20, rank, world, None, dev)
+            km = KMeans(karena, kk, npts)
+            km.set_centroids(centres + 0.05)
+            for _ in range(2):
+                km.iterate(pts)
+            barrier()
+            k0, k1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            k0.record()
+            for _ in range(a.steps):
+                km.iterate(pts)
+            k1.record()
+            barrier()
+            kms = max_over_ranks(k0.elapsed_time(k1)) / a.steps
+            extra["kmeans"] = {"metric": "kmeans_seconds_per_iteration", "value": kms * 1e-3, "unit": "s",
+                               "points_per_gpu": npts, "dims": 128, "k": kk, "points_per_s": world * npts / (kms * 1e-3),
+                               "tf32_tflops_per_gpu": 2.0 * npts * kk * 128 / (kms * 1e-3) / 1e12,
+                               "total_count_ok": int(km.total_counts.sum().item()) == world * npts}
+        except Exception as ex:  # noqa: BLE001
+            extra["kmeans"] = {"error": f"{type(ex).__name__}: {ex}"}
+
     if rank == 0:
         line = {
             "metric": METRIC, "value": gbs, "unit": "GB/s", "n_gpus": world, "steps": a.steps, "warmup": a.warmup,
@@ -222,7 +257,7 @@ def main():
                        "global_batch": world * n, "rows_per_gpu": n, "seq_len": W,
                        "parallelism": f"dp{world} (range-partitioned, one partition per GPU)",
                        "l2_policy": f"inputs exceed L2 ({n * W / 1e9:.1f} GB per GPU vs 126 MB)"},
-            "clocks": clocks, "gpu_launches": launches, "e2e": e2e, "groupby_agg": groupby,
+            "clocks": clocks, "gpu_launches": launches, "e2e": e2e, "groupby_agg": groupby, "extra": extra,
         }
         print(json.dumps(line))
     if world > 1:

@@ -237,6 +237,38 @@ __global__ void join_probe_kernel(const uint64_t* __restrict__ keys, const int32
   }
 }
 
+// K8 + C4 fused: broadcast join build.  Every rank owns a slice of the small (dimension) table;
+// this kernel replicates the slice's payload columns into EVERY rank's replica buffers and inserts
+// each key into EVERY rank's hash table, all with stores / system-scope atomics on peer HBM over
+// NVLink — the broadcast and the hash build are one pass over the slice (reference: Tee +
+// CrossProduct + Merge(parCount) then HashJoin, LinqToDryad/DryadLinqQueryGen.cs:2957-3001,
+// LinqToDryad/DryadLinqVertex.cs:6703-7315).
+struct BcastTables {
+  int world, ncols;
+  uint64_t* keys[DRYAD_MAX_PEERS];
+  int32_t* head[DRYAD_MAX_PEERS];
+  int32_t* next[DRYAD_MAX_PEERS];
+  int64_t* cols[DRYAD_MAX_PEERS][DRYAD_MAX_LANES];
+  const int64_t* src[DRYAD_MAX_LANES];
+  uint64_t cap;
+};
+
+__global__ void __launch_bounds__(256) join_build_bcast_kernel(BcastTables T, const uint64_t* __restrict__ keys,
+                                                               int64_t n, int64_t row_base, int32_t* status) {
+  int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  int64_t stride = (int64_t)gridDim.x * blockDim.x;
+  for (; i < n; i += stride) {
+    const uint64_t key = keys[i];
+    const int32_t g = (int32_t)(row_base + i);
+    for (int r = 0; r < T.world; ++r) {
+      for (int c = 0; c < T.ncols; ++c) T.cols[r][c][g] = T.src[c][i];
+      uint64_t s = find_or_insert<true>(T.keys[r], T.cap, key);
+      if (s == T.cap) { atomicMax(status, 1); continue; }
+      T.next[r][g] = atomicExch_system(&T.head[r][s], g);
+    }
+  }
+}
+
 // Set membership: out[i] = 1 if probe key is present.
 __global__ void set_contains_kernel(const uint64_t* __restrict__ keys, uint64_t cap,
                                     const uint64_t* __restrict__ probe_keys, int64_t n,
@@ -342,6 +374,30 @@ int dryad_join_probe(const uint64_t* tbl_keys, const int32_t* head, uint64_t cap
   if (!pow2(cap)) return DRYAD_ERR_BAD_ARG;
   if (n <= 0) return DRYAD_OK;
   join_probe_kernel<<<grid_for(n), 256, 0, (cudaStream_t)stream>>>(tbl_keys, head, cap, next, probe_keys, n, mode, counts_or_offsets, out_probe, out_build);
+  DRYAD_LAUNCH_CHECK();
+  return DRYAD_OK;
+}
+
+int dryad_join_table_init(uint64_t* tbl_keys, int32_t* head, uint64_t cap, void* stream) {
+  if (!pow2(cap)) return DRYAD_ERR_BAD_ARG;
+  join_init_kernel<<<grid_for((int64_t)cap), 256, 0, (cudaStream_t)stream>>>(tbl_keys, head, cap);
+  DRYAD_LAUNCH_CHECK();
+  return DRYAD_OK;
+}
+
+int dryad_join_build_bcast(const uint64_t* keys_local, int64_t n_local, int64_t row_base, int world,
+                           uint64_t* const* peer_keys, int32_t* const* peer_head, int32_t* const* peer_next,
+                           uint64_t cap, int ncols, const int64_t* const* col_src,
+                           int64_t* const* peer_cols /* [world][ncols] */, int32_t* status, void* stream) {
+  if (!pow2(cap) || world < 1 || world > DRYAD_MAX_PEERS || ncols < 0 || ncols > DRYAD_MAX_LANES) return DRYAD_ERR_BAD_ARG;
+  if (n_local <= 0) return DRYAD_OK;
+  BcastTables T; T.world = world; T.ncols = ncols; T.cap = cap;
+  for (int r = 0; r < world; ++r) {
+    T.keys[r] = peer_keys[r]; T.head[r] = peer_head[r]; T.next[r] = peer_next[r];
+    for (int c = 0; c < ncols; ++c) T.cols[r][c] = peer_cols[r * ncols + c];
+  }
+  for (int c = 0; c < ncols; ++c) T.src[c] = col_src[c];
+  join_build_bcast_kernel<<<grid_for(n_local), 256, 0, (cudaStream_t)stream>>>(T, keys_local, n_local, row_base, status);
   DRYAD_LAUNCH_CHECK();
   return DRYAD_OK;
 }

@@ -1,0 +1,99 @@
+"""Distributed joins.
+
+`BroadcastJoin` (K8 + C4): the small side is replicated to every GPU by the build kernel itself
+(stores + system atomics on peer HBM), then every rank probes its own fact partition locally — the
+large side never moves.  The reference expresses this as Tee + CrossProduct + Merge(parCount) feeding
+a HashJoin (LinqToDryad/DryadLinqQueryGen.cs:2957-3001); the planner rule that picks it by size is
+QueryGen._visit_join.
+
+`shuffle_hash_join`: both sides hash-partitioned by key with the fused shuffle, then a local hash
+join (the reference's default plan, DryadLinqQueryGen.cs:1483-1608).
+"""
+from __future__ import annotations
+
+import ctypes as C
+from typing import List, Sequence
+
+import torch
+
+from .. import _native as N
+from ..ops import core as K
+from .shuffle import ColSpec, FusedShuffle
+from .symm import SymmetricArena
+
+
+class BroadcastJoin:
+    def __init__(self, arena: SymmetricArena, dim_rows_total: int, ncols: int, load: float = 0.5):
+        self.arena, self.world, self.rank = arena, arena.world, arena.rank
+        self.nrows, self.ncols = int(dim_rows_total), ncols
+        self.cap = K._next_pow2(int(dim_rows_total / load) + 64)
+        dev = arena.device
+        self.keys, ko = arena.alloc((self.cap,), torch.int64)
+        self.head, ho = arena.alloc((self.cap,), torch.int32)
+        self.next, no = arena.alloc((max(self.nrows, 1),), torch.int32)
+        self.cols, offs = [], []
+        for _ in range(ncols):
+            t, o = arena.alloc((max(self.nrows, 1),), torch.int64)
+            self.cols.append(t)
+            offs.append(o)
+        arena.check_symmetric("BroadcastJoin tables")
+        W = self.world
+        self._pk = (C.c_void_p * W)(*[arena.peer_ptr(r, ko) for r in range(W)])
+        self._ph = (C.c_void_p * W)(*[arena.peer_ptr(r, ho) for r in range(W)])
+        self._pn = (C.c_void_p * W)(*[arena.peer_ptr(r, no) for r in range(W)])
+        self._pc = (C.c_void_p * max(W * ncols, 1))(*[arena.peer_ptr(r, offs[c]) for r in range(W) for c in range(ncols)])
+        self.status = torch.zeros(1, dtype=torch.int32, device=dev)
+
+    def build(self, keys_local: torch.Tensor, cols_local: Sequence[torch.Tensor], row_base: int) -> None:
+        """keys_local/cols_local: this rank's slice of the small side; row_base: its global offset."""
+        lib = N.kernels()
+        N.check(lib.dryad_join_table_init(K.ptr(self.keys), K.ptr(self.head), self.cap, K.stream()), "join_table_init")
+        K._count()
+        if self.world > 1:
+            self.arena.barrier(slot=2)             # every table is reset before any rank inserts
+        src = (C.c_void_p * max(self.ncols, 1))(*[c.data_ptr() for c in cols_local])
+        N.check(lib.dryad_join_build_bcast(K.ptr(keys_local), keys_local.numel(), row_base, self.world, self._pk,
+                                           self._ph, self._pn, self.cap, self.ncols, src, self._pc,
+                                           K.ptr(self.status), K.stream()), "join_build_bcast")
+        K._count()
+        if self.world > 1:
+            self.arena.barrier(slot=3)             # all slices have landed everywhere
+
+    def probe(self, probe_keys: torch.Tensor):
+        """(probe_idx, dim_row) int32 pairs for this rank's probe keys against the full small side."""
+        n = probe_keys.numel()
+        dev = probe_keys.device
+        lib = N.kernels()
+        counts = torch.empty(n, dtype=torch.int64, device=dev)
+        N.check(lib.dryad_join_probe(K.ptr(self.keys), K.ptr(self.head), self.cap, K.ptr(self.next), K.ptr(probe_keys),
+                                     n, 0, K.ptr(counts), None, None, K.stream()), "join_probe")
+        offs = torch.cumsum(counts, 0) - counts
+        total = int((offs[-1] + counts[-1]).item()) if n else 0
+        op = torch.empty(total, dtype=torch.int32, device=dev)
+        ob = torch.empty(total, dtype=torch.int32, device=dev)
+        if total:
+            N.check(lib.dryad_join_probe(K.ptr(self.keys), K.ptr(self.head), self.cap, K.ptr(self.next),
+                                         K.ptr(probe_keys), n, 1, K.ptr(offs), K.ptr(op), K.ptr(ob), K.stream()), "join_probe")
+        K._count(2)
+        return op, ob
+
+
+def shuffle_hash_join(arena: SymmetricArena, left: Sequence[torch.Tensor], right: Sequence[torch.Tensor],
+                      cap_left: int, cap_right: int):
+    """left/right: [key, payload...] int64 columns on this rank.  Both sides are hash-partitioned by
+    key to their owner rank with the fused shuffle, then joined locally.  Returns
+    (left_cols_received, right_cols_received, left_idx, right_idx)."""
+    mark = arena.mark()
+    try:
+        shl = FusedShuffle(arena, [ColSpec(8, torch.int64)] * len(left), cap_left, max_rows_in=left[0].numel())
+        shr = FusedShuffle(arena, [ColSpec(8, torch.int64)] * len(right), cap_right, max_rows_in=right[0].numel())
+        shl.run(list(left), mode="hash", key_col=0)
+        shr.run(list(right), mode="hash", key_col=0)
+        ml, mr = shl.received_rows()[0], shr.received_rows()[0]
+        lc = [shl.recv[c][0][:ml].clone() for c in range(len(left))]
+        rc = [shr.recv[c][0][:mr].clone() for c in range(len(right))]
+    finally:
+        arena.release_to(mark)
+    jt = K.JoinTable(rc[0].contiguous())
+    li, ri = jt.probe(lc[0].contiguous())
+    return lc, rc, li, ri

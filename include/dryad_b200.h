@@ -175,6 +175,15 @@ int dryad_join_probe(const uint64_t* tbl_keys, const int32_t* head, uint64_t cap
                      void* stream);
 int dryad_set_contains(const uint64_t* tbl_keys, uint64_t cap, const uint64_t* probe_keys,
                        int64_t n, uint8_t* out, void* stream);
+/* Broadcast join (K8 + C4): replicate this rank's slice of the small side (int64 payload columns)
+ * into every rank's replica buffers and insert its keys into every rank's hash table, over peer
+ * memory (LinqToDryad/DryadLinqQueryGen.cs:2957-3001 Tee+CrossProduct+Merge, then HashJoin). */
+int dryad_join_table_init(uint64_t* tbl_keys, int32_t* head, uint64_t cap, void* stream);
+int dryad_join_build_bcast(const uint64_t* keys_local, int64_t n_local, int64_t row_base, int world,
+                           uint64_t* const* peer_keys, int32_t* const* peer_head,
+                           int32_t* const* peer_next, uint64_t cap, int ncols,
+                           const int64_t* const* col_src, int64_t* const* peer_cols,
+                           int32_t* status, void* stream);
 
 /* ---- K12 fused elementwise programs + compaction: LinqToDryad/DryadLinqVertex.cs:74-198,
  *      LinqToDryad/DryadLinqCodeGen.cs:2084-2138 ----------------------------------------------- */

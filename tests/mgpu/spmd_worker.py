@@ -105,6 +105,25 @@ def gpu_checks(rank, world):
     dist.all_reduce(full_k[0]); dist.all_reduce(full_k[1])
     assert torch.equal(ol[0], full_k[0][ok_]) and torch.equal(ol[1], full_k[1][ok_])
 
+    # 3b. broadcast join: the small side is replicated by the build kernel, the fact side stays put
+    from dryad_b200.models import joins
+    jr = joins.bench(rank, world, dev, 1_000_000, 50_000, steps=1, warmup=1,
+                     max_over_ranks=lambda x: x, barrier=lambda: (dist.barrier(), torch.cuda.synchronize()))
+    assert jr["valid"], jr
+    # 3c. k-means: tcgen05 assign on every rank + peer-load all-reduce; all ranks end with equal centroids
+    from dryad_b200.models import kmeans as KM
+    from dryad_b200.parallel.kmeans import KMeans
+    pts, centres = KM.generate(200_000, 256, seed=21, device=dev, rank=rank)
+    km = KMeans(arena, 256, 200_000)
+    km.set_centroids(centres + 0.05)
+    for _ in range(2):
+        km.iterate(pts)
+    torch.cuda.synchronize()
+    allc = [torch.zeros_like(km.centroids) for _ in range(world)]
+    dist.all_gather(allc, km.centroids)
+    assert all(torch.equal(allc[0], c) for c in allc)
+    assert int(km.total_counts.sum().item()) == 200_000 * world
+
     # 4. the same sort through the public API (SPMD executor -> RowSorter)
     ctx = D.DryadLinqContext(platform="B200", device=str(dev))
     host = rows.cpu().pin_memory()

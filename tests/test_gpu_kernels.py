@@ -249,3 +249,10 @@ def test_kmeans_tcgen05_iteration(K, n, k):
     assert torch.allclose(km.centroids.double(), new_ref, rtol=1e-4, atol=1e-4)
     # the reported objective uses the TF32 distances (about 1e-3 of |c|^2 + 2|x.c| per point)
     assert abs(float(km.inertia.item()) - float((chosen + xn).sum())) <= 3e-2 * float((chosen + xn).sum()) + 1.0
+
+
+def test_broadcast_join_single_rank(K):
+    from dryad_b200.models import joins
+    r = joins.bench(0, 1, torch.device("cuda", 0), 500_000, 20_000, steps=1, warmup=1,
+                    max_over_ranks=lambda x: x, barrier=torch.cuda.synchronize)
+    assert r["valid"] and r["matches_local"] > 0
