@@ -269,6 +269,21 @@ __global__ void __launch_bounds__(256) join_build_bcast_kernel(BcastTables T, co
   }
 }
 
+// Probe for a build side with UNIQUE keys (dimension tables): one pass, no count/scan/emit —
+// out_row[i] = matching build row (0 when absent), matched[i] = 1/0.
+__global__ void join_probe_unique_kernel(const uint64_t* __restrict__ keys, const int32_t* __restrict__ head,
+                                         uint64_t cap, const uint64_t* __restrict__ probe_keys, int64_t n,
+                                         int32_t* __restrict__ out_row, uint8_t* __restrict__ matched) {
+  int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  int64_t stride = (int64_t)gridDim.x * blockDim.x;
+  for (; i < n; i += stride) {
+    uint64_t s = find_slot(keys, cap, probe_keys[i]);
+    int32_t r = (s != cap) ? head[s] : -1;
+    out_row[i] = r < 0 ? 0 : r;
+    matched[i] = r >= 0;
+  }
+}
+
 // Set membership: out[i] = 1 if probe key is present.
 __global__ void set_contains_kernel(const uint64_t* __restrict__ keys, uint64_t cap,
                                     const uint64_t* __restrict__ probe_keys, int64_t n,
@@ -374,6 +389,16 @@ int dryad_join_probe(const uint64_t* tbl_keys, const int32_t* head, uint64_t cap
   if (!pow2(cap)) return DRYAD_ERR_BAD_ARG;
   if (n <= 0) return DRYAD_OK;
   join_probe_kernel<<<grid_for(n), 256, 0, (cudaStream_t)stream>>>(tbl_keys, head, cap, next, probe_keys, n, mode, counts_or_offsets, out_probe, out_build);
+  DRYAD_LAUNCH_CHECK();
+  return DRYAD_OK;
+}
+
+int dryad_join_probe_unique(const uint64_t* tbl_keys, const int32_t* head, uint64_t cap,
+                            const uint64_t* probe_keys, int64_t n, int32_t* out_row, uint8_t* matched,
+                            void* stream) {
+  if (!pow2(cap)) return DRYAD_ERR_BAD_ARG;
+  if (n <= 0) return DRYAD_OK;
+  join_probe_unique_kernel<<<grid_for(n), 256, 0, (cudaStream_t)stream>>>(tbl_keys, head, cap, probe_keys, n, out_row, matched);
   DRYAD_LAUNCH_CHECK();
   return DRYAD_OK;
 }

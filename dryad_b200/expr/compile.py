@@ -177,7 +177,16 @@ def compile_program(outputs: Mapping[str, Expr], predicate: Optional[Expr], col_
 
 def run_on_gpu(outputs: Mapping[str, Expr], cols: Mapping[str, torch.Tensor], n: int,
                predicate: Optional[Expr] = None):
-    """Evaluate projections (+ optional predicate) in ONE kernel.  Returns (out_cols, flags)."""
+    """Evaluate projections (+ optional predicate) in ONE kernel.  Returns (out_cols, flags).
+    Preferred path: a kernel generated for this exact pipeline and compiled with NVRTC
+    (expr/codegen.py); fallback: the generic register-program interpreter kernel."""
+    import os
+    if os.environ.get("DRYAD_EXPR_CODEGEN", "1") != "0":
+        from . import codegen
+        try:
+            return codegen.run_fused(outputs, cols, n, predicate)
+        except codegen.CodegenUnavailable:
+            pass
     from ..ops import core as K
     from .ir import retype
     col_dtypes = {k: v.dtype for k, v in cols.items() if isinstance(v, torch.Tensor) and v.dim() == 1}

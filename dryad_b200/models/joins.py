@@ -18,7 +18,7 @@ def generate(n_fact: int, n_dim: int, seed: int, device, rank: int = 0, world: i
 
 
 def bench(rank, world, dev, n_fact, n_dim, steps, warmup, max_over_ranks, barrier, threshold=500):
-    from ..expr import col
+    from ..expr import col, where
     from ..expr.compile import run_on_gpu
     from ..ops import core as K
     from ..parallel.djoin import BroadcastJoin
@@ -29,15 +29,12 @@ def bench(rank, world, dev, n_fact, n_dim, steps, warmup, max_over_ranks, barrie
 
     def step():
         bj.build(dk, [da], base)                                      # fused broadcast + build
-        _, flags = run_on_gpu({}, {"v": fv}, n_fact, predicate=col("v") >= threshold)   # Where
-        idx, m = K.compact_flags(flags)
-        pk = K.gather_rows(fk, idx)
-        pv = K.gather_rows(fv, idx)
-        pi, di = bj.probe(pk)                                         # local probe: the fact side never moves
-        v = K.gather_rows(pv, pi)
+        di, matched = bj.probe_unique(fk)                             # local probe: the fact side never moves
         a = K.gather_rows(bj.cols[0], di)
-        out, _ = run_on_gpu({"r": col("v") * col("a")}, {"v": v, "a": a}, v.numel())      # Select
-        return K.reduce(out["r"], "sum"), v.numel()
+        # Where(v >= t) and Select(v * attr) fused into one register program; unmatched rows give 0
+        out, flags = run_on_gpu({"r": where((col("v") >= threshold) & (col("m") != 0), col("v") * col("a"), 0)},
+                                {"v": fv, "a": a, "m": matched}, n_fact, predicate=(col("v") >= threshold) & (col("m") != 0))
+        return K.reduce(out["r"], "sum"), K.reduce(flags, "sum")
 
     for _ in range(max(warmup, 1)):
         s, m = step()
@@ -52,6 +49,7 @@ def bench(rank, world, dev, n_fact, n_dim, steps, warmup, max_over_ranks, barrie
     ms = max_over_ranks(e0.elapsed_time(e1)) / steps
     sel = fv >= threshold
     ref = int((fv[sel] * ((fk[sel] * 2654435761) % 97)).sum().item())
+    m = int(m.item())
     ok = int(s.item()) == ref and m == int(sel.sum().item())
     return {"metric": "broadcast_join_fact_rows_per_s", "value": world * n_fact / (ms * 1e-3), "unit": "rows/s",
             "ms_per_step": ms, "fact_rows_per_gpu": n_fact, "dim_rows": n_dim, "matches_local": m, "valid": bool(ok),

@@ -78,6 +78,17 @@ class BroadcastJoin:
         return op, ob
 
 
+    def probe_unique(self, probe_keys: torch.Tensor):
+        """For a small side with unique keys: (dim_row int32 [n], matched uint8 [n]) in one pass."""
+        n = probe_keys.numel()
+        rows = torch.empty(n, dtype=torch.int32, device=probe_keys.device)
+        matched = torch.empty(n, dtype=torch.uint8, device=probe_keys.device)
+        N.check(N.kernels().dryad_join_probe_unique(K.ptr(self.keys), K.ptr(self.head), self.cap, K.ptr(probe_keys), n,
+                                                    K.ptr(rows), K.ptr(matched), K.stream()), "join_probe_unique")
+        K._count()
+        return rows, matched
+
+
 def shuffle_hash_join(arena: SymmetricArena, left: Sequence[torch.Tensor], right: Sequence[torch.Tensor],
                       cap_left: int, cap_right: int):
     """left/right: [key, payload...] int64 columns on this rank.  Both sides are hash-partitioned by

@@ -179,6 +179,10 @@ int dryad_set_contains(const uint64_t* tbl_keys, uint64_t cap, const uint64_t* p
  * into every rank's replica buffers and insert its keys into every rank's hash table, over peer
  * memory (LinqToDryad/DryadLinqQueryGen.cs:2957-3001 Tee+CrossProduct+Merge, then HashJoin). */
 int dryad_join_table_init(uint64_t* tbl_keys, int32_t* head, uint64_t cap, void* stream);
+/* Probe against a build side whose keys are unique: out_row[i] = build row (0 if none), matched[i]. */
+int dryad_join_probe_unique(const uint64_t* tbl_keys, const int32_t* head, uint64_t cap,
+                            const uint64_t* probe_keys, int64_t n, int32_t* out_row, uint8_t* matched,
+                            void* stream);
 int dryad_join_build_bcast(const uint64_t* keys_local, int64_t n_local, int64_t row_base, int world,
                            uint64_t* const* peer_keys, int32_t* const* peer_head,
                            int32_t* const* peer_next, uint64_t cap, int ncols,

@@ -256,3 +256,22 @@ def test_broadcast_join_single_rank(K):
     r = joins.bench(0, 1, torch.device("cuda", 0), 500_000, 20_000, steps=1, warmup=1,
                     max_over_ranks=lambda x: x, barrier=torch.cuda.synchronize)
     assert r["valid"] and r["matches_local"] > 0
+
+
+def test_expr_interpreter_fallback_matches_codegen(K, monkeypatch):
+    from dryad_b200.expr import col, where
+    from dryad_b200.expr.compile import run_on_gpu
+    n = 10_007
+    a = torch.randint(-50, 50, (n,), dtype=torch.int64, device="cuda")
+    b = torch.rand(n, dtype=torch.float64, device="cuda")
+    proj = {"x": where(col("a") % 3 == 0, col("a") // 2, -col("a")), "y": (col("b") * 4.0).floor() + col("a"),
+            "h": col("a").hash()}
+    pred = (col("a") > -10) & (col("b") < 0.7)
+    o1, f1 = run_on_gpu(proj, {"a": a, "b": b}, n, predicate=pred)
+    monkeypatch.setenv("DRYAD_EXPR_CODEGEN", "0")
+    o2, f2 = run_on_gpu(proj, {"a": a, "b": b}, n, predicate=pred)
+    for k in proj:
+        assert torch.equal(o1[k], o2[k]), k
+    assert torch.equal(f1, f2)
+    ref_x = torch.where(torch.fmod(a, 3) == 0, torch.div(a, 2, rounding_mode="trunc"), -a)
+    assert torch.equal(o1["x"], ref_x)
