@@ -269,6 +269,24 @@ __global__ void __launch_bounds__(256) join_build_bcast_kernel(BcastTables T, co
   }
 }
 
+// K17 + C4: replicate this rank's slice of (key, payload...) columns into every rank's replica
+// buffers with 16-byte P2P stores (the "CP" copy vertex of the reference's broadcast tree,
+// DryadVertex/VertexHost/vertex/vertexHost/vertexHost.cpp:331-571, done by the producer itself).
+struct ReplTables {
+  int world, ncols;
+  int64_t* dst[DRYAD_MAX_PEERS][DRYAD_MAX_LANES + 1];
+  const int64_t* src[DRYAD_MAX_LANES + 1];
+};
+__global__ void __launch_bounds__(256) replicate_slice_kernel(ReplTables T, int64_t n, int64_t row_base) {
+  int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  int64_t stride = (int64_t)gridDim.x * blockDim.x;
+  for (; i < n; i += stride)
+    for (int c = 0; c < T.ncols; ++c) {
+      const int64_t v = T.src[c][i];
+      for (int r = 0; r < T.world; ++r) T.dst[r][c][row_base + i] = v;
+    }
+}
+
 // Probe for a build side with UNIQUE keys (dimension tables): one pass, no count/scan/emit —
 // out_row[i] = matching build row (0 when absent), matched[i] = 1/0.
 __global__ void join_probe_unique_kernel(const uint64_t* __restrict__ keys, const int32_t* __restrict__ head,
@@ -389,6 +407,18 @@ int dryad_join_probe(const uint64_t* tbl_keys, const int32_t* head, uint64_t cap
   if (!pow2(cap)) return DRYAD_ERR_BAD_ARG;
   if (n <= 0) return DRYAD_OK;
   join_probe_kernel<<<grid_for(n), 256, 0, (cudaStream_t)stream>>>(tbl_keys, head, cap, next, probe_keys, n, mode, counts_or_offsets, out_probe, out_build);
+  DRYAD_LAUNCH_CHECK();
+  return DRYAD_OK;
+}
+
+int dryad_replicate_slice(int world, int ncols, const int64_t* const* src, int64_t* const* peer_dst /* [world][ncols] */,
+                          int64_t n_local, int64_t row_base, void* stream) {
+  if (world < 1 || world > DRYAD_MAX_PEERS || ncols < 1 || ncols > DRYAD_MAX_LANES + 1) return DRYAD_ERR_BAD_ARG;
+  if (n_local <= 0) return DRYAD_OK;
+  ReplTables T; T.world = world; T.ncols = ncols;
+  for (int c = 0; c < ncols; ++c) T.src[c] = src[c];
+  for (int r = 0; r < world; ++r) for (int c = 0; c < ncols; ++c) T.dst[r][c] = peer_dst[r * ncols + c];
+  replicate_slice_kernel<<<grid_for(n_local), 256, 0, (cudaStream_t)stream>>>(T, n_local, row_base);
   DRYAD_LAUNCH_CHECK();
   return DRYAD_OK;
 }

@@ -111,6 +111,7 @@ def _declare_kernels(lib):
     _sig(lib, "dryad_tokenize_count", c_int, [P, c_int64, c_int, c_int, P, P, c_size_t, P])
     _sig(lib, "dryad_tokenize_write", c_int, [P, c_int64, c_int, c_int, P, P, P, P, c_size_t, P])
     _sig(lib, "dryad_tokenize_verify", c_int, [P, P, P, P, P, c_int64, P, P])
+    _sig(lib, "dryad_replicate_slice", c_int, [c_int, c_int, P, P, c_int64, c_int64, P])
     _sig(lib, "dryad_join_table_init", c_int, [P, P, c_uint64, P])
     _sig(lib, "dryad_join_probe_unique", c_int, [P, P, c_uint64, P, c_int64, P, P, P])
     _sig(lib, "dryad_join_build_bcast", c_int, [P, c_int64, c_int64, c_int, P, P, P, c_uint64, c_int, P, P, P, P])

@@ -31,6 +31,7 @@ class BroadcastJoin:
         self.keys, ko = arena.alloc((self.cap,), torch.int64)
         self.head, ho = arena.alloc((self.cap,), torch.int32)
         self.next, no = arena.alloc((max(self.nrows, 1),), torch.int32)
+        self.rkeys, rko = arena.alloc((max(self.nrows, 1),), torch.int64)     # replicated key column
         self.cols, offs = [], []
         for _ in range(ncols):
             t, o = arena.alloc((max(self.nrows, 1),), torch.int64)
@@ -42,10 +43,29 @@ class BroadcastJoin:
         self._ph = (C.c_void_p * W)(*[arena.peer_ptr(r, ho) for r in range(W)])
         self._pn = (C.c_void_p * W)(*[arena.peer_ptr(r, no) for r in range(W)])
         self._pc = (C.c_void_p * max(W * ncols, 1))(*[arena.peer_ptr(r, offs[c]) for r in range(W) for c in range(ncols)])
+        self._prepl = (C.c_void_p * (W * (ncols + 1)))(*[arena.peer_ptr(r, o) for r in range(W) for o in [rko] + offs])
         self.status = torch.zeros(1, dtype=torch.int32, device=dev)
 
     def build(self, keys_local: torch.Tensor, cols_local: Sequence[torch.Tensor], row_base: int) -> None:
-        """keys_local/cols_local: this rank's slice of the small side; row_base: its global offset."""
+        """Replicate this rank's slice of the small side (key + payload columns) to every rank with
+        P2P stores, then build the hash table over the full replica LOCALLY (local atomics are far
+        cheaper than remote ones).  `row_base`: global offset of this rank's slice."""
+        lib = N.kernels()
+        if self.world > 1:
+            self.arena.barrier(slot=2)             # nobody still probes the previous replica
+        src = (C.c_void_p * (self.ncols + 1))(keys_local.data_ptr(), *[c.data_ptr() for c in cols_local])
+        N.check(lib.dryad_replicate_slice(self.world, self.ncols + 1, src, self._prepl, keys_local.numel(), row_base,
+                                          K.stream()), "replicate_slice")
+        K._count()
+        if self.world > 1:
+            self.arena.barrier(slot=3)             # all slices have landed everywhere
+        N.check(lib.dryad_join_build(K.ptr(self.keys), K.ptr(self.head), self.cap, K.ptr(self.rkeys), K.ptr(self.next),
+                                     self.nrows, K.ptr(self.status), K.stream()), "join_build")
+        K._count(2)
+
+    def build_remote_atomics(self, keys_local: torch.Tensor, cols_local: Sequence[torch.Tensor], row_base: int) -> None:
+        """Alternative single-kernel form: insert into every rank's table with system-scope atomics
+        over NVLink (kept for comparison; slower at 8 GPUs than replicate + local build)."""
         lib = N.kernels()
         N.check(lib.dryad_join_table_init(K.ptr(self.keys), K.ptr(self.head), self.cap, K.stream()), "join_table_init")
         K._count()

@@ -62,6 +62,21 @@ class RowSorter:
         self.idx_b = torch.empty(n, dtype=torch.int32, device=dev)
         self.out = torch.empty((n, width), dtype=torch.uint8, device=dev)
         self.last_long_runs: Optional[torch.Tensor] = None
+        self.profile = False                  # diagnostic: record per-phase device times in self.timing
+        self.timing: dict = {}
+        self._marks: list = []
+
+    def _mark(self, name: str) -> None:
+        if self.profile:
+            e = torch.cuda.Event(enable_timing=True)
+            e.record()
+            self._marks.append((name, e))
+
+    def _finish_marks(self) -> None:
+        if self.profile and self._marks:
+            torch.cuda.synchronize()
+            self.timing = {b[0]: a[1].elapsed_time(b[1]) for a, b in zip(self._marks, self._marks[1:])}
+            self._marks = []
 
     # -- separators ----------------------------------------------------------------------------
     def _separators(self, rows: torch.Tensor) -> torch.Tensor:
@@ -126,12 +141,16 @@ class RowSorter:
         if n > self.max_rows:
             raise ValueError("RowSorter: more rows than the sorter was sized for")
         M64 = (1 << 64) - 1
+        self._mark("start")
         if self.world > 1:
             seps = self._separators(rows)
+            self._mark("sample+separators")
             mode = "range_desc" if self.descending else "range_asc"
             self.shuffle.run([rows], mode=mode, key_col=0, key_kind=1, key_off=self.key_off, separators=seps)
+            self._mark("shuffle")
             sl = [x & M64 for x in seps.tolist()]              # host sync (tiny): this rank's key range
             m = self.shuffle.received_rows()[0]               # host sync: sizes the local sort
+            self._mark("host sync")
             src_rows = self.shuffle.recv[0][0]
             keys = self.shuffle.recv_key[0][:m]
             r = self.rank
@@ -149,6 +168,9 @@ class RowSorter:
             keys = self.keys_a[:m]
             lo, hi = 0, M64
         sidx = self._local_sort(keys, m, src_rows, lo, hi)
+        self._mark("local sort + ties")
         out = self.out[:m]
         K.gather_rows(src_rows, sidx, out)
+        self._mark("gather")
+        self._finish_marks()
         return out, m

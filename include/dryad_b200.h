@@ -178,6 +178,10 @@ int dryad_set_contains(const uint64_t* tbl_keys, uint64_t cap, const uint64_t* p
 /* Broadcast join (K8 + C4): replicate this rank's slice of the small side (int64 payload columns)
  * into every rank's replica buffers and insert its keys into every rank's hash table, over peer
  * memory (LinqToDryad/DryadLinqQueryGen.cs:2957-3001 Tee+CrossProduct+Merge, then HashJoin). */
+/* K17: copy this rank's slice of up to 9 int64 columns into every rank's replica buffers (P2P stores;
+ * role of the "CP" copy vertex, DryadVertex/VertexHost/vertex/vertexHost/vertexHost.cpp:331-571). */
+int dryad_replicate_slice(int world, int ncols, const int64_t* const* src, int64_t* const* peer_dst,
+                          int64_t n_local, int64_t row_base, void* stream);
 int dryad_join_table_init(uint64_t* tbl_keys, int32_t* head, uint64_t cap, void* stream);
 /* Probe against a build side whose keys are unique: out_row[i] = build row (0 if none), matched[i]. */
 int dryad_join_probe_unique(const uint64_t* tbl_keys, const int32_t* head, uint64_t cap,
