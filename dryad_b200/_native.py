@@ -115,6 +115,9 @@ def _declare_kernels(lib):
     _sig(lib, "dryad_join_table_init", c_int, [P, P, c_uint64, P])
     _sig(lib, "dryad_join_probe_unique", c_int, [P, P, c_uint64, P, c_int64, P, P, P])
     _sig(lib, "dryad_join_build_bcast", c_int, [P, c_int64, c_int64, c_int, P, P, P, c_uint64, c_int, P, P, P, P])
+    _sig(lib, "dryad_merge_pairs_u64", c_int, [P, P, c_int64, P, P, c_int64, P, P, P])
+    _sig(lib, "dryad_sorted_bounds", c_int, [P, c_int64, P, c_int64, P, P, P])
+    _sig(lib, "dryad_emit_ranges", c_int, [P, P, P, c_int64, P, P, P])
     _sig(lib, "dryad_kmeans_norms", c_int, [P, c_int, P, P])
     _sig(lib, "dryad_kmeans_assign", c_int, [P, c_int64, P, P, c_int, P, P, P, P, c_int, P])
     _sig(lib, "dryad_kmeans_update", c_int, [P, P, c_int, c_int, P, P, P, P])

@@ -400,3 +400,55 @@ def tokenize_verify(text, starts, lens, rep_start, rep_len) -> int:
             "tokenize_verify")
     _count()
     return int(mism.item())
+
+
+# ---- K5 / K9 ---------------------------------------------------------------------------------
+def merge_pairs(ka: torch.Tensor, va: Optional[torch.Tensor], kb: torch.Tensor, vb: Optional[torch.Tensor]):
+    """Stable merge of two ascending (key bits, int32 value) runs (ties: run A first)."""
+    require_cuda(ka, kb, va, vb)
+    n = ka.numel() + kb.numel()
+    ko = torch.empty(n, dtype=torch.int64, device=ka.device)
+    vo = torch.empty(n, dtype=torch.int32, device=ka.device) if va is not None else None
+    N.check(N.kernels().dryad_merge_pairs_u64(ptr(ka), ptr(va), ka.numel(), ptr(kb), ptr(vb), kb.numel(), ptr(ko), ptr(vo),
+                                              stream()), "merge_pairs")
+    _count()
+    return ko, vo
+
+
+def kway_merge(runs):
+    """Merge k ascending (keys, values) runs by a tree of merge-path 2-way merges; port order
+    breaks ties (the reference's MergeSort keeps port order, DryadLinqVertex.cs:319-423)."""
+    runs = [r for r in runs]
+    if not runs:
+        raise ValueError("no runs")
+    while len(runs) > 1:
+        nxt = []
+        for i in range(0, len(runs), 2):
+            if i + 1 < len(runs):
+                nxt.append(merge_pairs(runs[i][0], runs[i][1], runs[i + 1][0], runs[i + 1][1]))
+            else:
+                nxt.append(runs[i])
+        runs = nxt
+    return runs[0]
+
+
+def merge_join(outer_sorted: torch.Tensor, inner_sorted: torch.Tensor):
+    """Join two ASCENDING key columns (unsigned bit order): returns (outer_idx, inner_idx) int32
+    pairs in outer order — the MergeJoin of key-sorted inputs."""
+    require_cuda(outer_sorted, inner_sorted)
+    n, m = outer_sorted.numel(), inner_sorted.numel()
+    dev = outer_sorted.device
+    lo = torch.empty(n, dtype=torch.int64, device=dev)
+    hi = torch.empty(n, dtype=torch.int64, device=dev)
+    lib = N.kernels()
+    N.check(lib.dryad_sorted_bounds(ptr(inner_sorted), m, ptr(outer_sorted), n, ptr(lo), ptr(hi), stream()), "sorted_bounds")
+    _count()
+    cnt = hi - lo
+    offs = torch.cumsum(cnt, 0) - cnt
+    total = int((offs[-1] + cnt[-1]).item()) if n else 0
+    oo = torch.empty(total, dtype=torch.int32, device=dev)
+    oi = torch.empty(total, dtype=torch.int32, device=dev)
+    if total:
+        N.check(lib.dryad_emit_ranges(ptr(lo), ptr(hi), ptr(offs), n, ptr(oo), ptr(oi), stream()), "emit_ranges")
+        _count()
+    return oo, oi

@@ -109,8 +109,22 @@ def _input(be: GpuBackend, node, part, inputs, env):
 
 
 def _passthrough(be, node, part, inputs, env):
-    if node.params.get("sort_key") is not None:
-        return NotImplemented
+    sk = node.params.get("sort_key")
+    if sk is not None:
+        # ordered merge of key-sorted runs (MergeSort over the producer ports): merge-path k-way merge
+        if node.params.get("comparer") is not None or not isinstance(sk.ir, X.Expr):
+            return NotImplemented
+        runs, base, batches = [], 0, [b for b in inputs[0] if b.n]
+        if len(batches) <= 1:
+            return [be._cat(inputs[0])]
+        for b in batches:
+            out, _ = run_on_gpu({"k": sk.ir}, b.cols, b.n)
+            bits = K.sort_key_bits(out["k"], descending=bool(node.params.get("descending"))).contiguous()
+            idx = (torch.arange(b.n, device=be.device) + base).to(torch.int32)
+            runs.append((bits, idx))
+            base += b.n
+        _, order = K.kway_merge(runs)
+        return [ColumnBatch.concat(batches).take(order)]
     return [be._cat(inputs[0])]
 
 
@@ -173,6 +187,11 @@ def _key_column(src: ColumnBatch, lam) -> Optional[torch.Tensor]:
     if t.dtype == torch.float64:
         return t.view(torch.int64)
     return t.to(torch.int64) if t.dtype != torch.int64 else t
+
+
+def _typed_key(src: ColumnBatch, lam, bits: torch.Tensor) -> torch.Tensor:
+    """Key column in its numeric dtype (float keys travel as bit patterns in _key_column)."""
+    return bits.view(torch.float64) if lam.ir.kind == "f" else bits
 
 
 def _group_by(be, node, part, inputs, env):
@@ -439,8 +458,9 @@ def _basic_aggregate(be, node, part, inputs, env):
 
 def _join(be, node, part, inputs, env):
     p = node.params
-    if node.type != NodeType.Join or p.get("algorithm") != "hash" or p.get("comparer") is not None:
+    if node.type != NodeType.Join or p.get("comparer") is not None:
         return NotImplemented
+    use_merge = p.get("algorithm") == "merge"
     res = p["result"].ir
     if not isinstance(res, (dict, X.Expr)):
         return NotImplemented
@@ -455,8 +475,14 @@ def _join(be, node, part, inputs, env):
         dt = {"i": torch.int64, "f": torch.float64, "b": torch.bool}
         return [ColumnBatch({k: torch.empty(0, dtype=dt[e.kind], device=be.device) for k, e in proj.items()}, 0,
                             tuple_like=isinstance(res, X.TupleFields))]
-    jt = K.JoinTable(ik.contiguous())                    # build on the inner (usually smaller) side
-    op, ib = jt.probe(ok.contiguous())
+    if use_merge:                                        # both inputs are key-sorted: merge join (K9)
+        desc = bool(p.get("descending"))
+        okb = K.sort_key_bits(_typed_key(outer, p["outer_key"], ok), descending=desc).contiguous()
+        ikb = K.sort_key_bits(_typed_key(inner, p["inner_key"], ik), descending=desc).contiguous()
+        op, ib = K.merge_join(okb, ikb)
+    else:
+        jt = K.JoinTable(ik.contiguous())                # build on the inner (usually smaller) side
+        op, ib = jt.probe(ok.contiguous())
     o_sel, i_sel = outer.take(op), inner.take(ib)
     cols = {("o." + k): v for k, v in o_sel.cols.items()}
     cols.update({("i." + k): v for k, v in i_sel.cols.items()})

@@ -245,6 +245,14 @@ int dryad_tokenize_verify(const uint8_t* text, const int64_t* starts, const int3
                           const int64_t* rep_start, const int32_t* rep_len, int64_t ntok,
                           unsigned long long* mismatches, void* stream);
 
+/* ---- K5 k-way merge / K9 merge join: LinqToDryad/DryadLinqVertex.cs:319-423, 898-1230, 9819-10140 */
+int dryad_merge_pairs_u64(const uint64_t* ka, const uint32_t* va, int64_t na, const uint64_t* kb,
+                          const uint32_t* vb, int64_t nb, uint64_t* ko, uint32_t* vo, void* stream);
+int dryad_sorted_bounds(const uint64_t* sorted, int64_t m, const uint64_t* probe, int64_t n,
+                        int64_t* lower, int64_t* upper, void* stream);
+int dryad_emit_ranges(const int64_t* lower, const int64_t* upper, const int64_t* offsets, int64_t n,
+                      int32_t* out_outer, int32_t* out_inner, void* stream);
+
 /* ---- K19 + C3 k-means on tcgen05/TMEM/TMA (BASELINE config 5; the client loop is
  *      LinqToDryad/DryadLinqQueryable.cs:1280-1306 DoWhile) ------------------------------------
  * points [n,128] fp32 and centroids [k,128] fp32 (k multiple of 128, k <= 2048), 16-byte aligned.

@@ -105,6 +105,11 @@ int64_t cache_get(void* h, const char* key, void* out, int64_t cap);
 int cache_stats(void* h, int64_t* resident, int64_t* spills, int64_t* loads, int64_t* blocks);
 uint64_t fprint64(uint64_t seed, const void* data, int64_t n);
 
+/* ---- timed CPU baselines (multi-threaded restatements of the benchmark queries) ------------------ */
+int64_t cpu_wordcount(const char* text, int64_t n, int threads, int keep_empty, int64_t* total_tokens);
+int cpu_sort_rows(const uint8_t* rows, int64_t n, int width, int key_len, int threads, uint8_t* out);
+int64_t cpu_groupby_sum_count(const int64_t* keys, const int64_t* vals, int64_t n, int threads, int64_t* checksum);
+
 #ifdef __cplusplus
 }
 #endif

@@ -78,3 +78,22 @@ def test_rows_order_by_through_api():
     assert viol == 0 and n == 100_000 and checksum == terasort.key_checksum(rows)
     out = res.expr.params["table"].partitions[0].cols["row"].cpu()
     assert terasort.validate_sorted(out)
+
+
+def test_merge_join_and_take_after_order_on_gpu():
+    ld = D.DryadLinqContext(1, local_debug=True)
+    left = [{"k": (i * 37) % 50, "a": i} for i in range(400)]
+    right = [{"k": i % 60, "b": -i} for i in range(300)]
+
+    def build(c, n):
+        l = c.from_enumerable(left, n).order_by(lambda r: r.k)
+        return l.join(c.from_enumerable(right, n), lambda r: r.k, lambda r: r.k, lambda x, y: {"k": x.k, "s": x.a + y.b})
+    canon = lambda rows: sorted(tuple(sorted(dict(r).items())) for r in rows)
+    want = canon(build(ld, 1).to_list())
+    ctx = D.DryadLinqContext(1, device="cuda")
+    q = build(ctx, 1)
+    assert "algorithm=merge" in q.explain()
+    assert canon(q.to_list()) == want
+    vals = [(i * 7919) % 1000 for i in range(2000)]
+    c4 = D.DryadLinqContext(4, device="cuda")
+    assert c4.from_enumerable(vals, 4).order_by(lambda x: x).take(10).to_list() == sorted(vals)[:10]

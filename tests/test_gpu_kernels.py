@@ -275,3 +275,26 @@ def test_expr_interpreter_fallback_matches_codegen(K, monkeypatch):
     assert torch.equal(f1, f2)
     ref_x = torch.where(torch.fmod(a, 3) == 0, torch.div(a, 2, rounding_mode="trunc"), -a)
     assert torch.equal(o1["x"], ref_x)
+
+
+def test_kway_merge_and_merge_join(K):
+    g = torch.Generator(device="cuda").manual_seed(77)
+    runs, allk = [], []
+    for r, n in enumerate((5000, 1, 12345, 0, 2048, 7)):
+        k = torch.sort(torch.randint(0, 5000, (n,), dtype=torch.int64, device="cuda", generator=g)).values
+        v = (torch.arange(n, device="cuda") + r * 100000).to(torch.int32)
+        runs.append((k, v))
+        allk.append((k, v))
+    mk, mv = K.kway_merge(runs)
+    cat_k = torch.cat([k for k, _ in allk]); cat_v = torch.cat([v for _, v in allk])
+    order = torch.sort(cat_k, stable=True).indices          # stable: earlier run first on ties
+    assert torch.equal(mk, cat_k[order]) and torch.equal(mv, cat_v[order])
+    outer = torch.sort(torch.randint(0, 300, (4000,), dtype=torch.int64, device="cuda", generator=g)).values
+    inner = torch.sort(torch.randint(0, 400, (3000,), dtype=torch.int64, device="cuda", generator=g)).values
+    oo, oi = K.merge_join(outer, inner)
+    ic = inner.cpu().tolist()
+    by = {}
+    for j, kk in enumerate(ic):
+        by.setdefault(kk, []).append(j)
+    want = [(i, j) for i, kk in enumerate(outer.cpu().tolist()) for j in by.get(kk, [])]
+    assert list(zip(oo.cpu().tolist(), oi.cpu().tolist())) == want
