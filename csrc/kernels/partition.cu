@@ -22,6 +22,7 @@
 // (status = overflow) instead of corrupting memory.
 #include "common.cuh"
 #include "../../include/dryad_b200.h"
+#include <stdlib.h>
 
 namespace dryad { namespace sh {
 
@@ -351,6 +352,202 @@ __global__ void __launch_bounds__(THREADS) sh_scatter(Params P) {
   __threadfence_system();
 }
 
+// ---- TMA-pipelined scatter (single payload column, the wide-record path) ----------------------
+// Same semantics as sh_scatter, restructured so neither the HBM reads nor the NVLink writes stall
+// the SM: tile t+1 is fetched by a bulk async copy (cp.async.bulk global->shared, mbarrier
+// complete_tx) while tile t is ranked and permuted, and the destination runs of tile t leave
+// through bulk async stores (cp.async.bulk shared->global, to local or PEER HBM) that drain in the
+// background while the CTA already works on the next tile (double-buffered in/out tiles).
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count));
+}
+__device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
+  const uint32_t addr = smem_u32(bar);
+  uint32_t done;
+  do {
+    asm volatile("{\n\t.reg .pred p;\n\tmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\tselp.u32 %0, 1, 0, p;\n\t}"
+                 : "=r"(done) : "r"(addr), "r"(parity) : "memory");
+  } while (!done);
+}
+__device__ __forceinline__ void bulk_load(void* smem_dst, const void* gsrc, uint32_t bytes, uint64_t* bar) {
+  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+               ::"r"(smem_u32(smem_dst)), "l"(gsrc), "r"(bytes), "r"(smem_u32(bar)) : "memory");
+}
+__device__ __forceinline__ void bulk_store(void* gdst, const void* smem_src, uint32_t bytes) {
+  asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;"
+               ::"l"(gdst), "r"(smem_u32(smem_src)), "r"(bytes) : "memory");
+}
+
+__global__ void __launch_bounds__(THREADS) sh_scatter_tma(Params P) {
+  extern __shared__ __align__(128) unsigned char smem[];
+  const int np = P.nparts;
+  const int npa = (np + 3) & ~3;
+  const uint32_t w = P.width[0];
+  const size_t in_bytes = ((size_t)TILE * w + 127) & ~(size_t)127;
+  const size_t out_bytes = ((size_t)TILE * w + 32 * (size_t)np + 16 + 127) & ~(size_t)127;
+  const size_t kout_bytes = P.emit_key ? (((size_t)TILE * 8 + 32 * (size_t)np + 16 + 127) & ~(size_t)127) : 0;
+  unsigned char* s_in = smem;                                   // [2][in_bytes]
+  unsigned char* s_out = s_in + 2 * in_bytes;                   // [2][out_bytes]
+  unsigned char* s_kout = s_out + 2 * out_bytes;                // [2][kout_bytes]
+  uint64_t* s_seps = reinterpret_cast<uint64_t*>(s_kout + 2 * kout_bytes);
+  int64_t* s_gbase = reinterpret_cast<int64_t*>(s_seps + npa);
+  uint32_t* s_wcnt = reinterpret_cast<uint32_t*>(s_gbase + npa);
+  uint32_t* s_tcnt = s_wcnt + WARPS * npa;
+  uint32_t* s_tstart = s_tcnt + npa;
+  uint32_t* s_uoff = s_tstart + npa + 4;                         // payload run offsets in s_out
+  uint32_t* s_koff = s_uoff + npa;                               // key run offsets in s_kout
+  __shared__ uint64_t s_full[2];
+  __shared__ int s_abort;
+
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  if (tid == 0) { s_abort = 0; mbar_init(&s_full[0], 1); mbar_init(&s_full[1], 1);
+                  asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory"); }
+  __syncthreads();
+
+  // prefetch the first tile while waiting for the peers' counts
+  const int64_t tile0 = (int64_t)blockIdx.x * P.tiles_per_block;
+  const int64_t ntiles_total = (P.n + TILE - 1) / TILE;
+  int my_tiles = (int)min((int64_t)P.tiles_per_block, ntiles_total - tile0);
+  if (my_tiles < 0) my_tiles = 0;
+  auto issue_load = [&](int t) {
+    const int64_t row0 = (tile0 + t) * TILE;
+    const int valid = (int)min((int64_t)TILE, P.n - row0);
+    const uint32_t bytes = ((uint32_t)valid * w) & ~15u;
+    uint64_t* bar = &s_full[t & 1];
+    mbar_expect_tx(bar, bytes);
+    if (bytes) bulk_load(s_in + (t & 1) * in_bytes, P.src[0] + (size_t)row0 * w, bytes, bar);
+  };
+  if (tid == 0 && my_tiles > 0) issue_load(0);
+
+  if (tid < P.world) {
+    if (!spin_until_ge(&P.flags_local[tid], P.epoch, SPIN_CYCLES)) { s_abort = 2; }
+  }
+  __syncthreads();
+  if (s_abort) { if (tid == 0) atomicMax(P.status, 2); if (tid == 0 && my_tiles > 0) mbar_wait(&s_full[0], 0); return; }
+  for (int p = tid; p < np; p += THREADS) {
+    int64_t before = 0, total = 0;
+    for (int r = 0; r < P.world; ++r) {
+      int64_t c = reinterpret_cast<const volatile int64_t*>(P.counts_local)[(size_t)r * np + p];
+      if (r < P.rank) before += c;
+      total += c;
+    }
+    if (total > P.capacity[p]) s_abort = 1;
+    s_gbase[p] = before + (int64_t)P.block_counts[(size_t)p * P.nblocks + blockIdx.x];
+  }
+  if (P.mode == DRYAD_PART_RANGE_ASC || P.mode == DRYAD_PART_RANGE_DESC)
+    for (int i = tid; i < np - 1; i += THREADS) s_seps[i] = P.separators[i];
+  __syncthreads();
+  if (s_abort) { if (tid == 0) atomicMax(P.status, 1); if (tid == 0 && my_tiles > 0) mbar_wait(&s_full[0], 0); return; }
+
+  for (int t = 0; t < my_tiles; ++t) {
+    const int buf = t & 1;
+    const int64_t row0 = (tile0 + t) * TILE;
+    const int valid = (int)min((int64_t)TILE, P.n - row0);
+    unsigned char* in = s_in + buf * in_bytes;
+    unsigned char* out = s_out + buf * out_bytes;
+    unsigned char* kout = s_kout + buf * kout_bytes;
+    if (tid == 0 && t + 1 < my_tiles) issue_load(t + 1);       // in[buf^1] was released at the end of t-1
+    mbar_wait(&s_full[buf], (t >> 1) & 1);
+    {   // tail bytes that are not a multiple of 16 (last partial tile only)
+      const uint32_t total_b = (uint32_t)valid * w, bulk_b = total_b & ~15u;
+      for (uint32_t b = bulk_b + 4 * tid; b < total_b; b += 4 * THREADS)
+        *reinterpret_cast<uint32_t*>(in + b) = *reinterpret_cast<const uint32_t*>(P.src[0] + (size_t)row0 * w + b);
+    }
+    for (int i = tid; i < WARPS * np; i += THREADS) s_wcnt[i] = 0;
+    __syncthreads();
+
+    uint64_t key = 0; uint32_t part = 0, rank = 0;
+    const bool active = tid < valid;
+    if (active) { key = key_from_smem(P, in + (size_t)tid * w); part = part_of(key, P.mode, np, s_seps); }
+    {
+      uint32_t amask = __ballot_sync(0xffffffffu, active);
+      if (active) {
+        uint32_t peers = __match_any_sync(amask, part);
+        rank = __popc(peers & lanemask_lt());
+        if ((peers >> lane) <= 1u) s_wcnt[warp * np + part] = __popc(peers);
+      }
+    }
+    __syncthreads();
+    for (int p = tid; p < np; p += THREADS) {
+      uint32_t sum = 0;
+#pragma unroll
+      for (int wp = 0; wp < WARPS; ++wp) { uint32_t c = s_wcnt[wp * np + p]; s_wcnt[wp * np + p] = sum; sum += c; }
+      s_tcnt[p] = sum;
+    }
+    __syncthreads();
+    if (tid == 0) {
+      // the bulk stores that read out[buf] two tiles ago must have finished reading shared memory
+      asm volatile("cp.async.bulk.wait_group.read 1;" ::: "memory");
+      uint32_t acc = 0, off = 0, koff = 0;
+      for (int p = 0; p < np; ++p) {
+        s_tstart[p] = acc; const uint32_t cnt = s_tcnt[p]; acc += cnt;
+        unsigned char* dbase = reinterpret_cast<unsigned char*>(P.dst_table[p]);
+        uint32_t mis = (uint32_t)((reinterpret_cast<uintptr_t>(dbase) + (uintptr_t)s_gbase[p] * w) & 15);
+        s_uoff[p] = off + mis;
+        off += cnt ? ((mis + cnt * w + 15) & ~15u) : 0;
+        if (P.emit_key) {
+          uint32_t kmis = (uint32_t)((reinterpret_cast<uintptr_t>(P.dst_key_table[p]) + (uintptr_t)s_gbase[p] * 8) & 15);
+          s_koff[p] = koff + kmis;
+          koff += cnt ? ((kmis + cnt * 8 + 15) & ~15u) : 0;
+        }
+      }
+      s_tstart[np] = acc;
+    }
+    __syncthreads();
+    if (active) {
+      const uint32_t rip = rank + s_wcnt[warp * np + part];        // rank inside the destination run
+      uint32_t* d = reinterpret_cast<uint32_t*>(out + s_uoff[part] + (size_t)rip * w);
+      const uint32_t* sp = reinterpret_cast<const uint32_t*>(in + (size_t)tid * w);
+      const int ww = (int)(w / 4);
+      for (int k = 0; k < ww; ++k) d[k] = sp[k];
+      if (P.emit_key) {
+        uint32_t* kd = reinterpret_cast<uint32_t*>(kout + s_koff[part] + (size_t)rip * 8);
+        kd[0] = (uint32_t)key; kd[1] = (uint32_t)(key >> 32);
+      }
+    }
+    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");   // generic smem writes -> async proxy
+    __syncthreads();
+    // stores: heads/tails by lanes, 16-byte aligned bodies by bulk async copies (one issuing thread)
+    for (int p = warp; p < np; p += WARPS) {
+      const uint32_t cnt = s_tcnt[p];
+      if (cnt == 0) continue;
+      for (int col = 0; col < (P.emit_key ? 2 : 1); ++col) {
+        const uint32_t cw = col ? 8u : w;
+        unsigned char* sbase = col ? kout : out;
+        const uint32_t run_s = col ? s_koff[p] : s_uoff[p], run_e = run_s + cnt * cw;
+        unsigned char* dbase = col ? reinterpret_cast<unsigned char*>(P.dst_key_table[p]) : reinterpret_cast<unsigned char*>(P.dst_table[p]);
+        const uintptr_t ga = reinterpret_cast<uintptr_t>(dbase) + (uintptr_t)s_gbase[p] * cw;
+        const uint32_t body_s = (run_s + 15) & ~15u, body_e = run_e & ~15u;
+        // head words [run_s, body_s) and tail words [body_e, run_e): at most 3 + 3 words
+        const uint32_t b = (lane < 4) ? run_s + 4 * lane : body_e + 4 * (lane - 4);
+        const bool in_head = lane < 4 && b < body_s && b < run_e;
+        const bool in_tail = lane >= 4 && lane < 8 && b < run_e && b >= body_s;
+        if (body_e <= body_s) {                                   // run shorter than one aligned unit
+          for (uint32_t bb = run_s + 4 * lane; bb < run_e; bb += 128)
+            *reinterpret_cast<uint32_t*>(ga + (bb - run_s)) = *reinterpret_cast<const uint32_t*>(sbase + bb);
+        } else {
+          if (in_head || in_tail) *reinterpret_cast<uint32_t*>(ga + (b - run_s)) = *reinterpret_cast<const uint32_t*>(sbase + b);
+          if (lane == 0) bulk_store(reinterpret_cast<void*>(ga + (body_s - run_s)), sbase + body_s, body_e - body_s);
+        }
+      }
+    }
+    __syncwarp();
+    if (lane == 0) asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+    __syncthreads();
+    for (int p = tid; p < np; p += THREADS) s_gbase[p] += s_tcnt[p];
+    // every warp leader owns its own bulk groups: before ITS out[buf] slot is rewritten (tile t+2)
+    // it must have drained the reads of tile t; warp leaders wait here, one tile late
+    if (lane == 0) asm volatile("cp.async.bulk.wait_group.read 1;" ::: "memory");
+    __syncthreads();
+  }
+  if (lane == 0) asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");   // writes performed
+  __threadfence_system();
+}
+
 // Epoch barrier across ranks: every rank's prior stream work is complete and visible.
 __global__ void sh_barrier(uint64_t* const* flags_peers, uint64_t* flags_local, int rank,
                            int world, int slot, uint64_t epoch, int32_t* status) {
@@ -371,6 +568,17 @@ static size_t scatter_smem(int maxw, int nparts) {
   b += 8 * npa + 8 * npa;                               // seps, gbase
   b += 4 * (WARPS * npa + npa + (npa + 4) * 2 + npa);
   return (b + 15) & ~(size_t)15;
+}
+
+static size_t scatter_tma_smem(int w, int nparts, int emit_key) {
+  size_t in_b = ((size_t)TILE * w + 127) & ~(size_t)127;
+  size_t out_b = ((size_t)TILE * w + 32 * (size_t)nparts + 16 + 127) & ~(size_t)127;
+  size_t k_b = emit_key ? (((size_t)TILE * 8 + 32 * (size_t)nparts + 16 + 127) & ~(size_t)127) : 0;
+  size_t npa = ((size_t)nparts + 3) & ~(size_t)3;
+  size_t b = 2 * in_b + 2 * out_b + 2 * k_b;
+  b += 8 * npa + 8 * npa;
+  b += 4 * (WARPS * npa + npa + (npa + 4) + npa + npa);
+  return (b + 127) & ~(size_t)127;
 }
 
 static int pick_blocks(int64_t n, int* tiles_per_block) {
@@ -431,9 +639,18 @@ int dryad_shuffle_run(const DryadShuffleDesc* d, void* stream) {
   DRYAD_LAUNCH_CHECK();
   sh_publish<<<P.nparts, 256, 0, st>>>(P, done_counter);
   DRYAD_LAUNCH_CHECK();
-  size_t smem = scatter_smem(maxw, P.nparts);
-  DRYAD_CUDA_TRY(cudaFuncSetAttribute(sh_scatter, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-  sh_scatter<<<P.nblocks, THREADS, smem, st>>>(P);
+  const char* no_tma = getenv("DRYAD_SHUFFLE_NO_TMA");
+  const bool tma_ok = d->ncols == 1 && d->width[0] >= 16 && (((uintptr_t)d->src[0]) & 15) == 0 &&
+                      scatter_tma_smem((int)d->width[0], P.nparts, d->emit_key) <= 200 * 1024 && !(no_tma && no_tma[0] == '1');
+  if (tma_ok) {
+    size_t smem = scatter_tma_smem((int)d->width[0], P.nparts, d->emit_key);
+    DRYAD_CUDA_TRY(cudaFuncSetAttribute(sh_scatter_tma, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    sh_scatter_tma<<<P.nblocks, THREADS, smem, st>>>(P);
+  } else {
+    size_t smem = scatter_smem(maxw, P.nparts);
+    DRYAD_CUDA_TRY(cudaFuncSetAttribute(sh_scatter, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    sh_scatter<<<P.nblocks, THREADS, smem, st>>>(P);
+  }
   DRYAD_LAUNCH_CHECK();
   sh_barrier<<<1, 32, 0, st>>>(d->flags_peers, d->flags_local, d->rank, d->world, 1, d->epoch,
                                d->status);
