@@ -187,6 +187,84 @@ __global__ void __launch_bounds__(256) gather_rows_kernel(const uint32_t* __rest
   }
 }
 
+// Compile-time row width: all WORDS loads of a 32-row group are issued before the first store, so
+// each warp keeps WORDS independent 128-byte requests in flight (memory-level parallelism).
+template <int WORDS>
+__global__ void __launch_bounds__(256) gather_rows_fixed_kernel(const uint32_t* __restrict__ in,
+                                                                const uint32_t* __restrict__ idx,
+                                                                uint32_t* __restrict__ out, int64_t n) {
+  const int lane = threadIdx.x & 31;
+  int64_t warp = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  int64_t nwarps = ((int64_t)gridDim.x * blockDim.x) >> 5;
+  int64_t groups = n / 32;                      // full groups only; the tail uses the generic kernel
+  for (int64_t g = warp; g < groups; g += nwarps) {
+    const uint32_t my = idx[g * 32 + lane];
+    uint32_t v[WORDS];
+#pragma unroll
+    for (int it = 0; it < WORDS; ++it) {
+      const int j = it * 32 + lane;
+      const int row = j / WORDS, w = j - row * WORDS;
+      const uint32_t src = __shfl_sync(0xffffffffu, my, row);
+      v[it] = __ldg(in + (size_t)src * WORDS + w);
+    }
+    uint32_t* o = out + (size_t)g * 32 * WORDS;
+#pragma unroll
+    for (int it = 0; it < WORDS; ++it) o[it * 32 + lane] = v[it];
+  }
+}
+
+// Window of the big-endian key: out32[i] = (be64(row key) >> shift) as uint32.
+__global__ void extract_be_window_kernel(const unsigned char* __restrict__ rowsp, int64_t n, int width, int key_off,
+                                         int shift, uint32_t* __restrict__ out) {
+  int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  int64_t stride = (int64_t)gridDim.x * blockDim.x;
+  for (; i < n; i += stride) {
+    const unsigned char* k = rowsp + (size_t)i * width + key_off;
+    uint64_t v = 0;
+#pragma unroll
+    for (int b = 0; b < 8; ++b) v = (v << 8) | (uint64_t)k[b];
+    out[i] = (uint32_t)(v >> shift);
+  }
+}
+__global__ void shift_u64_to_u32_kernel(const uint64_t* __restrict__ in, int64_t n, int shift, uint32_t* __restrict__ out) {
+  int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  int64_t stride = (int64_t)gridDim.x * blockDim.x;
+  for (; i < n; i += stride) out[i] = (uint32_t)(in[i] >> shift);
+}
+
+// Tie repair over 32-bit sorted window keys (see fix_ties_kernel).
+__global__ void fix_ties32_kernel(const uint32_t* __restrict__ keys, uint32_t* __restrict__ idx, int64_t n,
+                                  const unsigned char* __restrict__ rowsp, int width, int extra_off, int extra,
+                                  int max_run, int descending, int32_t* __restrict__ long_runs) {
+  int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  int64_t stride = (int64_t)gridDim.x * blockDim.x;
+  for (; i < n; i += stride) {
+    const uint32_t k = keys[i];
+    if (i + 1 >= n || keys[i + 1] != k) continue;
+    if (i > 0 && keys[i - 1] == k) continue;
+    int64_t e = i + 1;
+    while (e < n && keys[e] == k) ++e;
+    if (e - i > max_run) { atomicAdd(long_runs, 1); continue; }
+    for (int64_t a = i + 1; a < e; ++a) {
+      uint32_t ia = idx[a];
+      const unsigned char* ra = rowsp + (size_t)ia * width + extra_off;
+      int64_t b = a - 1;
+      while (b >= i) {
+        uint32_t ib = idx[b];
+        const unsigned char* rb = rowsp + (size_t)ib * width + extra_off;
+        int cmp = 0;
+        for (int t = 0; t < extra && cmp == 0; ++t) cmp = (int)rb[t] - (int)ra[t];
+        if (descending) cmp = -cmp;
+        if (cmp == 0) cmp = (ib > ia) ? 1 : -1;
+        if (cmp <= 0) break;
+        idx[b + 1] = ib;
+        --b;
+      }
+      idx[b + 1] = ia;
+    }
+  }
+}
+
 // Element gather for 4- and 8-byte columns.
 template <typename T>
 __global__ void gather_elems_kernel(const T* __restrict__ in, const uint32_t* __restrict__ idx,
@@ -309,8 +387,42 @@ int dryad_gather_rows(const void* in, const uint32_t* idx, void* out, int64_t n,
     int64_t groups = (n + 31) / 32;
     int64_t blocks = (groups + 7) / 8;
     if (blocks > 148 * 32) blocks = 148 * 32;
-    gather_rows_kernel<<<(int)blocks, 256, 0, st>>>((const uint32_t*)in, idx, (uint32_t*)out, n, width / 4);
+    const int words = width / 4;
+    int64_t full = (n / 32) * 32;
+    if (words == 25 && full > 0) {                 // 100-byte records: unrolled fast path + generic tail
+      gather_rows_fixed_kernel<25><<<(int)blocks, 256, 0, st>>>((const uint32_t*)in, idx, (uint32_t*)out, n);
+      DRYAD_LAUNCH_CHECK();
+      if (n > full)
+        gather_rows_kernel<<<1, 256, 0, st>>>((const uint32_t*)in, idx + full, (uint32_t*)out + (size_t)full * words, n - full, words);
+    } else {
+      gather_rows_kernel<<<(int)blocks, 256, 0, st>>>((const uint32_t*)in, idx, (uint32_t*)out, n, words);
+    }
   }
+  DRYAD_LAUNCH_CHECK();
+  return DRYAD_OK;
+}
+
+int dryad_extract_be_window(const uint8_t* rowsp, int64_t n, int width, int key_off, int shift, uint32_t* out, void* stream) {
+  if (n <= 0) return DRYAD_OK;
+  if (width <= 0 || key_off < 0 || key_off + 8 > width || shift < 0 || shift > 32) return DRYAD_ERR_BAD_ARG;
+  extract_be_window_kernel<<<grid_for(n, 256), 256, 0, (cudaStream_t)stream>>>(rowsp, n, width, key_off, shift, out);
+  DRYAD_LAUNCH_CHECK();
+  return DRYAD_OK;
+}
+
+int dryad_shift_u64_to_u32(const uint64_t* in, int64_t n, int shift, uint32_t* out, void* stream) {
+  if (n <= 0) return DRYAD_OK;
+  if (shift < 0 || shift > 32) return DRYAD_ERR_BAD_ARG;
+  shift_u64_to_u32_kernel<<<grid_for(n, 256), 256, 0, (cudaStream_t)stream>>>(in, n, shift, out);
+  DRYAD_LAUNCH_CHECK();
+  return DRYAD_OK;
+}
+
+int dryad_fix_ties32(const uint32_t* keys, uint32_t* idx, int64_t n, const uint8_t* rowsp, int width, int extra_off,
+                     int extra, int max_run, int descending, int32_t* long_runs, void* stream) {
+  if (n <= 1 || extra <= 0) return DRYAD_OK;
+  if (extra_off < 0 || extra_off + extra > width) return DRYAD_ERR_BAD_ARG;
+  fix_ties32_kernel<<<grid_for(n, 256), 256, 0, (cudaStream_t)stream>>>(keys, idx, n, rowsp, width, extra_off, extra, max_run, descending, long_runs);
   DRYAD_LAUNCH_CHECK();
   return DRYAD_OK;
 }

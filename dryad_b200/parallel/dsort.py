@@ -106,29 +106,37 @@ class RowSorter:
         top = max((lo ^ hi).bit_length(), RowSorter.WINDOW_BITS)
         return top - RowSorter.WINDOW_BITS, top
 
-    def _local_sort(self, keys: torch.Tensor, m: int, src_rows: torch.Tensor, lo: int, hi: int):
-        """(64-bit prefix, row) -> sort permutation.  Fast path: 4 radix passes over a 32-bit window
-        + tie repair on the remaining key bytes; a partition with long runs of equal windows (not
-        TeraSort-like) falls back to all 8 passes."""
-        M64 = (1 << 64) - 1
+    def _local_sort(self, keys, m: int, src_rows: torch.Tensor, lo: int, hi: int):
+        """Sort permutation of the first m rows of src_rows.  `keys`: the rows' 64-bit key prefixes
+        (int64 bits) when the shuffle delivered them, else None.  Fast path: a 32-bit window of the
+        prefix (leading bits shared by the whole partition are skipped) sorted as (u32, u32) pairs in
+        4 radix passes + tie repair on the remaining key bytes; a partition with long runs of equal
+        windows (not TeraSort-like) falls back to all 8 passes over the 64-bit prefix."""
+        from .. import _native as N
+        lib = N.kernels()
         b0, b1 = self._window(lo, hi)
-        if self.descending:
-            keys = ~keys
-        if b0 > 0:
-            skeys, sidx = K.radix_sort_pairs(keys, self.idx_a[:m], iota=True, begin_bit=b0, end_bit=b1,
-                                             keys_alt=self.keys_b[:m], vals_alt=self.idx_b[:m])
-            mask = (M64 << b0) & M64
+        k32 = self.keys_a.view(torch.int32)[:m]
+        if not self.descending:
+            if keys is None:
+                N.check(lib.dryad_extract_be_window(K.ptr(src_rows), m, self.width, self.key_off, b0, K.ptr(k32), K.stream()), "extract_be_window")
+            else:
+                N.check(lib.dryad_shift_u64_to_u32(K.ptr(keys), m, b0, K.ptr(k32), K.stream()), "shift_u64_to_u32")
+            K._count()
+            skeys, sidx = K.radix_sort_pairs(k32, self.idx_a[:m], iota=True, keys_alt=self.keys_b.view(torch.int32)[:m],
+                                             vals_alt=self.idx_b[:m])
             first_byte = (64 - b0) // 8               # key bytes before this are equal inside a run
-            runs = K.fix_ties(skeys, sidx, src_rows, self.key_off + first_byte, self.key_len - first_byte,
-                              max_run=self.WINDOW_MAX_RUN, descending=self.descending, prefix_mask=mask)
+            runs = torch.zeros(1, dtype=torch.int32, device=src_rows.device)
+            N.check(lib.dryad_fix_ties32(K.ptr(skeys), K.ptr(sidx), m, K.ptr(src_rows), self.width, self.key_off + first_byte,
+                                         self.key_len - first_byte, self.WINDOW_MAX_RUN, 0, K.ptr(runs), K.stream()), "fix_ties32")
+            K._count()
             if int(runs.item()) == 0:
                 self.last_long_runs = runs
                 return sidx
-            keys = K.extract_be64(src_rows[:m], self.key_off, out=self.keys_a)[:m]   # the sort clobbered them
-            if self.descending:
-                keys = ~keys
-        skeys, sidx = K.radix_sort_pairs(keys, self.idx_a[:m], iota=True, keys_alt=self.keys_b[:m],
-                                         vals_alt=self.idx_b[:m])
+        # general path (descending order, or long runs of equal windows): full 64-bit prefix
+        k64 = K.extract_be64(src_rows[:m], self.key_off, out=self.keys_a)[:m]
+        if self.descending:
+            k64 = ~k64
+        skeys, sidx = K.radix_sort_pairs(k64, self.idx_a[:m], iota=True, keys_alt=self.keys_b[:m], vals_alt=self.idx_b[:m])
         if self.key_len > 8:
             self.last_long_runs = K.fix_ties(skeys, sidx, src_rows, self.key_off + 8, self.key_len - 8,
                                              descending=self.descending)
@@ -164,8 +172,7 @@ class RowSorter:
         else:
             m = n
             src_rows = rows
-            K.extract_be64(rows, self.key_off, out=self.keys_a)
-            keys = self.keys_a[:m]
+            keys = None
             lo, hi = 0, M64
         sidx = self._local_sort(keys, m, src_rows, lo, hi)
         self._mark("local sort + ties")

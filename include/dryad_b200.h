@@ -135,6 +135,11 @@ int dryad_extract_be64(const uint8_t* rows, int64_t n, int width, int key_off, u
 int dryad_fix_ties(const uint64_t* keys, uint32_t* idx, int64_t n, const uint8_t* rows, int width,
                    int extra_off, int extra, int max_run, int descending, uint64_t prefix_mask,
                    int32_t* long_runs, void* stream);
+/* 32-bit key window variants used by the wide-record OrderBy fast path. */
+int dryad_extract_be_window(const uint8_t* rows, int64_t n, int width, int key_off, int shift, uint32_t* out, void* stream);
+int dryad_shift_u64_to_u32(const uint64_t* in, int64_t n, int shift, uint32_t* out, void* stream);
+int dryad_fix_ties32(const uint32_t* keys, uint32_t* idx, int64_t n, const uint8_t* rows, int width, int extra_off,
+                     int extra, int max_run, int descending, int32_t* long_runs, void* stream);
 int dryad_gather_rows(const void* in, const uint32_t* idx, void* out, int64_t n, int width,
                       void* stream);
 int dryad_check_sorted_rows(const uint8_t* rows, int64_t n, int width, int key_off, int key_len,
