@@ -11,7 +11,9 @@
 //   warp 1      tcgen05.mma issuer (one elected lane): kind::tf32, M=128 N=128 K=8, accumulating
 //               x.c_j for 128 points x 128 centroids into one of two TMEM accumulator buffers;
 //               tcgen05.commit releases ring slots and publishes accumulators.
-//   warps 2-5   epilogue: tcgen05.ld the accumulator rows (one point per thread), fused
+//   warps 2-9   epilogue (two warps per TMEM lane quarter, each scanning half of the accumulator
+//               columns with two independent running minima so the argmin chain is not
+//               latency-bound): tcgen05.ld the accumulator rows (one point per thread pair), fused
 //               argmin with the fp32 centroid norms, then the point's exact fp32 coordinates are
 //               read back from the swizzled shared tile and added to the winner's sum with
 //               16-byte vector reductions (red.global.add.v4.f32) — sums stay fp32-exact, the
@@ -22,6 +24,7 @@
 #include "../../include/dryad_b200.h"
 #include <cuda.h>
 #include <cudaTypedefs.h>
+#include <stdlib.h>
 
 namespace dryad { namespace km {
 
@@ -31,14 +34,14 @@ constexpr int A_KB_BYTES = BM * KB * 4;          // 16 KiB
 constexpr int A_BYTES = A_KB_BYTES * NKB;        // 64 KiB
 constexpr int B_STAGE_BYTES = BN * KB * 4;       // 16 KiB
 constexpr int MAX_K = 2048;
-constexpr int THREADS = 192;
+constexpr int THREADS = 320;                     // warp 0 TMA, warp 1 MMA, warps 2-9 epilogue
 constexpr int TMEM_COLS = 256;                   // two accumulator buffers of 128 fp32 columns
 
 constexpr size_t OFF_A = 0;
 constexpr size_t OFF_B = OFF_A + 2 * A_BYTES;
 constexpr size_t OFF_CN = OFF_B + (size_t)B_STAGES * B_STAGE_BYTES;
 constexpr size_t OFF_BAR = OFF_CN + MAX_K * 4;
-constexpr size_t SMEM_BYTES = OFF_BAR + 256 + 1024;   // + slack for 1024-byte alignment
+constexpr size_t SMEM_BYTES = OFF_BAR + 192 + 128 * 8 + 1024;   // barriers, pair-exchange, alignment slack   // + slack for 1024-byte alignment
 
 // ---- PTX wrappers ----------------------------------------------------------------------------
 __device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
@@ -119,7 +122,7 @@ struct Bars {
 __global__ void __launch_bounds__(THREADS, 1)
 km_assign(const __grid_constant__ CUtensorMap map_x, const __grid_constant__ CUtensorMap map_c,
           const float* __restrict__ cnorm, int64_t n, int k, int32_t* __restrict__ assign,
-          float* __restrict__ sums, unsigned long long* __restrict__ counts, float* __restrict__ inertia) {
+          float* __restrict__ sums, unsigned long long* __restrict__ counts, float* __restrict__ inertia, int dbg) {
   extern __shared__ unsigned char smem_raw[];
   unsigned char* smem = reinterpret_cast<unsigned char*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
   unsigned char* sA = smem + OFF_A;
@@ -133,8 +136,8 @@ km_assign(const __grid_constant__ CUtensorMap map_x, const __grid_constant__ CUt
 
   for (int i = threadIdx.x; i < k; i += THREADS) s_cn[i] = cnorm[i];
   if (threadIdx.x == 0) {
-    for (int i = 0; i < 2; ++i) { mbar_init(&bars->a_full[i], 1); mbar_init(&bars->a_empty[i], 128);
-                                  mbar_init(&bars->t_full[i], 1); mbar_init(&bars->t_empty[i], 128); }
+    for (int i = 0; i < 2; ++i) { mbar_init(&bars->a_full[i], 1); mbar_init(&bars->a_empty[i], 256);
+                                  mbar_init(&bars->t_full[i], 1); mbar_init(&bars->t_empty[i], 256); }
     for (int i = 0; i < B_STAGES; ++i) { mbar_init(&bars->b_full[i], 1); mbar_init(&bars->b_empty[i], 1); }
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
@@ -194,51 +197,73 @@ km_assign(const __grid_constant__ CUtensorMap map_x, const __grid_constant__ CUt
       }
     }
   } else {
-    // ===== epilogue: one point per thread =====
+    // ===== epilogue: one point per thread pair (column halves) =====
+    const int ew = warp - 2;                        // 0..7
     const int q = warp & 3;                         // TMEM lane quarter this warp may read
+    const int half = ew >> 2;                       // which 64 of the 128 accumulator columns
     const int r = q * 32 + lane;                    // row inside the tile
+    float* s_best = reinterpret_cast<float*>(smem + OFF_BAR + 192);        // [128] partner exchange
+    int* s_bi = reinterpret_cast<int*>(s_best + 128);                      // [128]
     uint32_t it = 0, cc = 0;
     float local_inertia = 0.f;
     for (int64_t tile = blockIdx.x; tile < ntiles; tile += gridDim.x, ++it) {
       const uint32_t ab = it & 1;
-      float best = 3.4e38f;
-      int bi = 0;
+      float best0 = 3.4e38f, best1 = 3.4e38f;
+      int bi0 = 0, bi1 = 0;
       for (int c = 0; c < nchunks; ++c, ++cc) {
         const uint32_t tb = cc & 1;
         mbar_wait(&bars->t_full[tb], (cc >> 1) & 1);
         tc_fence_after();
 #pragma unroll 1
-        for (int sub = 0; sub < BN / 32; ++sub) {
+        for (int sub = 0; sub < 2; ++sub) {
           float v[32];
-          tc_ld_32x32(tmem_base + ((uint32_t)(q * 32) << 16) + tb * BN + sub * 32, v);
-          const int j0 = c * BN + sub * 32;
+          const int col = half * 64 + sub * 32;
+          tc_ld_32x32(tmem_base + ((uint32_t)(q * 32) << 16) + tb * BN + col, v);
+          const int j0 = c * BN + col;
 #pragma unroll
-          for (int j = 0; j < 32; ++j) {
-            float val = fmaf(-2.f, v[j], s_cn[j0 + j]);
-            if (val < best) { best = val; bi = j0 + j; }
+          for (int j = 0; j < 32; j += 2) {
+            float v0 = fmaf(-2.f, v[j], s_cn[j0 + j]);
+            float v1 = fmaf(-2.f, v[j + 1], s_cn[j0 + j + 1]);
+            if (v0 < best0) { best0 = v0; bi0 = j0 + j; }
+            if (v1 < best1) { best1 = v1; bi1 = j0 + j + 1; }
           }
         }
         tc_fence_before();
         mbar_arrive(&bars->t_empty[tb]);
       }
+      float best = best0; int bi = bi0;
+      if (best1 < best || (best1 == best && bi1 < bi)) { best = best1; bi = bi1; }
+      // merge the two column halves of each row through shared memory (named barrier: epilogue only)
+      if (half == 1) { s_best[r] = best; s_bi[r] = bi; }
+      asm volatile("bar.sync 1, 256;" ::: "memory");
+      if (half == 0) {
+        const float ob = s_best[r]; const int oi = s_bi[r];
+        if (ob < best || (ob == best && oi < bi)) { best = ob; bi = oi; }
+        s_best[r] = best; s_bi[r] = bi;
+      }
+      asm volatile("bar.sync 1, 256;" ::: "memory");
+      best = s_best[r]; bi = s_bi[r];
       mbar_wait(&bars->a_full[ab], (it >> 1) & 1);  // TMA-written tile visible to this thread
       const int64_t row = tile * BM + r;
       if (row < n) {
-        assign[row] = bi;
-        atomicAdd(&counts[bi], 1ull);
+        if (half == 0) { assign[row] = bi; atomicAdd(&counts[bi], 1ull); }
         float xn = 0.f;
         float* dst = sums + (size_t)bi * D;
         const unsigned char* base = sA + ab * A_BYTES + (r >> 3) * 1024 + (r & 7) * 128;
+        // each thread of the pair adds one half of the point's 128 coordinates
 #pragma unroll
-        for (int kb = 0; kb < NKB; ++kb)
+        for (int kk = 0; kk < NKB / 2; ++kk) {
+          const int kb = half * (NKB / 2) + kk;
 #pragma unroll
           for (int ch = 0; ch < 8; ++ch) {
             float4 x = *reinterpret_cast<const float4*>(base + kb * A_KB_BYTES + ((ch ^ (r & 7)) << 4));
             xn += x.x * x.x + x.y * x.y + x.z * x.z + x.w * x.w;
-            red_add_v4(dst + kb * KB + ch * 4, x);
+            if (!(dbg & 1)) red_add_v4(dst + kb * KB + ch * 4, x);
           }
-        local_inertia += fmaxf(best + xn, 0.f);
+        }
+        local_inertia += xn + (half == 0 ? best : 0.f);
       }
+      asm volatile("bar.sync 1, 256;" ::: "memory");   // s_best/s_bi reused by the next tile
       mbar_arrive(&bars->a_empty[ab]);
     }
     local_inertia = warp_sum(local_inertia);
@@ -343,7 +368,8 @@ int dryad_kmeans_assign(const float* points, int64_t n, const float* centroids, 
   int64_t ntiles = (n + BM - 1) / BM;
   int grid = (int)(ntiles < sms ? ntiles : sms);
   if (max_ctas > 0 && grid > max_ctas) grid = max_ctas;
-  km_assign<<<grid, THREADS, SMEM_BYTES, (cudaStream_t)stream>>>(mx, mc, cnorm, n, k, assign, sums, counts, inertia);
+  const char* dbg = getenv("DRYAD_KM_DEBUG");
+  km_assign<<<grid, THREADS, SMEM_BYTES, (cudaStream_t)stream>>>(mx, mc, cnorm, n, k, assign, sums, counts, inertia, dbg ? atoi(dbg) : 0);
   DRYAD_LAUNCH_CHECK();
   return DRYAD_OK;
 }
