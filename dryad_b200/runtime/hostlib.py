@@ -108,3 +108,16 @@ _d("fprint64", c_uint64, [c_uint64, c_char_p, c_int64])
 _d("cpu_wordcount", c_int64, [c_char_p, c_int64, c_int, c_int, C.POINTER(c_int64)])
 _d("cpu_sort_rows", c_int, [P, c_int64, c_int, c_int, c_int, P])
 _d("cpu_groupby_sum_count", c_int64, [P, P, c_int64, c_int, C.POINTER(c_int64)])
+_d("vc_create", P, [c_int, c_int, c_int])
+_d("vc_destroy", None, [P])
+_d("vc_add_arg", None, [P, c_char_p])
+_d("vc_add_input", None, [P, c_char_p, c_int64])
+_d("vc_add_output", None, [P, c_char_p, c_int64])
+_d("vc_set_status", None, [P, c_int, c_int, c_char_p])
+_d("vc_add_channel_status", None, [P, c_int64, c_int])
+_d("vc_serialize", c_int64, [P, c_char_p, c_int64])
+_d("vc_parse", P, [c_char_p, c_int64])
+_d("vc_get_header", c_int, [P] + [C.POINTER(c_int)] * 5)
+_d("vc_count", c_int, [P, c_int])
+_d("vc_get_item", c_int64, [P, c_int, c_int, c_char_p, c_int])
+_d("affinity_merge", c_int, [c_int, C.POINTER(c_int32), C.POINTER(c_int64), C.POINTER(c_int32), c_int, c_double, C.POINTER(c_int32)])

@@ -105,6 +105,24 @@ int64_t cache_get(void* h, const char* key, void* out, int64_t cap);
 int cache_stats(void* h, int64_t* resident, int64_t* spills, int64_t* loads, int64_t* blocks);
 uint64_t fprint64(uint64_t seed, const void* data, int64_t n);
 
+/* ---- vertex command / status blocks (tagged TLV) and affinity merging:
+ *      DryadVertex/VertexHost/system/common/include/dvertexcommand.h:48-243, GraphManager/vertex/DrVertexCommand.cpp,
+ *      GraphManager/gang/DrProperty.cpp, GraphManager/kernel/DrResources.cpp ------------------------------ */
+void* vc_create(int command, int vertex_id, int version);
+void vc_destroy(void* h);
+void vc_add_arg(void* h, const char* a);
+void vc_add_input(void* h, const char* uri, int64_t length);
+void vc_add_output(void* h, const char* uri, int64_t size_hint);
+void vc_set_status(void* h, int state, int exit_code, const char* message);
+void vc_add_channel_status(void* h, int64_t bytes, int error);
+int64_t vc_serialize(void* h, void* out, int64_t cap);
+void* vc_parse(const void* data, int64_t n);
+int vc_get_header(void* h, int* command, int* vertex_id, int* version, int* state, int* exit_code);
+int vc_count(void* h, int what);
+int64_t vc_get_item(void* h, int what, int i, char* buf, int cap);
+int affinity_merge(int n, const int32_t* computer, const int64_t* weight, const int32_t* rack_of, int ncomputers,
+                   double threshold, int32_t* choice);
+
 /* ---- timed CPU baselines (multi-threaded restatements of the benchmark queries) ------------------ */
 int64_t cpu_wordcount(const char* text, int64_t n, int threads, int keep_empty, int64_t* total_tokens);
 int cpu_sort_rows(const uint8_t* rows, int64_t n, int width, int key_len, int threads, uint8_t* out);

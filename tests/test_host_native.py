@@ -243,3 +243,43 @@ def test_block_stream_never_splits_records_and_gzip(tmp_path):
     raw = os.path.getsize(f"{tmp_path}/t_None.00000001")
     gz = os.path.getsize(f"{tmp_path}/t_Gzip.00000001")
     assert gz < raw / 5
+
+
+def test_vertex_command_wire_format_round_trip():
+    from dryad_b200.runtime.command import CMD_START, STATE_COMPLETED, VertexCommand, affinity_merge
+    c = VertexCommand(CMD_START, vertex_id=17, version=2, args=["--flag", "Select__3"],
+                      inputs=[("file:///tmp/3_0_1.tmp", 1234), ("fifo://32/4_1_0", -1)], outputs=[("hbm://17_0_2", 1 << 30)])
+    wire = c.serialize()
+    back = VertexCommand.parse(wire)
+    assert back == c
+    st = VertexCommand(0, 17, 2, state=STATE_COMPLETED, exit_code=0, message="ok", channel_status=[(1234, 0), (99, 5)])
+    assert VertexCommand.parse(st.serialize()) == st
+    assert VertexCommand.parse(wire[:-3]) is None and VertexCommand.parse(b"garbage") is None
+    assert affinity_merge([(0, 900), (1, 50), (2, 50)], rack_of=[0, 0, 1]) == ("computer", 0)
+    assert affinity_merge([(0, 400), (1, 350), (2, 250)], rack_of=[0, 0, 1]) == ("rack", 0)
+    assert affinity_merge([(0, 300), (2, 300), (4, 400)], rack_of=[0, 0, 1, 1, 2, 2])[0] == "cluster"
+
+
+def test_channel_factory_file_fifo_null(tmp_path):
+    from dryad_b200.channel.factory import ChannelReader, ChannelWriter, channel_name, fifo_uri
+    recs = [("k%d" % i, i, [i, i + 1]) for i in range(5000)]
+    uri = "file://" + str(tmp_path / channel_name(3, 0, 1))
+    w = ChannelWriter(uri)
+    for r in recs:
+        w.write(r)
+    w.close()
+    assert list(ChannelReader(uri)) == recs and w.records == 5000
+    fu = fifo_uri(9, 0, 0)
+    got = []
+    t = threading.Thread(target=lambda: got.extend(ChannelReader(fu)))
+    t.start()
+    fw = ChannelWriter(fu)
+    for r in recs:
+        fw.write(r)
+    fw.close()
+    t.join()
+    assert got == recs
+    nw = ChannelWriter("null://x")
+    nw.write(1)
+    nw.close()
+    assert list(ChannelReader("null://x")) == []

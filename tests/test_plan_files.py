@@ -1,0 +1,93 @@
+"""Plan file round trip, golden plan shapes, object store, small utilities."""
+import pytest
+
+import dryad_b200 as D
+from dryad_b200.plan import xmlplan
+from dryad_b200.plan.object_store import ObjectStore
+from dryad_b200.plan.querygen import QueryGen
+from dryad_b200.utils.collections import BitVector, ReadOnlyAfterSubmitDict, ReadOnlyAfterSubmitList
+
+
+def _plan(q):
+    return QueryGen(q.context, [q.materialize_lazy()]).build()
+
+
+def test_xml_plan_round_trip_and_graph_manager_from_file():
+    ctx = D.DryadLinqContext(3)
+    q = (ctx.from_enumerable(["a b", "c"], 3).select_many(lambda l: l.split(" ")).group_by(lambda w: w)
+         .select(lambda g: (g.key, g.count())))
+    gen = _plan(q)
+    plan = xmlplan.parse_query_xml(gen.to_xml())
+    assert plan.version == ctx.version and plan.enable_speculative_duplication
+    assert [v.unique_id for v in plan.topological()] == [n.uid for n in gen.nodes]
+    by_id = {n.uid: n for n in gen.nodes}
+    for v in plan.topological():
+        n = by_id[v.unique_id]
+        assert v.partitions == n.partition_count
+        assert [p.unique_id for p in v.children] == [c.uid for c, _ in n.children]
+    assert any(p.connection_operator == "CROSSPRODUCT" for v in plan.vertices.values() for p in v.children)
+    assert plan.vertices[0].type == "INPUTTABLE" and any(v.type == "SUPER" for v in plan.vertices.values())
+    gm, sid = xmlplan.to_graph_manager(plan)
+    gm.start()
+    ran = 0
+    while True:
+        nxt = gm.next_ready(0.0)
+        if nxt is None:
+            break
+        gm.completed(nxt[0], nxt[1], 0.01)
+        ran += 1
+    assert gm.state == "Succeeded" and ran == sum(v.partitions for v in plan.vertices.values())
+    with pytest.raises(ValueError):
+        xmlplan.parse_query_xml("<NotAQuery/>")
+
+
+def _shape(q):
+    out = []
+    for n in _plan(q).nodes:
+        out.append(n.type.value if not n.members else "Super[" + ",".join(m.type.value for m in n.members) + "]")
+    return out
+
+
+def test_golden_plan_shapes():
+    ctx = D.DryadLinqContext(4)
+    src = lambda: ctx.from_enumerable(range(100), 4)
+    # decomposable GroupBy: partial -> HashPartition | Merge -> final -> finalizer (QueryGen.cs:2094-2357)
+    assert _shape(src().group_by(lambda x: x % 5).select(lambda g: (g.key, g.sum()))) == [
+        "InputTable", "Super[GroupBy,HashPartition]", "Super[Merge,GroupBy,Select,OutputTable]"]
+    # OrderBy: sample -> one vertex -> separators; RangePartition x Merge; Sort (QueryGen.cs:2362-2521)
+    assert _shape(src().order_by(lambda x: x)) == [
+        "InputTable", "Sampler", "Super[Merge,RangeSampler]", "RangePartition", "Super[Merge,OrderBy,OutputTable]"]
+    # scalar aggregate: stage 1 per partition, stage 2 on one partition (QueryGen.cs:1954-2005)
+    assert _shape(src().sum_as_query()) == ["InputTable", "BasicAggregate", "Super[Merge,BasicAggregate,OutputTable]"]
+    # Take(n): per-partition take, ordered merge to one partition, final take (QueryGen.cs:2546-2624)
+    assert _shape(src().take(3)) == ["InputTable", "PartitionOp", "Super[Merge,PartitionOp,OutputTable]"]
+    # non-homomorphic Apply merges to one partition first (QueryGen.cs:2925-2955)
+    assert _shape(src().apply(lambda xs: xs)) == ["InputTable", "Super[Merge,Apply,OutputTable]"]
+    # Where/Select pipeline fuses into one super vertex with the output
+    assert _shape(src().where(lambda x: x > 1).select(lambda x: x + 1)) == ["InputTable", "Super[Where,Select,OutputTable]"]
+    # Distinct: hash partition by element, then Distinct
+    assert _shape(src().distinct()) == ["InputTable", "HashPartition", "Super[Merge,Distinct,OutputTable]"]
+
+
+def test_object_store_and_utils(tmp_path):
+    s = ObjectStore()
+    cmp_keys = [3, 7, 11]
+    i = s.put(cmp_keys)
+    assert s.put(cmp_keys) == i and s.get(i) is cmp_keys
+    s.save(str(tmp_path / "objs.bin"))
+    with pytest.raises(RuntimeError):
+        s.put("late")
+    assert ObjectStore.load(str(tmp_path / "objs.bin")).get(i) == cmp_keys
+    d, l = ReadOnlyAfterSubmitDict(a=1), ReadOnlyAfterSubmitList([1])
+    d["b"] = 2
+    l.append(2)
+    d.freeze()
+    l.freeze()
+    with pytest.raises(D.DryadLinqException):
+        d["c"] = 3
+    with pytest.raises(D.DryadLinqException):
+        l.append(3)
+    bv = BitVector(4)
+    bv.set(2)
+    bv.set(70)
+    assert bv[2] and bv[70] and not bv[3] and bv.count() == 2 and list(bv) == [2, 70]
