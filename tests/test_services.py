@@ -1,0 +1,61 @@
+"""Cluster abstraction, node daemon over HTTP, local multi-process job submission."""
+import os
+import sys
+import urllib.request
+
+from dryad_b200.api.context import JobStatus
+from dryad_b200.api.submission import LocalJobSubmission
+from dryad_b200.runtime.process_service import H_STATUS, H_VERSION, ProcessService
+from dryad_b200.sched.cluster import Affinity, IProcessWatcher, LocalCluster, Process
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+
+
+def test_local_cluster_matches_processes_to_idle_gpus():
+    events = []
+
+    class W(IProcessWatcher):
+        def on_queued(self, p): events.append(("queued", p.id))
+        def on_matched(self, p, c): events.append(("matched", p.id, c.name))
+
+    cl = LocalCluster(4, "/tmp")
+    assert [c.name for c in cl.get_computers()] == ["gpu0", "gpu1", "gpu2", "gpu3"]
+    cl.schedule_process(Process(1, "worker --vertex 1", Affinity([2], 100), W()))
+    cl.schedule_process(Process(2, "worker --vertex 2", Affinity([3], 100, hard=True), W()))
+    assert cl.computer_idle(0) is None                     # nothing prefers gpu0 yet
+    assert cl.computer_idle(2).id == 1
+    assert cl.computer_idle(0, age_bias=5.0) is None       # hard constraint on gpu3 never relaxes
+    assert cl.computer_idle(3).id == 2
+    assert ("matched", 1, "gpu2") in events and cl.local_path(cl.computers[1], "3_0_1.tmp") == "file:///tmp/3_0_1.tmp?c=None"
+
+
+def test_process_service_mailbox_long_poll_and_ranged_file_get(tmp_path):
+    svc = ProcessService(str(tmp_path))
+    try:
+        (tmp_path / "chan.tmp").write_bytes(bytes(range(200)))
+        req = urllib.request.Request(f"{svc.uri}/process/p1/setvalue?key=cmd&status=start", data=b"launch-descriptor", method="PUT")
+        with urllib.request.urlopen(req) as r:
+            v1 = int(r.headers[H_VERSION])
+        with urllib.request.urlopen(f"{svc.uri}/process/p1/status?key=cmd&version=0&timeout=1") as r:
+            assert r.status == 200 and int(r.headers[H_VERSION]) == v1 and r.headers[H_STATUS] == "start"
+            assert r.read() == b"launch-descriptor"
+        with urllib.request.urlopen(f"{svc.uri}/process/p1/status?key=cmd&version={v1}&timeout=0.1") as r:
+            assert r.status == 204                         # nothing newer: long poll timed out
+        req = urllib.request.Request(f"{svc.uri}/file/chan.tmp", headers={"Range": "bytes=10-19"})
+        with urllib.request.urlopen(req) as r:
+            assert r.status == 206 and r.read() == bytes(range(10, 20))
+    finally:
+        svc.close()
+
+
+def test_local_job_submission_runs_spmd_workers(tmp_path):
+    job = LocalJobSubmission(os.path.join(HERE, "mgpu", "spmd_worker.py"), ["--mode", "cpu"], num_processes=2,
+                             dryad_home=str(tmp_path))
+    job.add_job_option("friendlyname", "spmd smoke")
+    assert job.get_status() == JobStatus.NotSubmitted
+    job.submit_job()
+    assert job.wait_for_completion(timeout=300) == JobStatus.Success, job.error_text()
+    assert os.path.isdir(os.path.join(job.job_dir, "log")) and "checks passed" in job.error_text()
+    bad = LocalJobSubmission(os.path.join(HERE, "mgpu", "does_not_exist.py"), num_processes=1, dryad_home=str(tmp_path))
+    bad.submit_job()
+    assert bad.wait_for_completion(timeout=120) == JobStatus.Failure
