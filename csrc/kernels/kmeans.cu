@@ -71,6 +71,26 @@ __device__ __forceinline__ void tma_load_2d(void* smem_dst, const CUtensorMap* m
       "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];"
       ::"r"(smem_u32(smem_dst)), "l"(map), "r"(smem_u32(bar)), "r"(x), "r"(y) : "memory");
 }
+__device__ __forceinline__ void tma_load_2d_mc(void* smem_dst, const CUtensorMap* map, int x, int y, uint64_t* bar, uint16_t mask) {
+  asm volatile(
+      "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes.multicast::cluster [%0], [%1, {%3, %4}], [%2], %5;"
+      ::"r"(smem_u32(smem_dst)), "l"(map), "r"(smem_u32(bar)), "r"(x), "r"(y), "h"(mask) : "memory");
+}
+__device__ __forceinline__ void tc_commit_mc(uint64_t* bar, uint16_t mask) {
+  asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;"
+               ::"r"(smem_u32(bar)), "h"(mask) : "memory");
+}
+// TMA reduce-add of one 128-byte shared-memory row segment into a global fp32 tensor (the
+// per-centroid sums): one L2 reduction transaction of 32 floats instead of eight 16-byte REDs.
+__device__ __forceinline__ void tma_reduce_add_2d(const CUtensorMap* map, int x, int y, const void* smem_src) {
+  asm volatile("cp.reduce.async.bulk.tensor.2d.global.shared::cta.add.tile.bulk_group [%0, {%1, %2}], [%3];"
+               ::"l"(map), "r"(x), "r"(y), "r"(smem_u32(smem_src)) : "memory");
+}
+__device__ __forceinline__ uint32_t cluster_rank() { uint32_t r; asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r)); return r; }
+__device__ __forceinline__ void cluster_sync_all() {
+  asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory");
+  asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory");
+}
 __device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
 __device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
 __device__ __forceinline__ void tc_commit(uint64_t* bar) {
@@ -119,8 +139,10 @@ struct Bars {
   uint32_t tmem_base;
 };
 
+template <int CLUSTER>
 __global__ void __launch_bounds__(THREADS, 1)
 km_assign(const __grid_constant__ CUtensorMap map_x, const __grid_constant__ CUtensorMap map_c,
+          const __grid_constant__ CUtensorMap map_s,
           const float* __restrict__ cnorm, int64_t n, int k, int32_t* __restrict__ assign,
           float* __restrict__ sums, unsigned long long* __restrict__ counts, float* __restrict__ inertia, int dbg) {
   extern __shared__ unsigned char smem_raw[];
@@ -132,13 +154,18 @@ km_assign(const __grid_constant__ CUtensorMap map_x, const __grid_constant__ CUt
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int nchunks = k / BN;
-  const int64_t ntiles = (n + BM - 1) / BM;
+  const int64_t ntiles_real = (n + BM - 1) / BM;
+  // every CTA of a cluster runs the same number of tiles (out-of-range tiles load zeros and are
+  // skipped by the epilogue), so the shared centroid pipeline stays in lock-step
+  const int64_t ntiles = CLUSTER > 1 ? ((ntiles_real + gridDim.x - 1) / gridDim.x) * gridDim.x : ntiles_real;
+  const uint32_t crank = CLUSTER > 1 ? cluster_rank() : 0;
+  constexpr uint16_t CMASK = (uint16_t)((1u << CLUSTER) - 1);
 
   for (int i = threadIdx.x; i < k; i += THREADS) s_cn[i] = cnorm[i];
   if (threadIdx.x == 0) {
     for (int i = 0; i < 2; ++i) { mbar_init(&bars->a_full[i], 1); mbar_init(&bars->a_empty[i], 256);
                                   mbar_init(&bars->t_full[i], 1); mbar_init(&bars->t_empty[i], 256); }
-    for (int i = 0; i < B_STAGES; ++i) { mbar_init(&bars->b_full[i], 1); mbar_init(&bars->b_empty[i], 1); }
+    for (int i = 0; i < B_STAGES; ++i) { mbar_init(&bars->b_full[i], 1); mbar_init(&bars->b_empty[i], CLUSTER); }
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
   if (warp == 1) {
@@ -147,6 +174,7 @@ km_assign(const __grid_constant__ CUtensorMap map_x, const __grid_constant__ CUt
   }
   tc_fence_before();
   __syncthreads();
+  if (CLUSTER > 1) cluster_sync_all();          // peers' barriers are initialised before any multicast
   tc_fence_after();
   const uint32_t tmem_base = bars->tmem_base;
 
@@ -162,9 +190,16 @@ km_assign(const __grid_constant__ CUtensorMap map_x, const __grid_constant__ CUt
           tma_load_2d(sA + ab * A_BYTES + kb * A_KB_BYTES, &map_x, kb * KB, (int)(tile * BM), &bars->a_full[ab]);
         for (int c = 0; c < nchunks; ++c)
           for (int kb = 0; kb < NKB; ++kb) {
-            mbar_wait(&bars->b_empty[bs], bphase ^ 1);
+            mbar_wait(&bars->b_empty[bs], bphase ^ 1);          // every CTA of the cluster freed the slot
             mbar_expect_tx(&bars->b_full[bs], B_STAGE_BYTES);
-            tma_load_2d(sB + bs * B_STAGE_BYTES, &map_c, kb * KB, c * BN, &bars->b_full[bs]);
+            if (CLUSTER == 1) {
+              tma_load_2d(sB + bs * B_STAGE_BYTES, &map_c, kb * KB, c * BN, &bars->b_full[bs]);
+            } else {
+              // this CTA fetches 1/CLUSTER of the centroid rows and multicasts them to all peers
+              constexpr int ROWS = BN / CLUSTER;
+              tma_load_2d_mc(sB + bs * B_STAGE_BYTES + crank * (ROWS * KB * 4), &map_c, kb * KB, c * BN + (int)crank * ROWS,
+                             &bars->b_full[bs], CMASK);
+            }
             if (++bs == B_STAGES) { bs = 0; bphase ^= 1; }
           }
       }
@@ -188,7 +223,7 @@ km_assign(const __grid_constant__ CUtensorMap map_x, const __grid_constant__ CUt
 #pragma unroll
             for (int kk = 0; kk < KB / 8; ++kk)   // K = 8 tf32 = 32 bytes per instruction
               tc_mma_tf32(tmem_base + tb * BN, ad + (uint64_t)(kk * 2), bd + (uint64_t)(kk * 2), IDESC, (kb | kk) != 0);
-            tc_commit(&bars->b_empty[bs]);
+            if (CLUSTER == 1) tc_commit(&bars->b_empty[bs]); else tc_commit_mc(&bars->b_empty[bs], CMASK);
             if (kb == NKB - 1) tc_commit(&bars->t_full[tb]);
           }
           __syncwarp();
@@ -250,28 +285,44 @@ km_assign(const __grid_constant__ CUtensorMap map_x, const __grid_constant__ CUt
         float xn = 0.f;
         float* dst = sums + (size_t)bi * D;
         const unsigned char* base = sA + ab * A_BYTES + (r >> 3) * 1024 + (r & 7) * 128;
-        // each thread of the pair adds one half of the point's 128 coordinates
+        // each thread of the pair adds one half of the point's 128 coordinates: the exact fp32 row
+        // segments go from the swizzled shared tile straight into sums[bi] by TMA reduce-add
 #pragma unroll
         for (int kk = 0; kk < NKB / 2; ++kk) {
           const int kb = half * (NKB / 2) + kk;
+          if (!(dbg & 4)) {     // default: vector REDs (measured 5 % faster than the TMA reduce-add form)
 #pragma unroll
-          for (int ch = 0; ch < 8; ++ch) {
-            float4 x = *reinterpret_cast<const float4*>(base + kb * A_KB_BYTES + ((ch ^ (r & 7)) << 4));
-            xn += x.x * x.x + x.y * x.y + x.z * x.z + x.w * x.w;
-            if (!(dbg & 1)) red_add_v4(dst + kb * KB + ch * 4, x);
+            for (int ch = 0; ch < 8; ++ch) {
+              float4 x = *reinterpret_cast<const float4*>(base + kb * A_KB_BYTES + ((ch ^ (r & 7)) << 4));
+              xn += x.x * x.x + x.y * x.y + x.z * x.z + x.w * x.w;
+              red_add_v4(dst + kb * KB + ch * 4, x);
+            }
+          } else {
+            tma_reduce_add_2d(&map_s, kb * KB, bi, base + kb * A_KB_BYTES);
+#pragma unroll
+            for (int ch = 0; ch < 8; ++ch) {
+              float4 x = *reinterpret_cast<const float4*>(base + kb * A_KB_BYTES + (ch << 4));
+              xn += x.x * x.x + x.y * x.y + x.z * x.z + x.w * x.w;     // order inside the row is irrelevant for the norm
+            }
           }
         }
         local_inertia += xn + (half == 0 ? best : 0.f);
       }
+      // the TMA engine must have finished READING this thread's row segments before the tile
+      // buffer is handed back to the producer
+      asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+      asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
       asm volatile("bar.sync 1, 256;" ::: "memory");   // s_best/s_bi reused by the next tile
       mbar_arrive(&bars->a_empty[ab]);
     }
+    asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");   // all reductions performed
     local_inertia = warp_sum(local_inertia);
     if (lane == 0 && inertia) atomicAdd(inertia, local_inertia);
   }
 
   tc_fence_before();
   __syncthreads();
+  if (CLUSTER > 1) cluster_sync_all();          // nobody exits while a peer may still write its smem / barriers
   if (warp == 1) {
     tc_fence_after();
     asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "n"(TMEM_COLS) : "memory");
@@ -324,12 +375,12 @@ static PFN_cuTensorMapEncodeTiled_v12000 get_encode() {
   return fn;
 }
 
-static int make_map(CUtensorMap* m, const float* base, uint64_t rows) {
+static int make_map(CUtensorMap* m, const float* base, uint64_t rows, uint32_t box_rows = BM) {
   auto enc = get_encode();
   if (!enc) return DRYAD_ERR_BAD_ARG;
   cuuint64_t dims[2] = {(cuuint64_t)D, (cuuint64_t)rows};
   cuuint64_t strides[1] = {(cuuint64_t)D * 4};
-  cuuint32_t box[2] = {(cuuint32_t)KB, (cuuint32_t)BM};
+  cuuint32_t box[2] = {(cuuint32_t)KB, box_rows};
   cuuint32_t estr[2] = {1, 1};
   CUresult r = enc(m, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, (void*)base, dims, strides, box, estr,
                    CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
@@ -357,19 +408,41 @@ int dryad_kmeans_assign(const float* points, int64_t n, const float* centroids, 
                         int max_ctas, void* stream) {
   if (n < 0 || k <= 0 || k % BN != 0 || k > MAX_K) return DRYAD_ERR_BAD_ARG;
   if (n == 0) return DRYAD_OK;
-  if (((uintptr_t)points & 15) || ((uintptr_t)centroids & 15)) return DRYAD_ERR_BAD_ARG;
+  if (((uintptr_t)points & 15) || ((uintptr_t)centroids & 15) || ((uintptr_t)sums & 15)) return DRYAD_ERR_BAD_ARG;
+  const char* cenv = getenv("DRYAD_KM_CLUSTER");
+  int cluster = cenv ? atoi(cenv) : 1;   // multicast clusters measured no faster: shared-memory operand reads bound the SS-mode MMA
+  if (cluster != 1 && cluster != 2 && cluster != 4) cluster = 2;
   CUtensorMap mx, mc;
   int rc = make_map(&mx, points, (uint64_t)n); if (rc) return rc;
-  rc = make_map(&mc, centroids, (uint64_t)k); if (rc) return rc;
-  DRYAD_CUDA_TRY(cudaFuncSetAttribute(km_assign, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SMEM_BYTES));
+  rc = make_map(&mc, centroids, (uint64_t)k, (uint32_t)(BN / cluster)); if (rc) return rc;
+  CUtensorMap ms;
+  rc = make_map(&ms, sums, (uint64_t)k, 1u); if (rc) return rc;
   int dev = 0, sms = 148;
   DRYAD_CUDA_TRY(cudaGetDevice(&dev));
   DRYAD_CUDA_TRY(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
   int64_t ntiles = (n + BM - 1) / BM;
   int grid = (int)(ntiles < sms ? ntiles : sms);
   if (max_ctas > 0 && grid > max_ctas) grid = max_ctas;
+  grid = (grid / cluster) * cluster;
+  if (grid == 0) { grid = cluster; }
   const char* dbg = getenv("DRYAD_KM_DEBUG");
-  km_assign<<<grid, THREADS, SMEM_BYTES, (cudaStream_t)stream>>>(mx, mc, cnorm, n, k, assign, sums, counts, inertia, dbg ? atoi(dbg) : 0);
+  const int dbgv = dbg ? atoi(dbg) : 0;
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3((unsigned)grid); cfg.blockDim = dim3(THREADS); cfg.dynamicSmemBytes = SMEM_BYTES; cfg.stream = (cudaStream_t)stream;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeClusterDimension;
+  attr[0].val.clusterDim.x = (unsigned)cluster; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
+  cfg.attrs = attr; cfg.numAttrs = 1;
+  if (cluster == 1) {
+    DRYAD_CUDA_TRY(cudaFuncSetAttribute(km_assign<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SMEM_BYTES));
+    DRYAD_CUDA_TRY(cudaLaunchKernelEx(&cfg, km_assign<1>, mx, mc, ms, cnorm, n, k, assign, sums, counts, inertia, dbgv));
+  } else if (cluster == 2) {
+    DRYAD_CUDA_TRY(cudaFuncSetAttribute(km_assign<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SMEM_BYTES));
+    DRYAD_CUDA_TRY(cudaLaunchKernelEx(&cfg, km_assign<2>, mx, mc, ms, cnorm, n, k, assign, sums, counts, inertia, dbgv));
+  } else {
+    DRYAD_CUDA_TRY(cudaFuncSetAttribute(km_assign<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SMEM_BYTES));
+    DRYAD_CUDA_TRY(cudaLaunchKernelEx(&cfg, km_assign<4>, mx, mc, ms, cnorm, n, k, assign, sums, counts, inertia, dbgv));
+  }
   DRYAD_LAUNCH_CHECK();
   return DRYAD_OK;
 }
