@@ -96,6 +96,7 @@ def _declare_kernels(lib):
     _sig(lib, "dryad_shift_u64_to_u32", c_int, [P, c_int64, c_int, P, P])
     _sig(lib, "dryad_fix_ties32", c_int, [P, P, c_int64, P, c_int, c_int, c_int, c_int, c_int, P, P])
     _sig(lib, "dryad_check_sorted_rows", c_int, [P, c_int64, c_int, c_int, c_int, c_int, P, P])
+    _sig(lib, "dryad_hash_agg_lane_stride", c_int, [c_int])
     _sig(lib, "dryad_hash_agg_init", c_int, [P, c_uint64, c_int, P, P, P])
     _sig(lib, "dryad_hash_agg_update", c_int, [P, c_uint64, c_int, P, P, P, P, c_int64, c_int, P, P])
     _sig(lib, "dryad_hash_agg_merge_peers", c_int, [P, c_uint64, c_int, P, P, c_int, P, P,

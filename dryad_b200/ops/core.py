@@ -222,24 +222,39 @@ def _next_pow2(x: int) -> int:
     return p
 
 
-class HashAggTable:
-    """Open-addressing aggregation table in HBM: int64 key bits -> up to 8 aggregate lanes."""
+def agg_lane_stride(nlanes: int) -> int:
+    """Words per slot of a HashAggTable value array (1, 2, 4 or 8)."""
+    return 1 if nlanes <= 1 else 2 if nlanes <= 2 else 4 if nlanes <= 4 else 8
 
-    def __init__(self, capacity: int, ops: Sequence[str], device, *, keys=None, lanes=None):
-        self.cap = _next_pow2(max(int(capacity), 64))
+
+def agg_capacity(groups: int, load: float = 1.0 / 3.0) -> int:
+    """Table capacity (a multiple of the 4-key bucket) for an expected number of groups.  One
+    third full keeps second-bucket probes under 1 % (bench/micro/agg_variants3.cu)."""
+    return max(64, (int(groups / load) + 3) // 4 * 4)
+
+
+class HashAggTable:
+    """Open-addressing aggregation table in HBM: int64 key bits -> up to 8 aggregate lanes.
+    `keys[cap]` is probed in 4-key buckets; `vals[cap, L]` is slot-major (L = lane stride) so a
+    group's aggregates share one 32-byte sector (see csrc/kernels/hash_table.cu)."""
+
+    def __init__(self, capacity: int, ops: Sequence[str], device, *, keys=None, vals=None):
+        self.cap = max((int(capacity) + 3) // 4 * 4, 64)
         self.ops = list(ops)
         self.nl = len(self.ops)
+        self.stride = agg_lane_stride(self.nl)
         self.device = device
         self.keys = keys if keys is not None else torch.empty(self.cap, dtype=torch.int64, device=device)
-        self.lanes = lanes if lanes is not None else torch.empty((max(self.nl, 1), self.cap), dtype=torch.int64, device=device)
+        self.vals = vals if vals is not None else torch.empty((self.cap, self.stride), dtype=torch.int64, device=device)
+        if self.keys.numel() != self.cap or self.vals.numel() != self.cap * self.stride:
+            raise ValueError("HashAggTable: keys/vals do not match the capacity and lane stride")
         self._ops_c = (C.c_int * max(self.nl, 1))(*[AGG[o] for o in self.ops])
-        self._lanes_c = (C.c_void_p * max(self.nl, 1))(*[self.lanes[l].data_ptr() for l in range(self.nl)])
         self.status = torch.zeros(1, dtype=torch.int32, device=device)
         self.reset()
 
     def reset(self):
         N.check(N.kernels().dryad_hash_agg_init(ptr(self.keys), self.cap, self.nl, self._ops_c,
-                                                self._lanes_c, stream()), "hash_agg_init")
+                                                ptr(self.vals), stream()), "hash_agg_init")
         self.status.zero_()
         _count()
 
@@ -255,16 +270,16 @@ class HashAggTable:
                 ins.append(c.data_ptr())
         in_c = (C.c_void_p * max(self.nl, 1))(*ins) if self.nl else (C.c_void_p * 1)()
         N.check(N.kernels().dryad_hash_agg_update(ptr(self.keys), self.cap, self.nl, self._ops_c,
-                                                  self._lanes_c, ptr(keys), in_c, keys.numel(),
+                                                  ptr(self.vals), ptr(keys), in_c, keys.numel(),
                                                   int(combine), ptr(self.status), stream()),
                 "hash_agg_update")
         _count()
 
-    def merge_into_peers(self, world: int, peer_keys_ptrs: Sequence[int], peer_lane_ptrs: Sequence[int], peer_cap: int):
+    def merge_into_peers(self, world: int, peer_keys_ptrs: Sequence[int], peer_vals_ptrs: Sequence[int], peer_cap: int):
         pk = (C.c_void_p * world)(*peer_keys_ptrs)
-        pl = (C.c_void_p * (world * max(self.nl, 1)))(*peer_lane_ptrs)
+        pv = (C.c_void_p * world)(*peer_vals_ptrs)
         N.check(N.kernels().dryad_hash_agg_merge_peers(ptr(self.keys), self.cap, self.nl, self._ops_c,
-                                                       self._lanes_c, world, pk, pl, peer_cap,
+                                                       ptr(self.vals), world, pk, pv, peer_cap,
                                                        ptr(self.status), stream()),
                 "hash_agg_merge_peers")
         _count()
@@ -278,7 +293,7 @@ class HashAggTable:
         lane_ptrs = torch.tensor([out_lanes[l].data_ptr() for l in range(max(self.nl, 1))], dtype=torch.int64).to(self.device)
         cnt = torch.zeros(1, dtype=torch.int64, device=self.device)
         N.check(N.kernels().dryad_hash_agg_extract(ptr(self.keys), self.cap, self.nl, self._ops_c,
-                                                   self._lanes_c, ptr(out_keys), ptr(lane_ptrs),
+                                                   ptr(self.vals), ptr(out_keys), ptr(lane_ptrs),
                                                    ptr(cnt), max_out, stream()), "hash_agg_extract")
         _count()
         m = int(cnt.item())

@@ -22,15 +22,15 @@ class DistributedHashAggregate:
     def __init__(self, arena: SymmetricArena, lanes: Sequence[str], local_cap: int, final_cap: int):
         self.arena, self.lanes = arena, list(lanes)
         self.world, self.rank = arena.world, arena.rank
-        nl = max(len(self.lanes), 1)
         dev = arena.device
-        fcap = K._next_pow2(max(final_cap, 64))
+        stride = K.agg_lane_stride(len(self.lanes))
+        fcap = max((int(final_cap) + 3) // 4 * 4, 64)
         fk, fk_off = arena.alloc((fcap,), torch.int64)
-        fl, fl_off = arena.alloc((nl, fcap), torch.int64)
-        self.final = K.HashAggTable(fcap, self.lanes, dev, keys=fk, lanes=fl)
+        fv, fv_off = arena.alloc((fcap, stride), torch.int64)
+        self.final = K.HashAggTable(fcap, self.lanes, dev, keys=fk, vals=fv)
         self.final_cap = fcap
         self.peer_keys = [arena.peer_ptr(r, fk_off) for r in range(self.world)]
-        self.peer_lanes = [arena.peer_ptr(r, fl_off + l * fcap * 8) for r in range(self.world) for l in range(nl)]
+        self.peer_vals = [arena.peer_ptr(r, fv_off) for r in range(self.world)]
         self.local = K.HashAggTable(local_cap, self.lanes, dev) if self.world > 1 else None
 
     def run(self, keys: torch.Tensor, cols: Sequence[Optional[torch.Tensor]]):
@@ -44,7 +44,7 @@ class DistributedHashAggregate:
         self.local.reset()
         self.local.update(keys, cols)
         self.arena.barrier(slot=2)                 # every owner table is reset before anyone merges
-        self.local.merge_into_peers(self.world, self.peer_keys, self.peer_lanes, self.final_cap)
+        self.local.merge_into_peers(self.world, self.peer_keys, self.peer_vals, self.final_cap)
         self.arena.barrier(slot=3)                 # all partials have landed
         if int(self.local.status.item()) == 1:
             raise K.N.NativeError("hash aggregate table full")

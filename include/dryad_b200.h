@@ -151,22 +151,28 @@ enum {
   DRYAD_AGG_COUNT = 0, DRYAD_AGG_SUM_I64 = 1, DRYAD_AGG_SUM_I64_CHECKED = 2, DRYAD_AGG_SUM_F64 = 3,
   DRYAD_AGG_MIN_I64 = 4, DRYAD_AGG_MAX_I64 = 5, DRYAD_AGG_MIN_F64 = 6, DRYAD_AGG_MAX_F64 = 7
 };
-/* Table = keys[cap] (cap power of two; key ~0 is reserved) + nlanes int64/double lanes [cap].
- * status: 1 table full, 3 checked-sum overflow. */
+/* Table = keys[cap] + vals[cap * L].  cap is any multiple of 4 (keys are probed in 4-key buckets,
+ * one 32-byte sector per probe; key ~0 is reserved).  Values are slot-major: the aggregates of
+ * slot s are the int64/double words vals[s*L .. s*L + nlanes), L = dryad_hash_agg_lane_stride(
+ * nlanes) (1, 2, 4 or 8), so one row's reductions hit one sector and are issued by adjacent
+ * threads of a single warp instruction.  The same probing scheme serves the join and set tables
+ * below.  status: 1 table full, 3 checked-sum overflow. */
+int dryad_hash_agg_lane_stride(int nlanes);
 int dryad_hash_agg_init(uint64_t* tbl_keys, uint64_t cap, int nlanes, const int* ops,
-                        int64_t* const* tbl_lanes, void* stream);
+                        int64_t* tbl_vals, void* stream);
 int dryad_hash_agg_update(uint64_t* tbl_keys, uint64_t cap, int nlanes, const int* ops,
-                          int64_t* const* tbl_lanes, const uint64_t* in_keys,
+                          int64_t* tbl_vals, const uint64_t* in_keys,
                           const int64_t* const* in_lanes, int64_t n, int combine, int32_t* status,
                           void* stream);
 /* Fused reduce-scatter: fold local partials into the key owner's table (owner =
- * hash_bucket(key, world)) with system-scope atomics on peer HBM. */
+ * hash_bucket(key, world)) with system-scope atomics on peer HBM.  peer_vals[r] is rank r's
+ * vals array (same lane stride). */
 int dryad_hash_agg_merge_peers(const uint64_t* tbl_keys, uint64_t cap, int nlanes, const int* ops,
-                               int64_t* const* tbl_lanes, int world, uint64_t* const* peer_keys,
-                               int64_t* const* peer_lanes, uint64_t peer_cap, int32_t* status,
+                               const int64_t* tbl_vals, int world, uint64_t* const* peer_keys,
+                               int64_t* const* peer_vals, uint64_t peer_cap, int32_t* status,
                                void* stream);
 int dryad_hash_agg_extract(const uint64_t* tbl_keys, uint64_t cap, int nlanes, const int* ops,
-                           int64_t* const* tbl_lanes, uint64_t* out_keys,
+                           const int64_t* tbl_vals, uint64_t* out_keys,
                            int64_t* const* out_lanes_dev, unsigned long long* out_count,
                            int64_t out_cap, void* stream);
 
