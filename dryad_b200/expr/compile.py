@@ -176,17 +176,23 @@ def compile_program(outputs: Mapping[str, Expr], predicate: Optional[Expr], col_
 
 
 def run_on_gpu(outputs: Mapping[str, Expr], cols: Mapping[str, torch.Tensor], n: int,
-               predicate: Optional[Expr] = None):
+               predicate: Optional[Expr] = None, *, tables=None, arrays=None, reduce=None,
+               count_flags: bool = False):
     """Evaluate projections (+ optional predicate) in ONE kernel.  Returns (out_cols, flags).
     Preferred path: a kernel generated for this exact pipeline and compiled with NVRTC
-    (expr/codegen.py); fallback: the generic register-program interpreter kernel."""
+    (expr/codegen.py); fallback: the generic register-program interpreter kernel.
+    `tables` / `arrays` / `reduce` / `count_flags` (fused join probes, side-array gathers and
+    in-kernel reductions, see codegen.run_fused) exist only in generated code."""
     import os
-    if os.environ.get("DRYAD_EXPR_CODEGEN", "1") != "0":
+    fused_only = bool(tables or arrays or reduce or count_flags)
+    if fused_only or os.environ.get("DRYAD_EXPR_CODEGEN", "1") != "0":
         from . import codegen
         try:
-            return codegen.run_fused(outputs, cols, n, predicate)
-        except codegen.CodegenUnavailable:
-            pass
+            return codegen.run_fused(outputs, cols, n, predicate, tables=tables, arrays=arrays,
+                                     reduce=reduce, count_flags=count_flags)
+        except codegen.CodegenUnavailable as ex:
+            if fused_only:
+                raise CompileError(f"fused probe/reduce pipeline needs NVRTC code generation: {ex}") from ex
     from ..ops import core as K
     from .ir import retype
     col_dtypes = {k: v.dtype for k, v in cols.items() if isinstance(v, torch.Tensor) and v.dim() == 1}

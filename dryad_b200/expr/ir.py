@@ -215,6 +215,17 @@ def retype(e: Expr, col_kinds: Mapping[str, str]) -> Expr:
     return Expr(e.op, tuple(a), e.kind)
 
 
+def probe(table: str, key) -> Expr:
+    """Row of the build side of hash table `table` whose key equals `key`, or -1 (GPU-only node:
+    the probe of a unique-key join fused into the consuming pipeline, expr/codegen.py)."""
+    return Expr("probe", (table, wrap(key)), "i")
+
+
+def gather(array: str, index, kind: str = "i") -> Expr:
+    """array[index] for a side array that is not row-aligned with the inputs (0 where index < 0)."""
+    return Expr("gather", (array, wrap(index)), kind)
+
+
 def rowid() -> Expr:
     """Position of the row inside its partition (indexed Select/Where support)."""
     return Expr("rowid", (), "i")

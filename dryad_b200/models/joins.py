@@ -18,7 +18,8 @@ def generate(n_fact: int, n_dim: int, seed: int, device, rank: int = 0, world: i
 
 
 def bench(rank, world, dev, n_fact, n_dim, steps, warmup, max_over_ranks, barrier, threshold=500):
-    from ..expr import col, where
+    import os
+    from ..expr import col, gather, probe, where
     from ..expr.compile import run_on_gpu
     from ..ops import core as K
     from ..parallel.djoin import BroadcastJoin
@@ -27,8 +28,19 @@ def bench(rank, world, dev, n_fact, n_dim, steps, warmup, max_over_ranks, barrie
     arena = SymmetricArena(K._next_pow2(2 * n_dim + 64) * 12 + n_dim * 12 + (16 << 20), rank, world, None, dev)
     bj = BroadcastJoin(arena, n_dim, 1)
 
+    fused = os.environ.get("DRYAD_JOIN_FUSED", "1") != "0"
+
     def step():
         bj.build(dk, [da], base)                                      # fused broadcast + build
+        if fused:
+            # probe + payload gather + Where + Select + Sum in ONE generated kernel: the fact side is
+            # read once and nothing per-row is written (expr.probe / expr.gather, expr/codegen.py)
+            hit = probe("dim", col("k"))
+            keep = (col("v") >= threshold) & (hit >= 0)
+            out, cnt = run_on_gpu({"r": where(keep, col("v") * gather("attr", hit), 0)}, {"k": fk, "v": fv}, n_fact,
+                                  predicate=keep, tables={"dim": bj}, arrays={"attr": bj.cols[0]},
+                                  reduce={"r": "sum"}, count_flags=True)
+            return out["r"], cnt
         di, matched = bj.probe_unique(fk)                             # local probe: the fact side never moves
         a = K.gather_rows(bj.cols[0], di)
         # Where(v >= t) and Select(v * attr) fused into one register program; unmatched rows give 0
@@ -52,5 +64,5 @@ def bench(rank, world, dev, n_fact, n_dim, steps, warmup, max_over_ranks, barrie
     m = int(m.item())
     ok = int(s.item()) == ref and m == int(sel.sum().item())
     return {"metric": "broadcast_join_fact_rows_per_s", "value": world * n_fact / (ms * 1e-3), "unit": "rows/s",
-            "ms_per_step": ms, "fact_rows_per_gpu": n_fact, "dim_rows": n_dim, "matches_local": m, "valid": bool(ok),
+            "ms_per_step": ms, "fact_rows_per_gpu": n_fact, "dim_rows": n_dim, "matches_local": m, "valid": bool(ok), "fused_probe_pipeline": fused,
             "gpu_launches": K.launch_count() - l0}

@@ -319,9 +319,21 @@ class JoinTable:
         self.next = torch.empty(max(n, 1), dtype=torch.int32, device=dev)
         self.status = torch.zeros(1, dtype=torch.int32, device=dev)
         self.n = n
+        self._unique = None
         N.check(N.kernels().dryad_join_build(ptr(self.keys), ptr(self.head), self.cap, ptr(build_keys),
                                              ptr(self.next), n, ptr(self.status), stream()), "join_build")
         _count(2)
+
+    @property
+    def unique(self) -> bool:
+        """True when every build key is distinct (syncs once): the build side is a dimension table
+        and the probe can be fused into the consuming pipeline (`expr.probe`)."""
+        if self._unique is None:
+            st = int(self.status.item())
+            if st == 1:
+                raise N.NativeError("join table full")
+            self._unique = st == 0
+        return self._unique
 
     def probe(self, probe_keys: torch.Tensor):
         """Returns (probe_idx, build_idx) int32 index pairs of all matches."""

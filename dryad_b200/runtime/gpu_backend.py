@@ -482,6 +482,9 @@ def _join(be, node, part, inputs, env):
         op, ib = K.merge_join(okb, ikb)
     else:
         jt = K.JoinTable(ik.contiguous())                # build on the inner (usually smaller) side
+        fused = _join_fused(be, jt, outer, inner, ok, res)
+        if fused is not None:
+            return fused
         op, ib = jt.probe(ok.contiguous())
     o_sel, i_sel = outer.take(op), inner.take(ib)
     cols = {("o." + k): v for k, v in o_sel.cols.items()}
@@ -492,6 +495,53 @@ def _join(be, node, part, inputs, env):
         dt = {"i": torch.int64, "f": torch.float64, "b": torch.bool}
         out = {k: torch.empty(0, dtype=dt[e.kind], device=be.device) for k, e in proj.items()}
     return [ColumnBatch(out, op.numel(), tuple_like=isinstance(res, X.TupleFields))]
+
+
+def _join_fused(be, jt, outer: ColumnBatch, inner: ColumnBatch, ok: torch.Tensor, res):
+    """Unique-key build side (dimension table): probe, inner-column gather and the result selector
+    run as ONE generated kernel over the outer rows — no (probe, build) pair lists, no gathered
+    intermediates; matched rows are then compacted.  Returns None when not applicable."""
+    try:
+        if not jt.unique:
+            return None
+        proj = res if isinstance(res, dict) else {"value": res}
+        hit = X.probe("jt", X.col("__okey"))
+        sub = {}
+        arrays = {}
+        for k, v in inner.cols.items():
+            if v.dim() != 1:
+                return None
+            kind = "f" if v.dtype in (torch.float32, torch.float64) else ("b" if v.dtype == torch.bool else "i")
+            g = X.gather("i." + k, hit, "f" if kind == "f" else "i")
+            sub["i." + k] = X.cast(g, "b") if kind == "b" else g
+            arrays["i." + k] = (v.view(torch.uint8) if v.dtype == torch.bool else v).contiguous()
+        outs = {}
+        for name, e in proj.items():
+            e = X.wrap(e)
+            if e.kind not in ("i", "f", "b"):
+                return None
+            used = {c for c in e.columns() if c.startswith("i.")}
+            outs[name] = e.substitute({c: sub[c] for c in used})
+        cols = {("o." + k): v for k, v in outer.cols.items()}
+        cols["__okey"] = ok.contiguous()
+        need = set()
+        for e in outs.values():
+            need |= {a for a in arrays if _mentions_array(e, a)}
+        out, flags = run_on_gpu(outs, cols, outer.n, predicate=hit >= 0, tables={"jt": jt},
+                                arrays={a: arrays[a] for a in need})
+    except (CompileError, X.TraceError):
+        return None
+    idx, m = K.compact_flags(flags)
+    batch = ColumnBatch(out, outer.n, tuple_like=isinstance(res, X.TupleFields))
+    return [batch.take(idx)]
+
+
+def _mentions_array(e, name: str) -> bool:
+    if not isinstance(e, X.Expr):
+        return False
+    if e.op == "gather" and e.args[0] == name:
+        return True
+    return any(_mentions_array(a, name) for a in e.args)
 
 
 def _distinct(be, node, part, inputs, env):

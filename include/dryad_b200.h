@@ -178,6 +178,8 @@ int dryad_hash_agg_extract(const uint64_t* tbl_keys, uint64_t cap, int nlanes, c
 
 /* ---- K8 hash join / K10 hash sets: LinqToDryad/DryadLinqVertex.cs:775-1030, 6703-7315,
  *      1239-1660 ----------------------------------------------------------------------------- */
+/* status after a build: 1 = table full, 2 = the build side has duplicate keys (the single-pass
+ * unique-key probes must not be used), 0 = all build keys distinct. */
 int dryad_join_build(uint64_t* tbl_keys, int32_t* head, uint64_t cap, const uint64_t* build_keys,
                      int32_t* next, int64_t n, int32_t* status, void* stream);
 int dryad_join_probe(const uint64_t* tbl_keys, const int32_t* head, uint64_t cap,

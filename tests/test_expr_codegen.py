@@ -34,3 +34,21 @@ def test_generated_cuda_compiles_for_sm100a():
     (err,) = nvrtc.nvrtcCompileProgram(prog, len(opts), opts)
     assert int(err) == 0, src
     assert "dryad_fused" in src and src.count("in0[i]") == 1      # every input column is loaded exactly once
+
+
+@pytest.mark.skipif(not codegen.available(), reason="cuda-python/nvrtc not importable")
+def test_fused_probe_gather_reduce_source_compiles():
+    """A join probe, a side-array gather and in-kernel reductions are part of the generated
+    pipeline: one probe per row even when the node is used twice (CSE), per-block partials out."""
+    from cuda.bindings import nvrtc
+    from dryad_b200.expr import gather, probe
+    hit = probe("dim", col("k"))
+    keep = (col("v") >= 500) & (hit >= 0)
+    src = codegen._source({"r": where(keep, col("v") * gather("attr", hit), 0), "f": gather("w", hit, "f") * 2.0}, keep,
+                          ["k", "v"], [torch.int64, torch.int64], tables=["dim"],
+                          arrays=[("attr", torch.int64), ("w", torch.float64)], reduce={"r": "sum", "f": "max"}, count_flags=True)
+    assert src.count("dryad_probe(tk0") == 1
+    err, prog = nvrtc.nvrtcCreateProgram(src.encode(), b"t.cu", 0, [], [])
+    opts = [b"--gpu-architecture=sm_100a"]
+    (err,) = nvrtc.nvrtcCompileProgram(prog, len(opts), opts)
+    assert int(err) == 0, src

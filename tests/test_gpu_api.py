@@ -97,3 +97,45 @@ def test_merge_join_and_take_after_order_on_gpu():
     vals = [(i * 7919) % 1000 for i in range(2000)]
     c4 = D.DryadLinqContext(4, device="cuda")
     assert c4.from_enumerable(vals, 4).order_by(lambda x: x).take(10).to_list() == sorted(vals)[:10]
+
+
+def test_join_against_unique_dimension_runs_as_one_fused_kernel():
+    """Dimension-table join (unique build keys): probe + gather + result selector are one generated
+    kernel; a build side with duplicate keys takes the general pair-emitting path.  Both agree with
+    the oracle."""
+    from dryad_b200.ops import core as K
+    fact = [{"k": (i * 31) % 140, "v": i} for i in range(3000)]            # keys 100..139 have no match
+    dim = [{"k": i, "w": i * 3 + 1, "f": i * 0.5} for i in range(100)]
+    dup = dim + [{"k": 7, "w": -1, "f": 0.25}]
+    sel = lambda a, b: {"k": a.k, "x": a.v * b.w, "g": b.f + 1.0}    # noqa: E731
+    ld = D.DryadLinqContext(1, local_debug=True)
+    for d in (dim, dup):
+        want = sorted(ld.from_enumerable(fact).join(ld.from_enumerable(d), lambda a: a.k, lambda b: b.k, sel).to_list(), key=repr)
+        ctx = D.DryadLinqContext(2, device="cuda")
+        before = K.launch_count()
+        got = sorted(ctx.from_enumerable(fact, 2).join(ctx.from_enumerable(d, 1), lambda a: a.k, lambda b: b.k, sel).to_list(), key=repr)
+        assert got == want
+        assert K.launch_count() > before and ctx._backend().host_fallbacks == 0
+
+
+def test_fused_probe_reduce_matches_torch():
+    from dryad_b200.expr import col, gather, probe, where
+    from dryad_b200.expr.compile import run_on_gpu
+    from dryad_b200.ops import core as K
+    dev = torch.device("cuda")
+    g = torch.Generator(device=dev).manual_seed(5)
+    n, nd = 1_000_003, 5000
+    fk = torch.randint(0, nd + 700, (n,), dtype=torch.int64, device=dev, generator=g)
+    fv = torch.randint(0, 1000, (n,), dtype=torch.int64, device=dev, generator=g)
+    dk = torch.randperm(nd, device=dev, generator=g).to(torch.int64)
+    da = (dk * 2654435761) % 97
+    jt = K.JoinTable(dk.contiguous())
+    assert jt.unique
+    hit = probe("dim", col("k"))
+    keep = (col("v") >= 500) & (hit >= 0)
+    out, cnt = run_on_gpu({"r": where(keep, col("v") * gather("a", hit), 0)}, {"k": fk, "v": fv}, n, predicate=keep,
+                          tables={"dim": jt}, arrays={"a": da}, reduce={"r": "sum"}, count_flags=True)
+    m = (fv >= 500) & (fk < nd)
+    assert int(cnt.item()) == int(m.sum().item())
+    assert int(out["r"].item()) == int((fv[m] * ((fk[m] * 2654435761) % 97)).sum().item())
+    assert not K.JoinTable(torch.cat([dk, dk[:3]]).contiguous()).unique
