@@ -13,7 +13,7 @@ from dryad_b200.parallel.symm import SymmetricArena  # noqa: E402
 n = int(sys.argv[1]) if len(sys.argv) > 1 else 8_000_000
 pts, centres = KM.generate(n, 1024, 5, "cuda")
 out = {}
-for mode, ew in (("0", "16"), ("1", "8"), ("1", "16")):
+for mode, ew in (("0", "16"), ("1", "8")):
     os.environ["DRYAD_KM_PAIR"] = mode
     os.environ["DRYAD_KM_EPI_WARPS"] = ew
     km = KMeans(SymmetricArena(16 << 20), 1024, n)
@@ -32,7 +32,7 @@ for mode, ew in (("0", "16"), ("1", "8"), ("1", "16")):
     torch.cuda.synchronize()
     print("pair ew=" + ew if mode == "1" else "single", "ms/iter", round(e0.elapsed_time(e1) / 5, 3), flush=True)
 a0, c0, _ = out["016"]
-for key in ("18", "116"):
+for key in ("18",):
     a1, c1, _ = out[key]
     diff = int((a0 != a1).sum().item())
     print(key, "assignments differing:", diff, "of", n, " max centroid delta:", float((c0 - c1).abs().max().item()))

@@ -66,6 +66,15 @@ __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
         : "=r"(done) : "r"(addr), "r"(parity) : "memory");
   } while (!done);
 }
+__device__ __forceinline__ bool mbar_try(uint64_t* bar, uint32_t parity) {
+  uint32_t done;
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+      "selp.u32 %0, 1, 0, p;\n\t}"
+      : "=r"(done) : "r"(smem_u32(bar)), "r"(parity) : "memory");
+  return done != 0;
+}
 __device__ __forceinline__ void tma_load_2d(void* smem_dst, const CUtensorMap* map, int x, int y, uint64_t* bar) {
   asm volatile(
       "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];"
@@ -444,21 +453,32 @@ km_assign_pair(const __grid_constant__ CUtensorMap map_x, const __grid_constant_
 
   if (warp == 0) {
     // ===== TMA producer (both CTAs) =====
+    // The point tile of the NEXT pair-tile is requested as soon as its buffer is free (polled
+    // between centroid stages), not after the current tile's last centroid stage: a 64 KiB tile
+    // straight from HBM takes longer than the five stages of look-ahead (ncu: the MMA issuer spent
+    // 76 % of its time waiting for A before this).
     if (lane == 0) {
       uint32_t it = 0, bs = 0, bphase = 0;
-      for (int64_t tile = pair; tile < ntiles; tile += npairs, ++it) {
-        const uint32_t ab = it & 1;
-        mbar_wait(&bars->a_empty[ab], ((it >> 1) & 1) ^ 1);
+      auto issue_a = [&](int64_t tile, uint32_t itx) {
+        const uint32_t ab = itx & 1;
         mbar_expect_tx(&bars->a_full[ab], A_BYTES);
         for (int kb = 0; kb < NKB; ++kb)
           tma_load_2d(sA + ab * A_BYTES + kb * A_KB_BYTES, &map_x, kb * KB, (int)(tile * 2 * BM + crank * BM), &bars->a_full[ab]);
+      };
+      if (pair < ntiles) issue_a(pair, 0);                       // buffers start empty
+      for (int64_t tile = pair; tile < ntiles; tile += npairs, ++it) {
+        const int64_t next = tile + npairs;
+        bool next_done = next >= ntiles;
+        const uint32_t nab = (it + 1) & 1, nparity = (((it + 1) >> 1) & 1) ^ 1;
         for (int c = 0; c < nchunks; ++c)
           for (int kb = 0; kb < NKB; ++kb) {
+            if (!next_done && mbar_try(&bars->a_empty[nab], nparity)) { issue_a(next, it + 1); next_done = true; }
             mbar_wait(&bars->b_empty[bs], bphase ^ 1);            // leader's multicast commit freed the slot in both CTAs
             if (leader) mbar_expect_tx(&bars->b_full[bs], 2 * B_STAGE_BYTES);   // both halves report to the leader
             tma_load_2d_pair(sB + bs * B_STAGE_BYTES, &map_c, kb * KB, c * BN2 + (int)crank * BN, &bars->b_full[bs]);
             if (++bs == B_STAGES) { bs = 0; bphase ^= 1; }
           }
+        if (!next_done) { mbar_wait(&bars->a_empty[nab], nparity); issue_a(next, it + 1); }
       }
     }
   } else if (warp == 1) {
@@ -517,64 +537,92 @@ km_assign_pair(const __grid_constant__ CUtensorMap map_x, const __grid_constant_
       const uint32_t ab = it & 1;
       float best = 3.4e38f;
       int bchunk = 0;
+      // Accumulator columns travel TMEM -> registers in 64-column granules, two per chunk, always
+      // one load in flight while the previous granule is reduced; the buffer is handed back to the
+      // MMA issuer the moment its last granule has landed.
+      constexpr int G = 64, NG = COLS / G;
+      static_assert(NG == 2, "the granule pipeline below is written for two granules per chunk");
+      uint32_t va[G], vb[G];
+      const uint32_t trow = tmem_base + ((uint32_t)(q * 32) << 16) + part * COLS;
+      mbar_wait(&bars->t_full[cc & 1], (cc >> 1) & 1);
+      tc_fence_after();
+      tc_ld_32x32_x64_nowait(trow + (cc & 1) * BN2, va);
       for (int c = 0; c < nchunks; ++c, ++cc) {
         const uint32_t tb = cc & 1;
-        mbar_wait(&bars->t_full[tb], (cc >> 1) & 1);
-        tc_fence_after();
-        // pull this thread's whole column range into registers, hand the accumulator buffer back
-        // to the MMA issuer at once, and only then do the arithmetic
-        uint32_t vr[COLS];
+        const uint32_t cn_s = smem_u32(s_cn + c * BN2 + part * COLS);
+        float m0 = 3.4e38f, m1 = 3.4e38f, m2 = 3.4e38f, m3 = 3.4e38f;
+        tc_ld_wait();                                             // granule A of chunk c is in registers
+        tc_ld_32x32_x64_nowait(trow + tb * BN2 + G, vb);          // granule B in flight ...
 #pragma unroll
-        for (int sub = 0; sub < COLS / 64; ++sub)
-          tc_ld_32x32_x64_nowait(tmem_base + ((uint32_t)(q * 32) << 16) + tb * BN2 + part * COLS + sub * 64, vr + sub * 64);
-        tc_ld_wait();
+        for (int j = 0; j < G; j += 4) {                          // ... while A is reduced
+          const float4 n4 = lds_f4(cn_s + j * 4);
+          m0 = fminf(m0, pack_idx(fmaf(-2.f, __uint_as_float(va[j]), n4.x), j));
+          m1 = fminf(m1, pack_idx(fmaf(-2.f, __uint_as_float(va[j + 1]), n4.y), j + 1));
+          m2 = fminf(m2, pack_idx(fmaf(-2.f, __uint_as_float(va[j + 2]), n4.z), j + 2));
+          m3 = fminf(m3, pack_idx(fmaf(-2.f, __uint_as_float(va[j + 3]), n4.w), j + 3));
+        }
+        tc_ld_wait();                                             // the whole chunk has left TMEM
         tc_fence_before();
         __syncwarp();
         if (lane == 0) { if (leader) mbar_arrive(&bars->t_empty[tb]); else mbar_arrive_leader_relaxed(&bars->t_empty[tb]); }
-        float m0 = 3.4e38f, m1 = 3.4e38f, m2 = 3.4e38f, m3 = 3.4e38f;
-        const uint32_t cn_s = smem_u32(s_cn + c * BN2 + part * COLS);
+        if (c + 1 < nchunks) {                                    // first granule of the next chunk in flight
+          mbar_wait(&bars->t_full[tb ^ 1], ((cc + 1) >> 1) & 1);
+          tc_fence_after();
+          tc_ld_32x32_x64_nowait(trow + (tb ^ 1) * BN2, va);
+        }
 #pragma unroll
-        for (int j = 0; j < COLS; j += 4) {
-          const float4 n4 = lds_f4(cn_s + j * 4);
-          m0 = fminf(m0, pack_idx(fmaf(-2.f, __uint_as_float(vr[j]), n4.x), j));
-          m1 = fminf(m1, pack_idx(fmaf(-2.f, __uint_as_float(vr[j + 1]), n4.y), j + 1));
-          m2 = fminf(m2, pack_idx(fmaf(-2.f, __uint_as_float(vr[j + 2]), n4.z), j + 2));
-          m3 = fminf(m3, pack_idx(fmaf(-2.f, __uint_as_float(vr[j + 3]), n4.w), j + 3));
+        for (int j = 0; j < G; j += 4) {
+          const float4 n4 = lds_f4(cn_s + (G + j) * 4);
+          m0 = fminf(m0, pack_idx(fmaf(-2.f, __uint_as_float(vb[j]), n4.x), G + j));
+          m1 = fminf(m1, pack_idx(fmaf(-2.f, __uint_as_float(vb[j + 1]), n4.y), G + j + 1));
+          m2 = fminf(m2, pack_idx(fmaf(-2.f, __uint_as_float(vb[j + 2]), n4.z), G + j + 2));
+          m3 = fminf(m3, pack_idx(fmaf(-2.f, __uint_as_float(vb[j + 3]), n4.w), G + j + 3));
         }
         const float cm = fminf(fminf(m0, m1), fminf(m2, m3));
         if (cm < best) { best = cm; bchunk = c; }
       }
       int bi = bchunk * BN2 + part * COLS + (int)(__float_as_uint(best) & 0x7Fu);
       best = __uint_as_float(__float_as_uint(best) & 0xFFFFFF80u);
-      // every part publishes its candidate, one named barrier, every part reads all candidates
+      // every part publishes its candidate, one named barrier, every reader merges all candidates
       float2* xrow = s_x + (size_t)ab * PARTS * 128;
       xrow[part * 128 + r] = make_float2(best, __int_as_float(bi));
       asm volatile("bar.sync 1, %0;" ::"n"(EW * 32) : "memory");
-#pragma unroll
-      for (int p = 0; p < PARTS; ++p) {
-        const float2 o = xrow[p * 128 + r];
-        const int oi = __float_as_int(o.y);
-        if (o.x < best || (o.x == best && oi < bi)) { best = o.x; bi = oi; }
-      }
       mbar_wait(&bars->a_full[ab], (it >> 1) & 1);  // TMA-written tile visible to this thread
-      const int64_t row = tile * 2 * BM + crank * BM + r;
-      if (row < n) {
-        if (part == 0) { assign[row] = bi; atomicAdd(&counts[bi], 1ull); }
+      const int64_t row0 = tile * 2 * BM + crank * BM;
+      if (part == 0) {                              // one thread per point: assignment and count
+#pragma unroll
+        for (int p = 1; p < PARTS; ++p) {
+          const float2 o = xrow[p * 128 + r];
+          const int oi = __float_as_int(o.y);
+          if (o.x < best || (o.x == best && oi < bi)) { best = o.x; bi = oi; }
+        }
+        if (row0 + r < n) { assign[row0 + r] = bi; atomicAdd(&counts[bi], 1ull); local_inertia += best; }
+      }
+      // sums: one WARP per point — 32 lanes x 16 bytes = the point's whole fp32 row, read from the
+      // swizzled tile and added to its centroid's row with one coalesced 512-byte reduction
+      // (the lane-per-point form issued 32 half-used sectors per instruction; ncu: lg_throttle).
+      {
+        constexpr int ROWS_PER_WARP = BM / EW;
+        const int kb = lane >> 3, ch = lane & 7;
         float xn = 0.f;
-        float* dst = sums + (size_t)bi * D;
-        const uint32_t base_s = smem_u32(sA + ab * A_BYTES + (r >> 3) * 1024 + (r & 7) * 128);
-        // each of the PARTS threads of a point adds its share of the 128 exact fp32 coordinates
+#pragma unroll 4
+        for (int i = 0; i < ROWS_PER_WARP; ++i) {
+          const int rr = ew * ROWS_PER_WARP + i;
+          float2 o = xrow[rr];
+          int wi = __float_as_int(o.y);
 #pragma unroll
-        for (int kk = 0; kk < NKB / PARTS; ++kk) {
-          const int kb = part * (NKB / PARTS) + kk;
-#pragma unroll
-          for (int ch = 0; ch < 8; ++ch) {
-            const float4 x = lds_f4(base_s + kb * A_KB_BYTES + ((ch ^ (r & 7)) << 4));
+          for (int p = 1; p < PARTS; ++p) {
+            const float2 o2 = xrow[p * 128 + rr];
+            const int oi = __float_as_int(o2.y);
+            if (o2.x < o.x || (o2.x == o.x && oi < wi)) { o = o2; wi = oi; }
+          }
+          if (row0 + rr < n) {
+            const float4 x = lds_f4(smem_u32(sA + ab * A_BYTES + kb * A_KB_BYTES + (rr >> 3) * 1024 + (rr & 7) * 128 + ((ch ^ (rr & 7)) << 4)));
             xn += x.x * x.x + x.y * x.y + x.z * x.z + x.w * x.w;
-            if (!(dbg & 1)) red_add_v4(dst + kb * KB + ch * 4, x);
+            if (!(dbg & 1)) red_add_v4(sums + (size_t)wi * D + kb * KB + ch * 4, x);
           }
         }
-        local_inertia += xn + (part == 0 ? best : 0.f);
+        local_inertia += xn;
       }
       mbar_arrive(&bars->a_empty[ab]);
     }
@@ -689,21 +737,15 @@ int dryad_kmeans_assign(const float* points, int64_t n, const float* centroids, 
     const char* dbg = getenv("DRYAD_KM_DEBUG");
     const int dbgv = dbg ? atoi(dbg) : 0;
     cudaLaunchConfig_t cfg = {};
-    const char* wenv = getenv("DRYAD_KM_EPI_WARPS");
-    const int ew = wenv ? atoi(wenv) : 8;       // 16 epilogue warps measured slower (4.6 ms)
-    cfg.gridDim = dim3((unsigned)(2 * pairs)); cfg.blockDim = dim3((unsigned)((2 + (ew == 8 ? 8 : 16)) * 32));
+    // 8 epilogue warps; a 16-warp variant (64 columns per thread) measured slower (4.3-4.6 ms)
+    cfg.gridDim = dim3((unsigned)(2 * pairs)); cfg.blockDim = dim3((unsigned)((2 + 8) * 32));
     cfg.dynamicSmemBytes = SMEM_BYTES2; cfg.stream = (cudaStream_t)stream;
     cudaLaunchAttribute attr[1];
     attr[0].id = cudaLaunchAttributeClusterDimension;
     attr[0].val.clusterDim.x = 2; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
     cfg.attrs = attr; cfg.numAttrs = 1;
-    if (ew == 8) {
-      DRYAD_CUDA_TRY(cudaFuncSetAttribute(km_assign_pair<8>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SMEM_BYTES2));
-      DRYAD_CUDA_TRY(cudaLaunchKernelEx(&cfg, km_assign_pair<8>, mx, mc, cnorm, n, k, assign, sums, counts, inertia, dbgv));
-    } else {
-      DRYAD_CUDA_TRY(cudaFuncSetAttribute(km_assign_pair<16>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SMEM_BYTES2));
-      DRYAD_CUDA_TRY(cudaLaunchKernelEx(&cfg, km_assign_pair<16>, mx, mc, cnorm, n, k, assign, sums, counts, inertia, dbgv));
-    }
+    DRYAD_CUDA_TRY(cudaFuncSetAttribute(km_assign_pair<8>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SMEM_BYTES2));
+    DRYAD_CUDA_TRY(cudaLaunchKernelEx(&cfg, km_assign_pair<8>, mx, mc, cnorm, n, k, assign, sums, counts, inertia, dbgv));
     DRYAD_LAUNCH_CHECK();
     return DRYAD_OK;
   }
