@@ -18,6 +18,13 @@
 //  * GraphManager/stagemanager/DrDefaultManager.cpp:664-714  CheckForDuplicates.
 //  * GraphManager/stagemanager/DrDynamicAggregateManager.h:174-179, DrDynamicDistributor.h:64,
 //    DrDynamicBroadcast.cpp:125-130  dynamic graph rewrites.
+//  * GraphManager/vertex/DrClique.h:28-64, DrCohort.cpp:852-929  start cliques / gangs: vertices
+//    joined by FIFO or pipe edges start together once every member's external (file) inputs exist,
+//    and fail together (a streamed edge keeps nothing to re-read).
+//  * GraphManager/stagemanager/DrPipelineSplitManager.h:22-83  a dynamic split of a stage is
+//    followed 1:1 by the pointwise stages downstream (semi variant: side inputs are re-broadcast).
+//  * GraphManager/stagemanager/DrDynamicRangeDistributor.h:22-78  consumer count of a range
+//    distributor from sample volume / sampling rate.
 #include "../../include/dryad_host.h"
 
 #include <math.h>
@@ -45,11 +52,15 @@ struct Vertex {
   int next_version = 0;
   int completed_version = -1;
   int failures = 0;
-  int pending_inputs = 0;
+  int pending_inputs = 0;       // outstanding EXTERNAL (file) inputs; streamed edges are not counted
+  int clique = -1;              // start clique (gang) id, -1 = starts alone
+  bool removed = false;         // replaced by a dynamic resize of its stage
   bool duplicate_requested = false;
   std::vector<Attempt> running;
   std::vector<int> inputs;      // producer vertex ids (with multiplicity)
+  std::vector<uint8_t> input_fifo;
   std::vector<int> consumers;
+  std::vector<uint8_t> consumer_fifo;
   double seconds = 0, bytes_in = 0;
 };
 
@@ -58,29 +69,107 @@ struct Sample { double bytes, seconds; };
 struct Stage {
   std::string name;
   int nparts;
-  int first_vertex;
+  std::vector<int> vids;        // vertex ids of the live partitions
   std::vector<Sample> samples;
   double startup = 0, per_byte = 0, sigma = 0, inlier_max = 0;
   bool have_model = false;
   int completed = 0;
 };
 
+struct Conn { int src, dst, kind, channel; };
+
 struct GM {
   std::mutex mu;
   std::vector<Stage> stages;
   std::vector<Vertex> verts;
+  std::vector<Conn> conns;
+  std::vector<std::vector<int>> cliques;
+  int live = 0;                 // vertices that are not `removed`
   int jstate = J_NOT_STARTED;
   int max_failures = 6;
   int max_running_versions = 3;
   bool speculative = true;
   double default_outlier_s = 600.0, min_outlier_s = 10.0, nonparam_fraction = 0.5;
   int completed = 0;
-  int total_failures = 0, duplicates_started = 0, invalidations = 0;
+  int total_failures = 0, duplicates_started = 0, invalidations = 0, gang_restarts = 0;
   std::string error;
 };
 
 void make_ready_if_possible(GM* g, Vertex& v) {
-  if (v.state == V_WAITING && v.pending_inputs == 0) v.state = V_READY;
+  if (v.removed) return;
+  if (v.clique < 0) {
+    if (v.state == V_WAITING && v.pending_inputs == 0) v.state = V_READY;
+    return;
+  }
+  // DrStartClique::StartVersionIfReady: the whole clique becomes runnable at once, and only when
+  // no member still waits for an external input
+  const std::vector<int>& m = g->cliques[v.clique];
+  for (int id : m) {
+    const Vertex& o = g->verts[id];
+    if (o.state == V_COMPLETED) continue;
+    if (o.state != V_WAITING || o.pending_inputs != 0) return;
+  }
+  for (int id : m) if (g->verts[id].state == V_WAITING) g->verts[id].state = V_READY;
+}
+
+// Take back a completed vertex's output (it has to run again); consumers that have not completed
+// wait for it once more.
+void revoke(GM* g, Vertex& up) {
+  if (up.state != V_COMPLETED) return;
+  up.state = V_WAITING; up.completed_version = -1; g->completed--; g->stages[up.stage].completed--;
+  g->invalidations++;
+  for (size_t i = 0; i < up.consumers.size(); ++i) {
+    if (up.consumer_fifo[i]) continue;
+    Vertex& cv = g->verts[up.consumers[i]];
+    if (cv.state != V_COMPLETED) { cv.pending_inputs++; if (cv.state == V_READY || (cv.state == V_RUNNING && cv.running.empty())) cv.state = V_WAITING; }
+  }
+}
+
+int add_edges(GM* g, const Conn& c) {
+  Stage& S = g->stages[c.src]; Stage& Dd = g->stages[c.dst];
+  const bool fifo = c.channel != 0;
+  auto edge = [&](int sp, int dp) {
+    Vertex& sv = g->verts[S.vids[sp]]; Vertex& dv = g->verts[Dd.vids[dp]];
+    dv.inputs.push_back(sv.id); dv.input_fifo.push_back(fifo); sv.consumers.push_back(dv.id); sv.consumer_fifo.push_back(fifo);
+    if (!fifo && sv.state != V_COMPLETED) dv.pending_inputs++;
+  };
+  if (c.kind == 1) { for (int a = 0; a < S.nparts; ++a) for (int b = 0; b < Dd.nparts; ++b) edge(a, b); }
+  else if (S.nparts == Dd.nparts) { for (int i = 0; i < S.nparts; ++i) edge(i, i); }
+  else if (S.nparts == 1) { for (int b = 0; b < Dd.nparts; ++b) edge(0, b); }
+  else if (Dd.nparts == 1) { for (int a = 0; a < S.nparts; ++a) edge(a, 0); }
+  else if (S.nparts % Dd.nparts == 0) { int f = S.nparts / Dd.nparts; for (int a = 0; a < S.nparts; ++a) edge(a, a / f); }
+  else if (Dd.nparts % S.nparts == 0) { int f = Dd.nparts / S.nparts; for (int b = 0; b < Dd.nparts; ++b) edge(b / f, b); }
+  else return -2;               // widths that do not divide cannot be connected pointwise
+  return 0;
+}
+
+void new_vertices(GM* g, int stage, int nparts) {
+  Stage& s = g->stages[stage];
+  s.vids.clear(); s.nparts = nparts;
+  for (int p = 0; p < nparts; ++p) {
+    Vertex v; v.id = (int)g->verts.size(); v.stage = stage; v.part = p;
+    g->verts.push_back(v); s.vids.push_back(v.id); g->live++;
+  }
+}
+
+// Connected components over streamed edges = start cliques.
+void build_cliques(GM* g) {
+  std::vector<int> parent(g->verts.size());
+  for (size_t i = 0; i < parent.size(); ++i) parent[i] = (int)i;
+  auto find = [&](int x) { while (parent[x] != x) { parent[x] = parent[parent[x]]; x = parent[x]; } return x; };
+  for (auto& v : g->verts) {
+    if (v.removed) continue;
+    for (size_t i = 0; i < v.inputs.size(); ++i) if (v.input_fifo[i] && !g->verts[v.inputs[i]].removed) parent[find(v.id)] = find(v.inputs[i]);
+  }
+  std::map<int, std::vector<int>> comp;
+  for (auto& v : g->verts) if (!v.removed) comp[find(v.id)].push_back(v.id);
+  g->cliques.clear();
+  for (auto& v : g->verts) v.clique = -1;
+  for (auto& kv : comp) {
+    if (kv.second.size() < 2) continue;
+    for (int id : kv.second) g->verts[id].clique = (int)g->cliques.size();
+    g->cliques.push_back(kv.second);
+  }
 }
 
 // Robust fit time = a + b*bytes: least squares over random subsamples, keep the fit with the
@@ -131,7 +220,7 @@ double outlier_threshold(const GM* g, const Stage& s, double bytes) {
 }
 
 void check_done(GM* g) {
-  if (g->jstate == J_RUNNING && g->completed == (int)g->verts.size()) g->jstate = J_SUCCEEDED;
+  if (g->jstate == J_RUNNING && g->completed == g->live) g->jstate = J_SUCCEEDED;
 }
 
 }  // namespace
@@ -155,41 +244,105 @@ void gm_set_outlier_params(void* h, double default_s, double min_s, double nonpa
 int gm_add_stage(void* h, const char* name, int nparts) {
   GM* g = (GM*)h;
   std::lock_guard<std::mutex> l(g->mu);
-  Stage s; s.name = name ? name : ""; s.nparts = nparts; s.first_vertex = (int)g->verts.size();
-  for (int p = 0; p < nparts; ++p) {
-    Vertex v; v.id = (int)g->verts.size(); v.stage = (int)g->stages.size(); v.part = p;
-    g->verts.push_back(v);
-  }
+  Stage s; s.name = name ? name : ""; s.nparts = nparts;
   g->stages.push_back(s);
+  new_vertices(g, (int)g->stages.size() - 1, nparts);
   return (int)g->stages.size() - 1;
 }
 
-// kind 0 = pointwise (N:N, 1:N broadcast, N:1 gather), 1 = cross product (every src -> every dst).
-int gm_connect(void* h, int src_stage, int dst_stage, int kind) {
+// kind 0 = pointwise (N:N, 1:N broadcast, N:1 gather, k*N:N / N:k*N grouped), 1 = cross product
+// (every src -> every dst).  channel 0 = file (the producer's output persists), 1 = FIFO / pipe
+// (streamed: producer and consumer belong to one start clique).
+int gm_connect_ex(void* h, int src_stage, int dst_stage, int kind, int channel) {
   GM* g = (GM*)h;
   std::lock_guard<std::mutex> l(g->mu);
   if (src_stage < 0 || dst_stage < 0 || src_stage >= (int)g->stages.size() || dst_stage >= (int)g->stages.size()) return -1;
-  Stage& S = g->stages[src_stage]; Stage& Dd = g->stages[dst_stage];
-  auto edge = [&](int s, int d) {
-    Vertex& sv = g->verts[S.first_vertex + s]; Vertex& dv = g->verts[Dd.first_vertex + d];
-    dv.inputs.push_back(sv.id); sv.consumers.push_back(dv.id); dv.pending_inputs++;
-  };
-  if (kind == 1) { for (int s = 0; s < S.nparts; ++s) for (int d = 0; d < Dd.nparts; ++d) edge(s, d); }
-  else if (S.nparts == Dd.nparts) { for (int i = 0; i < S.nparts; ++i) edge(i, i); }
-  else if (S.nparts == 1) { for (int d = 0; d < Dd.nparts; ++d) edge(0, d); }
-  else if (Dd.nparts == 1) { for (int s = 0; s < S.nparts; ++s) edge(s, 0); }
-  else if (S.nparts % Dd.nparts == 0) { int gsz = S.nparts / Dd.nparts; for (int s = 0; s < S.nparts; ++s) edge(s, s / gsz); }
-  else return -2;
-  return 0;
+  Conn c{src_stage, dst_stage, kind, channel};
+  int rc = add_edges(g, c);
+  if (rc == 0) g->conns.push_back(c);
+  return rc;
 }
+int gm_connect(void* h, int src_stage, int dst_stage, int kind) { return gm_connect_ex(h, src_stage, dst_stage, kind, 0); }
 
 int gm_start(void* h) {
   GM* g = (GM*)h;
   std::lock_guard<std::mutex> l(g->mu);
   if (g->jstate != J_NOT_STARTED) return -1;
-  g->jstate = g->verts.empty() ? J_SUCCEEDED : J_RUNNING;
+  g->jstate = g->live == 0 ? J_SUCCEEDED : J_RUNNING;
+  build_cliques(g);
   for (auto& v : g->verts) make_ready_if_possible(g, v);
   return 0;
+}
+
+// Dynamic resize of a stage that has not started (DrDynamicDistributionManager changes the width
+// of a consumer stage once its producers' sizes are known).  With `follow` != 0 the new width is
+// propagated to the pointwise stages downstream that had the same width (DrPipelineSplitManager;
+// stages fed by other, narrower inputs keep those as re-broadcast side inputs = the semi variant).
+// Returns the number of stages resized, or -1 if a vertex of an affected stage already started.
+int gm_resize_stage(void* h, int stage, int new_parts, int follow) {
+  GM* g = (GM*)h;
+  std::lock_guard<std::mutex> l(g->mu);
+  if (stage < 0 || stage >= (int)g->stages.size() || new_parts < 1) return -1;
+  std::vector<int> todo{stage};
+  const int old_parts = g->stages[stage].nparts;
+  if (follow)
+    for (size_t k = 0; k < todo.size(); ++k)
+      for (auto& c : g->conns)
+        if (c.src == todo[k] && c.kind == 0 && g->stages[c.dst].nparts == old_parts &&
+            std::find(todo.begin(), todo.end(), c.dst) == todo.end()) todo.push_back(c.dst);
+  for (int st : todo)
+    for (int id : g->stages[st].vids) { const Vertex& v = g->verts[id]; if (v.state != V_WAITING && v.state != V_READY) return -1; }
+  auto affected = [&](int st) { return std::find(todo.begin(), todo.end(), st) != todo.end(); };
+  // drop every edge that touches a resized stage, retire its vertices, create the new ones
+  for (auto& v : g->verts) {
+    if (v.removed) continue;
+    const bool mine = affected(v.stage);
+    std::vector<int> in2; std::vector<uint8_t> inf2; int pend = 0;
+    for (size_t i = 0; i < v.inputs.size(); ++i) {
+      const Vertex& up = g->verts[v.inputs[i]];
+      if (mine || affected(up.stage)) continue;
+      in2.push_back(v.inputs[i]); inf2.push_back(v.input_fifo[i]);
+      if (!v.input_fifo[i] && up.state != V_COMPLETED) ++pend;
+    }
+    std::vector<int> c2; std::vector<uint8_t> cf2;
+    for (size_t i = 0; i < v.consumers.size(); ++i) {
+      if (mine || affected(g->verts[v.consumers[i]].stage)) continue;
+      c2.push_back(v.consumers[i]); cf2.push_back(v.consumer_fifo[i]);
+    }
+    v.inputs.swap(in2); v.input_fifo.swap(inf2); v.consumers.swap(c2); v.consumer_fifo.swap(cf2);
+    if (v.state == V_WAITING || v.state == V_READY) { v.pending_inputs = pend; v.state = V_WAITING; }
+  }
+  for (int st : todo) {
+    for (int id : g->stages[st].vids) { g->verts[id].removed = true; g->live--; }
+    new_vertices(g, st, new_parts);
+  }
+  int bad = 0;
+  for (auto& c : g->conns) if ((affected(c.src) || affected(c.dst)) && add_edges(g, c) != 0) bad = 1;
+  if (bad) { g->jstate = J_FAILED; g->error = "dynamic resize produced widths that cannot be connected pointwise"; return -2; }
+  if (g->jstate == J_RUNNING) {
+    build_cliques(g);
+    for (auto& v : g->verts) make_ready_if_possible(g, v);
+  }
+  return (int)todo.size();
+}
+
+int gm_stage_vertices(void* h, int stage, int* out, int cap) {
+  GM* g = (GM*)h; std::lock_guard<std::mutex> l(g->mu);
+  if (stage < 0 || stage >= (int)g->stages.size()) return -1;
+  const Stage& s = g->stages[stage];
+  for (int i = 0; i < (int)s.vids.size() && i < cap; ++i) out[i] = s.vids[i];
+  return (int)s.vids.size();
+}
+
+// Start clique of a vertex: returns its size (1 = starts alone) and writes up to cap member ids.
+int gm_vertex_clique(void* h, int vertex, int* out, int cap) {
+  GM* g = (GM*)h; std::lock_guard<std::mutex> l(g->mu);
+  if (vertex < 0 || vertex >= (int)g->verts.size()) return -1;
+  const Vertex& v = g->verts[vertex];
+  if (v.clique < 0) { if (cap > 0) out[0] = vertex; return 1; }
+  const std::vector<int>& m = g->cliques[v.clique];
+  for (int i = 0; i < (int)m.size() && i < cap; ++i) out[i] = m[i];
+  return (int)m.size();
 }
 
 // Next vertex attempt to launch: a READY vertex, or a RUNNING vertex with a duplicate request.
@@ -199,6 +352,7 @@ int gm_next_ready(void* h, double now, int* vertex, int* version) {
   std::lock_guard<std::mutex> l(g->mu);
   if (g->jstate != J_RUNNING) return -1;
   for (auto& v : g->verts) {
+    if (v.removed) continue;
     bool dup = v.state == V_RUNNING && v.duplicate_requested && (int)v.running.size() < g->max_running_versions;
     if (v.state == V_READY || dup) {
       Attempt a; a.version = v.next_version++; a.start = now;
@@ -231,7 +385,11 @@ int gm_report_completed(void* h, int vertex, int version, double seconds, double
   if (s.completed * 2 >= s.nparts && (s.completed == (s.nparts + 1) / 2 || (s.completed * 20) % std::max(1, s.nparts) == 0 || s.completed == s.nparts))
     refit(s);
   g->completed++;
-  for (int c : v.consumers) { Vertex& cv = g->verts[c]; if (cv.pending_inputs > 0) cv.pending_inputs--; make_ready_if_possible(g, cv); }
+  for (size_t i = 0; i < v.consumers.size(); ++i) {
+    Vertex& cv = g->verts[v.consumers[i]];
+    if (!v.consumer_fifo[i] && cv.pending_inputs > 0) cv.pending_inputs--;
+    make_ready_if_possible(g, cv);
+  }
   check_done(g);
   return 1;
 }
@@ -255,14 +413,7 @@ int gm_report_failed(void* h, int vertex, int version, int bad_input, const char
       g->jstate = J_FAILED; g->error = std::string("input unreadable too many times: ") + (message ? message : "");
       return 1;
     }
-    if (up.state == V_COMPLETED) {
-      up.state = V_READY; up.completed_version = -1; g->completed--; g->stages[up.stage].completed--;
-      g->invalidations++;
-      for (int c : up.consumers) {                  // consumers that have not completed wait again
-        Vertex& cv = g->verts[c];
-        if (cv.state != V_COMPLETED) { cv.pending_inputs++; if (cv.state == V_READY || (cv.state == V_RUNNING && cv.running.empty())) cv.state = V_WAITING; }
-      }
-    }
+    if (up.state == V_COMPLETED) { revoke(g, up); make_ready_if_possible(g, up); }
     if (v.running.empty()) v.state = V_WAITING;
     make_ready_if_possible(g, v);
     return 2;
@@ -273,6 +424,22 @@ int gm_report_failed(void* h, int vertex, int version, int bad_input, const char
     g->error = std::string("vertex ") + g->stages[v.stage].name + "[" + std::to_string(v.part) + "] failed " +
                std::to_string(v.failures) + " times: " + (message ? message : "");
     return 1;
+  }
+  if (v.clique >= 0) {
+    // gang semantics: a streamed edge keeps nothing to re-read, so every member that has not
+    // finished restarts, and finished members whose streamed consumer has not finished run again
+    g->gang_restarts++;
+    for (int id : g->cliques[v.clique]) {
+      Vertex& o = g->verts[id];
+      if (o.state == V_COMPLETED) {
+        bool needed = false;
+        for (size_t i = 0; i < o.consumers.size(); ++i)
+          if (o.consumer_fifo[i] && g->verts[o.consumers[i]].state != V_COMPLETED) needed = true;
+        if (needed) revoke(g, o);
+      } else { o.running.clear(); o.duplicate_requested = false; o.state = V_WAITING; }
+    }
+    make_ready_if_possible(g, v);
+    return 0;
   }
   if (v.running.empty()) { v.state = V_WAITING; make_ready_if_possible(g, v); }
   return 0;
@@ -286,6 +453,7 @@ int gm_check_duplicates(void* h, double now) {
   if (!g->speculative || g->jstate != J_RUNNING) return 0;
   int n = 0;
   for (auto& v : g->verts) {
+    if (v.removed || v.clique >= 0) continue;        // gang members are never duplicated alone
     if (v.state != V_RUNNING || v.running.empty() || v.duplicate_requested) continue;
     if ((int)v.running.size() >= g->max_running_versions) continue;
     double thr = outlier_threshold(g, g->stages[v.stage], v.bytes_in);
@@ -297,11 +465,13 @@ int gm_check_duplicates(void* h, double now) {
 
 int gm_job_state(void* h) { GM* g = (GM*)h; std::lock_guard<std::mutex> l(g->mu); return g->jstate; }
 int gm_vertex_count(void* h) { GM* g = (GM*)h; std::lock_guard<std::mutex> l(g->mu); return (int)g->verts.size(); }
+int gm_live_vertex_count(void* h) { GM* g = (GM*)h; std::lock_guard<std::mutex> l(g->mu); return g->live; }
+int gm_gang_restarts(void* h) { GM* g = (GM*)h; std::lock_guard<std::mutex> l(g->mu); return g->gang_restarts; }
 int gm_vertex_info(void* h, int vertex, int* stage, int* part, int* state, int* completed_version, int* failures) {
   GM* g = (GM*)h; std::lock_guard<std::mutex> l(g->mu);
   if (vertex < 0 || vertex >= (int)g->verts.size()) return -1;
   Vertex& v = g->verts[vertex];
-  *stage = v.stage; *part = v.part; *state = v.state; *completed_version = v.completed_version; *failures = v.failures;
+  *stage = v.stage; *part = v.part; *state = v.removed ? 5 : v.state; *completed_version = v.completed_version; *failures = v.failures;
   return 0;
 }
 int gm_counters(void* h, int* completed, int* failures, int* duplicates, int* invalidations) {
@@ -353,6 +523,17 @@ int dyn_consumer_count(int64_t total_bytes, int64_t data_per_vertex, int min_cou
   if (c < min_count) c = min_count;
   if (c > max_count) c = max_count;
   return (int)c;
+}
+
+// Range distributor sizing (DrDynamicRangeDistributor): the producers are SAMPLERS, so the data
+// volume is estimated as sample bytes / sampling rate; the resulting consumer count is also handed
+// to the bucketizer as its partition-count argument.
+int dyn_range_consumer_count(int64_t sample_bytes, double sampling_rate, int64_t data_per_vertex,
+                             int min_count, int max_count) {
+  if (sampling_rate <= 0) sampling_rate = 0.001;
+  double est = (double)sample_bytes / sampling_rate;
+  if (est > 9.0e18) est = 9.0e18;
+  return dyn_consumer_count((int64_t)est, data_per_vertex, min_count, max_count);
 }
 
 // Broadcast tree (DrDynamicBroadcast.cpp:125-130): >= 5 consumers get floor(sqrt(n)) copy vertices;

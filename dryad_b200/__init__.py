@@ -9,7 +9,7 @@ from .api.decomposable import IAssociative, IDecomposable, associative, decompos
 from .api.errors import DryadLinqException, ErrorCategory, ErrorCode
 from .api.query import KeyedMultiQuery, MultiQuery, Query
 from .api.rows import RowKey
-from .api.types import AggregateValue, ForkTuple, Grouping, LineRecord, Pair, Record
+from .api.types import AggregateValue, ForkTuple, ForkValue, Grouping, LineRecord, Pair, Record
 from .expr import col, lit, where
 
 __version__ = "0.2.1b200"
@@ -17,5 +17,5 @@ __all__ = [
     "DryadLinqContext", "DryadLinqJobInfo", "JobStatus", "PlatformKind", "QueryLoggingLevel", "CompressionScheme",
     "Table", "IDecomposable", "IAssociative", "decomposable", "associative", "resource", "DryadLinqException",
     "ErrorCode", "ErrorCategory", "Query", "MultiQuery", "KeyedMultiQuery", "Record", "Pair", "LineRecord",
-    "RowKey", "ForkTuple", "Grouping", "AggregateValue", "col", "lit", "where",
+    "RowKey", "ForkTuple", "ForkValue", "Grouping", "AggregateValue", "col", "lit", "where",
 ]

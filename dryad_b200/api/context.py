@@ -373,6 +373,7 @@ class DryadLinqContext:
                 else:
                     ex = JobExecutor(self, plan)
                 tables = ex.run()
+                self.last_executor = ex
                 self.last_job_stats = ex.stats
                 self.last_plan = plan
             job.results = []

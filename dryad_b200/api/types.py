@@ -80,3 +80,44 @@ class AggregateValue:
 
 
 __all__ = ["Record", "Pair", "LineRecord", "ForkTuple", "AggregateValue", "Grouping"]
+
+
+class ForkValue:
+    """An element that may carry no value — the single-output sibling of ForkTuple
+    (`ForkValue<T>`, LinqToDryad/ForkTuple.cs:32-110): `has_value` is false for a default
+    instance, assigning `value` makes it valid; equal when both are empty or both values match;
+    an empty instance hashes to 0."""
+
+    __slots__ = ("_x", "_has")
+
+    def __init__(self, *x):
+        if len(x) > 1:
+            raise TypeError("ForkValue takes at most one value")
+        self._has = bool(x)
+        self._x = x[0] if x else None
+
+    @property
+    def has_value(self) -> bool:
+        return self._has
+
+    @property
+    def value(self):
+        return self._x
+
+    @value.setter
+    def value(self, v):
+        self._x, self._has = v, True
+
+    HasValue = has_value
+    Value = value
+
+    def __eq__(self, o):
+        if not isinstance(o, ForkValue):
+            return NotImplemented
+        return (not self._has and not o._has) or (self._has and o._has and self._x == o._x)
+
+    def __hash__(self):
+        return hash(self._x) if self._has else 0
+
+    def __repr__(self):
+        return f"ForkValue({self._x!r})" if self._has else "ForkValue()"

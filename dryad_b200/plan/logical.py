@@ -16,6 +16,19 @@ _ids = itertools.count(1)
 Schema = Optional[Dict[str, str]]   # column name -> kind ('i','f','b','o'); None = opaque objects
 
 
+def _records_out(fn: Callable) -> Callable:
+    """A lambda that builds `{...}` (the anonymous-type idiom, `new { k, v }` in the reference's C#)
+    yields Records — dicts with attribute access — so later lambdas can write `r.k`."""
+    from ..api.types import Record
+
+    def wrapped(*a):
+        out = fn(*a)
+        return Record(out) if type(out) is dict else out
+    wrapped.__name__ = getattr(fn, "__name__", "λ")
+    wrapped.__wrapped__ = fn
+    return wrapped
+
+
 class Lam:
     """A user lambda plus its traced form.  `ir` is an Expr (scalar result), a dict of Exprs
     (record construction) or None (opaque Python: host path only)."""
@@ -30,7 +43,7 @@ class Lam:
         ir = None
         if schema is not None and nargs == 1 and all(k != "o" for k in schema.values()):
             ir = X.trace(fn, schema)
-        return Lam(fn, ir, nargs)
+        return Lam(_records_out(fn), ir, nargs, name=getattr(fn, "__name__", "λ"))
 
     @property
     def is_traced(self) -> bool:

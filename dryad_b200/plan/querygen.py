@@ -577,6 +577,30 @@ class QueryGen:
                     and n.children[0][0].partition_count == n.partition_count and n.params.get("sort_key") is None:
                 self._splice_out(n)
 
+        self._assign_fifo_channels()
+
+    def _assign_fifo_channels(self):
+        """StaticConfig.UseMemoryFIFO: the inputs of multi-input vertices (Join, set operations,
+        multi-source Apply) stream through in-memory FIFOs instead of files, unless the child is
+        an input table, is forked, has one partition, or both ends are stateful
+        (LinqToDryad/DryadLinqQueryNode.cs:2094-2107, 3225-3238, 4245-4258).  A FIFO edge puts
+        producer and consumer into one start clique of the graph manager."""
+        from . import static_config
+        from .qnodes import ChannelType
+        if not static_config.USE_MEMORY_FIFO:
+            return
+        multi = (NodeType.Join, NodeType.GroupJoin, NodeType.SetOperation, NodeType.Apply)
+        for n in self._all_nodes():
+            head = n.members[0].type if n.type == NodeType.Super and n.members else n.type
+            if head not in multi or len(n.children) < 2:
+                continue
+            stateful = n.is_stateful
+            for child, _ in n.children:
+                if child.type != NodeType.InputTable and not child.is_forked and child.partition_count > 1 \
+                        and not (stateful and child.is_stateful):
+                    child.channel_type = ChannelType.MemoryFIFO
+                stateful = stateful or child.is_stateful
+
     def _splice_out(self, n: DLinqQueryNode):
         child, _ = n.children[0]
         child.parents = [x for x in child.parents if x is not n]

@@ -112,14 +112,19 @@ def parse_query_xml(xml_text: str) -> QueryPlan:
     return q
 
 
-def to_graph_manager(plan: QueryPlan, max_failures: int = 6):
+def to_graph_manager(plan: QueryPlan, max_failures: int = 6, app=None):
     """Build the native graph manager's stage graph from a parsed plan file (GraphBuilder role,
-    DryadLinqGraphManager/GraphBuilder.cs:564-748)."""
-    from ..sched.gm import CROSS_PRODUCT, POINTWISE, GraphManager
+    DryadLinqGraphManager/GraphBuilder.cs:564-748).  Edge channel types follow the child's
+    <ChannelType> (DISKFILE -> file edge, MEMORYFIFO / TCPPIPE -> streamed edge = start clique,
+    GraphBuilder.cs:508-562).  `app` (sched.app.DryadLinqApp) receives the plan-vertex -> stage
+    identity map."""
+    from ..sched.gm import CHANNEL_FIFO, CHANNEL_FILE, CROSS_PRODUCT, POINTWISE, GraphManager
     gm = GraphManager(max_failures=max_failures, speculative=plan.enable_speculative_duplication)
     sid = {}
     for v in plan.topological():
         sid[v.unique_id] = gm.add_stage(f"{v.name}#{v.unique_id}", v.partitions)
+        if app is not None:
+            app.record_identity(v.unique_id, sid[v.unique_id], v.name)
     for v in plan.topological():
         for p in v.children:
             child = plan.vertices[p.unique_id]
@@ -127,5 +132,7 @@ def to_graph_manager(plan: QueryPlan, max_failures: int = 6):
             if kind == POINTWISE and not (child.partitions == v.partitions or child.partitions == 1 or v.partitions == 1
                                           or (v.partitions and child.partitions % v.partitions == 0)):
                 kind = CROSS_PRODUCT
-            gm.connect(sid[p.unique_id], sid[v.unique_id], kind)
+            streamed = kind == POINTWISE and child.partitions == v.partitions and \
+                child.channel_type.upper() in ("MEMORYFIFO", "TCPPIPE")
+            gm.connect(sid[p.unique_id], sid[v.unique_id], kind, CHANNEL_FIFO if streamed else CHANNEL_FILE)
     return gm, sid

@@ -112,7 +112,7 @@ class JobExecutor:
     def _build_gm(self):
         """Mirror the physical plan into the native graph manager: one GM stage per plan node, one
         GM vertex per partition, edges expanded by the same connection rules the data follows."""
-        from ..sched.gm import CROSS_PRODUCT, POINTWISE, GraphManager
+        from ..sched.gm import CHANNEL_FIFO, CHANNEL_FILE, CROSS_PRODUCT, POINTWISE, GraphManager
         ctx = self.context
         gm = GraphManager(max_failures=ctx.max_failures_per_vertex, speculative=ctx.enable_speculative_duplication)
         sid = {}
@@ -127,7 +127,9 @@ class JobExecutor:
                 cpc, pc = child.partition_count, node.partition_count
                 conservative = head in special or not (cpc == pc or cpc == 1 or pc == 1 or (pc and cpc % pc == 0))
                 kind = CROSS_PRODUCT if (op == ConnOp.CrossProduct or conservative) else POINTWISE
-                gm.connect(sid[child.uid], sid[node.uid], kind)
+                # a MemoryFIFO edge streams: producer and consumer vertices form one start clique
+                fifo = kind == POINTWISE and cpc == pc and getattr(child.channel_type, "value", "") == "MemoryFIFO"
+                gm.connect(sid[child.uid], sid[node.uid], kind, CHANNEL_FIFO if fifo else CHANNEL_FILE)
                 for d in range(pc):                      # same expansion order as gm_connect
                     lst = self._gm_inputs.setdefault(first + d, [])
                     if kind == CROSS_PRODUCT:

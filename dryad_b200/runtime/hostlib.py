@@ -62,6 +62,12 @@ _d("gm_destroy", None, [P])
 _d("gm_set_outlier_params", None, [P, c_double, c_double, c_double])
 _d("gm_add_stage", c_int, [P, c_char_p, c_int])
 _d("gm_connect", c_int, [P, c_int, c_int, c_int])
+_d("gm_connect_ex", c_int, [P, c_int, c_int, c_int, c_int])
+_d("gm_resize_stage", c_int, [P, c_int, c_int, c_int])
+_d("gm_stage_vertices", c_int, [P, c_int, C.POINTER(c_int), c_int])
+_d("gm_vertex_clique", c_int, [P, c_int, C.POINTER(c_int), c_int])
+_d("gm_live_vertex_count", c_int, [P])
+_d("gm_gang_restarts", c_int, [P])
 _d("gm_start", c_int, [P])
 _d("gm_next_ready", c_int, [P, c_double, C.POINTER(c_int), C.POINTER(c_int)])
 _d("gm_report_completed", c_int, [P, c_int, c_int, c_double, c_double])
@@ -77,6 +83,7 @@ _d("dyn_aggregate_groups", c_int, [c_int, C.POINTER(c_int64), C.POINTER(c_int32)
                                    c_int64, C.POINTER(c_int32)])
 _d("dyn_consumer_count", c_int, [c_int64, c_int64, c_int, c_int])
 _d("dyn_broadcast_tree", c_int, [c_int, C.POINTER(c_int32)])
+_d("dyn_range_consumer_count", c_int, [c_int64, c_double, c_int64, c_int, c_int])
 PUMP_HANDLER = C.CFUNCTYPE(None, c_int64, c_int64, P)
 _d("pump_create", P, [c_int, PUMP_HANDLER, P])
 _d("pump_post", None, [P, c_int64, c_int64, c_double])

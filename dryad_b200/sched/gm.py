@@ -9,8 +9,9 @@ from typing import List, Optional, Tuple
 from .. import _native as N
 
 JOB_STATES = {0: "NotStarted", 1: "Running", 2: "Stopping", 3: "Succeeded", 4: "Failed"}
-VERTEX_STATES = {0: "Waiting", 1: "Ready", 2: "Running", 3: "Completed", 4: "Failed"}
+VERTEX_STATES = {0: "Waiting", 1: "Ready", 2: "Running", 3: "Completed", 4: "Failed", 5: "Removed"}
 POINTWISE, CROSS_PRODUCT = 0, 1
+CHANNEL_FILE, CHANNEL_FIFO = 0, 1
 
 
 class GraphManager:
@@ -37,10 +38,42 @@ class GraphManager:
         self._nverts += nparts
         return sid
 
-    def connect(self, src: int, dst: int, kind: int = POINTWISE) -> None:
-        rc = self.lib.gm_connect(self.h, src, dst, kind)
+    def connect(self, src: int, dst: int, kind: int = POINTWISE, channel: int = CHANNEL_FILE) -> None:
+        """channel=CHANNEL_FIFO streams the edge: producer and consumer vertices form a start clique
+        (gang start / gang restart, GraphManager/vertex/DrClique.h:28-64)."""
+        rc = self.lib.gm_connect_ex(self.h, src, dst, kind, channel)
         if rc:
             raise ValueError(f"cannot connect stage {src} -> {dst} (rc {rc})")
+
+    def resize_stage(self, stage: int, new_parts: int, follow: bool = True) -> int:
+        """Change the width of a stage that has not started (dynamic distributor); with `follow`
+        the pointwise stages downstream of equal width are resized with it
+        (DrPipelineSplitManager / DrSemiPipelineSplitManager).  Returns the number of stages resized."""
+        rc = self.lib.gm_resize_stage(self.h, stage, new_parts, int(follow))
+        if rc < 0:
+            raise ValueError(f"stage {stage} cannot be resized to {new_parts} (rc {rc})")
+        return rc
+
+    def stage_vertices(self, stage: int) -> List[int]:
+        n = self.lib.gm_stage_vertices(self.h, stage, None, 0)
+        out = (C.c_int * max(n, 1))()
+        self.lib.gm_stage_vertices(self.h, stage, out, n)
+        return list(out)[:n]
+
+    def clique(self, vertex: int) -> List[int]:
+        """Members of the vertex's start clique ([vertex] when it starts alone)."""
+        n = self.lib.gm_vertex_clique(self.h, vertex, None, 0)
+        out = (C.c_int * max(n, 1))()
+        self.lib.gm_vertex_clique(self.h, vertex, out, n)
+        return list(out)[:n]
+
+    @property
+    def live_vertices(self) -> int:
+        return self.lib.gm_live_vertex_count(self.h)
+
+    @property
+    def gang_restarts(self) -> int:
+        return self.lib.gm_gang_restarts(self.h)
 
     def set_outlier_params(self, default_s: float = 600.0, min_s: float = 10.0, nonparam_fraction: float = 0.5):
         self.lib.gm_set_outlier_params(self.h, default_s, min_s, nonparam_fraction)
@@ -102,6 +135,13 @@ def aggregate_groups(bytes_: List[int], machine: List[int], pod: List[int], max_
 
 def consumer_count(total_bytes: int, data_per_vertex: int = 1 << 30, lo: int = 1, hi: int = 20000) -> int:
     return N.host().dyn_consumer_count(total_bytes, data_per_vertex, lo, hi)
+
+
+def range_consumer_count(sample_bytes: int, sampling_rate: float = 0.001, data_per_vertex: int = 1 << 30,
+                         lo: int = 1, hi: int = 20000) -> int:
+    """Consumers of a dynamic range distributor: data volume = sample volume / sampling rate
+    (GraphManager/stagemanager/DrDynamicRangeDistributor.h:22-78)."""
+    return N.host().dyn_range_consumer_count(sample_bytes, sampling_rate, data_per_vertex, lo, hi)
 
 
 def broadcast_tree(consumers: int) -> Tuple[int, List[int]]:

@@ -51,6 +51,16 @@ void gm_destroy(void* h);
 void gm_set_outlier_params(void* h, double default_s, double min_s, double nonparam_fraction);
 int gm_add_stage(void* h, const char* name, int nparts);
 int gm_connect(void* h, int src_stage, int dst_stage, int kind);      /* 0 pointwise, 1 cross product */
+/* channel 0 = file (output persists), 1 = FIFO / pipe: producer and consumer form a start clique
+ * (DrClique): they become runnable together and restart together. */
+int gm_connect_ex(void* h, int src_stage, int dst_stage, int kind, int channel);
+/* Dynamic resize of a not-yet-started stage; follow != 0 propagates the new width to the pointwise
+ * stages downstream of equal width (DrPipelineSplitManager).  Returns stages resized or < 0. */
+int gm_resize_stage(void* h, int stage, int new_parts, int follow);
+int gm_stage_vertices(void* h, int stage, int* out, int cap);
+int gm_vertex_clique(void* h, int vertex, int* out, int cap);
+int gm_live_vertex_count(void* h);
+int gm_gang_restarts(void* h);
 int gm_start(void* h);
 int gm_next_ready(void* h, double now, int* vertex, int* version);
 int gm_report_completed(void* h, int vertex, int version, double seconds, double bytes_in);
@@ -67,6 +77,9 @@ int dyn_aggregate_groups(int n, const int64_t* bytes, const int32_t* machine, co
                          int max_inputs, int64_t max_bytes, int64_t skip_bytes, int32_t* group_out);
 int dyn_consumer_count(int64_t total_bytes, int64_t data_per_vertex, int min_count, int max_count);
 int dyn_broadcast_tree(int consumers, int32_t* copy_of);
+/* DrDynamicRangeDistributor: consumers from sample volume / sampling rate. */
+int dyn_range_consumer_count(int64_t sample_bytes, double sampling_rate, int64_t data_per_vertex,
+                             int min_count, int max_count);
 
 /* ---- message pump: GraphManager/kernel/DrMessagePump.h ------------------------------------------ */
 typedef void (*dh_pump_handler)(int64_t listener, int64_t message, void* user);

@@ -103,3 +103,26 @@ def test_event_log_plan_files_and_report(tmp_path):
     names = [s["name"] for s in job["stages"]]
     assert any("HashPartition" in n for n in names) and job["success"]
     assert jobreport.main([jd]) == 0
+
+
+def test_memory_fifo_channels_form_start_cliques_and_results_are_unchanged(monkeypatch):
+    """StaticConfig.UseMemoryFIFO streams the inputs of a Join: those edges are FIFO in the plan
+    and the graph manager starts producer and consumer as one clique; the query result is the same."""
+    import dryad_b200 as D
+    from dryad_b200.plan import static_config
+    left = [{"k": i % 50, "a": i} for i in range(400)]
+    right = [{"k": i, "b": i * 3} for i in range(50)]
+
+    def run(ctx):
+        l = ctx.from_enumerable(left, 4).select(lambda r: {"k": r.k, "a": r.a + 1}).hash_partition(lambda r: r.k, 4)
+        r = ctx.from_enumerable(right, 4).select(lambda r: {"k": r.k, "b": r.b}).hash_partition(lambda r: r.k, 4)
+        return l.join(r, lambda x: x.k, lambda y: y.k, lambda x, y: (x.k, x.a + y.b))
+
+    want = sorted(run(D.DryadLinqContext(1, local_debug=True)).to_list())
+    monkeypatch.setattr(static_config, "USE_MEMORY_FIFO", True)
+    ctx = D.DryadLinqContext(4)
+    q = run(ctx)
+    assert "MEMORYFIFO" in q.to_xml()
+    assert sorted(q.to_list()) == want
+    gm = ctx.last_executor.gm
+    assert any(len(gm.clique(v)) > 1 for v in range(gm.live_vertices))

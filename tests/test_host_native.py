@@ -283,3 +283,78 @@ def test_channel_factory_file_fifo_null(tmp_path):
     nw.write(1)
     nw.close()
     assert list(ChannelReader("null://x")) == []
+
+
+def _ready_all(g, now=0.0):
+    out = []
+    while True:
+        x = g.next_ready(now)
+        if not x:
+            return out
+        out.append(x)
+
+
+def test_start_cliques_gang_start_and_gang_restart():
+    """Vertices joined by FIFO edges start together and restart together
+    (GraphManager/vertex/DrClique.h:28-64, DrCohort.cpp:852-929)."""
+    from dryad_b200.sched.gm import CHANNEL_FIFO, GraphManager
+    g = GraphManager()
+    src, a, b, sink = g.add_stage("src", 2), g.add_stage("read", 2), g.add_stage("map", 2), g.add_stage("sink", 1)
+    g.connect(src, a, 0)                       # file edge: external input of the clique
+    g.connect(a, b, 0, CHANNEL_FIFO)           # streamed: read[i] and map[i] form a clique
+    g.connect(b, sink, 0)
+    g.start()
+    assert sorted(g.clique(2)) == [2, 4] and g.clique(6) == [6]
+    first = _ready_all(g)
+    assert sorted(v for v, _ in first) == [0, 1]            # clique members wait for their external inputs
+    g.completed(0, 0, 1.0, 10)
+    ready = _ready_all(g)
+    assert sorted(v for v, _ in ready) == [2, 4]            # both members of clique 0 at once, not clique 1
+    g.completed(1, 0, 1.0, 10)
+    assert sorted(v for v, _ in _ready_all(g)) == [3, 5]
+    # the consumer of clique 0 fails: the whole gang (2 and 4) runs again, clique 1 is untouched
+    assert g.failed(4, 0, "boom") == 0
+    assert g.gang_restarts == 1
+    again = _ready_all(g)
+    assert sorted(again) == [(2, 1), (4, 1)]
+    for v, ver in again + [(3, 0), (5, 0)]:
+        g.completed(v, ver, 1.0, 10)
+    (last,) = _ready_all(g)
+    g.completed(*last, 1.0, 1)
+    assert g.state == "Succeeded"
+
+
+def test_dynamic_resize_follows_pointwise_stages_and_range_distributor_sizing():
+    """DrDynamicRangeDistributor sizes the consumers from the sample volume; DrPipelineSplitManager
+    propagates the new width to the pointwise stages downstream."""
+    from dryad_b200.sched.gm import CROSS_PRODUCT, GraphManager, range_consumer_count
+    assert range_consumer_count(5 << 20, 0.001, 1 << 30) == 5          # 5 MiB of samples at 0.1 % = 5 GiB
+    assert range_consumer_count(0, 0.001, 1 << 30) == 1
+    g = GraphManager()
+    samp, dist, sort, out = (g.add_stage(n, 4) for n in ("sample", "distribute", "sort", "output"))
+    g.connect(samp, dist, 0)
+    g.connect(dist, sort, CROSS_PRODUCT)
+    g.connect(sort, out, 0)
+    g.start()
+    for v, ver in _ready_all(g):
+        g.completed(v, ver, 1.0, 100)
+    assert g.resize_stage(sort, 6) == 2                                 # sort and the pointwise output follow
+    assert len(g.stage_vertices(sort)) == 6 and len(g.stage_vertices(out)) == 6 and g.live_vertices == 4 + 4 + 6 + 6
+    for v, ver in _ready_all(g):                                            # the distributors
+        g.completed(v, ver, 1.0, 100)
+    sorts = _ready_all(g)
+    assert sorted(v for v, _ in sorts) == sorted(g.stage_vertices(sort))
+    for v, ver in sorts:
+        g.completed(v, ver, 1.0, 100)
+    for v, ver in _ready_all(g):
+        g.completed(v, ver, 1.0, 100)
+    assert g.state == "Succeeded"
+    # a started stage cannot be resized
+    g2 = GraphManager()
+    s0, s1 = g2.add_stage("a", 2), g2.add_stage("b", 2)
+    g2.connect(s0, s1, 0)
+    g2.start()
+    _ready_all(g2)
+    import pytest
+    with pytest.raises(ValueError):
+        g2.resize_stage(s0, 3)

@@ -91,3 +91,60 @@ def test_object_store_and_utils(tmp_path):
     bv.set(2)
     bv.set(70)
     assert bv[2] and bv[70] and not bv[3] and bv.count() == 2 and list(bv) == [2, 70]
+
+
+def test_graph_manager_app_options_identity_map_and_streamed_edges(tmp_path):
+    """DryadLINQApp option table (-mai/-mafi/-at/-nca), the <plan>.map identity file, and plan
+    edges whose child channel is MEMORYFIFO becoming start cliques in the graph manager."""
+    import pytest
+    from dryad_b200.plan import static_config
+    from dryad_b200.plan.xmlplan import parse_query_xml, to_graph_manager
+    from dryad_b200.sched.app import DryadLinqApp, parse_data_size
+    import dryad_b200 as D
+    assert parse_data_size("12KB") == 12 << 10 and parse_data_size("20.5mb") == int(20.5 * (1 << 20)) and parse_data_size("77") == 77
+    with pytest.raises(ValueError):
+        parse_data_size("1.5")
+    app = DryadLinqApp.parse(["-mai", "64", "--maxaggregatefilterinputs", "8", "-at", "256MB", "-nca", "-amd64", "plan.xml"])
+    assert (app.max_aggregate_inputs, app.max_aggregate_filter_inputs, app.aggregate_threshold, app.cluster_affinity) == (64, 8, 256 << 20, False)
+    assert app.positional == ["plan.xml"] and "-mai" in DryadLinqApp.usage()
+    with pytest.raises(ValueError):
+        DryadLinqApp.parse(["-bogus"])
+    # -nca: grouping ignores topology; the input cap applies
+    groups = app.aggregate_groups([10] * 20, machine=list(range(20)), pod=[i % 4 for i in range(20)], filtered=True)
+    assert max(groups) + 1 == 3 and all(groups.count(g) <= 8 for g in set(groups))
+    old = static_config.USE_MEMORY_FIFO
+    static_config.USE_MEMORY_FIFO = True
+    try:
+        ctx = D.DryadLinqContext(3)
+        a = ctx.from_enumerable(list(range(60)), 3).select(lambda x: x + 1).hash_partition(lambda x: x, 3)
+        b = ctx.from_enumerable(list(range(30)), 3).select(lambda x: x * 2).hash_partition(lambda x: x, 3)
+        xml = a.join(b, lambda x: x, lambda y: y, lambda x, y: x + y).to_xml()
+    finally:
+        static_config.USE_MEMORY_FIFO = old
+    plan = parse_query_xml(xml)
+    (tmp_path / "plan.xml").write_text(xml)
+    app.open_identity_map(str(tmp_path / "plan.xml"))
+    gm, sid = to_graph_manager(plan, app=app)
+    ident = DryadLinqApp.read_identity_map(tmp_path / "plan.xml.map")
+    assert {k: v[0] for k, v in ident.items()} == sid
+    gm.start()
+    assert any(len(gm.clique(v)) > 1 for v in range(gm.live_vertices))
+
+
+def test_fork_value_type_system_and_query_doc():
+    import xml.etree.ElementTree as ET
+    import dryad_b200 as D
+    from dryad_b200.plan import type_system as T
+    from dryad_b200.plan.query_doc import QueryDoc
+    e, v = D.ForkValue(), D.ForkValue(5)
+    assert not e.has_value and v.has_value and v.value == 5 and hash(e) == 0 and e == D.ForkValue() and v != e
+    e.value = 5
+    assert e == v and e.has_value
+    assert T.is_query_operator("GroupBy") and T.is_query_operator("select_many") and not T.is_query_operator("frobnicate")
+    assert T.is_identity_function(None) and T.is_identity_function(lambda x: x) and not T.is_identity_function(lambda x: x + 1)
+    assert T.is_anonymous_type({"a": 1}) and T.schema_of_record((1, 2.0)) == {"item1": "i", "item2": "f"}
+    assert T.kind_of_value(True) == "b" and T.kind_of_value(1 << 70) == "o"
+    assert any(p.endswith("type_system.py") for p in T.loaded_non_system_modules())
+    doc = QueryDoc("Query").element("ClusterName", "local").open("Vertex", {"id": 3}).cdata("Explain", "x => x < 3 && y ]]> 0").close("Vertex")
+    root = ET.fromstring(doc.to_string())
+    assert root.find("ClusterName").text == "local" and root.find("Vertex/Explain").text == "x => x < 3 && y ]]> 0"
