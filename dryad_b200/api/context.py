@@ -230,6 +230,10 @@ class DryadLinqContext:
         self._check_not_disposed()
         from ..runtime.columnar import ColumnBatch
         batch = ColumnBatch.from_columns(columns)
+        if self.world > 1:                    # SPMD: the columns are THIS rank's partition
+            sparts: List[Any] = [None] * self.world
+            sparts[self.rank] = batch
+            return self._from_table(Table(sparts, batch.schema, None, None, True))
         n = int(num_partitions) if num_partitions else 1
         parts = batch.split(n)
         return self._from_table(Table(parts, batch.schema, None, None, True))

@@ -19,7 +19,10 @@ Schema = Optional[Dict[str, str]]   # column name -> kind ('i','f','b','o'); Non
 def _records_out(fn: Callable) -> Callable:
     """A lambda that builds `{...}` (the anonymous-type idiom, `new { k, v }` in the reference's C#)
     yields Records — dicts with attribute access — so later lambdas can write `r.k`."""
+    import types
     from ..api.types import Record
+    if not isinstance(fn, (types.FunctionType, types.MethodType)):
+        return fn                     # callable objects (RowKey, comparers, ...) keep their identity
 
     def wrapped(*a):
         out = fn(*a)

@@ -276,6 +276,8 @@ def _partition_generic(be, node, src: ColumnBatch, kbits: torch.Tensor, mode: st
             return None
         specs.append(ColSpec(w, t.dtype, t.shape[1] if t.dim() > 1 else 1))
     n = src.n
+    if getattr(be, "spmd_exchange", False) and nports == be.context.world and be.context.world > 1:
+        return _partition_exchange(be, src, names, cols, specs, mode, seps)
     cap = n + 16                      # worst case: everything lands in one partition
     total = sum(s.width for s in specs) * cap * nports
     if total > (8 << 30):
@@ -294,6 +296,43 @@ def _partition_generic(be, node, src: ColumnBatch, kbits: torch.Tensor, mode: st
         b._keepalive = (arena, sh)
         ports.append(b)
     return ports
+
+
+def _partition_exchange(be, src: ColumnBatch, names, cols, specs, mode: str, seps):
+    """SPMD form of a distributor stage (one process per GPU, partition p lives on rank p): the
+    partition function, the all-to-all and the consumer's Merge are ONE fused kernel chain writing
+    straight into the owners' receive buffers over NVLink (parallel/shuffle.py).  The vertex's
+    single output port already holds the rows this rank owns; it is tagged so the executor does not
+    exchange it again.  Sizes travel on the control plane (two tiny all-reduces)."""
+    import torch.distributed as dist
+    from ..parallel.shuffle import FusedShuffle
+    ctx = be.context
+    n = src.n
+    t = torch.tensor([n, -n], dtype=torch.int64, device=be.device)
+    tot = torch.tensor([n], dtype=torch.int64, device=be.device)
+    dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    dist.all_reduce(tot)
+    n_max, total = int(t[0].item()), int(tot.item())
+    row_bytes = sum(sp.width for sp in specs)
+    cap = total + 16                                   # skew-proof when it is affordable
+    if cap * row_bytes > (2 << 30):
+        cap = max(4096, 2 * total // ctx.world + 4096)   # else 2x the mean; overflow is reported, not silent
+    arena = ctx._spmd_arena()
+    mark = arena.mark()
+    try:
+        sh = FusedShuffle(arena, specs, cap, parts_per_rank=1, emit_key=False, max_rows_in=max(n_max, 1))
+        sh.run(cols, mode=mode, key_col=0, key_kind=0, separators=seps)
+        m = sh.received_rows()[0]
+        d = {k: sh.recv[c + 1][0][:m].clone() for c, k in enumerate(names)}
+    finally:
+        arena.release_to(mark)
+    for k in names:
+        if src.cols[k].dtype == torch.bool:
+            d[k] = d[k].view(torch.bool) if d[k].dtype == torch.uint8 else d[k]
+    b = ColumnBatch(d, m, src.tuple_like, src.key_spec)
+    b._exchanged = True
+    be.fused_exchanges = getattr(be, "fused_exchanges", 0) + 1
+    return [b]
 
 
 def _hash_partition(be, node, part, inputs, env):

@@ -10,8 +10,9 @@ over the symmetric arena:
   1:N broadcast (side inputs)          small control-plane broadcast from rank 0
   OrderBy over byte rows               the whole sample → separators → range shuffle → sort subplan
                                        is executed by the fused `RowSorter` (parallel/dsort.py)
-(The decomposable GroupBy stages run through the generic edges here; the fused NVLink
-reduce-scatter form of that plan is `parallel/dagg.py`, driven directly by models/groupby.py.)
+(The decomposable GroupBy plan runs through these edges: its HashPartition stage is the fused
+shuffle; the single-kernel NVLink reduce-scatter form of the same plan is `parallel/dagg.py`,
+driven directly by models/groupby.py.)
 
 Reference roles: GraphBuilder.ConnectPointwise/ConnectCrossProduct (DryadLinqGraphManager/
 GraphBuilder.cs:420-504) and the GM run loop; the reference gets these edges from files + HTTP.
@@ -81,6 +82,10 @@ class SpmdExecutor(JobExecutor):
             raise DryadLinqException(ErrorCode.Internal,
                                      "SPMD execution needs every stage to have 1 or world partitions")
         self._find_row_sort_patterns()
+        # GPU backend: distributor stages (HashPartition / RangePartition into `world` ports) run
+        # the fused partition + all-to-all kernel over the symmetric arena instead of emitting ports
+        if getattr(self.backend, "name", "") == "gpu":
+            self.backend.spmd_exchange = True
         rep = self.reporter
         rep.job_start(self.plan)
         t_job = time.perf_counter()
@@ -126,6 +131,9 @@ class SpmdExecutor(JobExecutor):
             cpc = child.partition_count
             if op == ConnOp.CrossProduct:
                 ports = self.out[child.uid][self.rank] if cpc == self.world else (self.out[child.uid][0] if self.rank == 0 else None)
+                if ports is not None and len(ports) == 1 and getattr(ports[0], "_exchanged", False):
+                    ins.append([ports[0]])                # the distributor already ran the fused all-to-all
+                    continue
                 recs = [self.backend.to_records(p) for p in ports] if ports is not None else None
                 everyone: List = [None] * self.world
                 dist.all_gather_object(everyone, recs)
