@@ -381,6 +381,97 @@ def compact_flags(flags: torch.Tensor):
     return idx[:m], m
 
 
+# ---- K7 --------------------------------------------------------------------------------------
+def group_by_sort(key_bits: torch.Tensor):
+    """Sort-based grouping of a key column (int64 bit patterns).  Returns (order, starts, keys):
+    `order` int32[n] is the STABLE sort permutation (rows of one group keep their source order),
+    `starts` int32[g] the first position of every group in the sorted order, `keys` int64[g] the
+    group keys ascending by bit pattern — a CSR view of the groups."""
+    require_cuda(key_bits)
+    n = key_bits.numel()
+    if n == 0:
+        z = torch.empty(0, dtype=torch.int32, device=key_bits.device)
+        return z, z.clone(), key_bits[:0]
+    skeys, order = radix_sort_pairs(key_bits.clone(), None, iota=True)
+    flags = torch.empty(n, dtype=torch.uint8, device=key_bits.device)
+    N.check(N.kernels().dryad_mark_boundaries(ptr(skeys), n, ptr(flags), stream()), "mark_boundaries")
+    _count()
+    starts, g = compact_flags(flags)
+    return order, starts, skeys[starts.long()]
+
+
+# ---- K15 -------------------------------------------------------------------------------------
+_W2DT = {1: torch.uint8, 2: torch.int16, 4: torch.int32, 8: torch.int64}
+
+
+def rows_to_columns(rows: torch.Tensor, fields: Sequence[tuple]):
+    """rows: [n, stride] uint8 packed little-endian records; fields: (offset, torch dtype) per
+    column.  Returns one tensor per field (the partfile record format -> columnar)."""
+    require_cuda(rows)
+    n, stride = rows.shape
+    nc = len(fields)
+    outs = [torch.empty(n, dtype=dt, device=rows.device) for _, dt in fields]
+    offs = (C.c_int * nc)(*[int(o) for o, _ in fields])
+    widths = (C.c_int * nc)(*[o.element_size() for o in outs])
+    ptrs = (C.c_void_p * nc)(*[o.data_ptr() if n else 1 for o in outs])
+    N.check(N.kernels().dryad_rows_to_columns(ptr(rows), n, stride, nc, offs, widths, ptrs, stream()), "rows_to_columns")
+    _count()
+    return outs
+
+
+def columns_to_rows(cols: Sequence[torch.Tensor], offsets: Sequence[int], stride: int) -> torch.Tensor:
+    """Inverse of rows_to_columns: packs columns into [n, stride] uint8 records (gaps are zero)."""
+    require_cuda(*cols)
+    n = cols[0].numel()
+    nc = len(cols)
+    rows = torch.empty((n, stride), dtype=torch.uint8, device=cols[0].device)
+    offs = (C.c_int * nc)(*[int(o) for o in offsets])
+    widths = (C.c_int * nc)(*[c.element_size() for c in cols])
+    ptrs = (C.c_void_p * nc)(*[c.data_ptr() if n else 1 for c in cols])
+    N.check(N.kernels().dryad_columns_to_rows(ptr(rows), n, stride, nc, offs, widths, ptrs, stream()), "columns_to_rows")
+    _count()
+    return rows
+
+
+# ---- K10 -------------------------------------------------------------------------------------
+def set_contains(table: "HashAggTable", probe: torch.Tensor) -> torch.Tensor:
+    """uint8 flag per probe key: present in the (finished) key table."""
+    require_cuda(probe)
+    out = torch.empty(probe.numel(), dtype=torch.uint8, device=probe.device)
+    N.check(N.kernels().dryad_set_contains(ptr(table.keys), table.cap, ptr(probe), probe.numel(), ptr(out), stream()), "set_contains")
+    _count()
+    return out
+
+
+def distinct_keys(key_bits: torch.Tensor) -> torch.Tensor:
+    tbl = HashAggTable(agg_capacity(max(key_bits.numel(), 16), 0.5), [], key_bits.device)
+    if key_bits.numel():
+        tbl.update(key_bits.contiguous(), [])
+    return tbl.extract()[0]
+
+
+def set_operation(op: str, a: torch.Tensor, b: torch.Tensor) -> torch.Tensor:
+    """Hash-set algebra on key bit patterns: 'union' = Distinct(a ++ b); 'intersect' / 'except' =
+    Distinct of the rows of `a` that are (not) present in `b` (LinqToDryad/DryadLinqVertex.cs:1239-1660)."""
+    if op == "union":
+        return distinct_keys(torch.cat([a, b]))
+    if op not in ("intersect", "except"):
+        raise ValueError(op)
+    if a.numel() == 0:
+        return a
+    if b.numel() == 0:
+        return a[:0] if op == "intersect" else distinct_keys(a)
+    tb = HashAggTable(agg_capacity(b.numel(), 0.5), [], b.device)
+    tb.update(b.contiguous(), [])
+    if int(tb.status.item()) == 1:
+        raise N.NativeError("hash set table full")
+    flags = set_contains(tb, a.contiguous())
+    if op == "except":
+        flags = 1 - flags
+    idx, _ = compact_flags(flags)
+    return distinct_keys(a[idx.long()])
+
+
 def reduce(col: torch.Tensor, op: str):
     """Deterministic two-stage Sum/Min/Max; returns a 1-element device tensor (int64 or float64)."""
     require_cuda(col)

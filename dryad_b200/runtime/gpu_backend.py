@@ -194,9 +194,36 @@ def _typed_key(src: ColumnBatch, lam, bits: torch.Tensor) -> torch.Tensor:
     return bits.view(torch.float64) if lam.ir.kind == "f" else bits
 
 
+def _group_by_sorted(be, node, src: ColumnBatch):
+    """Non-decomposable GroupBy (K7): stable radix sort of the key column + run boundaries give the
+    groups as CSR on the GPU; one gather brings the rows into group order and the host only slices
+    the record list (the reference's ParallelSortGroupBy, LinqToDryad/DryadLinqVertex.cs:6418)."""
+    from ..oracle.linq import Grouping
+    p = node.params
+    if src.is_rows or src.n == 0:
+        return NotImplemented
+    kb = _key_column(src, p["key"])
+    if kb is None:
+        return NotImplemented
+    order, starts, _keys = K.group_by_sort(kb.contiguous())
+    recs = src.take(order).to_records()
+    bounds = starts.tolist() + [src.n]
+    key_fn = p["key"].fn
+    elem = p["elem"].fn if p.get("elem") is not None else None
+    res = p["result"].fn if p.get("result") is not None else None
+    out = []
+    for a, b in zip(bounds, bounds[1:]):
+        g = Grouping(key_fn(recs[a]))
+        g.extend(recs[a:b] if elem is None else [elem(x) for x in recs[a:b]])
+        out.append(res(g.key, g) if res is not None else g)
+    return [out]
+
+
 def _group_by(be, node, part, inputs, env):
     p = node.params
     dec = p.get("decomp")
+    if p.get("mode") == "full":
+        return _group_by_sorted(be, node, be._cat(inputs[0]))
     if dec is None or p.get("elem") is not None:
         return NotImplemented
     lanes = dec.gpu_lanes()
@@ -597,6 +624,18 @@ def _distinct(be, node, part, inputs, env):
     return [ColumnBatch({"value": gk.view(torch.float64) if v.dtype == torch.float64 else gk}, gk.numel())]
 
 
+def _set_operation(be, node, part, inputs, env):
+    a, b = be._cat(inputs[0]), be._cat(inputs[1])
+    ok = lambda x: (not x.is_rows) and list(x.cols) == ["value"] and x.cols["value"].dtype in (torch.int64, torch.float64)   # noqa: E731
+    if not ok(a) or not ok(b) or a.cols["value"].dtype != b.cols["value"].dtype:
+        return NotImplemented
+    f = a.cols["value"].dtype == torch.float64
+    ab = a.cols["value"].view(torch.int64) if f else a.cols["value"]
+    bb = b.cols["value"].view(torch.int64) if f else b.cols["value"]
+    r = K.set_operation(node.params["op"], ab.contiguous(), bb.contiguous())
+    return [ColumnBatch({"value": r.view(torch.float64) if f else r}, r.numel())]
+
+
 _GPU_OPS = {
     NodeType.InputTable: _input, NodeType.OutputTable: _passthrough, NodeType.Dummy: _passthrough,
     NodeType.Merge: _passthrough, NodeType.Concat: _passthrough, NodeType.ForkBranch: _passthrough,
@@ -604,4 +643,5 @@ _GPU_OPS = {
     NodeType.HashPartition: _hash_partition, NodeType.RangePartition: _range_partition,
     NodeType.Sampler: _sampler, NodeType.RangeSampler: _range_sampler, NodeType.OrderBy: _order_by,
     NodeType.BasicAggregate: _basic_aggregate, NodeType.Join: _join, NodeType.Distinct: _distinct,
+    NodeType.SetOperation: _set_operation,
 }

@@ -127,6 +127,26 @@ class SpmdExecutor(JobExecutor):
 
     def _spmd_inputs(self, node, i) -> List[List]:
         ins: List[List] = []
+        head = _head(node)
+        if head.type == NodeType.SlidingWindow and node.partition_count == self.world:
+            # C6 neighbour shift: a partition only needs the w-1 records that precede it, so every
+            # rank publishes just its tail (a few records) instead of exchanging partitions
+            # (reference: HashPartition(x => x.Index) of the boundary records,
+            # LinqToDryad/DryadLinqQueryGen.cs:3273-3280)
+            w = head.params["window"]
+            child = node.children[0][0]
+            own = self.out[child.uid][self.rank][0]
+            recs = self.backend.to_records(own)
+            tails: List = [None] * self.world
+            dist.all_gather_object(tails, list(recs[-(w - 1):]) if w > 1 else [])
+            halo: List = []
+            s = self.rank - 1
+            while s >= 0 and len(halo) < w - 1:
+                seg = tails[s]
+                take = (w - 1) - len(halo)
+                halo = list(seg[-take:]) + halo if take > 0 and seg else halo
+                s -= 1
+            return [[own], [halo if self.rank > 0 else []]]
         for child, op in node.children:
             cpc = child.partition_count
             if op == ConnOp.CrossProduct:

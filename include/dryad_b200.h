@@ -176,6 +176,18 @@ int dryad_hash_agg_extract(const uint64_t* tbl_keys, uint64_t cap, int nlanes, c
                            int64_t* const* out_lanes_dev, unsigned long long* out_count,
                            int64_t out_cap, void* stream);
 
+/* ---- K7 sort-based grouping, K15 record transcoding ---------------------------------------------
+ * mark_boundaries: flags[i] = 1 where a run of equal keys starts in a SORTED key column (compact
+ * the flags to get the CSR run starts).  rows_to_columns / columns_to_rows: fixed-stride packed
+ * little-endian records (the partfile record format for numeric schemas) <-> one array per field;
+ * field widths 1/2/4/8 bytes, stride <= 512. */
+#define DRYAD_TRANSCODE_MAX_COLS 16
+int dryad_mark_boundaries(const uint64_t* sorted_keys, int64_t n, uint8_t* flags, void* stream);
+int dryad_rows_to_columns(const uint8_t* rows, int64_t n, int stride, int ncols, const int* offs,
+                          const int* widths, void* const* cols, void* stream);
+int dryad_columns_to_rows(uint8_t* rows, int64_t n, int stride, int ncols, const int* offs,
+                          const int* widths, const void* const* cols, void* stream);
+
 /* ---- K8 hash join / K10 hash sets: LinqToDryad/DryadLinqVertex.cs:775-1030, 6703-7315,
  *      1239-1660 ----------------------------------------------------------------------------- */
 /* status after a build: 1 = table full, 2 = the build side has duplicate keys (the single-pass

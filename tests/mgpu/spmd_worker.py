@@ -34,6 +34,13 @@ def cpu_checks(rank, world):
     allp = [None] * world
     dist.all_gather_object(allp, srt)
     assert sum(allp, []) == sorted(vals)
+    # sliding window: only the w-1 boundary records move between neighbours
+    seq = list(range(100, 160))
+    per = len(seq) // world
+    win = ctx.from_enumerable(seq, world).sliding_window(lambda w_: sum(w_), 4).partitions()[0]
+    allp = [None] * world
+    dist.all_gather_object(allp, win)
+    assert sum(allp, []) == [sum(seq[j:j + 4]) for j in range(len(seq) - 3)], allp
     # scalar aggregate lands on rank 0
     total = ctx.from_enumerable(vals, world).sum_as_query().partitions()[0]
     if rank == 0:

