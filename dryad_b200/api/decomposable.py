@@ -75,6 +75,21 @@ def resource(is_stateful: bool = True, is_expensive: bool = False):
     return mark
 
 
+def nullable(*fields: str):
+    """[Nullable]: the named fields of a record class (or every field when none are named) may be
+    None; the serializer writes a presence byte for them (LinqToDryad/Attributes.cs:37-60).  The
+    self-describing record encoding here always carries presence, so this only records intent —
+    `nullable_fields(cls)` lets schema inference keep such columns off the GPU fast path."""
+    def mark(cls):
+        cls.__dryad_nullable__ = tuple(fields) or True
+        return cls
+    return mark
+
+
+def nullable_fields(cls):
+    return getattr(cls, "__dryad_nullable__", ())
+
+
 def is_associative(fn: Callable) -> bool:
     import operator
     if getattr(fn, "__dryad_associative__", None):

@@ -17,6 +17,28 @@ from typing import Any, List, Tuple
 from ..api.types import ForkTuple, Grouping, LineRecord, Pair, Record
 
 T_NONE, T_FALSE, T_TRUE, T_INT, T_FLOAT, T_STR, T_BYTES, T_TUPLE, T_LIST, T_RECORD, T_PAIR, T_GROUP, T_LINE, T_BIGINT, T_DICT, T_FORK = range(16)
+T_GUID, T_DATETIME, T_DECIMAL, T_FORKVALUE, T_CUSTOM = 16, 17, 18, 19, 20
+
+# ---- custom serializers ([CustomDryadLinqSerializer], LinqToDryad/Attributes.cs:37-275;
+#      IDryadLinqSerializer<T>.Read/Write, DryadLinqSerialization.cs:41-789) --------------------------
+_CUSTOM_BY_TYPE: dict = {}
+_CUSTOM_BY_NAME: dict = {}
+
+
+def register_serializer(cls, name: str, write, read) -> None:
+    """`write(obj) -> bytes`, `read(bytes) -> obj`.  `name` travels in the stream, so the reading
+    process must have registered the same name (the reference ships the generated serializer
+    assembly with the job; here the job's modules are imported on every worker)."""
+    _CUSTOM_BY_TYPE[cls] = (name, write)
+    _CUSTOM_BY_NAME[name] = read
+
+
+def custom_serializer(write, read, name: str = ""):
+    """Class decorator form: `@custom_serializer(write=..., read=...)`."""
+    def mark(cls):
+        register_serializer(cls, name or f"{cls.__module__}.{cls.__qualname__}", write, read)
+        return cls
+    return mark
 
 
 def compact(v: int) -> bytes:
@@ -92,6 +114,12 @@ def encode(obj: Any, out: List[bytes]) -> None:
         out.append(bytes((T_LIST,)) + compact(len(obj)))
         for x in obj:
             encode(x, out)
+    elif type(obj) in _CUSTOM_BY_TYPE:
+        name, write = _CUSTOM_BY_TYPE[type(obj)]
+        body = write(obj)
+        out.append(bytes((T_CUSTOM,)) + enc_string(name) + compact(len(body)) + bytes(body))
+    elif _is_builtin_extra(obj):
+        _encode_extra(obj, out)
     else:
         import numpy as np
         if isinstance(obj, np.integer):
@@ -104,6 +132,36 @@ def encode(obj: Any, out: List[bytes]) -> None:
             from ..api.errors import DryadLinqException, ErrorCode
             raise DryadLinqException(ErrorCode.TypeNotSerializable,
                                      f"records of type {type(obj).__name__} cannot be serialised")
+
+
+def _is_builtin_extra(obj) -> bool:
+    import datetime
+    import decimal
+    import uuid
+    from ..api.types import ForkValue
+    return isinstance(obj, (uuid.UUID, datetime.datetime, decimal.Decimal, ForkValue))
+
+
+def _encode_extra(obj, out: List[bytes]) -> None:
+    """Guid (16 bytes, .NET field order = bytes_le), DateTime (int64 ticks of 100 ns since
+    0001-01-01, the reference's SqlDateTime/DateTime writers), Decimal (string form), ForkValue."""
+    import datetime
+    import decimal
+    import uuid
+    from ..api.types import ForkValue
+    if isinstance(obj, uuid.UUID):
+        out.append(bytes((T_GUID,)) + obj.bytes_le)
+    elif isinstance(obj, datetime.datetime):
+        naive = obj.replace(tzinfo=None) - (obj.utcoffset() or datetime.timedelta(0))
+        delta = naive - datetime.datetime(1, 1, 1)
+        ticks = (delta.days * 86400 + delta.seconds) * 10_000_000 + delta.microseconds * 10
+        out.append(bytes((T_DATETIME,)) + struct.pack("<q", ticks))
+    elif isinstance(obj, decimal.Decimal):
+        out.append(bytes((T_DECIMAL,)) + enc_string(str(obj)))
+    elif isinstance(obj, ForkValue):
+        out.append(bytes((T_FORKVALUE, 1 if obj.has_value else 0)))
+        if obj.has_value:
+            encode(obj.value, out)
 
 
 def encode_record(obj: Any) -> bytes:
@@ -177,5 +235,32 @@ def decode(buf: memoryview, pos: int) -> Tuple[Any, int]:
             v, pos = decode(buf, pos)
             d[k] = v
         return d, pos
+    if t == T_GUID:
+        import uuid
+        return uuid.UUID(bytes_le=bytes(buf[pos:pos + 16])), pos + 16
+    if t == T_DATETIME:
+        import datetime
+        ticks = struct.unpack_from("<q", buf, pos)[0]
+        return datetime.datetime(1, 1, 1) + datetime.timedelta(microseconds=ticks // 10), pos + 8
+    if t == T_DECIMAL:
+        import decimal
+        sv, pos = _dec_string(buf, pos)
+        return decimal.Decimal(sv), pos
+    if t == T_FORKVALUE:
+        from ..api.types import ForkValue
+        has = buf[pos]
+        pos += 1
+        if not has:
+            return ForkValue(), pos
+        v, pos = decode(buf, pos)
+        return ForkValue(v), pos
+    if t == T_CUSTOM:
+        name, pos = _dec_string(buf, pos)
+        n, pos = read_compact(buf, pos)
+        read = _CUSTOM_BY_NAME.get(name)
+        from ..api.errors import DryadLinqException, ErrorCode
+        if read is None:
+            raise DryadLinqException(ErrorCode.FailedToDeserialize, f"no serializer registered for {name!r}")
+        return read(bytes(buf[pos:pos + n])), pos + n
     from ..api.errors import DryadLinqException, ErrorCode
     raise DryadLinqException(ErrorCode.FailedToDeserialize, f"unknown record tag {t}")

@@ -32,10 +32,55 @@ def _kfn(lam) -> Callable:
 
 
 class VertexEnv:
-    """Per-vertex environment (LinqToDryad/VertexEnv.cs:34-367): ids, partition index, context."""
+    """Per-vertex environment (LinqToDryad/VertexEnv.cs:34-367): ids, partition index, context,
+    thread count, write-buffer sizing and the error report file."""
 
-    def __init__(self, context, vertex_id: int, part: int, version: int = 0):
+    DEFAULT_WRITE_BUFFER = 8 << 20          # VertexEnv.cs:261-283
+    LARGE_WRITE_BUFFER = 256 << 20
+    MIN_WRITE_BUFFER = 16 << 10
+
+    def __init__(self, context, vertex_id: int, part: int, version: int = 0, n_outputs: int = 1,
+                 use_large_buffer: bool = False):
         self.context, self.vertex_id, self.part, self.version = context, vertex_id, part, version
+        self.n_outputs = max(1, n_outputs)
+        self.use_large_buffer = use_large_buffer
+
+    @property
+    def threads_per_worker(self) -> int:
+        """DRYAD_THREADS_PER_WORKER, else the context setting, else the core count (VertexEnv.cs:72-86)."""
+        import os
+        v = os.environ.get("DRYAD_THREADS_PER_WORKER")
+        if v and v.isdigit() and int(v) > 0:
+            return int(v)
+        t = getattr(self.context, "threads_per_worker", 0) or 0
+        return t if t > 0 else (os.cpu_count() or 1)
+
+    def write_buffer_size(self, available_physical: int = 0) -> int:
+        """8 MB per output (256 MB when a large buffer is requested), capped by a quarter of the
+        available physical memory shared among the outputs, never below 16 KB (GetWriteBuffSize)."""
+        want = self.LARGE_WRITE_BUFFER if self.use_large_buffer else self.DEFAULT_WRITE_BUFFER
+        if available_physical <= 0:
+            try:
+                import psutil
+                available_physical = int(psutil.virtual_memory().available)
+            except Exception:  # noqa: BLE001
+                available_physical = 0
+        if available_physical > 0:
+            want = min(want, available_physical // 4 // self.n_outputs)
+        return max(self.MIN_WRITE_BUFFER, want)
+
+    def report_vertex_error(self, exc: BaseException, directory: str = None) -> str:
+        """Write the failure to `VertexException.txt` in the vertex's working directory so the
+        graph manager / job browser can show it (ReportVertexError, VertexEnv.cs:230-259)."""
+        import os
+        import traceback
+        d = directory or getattr(self.context, "work_dir", ".")
+        os.makedirs(d, exist_ok=True)
+        path = os.path.join(d, "VertexException.txt")
+        with open(path, "w", encoding="utf-8") as f:
+            f.write(f"vertex {self.vertex_id} partition {self.part} version {self.version}\n")
+            f.write("".join(traceback.format_exception(type(exc), exc, exc.__traceback__)))
+        return path
 
 
 def run(node: DLinqQueryNode, part: int, inputs: List[List], env: VertexEnv) -> List[List]:

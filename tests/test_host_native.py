@@ -358,3 +358,49 @@ def test_dynamic_resize_follows_pointwise_stages_and_range_distributor_sizing():
     import pytest
     with pytest.raises(ValueError):
         g2.resize_stage(s0, 3)
+
+
+def test_builtin_and_custom_record_serializers_round_trip():
+    """Guid / DateTime / Decimal / ForkValue built-ins and a [CustomDryadLinqSerializer] type
+    (LinqToDryad/DryadLinqSerialization.cs:41-789, Attributes.cs:37-275)."""
+    import datetime
+    import decimal
+    import uuid
+    import dryad_b200 as D
+    from dryad_b200.channel import records as R
+
+    class Money:
+        def __init__(self, cents):
+            self.cents = cents
+
+        def __eq__(self, o):
+            return isinstance(o, Money) and o.cents == self.cents
+
+    R.register_serializer(Money, "test.Money", lambda m: m.cents.to_bytes(8, "little", signed=True),
+                          lambda b: Money(int.from_bytes(b, "little", signed=True)))
+    rec = D.Record(id=uuid.UUID("12345678-1234-5678-1234-567812345678"), t=datetime.datetime(2014, 3, 1, 12, 30, 15, 250000),
+                   d=decimal.Decimal("12.3400"), fv=D.ForkValue((1, "x")), none=D.ForkValue(), m=Money(-995))
+    buf = R.encode_record(rec)
+    back, pos = R.decode(memoryview(buf), 0)
+    assert pos == len(buf) and back == rec and back.m == Money(-995) and not back.none.has_value
+    # .NET Guid layout: first three groups little-endian
+    assert buf[buf.index(bytes((R.T_GUID,))) + 1:][:4] == bytes.fromhex("78563412")
+
+
+def test_vertex_env_buffer_sizing_threads_and_error_report(tmp_path, monkeypatch):
+    from dryad_b200.runtime.vertex_ops import VertexEnv
+    import dryad_b200 as D
+    ctx = D.DryadLinqContext(1)
+    env = VertexEnv(ctx, 7, 2, 1, n_outputs=4)
+    assert env.write_buffer_size(available_physical=1 << 40) == 8 << 20
+    assert env.write_buffer_size(available_physical=64 << 20) == (64 << 20) // 4 // 4
+    assert env.write_buffer_size(available_physical=100) == 16 << 10
+    assert VertexEnv(ctx, 7, 2, use_large_buffer=True).write_buffer_size(available_physical=1 << 40) == 256 << 20
+    monkeypatch.setenv("DRYAD_THREADS_PER_WORKER", "3")
+    assert env.threads_per_worker == 3
+    try:
+        raise ValueError("bad record")
+    except ValueError as ex:
+        path = env.report_vertex_error(ex, str(tmp_path))
+    text = open(path).read()
+    assert path.endswith("VertexException.txt") and "vertex 7 partition 2 version 1" in text and "bad record" in text
