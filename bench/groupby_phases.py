@@ -23,7 +23,7 @@ if world > 1:
     dist.init_process_group("nccl", device_id=dev)
 keys, vals = groupby.generate(n, nkeys, 11, dev, rank)
 fcap = K.agg_capacity(int(1.25 * nkeys) // world + 1024)
-arena = SymmetricArena(fcap * 8 * 3 + (8 << 20), rank, world, None, dev)
+arena = SymmetricArena(fcap * 8 * 3 + (fcap // 3 + 1024) * world * 24 + (16 << 20), rank, world, None, dev)
 agg = DistributedHashAggregate(arena, ["sum_i64", "count"], K.agg_capacity(nkeys), fcap)
 for _ in range(3):
     agg.run(keys, [vals, None])
@@ -47,7 +47,17 @@ for _ in range(R):
     marks.append(("reset", ev()))
     (agg.local if world > 1 else agg.final).update(keys, [vals, None])
     marks.append(("local update", ev()))
-    if world > 1:
+    if world > 1 and agg.shuffle is not None:
+        agg.nrows.zero_()
+        agg.local.extract_rows(agg.rows, agg.nrows)
+        m = int(agg.nrows.item())
+        marks.append(("extract partial rows", ev()))
+        agg.shuffle.run([agg.rows[:m]], mode="hash", key_col=0, key_kind=0)
+        got = agg.shuffle.received_rows()[0]
+        marks.append(("shuffle partials", ev()))
+        agg.final.update_rows(agg.shuffle.recv[0][0], got, combine=True)
+        marks.append(("fold received", ev()))
+    elif world > 1:
         arena.barrier(slot=2)
         marks.append(("barrier", ev()))
         agg.local.merge_into_peers(world, agg.peer_keys, agg.peer_vals, agg.final_cap)

@@ -30,6 +30,7 @@ constexpr uint64_t NOSLOT = ~0ull;
 
 struct AggDesc {
   int nlanes;
+  int in_stride;                       // elements between consecutive rows of the inputs (1 = columns)
   int op[DRYAD_MAX_LANES];
   const int64_t* in[DRYAD_MAX_LANES];  // input columns (may be null for COUNT)
 };
@@ -111,9 +112,11 @@ __device__ __forceinline__ void apply(int op, int64_t* slot, int64_t v, bool com
 template <bool SYSTEM>
 __device__ __forceinline__ void load_bucket(const uint64_t* p, uint64_t (&k)[4]) {
   if (SYSTEM) {
-#pragma unroll
-    for (int j = 0; j < 4; ++j)
-      asm volatile("ld.relaxed.sys.global.u64 %0, [%1];" : "=l"(k[j]) : "l"(p + j) : "memory");
+    // peer HBM: one 32-byte NVLink read (served by the home GPU's L2, the point of coherence for the
+    // system-scope CAS/RED that follow; never cached on this side: .cg bypasses L1 and peer lines do
+    // not live in the local L2).  Four scalar relaxed.sys loads cost four round-trip packets.
+    asm volatile("ld.global.cg.v4.u64 {%0, %1, %2, %3}, [%4];"
+                 : "=l"(k[0]), "=l"(k[1]), "=l"(k[2]), "=l"(k[3]) : "l"(p) : "memory");
   } else {
     asm volatile("ld.global.cg.v4.u64 {%0, %1, %2, %3}, [%4];"
                  : "=l"(k[0]), "=l"(k[1]), "=l"(k[2]), "=l"(k[3]) : "l"(p) : "memory");
@@ -217,10 +220,10 @@ __global__ void __launch_bounds__(256) agg_update_kernel(uint64_t* keys, uint64_
 #pragma unroll
     for (int l = 0; l < L; ++l) v[l] = 1;
     if (i < n) {
-      const uint64_t key = (uint64_t)ld_stream(reinterpret_cast<const int64_t*>(in_keys) + i);
+      const uint64_t key = (uint64_t)ld_stream(reinterpret_cast<const int64_t*>(in_keys) + i * A.in_stride);
 #pragma unroll
       for (int l = 0; l < L; ++l)
-        if (l < A.nlanes && A.in[l]) v[l] = ld_stream(A.in[l] + i);
+        if (l < A.nlanes && A.in[l]) v[l] = ld_stream(A.in[l] + i * A.in_stride);
       s = find_or_insert<false>(keys, cap, key);
       if (s == cap) { atomicMax(status, 1); s = NOSLOT; }
     }
@@ -311,6 +314,58 @@ __global__ void __launch_bounds__(256) agg_extract_kernel(const uint64_t* __rest
       ++o;
     }
     __syncthreads();                 // warp_tot / tile_base are reused by the next tile
+  }
+}
+
+// Same compaction, but every occupied slot becomes ONE packed row {key, vals[0..nlanes)} of
+// (1 + nlanes) words: the unit the fused shuffle moves when partial aggregates travel to their
+// key owners as a push (stores) instead of remote probes.
+template <int L>
+__global__ void __launch_bounds__(256) agg_extract_rows_kernel(const uint64_t* __restrict__ keys,
+                                                               uint64_t cap, AggDesc A, const int64_t* __restrict__ vals,
+                                                               int64_t* __restrict__ out_rows,
+                                                               unsigned long long* __restrict__ out_count,
+                                                               int64_t out_cap) {
+  __shared__ uint32_t warp_tot[8];
+  __shared__ unsigned long long tile_base;
+  const uint64_t nb = cap >> 2;
+  const int lane = (int)lane_id(), warp = threadIdx.x >> 5;
+  const int rw = 1 + A.nlanes;
+  for (uint64_t b0 = (uint64_t)blockIdx.x * 256; b0 < nb; b0 += (uint64_t)gridDim.x * 256) {
+    const uint64_t b = b0 + threadIdx.x;
+    uint64_t k[4] = {EMPTY, EMPTY, EMPTY, EMPTY};
+    if (b < nb)
+      asm volatile("ld.global.nc.v4.u64 {%0, %1, %2, %3}, [%4];"
+                   : "=l"(k[0]), "=l"(k[1]), "=l"(k[2]), "=l"(k[3]) : "l"(keys + b * 4));
+    uint32_t mine = 0;
+#pragma unroll
+    for (int j = 0; j < 4; ++j) mine += (k[j] != EMPTY);
+    uint32_t incl = mine;
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) {
+      const uint32_t t = __shfl_up_sync(0xffffffffu, incl, d);
+      if (lane >= d) incl += t;
+    }
+    if (lane == 31) warp_tot[warp] = incl;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+      uint32_t tot = 0;
+#pragma unroll
+      for (int w = 0; w < 8; ++w) { const uint32_t t = warp_tot[w]; warp_tot[w] = tot; tot += t; }
+      tile_base = tot ? atomicAdd(out_count, (unsigned long long)tot) : 0ull;
+    }
+    __syncthreads();
+    int64_t o = (int64_t)tile_base + warp_tot[warp] + (incl - mine);
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      if (k[j] == EMPTY) continue;
+      if (o < out_cap) {
+        out_rows[o * rw] = (int64_t)k[j];
+        for (int l = 0; l < A.nlanes; ++l) out_rows[o * rw + 1 + l] = vals[(b * 4 + j) * L + l];
+      }
+      ++o;
+    }
+    __syncthreads();
   }
 }
 
@@ -441,6 +496,7 @@ static inline int grid_for(int64_t n) {
 static int fill_desc(AggDesc& A, int nlanes, const int* ops, const int64_t* const* in) {
   if (nlanes < 0 || nlanes > DRYAD_MAX_LANES) return DRYAD_ERR_BAD_ARG;
   A.nlanes = nlanes;
+  A.in_stride = 1;
   for (int l = 0; l < DRYAD_MAX_LANES; ++l) { A.op[l] = 0; A.in[l] = nullptr; }
   for (int l = 0; l < nlanes; ++l) {
     if (ops[l] < 0 || ops[l] > DRYAD_AGG_MAX_F64) return DRYAD_ERR_BAD_ARG;
@@ -503,6 +559,32 @@ int dryad_hash_agg_merge_peers(const uint64_t* tbl_keys, uint64_t cap, int nlane
   for (int r = 0; r < world; ++r) { T.keys[r] = peer_keys[r]; T.vals[r] = peer_vals[r]; }
   int64_t g = ((int64_t)cap + 255) / 256; if (g > 148 * 16) g = 148 * 16;
   DRYAD_DISPATCH_L(nlanes, (agg_merge_peers_kernel<L><<<(int)g, 256, 0, (cudaStream_t)stream>>>(tbl_keys, cap, A, tbl_vals, T, status)));
+  DRYAD_LAUNCH_CHECK();
+  return DRYAD_OK;
+}
+
+/* Fold packed rows {key, v[0..nlanes)} (stride 1 + nlanes words) into the table; combine != 0
+ * treats the values as partial aggregates (COUNT partials add). */
+int dryad_hash_agg_update_rows(uint64_t* tbl_keys, uint64_t cap, int nlanes, const int* ops,
+                               int64_t* tbl_vals, const int64_t* rows, int64_t n, int combine,
+                               int32_t* status, void* stream) {
+  if (!cap_ok(cap)) return DRYAD_ERR_BAD_ARG;
+  if (n <= 0) return DRYAD_OK;
+  AggDesc A; int rc = fill_desc(A, nlanes, ops, nullptr); if (rc) return rc;
+  A.in_stride = 1 + nlanes;
+  for (int l = 0; l < nlanes; ++l) A.in[l] = rows + 1 + l;
+  int64_t g = (n + 255) / 256; if (g > 148 * 16) g = 148 * 16;
+  DRYAD_DISPATCH_L(nlanes, (agg_update_kernel<L><<<(int)g, 256, 0, (cudaStream_t)stream>>>(tbl_keys, cap, A, tbl_vals, reinterpret_cast<const uint64_t*>(rows), n, combine, status)));
+  DRYAD_LAUNCH_CHECK();
+  return DRYAD_OK;
+}
+
+int dryad_hash_agg_extract_rows(const uint64_t* tbl_keys, uint64_t cap, int nlanes, const int* ops,
+                                const int64_t* tbl_vals, int64_t* out_rows,
+                                unsigned long long* out_count, int64_t out_cap, void* stream) {
+  if (!cap_ok(cap)) return DRYAD_ERR_BAD_ARG;
+  AggDesc A; int rc = fill_desc(A, nlanes, ops, nullptr); if (rc) return rc;
+  DRYAD_DISPATCH_L(nlanes, (agg_extract_rows_kernel<L><<<grid_for((int64_t)cap), 256, 0, (cudaStream_t)stream>>>(tbl_keys, cap, A, tbl_vals, out_rows, out_count, out_cap)));
   DRYAD_LAUNCH_CHECK();
   return DRYAD_OK;
 }

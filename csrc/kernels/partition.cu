@@ -619,7 +619,9 @@ int dryad_shuffle_run(const DryadShuffleDesc* d, void* stream) {
     if ((int)d->width[c] > maxw) maxw = (int)d->width[c];
   }
   if (d->key_col < 0 || d->key_col >= d->ncols) return DRYAD_ERR_BAD_ARG;
-  if (d->key_kind == 0 && d->width[d->key_col] != 8) return DRYAD_ERR_BAD_ARG;
+  // key_kind 0: the key is the little-endian u64 at the start of the key column's row (rows of
+  // several 8-byte words are allowed: packed {key, payload...} records)
+  if (d->key_kind == 0 && (d->width[d->key_col] < 8 || (d->width[d->key_col] & 7))) return DRYAD_ERR_BAD_ARG;
   if (d->key_kind == 1 && (d->key_off < 0 || d->key_off + 8 > (int)d->width[d->key_col]))
     return DRYAD_ERR_BAD_ARG;
   P.max_width = maxw;

@@ -20,7 +20,7 @@ def bench(rank, world, dev, n, nkeys, steps, warmup, max_over_ranks, barrier):
     keys, vals = generate(n, nkeys, 11, dev, rank)
     # owner tables hold ~nkeys/world groups (1.25x for hash imbalance), the local partial table all nkeys
     fcap = K.agg_capacity(int(1.25 * nkeys) // world + 1024)
-    arena = SymmetricArena(fcap * 8 * 3 + (8 << 20), rank, world, None, dev)
+    arena = SymmetricArena(fcap * 8 * 3 + (fcap // 3 + 1024) * world * 24 + (16 << 20), rank, world, None, dev)
     agg = DistributedHashAggregate(arena, ["sum_i64", "count"], K.agg_capacity(nkeys), fcap)
     for _ in range(max(warmup, 1)):
         gk, gl = agg.run(keys, [vals, None])

@@ -284,6 +284,22 @@ class HashAggTable:
                 "hash_agg_merge_peers")
         _count()
 
+    def update_rows(self, rows: torch.Tensor, n: int, combine: bool = True):
+        """Fold packed rows [n, 1 + nlanes] int64 {key, values...} into the table."""
+        require_cuda(rows)
+        N.check(N.kernels().dryad_hash_agg_update_rows(ptr(self.keys), self.cap, self.nl, self._ops_c, ptr(self.vals),
+                                                       ptr(rows), int(n), int(combine), ptr(self.status), stream()),
+                "hash_agg_update_rows")
+        _count()
+
+    def extract_rows(self, out: torch.Tensor, count: torch.Tensor) -> None:
+        """Compact the occupied slots into packed rows `out` [cap_rows, 1 + nlanes] int64; `count`
+        (int64[1], zeroed by the caller) receives the number of rows.  No host sync."""
+        N.check(N.kernels().dryad_hash_agg_extract_rows(ptr(self.keys), self.cap, self.nl, self._ops_c, ptr(self.vals),
+                                                        ptr(out), ptr(count), out.shape[0], stream()),
+                "hash_agg_extract_rows")
+        _count()
+
     def extract(self, max_out: Optional[int] = None):
         """Returns (keys[m], lanes[nl][m]) of occupied slots (order unspecified).  Syncs once to
         learn m."""

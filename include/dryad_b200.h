@@ -171,6 +171,14 @@ int dryad_hash_agg_merge_peers(const uint64_t* tbl_keys, uint64_t cap, int nlane
                                const int64_t* tbl_vals, int world, uint64_t* const* peer_keys,
                                int64_t* const* peer_vals, uint64_t peer_cap, int32_t* status,
                                void* stream);
+/* Packed-row forms: rows of (1 + nlanes) int64 words {key, v[0..nlanes)} — the record the fused
+ * shuffle carries when partials are PUSHED to their key owners and folded there locally. */
+int dryad_hash_agg_update_rows(uint64_t* tbl_keys, uint64_t cap, int nlanes, const int* ops,
+                               int64_t* tbl_vals, const int64_t* rows, int64_t n, int combine,
+                               int32_t* status, void* stream);
+int dryad_hash_agg_extract_rows(const uint64_t* tbl_keys, uint64_t cap, int nlanes, const int* ops,
+                                const int64_t* tbl_vals, int64_t* out_rows,
+                                unsigned long long* out_count, int64_t out_cap, void* stream);
 int dryad_hash_agg_extract(const uint64_t* tbl_keys, uint64_t cap, int nlanes, const int* ops,
                            const int64_t* tbl_vals, uint64_t* out_keys,
                            int64_t* const* out_lanes_dev, unsigned long long* out_count,

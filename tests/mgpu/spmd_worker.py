@@ -101,16 +101,20 @@ def gpu_checks(rank, world):
     nk = 50_000
     gk = torch.randint(0, nk, (2_000_000,), dtype=torch.int64, device=dev, generator=g)
     gv = torch.randint(0, 100, (2_000_000,), dtype=torch.int64, device=dev, generator=g)
-    agg = DistributedHashAggregate(arena, ["sum_i64", "count"], 2 * nk, 4 * nk)
-    for _ in range(2):
-        ok_, ol = agg.run(gk, [gv, None])
-    own = hash_bucket_np(ok_.cpu().numpy().view(np.uint64), world)
-    assert (own == rank).all()
     full_k = [torch.zeros(nk, dtype=torch.int64, device=dev) for _ in range(2)]
     full_k[0].index_add_(0, gk, gv)
     full_k[1].index_add_(0, gk, torch.ones_like(gv))
     dist.all_reduce(full_k[0]); dist.all_reduce(full_k[1])
-    assert torch.equal(ol[0], full_k[0][ok_]) and torch.equal(ol[1], full_k[1][ok_])
+    for merge in ("push", "atomics"):          # partials pushed through the fused shuffle / remote atomics
+        agg = DistributedHashAggregate(arena, ["sum_i64", "count"], 2 * nk, 4 * nk, merge=merge)
+        for _ in range(2):
+            ok_, ol = agg.run(gk, [gv, None])
+        own = hash_bucket_np(ok_.cpu().numpy().view(np.uint64), world)
+        assert (own == rank).all(), merge
+        assert torch.equal(ol[0], full_k[0][ok_]) and torch.equal(ol[1], full_k[1][ok_]), merge
+        cnt_g = torch.tensor([ok_.numel()], dtype=torch.int64, device=dev)
+        dist.all_reduce(cnt_g)
+        assert int(cnt_g.item()) == int((full_k[1] > 0).sum().item()), merge
 
     # 3b. broadcast join: the small side is replicated by the build kernel, the fact side stays put
     from dryad_b200.models import joins
