@@ -99,6 +99,8 @@ def main():
             return 2
     torch.cuda.set_device(local_rank)
     dev = torch.device("cuda", local_rank)
+    from dryad_b200.utils.numa import bind_to_gpu
+    bound = bind_to_gpu(local_rank)            # pinned staging memory is first-touched on the GPU's socket
     if world > 1:
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
         dist.init_process_group("nccl", device_id=dev)
@@ -197,7 +199,7 @@ def main():
             barrier()
             e_ms = max_over_ranks(s0.elapsed_time(s1)) / a.steps
             e2e = {"value": world * n * W / (e_ms * 1e-3) / 1e9, "unit": "GB/s", "ms_per_step": e_ms,
-                   "h2d_bytes_per_step": n * W, "d2h_bytes_per_step": 24,
+                   "h2d_bytes_per_step": n * W, "d2h_bytes_per_step": 24, "cpus_bound": len(bound) if bound else 0,
                    "violations": int(summ[0]), "rows_out_local": int(summ[2])}
         except Exception as ex:  # noqa: BLE001
             e2e = {"error": f"{type(ex).__name__}: {ex}"}

@@ -152,6 +152,11 @@ class DryadLinqContext:
         self.world = int(os.environ.get("WORLD_SIZE", "1")) if self.platform == PlatformKind.B200 else 1
         if self.platform == PlatformKind.B200:
             self.num_partitions = self.world
+            if str(self.device).startswith("cuda") and self.world > 1:
+                # one process per GPU: keep host staging memory and threads on the GPU's socket
+                from ..utils.numa import bind_to_gpu
+                idx = str(self.device).partition(":")[2]
+                self.cpus_bound = bind_to_gpu(int(idx) if idx.isdigit() else int(os.environ.get("LOCAL_RANK", "0")))
         self._arena = None
         self._sorters: Dict[tuple, Any] = {}
         self._disposed = False
