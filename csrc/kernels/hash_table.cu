@@ -29,8 +29,13 @@ constexpr uint64_t EMPTY = ~0ull;  // reserved key; the engine remaps a genuine 
 constexpr uint64_t NOSLOT = ~0ull;
 
 struct AggDesc {
-  int nlanes;
+  int nlanes;                          // lanes the kernels update (user lanes + a hidden row counter in direct mode)
+  int nlanes_out;                      // user lanes (what extract / merge hand on)
   int in_stride;                       // elements between consecutive rows of the inputs (1 = columns)
+  int direct;                          // 1: slot = key - key_lo, no key array, no probing
+  int occ_lane;                        // direct mode: the COUNT lane whose value > 0 marks an occupied slot
+  int src_stride;                      // merge: lane stride of the LOCAL table (may differ from the owners')
+  uint64_t key_lo;
   int op[DRYAD_MAX_LANES];
   const int64_t* in[DRYAD_MAX_LANES];  // input columns (may be null for COUNT)
 };
@@ -173,13 +178,34 @@ __device__ __forceinline__ int64_t ld_stream(const int64_t* p) {
   return (int64_t)__ldcs(reinterpret_cast<const unsigned long long*>(p));
 }
 
+// The four slot keys of bucket b and a 4-bit occupancy mask: the key array of a hashed table
+// (EMPTY marks a free slot), or (direct tables) key_lo + slot for the slots whose row counter is
+// non-zero — there every 64-bit value, ~0 included, is a legitimate key.
+__device__ __forceinline__ uint32_t bucket_keys(const uint64_t* __restrict__ keys, const int64_t* __restrict__ vals,
+                                                const AggDesc& A, int stride, uint64_t b, uint64_t (&k)[4]) {
+  uint32_t mask = 0;
+  if (!A.direct) {
+    asm volatile("ld.global.nc.v4.u64 {%0, %1, %2, %3}, [%4];"
+                 : "=l"(k[0]), "=l"(k[1]), "=l"(k[2]), "=l"(k[3]) : "l"(keys + b * 4));
+#pragma unroll
+    for (int j = 0; j < 4; ++j) mask |= (uint32_t)(k[j] != EMPTY) << j;
+  } else {
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      k[j] = A.key_lo + b * 4 + j;
+      mask |= (uint32_t)(vals[(b * 4 + j) * stride + A.occ_lane] != 0) << j;
+    }
+  }
+  return mask;
+}
+
 template <int L>
 __global__ void agg_init_kernel(uint64_t* keys, uint64_t cap, AggDesc A, int64_t* vals) {
   uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
   uint64_t stride = (uint64_t)gridDim.x * blockDim.x;
   for (; i < cap * L; i += stride) {
     const int l = (int)(i & (L - 1));
-    if (l == 0) keys[i / L] = EMPTY;
+    if (l == 0 && keys) keys[i / L] = EMPTY;
     vals[i] = (l < A.nlanes) ? identity_of(A.op[l]) : 0;
   }
 }
@@ -224,8 +250,13 @@ __global__ void __launch_bounds__(256) agg_update_kernel(uint64_t* keys, uint64_
 #pragma unroll
       for (int l = 0; l < L; ++l)
         if (l < A.nlanes && A.in[l]) v[l] = ld_stream(A.in[l] + i * A.in_stride);
-      s = find_or_insert<false>(keys, cap, key);
-      if (s == cap) { atomicMax(status, 1); s = NOSLOT; }
+      if (A.direct) {
+        s = key - A.key_lo;                      // dense key range: the key IS the slot
+        if (s >= cap) { atomicMax(status, 4); s = NOSLOT; }
+      } else {
+        s = find_or_insert<false>(keys, cap, key);
+        if (s == cap) { atomicMax(status, 1); s = NOSLOT; }
+      }
     }
     apply_rows<L, false>(A, vals, s, v, combine != 0, status);
   }
@@ -242,13 +273,18 @@ __global__ void __launch_bounds__(256) agg_merge_peers_kernel(const uint64_t* __
   const int sub = lane & (L - 1);
   int op = -1;                               // unrolled select: no dynamic index into the params
 #pragma unroll
-  for (int l = 0; l < L; ++l) if (l == sub && l < A.nlanes) op = A.op[l];
+  for (int l = 0; l < L; ++l) if (l == sub && l < A.nlanes_out) op = A.op[l];
   for (; base < cap; base += stride) {
     const uint64_t i = base + threadIdx.x;
-    const uint64_t key = (i < cap) ? keys[i] : EMPTY;
+    uint64_t key = EMPTY;
+    bool occupied = false;
+    if (i < cap) {
+      if (A.direct) { key = A.key_lo + i; occupied = vals[i * A.src_stride + A.occ_lane] != 0; }
+      else { key = keys[i]; occupied = key != EMPTY; }
+    }
     uint64_t s = NOSLOT;
     int owner = 0;
-    if (key != EMPTY) {
+    if (occupied) {
       owner = (int)hash_bucket(key, (uint32_t)T.world);
       s = find_or_insert<true>(T.keys[owner], T.cap, key);
       if (s == T.cap) { atomicMax(status, 1); s = NOSLOT; }
@@ -260,7 +296,7 @@ __global__ void __launch_bounds__(256) agg_merge_peers_kernel(const uint64_t* __
       const int ow = __shfl_sync(0xffffffffu, owner, src);
       const uint64_t row = base + (threadIdx.x & ~31u) + src;   // local slot probed by lane `src`
       if (ss != NOSLOT && op >= 0)
-        apply<true>(op, T.vals[ow] + ss * L + sub, vals[row * L + sub], true, status);
+        apply<true>(op, T.vals[ow] + ss * L + sub, vals[row * A.src_stride + sub], true, status);
     }
   }
 }
@@ -282,12 +318,8 @@ __global__ void __launch_bounds__(256) agg_extract_kernel(const uint64_t* __rest
   for (uint64_t b0 = (uint64_t)blockIdx.x * 256; b0 < nb; b0 += (uint64_t)gridDim.x * 256) {
     const uint64_t b = b0 + threadIdx.x;
     uint64_t k[4] = {EMPTY, EMPTY, EMPTY, EMPTY};
-    if (b < nb)
-      asm volatile("ld.global.nc.v4.u64 {%0, %1, %2, %3}, [%4];"
-                   : "=l"(k[0]), "=l"(k[1]), "=l"(k[2]), "=l"(k[3]) : "l"(keys + b * 4));
-    uint32_t mine = 0;
-#pragma unroll
-    for (int j = 0; j < 4; ++j) mine += (k[j] != EMPTY);
+    const uint32_t occ = (b < nb) ? bucket_keys(keys, vals, A, L, b, k) : 0u;
+    const uint32_t mine = __popc(occ);
     uint32_t incl = mine;
 #pragma unroll
     for (int d = 1; d < 32; d <<= 1) {
@@ -306,10 +338,10 @@ __global__ void __launch_bounds__(256) agg_extract_kernel(const uint64_t* __rest
     int64_t o = (int64_t)tile_base + warp_tot[warp] + (incl - mine);
 #pragma unroll
     for (int j = 0; j < 4; ++j) {
-      if (k[j] == EMPTY) continue;
+      if (!((occ >> j) & 1)) continue;
       if (o < out_cap) {
         out_keys[o] = k[j];
-        for (int l = 0; l < A.nlanes; ++l) out_lanes[l][o] = vals[(b * 4 + j) * L + l];
+        for (int l = 0; l < A.nlanes_out; ++l) out_lanes[l][o] = vals[(b * 4 + j) * L + l];
       }
       ++o;
     }
@@ -330,16 +362,12 @@ __global__ void __launch_bounds__(256) agg_extract_rows_kernel(const uint64_t* _
   __shared__ unsigned long long tile_base;
   const uint64_t nb = cap >> 2;
   const int lane = (int)lane_id(), warp = threadIdx.x >> 5;
-  const int rw = 1 + A.nlanes;
+  const int rw = 1 + A.nlanes_out;
   for (uint64_t b0 = (uint64_t)blockIdx.x * 256; b0 < nb; b0 += (uint64_t)gridDim.x * 256) {
     const uint64_t b = b0 + threadIdx.x;
     uint64_t k[4] = {EMPTY, EMPTY, EMPTY, EMPTY};
-    if (b < nb)
-      asm volatile("ld.global.nc.v4.u64 {%0, %1, %2, %3}, [%4];"
-                   : "=l"(k[0]), "=l"(k[1]), "=l"(k[2]), "=l"(k[3]) : "l"(keys + b * 4));
-    uint32_t mine = 0;
-#pragma unroll
-    for (int j = 0; j < 4; ++j) mine += (k[j] != EMPTY);
+    const uint32_t occ = (b < nb) ? bucket_keys(keys, vals, A, L, b, k) : 0u;
+    const uint32_t mine = __popc(occ);
     uint32_t incl = mine;
 #pragma unroll
     for (int d = 1; d < 32; d <<= 1) {
@@ -358,10 +386,10 @@ __global__ void __launch_bounds__(256) agg_extract_rows_kernel(const uint64_t* _
     int64_t o = (int64_t)tile_base + warp_tot[warp] + (incl - mine);
 #pragma unroll
     for (int j = 0; j < 4; ++j) {
-      if (k[j] == EMPTY) continue;
+      if (!((occ >> j) & 1)) continue;
       if (o < out_cap) {
         out_rows[o * rw] = (int64_t)k[j];
-        for (int l = 0; l < A.nlanes; ++l) out_rows[o * rw + 1 + l] = vals[(b * 4 + j) * L + l];
+        for (int l = 0; l < A.nlanes_out; ++l) out_rows[o * rw + 1 + l] = vals[(b * 4 + j) * L + l];
       }
       ++o;
     }
@@ -493,10 +521,13 @@ static inline int grid_for(int64_t n) {
   return (int)g;
 }
 
+static inline int lane_stride(int nlanes) { return nlanes <= 1 ? 1 : nlanes <= 2 ? 2 : nlanes <= 4 ? 4 : 8; }
+
 static int fill_desc(AggDesc& A, int nlanes, const int* ops, const int64_t* const* in) {
   if (nlanes < 0 || nlanes > DRYAD_MAX_LANES) return DRYAD_ERR_BAD_ARG;
-  A.nlanes = nlanes;
-  A.in_stride = 1;
+  A.nlanes = nlanes; A.nlanes_out = nlanes;
+  A.in_stride = 1; A.direct = 0; A.occ_lane = 0; A.key_lo = 0;
+  A.src_stride = lane_stride(nlanes);
   for (int l = 0; l < DRYAD_MAX_LANES; ++l) { A.op[l] = 0; A.in[l] = nullptr; }
   for (int l = 0; l < nlanes; ++l) {
     if (ops[l] < 0 || ops[l] > DRYAD_AGG_MAX_F64) return DRYAD_ERR_BAD_ARG;
@@ -508,8 +539,6 @@ static int fill_desc(AggDesc& A, int nlanes, const int* ops, const int64_t* cons
 
 // table capacities: any multiple of the 4-key bucket
 static inline bool cap_ok(uint64_t x) { return x >= 4 && (x & 3) == 0; }
-
-static inline int lane_stride(int nlanes) { return nlanes <= 1 ? 1 : nlanes <= 2 ? 2 : nlanes <= 4 ? 4 : 8; }
 
 #define DRYAD_DISPATCH_L(nl, CALL)                 \
   switch (lane_stride(nl)) {                       \
@@ -559,6 +588,108 @@ int dryad_hash_agg_merge_peers(const uint64_t* tbl_keys, uint64_t cap, int nlane
   for (int r = 0; r < world; ++r) { T.keys[r] = peer_keys[r]; T.vals[r] = peer_vals[r]; }
   int64_t g = ((int64_t)cap + 255) / 256; if (g > 148 * 16) g = 148 * 16;
   DRYAD_DISPATCH_L(nlanes, (agg_merge_peers_kernel<L><<<(int)g, 256, 0, (cudaStream_t)stream>>>(tbl_keys, cap, A, tbl_vals, T, status)));
+  DRYAD_LAUNCH_CHECK();
+  return DRYAD_OK;
+}
+
+// One pass min/max of a signed 64-bit column (key-range statistics for the dense-key decision).
+__global__ void minmax_init_kernel(long long* out) { out[0] = INT64_MAX; out[1] = INT64_MIN; }
+__global__ void __launch_bounds__(256) minmax_kernel(const long long* __restrict__ x, int64_t n, long long* out) {
+  long long lo = INT64_MAX, hi = INT64_MIN;
+  int64_t i = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) * 2;
+  const int64_t stride = (int64_t)gridDim.x * blockDim.x * 2;
+  for (; i + 1 < n; i += stride) {
+    const longlong2 v = __ldcs(reinterpret_cast<const longlong2*>(x + i));
+    lo = min(lo, min(v.x, v.y)); hi = max(hi, max(v.x, v.y));
+  }
+  if (i < n) { const long long v = x[i]; lo = min(lo, v); hi = max(hi, v); }
+#pragma unroll
+  for (int d = 16; d > 0; d >>= 1) {
+    lo = min(lo, __shfl_xor_sync(0xffffffffu, lo, d));
+    hi = max(hi, __shfl_xor_sync(0xffffffffu, hi, d));
+  }
+  __shared__ long long slo[8], shi[8];
+  if ((threadIdx.x & 31) == 0) { slo[threadIdx.x >> 5] = lo; shi[threadIdx.x >> 5] = hi; }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    for (int w = 1; w < 8; ++w) { lo = min(lo, slo[w]); hi = max(hi, shi[w]); }
+    atomicMin(out, lo); atomicMax(out + 1, hi);
+  }
+}
+
+// ---- direct-addressed tables: dense key ranges need neither a key array nor probing ----------
+// slot = key - key_lo.  Occupancy is a row counter: the table's own COUNT lane when it has one,
+// else a hidden COUNT lane appended after the user lanes (so the lane stride may grow).
+static int fill_direct(AggDesc& A, int nlanes, const int* ops, const int64_t* const* in, uint64_t key_lo) {
+  int rc = fill_desc(A, nlanes, ops, in); if (rc) return rc;
+  A.direct = 1; A.key_lo = key_lo; A.occ_lane = -1;
+  for (int l = 0; l < nlanes; ++l) if (ops[l] == DRYAD_AGG_COUNT) { A.occ_lane = l; break; }
+  if (A.occ_lane < 0) {
+    if (nlanes >= DRYAD_MAX_LANES) return DRYAD_ERR_BAD_ARG;
+    A.op[nlanes] = DRYAD_AGG_COUNT; A.in[nlanes] = nullptr; A.occ_lane = nlanes; A.nlanes = nlanes + 1;
+  }
+  A.src_stride = lane_stride(A.nlanes);
+  return DRYAD_OK;
+}
+
+int dryad_minmax_i64(const int64_t* x, int64_t n, int64_t* out_min_max, void* stream) {
+  if (((uintptr_t)x & 15) != 0) return DRYAD_ERR_BAD_ARG;
+  minmax_init_kernel<<<1, 1, 0, (cudaStream_t)stream>>>((long long*)out_min_max);
+  DRYAD_LAUNCH_CHECK();
+  if (n <= 0) return DRYAD_OK;
+  int64_t g = (n + 2047) / 2048; if (g > 148 * 8) g = 148 * 8;
+  minmax_kernel<<<(int)g, 256, 0, (cudaStream_t)stream>>>((const long long*)x, n, (long long*)out_min_max);
+  DRYAD_LAUNCH_CHECK();
+  return DRYAD_OK;
+}
+
+int dryad_hash_agg_direct_lane_stride(int nlanes, const int* ops) {
+  AggDesc A; if (fill_direct(A, nlanes, ops, nullptr, 0)) return -1;
+  return lane_stride(A.nlanes);
+}
+
+int dryad_hash_agg_init_direct(int64_t* tbl_vals, uint64_t cap, int nlanes, const int* ops, void* stream) {
+  if (!cap_ok(cap)) return DRYAD_ERR_BAD_ARG;
+  AggDesc A; int rc = fill_direct(A, nlanes, ops, nullptr, 0); if (rc) return rc;
+  DRYAD_DISPATCH_L(A.nlanes, (agg_init_kernel<L><<<grid_for((int64_t)cap * L), 256, 0, (cudaStream_t)stream>>>(nullptr, cap, A, tbl_vals)));
+  DRYAD_LAUNCH_CHECK();
+  return DRYAD_OK;
+}
+
+/* Raw rows only (COUNT lanes count rows).  status 4: a key fell outside [key_lo, key_lo + cap). */
+int dryad_hash_agg_update_direct(int64_t* tbl_vals, uint64_t cap, int nlanes, const int* ops, uint64_t key_lo,
+                                 const uint64_t* in_keys, const int64_t* const* in_lanes, int64_t n,
+                                 int32_t* status, void* stream) {
+  if (!cap_ok(cap)) return DRYAD_ERR_BAD_ARG;
+  if (n <= 0) return DRYAD_OK;
+  AggDesc A; int rc = fill_direct(A, nlanes, ops, in_lanes, key_lo); if (rc) return rc;
+  int64_t g = (n + 255) / 256; if (g > 148 * 16) g = 148 * 16;
+  DRYAD_DISPATCH_L(A.nlanes, (agg_update_kernel<L><<<(int)g, 256, 0, (cudaStream_t)stream>>>(nullptr, cap, A, tbl_vals, in_keys, n, 0, status)));
+  DRYAD_LAUNCH_CHECK();
+  return DRYAD_OK;
+}
+
+int dryad_hash_agg_extract_direct(const int64_t* tbl_vals, uint64_t cap, int nlanes, const int* ops, uint64_t key_lo,
+                                  uint64_t* out_keys, int64_t* const* out_lanes_dev, unsigned long long* out_count,
+                                  int64_t out_cap, void* stream) {
+  if (!cap_ok(cap)) return DRYAD_ERR_BAD_ARG;
+  AggDesc A; int rc = fill_direct(A, nlanes, ops, nullptr, key_lo); if (rc) return rc;
+  DRYAD_DISPATCH_L(A.nlanes, (agg_extract_kernel<L><<<grid_for((int64_t)cap), 256, 0, (cudaStream_t)stream>>>(nullptr, cap, A, tbl_vals, out_keys, out_lanes_dev, out_count, out_cap)));
+  DRYAD_LAUNCH_CHECK();
+  return DRYAD_OK;
+}
+
+/* Local direct table -> the key owners' HASHED tables (lane stride of nlanes user lanes). */
+int dryad_hash_agg_merge_peers_direct(const int64_t* tbl_vals, uint64_t cap, int nlanes, const int* ops, uint64_t key_lo,
+                                      int world, uint64_t* const* peer_keys, int64_t* const* peer_vals,
+                                      uint64_t peer_cap, int32_t* status, void* stream) {
+  if (!cap_ok(cap) || !cap_ok(peer_cap) || world < 1 || world > DRYAD_MAX_PEERS) return DRYAD_ERR_BAD_ARG;
+  AggDesc A; int rc = fill_direct(A, nlanes, ops, nullptr, key_lo); if (rc) return rc;
+  PeerTables T; T.world = world; T.cap = peer_cap;
+  for (int r = 0; r < DRYAD_MAX_PEERS; ++r) { T.keys[r] = nullptr; T.vals[r] = nullptr; }
+  for (int r = 0; r < world; ++r) { T.keys[r] = peer_keys[r]; T.vals[r] = peer_vals[r]; }
+  int64_t g = ((int64_t)cap + 255) / 256; if (g > 148 * 16) g = 148 * 16;
+  DRYAD_DISPATCH_L(nlanes, (agg_merge_peers_kernel<L><<<(int)g, 256, 0, (cudaStream_t)stream>>>(nullptr, cap, A, tbl_vals, T, status)));
   DRYAD_LAUNCH_CHECK();
   return DRYAD_OK;
 }

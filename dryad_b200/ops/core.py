@@ -323,6 +323,80 @@ class HashAggTable:
         return out_keys[:m], out_lanes[:, :m]
 
 
+def minmax_i64(col: torch.Tensor) -> torch.Tensor:
+    """[min, max] of an int64 column in one pass (device tensor of 2; no host sync)."""
+    require_cuda(col)
+    out = torch.empty(2, dtype=torch.int64, device=col.device)
+    N.check(N.kernels().dryad_minmax_i64(ptr(col), col.numel(), ptr(out), stream()), "minmax_i64")
+    _count(2)
+    return out
+
+
+class DirectAggTable:
+    """Aggregation table for a DENSE key range [key_lo, key_lo + cap): the key is the slot, so an
+    update is one lane-paired reduction per row with no probe (csrc/kernels/hash_table.cu, direct
+    mode).  Same extract / merge contract as HashAggTable; raw-row updates only."""
+
+    def __init__(self, key_lo: int, span: int, ops: Sequence[str], device):
+        self.key_lo = int(key_lo)
+        self.cap = max((int(span) + 3) // 4 * 4, 64)
+        self.ops = list(ops)
+        self.nl = len(self.ops)
+        self._ops_c = (C.c_int * max(self.nl, 1))(*[AGG[o] for o in self.ops])
+        self.stride = N.kernels().dryad_hash_agg_direct_lane_stride(self.nl, self._ops_c)
+        if self.stride < 1:
+            raise ValueError("too many aggregate lanes for a direct table")
+        self.device = device
+        self.vals = torch.empty((self.cap, self.stride), dtype=torch.int64, device=device)
+        self.status = torch.zeros(1, dtype=torch.int32, device=device)
+        self.reset()
+
+    def _lo(self) -> int:
+        return self.key_lo & ((1 << 64) - 1)
+
+    def reset(self, key_lo: Optional[int] = None):
+        if key_lo is not None:
+            self.key_lo = int(key_lo)
+        N.check(N.kernels().dryad_hash_agg_init_direct(ptr(self.vals), self.cap, self.nl, self._ops_c, stream()),
+                "hash_agg_init_direct")
+        self.status.zero_()
+        _count()
+
+    def update(self, keys: torch.Tensor, cols: Sequence[Optional[torch.Tensor]]):
+        require_cuda(keys, *[c for c in cols if c is not None])
+        in_c = (C.c_void_p * max(self.nl, 1))(*[None if c is None else c.data_ptr() for c in cols]) if self.nl else (C.c_void_p * 1)()
+        N.check(N.kernels().dryad_hash_agg_update_direct(ptr(self.vals), self.cap, self.nl, self._ops_c, self._lo(),
+                                                         ptr(keys), in_c, keys.numel(), ptr(self.status), stream()),
+                "hash_agg_update_direct")
+        _count()
+
+    def merge_into_peers(self, world: int, peer_keys_ptrs: Sequence[int], peer_vals_ptrs: Sequence[int], peer_cap: int):
+        pk = (C.c_void_p * world)(*peer_keys_ptrs)
+        pv = (C.c_void_p * world)(*peer_vals_ptrs)
+        N.check(N.kernels().dryad_hash_agg_merge_peers_direct(ptr(self.vals), self.cap, self.nl, self._ops_c, self._lo(),
+                                                              world, pk, pv, peer_cap, ptr(self.status), stream()),
+                "hash_agg_merge_peers_direct")
+        _count()
+
+    def extract(self, max_out: Optional[int] = None):
+        max_out = self.cap if max_out is None else max_out
+        out_keys = torch.empty(max_out, dtype=torch.int64, device=self.device)
+        out_lanes = torch.empty((max(self.nl, 1), max_out), dtype=torch.int64, device=self.device)
+        lane_ptrs = torch.tensor([out_lanes[l].data_ptr() for l in range(max(self.nl, 1))], dtype=torch.int64).to(self.device)
+        cnt = torch.zeros(1, dtype=torch.int64, device=self.device)
+        N.check(N.kernels().dryad_hash_agg_extract_direct(ptr(self.vals), self.cap, self.nl, self._ops_c, self._lo(),
+                                                          ptr(out_keys), ptr(lane_ptrs), ptr(cnt), max_out, stream()),
+                "hash_agg_extract_direct")
+        _count()
+        m = int(cnt.item())
+        st = int(self.status.item())
+        if st == 4:
+            raise N.NativeError("direct aggregate table: key outside the declared range")
+        if st == 3:
+            raise OverflowError("checked int64 Sum overflowed")
+        return out_keys[:m], out_lanes[:, :m]
+
+
 # ---- K8 / K10 --------------------------------------------------------------------------------
 class JoinTable:
     def __init__(self, build_keys: torch.Tensor, load: float = 0.5):

@@ -260,6 +260,22 @@ def _group_by(be, node, part, inputs, env):
         combine = False
     cap = max(1024, min(2 * n + 64, be.context.group_capacity_hint))
     in_views = [None if c is None else (c.view(torch.int64) if c.dtype == torch.float64 else c.to(torch.int64)) for c in in_cols]
+    # dense integer key range (ids, codes): direct-addressed table, one reduction request per row
+    if n >= (1 << 16) and not combine and not key_is_f and len(lanes) < 8:
+        lo, hi = K.minmax_i64(kbits.contiguous()).tolist()
+        span = hi - lo + 1
+        if span <= 4 * min(n, be.context.group_capacity_hint) and span * 64 <= (1 << 30):
+            try:
+                dt = K.DirectAggTable(lo, span, lanes, be.device)
+                dt.update(kbits.contiguous(), [None if c is None else c.contiguous() for c in in_views])
+                gk, gl = dt.extract()
+                cols_d: Dict[str, torch.Tensor] = {"key": gk}
+                for i, a in enumerate(dec.aggs):
+                    lane = gl[i].contiguous()
+                    cols_d[f"agg{i}"] = lane.view(torch.float64) if lanes[i].endswith("f64") else lane
+                return [ColumnBatch(cols_d, gk.numel(), acc_lanes=len(dec.aggs))]
+            except OverflowError as ex:
+                raise DryadLinqException(ErrorCode.FailureInHashGroupBy, "Arithmetic operation resulted in an overflow.") from ex
     while True:
         tbl = K.HashAggTable(cap, lanes, be.device)
         if n:

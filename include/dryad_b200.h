@@ -171,6 +171,27 @@ int dryad_hash_agg_merge_peers(const uint64_t* tbl_keys, uint64_t cap, int nlane
                                const int64_t* tbl_vals, int world, uint64_t* const* peer_keys,
                                int64_t* const* peer_vals, uint64_t peer_cap, int32_t* status,
                                void* stream);
+/* Direct-addressed tables for DENSE key ranges: slot = key - key_lo, no key array, no probing (one
+ * L2 reduction request per row instead of a probe plus a reduction).  `tbl_vals` has
+ * cap * dryad_hash_agg_direct_lane_stride(nlanes, ops) words: when no lane is a COUNT, a hidden row
+ * counter lane is appended to tell occupied slots apart.  Raw rows only (no `combine`).
+ * status 4: a key outside [key_lo, key_lo + cap).  dryad_minmax_i64 gives the range in one pass
+ * (out_min_max: 2 device words). */
+int dryad_minmax_i64(const int64_t* x, int64_t n, int64_t* out_min_max, void* stream);
+int dryad_hash_agg_direct_lane_stride(int nlanes, const int* ops);
+int dryad_hash_agg_init_direct(int64_t* tbl_vals, uint64_t cap, int nlanes, const int* ops, void* stream);
+int dryad_hash_agg_update_direct(int64_t* tbl_vals, uint64_t cap, int nlanes, const int* ops,
+                                 uint64_t key_lo, const uint64_t* in_keys,
+                                 const int64_t* const* in_lanes, int64_t n, int32_t* status,
+                                 void* stream);
+int dryad_hash_agg_extract_direct(const int64_t* tbl_vals, uint64_t cap, int nlanes, const int* ops,
+                                  uint64_t key_lo, uint64_t* out_keys, int64_t* const* out_lanes_dev,
+                                  unsigned long long* out_count, int64_t out_cap, void* stream);
+int dryad_hash_agg_merge_peers_direct(const int64_t* tbl_vals, uint64_t cap, int nlanes,
+                                      const int* ops, uint64_t key_lo, int world,
+                                      uint64_t* const* peer_keys, int64_t* const* peer_vals,
+                                      uint64_t peer_cap, int32_t* status, void* stream);
+
 /* Packed-row forms: rows of (1 + nlanes) int64 words {key, v[0..nlanes)} — the record the fused
  * shuffle carries when partials are PUSHED to their key owners and folded there locally. */
 int dryad_hash_agg_update_rows(uint64_t* tbl_keys, uint64_t cap, int nlanes, const int* ops,

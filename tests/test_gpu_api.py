@@ -161,3 +161,23 @@ def test_non_decomposable_group_by_and_set_operations_on_gpu():
         assert sorted(qa.intersect(qb).to_list()) == sorted(set(a) & set(b))
         assert sorted(qa.except_(qb).to_list()) == sorted(set(a) - set(b))
         assert ctx._backend().host_fallbacks == 0
+
+
+def test_group_by_dense_integer_keys_uses_direct_table_and_agrees():
+    """Large partitions with a dense integer key range take the direct-addressed aggregate table."""
+    import numpy as np
+    n = 300_000
+    rng = np.random.default_rng(9)
+    k = rng.integers(-50, 4000, n)
+    v = rng.integers(-100, 100, n)
+    ctx = D.DryadLinqContext(1, device="cuda")
+    got = ctx.from_columns({"k": k, "v": v}).group_by(lambda r: r.k).select(
+        lambda g: {"k": g.key, "s": g.sum(lambda r: r.v), "c": g.count(), "mx": g.max(lambda r: r.v)}).to_list()
+    want_s = np.zeros(4050, dtype=np.int64); np.add.at(want_s, k + 50, v)
+    want_c = np.bincount(k + 50, minlength=4050)
+    want_m = np.full(4050, -1000); np.maximum.at(want_m, k + 50, v)
+    assert len(got) == int((want_c > 0).sum())
+    for r in got:
+        j = r["k"] + 50
+        assert (r["s"], r["c"], r["mx"]) == (want_s[j], want_c[j], want_m[j])
+    assert ctx._backend().host_fallbacks == 0

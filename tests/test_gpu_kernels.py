@@ -341,3 +341,38 @@ def test_record_transcoding_round_trip(K):
     assert np.array_equal(cols[2].cpu().numpy(), rec["c"]) and np.array_equal(cols[3].cpu().numpy(), rec["d"])
     back = K.columns_to_rows(cols, [0, 8, 17, 21], 23)
     assert torch.equal(back, rows)
+
+
+def test_direct_addressed_aggregate_matches_torch(K):
+    """Dense key range: slot = key - lo, with a COUNT lane as occupancy or a hidden row counter."""
+    dev = torch.device("cuda")
+    g = torch.Generator(device=dev).manual_seed(23)
+    n, lo, span = 500_003, -1234, 7000
+    keys = torch.randint(lo, lo + span, (n,), dtype=torch.int64, device=dev, generator=g)
+    keys[keys % 7 == 0] = lo + 5                     # leave many slots empty, one heavy
+    vals = torch.randint(-1000, 1000, (n,), dtype=torch.int64, device=dev, generator=g)
+    mm = K.minmax_i64(keys).tolist()
+    assert mm == [int(keys.min()), int(keys.max())]
+    idx = keys - lo
+    want_sum = torch.zeros(span, dtype=torch.int64, device=dev).index_add_(0, idx, vals)
+    want_cnt = torch.bincount(idx, minlength=span)
+    want_max = torch.full((span,), -(1 << 62), dtype=torch.int64, device=dev).scatter_reduce_(0, idx, vals, "amax")
+    for ops, cols in ((["sum_i64", "count"], [vals, None]), (["sum_i64", "max_i64"], [vals, vals]), (["min_i64"], [vals])):
+        t = K.DirectAggTable(lo, span, ops, dev)
+        t.update(keys, cols)
+        gk, gl = t.extract()
+        order = torch.argsort(gk)
+        gk, gl = gk[order], gl[:, order]
+        occ = torch.nonzero(want_cnt > 0).squeeze(1)
+        assert torch.equal(gk, occ + lo), ops
+        for j, op in enumerate(ops):
+            if op == "sum_i64":
+                assert torch.equal(gl[j], want_sum[occ])
+            elif op == "count":
+                assert torch.equal(gl[j], want_cnt[occ])
+            elif op == "max_i64":
+                assert torch.equal(gl[j], want_max[occ])
+    bad = K.DirectAggTable(lo, 64, ["count"], dev)
+    bad.update(keys, [None])
+    with pytest.raises(Exception):
+        bad.extract()
