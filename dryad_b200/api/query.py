@@ -46,7 +46,7 @@ def _fn_from_ir(ir):
     if isinstance(ir, X.Expr):
         return lambda r: X.eval_row(ir, row_of(r))
     if isinstance(ir, X.TupleFields):
-        return lambda r: tuple(X.eval_row(e, row_of(r)) for e in ir.values())
+        return lambda r: ir.build(X.eval_row(e, row_of(r)) for e in ir.values())
     return lambda r: Record((k, X.eval_row(e, row_of(r))) for k, e in ir.items())
 
 

@@ -412,7 +412,14 @@ def trace(fn: Callable, schema: Mapping[str, str], *extra_args) -> Optional[Any]
 
 
 class TupleFields(dict):
-    """A traced tuple result: field dict that materialises back into a Python tuple."""
+    """A traced tuple result: field dict that materialises back into a Python tuple — or into the
+    tuple SUBCLASS the lambda built (`Pair(k, v)`, `ForkTuple(a, b)`), kept in `cls`."""
+
+    cls = tuple
+
+    def build(self, values):
+        values = tuple(values)
+        return values if self.cls is tuple else self.cls(*values)
 
 
 def normalise_traced(out: Any) -> Optional[Any]:
@@ -429,7 +436,10 @@ def normalise_traced(out: Any) -> Optional[Any]:
             res[k] = wrap(v)
         return res
     if isinstance(out, tuple) and out and all(isinstance(v, (Expr, int, float, bool)) for v in out):
-        return TupleFields((f"item{i + 1}", wrap(v)) for i, v in enumerate(out))
+        tf = TupleFields((f"item{i + 1}", wrap(v)) for i, v in enumerate(out))
+        if type(out) is not tuple:
+            tf.cls = type(out)
+        return tf
     if isinstance(out, (int, float, bool)):
         return lit(out)
     return None

@@ -120,7 +120,7 @@ class DecompositionInfo:
         """Apply the final reducer on the host: evaluate `result` with leaves bound."""
         env = _LeafEnv(key, [a.finalize(v) for a, v in zip(self.aggs, accs)], self.key_schema)
         if isinstance(self.result, X.TupleFields):
-            return tuple(_eval_with_leaves(e, env) for e in self.result.values())
+            return self.result.build(_eval_with_leaves(e, env) for e in self.result.values())
         if isinstance(self.result, dict):
             from ..api.types import Record
             return Record((k, _eval_with_leaves(e, env)) for k, e in self.result.items())

@@ -141,5 +141,7 @@ class ColumnBatch:
         if names == ["value"]:
             return host["value"]
         if self.tuple_like:
-            return list(zip(*[host[k] for k in names]))
+            cls = self.tuple_like if isinstance(self.tuple_like, type) else tuple
+            rows = zip(*[host[k] for k in names])
+            return list(rows) if cls is tuple else [cls(*r) for r in rows]
         return [Record(zip(names, vals)) for vals in zip(*[host[k] for k in names])]

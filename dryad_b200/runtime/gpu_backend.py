@@ -20,6 +20,11 @@ from . import vertex_ops
 from .columnar import ROW_COL, ColumnBatch
 
 
+def _tuple_cls(ir):
+    """False for record / scalar results; else the tuple class the lambda built (tuple, Pair, ...)."""
+    return ir.cls if isinstance(ir, X.TupleFields) else False
+
+
 def _numeric_schema(schema) -> bool:
     return bool(schema) and all(k in ("i", "f", "b") for k in schema.values())
 
@@ -152,14 +157,14 @@ def _select(be, node, part, inputs, env):
         res = dec.result
         proj = {k: _bind_leaves(e, kinds) for k, e in res.items()} if isinstance(res, dict) else {"value": _bind_leaves(res, kinds)}
         out, _ = run_on_gpu(proj, src.cols, src.n)
-        return [ColumnBatch(out, src.n, tuple_like=isinstance(res, X.TupleFields))]
+        return [ColumnBatch(out, src.n, tuple_like=_tuple_cls(res))]
     if p["indexed"]:
         return NotImplemented
     proj = _proj_of(p["fn"])
     if proj is None:
         return NotImplemented
     out, _ = run_on_gpu(proj, src.cols, src.n)
-    return [ColumnBatch(out, src.n, tuple_like=isinstance(p["fn"].ir, X.TupleFields))]
+    return [ColumnBatch(out, src.n, tuple_like=_tuple_cls(p["fn"].ir))]
 
 
 def _where(be, node, part, inputs, env):
@@ -556,7 +561,7 @@ def _join(be, node, part, inputs, env):
         proj = res if isinstance(res, dict) else {"value": res}
         dt = {"i": torch.int64, "f": torch.float64, "b": torch.bool}
         return [ColumnBatch({k: torch.empty(0, dtype=dt[e.kind], device=be.device) for k, e in proj.items()}, 0,
-                            tuple_like=isinstance(res, X.TupleFields))]
+                            tuple_like=_tuple_cls(res))]
     if use_merge:                                        # both inputs are key-sorted: merge join (K9)
         desc = bool(p.get("descending"))
         okb = K.sort_key_bits(_typed_key(outer, p["outer_key"], ok), descending=desc).contiguous()
@@ -576,7 +581,7 @@ def _join(be, node, part, inputs, env):
     if not op.numel():
         dt = {"i": torch.int64, "f": torch.float64, "b": torch.bool}
         out = {k: torch.empty(0, dtype=dt[e.kind], device=be.device) for k, e in proj.items()}
-    return [ColumnBatch(out, op.numel(), tuple_like=isinstance(res, X.TupleFields))]
+    return [ColumnBatch(out, op.numel(), tuple_like=_tuple_cls(res))]
 
 
 def _join_fused(be, jt, outer: ColumnBatch, inner: ColumnBatch, ok: torch.Tensor, res):
@@ -614,7 +619,7 @@ def _join_fused(be, jt, outer: ColumnBatch, inner: ColumnBatch, ok: torch.Tensor
     except (CompileError, X.TraceError):
         return None
     idx, m = K.compact_flags(flags)
-    batch = ColumnBatch(out, outer.n, tuple_like=isinstance(res, X.TupleFields))
+    batch = ColumnBatch(out, outer.n, tuple_like=_tuple_cls(res))
     return [batch.take(idx)]
 
 

@@ -87,3 +87,18 @@ def test_checked_sum_overflow_raises():
     with pytest.raises(Exception) as ei:
         D.DryadLinqContext(1).from_enumerable(big).group_by(lambda x: 0).select(lambda g: g.sum()).to_list()
     assert "overflow" in str(ei.value).lower()
+
+
+def test_pair_results_keep_their_type_through_decomposition_and_sorting():
+    """`new Pair(g.Key, g.Count())` stays a Pair (`.key` / `.value`) after the decomposed GroupBy,
+    so later operators can use its members (the WordCount sample's OrderByDescending(p => p.Value))."""
+    import dryad_b200 as D
+    words = ("a b c a b a d d d d".split()) * 3
+    for ctx in (D.DryadLinqContext(1, local_debug=True), D.DryadLinqContext(3)):
+        q = (ctx.from_enumerable(words, 3 if not ctx.local_debug else 1).group_by(lambda w: w)
+             .select(lambda g: D.Pair(g.key, g.count())).order_by_descending(lambda p: p.value).take(2))
+        got = q.to_list()
+        assert got == [D.Pair("d", 12), D.Pair("a", 9)] and all(isinstance(p, D.Pair) for p in got)
+    nums = list(range(100))
+    r = D.DryadLinqContext(2).from_enumerable(nums, 2).select(lambda x: D.Pair(x % 5, x * 2)).where(lambda p: p.key == 3).to_list()
+    assert r and all(isinstance(p, D.Pair) and p.key == 3 for p in r)
