@@ -23,7 +23,7 @@ from .symm import SymmetricArena
 
 
 class BroadcastJoin:
-    def __init__(self, arena: SymmetricArena, dim_rows_total: int, ncols: int, load: float = 0.5):
+    def __init__(self, arena: SymmetricArena, dim_rows_total: int, ncols: int, load: float = 0.5, use_nvls: bool = True):
         self.arena, self.world, self.rank = arena, arena.world, arena.rank
         self.nrows, self.ncols = int(dim_rows_total), ncols
         self.cap = K._next_pow2(int(dim_rows_total / load) + 64)
@@ -31,12 +31,27 @@ class BroadcastJoin:
         self.keys, ko = arena.alloc((self.cap,), torch.int64)
         self.head, ho = arena.alloc((self.cap,), torch.int32)
         self.next, no = arena.alloc((max(self.nrows, 1),), torch.int32)
-        self.rkeys, rko = arena.alloc((max(self.nrows, 1),), torch.int64)     # replicated key column
+        # the replicated small side lives in an NVLS buffer when the box has multicast: one store
+        # per 16 bytes reaches every GPU (K17 nvls_broadcast_copy) instead of `world` P2P stores
+        from .nvls import NvlsBuffer
+        nr = max(self.nrows, 1)
+        self.nvls = NvlsBuffer.create((ncols + 1) * (nr * 8 + 256) + 4096, dev, self.rank, self.world) if use_nvls else None
         self.cols, offs = [], []
-        for _ in range(ncols):
-            t, o = arena.alloc((max(self.nrows, 1),), torch.int64)
-            self.cols.append(t)
-            offs.append(o)
+        if self.nvls is not None:
+            self.rkeys, self._nv_key_off = self.nvls.alloc((nr,), torch.int64)
+            self._nv_col_off = []
+            for _ in range(ncols):
+                t, o = self.nvls.alloc((nr,), torch.int64)
+                self.cols.append(t)
+                self._nv_col_off.append(o)
+            rko = 0
+            offs = [0] * ncols
+        else:
+            self.rkeys, rko = arena.alloc((nr,), torch.int64)     # replicated key column
+            for _ in range(ncols):
+                t, o = arena.alloc((nr,), torch.int64)
+                self.cols.append(t)
+                offs.append(o)
         arena.check_symmetric("BroadcastJoin tables")
         W = self.world
         self._pk = (C.c_void_p * W)(*[arena.peer_ptr(r, ko) for r in range(W)])
@@ -53,10 +68,23 @@ class BroadcastJoin:
         lib = N.kernels()
         if self.world > 1:
             self.arena.barrier(slot=2)             # nobody still probes the previous replica
-        src = (C.c_void_p * (self.ncols + 1))(keys_local.data_ptr(), *[c.data_ptr() for c in cols_local])
-        N.check(lib.dryad_replicate_slice(self.world, self.ncols + 1, src, self._prepl, keys_local.numel(), row_base,
-                                          K.stream()), "replicate_slice")
-        K._count()
+        nl = keys_local.numel()
+        if self.nvls is not None and row_base % 2 == 0 and nl % 2 == 0:
+            self.nvls.broadcast(self._nv_key_off + row_base * 8, keys_local.contiguous())
+            for c, o in zip(cols_local, self._nv_col_off):
+                self.nvls.broadcast(o + row_base * 8, c.contiguous())
+        elif self.nvls is not None:
+            # odd slice boundaries are not 16-byte aligned: plain stores into every copy
+            for r in range(self.world):
+                from .symm import tensor_from_ptr
+                dev = keys_local.device
+                for t, o in [(keys_local, self._nv_key_off)] + list(zip(cols_local, self._nv_col_off)):
+                    tensor_from_ptr(self.nvls.peer_ptrs[r] + o + row_base * 8, nl * 8, dev).view(torch.int64).copy_(t, non_blocking=True)
+        else:
+            src = (C.c_void_p * (self.ncols + 1))(keys_local.data_ptr(), *[c.data_ptr() for c in cols_local])
+            N.check(lib.dryad_replicate_slice(self.world, self.ncols + 1, src, self._prepl, nl, row_base,
+                                              K.stream()), "replicate_slice")
+            K._count()
         if self.world > 1:
             self.arena.barrier(slot=3)             # all slices have landed everywhere
         N.check(lib.dryad_join_build(K.ptr(self.keys), K.ptr(self.head), self.cap, K.ptr(self.rkeys), K.ptr(self.next),
@@ -67,6 +95,8 @@ class BroadcastJoin:
         """Alternative single-kernel form: insert into every rank's table with system-scope atomics
         over NVLink (kept for comparison; slower at 8 GPUs than replicate + local build)."""
         lib = N.kernels()
+        if self.nvls is not None:
+            raise RuntimeError("build_remote_atomics needs the P2P replica layout: construct with use_nvls=False")
         N.check(lib.dryad_join_table_init(K.ptr(self.keys), K.ptr(self.head), self.cap, K.stream()), "join_table_init")
         K._count()
         if self.world > 1:

@@ -1,5 +1,7 @@
 """Distributed k-means iteration (K19 + C3): tcgen05 assign/accumulate kernel per GPU, then an
-all-reduce of (sums, counts) by peer loads over NVLink and the centroid update — no NCCL.
+all-reduce of (sums, counts) and the centroid update — no NCCL.  The all-reduce runs INSIDE the
+NVSwitch when the box offers NVLS multicast (multimem.ld_reduce + multimem.st on a symmetric buffer,
+parallel/nvls.py); otherwise every rank loads its peers' partials over NVLink in fixed rank order.
 
 Points are sharded by rows (the DP partitioning of the dataset); centroids are replicated.
 """
@@ -17,17 +19,25 @@ D = 128
 
 
 class KMeans:
-    def __init__(self, arena: SymmetricArena, k: int, n_local_max: int):
+    def __init__(self, arena: SymmetricArena, k: int, n_local_max: int, use_nvls: bool = True):
         if k % 128 or k > 2048:
             raise ValueError("k must be a multiple of 128 and at most 2048")
         self.arena, self.k = arena, k
         self.world, self.rank = arena.world, arena.rank
         dev = arena.device
-        self.sums, self.sums_off = arena.alloc((k, D), torch.float32)        # partials, peer-readable
-        self.counts, self.counts_off = arena.alloc((k,), torch.int64)
-        arena.check_symmetric("KMeans partials")
-        self.peer_sums = arena.peer_ptr_table(self.sums_off)
-        self.peer_counts = arena.peer_ptr_table(self.counts_off)
+        from .nvls import NvlsBuffer
+        self.nvls = NvlsBuffer.create(k * D * 4 + k * 8 + 4096, dev, self.rank, self.world) if use_nvls else None
+        if self.nvls is not None:
+            self.sums, self.sums_off = self.nvls.alloc((k, D), torch.float32)
+            self.counts, self.counts_off = self.nvls.alloc((k,), torch.int64)
+            own = lambda t: torch.tensor([t.data_ptr()], dtype=torch.int64).to(dev)   # noqa: E731
+            self.peer_sums, self.peer_counts = own(self.sums), own(self.counts)       # totals are local after the all-reduce
+        else:
+            self.sums, self.sums_off = arena.alloc((k, D), torch.float32)        # partials, peer-readable
+            self.counts, self.counts_off = arena.alloc((k,), torch.int64)
+            arena.check_symmetric("KMeans partials")
+            self.peer_sums = arena.peer_ptr_table(self.sums_off)
+            self.peer_counts = arena.peer_ptr_table(self.counts_off)
         self.centroids = torch.empty((k, D), dtype=torch.float32, device=dev)
         self.cnorm = torch.empty(k, dtype=torch.float32, device=dev)
         self.total_counts = torch.zeros(k, dtype=torch.int64, device=dev)
@@ -55,7 +65,12 @@ class KMeans:
         K._count()
         if self.world > 1:
             self.arena.barrier(slot=3)         # every rank's partials are complete and visible
-        N.check(lib.dryad_kmeans_update(K.ptr(self.peer_sums), K.ptr(self.peer_counts), self.world, self.k,
+        if self.nvls is not None:
+            # in-switch all-reduce, two-shot: every copy ends up with identical totals
+            self.nvls.allreduce_f32(self.sums_off, self.k * D)
+            self.nvls.allreduce_u64(self.counts_off, self.k)
+            self.arena.barrier(slot=2)         # all slices have been multicast back
+        N.check(lib.dryad_kmeans_update(K.ptr(self.peer_sums), K.ptr(self.peer_counts), 1 if self.nvls is not None else self.world, self.k,
                                         K.ptr(self.centroids), K.ptr(self.cnorm), K.ptr(self.total_counts),
                                         K.stream()), "kmeans_update")
         K._count()

@@ -205,6 +205,17 @@ int dryad_hash_agg_extract(const uint64_t* tbl_keys, uint64_t cap, int nlanes, c
                            int64_t* const* out_lanes_dev, unsigned long long* out_count,
                            int64_t out_cap, void* stream);
 
+/* ---- NVLS (NVSwitch multicast / in-switch reduction) ----------------------------------------------
+ * `mc` is the multicast address of a symmetric buffer (every GPU of the group has a copy at the same
+ * offset; the mapping is made by the caller, e.g. torch's symmetric-memory rendezvous).
+ * allreduce: two-shot, in place — rank r pulls the all-GPU sum of slice r out of the switch
+ * (multimem.ld_reduce) and multicasts it back (multimem.st), so all copies hold identical bits.
+ * Barrier across the group before and after.  n in elements (f32: multiple of 4).
+ * broadcast: local `src` -> the same byte range of every copy (nbytes multiple of 16). */
+int dryad_nvls_allreduce_f32(float* mc, int64_t n, int rank, int world, void* stream);
+int dryad_nvls_allreduce_u64(uint64_t* mc, int64_t n, int rank, int world, void* stream);
+int dryad_nvls_broadcast(void* mc_dst, const void* src, int64_t nbytes, void* stream);
+
 /* ---- K7 sort-based grouping, K15 record transcoding ---------------------------------------------
  * mark_boundaries: flags[i] = 1 where a run of equal keys starts in a SORTED key column (compact
  * the flags to get the CSR run starts).  rows_to_columns / columns_to_rows: fixed-stride packed

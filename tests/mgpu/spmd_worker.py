@@ -116,6 +116,31 @@ def gpu_checks(rank, world):
         dist.all_reduce(cnt_g)
         assert int(cnt_g.item()) == int((full_k[1] > 0).sum().item()), merge
 
+    # 3a. NVLS: in-switch all-reduce and multicast copy on a symmetric buffer (when the box has it)
+    from dryad_b200.parallel.nvls import NvlsBuffer
+    nv = NvlsBuffer.create(8 << 20, dev, rank, world)
+    if nv is not None:
+        xf, xo = nv.alloc((1 << 18,), torch.float32)
+        xu, uo = nv.alloc((4099,), torch.int64)
+        bd, bo = nv.alloc((world, 4096), torch.int64)
+        gg = torch.Generator(device=dev).manual_seed(50 + rank)
+        mine_f = torch.randint(-1000, 1000, (1 << 18,), device=dev, generator=gg).float()
+        mine_u = torch.randint(0, 1 << 40, (4099,), dtype=torch.int64, device=dev, generator=gg)
+        xf.copy_(mine_f); xu.copy_(mine_u); bd.zero_()
+        want_f, want_u = mine_f.clone(), mine_u.clone()
+        dist.all_reduce(want_f); dist.all_reduce(want_u)
+        arena.barrier(slot=2)
+        nv.allreduce_f32(xo, 1 << 18)
+        nv.allreduce_u64(uo, 4099)
+        nv.broadcast(bo + rank * 4096 * 8, torch.full((4096,), rank + 1, dtype=torch.int64, device=dev))
+        arena.barrier(slot=3)
+        torch.cuda.synchronize()
+        assert torch.equal(xf, want_f) and torch.equal(xu, want_u)          # integer-valued floats: exact
+        assert torch.equal(bd, (torch.arange(world, device=dev) + 1)[:, None].expand(world, 4096))
+        nvls_on = True
+    else:
+        nvls_on = False
+
     # 3b. broadcast join: the small side is replicated by the build kernel, the fact side stays put
     from dryad_b200.models import joins
     jr = joins.bench(rank, world, dev, 1_000_000, 50_000, steps=1, warmup=1,
