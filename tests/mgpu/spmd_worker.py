@@ -41,6 +41,21 @@ def cpu_checks(rank, world):
     allp = [None] * world
     dist.all_gather_object(allp, win)
     assert sum(allp, []) == [sum(seq[j:j + 4]) for j in range(len(seq) - 3)], allp
+    # streamed rank-to-rank channel (pointwise FIFO edge): blocks flow while the producer still produces
+    from dryad_b200.channel.pipe import PipeReader, PipeWriter
+    if world >= 2 and rank < 2:
+        if rank == 0:
+            w = PipeWriter(1, "cpu", depth=4)
+            for j in range(10):
+                w.write(torch.arange(1000 * j, 1000 * j + 777, dtype=torch.int64))
+            w.write(torch.linspace(0, 1, 33, dtype=torch.float64))
+            w.close()
+            assert w.blocks == 11
+        else:
+            got = list(PipeReader(0, "cpu"))
+            assert len(got) == 11 and got[-1].dtype == torch.float64 and got[-1].numel() == 33
+            assert all(torch.equal(got[j], torch.arange(1000 * j, 1000 * j + 777, dtype=torch.int64)) for j in range(10))
+    dist.barrier()
     # scalar aggregate lands on rank 0
     total = ctx.from_enumerable(vals, world).sum_as_query().partitions()[0]
     if rank == 0:
@@ -159,6 +174,20 @@ def gpu_checks(rank, world):
     dist.all_gather(allc, km.centroids)
     assert all(torch.equal(allc[0], c) for c in allc)
     assert int(km.total_counts.sum().item()) == 200_000 * world
+
+    # 3d. streamed channel between GPUs (NCCL p2p on a side stream, overlapped with the producer)
+    from dryad_b200.channel.pipe import PipeReader, PipeWriter
+    if rank < 2:
+        if rank == 0:
+            w = PipeWriter(1, dev, depth=4)
+            for j in range(8):
+                blk = torch.full((1 << 20,), j, dtype=torch.int64, device=dev) * 3 + 1    # produced on the compute stream
+                w.write(blk)
+            w.close()
+        else:
+            got = list(PipeReader(0, dev))
+            assert len(got) == 8 and all(int(b[0]) == 3 * j + 1 and int(b.sum()) == (3 * j + 1) * (1 << 20) for j, b in enumerate(got))
+    dist.barrier()
 
     # 4. the same sort through the public API (SPMD executor -> RowSorter)
     ctx = D.DryadLinqContext(platform="B200", device=str(dev))
