@@ -1,7 +1,8 @@
 """Distributed joins.
 
-`BroadcastJoin` (K8 + C4): the small side is replicated to every GPU by the build kernel itself
-(stores + system atomics on peer HBM), then every rank probes its own fact partition locally — the
+`BroadcastJoin` (K8 + C4): the small side is replicated to every GPU — one NVLS multicast store per
+16 bytes when the box has NVSwitch multicast (parallel/nvls.py), else P2P stores to every peer — the
+hash table is built locally over the replica, then every rank probes its own fact partition: the
 large side never moves.  The reference expresses this as Tee + CrossProduct + Merge(parCount) feeding
 a HashJoin (LinqToDryad/DryadLinqQueryGen.cs:2957-3001); the planner rule that picks it by size is
 QueryGen._visit_join.
@@ -75,9 +76,9 @@ class BroadcastJoin:
                 self.nvls.broadcast(o + row_base * 8, c.contiguous())
         elif self.nvls is not None:
             # odd slice boundaries are not 16-byte aligned: plain stores into every copy
+            from .symm import tensor_from_ptr
+            dev = keys_local.device
             for r in range(self.world):
-                from .symm import tensor_from_ptr
-                dev = keys_local.device
                 for t, o in [(keys_local, self._nv_key_off)] + list(zip(cols_local, self._nv_col_off)):
                     tensor_from_ptr(self.nvls.peer_ptrs[r] + o + row_base * 8, nl * 8, dev).view(torch.int64).copy_(t, non_blocking=True)
         else:
