@@ -371,8 +371,14 @@ __device__ __forceinline__ float4 lds_f4(uint32_t saddr) {
   asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "r"(saddr));
   return v;
 }
-__device__ __forceinline__ float pack_idx(float d, int idx) {
-  return __uint_as_float((__float_as_uint(d) & 0xFFFFFF80u) | (uint32_t)idx);
+// (d & mask) | idx as ONE three-input LOP3 (and + or with two immediates compiled to two
+// instructions: ncu showed 2.1 LOP3 per accumulator column, the largest stall bucket of the scan).
+// `mask` must be a value the assembler cannot fold (the kernel derives it from a run-time argument):
+// then it lives in one register and every column index becomes the instruction's immediate.
+__device__ __forceinline__ float pack_idx(float d, int idx, uint32_t mask) {
+  uint32_t r;
+  asm("lop3.b32 %0, %1, %2, %3, 0xEA;" : "=r"(r) : "r"(__float_as_uint(d)), "r"(mask), "r"((uint32_t)idx));
+  return __uint_as_float(r);
 }
 
 struct Bars2 {
@@ -526,6 +532,7 @@ km_assign_pair(const __grid_constant__ CUtensorMap map_x, const __grid_constant_
     // bits of the distance, so a running fminf carries value and index together (relative error
     // 2^-16, far below the TF32 product noise); four independent minima per thread.
     constexpr int PARTS = EW / 4, COLS = BN2 / PARTS, SUBS = COLS / 32;
+    const uint32_t pmask = 0xFFFFFF80u | ((uint32_t)k >> 31);      // = 0xFFFFFF80, opaque to the assembler
     const int ew = warp - 2;
     const int q = warp & 3;                         // TMEM lane quarter this warp may read
     const int part = ew >> 2;
@@ -556,10 +563,10 @@ km_assign_pair(const __grid_constant__ CUtensorMap map_x, const __grid_constant_
 #pragma unroll
         for (int j = 0; j < G; j += 4) {                          // ... while A is reduced
           const float4 n4 = lds_f4(cn_s + j * 4);
-          m0 = fminf(m0, pack_idx(fmaf(-2.f, __uint_as_float(va[j]), n4.x), j));
-          m1 = fminf(m1, pack_idx(fmaf(-2.f, __uint_as_float(va[j + 1]), n4.y), j + 1));
-          m2 = fminf(m2, pack_idx(fmaf(-2.f, __uint_as_float(va[j + 2]), n4.z), j + 2));
-          m3 = fminf(m3, pack_idx(fmaf(-2.f, __uint_as_float(va[j + 3]), n4.w), j + 3));
+          m0 = fminf(m0, pack_idx(fmaf(-2.f, __uint_as_float(va[j]), n4.x), j, pmask));
+          m1 = fminf(m1, pack_idx(fmaf(-2.f, __uint_as_float(va[j + 1]), n4.y), j + 1, pmask));
+          m2 = fminf(m2, pack_idx(fmaf(-2.f, __uint_as_float(va[j + 2]), n4.z), j + 2, pmask));
+          m3 = fminf(m3, pack_idx(fmaf(-2.f, __uint_as_float(va[j + 3]), n4.w), j + 3, pmask));
         }
         tc_ld_wait();                                             // the whole chunk has left TMEM
         tc_fence_before();
@@ -573,10 +580,10 @@ km_assign_pair(const __grid_constant__ CUtensorMap map_x, const __grid_constant_
 #pragma unroll
         for (int j = 0; j < G; j += 4) {
           const float4 n4 = lds_f4(cn_s + (G + j) * 4);
-          m0 = fminf(m0, pack_idx(fmaf(-2.f, __uint_as_float(vb[j]), n4.x), G + j));
-          m1 = fminf(m1, pack_idx(fmaf(-2.f, __uint_as_float(vb[j + 1]), n4.y), G + j + 1));
-          m2 = fminf(m2, pack_idx(fmaf(-2.f, __uint_as_float(vb[j + 2]), n4.z), G + j + 2));
-          m3 = fminf(m3, pack_idx(fmaf(-2.f, __uint_as_float(vb[j + 3]), n4.w), G + j + 3));
+          m0 = fminf(m0, pack_idx(fmaf(-2.f, __uint_as_float(vb[j]), n4.x), G + j, pmask));
+          m1 = fminf(m1, pack_idx(fmaf(-2.f, __uint_as_float(vb[j + 1]), n4.y), G + j + 1, pmask));
+          m2 = fminf(m2, pack_idx(fmaf(-2.f, __uint_as_float(vb[j + 2]), n4.z), G + j + 2, pmask));
+          m3 = fminf(m3, pack_idx(fmaf(-2.f, __uint_as_float(vb[j + 3]), n4.w), G + j + 3, pmask));
         }
         const float cm = fminf(fminf(m0, m1), fminf(m2, m3));
         if (cm < best) { best = cm; bchunk = c; }
