@@ -59,7 +59,12 @@ void pump_worker(Pump* p) {
         }
         if (!p->q.empty() || p->stop) break;
         if (p->delayed.empty()) p->cv.wait(l);
-        else p->cv.wait_until(l, p->delayed.begin()->first);
+        else {
+          // copy the deadline: wait_until keeps a reference to its argument while the mutex is
+          // released, and another worker may erase that multimap node meanwhile (found by ASan)
+          const Clock::time_point deadline = p->delayed.begin()->first;
+          p->cv.wait_until(l, deadline);
+        }
       }
       if (p->q.empty() && p->stop) return;
       m = p->q.front(); p->q.pop_front();

@@ -162,7 +162,10 @@ def kernels_path() -> Path:
 
 
 def host_path() -> Path:
-    return _LIB_DIR / "libdryad_host.so"
+    """DRYAD_HOST_LIB overrides the library (e.g. an ASan/UBSan or TSan build, bench/sanitize_host.sh)."""
+    import os
+    alt = os.environ.get("DRYAD_HOST_LIB")
+    return Path(alt) if alt else _LIB_DIR / "libdryad_host.so"
 
 
 def kernels():

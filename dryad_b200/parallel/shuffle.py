@@ -136,3 +136,46 @@ class FusedShuffle:
         tot = self.counts.sum(dim=0).tolist()
         r = self.arena.rank
         return [int(tot[r * self.ppr + j]) for j in range(self.ppr)]
+
+    # ---- debug protocol checker ---------------------------------------------------------------
+    def poison(self) -> None:
+        """Fill the receive buffers with 0xA5 so that rows a broken handshake failed to deliver
+        (or delivered to the wrong place) cannot masquerade as data."""
+        for bufs in self.recv:
+            for b in bufs:
+                b.view(torch.uint8).fill_(0xA5)
+        for b in self.recv_key:
+            b.view(torch.uint8).fill_(0xA5)
+
+    @staticmethod
+    def _checksum(t: torch.Tensor, rows: int) -> torch.Tensor:
+        if rows == 0:
+            return torch.zeros(2, dtype=torch.int64, device=t.device)
+        v = t[:rows].contiguous().view(torch.int32).to(torch.int64)
+        w = (torch.arange(v.shape[-1] if v.dim() > 1 else 1, device=t.device, dtype=torch.int64) * 2654435761 + 1) & 0xFFFFFFFF
+        v = v.view(rows, -1)
+        return torch.stack([v.sum(), (v * w[: v.shape[1]]).sum()])          # wraps modulo 2^64
+
+    def verify(self, srcs: Sequence[torch.Tensor]) -> None:
+        """After run(): every row that was sent arrived exactly once somewhere — global row count and
+        two position-weighted checksums per column over ALL ranks' received rows equal those of all
+        sent rows (order-independent, so it holds for any correct partition function).  Collective
+        over the process group; raises on mismatch.  Debug aid (`DRYAD_SHUFFLE_VERIFY=1` in tests),
+        not part of the hot path."""
+        import torch.distributed as dist
+        got = self.received_rows()
+        dev = self.arena.device
+        sent = [torch.tensor([srcs[0].shape[0], 0], dtype=torch.int64, device=dev)]
+        recv = [torch.tensor([sum(got), 0], dtype=torch.int64, device=dev)]
+        for c, t in enumerate(srcs):
+            sent.append(self._checksum(t, t.shape[0]))
+            acc = torch.zeros(2, dtype=torch.int64, device=dev)
+            for j in range(self.ppr):
+                acc = acc + self._checksum(self.recv[c][j], got[j])
+            recv.append(acc)
+        a, b = torch.stack(sent), torch.stack(recv)
+        if self.arena.world > 1:
+            dist.all_reduce(a)
+            dist.all_reduce(b)
+        if not torch.equal(a, b):
+            raise N.NativeError(f"shuffle verification failed: sent {a.tolist()} received {b.tolist()}")

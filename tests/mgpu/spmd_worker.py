@@ -82,7 +82,9 @@ def gpu_checks(rank, world):
     keys = torch.randint(-2**62, 2**62, (n,), dtype=torch.int64, device=dev, generator=g)
     vals = torch.arange(n, dtype=torch.int64, device=dev) + rank * 10_000_000
     sh = FusedShuffle(arena, [ColSpec(8, torch.int64), ColSpec(8, torch.int64)], int(1_010_000 * 1.3) + 4096, max_rows_in=1_010_000)   # same size on every rank
+    sh.poison()                                         # debug protocol checker: poisoned buffers + checksums
     sh.run([keys, vals], mode="hash", key_col=0, key_kind=0)
+    sh.verify([keys, vals])
     m = sh.received_rows()[0]
     rk, rv = sh.recv[0][0][:m], sh.recv[1][0][:m]
     import numpy as np

@@ -376,3 +376,21 @@ def test_direct_addressed_aggregate_matches_torch(K):
     bad.update(keys, [None])
     with pytest.raises(Exception):
         bad.extract()
+
+
+def test_shuffle_debug_verifier_accepts_good_and_rejects_corrupted(K):
+    from dryad_b200.parallel.shuffle import ColSpec, FusedShuffle
+    from dryad_b200.parallel.symm import SymmetricArena
+    dev = torch.device("cuda")
+    n = 100_001
+    g = torch.Generator(device=dev).manual_seed(4)
+    keys = torch.randint(-2**60, 2**60, (n,), dtype=torch.int64, device=dev, generator=g)
+    rows = torch.randint(0, 255, (n, 24), dtype=torch.uint8, device=dev, generator=g)
+    arena = SymmetricArena(64 << 20)
+    sh = FusedShuffle(arena, [ColSpec(8, torch.int64), ColSpec(24, torch.uint8, 24)], n + 16, parts_per_rank=4, max_rows_in=n)
+    sh.poison()
+    sh.run([keys, rows], mode="hash", key_col=0, key_kind=0)
+    sh.verify([keys, rows])
+    sh.recv[1][2][5, 3] ^= 0x40                      # flip one bit of one delivered row
+    with pytest.raises(Exception):
+        sh.verify([keys, rows])
