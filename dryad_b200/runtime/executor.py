@@ -44,6 +44,9 @@ class JobExecutor:
         self.out: Dict[int, List[Optional[List[List]]]] = {}     # node uid -> per partition -> ports
         self.stats: List[dict] = []
         self.backend = context._backend()
+        from ..utils import trace
+        self.timeline = trace.GpuTimeline() if (trace.enabled(context) and getattr(self.backend, "name", "") == "gpu") else None
+        self.gpu_timeline: List[dict] = []
 
     # ---- input assembly (GraphBuilder.ConnectPointwise / ConnectCrossProduct) --------------
     def _inputs(self, node: DLinqQueryNode, i: int) -> List[List]:
@@ -175,7 +178,11 @@ class JobExecutor:
                     if ctx.fault_injector is not None:
                         ctx.fault_injector(node, i, version)
                     env = VertexEnv(ctx, node.uid, i, version)
-                    ports = self.backend.run_vertex(node, i, ins, env)
+                    if self.timeline is not None:
+                        with self.timeline.span(f"{node.name}#{node.uid}[{i}]", stage=node.uid, part=i, version=version):
+                            ports = self.backend.run_vertex(node, i, ins, env)
+                    else:
+                        ports = self.backend.run_vertex(node, i, ins, env)
                     dt = time.perf_counter() - t0
                     self.out[node.uid][i] = ports
                     n_in = sum(self.backend.count(p) for inp in ins for p in inp)
@@ -208,11 +215,23 @@ class JobExecutor:
                 raise DryadLinqException(ErrorCode.DidNotCompleteSuccessfully,
                                          f"job ended in state {gm.state}: {gm.error()}")
             results = self._commit_outputs()
+            self._flush_timeline()
             rep.job_stop(True, "", seconds=time.perf_counter() - t_job, **gm.counters())
             return results
         except BaseException:
             self._discard_outputs()
             raise
+
+    def _flush_timeline(self):
+        """Resolve the device timeline (one synchronize) and store it next to the event log."""
+        if self.timeline is None:
+            return
+        import os
+        spans = self.timeline.resolve()
+        self.gpu_timeline = spans
+        job_dir = getattr(self.reporter, "job_dir", None)
+        if job_dir and spans:
+            self.timeline.write(os.path.join(job_dir, "gpu_timeline.jsonl"), spans)
 
     def _release_finished_children(self, node: DLinqQueryNode):
         """Drop a producer's buffers once every consumer stage has completed (bounded HBM / RAM);

@@ -95,19 +95,25 @@ class SpmdExecutor(JobExecutor):
                 continue
             mine = self.rank if node.partition_count == self.world else (0 if self.rank == 0 else None)
             t0 = time.perf_counter()
+            import contextlib
+            span = self.timeline.span(f"{node.name}#{node.uid}[{mine}]", stage=node.uid, part=mine, rank=self.rank) \
+                if (self.timeline is not None and mine is not None) else contextlib.nullcontext()
             if node.uid in self._fused:
-                ports = self._run_fused(node)
+                with span:
+                    ports = self._run_fused(node)
             elif mine is None:
                 self._participate_only(node)
                 continue
             else:
                 ins = self._spmd_inputs(node, mine)
                 env = VertexEnv(ctx, node.uid, mine, 0)
-                ports = self.backend.run_vertex(node, mine, ins, env)
+                with span:
+                    ports = self.backend.run_vertex(node, mine, ins, env)
             if mine is not None:
                 self.out[node.uid][mine] = ports
                 rep.vertex_event(node, mine, 0, "completed", seconds=time.perf_counter() - t0)
         results = self._commit_local()
+        self._flush_timeline()
         rep.job_stop(True, "", seconds=time.perf_counter() - t_job)
         return results
 

@@ -181,3 +181,20 @@ def test_group_by_dense_integer_keys_uses_direct_table_and_agrees():
         j = r["k"] + 50
         assert (r["s"], r["c"], r["mx"]) == (want_s[j], want_c[j], want_m[j])
     assert ctx._backend().host_fallbacks == 0
+
+
+def test_gpu_timeline_records_device_time_per_vertex(monkeypatch):
+    """DRYAD_TRACE=1: one CUDA-event span (+ NVTX range) per vertex, resolved once at job end and
+    written next to the event log."""
+    import json
+    import os
+    monkeypatch.setenv("DRYAD_TRACE", "1")
+    ctx = D.DryadLinqContext(2, device="cuda")
+    data = list(range(20000))
+    got = ctx.from_enumerable(data, 2).where(lambda x: x % 2 == 0).select(lambda x: x * 3).to_list()
+    assert sorted(got) == [x * 3 for x in data if x % 2 == 0]
+    ex = ctx.last_executor
+    assert ex.gpu_timeline and all(s["gpu_ms"] >= 0 and "stage" in s for s in ex.gpu_timeline)
+    path = os.path.join(ex.reporter.job_dir, "gpu_timeline.jsonl")
+    lines = [json.loads(l) for l in open(path)]
+    assert len(lines) == len(ex.gpu_timeline) >= 2
