@@ -236,7 +236,9 @@ __device__ __forceinline__ void apply_rows(const AggDesc& A, int64_t* vals, uint
 template <int L>
 __global__ void __launch_bounds__(256) agg_update_kernel(uint64_t* keys, uint64_t cap, AggDesc A, int64_t* vals,
                                                          const uint64_t* __restrict__ in_keys,
-                                                         int64_t n, int combine, int32_t* status) {
+                                                         int64_t n, int combine, int32_t* status,
+                                                         const int32_t* skip_if_set = nullptr) {
+  if (skip_if_set && *reinterpret_cast<const volatile int32_t*>(skip_if_set) != 0) return;   // the front-table kernel owns these rows
   int64_t base = (int64_t)blockIdx.x * blockDim.x;
   const int64_t stride = (int64_t)gridDim.x * blockDim.x;
   for (; base < n; base += stride) {          // block-uniform trip count (shuffles below)
@@ -259,6 +261,154 @@ __global__ void __launch_bounds__(256) agg_update_kernel(uint64_t* keys, uint64_
       }
     }
     apply_rows<L, false>(A, vals, s, v, combine != 0, status);
+  }
+}
+
+// ---- shared-memory front table: low-cardinality / skewed keys ----------------------------------
+// With few distinct keys every global reduction lands on a handful of addresses and the L2
+// serialises them (24 M tokens into 4 K words: 20 ms).  Each CTA therefore keeps a small table in
+// shared memory (1024 slots): rows whose key is resident there are folded with shared-memory
+// atomics; rows that miss go to the global table as usual (same lane-paired reductions).  A CTA
+// whose hit rate stays under a quarter for two consecutive tiles (high-cardinality data) stops
+// probing the front table.  At the end the front table is flushed into the global one as partial
+// aggregates.  Reference role: the per-thread AccumulateDictionary instances of
+// ParallelHashGroupByPartialAccumulate (LinqToDryad/DryadLinqVertex.cs:5718-6032).
+constexpr int FRONT_SLOTS = 1024;
+constexpr int FRONT_PROBES = 4;
+
+__device__ __forceinline__ void apply_shared(int op, int64_t* slot, int64_t v, bool combine) {
+  switch (op) {
+    case DRYAD_AGG_COUNT: atomicAdd((unsigned long long*)slot, combine ? (unsigned long long)v : 1ull); break;
+    case DRYAD_AGG_SUM_I64: atomicAdd((unsigned long long*)slot, (unsigned long long)v); break;
+    case DRYAD_AGG_SUM_F64: atomicAdd((double*)slot, __longlong_as_double(v)); break;
+    case DRYAD_AGG_MIN_I64: atomicMin((long long*)slot, (long long)v); break;
+    case DRYAD_AGG_MAX_I64: atomicMax((long long*)slot, (long long)v); break;
+    case DRYAD_AGG_MIN_F64: atomic_min_f64((double*)slot, __longlong_as_double(v)); break;
+    case DRYAD_AGG_MAX_F64: atomic_max_f64((double*)slot, __longlong_as_double(v)); break;
+    default: break;       // checked sums never use the front table (host side)
+  }
+}
+
+template <int L>
+__global__ void __launch_bounds__(256) agg_update_front_kernel(uint64_t* keys, uint64_t cap, AggDesc A, int64_t* vals,
+                                                               const uint64_t* __restrict__ in_keys,
+                                                               int64_t n, int combine, int32_t* status,
+                                                               const int32_t* run_if_set, int32_t* probe_stats) {
+  // run_if_set: skip unless the probe launch found the keys to be low-cardinality.
+  // probe_stats (probe launch only): [0] hits, [1] rows, [2] finished CTAs, [3] verdict.
+  if (run_if_set && *reinterpret_cast<const volatile int32_t*>(run_if_set) == 0) return;
+  extern __shared__ __align__(16) unsigned char front_raw[];
+  uint64_t* fkeys = reinterpret_cast<uint64_t*>(front_raw);                    // [FRONT_SLOTS]
+  int64_t* fvals = reinterpret_cast<int64_t*>(fkeys + FRONT_SLOTS);            // [FRONT_SLOTS][L]
+  __shared__ int s_hits, s_mode, s_low, s_fill;
+  for (int i = threadIdx.x; i < FRONT_SLOTS; i += blockDim.x) fkeys[i] = EMPTY;
+  for (int i = threadIdx.x; i < FRONT_SLOTS * L; i += blockDim.x) {
+    const int l = i & (L - 1);
+    fvals[i] = (l < A.nlanes) ? identity_of(A.op[l]) : 0;
+  }
+  if (threadIdx.x == 0) { s_hits = 0; s_mode = 1; s_low = 0; s_fill = 0; }
+  __syncthreads();
+  int tot_hits = 0, tot_rows = 0;                       // thread 0 only
+
+  int64_t base = (int64_t)blockIdx.x * blockDim.x;
+  const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+  // ---- phase 1: front table in use (left for good once the hit rate stays low) ----------------
+  for (; base < n; base += stride) {
+    if (s_mode == 0) break;                             // block-uniform: written before the last barrier
+    const int64_t i = base + threadIdx.x;
+    uint64_t s = NOSLOT;
+    int64_t v[L];
+#pragma unroll
+    for (int l = 0; l < L; ++l) v[l] = 1;
+    if (i < n) {
+      const uint64_t key = (uint64_t)ld_stream(reinterpret_cast<const int64_t*>(in_keys) + i * A.in_stride);
+#pragma unroll
+      for (int l = 0; l < L; ++l)
+        if (l < A.nlanes && A.in[l]) v[l] = ld_stream(A.in[l] + i * A.in_stride);
+      bool done = false, hit = false;
+      if (key != EMPTY) {
+        uint32_t f = (uint32_t)(mix64(key) >> 40) & (FRONT_SLOTS - 1);
+        for (int pr = 0; pr < FRONT_PROBES && !done; ++pr) {
+          uint64_t cur = *reinterpret_cast<volatile uint64_t*>(&fkeys[f]);
+          if (cur == EMPTY) {
+            // new keys are admitted only while the table is at most 3/4 full (short probe chains)
+            if (*reinterpret_cast<volatile int*>(&s_fill) >= FRONT_SLOTS * 3 / 4) break;
+            const unsigned long long old = atomicCAS((unsigned long long*)&fkeys[f], (unsigned long long)EMPTY, (unsigned long long)key);
+            if (old == (unsigned long long)EMPTY) { atomicAdd(&s_fill, 1); cur = key; } else { cur = (uint64_t)old; hit = cur == key; }
+          } else {
+            hit = cur == key;
+          }
+          if (cur == key) {
+#pragma unroll
+            for (int l = 0; l < L; ++l)
+              if (l < A.nlanes) apply_shared(A.op[l], &fvals[f * L + l], v[l], combine != 0);
+            done = true;
+          }
+          f = (f + 1) & (FRONT_SLOTS - 1);
+        }
+        if (hit) atomicAdd(&s_hits, 1);                // a first insertion is not a hit
+      }
+      if (!done) {
+        if (A.direct) {
+          s = key - A.key_lo;
+          if (s >= cap) { atomicMax(status, 4); s = NOSLOT; }
+        } else {
+          s = find_or_insert<false>(keys, cap, key);
+          if (s == cap) { atomicMax(status, 1); s = NOSLOT; }
+        }
+      }
+    }
+    apply_rows<L, false>(A, vals, s, v, combine != 0, status);
+    __syncthreads();
+    if (threadIdx.x == 0) {
+      tot_hits += s_hits; tot_rows += (int)min((int64_t)blockDim.x, n - base);
+      s_low = (s_hits * 4 < (int)blockDim.x) ? s_low + 1 : 0;
+      if (s_low >= 2 && !probe_stats) s_mode = 0;      // the probe launch keeps counting
+      s_hits = 0;
+    }
+    __syncthreads();
+  }
+  // ---- phase 2: plain global path (same as agg_update_kernel) ------------------------------------
+  for (; base < n; base += stride) {
+    const int64_t i = base + threadIdx.x;
+    uint64_t s = NOSLOT;
+    int64_t v[L];
+#pragma unroll
+    for (int l = 0; l < L; ++l) v[l] = 1;
+    if (i < n) {
+      const uint64_t key = (uint64_t)ld_stream(reinterpret_cast<const int64_t*>(in_keys) + i * A.in_stride);
+#pragma unroll
+      for (int l = 0; l < L; ++l)
+        if (l < A.nlanes && A.in[l]) v[l] = ld_stream(A.in[l] + i * A.in_stride);
+      if (A.direct) {
+        s = key - A.key_lo;
+        if (s >= cap) { atomicMax(status, 4); s = NOSLOT; }
+      } else {
+        s = find_or_insert<false>(keys, cap, key);
+        if (s == cap) { atomicMax(status, 1); s = NOSLOT; }
+      }
+    }
+    apply_rows<L, false>(A, vals, s, v, combine != 0, status);
+  }
+  __syncthreads();
+  // flush the front table: partial aggregates into the global table
+  for (int f = threadIdx.x; f < FRONT_SLOTS; f += blockDim.x) {
+    const uint64_t key = fkeys[f];
+    if (key == EMPTY) continue;
+    uint64_t s;
+    if (A.direct) { s = key - A.key_lo; if (s >= cap) { atomicMax(status, 4); continue; } }
+    else { s = find_or_insert<false>(keys, cap, key); if (s == cap) { atomicMax(status, 1); continue; } }
+    for (int l = 0; l < A.nlanes; ++l) apply<false>(A.op[l], vals + s * L + l, fvals[f * L + l], true, status);
+  }
+  if (probe_stats && threadIdx.x == 0) {
+    atomicAdd(&probe_stats[0], tot_hits);
+    atomicAdd(&probe_stats[1], tot_rows);
+    __threadfence();
+    if (atomicAdd(&probe_stats[2], 1) == (int)gridDim.x - 1) {
+      __threadfence();
+      const int h = *reinterpret_cast<volatile int32_t*>(&probe_stats[0]), r = *reinterpret_cast<volatile int32_t*>(&probe_stats[1]);
+      probe_stats[3] = (h * 5 >= r * 2) ? 1 : 0;        // >= 40 % of the probed rows hit a resident key
+    }
   }
 }
 
@@ -537,6 +687,42 @@ static int fill_desc(AggDesc& A, int nlanes, const int* ops, const int64_t* cons
   return DRYAD_OK;
 }
 
+// Adaptive update.  With a 4-word work area: (1) a small PROBE launch folds the first rows through
+// the shared-memory front table and records how many rows hit a resident key; (2) the rest of the
+// rows are covered by two launches of which exactly one does work, chosen on the device by the
+// probe's verdict — the plain lane-paired kernel for high-cardinality keys, the front-table kernel
+// for few / skewed keys.  No host synchronisation; each kernel keeps its own register and shared
+// memory budget.  Without a work area: the plain kernel.
+constexpr int64_t PROBE_ROWS = 8 * 1024;      // 8 CTAs x 4 tiles: a few microseconds
+template <int L>
+static int launch_update(uint64_t* keys, uint64_t cap, AggDesc A, int64_t* vals, const uint64_t* in_keys,
+                         int64_t n, int combine, int32_t* status, cudaStream_t st, int32_t* work = nullptr) {
+  bool checked = false;
+  for (int l = 0; l < A.nlanes; ++l) checked |= A.op[l] == DRYAD_AGG_SUM_I64_CHECKED;
+  static const bool front_off = [] { const char* e = getenv("DRYAD_AGG_FRONT"); return e && e[0] == '0'; }();
+  auto grid = [](int64_t rows) { int64_t g = (rows + 255) / 256; if (g > 148 * 16) g = 148 * 16; return (int)(g < 1 ? 1 : g); };
+  if (!work || checked || front_off || n < 32 * PROBE_ROWS) {
+    agg_update_kernel<L><<<grid(n), 256, 0, st>>>(keys, cap, A, vals, in_keys, n, combine, status);
+  } else {
+    const size_t smem = (size_t)FRONT_SLOTS * 8 * (1 + L);
+    if (smem > 48 * 1024) {
+      cudaError_t e = cudaFuncSetAttribute(agg_update_front_kernel<L>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+      if (e != cudaSuccess) return (int)e;
+    }
+    cudaError_t e = cudaMemsetAsync(work, 0, 16, st);
+    if (e != cudaSuccess) return (int)e;
+    agg_update_front_kernel<L><<<(int)(PROBE_ROWS / 1024), 256, smem, st>>>(keys, cap, A, vals, in_keys, PROBE_ROWS, combine, status, nullptr, work);
+    AggDesc R = A;                                      // the remaining rows
+    for (int l = 0; l < R.nlanes; ++l) if (R.in[l]) R.in[l] += PROBE_ROWS * R.in_stride;
+    const uint64_t* rk = in_keys + PROBE_ROWS * A.in_stride;
+    const int64_t rn = n - PROBE_ROWS;
+    agg_update_kernel<L><<<grid(rn), 256, 0, st>>>(keys, cap, R, vals, rk, rn, combine, status, work + 3);
+    agg_update_front_kernel<L><<<grid(rn), 256, smem, st>>>(keys, cap, R, vals, rk, rn, combine, status, work + 3, nullptr);
+  }
+  cudaError_t e = cudaGetLastError();
+  return e == cudaSuccess ? DRYAD_OK : (int)e;
+}
+
 // table capacities: any multiple of the 4-key bucket
 static inline bool cap_ok(uint64_t x) { return x >= 4 && (x & 3) == 0; }
 
@@ -571,10 +757,24 @@ int dryad_hash_agg_update(uint64_t* tbl_keys, uint64_t cap, int nlanes, const in
   if (!cap_ok(cap)) return DRYAD_ERR_BAD_ARG;
   if (n <= 0) return DRYAD_OK;
   AggDesc A; int rc = fill_desc(A, nlanes, ops, in_lanes); if (rc) return rc;
-  int64_t g = (n + 255) / 256; if (g > 148 * 16) g = 148 * 16;
-  DRYAD_DISPATCH_L(nlanes, (agg_update_kernel<L><<<(int)g, 256, 0, (cudaStream_t)stream>>>(tbl_keys, cap, A, tbl_vals, in_keys, n, combine, status)));
-  DRYAD_LAUNCH_CHECK();
-  return DRYAD_OK;
+  int lrc = 0;
+  DRYAD_DISPATCH_L(nlanes, (lrc = launch_update<L>(tbl_keys, cap, A, tbl_vals, in_keys, n, combine, status, (cudaStream_t)stream)));
+  return lrc;
+}
+
+/* Same as dryad_hash_agg_update, plus `work` (4 int32 words of device memory owned by the caller):
+ * the call probes the first rows and lets the DEVICE pick between the plain kernel and the
+ * shared-memory front-table kernel for the rest (few / skewed keys), without a host sync. */
+int dryad_hash_agg_update_auto(uint64_t* tbl_keys, uint64_t cap, int nlanes, const int* ops,
+                               int64_t* tbl_vals, const uint64_t* in_keys,
+                               const int64_t* const* in_lanes, int64_t n, int combine, int32_t* status,
+                               int32_t* work, void* stream) {
+  if (!cap_ok(cap)) return DRYAD_ERR_BAD_ARG;
+  if (n <= 0) return DRYAD_OK;
+  AggDesc A; int rc = fill_desc(A, nlanes, ops, in_lanes); if (rc) return rc;
+  int lrc = 0;
+  DRYAD_DISPATCH_L(nlanes, (lrc = launch_update<L>(tbl_keys, cap, A, tbl_vals, in_keys, n, combine, status, (cudaStream_t)stream, work)));
+  return lrc;
 }
 
 int dryad_hash_agg_merge_peers(const uint64_t* tbl_keys, uint64_t cap, int nlanes, const int* ops,
@@ -663,10 +863,20 @@ int dryad_hash_agg_update_direct(int64_t* tbl_vals, uint64_t cap, int nlanes, co
   if (!cap_ok(cap)) return DRYAD_ERR_BAD_ARG;
   if (n <= 0) return DRYAD_OK;
   AggDesc A; int rc = fill_direct(A, nlanes, ops, in_lanes, key_lo); if (rc) return rc;
-  int64_t g = (n + 255) / 256; if (g > 148 * 16) g = 148 * 16;
-  DRYAD_DISPATCH_L(A.nlanes, (agg_update_kernel<L><<<(int)g, 256, 0, (cudaStream_t)stream>>>(nullptr, cap, A, tbl_vals, in_keys, n, 0, status)));
-  DRYAD_LAUNCH_CHECK();
-  return DRYAD_OK;
+  int lrc = 0;
+  DRYAD_DISPATCH_L(A.nlanes, (lrc = launch_update<L>(nullptr, cap, A, tbl_vals, in_keys, n, 0, status, (cudaStream_t)stream)));
+  return lrc;
+}
+
+int dryad_hash_agg_update_direct_auto(int64_t* tbl_vals, uint64_t cap, int nlanes, const int* ops, uint64_t key_lo,
+                                      const uint64_t* in_keys, const int64_t* const* in_lanes, int64_t n,
+                                      int32_t* status, int32_t* work, void* stream) {
+  if (!cap_ok(cap)) return DRYAD_ERR_BAD_ARG;
+  if (n <= 0) return DRYAD_OK;
+  AggDesc A; int rc = fill_direct(A, nlanes, ops, in_lanes, key_lo); if (rc) return rc;
+  int lrc = 0;
+  DRYAD_DISPATCH_L(A.nlanes, (lrc = launch_update<L>(nullptr, cap, A, tbl_vals, in_keys, n, 0, status, (cudaStream_t)stream, work)));
+  return lrc;
 }
 
 int dryad_hash_agg_extract_direct(const int64_t* tbl_vals, uint64_t cap, int nlanes, const int* ops, uint64_t key_lo,
@@ -704,10 +914,9 @@ int dryad_hash_agg_update_rows(uint64_t* tbl_keys, uint64_t cap, int nlanes, con
   AggDesc A; int rc = fill_desc(A, nlanes, ops, nullptr); if (rc) return rc;
   A.in_stride = 1 + nlanes;
   for (int l = 0; l < nlanes; ++l) A.in[l] = rows + 1 + l;
-  int64_t g = (n + 255) / 256; if (g > 148 * 16) g = 148 * 16;
-  DRYAD_DISPATCH_L(nlanes, (agg_update_kernel<L><<<(int)g, 256, 0, (cudaStream_t)stream>>>(tbl_keys, cap, A, tbl_vals, reinterpret_cast<const uint64_t*>(rows), n, combine, status)));
-  DRYAD_LAUNCH_CHECK();
-  return DRYAD_OK;
+  int lrc = 0;
+  DRYAD_DISPATCH_L(nlanes, (lrc = launch_update<L>(tbl_keys, cap, A, tbl_vals, reinterpret_cast<const uint64_t*>(rows), n, combine, status, (cudaStream_t)stream)));
+  return lrc;
 }
 
 int dryad_hash_agg_extract_rows(const uint64_t* tbl_keys, uint64_t cap, int nlanes, const int* ops,

@@ -130,6 +130,8 @@ def _declare_kernels(lib):
     _sig(lib, "dryad_nvls_allreduce_f32", c_int, [P, c_int64, c_int, c_int, P])
     _sig(lib, "dryad_nvls_allreduce_u64", c_int, [P, c_int64, c_int, c_int, P])
     _sig(lib, "dryad_nvls_broadcast", c_int, [P, P, c_int64, P])
+    _sig(lib, "dryad_hash_agg_update_auto", c_int, [P, c_uint64, c_int, P, P, P, P, c_int64, c_int, P, P, P])
+    _sig(lib, "dryad_hash_agg_update_direct_auto", c_int, [P, c_uint64, c_int, P, c_uint64, P, P, c_int64, P, P, P])
     _sig(lib, "dryad_minmax_i64", c_int, [P, c_int64, P, P])
     _sig(lib, "dryad_hash_agg_direct_lane_stride", c_int, [c_int, P])
     _sig(lib, "dryad_hash_agg_init_direct", c_int, [P, c_uint64, c_int, P, P])

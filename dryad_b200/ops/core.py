@@ -250,6 +250,7 @@ class HashAggTable:
             raise ValueError("HashAggTable: keys/vals do not match the capacity and lane stride")
         self._ops_c = (C.c_int * max(self.nl, 1))(*[AGG[o] for o in self.ops])
         self.status = torch.zeros(1, dtype=torch.int32, device=device)
+        self._work = None
         self.reset()
 
     def reset(self):
@@ -269,11 +270,13 @@ class HashAggTable:
                     raise TypeError("aggregate input lanes must be int64 or float64")
                 ins.append(c.data_ptr())
         in_c = (C.c_void_p * max(self.nl, 1))(*ins) if self.nl else (C.c_void_p * 1)()
-        N.check(N.kernels().dryad_hash_agg_update(ptr(self.keys), self.cap, self.nl, self._ops_c,
-                                                  ptr(self.vals), ptr(keys), in_c, keys.numel(),
-                                                  int(combine), ptr(self.status), stream()),
+        if self._work is None:
+            self._work = torch.zeros(4, dtype=torch.int32, device=self.device)
+        N.check(N.kernels().dryad_hash_agg_update_auto(ptr(self.keys), self.cap, self.nl, self._ops_c,
+                                                       ptr(self.vals), ptr(keys), in_c, keys.numel(),
+                                                       int(combine), ptr(self.status), ptr(self._work), stream()),
                 "hash_agg_update")
-        _count()
+        _count(3 if keys.numel() >= (1 << 18) else 1)
 
     def merge_into_peers(self, world: int, peer_keys_ptrs: Sequence[int], peer_vals_ptrs: Sequence[int], peer_cap: int):
         pk = (C.c_void_p * world)(*peer_keys_ptrs)
@@ -349,6 +352,7 @@ class DirectAggTable:
         self.device = device
         self.vals = torch.empty((self.cap, self.stride), dtype=torch.int64, device=device)
         self.status = torch.zeros(1, dtype=torch.int32, device=device)
+        self._work = None
         self.reset()
 
     def _lo(self) -> int:
@@ -365,10 +369,13 @@ class DirectAggTable:
     def update(self, keys: torch.Tensor, cols: Sequence[Optional[torch.Tensor]]):
         require_cuda(keys, *[c for c in cols if c is not None])
         in_c = (C.c_void_p * max(self.nl, 1))(*[None if c is None else c.data_ptr() for c in cols]) if self.nl else (C.c_void_p * 1)()
-        N.check(N.kernels().dryad_hash_agg_update_direct(ptr(self.vals), self.cap, self.nl, self._ops_c, self._lo(),
-                                                         ptr(keys), in_c, keys.numel(), ptr(self.status), stream()),
+        if self._work is None:
+            self._work = torch.zeros(4, dtype=torch.int32, device=self.device)
+        N.check(N.kernels().dryad_hash_agg_update_direct_auto(ptr(self.vals), self.cap, self.nl, self._ops_c, self._lo(),
+                                                              ptr(keys), in_c, keys.numel(), ptr(self.status),
+                                                              ptr(self._work), stream()),
                 "hash_agg_update_direct")
-        _count()
+        _count(3 if keys.numel() >= (1 << 18) else 1)
 
     def merge_into_peers(self, world: int, peer_keys_ptrs: Sequence[int], peer_vals_ptrs: Sequence[int], peer_cap: int):
         pk = (C.c_void_p * world)(*peer_keys_ptrs)

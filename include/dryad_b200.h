@@ -164,6 +164,18 @@ int dryad_hash_agg_update(uint64_t* tbl_keys, uint64_t cap, int nlanes, const in
                           int64_t* tbl_vals, const uint64_t* in_keys,
                           const int64_t* const* in_lanes, int64_t n, int combine, int32_t* status,
                           void* stream);
+/* Adaptive forms: `work` = 4 int32 words of caller-owned device memory.  The first 8 Ki rows go
+ * through a per-CTA shared-memory front table and measure its hit rate; the device then picks, for
+ * the remaining rows, either the plain kernel (many distinct keys) or the front-table kernel (few or
+ * skewed keys: same-address reductions would serialise in the L2).  No host synchronisation. */
+int dryad_hash_agg_update_auto(uint64_t* tbl_keys, uint64_t cap, int nlanes, const int* ops,
+                               int64_t* tbl_vals, const uint64_t* in_keys,
+                               const int64_t* const* in_lanes, int64_t n, int combine,
+                               int32_t* status, int32_t* work, void* stream);
+int dryad_hash_agg_update_direct_auto(int64_t* tbl_vals, uint64_t cap, int nlanes, const int* ops,
+                                      uint64_t key_lo, const uint64_t* in_keys,
+                                      const int64_t* const* in_lanes, int64_t n, int32_t* status,
+                                      int32_t* work, void* stream);
 /* Fused reduce-scatter: fold local partials into the key owner's table (owner =
  * hash_bucket(key, world)) with system-scope atomics on peer HBM.  peer_vals[r] is rank r's
  * vals array (same lane stride). */

@@ -394,3 +394,34 @@ def test_shuffle_debug_verifier_accepts_good_and_rejects_corrupted(K):
     sh.recv[1][2][5, 3] ^= 0x40                      # flip one bit of one delivered row
     with pytest.raises(Exception):
         sh.verify([keys, rows])
+
+
+@pytest.mark.parametrize("nkeys", [7, 300, 5000])
+def test_hash_aggregate_front_table_low_cardinality(K, nkeys):
+    """Few distinct keys: rows are folded in the per-CTA shared-memory front table and flushed as
+    partials; results equal the PyTorch reference for integer and floating lanes."""
+    dev = torch.device("cuda")
+    g = torch.Generator(device=dev).manual_seed(31 + nkeys)
+    n = 1_500_007
+    keys = (torch.randint(0, nkeys, (n,), dtype=torch.int64, device=dev, generator=g) * 2654435761) - 77
+    vi = torch.randint(-1000, 1000, (n,), dtype=torch.int64, device=dev, generator=g)
+    vf = torch.randint(-512, 512, (n,), dtype=torch.int64, device=dev, generator=g).double() / 8.0     # exact in fp64
+    uk, inv = torch.unique(keys, return_inverse=True)
+    m = uk.numel()
+    t = K.HashAggTable(K.agg_capacity(m), ["sum_i64", "count", "min_i64", "max_i64"], dev)
+    t.update(keys, [vi, None, vi, vi])
+    gk, gl = t.extract()
+    order = torch.argsort(gk)
+    assert torch.equal(gk[order], uk)
+    z = torch.zeros(m, dtype=torch.int64, device=dev)
+    assert torch.equal(gl[0][order], z.clone().index_add_(0, inv, vi))
+    assert torch.equal(gl[1][order], torch.bincount(inv, minlength=m))
+    assert torch.equal(gl[2][order], torch.full((m,), 1 << 62, dtype=torch.int64, device=dev).scatter_reduce_(0, inv, vi, "amin"))
+    assert torch.equal(gl[3][order], torch.full((m,), -(1 << 62), dtype=torch.int64, device=dev).scatter_reduce_(0, inv, vi, "amax"))
+    tf = K.HashAggTable(K.agg_capacity(m), ["sum_f64", "min_f64", "max_f64"], dev)
+    tf.update(keys, [vf.view(torch.int64), vf.view(torch.int64), vf.view(torch.int64)])
+    fk, fl = tf.extract()
+    order = torch.argsort(fk)
+    assert torch.equal(fl[0][order].view(torch.float64), torch.zeros(m, dtype=torch.float64, device=dev).index_add_(0, inv, vf))
+    assert torch.equal(fl[1][order].view(torch.float64), torch.full((m,), 1e300, dtype=torch.float64, device=dev).scatter_reduce_(0, inv, vf, "amin"))
+    assert torch.equal(fl[2][order].view(torch.float64), torch.full((m,), -1e300, dtype=torch.float64, device=dev).scatter_reduce_(0, inv, vf, "amax"))
