@@ -213,6 +213,13 @@ def main():
                                 warmup=a.warmup, max_over_ranks=max_over_ranks, barrier=barrier)
         except Exception as ex:  # noqa: BLE001
             groupby = {"error": f"{type(ex).__name__}: {ex}"}
+        if not a.skip_e2e and isinstance(groupby, dict) and "error" not in groupby:
+            try:
+                torch.cuda.empty_cache()
+                groupby["e2e"] = gbm.bench_api(rank, world, dev, a.groupby_rows_per_gpu, a.groupby_keys, steps=max(2, a.steps // 2),
+                                               warmup=2, max_over_ranks=max_over_ranks, barrier=barrier)
+            except Exception as ex:  # noqa: BLE001
+                groupby["e2e"] = {"error": f"{type(ex).__name__}: {ex}"}
 
     # ---- further BASELINE.json configs, short runs: broadcast join (4) and k-means (5) -------------
     extra = {}

@@ -14,7 +14,7 @@ coming from the reference.
 """
 from __future__ import annotations
 
-from typing import Any, Callable, Iterable, List, Optional, Sequence
+from typing import Dict, Any, Callable, Iterable, List, Optional, Sequence
 
 from ..expr import ir as X
 from ..plan.decomposition import try_decompose
@@ -364,6 +364,24 @@ class Query:
 
     def __iter__(self):
         return iter(self.to_list())
+
+    def to_columns(self) -> Dict[str, Any]:
+        """Columnar egress (the counterpart of `from_columns`): runs the query and returns
+        name -> tensor for the partitions this process holds, concatenated in partition order.  On
+        the GPU backend the tensors stay in HBM — nothing is converted to Python objects."""
+        from ..runtime.columnar import ColumnBatch
+        res = self.context._execute(self)
+        t = res.expr.params["table"]
+        parts = [p for p in t.partitions if p is not None]
+        batches = []
+        for p in parts:
+            if isinstance(p, ColumnBatch):
+                batches.append(p)
+            elif len(p):
+                batches.append(ColumnBatch.from_records(list(p), t.schema, "cpu"))
+        if not batches:
+            return {}
+        return dict(ColumnBatch.concat(batches).cols)
 
     def partitions(self) -> List[List]:
         """Materialised per-partition contents (structural partition checks in tests)."""

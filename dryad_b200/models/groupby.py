@@ -42,3 +42,44 @@ def bench(rank, world, dev, n, nkeys, steps, warmup, max_over_ranks, barrier):
     return {"metric": "groupby_sum_count_rows_per_s", "value": world * n / (ms * 1e-3), "unit": "rows/s",
             "ms_per_step": ms, "rows_per_gpu": n, "distinct_keys": nkeys, "groups_out": int(tot[3]),
             "valid": bool(ok), "gpu_launches": K.launch_count() - l0}
+
+
+def bench_api(rank, world, dev, n, nkeys, steps, warmup, max_over_ranks, barrier):
+    """The same GroupBy through the PUBLIC API, end to end: every step copies this rank's (key, value)
+    columns from pinned host memory, runs `from_columns(...).group_by(k).select(sum, count)` on the
+    GPU backend (SPMD over `world` ranks: partial aggregate -> fused hash shuffle -> final
+    aggregate) and reads the number of groups and the total count back."""
+    import dryad_b200 as D
+    keys, vals = generate(n, nkeys, 11, dev, rank)
+    hk = torch.empty(n, dtype=torch.int64).pin_memory(); hk.copy_(keys)
+    hv = torch.empty(n, dtype=torch.int64).pin_memory(); hv.copy_(vals)
+    del keys, vals
+    ctx = D.DryadLinqContext(world, platform="B200" if world > 1 else "LOCAL", device=str(dev))
+    ctx.group_capacity_hint = max(ctx.group_capacity_hint, 2 * nkeys)
+
+    def step():
+        k = hk.to(dev, non_blocking=True)
+        v = hv.to(dev, non_blocking=True)
+        cols = ctx.from_columns({"k": k, "v": v}).group_by(lambda r: r.k).select(
+            lambda g: {"k": g.key, "s": g.sum(lambda r: r.v), "c": g.count()}).to_columns()
+        if not cols:
+            return 0, 0
+        return int(cols["k"].numel()), int(cols["c"].sum().item())          # D2H: 16 bytes
+
+    for _ in range(max(1, min(warmup, 2))):
+        g, c = step()
+    barrier()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(steps):
+        g, c = step()
+    e1.record()
+    barrier()
+    ms = max_over_ranks(e0.elapsed_time(e1)) / steps
+    tot = torch.tensor([g, c], dtype=torch.int64, device=dev)
+    if world > 1:
+        import torch.distributed as dist
+        dist.all_reduce(tot)
+    return {"value": world * n / (ms * 1e-3), "unit": "rows/s", "ms_per_step": ms, "h2d_bytes_per_step": 16 * n,
+            "d2h_bytes_per_step": 16, "groups_out": int(tot[0]), "valid": int(tot[1]) == world * n,
+            "host_fallbacks": ctx._backend().host_fallbacks}

@@ -198,3 +198,20 @@ def test_gpu_timeline_records_device_time_per_vertex(monkeypatch):
     path = os.path.join(ex.reporter.job_dir, "gpu_timeline.jsonl")
     lines = [json.loads(l) for l in open(path)]
     assert len(lines) == len(ex.gpu_timeline) >= 2
+
+
+def test_columnar_ingress_and_egress_stay_on_the_device():
+    import numpy as np
+    n = 200_000
+    rng = np.random.default_rng(2)
+    k, v = rng.integers(0, 3000, n), rng.integers(0, 50, n)
+    ctx = D.DryadLinqContext(2, device="cuda")
+    cols = ctx.from_columns({"k": torch.from_numpy(k).cuda(), "v": torch.from_numpy(v).cuda()}, 2).group_by(lambda r: r.k).select(
+        lambda g: {"k": g.key, "s": g.sum(lambda r: r.v), "c": g.count()}).to_columns()
+    assert cols["k"].is_cuda and cols["k"].numel() == len(set(k.tolist()))
+    order = torch.argsort(cols["k"])
+    want_s = np.zeros(3000, dtype=np.int64); np.add.at(want_s, k, v)
+    occ = np.nonzero(np.bincount(k, minlength=3000))[0]
+    assert cols["k"][order].cpu().tolist() == occ.tolist()
+    assert cols["s"][order].cpu().tolist() == want_s[occ].tolist()
+    assert int(cols["c"].sum()) == n
