@@ -74,3 +74,18 @@ class KMeans:
                                         K.ptr(self.centroids), K.ptr(self.cnorm), K.ptr(self.total_counts),
                                         K.stream()), "kmeans_update")
         K._count()
+
+    def iterate_graph(self, points: torch.Tensor) -> None:
+        """Single-GPU iterations as a CUDA graph (sub-graph vertex, runtime/graph_vertex.py): the five
+        launches of an iteration (two clears, assign, update, inertia clear) replay as one.  The
+        capture is keyed by the point buffer; multi-GPU iterations carry epoch-numbered barriers in
+        their kernel parameters and run eagerly."""
+        if self.world > 1:
+            return self.iterate(points)
+        key = (points.data_ptr(), points.shape[0])
+        if getattr(self, "_graph_key", None) != key:
+            from ..runtime.graph_vertex import GraphVertex
+            self._graph = GraphVertex(lambda: self.iterate(points), device=points.device).capture()
+            self._graph_key = key
+        self._graph.run()
+        K._count(2)

@@ -425,3 +425,23 @@ def test_hash_aggregate_front_table_low_cardinality(K, nkeys):
     assert torch.equal(fl[0][order].view(torch.float64), torch.zeros(m, dtype=torch.float64, device=dev).index_add_(0, inv, vf))
     assert torch.equal(fl[1][order].view(torch.float64), torch.full((m,), 1e300, dtype=torch.float64, device=dev).scatter_reduce_(0, inv, vf, "amin"))
     assert torch.equal(fl[2][order].view(torch.float64), torch.full((m,), -1e300, dtype=torch.float64, device=dev).scatter_reduce_(0, inv, vf, "amax"))
+
+
+def test_kmeans_iterations_as_cuda_graph_match_eager(K):
+    """Sub-graph vertex: a k-means iteration replayed as one CUDA graph gives the same centroids as
+    the eager launches."""
+    from dryad_b200.models import kmeans as KM
+    from dryad_b200.parallel.kmeans import KMeans
+    from dryad_b200.parallel.symm import SymmetricArena
+    pts, centres = KM.generate(100_000, 256, seed=9, device="cuda")
+    a, b = KMeans(SymmetricArena(8 << 20), 256, 100_000), KMeans(SymmetricArena(8 << 20), 256, 100_000)
+    a.set_centroids(centres + 0.05)
+    b.set_centroids(centres + 0.05)
+    for _ in range(3):
+        a.iterate(pts)
+        b.iterate_graph(pts)
+    torch.cuda.synchronize()
+    assert b._graph.replays == 3
+    assert torch.equal(a.assign[:100_000], b.assign[:100_000])
+    assert torch.allclose(a.centroids, b.centroids, rtol=1e-5, atol=1e-5)      # fp32 reductions reorder
+    assert torch.equal(a.total_counts, b.total_counts)
