@@ -217,6 +217,20 @@ int dryad_hash_agg_extract(const uint64_t* tbl_keys, uint64_t cap, int nlanes, c
                            int64_t* const* out_lanes_dev, unsigned long long* out_count,
                            int64_t out_cap, void* stream);
 
+/* ---- HBM ring FIFO between two GPUs (flag-based flow control, no host per block) ------------------
+ * The ring (slots x slot_bytes), the per-slot length words and `head` live in the CONSUMER's memory,
+ * `tail` in the PRODUCER's; `*_peer` pointers are the peer-mapped addresses of the other side.
+ * `done_local` is one zero-initialised u64 of scratch per direction and per side.  seq = number of
+ * blocks pushed (popped) before this call.  status 2: the peer did not move within the timeout,
+ * 1: block larger than the destination.  Producer and consumer must be different GPUs. */
+int dryad_ring_push(const void* src, uint64_t nbytes, void* ring_peer, uint64_t* len_peer,
+                    uint64_t* head_peer, const uint64_t* tail_local, uint64_t* done_local,
+                    uint64_t seq, int slots, uint64_t slot_bytes, int32_t* status, void* stream);
+int dryad_ring_pop(void* dst, uint64_t dst_cap, uint64_t* out_len, const void* ring_local,
+                   const uint64_t* len_local, const uint64_t* head_local, uint64_t* tail_peer,
+                   uint64_t* done_local, uint64_t seq, int slots, uint64_t slot_bytes,
+                   int32_t* status, void* stream);
+
 /* ---- NVLS (NVSwitch multicast / in-switch reduction) ----------------------------------------------
  * `mc` is the multicast address of a symmetric buffer (every GPU of the group has a copy at the same
  * offset; the mapping is made by the caller, e.g. torch's symmetric-memory rendezvous).

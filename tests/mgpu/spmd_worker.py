@@ -191,6 +191,27 @@ def gpu_checks(rank, world):
             assert len(got) == 8 and all(int(b[0]) == 3 * j + 1 and int(b.sum()) == (3 * j + 1) * (1 << 20) for j, b in enumerate(got))
     dist.barrier()
 
+    # 3e. HBM ring FIFO with flag-based flow control: 40 blocks through a 4-slot ring in both
+    #     directions between ranks 0 and 1, no host involvement per block beyond the launches
+    from dryad_b200.parallel.ring import HbmRing
+    fwd = HbmRing(arena, 0, 1, slots=4, slot_bytes=1 << 20)
+    bwd = HbmRing(arena, 1, 0, slots=4, slot_bytes=1 << 20)
+    if rank < 2:
+        out_ring, in_ring = (fwd, bwd) if rank == 0 else (bwd, fwd)
+        nblk, words = 40, (1 << 20) // 8
+        got = torch.empty((nblk, words), dtype=torch.int64, device=dev)
+        blocks = [torch.full((words - 3 * j,), 1000 * rank + j, dtype=torch.int64, device=dev) for j in range(nblk)]
+        for j in range(nblk):
+            out_ring.push(blocks[j])
+            in_ring.pop(got[j])
+        torch.cuda.synchronize()
+        out_ring.check(); in_ring.check()
+        peer = 1 - rank
+        for j in range(nblk):
+            assert bool((got[j, : words - 3 * j] == 1000 * peer + j).all()), (rank, j)
+        assert int(in_ring.out_len.item()) == (words - 3 * (nblk - 1)) * 8
+    dist.barrier()
+
     # 4. the same sort through the public API (SPMD executor -> RowSorter)
     ctx = D.DryadLinqContext(platform="B200", device=str(dev))
     host = rows.cpu().pin_memory()
