@@ -124,6 +124,19 @@ void pump_post(void* h, int64_t listener, int64_t message, double delay_seconds)
   }
   p->cv.notify_all();
 }
+// Stream-completion notifier: `pump_notifier_fn()` is a `void(void*)` suitable for
+// cudaLaunchHostFunc; when the stream reaches it, the message is posted to the pump and delivered
+// under the listener's lock like any other — a vertex's GPU work reports its own completion to the
+// graph-manager event loop without any thread blocking in a stream synchronize
+// (GraphManager/kernel/DrMessagePump.h:81-87 delivers process/vertex state changes the same way).
+struct Notifier { Pump* p; int64_t listener, message; };
+void* pump_make_notifier(void* h, int64_t listener, int64_t message) { return new Notifier{(Pump*)h, listener, message}; }
+static void pump_notifier_fire(void* arg) {
+  Notifier* n = (Notifier*)arg;
+  pump_post(n->p, n->listener, n->message, 0.0);
+  delete n;
+}
+void* pump_notifier_fn() { return (void*)&pump_notifier_fire; }
 // Wait until `count` messages have been delivered in total (or timeout). Returns delivered count.
 int64_t pump_wait_delivered(void* h, int64_t count, double timeout_seconds) {
   Pump* p = (Pump*)h;

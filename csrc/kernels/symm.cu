@@ -69,4 +69,12 @@ const char* dryad_error_string(int code) {
   }
 }
 
+/* Enqueue a host callback `fn(arg)` on the stream (cudaLaunchHostFunc): runs when all prior work of
+ * the stream has completed.  Used to post vertex-completion messages into the host message pump. */
+int dryad_stream_host_func(void* stream, void* fn, void* arg) {
+  if (!fn) return DRYAD_ERR_BAD_ARG;
+  cudaError_t e = cudaLaunchHostFunc((cudaStream_t)stream, (cudaHostFn_t)fn, arg);
+  return e == cudaSuccess ? DRYAD_OK : (int)e;
+}
+
 }  // extern "C"

@@ -127,6 +127,7 @@ def _declare_kernels(lib):
     _sig(lib, "dryad_kmeans_update", c_int, [P, P, c_int, c_int, P, P, P, P])
     _sig(lib, "dryad_radix_sort_pairs_u64_noalloc", c_int, [P, P, P, P, c_int64, c_int, c_int, c_int,
                                                             C.POINTER(c_int), P])
+    _sig(lib, "dryad_stream_host_func", c_int, [P, P, P])
     _sig(lib, "dryad_ring_push", c_int, [P, c_uint64, P, P, P, P, P, c_uint64, c_int, c_uint64, P, P])
     _sig(lib, "dryad_ring_pop", c_int, [P, c_uint64, P, P, P, P, P, P, c_uint64, c_int, c_uint64, P, P])
     _sig(lib, "dryad_nvls_allreduce_f32", c_int, [P, c_int64, c_int, c_int, P])

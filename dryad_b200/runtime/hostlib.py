@@ -88,6 +88,8 @@ PUMP_HANDLER = C.CFUNCTYPE(None, c_int64, c_int64, P)
 _d("pump_create", P, [c_int, PUMP_HANDLER, P])
 _d("pump_post", None, [P, c_int64, c_int64, c_double])
 _d("pump_wait_delivered", c_int64, [P, c_int64, c_double])
+_d("pump_make_notifier", P, [P, c_int64, c_int64])
+_d("pump_notifier_fn", P, [])
 _d("pump_destroy", None, [P])
 _d("mbox_create", P, [])
 _d("mbox_destroy", None, [P])

@@ -19,6 +19,15 @@ class MessagePump:
     def post(self, listener: int, message: int, delay: float = 0.0) -> None:
         self.lib.pump_post(self.h, listener, message, delay)
 
+    def post_on_stream_completion(self, listener: int, message: int, stream: Optional[int] = None) -> None:
+        """Post (listener, message) when all GPU work enqueued so far on `stream` (default: the
+        current torch stream) has finished — cudaLaunchHostFunc, no thread blocks in a synchronize.
+        This is how a vertex's kernels report their own completion to the event loop."""
+        import torch
+        st = torch.cuda.current_stream().cuda_stream if stream is None else stream
+        arg = self.lib.pump_make_notifier(self.h, listener, message)
+        N.check(N.kernels().dryad_stream_host_func(st, self.lib.pump_notifier_fn(), arg), "stream_host_func")
+
     def wait_delivered(self, count: int, timeout: float = 10.0) -> int:
         return self.lib.pump_wait_delivered(self.h, count, timeout)
 

@@ -217,6 +217,11 @@ int dryad_hash_agg_extract(const uint64_t* tbl_keys, uint64_t cap, int nlanes, c
                            int64_t* const* out_lanes_dev, unsigned long long* out_count,
                            int64_t out_cap, void* stream);
 
+/* Host callback on a stream (cudaLaunchHostFunc): fn(arg) runs once all prior work of the stream is
+ * complete.  With libdryad_host's pump_notifier_fn / pump_make_notifier this posts a completion
+ * message into the graph manager's message pump without anyone blocking on the stream. */
+int dryad_stream_host_func(void* stream, void* fn, void* arg);
+
 /* ---- HBM ring FIFO between two GPUs (flag-based flow control, no host per block) ------------------
  * The ring (slots x slot_bytes), the per-slot length words and `head` live in the CONSUMER's memory,
  * `tail` in the PRODUCER's; `*_peer` pointers are the peer-mapped addresses of the other side.

@@ -86,6 +86,10 @@ typedef void (*dh_pump_handler)(int64_t listener, int64_t message, void* user);
 void* pump_create(int threads, dh_pump_handler handler, void* user);
 void pump_post(void* h, int64_t listener, int64_t message, double delay_seconds);
 int64_t pump_wait_delivered(void* h, int64_t count, double timeout_seconds);
+/* CUDA stream completion -> pump message: pass pump_notifier_fn() and pump_make_notifier(...) to
+ * cudaLaunchHostFunc (dryad_stream_host_func in libdryad_kernels).  The notifier frees itself. */
+void* pump_make_notifier(void* h, int64_t listener, int64_t message);
+void* pump_notifier_fn(void);
 void pump_destroy(void* h);
 
 /* ---- versioned mailbox: ProcessService/ProcessService.cs:674-746 ---------------------------------- */

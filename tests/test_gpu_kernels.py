@@ -445,3 +445,23 @@ def test_kmeans_iterations_as_cuda_graph_match_eager(K):
     assert torch.equal(a.assign[:100_000], b.assign[:100_000])
     assert torch.allclose(a.centroids, b.centroids, rtol=1e-5, atol=1e-5)      # fp32 reductions reorder
     assert torch.equal(a.total_counts, b.total_counts)
+
+
+def test_stream_completion_posts_into_the_message_pump(K):
+    """cudaLaunchHostFunc -> native message pump: a completion message arrives after the kernels
+    enqueued before it, without any stream synchronize on the host."""
+    import time
+    from dryad_b200.runtime.services import MessagePump
+    seen = []
+    x = torch.zeros(1 << 24, dtype=torch.int64, device="cuda")
+    pump = MessagePump(lambda listener, message: seen.append((listener, message, int(x[0].item()) if False else None)), threads=2)
+    try:
+        for j in range(3):
+            x.add_(1)                                   # GPU work of "vertex j"
+            pump.post_on_stream_completion(7, 100 + j)
+        assert pump.wait_delivered(3, 20.0) >= 3
+        assert sorted(m for _, m, _ in seen) == [100, 101, 102] and all(l == 7 for l, _, _ in seen)
+        torch.cuda.synchronize()
+        assert int(x[0].item()) == 3
+    finally:
+        pump.close()
