@@ -249,6 +249,68 @@ def _order_by(node, part, inputs, env):
     return [L.order_by(_cat(inputs[0]), _kfn(p["key"]), bool(p["descending"]), p.get("comparer"))]
 
 
+_PLAIN_KEYS = (str, int, float, bool, bytes)
+
+
+def _is_identity(fn) -> bool:
+    probe = object()
+    try:
+        return fn(probe) is probe
+    except Exception:  # noqa: BLE001
+        return False
+
+
+def _fast_accumulate(src, key, elem, dec):
+    """Tight loops for the common decomposable shapes (Count / Sum / Min / Max over plain hashable
+    keys): the generic loop pays four Python calls per record (key wrapper, _hashable, seed or
+    accumulate per aggregate); these pay one or two.  Count with an identity key is a C-speed
+    `collections.Counter`.  Returns None when the shape does not qualify (generic loop runs).
+    Same results as the generic loop, including checked integer sums (Python ints do not wrap;
+    the int64 range check happens where the generic path does it: at combine / final time)."""
+    aggs = dec.aggs
+    if elem is not None or not src or any(a.kind not in ("count", "sum", "min", "max") for a in aggs):
+        return None
+    first = src[0]
+    if not isinstance(key(first), _PLAIN_KEYS):
+        return None
+    kinds = [a.kind for a in aggs]
+    sels = [a.selector.fn if a.selector is not None else None for a in aggs]
+    ident = _is_identity(key)
+    if kinds == ["count"]:
+        from collections import Counter
+        c = Counter(src) if ident else Counter(map(key, src))
+        if not all(isinstance(k, _PLAIN_KEYS) for k in c):
+            return None
+        return [(k, [n]) for k, n in c.items()]
+    from ..plan.decomposition import checked_add
+    table: Dict[Any, list] = {}
+    get = table.get
+    na = len(aggs)
+    for x in src:
+        k = x if ident else key(x)
+        if type(k) not in _PLAIN_KEYS:
+            return None                                   # mixed key types: let the generic loop decide
+        accs = get(k)
+        if accs is None:
+            table[k] = [1 if kinds[j] == "count" else (sels[j](x) if sels[j] is not None else x) for j in range(na)]
+            continue
+        for j in range(na):
+            kd = kinds[j]
+            if kd == "count":
+                accs[j] += 1
+                continue
+            v = sels[j](x) if sels[j] is not None else x
+            if kd == "sum":
+                a = accs[j]
+                accs[j] = checked_add(a, v) if type(a) is int and type(v) is int else a + v
+            elif kd == "min":
+                if v < accs[j]:
+                    accs[j] = v
+            elif v > accs[j]:
+                accs[j] = v
+    return [(k, accs) for k, accs in table.items()]
+
+
 def _group_by(node, part, inputs, env):
     p = node.params
     src = _cat(inputs[0])
@@ -265,6 +327,9 @@ def _group_by(node, part, inputs, env):
     table: Dict[Any, list] = {}
     keys: Dict[Any, Any] = {}
     if mode in ("partial_acc", "full_acc"):
+        fast = _fast_accumulate(src, key, elem, dec)
+        if fast is not None:
+            return [fast]
         for x in src:
             k = key(x)
             hk = L._hashable(k)
