@@ -188,6 +188,16 @@ def main():
                 res = q.submit_and_wait()
                 return terasort.validate(res)                 # D2H: [violations, checksum, count]
 
+            # context for the reader: this box's raw pinned-host -> device rate (not part of the timed region)
+            probe = torch.empty_like(host_rows, device=dev)
+            p0, p1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            probe.copy_(host_rows, non_blocking=True)
+            p0.record()
+            probe.copy_(host_rows, non_blocking=True)
+            p1.record()
+            torch.cuda.synchronize()
+            h2d_rate = n * W / (p0.elapsed_time(p1) * 1e-3) / 1e9
+            del probe
             for _ in range(max(1, min(a.warmup, 3))):
                 summ = e2e_step()
             barrier()
@@ -199,7 +209,7 @@ def main():
             barrier()
             e_ms = max_over_ranks(s0.elapsed_time(s1)) / a.steps
             e2e = {"value": world * n * W / (e_ms * 1e-3) / 1e9, "unit": "GB/s", "ms_per_step": e_ms,
-                   "h2d_bytes_per_step": n * W, "d2h_bytes_per_step": 24, "cpus_bound": len(bound) if bound else 0,
+                   "h2d_bytes_per_step": n * W, "d2h_bytes_per_step": 24, "cpus_bound": len(bound) if bound else 0, "box_h2d_GBps_per_gpu": round(h2d_rate, 1),
                    "violations": int(summ[0]), "rows_out_local": int(summ[2])}
         except Exception as ex:  # noqa: BLE001
             e2e = {"error": f"{type(ex).__name__}: {ex}"}
