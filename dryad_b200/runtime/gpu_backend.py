@@ -25,6 +25,13 @@ def _tuple_cls(ir):
     return ir.cls if isinstance(ir, X.TupleFields) else False
 
 
+def _has_reserved_key(*key_bits: torch.Tensor) -> bool:
+    """The hashed tables reserve the bit pattern ~0 (int64 -1, a NaN payload for floats) as their
+    EMPTY marker.  A vertex whose keys contain it runs on the host path instead (one pass + one
+    host sync per vertex; the direct-addressed dense-key table has no reserved value)."""
+    return any(t.numel() and bool((t == -1).any().item()) for t in key_bits)
+
+
 def _numeric_schema(schema) -> bool:
     return bool(schema) and all(k in ("i", "f", "b") for k in schema.values())
 
@@ -281,6 +288,8 @@ def _group_by(be, node, part, inputs, env):
                 return [ColumnBatch(cols_d, gk.numel(), acc_lanes=len(dec.aggs))]
             except OverflowError as ex:
                 raise DryadLinqException(ErrorCode.FailureInHashGroupBy, "Arithmetic operation resulted in an overflow.") from ex
+    if _has_reserved_key(kbits):
+        return NotImplemented
     while True:
         tbl = K.HashAggTable(cap, lanes, be.device)
         if n:
@@ -568,6 +577,8 @@ def _join(be, node, part, inputs, env):
         ikb = K.sort_key_bits(_typed_key(inner, p["inner_key"], ik), descending=desc).contiguous()
         op, ib = K.merge_join(okb, ikb)
     else:
+        if _has_reserved_key(ik, ok):
+            return NotImplemented
         jt = K.JoinTable(ik.contiguous())                # build on the inner (usually smaller) side
         fused = _join_fused(be, jt, outer, inner, ok, res)
         if fused is not None:
@@ -639,6 +650,8 @@ def _distinct(be, node, part, inputs, env):
     if src.n == 0:
         return [src]
     kb = v.view(torch.int64) if v.dtype == torch.float64 else v
+    if _has_reserved_key(kb):
+        return NotImplemented
     tbl = K.HashAggTable(2 * src.n + 64, [], be.device)
     tbl.update(kb.contiguous(), [])
     gk, _ = tbl.extract()
@@ -653,6 +666,8 @@ def _set_operation(be, node, part, inputs, env):
     f = a.cols["value"].dtype == torch.float64
     ab = a.cols["value"].view(torch.int64) if f else a.cols["value"]
     bb = b.cols["value"].view(torch.int64) if f else b.cols["value"]
+    if _has_reserved_key(ab, bb):
+        return NotImplemented
     r = K.set_operation(node.params["op"], ab.contiguous(), bb.contiguous())
     return [ColumnBatch({"value": r.view(torch.float64) if f else r}, r.numel())]
 

@@ -215,3 +215,29 @@ def test_columnar_ingress_and_egress_stay_on_the_device():
     assert cols["k"][order].cpu().tolist() == occ.tolist()
     assert cols["s"][order].cpu().tolist() == want_s[occ].tolist()
     assert int(cols["c"].sum()) == n
+
+
+def test_key_minus_one_is_an_ordinary_key_on_the_gpu_backend():
+    """int64 -1 has the bit pattern the hash tables reserve for EMPTY: queries whose keys contain
+    it must still agree with the oracle (host path for that vertex, or the direct table)."""
+    data = [{"k": (i % 7) - 1, "v": i} for i in range(2000)]               # keys -1 .. 5
+    ld = D.DryadLinqContext(1, local_debug=True)
+    q = lambda c, p: c.from_enumerable(data, p).group_by(lambda r: r.k).select(      # noqa: E731
+        lambda g: {"k": g.key, "s": g.sum(lambda r: r.v), "c": g.count()})
+    want = sorted(q(ld, 1).to_list(), key=repr)
+    for p in (1, 3):
+        assert sorted(q(D.DryadLinqContext(p, device="cuda"), p).to_list(), key=repr) == want
+    vals = [(i * 13) % 11 - 1 for i in range(500)]
+    other = [-1, 3, 99]
+    ctx = D.DryadLinqContext(2, device="cuda")
+    a, b = ctx.from_enumerable(vals, 2), ctx.from_enumerable(other, 1)
+    assert sorted(a.distinct().to_list()) == sorted(set(vals))
+    assert sorted(a.intersect(b).to_list()) == sorted(set(vals) & set(other))
+    assert sorted(a.union(b).to_list()) == sorted(set(vals) | set(other))
+    left = [{"id": i % 5 - 1, "a": i} for i in range(50)]
+    right = [{"id": i - 1, "b": i * 10} for i in range(5)]
+    wantj = sorted(ld.from_enumerable(left).join(ld.from_enumerable(right), lambda l: l.id, lambda r: r.id,
+                                                 lambda l, r: (l.id, l.a + r.b)).to_list())
+    gotj = sorted(ctx.from_enumerable(left, 2).join(ctx.from_enumerable(right, 1), lambda l: l.id, lambda r: r.id,
+                                                    lambda l, r: (l.id, l.a + r.b)).to_list())
+    assert gotj == wantj
