@@ -174,6 +174,40 @@ class DryadLinqContext:
 
     Dispose = dispose
 
+    # ---- settings identity (DryadLinqContext.Equals, DryadLinqContext.cs:1283-1308) ----------------
+    _SETTINGS = ("platform", "num_partitions", "device", "local_debug", "intermediate_data_compression_scheme",
+                 "output_data_compression_scheme", "compile_for_vertex_debugging", "job_friendly_name", "job_min_nodes",
+                 "job_max_nodes", "threads_per_worker", "application_master_mb_memory", "container_mb_memory", "queue",
+                 "node_group", "job_runtime_limit", "enable_speculative_duplication", "debug_break",
+                 "runtime_logging_level", "graph_manager_node", "select_order_preserving", "partition_unc_path")
+
+    def settings(self) -> tuple:
+        """Every user-visible setting; two contexts with equal settings may share one job (queries
+        from different contexts can only be combined when their contexts compare equal)."""
+        def norm(v):
+            if isinstance(v, dict):
+                return tuple(sorted((str(k), str(x)) for k, x in v.items()))
+            if isinstance(v, (list, set, tuple)):
+                return tuple(sorted(map(str, v)))
+            return str(v)
+        base = tuple(norm(getattr(self, n, None)) for n in self._SETTINGS)
+        return base + (norm(getattr(self, "job_environment_variables", {})), norm(getattr(self, "resources_to_add", [])),
+                       norm(getattr(self, "resources_to_remove", [])))
+
+    def equals(self, other) -> bool:
+        return isinstance(other, DryadLinqContext) and self.settings() == other.settings()
+
+    Equals = equals
+
+    def register_azure_account(self, account: str, key: str) -> None:
+        """Kept for API parity (DryadLinqContext.RegisterAzureAccount): the account is recorded, but
+        this engine has no Azure blob provider — `azureblob://` / `wasb://` URIs are rejected by the
+        data-provider registry with UnsupportedSchemeException."""
+        self._azure_accounts = getattr(self, "_azure_accounts", {})
+        self._azure_accounts[account] = key
+
+    RegisterAzureAccount = register_azure_account
+
     def __enter__(self):
         return self
 

@@ -174,3 +174,15 @@ def test_wordcount_local_text_file(tmp_path):
                   .select(lambda g: D.Pair(g.key, g.count())))
         got = dict(counts.to_list())
         assert got == {"the": 3, "quick": 1, "brown": 1, "fox": 1, "lazy": 1, "dog": 1, "end": 1}
+
+
+def test_context_equality_is_over_all_settings():
+    """DryadLinqContext.Equals (DryadLinqContext.cs:1283-1308): equal when every setting is equal."""
+    import dryad_b200 as D
+    a, b = D.DryadLinqContext(3), D.DryadLinqContext(3)
+    assert a.equals(b) and a.Equals(b)
+    b.enable_speculative_duplication = not b.enable_speculative_duplication
+    assert not a.equals(b)
+    c = D.DryadLinqContext(4)
+    assert not a.equals(c) and not a.equals("x")
+    a.register_azure_account("acct", "key")          # recorded only: no Azure provider on this engine
