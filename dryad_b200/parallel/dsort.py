@@ -40,8 +40,12 @@ class RowSorter:
         self.sample_cap = max(1024, min(MAX_SAMPLES // self.world, int(max_rows * sample_rate * 2) + 1024))
         if self.world > 1:
             self.cap_rows = int(max_rows * slack) + 4096
+            import os
+            # DRYAD_SORT_EMIT_KEY=0: do not ship the 8-byte key prefix next to each row; the receiver
+            # re-extracts it from the rows (7 % fewer NVLink bytes, one more pass over row heads)
+            self.emit_key = os.environ.get("DRYAD_SORT_EMIT_KEY", "1") != "0"
             self.shuffle = FusedShuffle(arena, [ColSpec(width, torch.uint8, width)], self.cap_rows,
-                                        emit_key=True, max_rows_in=max_rows)
+                                        emit_key=self.emit_key, max_rows_in=max_rows)
             self.all_samples, self.all_samples_off = arena.alloc((self.world, self.sample_cap), torch.int64)
             self.all_counts, self.all_counts_off = arena.alloc((self.world,), torch.int64)
             self._peer_sample_views = []
@@ -160,7 +164,7 @@ class RowSorter:
             m = self.shuffle.received_rows()[0]               # host sync: sizes the local sort
             self._mark("host sync")
             src_rows = self.shuffle.recv[0][0]
-            keys = self.shuffle.recv_key[0][:m]
+            keys = self.shuffle.recv_key[0][:m] if self.emit_key else None
             r = self.rank
             if self.descending:
                 lo = sl[r] if r < len(sl) else 0

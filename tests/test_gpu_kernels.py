@@ -465,3 +465,31 @@ def test_stream_completion_posts_into_the_message_pump(K):
         assert int(x[0].item()) == 3
     finally:
         pump.close()
+
+
+def test_packed_row_extract_and_update_round_trip(K):
+    """Partial aggregates leave a table as packed rows {key, partials...} and fold into another
+    table with combine semantics (the push form of the distributed merge)."""
+    dev = torch.device("cuda")
+    g = torch.Generator(device=dev).manual_seed(8)
+    n = 300_000
+    keys = torch.randint(0, 5000, (n,), dtype=torch.int64, device=dev, generator=g) * 7919 + 3
+    vals = torch.randint(-50, 50, (n,), dtype=torch.int64, device=dev, generator=g)
+    a = K.HashAggTable(K.agg_capacity(5000), ["sum_i64", "count", "max_i64"], dev)
+    a.update(keys[: n // 2], [vals[: n // 2], None, vals[: n // 2]])
+    b = K.HashAggTable(K.agg_capacity(5000), ["sum_i64", "count", "max_i64"], dev)
+    b.update(keys[n // 2:], [vals[n // 2:], None, vals[n // 2:]])
+    final = K.HashAggTable(K.agg_capacity(5000), ["sum_i64", "count", "max_i64"], dev)
+    for t in (a, b):
+        rows = torch.empty((t.cap, 4), dtype=torch.int64, device=dev)
+        cnt = torch.zeros(1, dtype=torch.int64, device=dev)
+        t.extract_rows(rows, cnt)
+        final.update_rows(rows, int(cnt.item()), combine=True)
+    gk, gl = final.extract()
+    uk, inv = torch.unique(keys, return_inverse=True)
+    order = torch.argsort(gk)
+    assert torch.equal(gk[order], uk)
+    m = uk.numel()
+    assert torch.equal(gl[0][order], torch.zeros(m, dtype=torch.int64, device=dev).index_add_(0, inv, vals))
+    assert torch.equal(gl[1][order], torch.bincount(inv, minlength=m))
+    assert torch.equal(gl[2][order], torch.full((m,), -(1 << 62), dtype=torch.int64, device=dev).scatter_reduce_(0, inv, vals, "amax"))
