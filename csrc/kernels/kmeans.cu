@@ -759,6 +759,18 @@ int dryad_kmeans_assign(const float* points, int64_t n, const float* centroids, 
   const char* cenv = getenv("DRYAD_KM_CLUSTER");
   int cluster = cenv ? atoi(cenv) : 1;   // multicast clusters measured no faster: shared-memory operand reads bound the SS-mode MMA
   if (cluster != 1 && cluster != 2 && cluster != 4) cluster = 2;
+  if (cluster > 1) {
+    // TMA multicast loads here read only this GPU's memory, since on B200 a TMA multicast load from
+    // another GPU's memory hung the GPU: the multicast variant runs only when the centroid array is
+    // an ordinary allocation of the CURRENT device; any other pointer takes the plain loads.
+    int cur = -1;
+    cudaPointerAttributes pa;
+    if (cudaGetDevice(&cur) != cudaSuccess || cudaPointerGetAttributes(&pa, centroids) != cudaSuccess ||
+        pa.type != cudaMemoryTypeDevice || pa.device != cur) {
+      cudaGetLastError();
+      cluster = 1;
+    }
+  }
   CUtensorMap mx, mc;
   int rc = make_map(&mx, points, (uint64_t)n); if (rc) return rc;
   rc = make_map(&mc, centroids, (uint64_t)k, (uint32_t)(BN / cluster)); if (rc) return rc;
