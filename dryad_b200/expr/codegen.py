@@ -29,6 +29,7 @@ __device__ __forceinline__ u64 dryad_mix64(u64 x) {
 __device__ __forceinline__ i64 dryad_div(i64 a, i64 b) { return b ? a / b : 0; }
 __device__ __forceinline__ i64 dryad_mod(i64 a, i64 b) { return b ? a % b : 0; }
 // read-only probe of a finished join table (4-key buckets, csrc/kernels/hash_table.cu find_slot)
+template <bool WANT_SLOT>
 __device__ __forceinline__ i64 dryad_probe(const u64* __restrict__ keys, const int* __restrict__ head, u64 cap, u64 key) {
   const u64 nb = cap >> 2;
   u64 b = __umul64hi(dryad_mix64(key), nb);
@@ -40,7 +41,7 @@ __device__ __forceinline__ i64 dryad_probe(const u64* __restrict__ keys, const i
     const u64 k[4] = {k0, k1, k2, k3};
 #pragma unroll
     for (int j = 0; j < 4; ++j) {
-      if (k[j] == key) return (i64)__ldg(head + b * 4 + j);
+      if (k[j] == key) return WANT_SLOT ? (i64)(b * 4 + j) : (i64)__ldg(head + b * 4 + j);
       if (k[j] == ~0ULL) return -1;
     }
     if (++b == nb) b = 0;
@@ -100,14 +101,15 @@ def emit(e: Expr, cols: Mapping[str, str], ctx: Optional[_Ctx] = None) -> str:
         return f"((i64){int(v)}LL)" if k == "i" else ("1" if v else "0")
     if op == "rowid":
         return "i"
-    if op == "probe":
+    if op in ("probe", "probe_slot"):
         if ctx is None or e.args[0] not in ctx.tables:
             raise TraceError(f"probe of unknown table {e.args[0]!r}")
         t = ctx.tables[e.args[0]]
         key = e.args[1]
         kc = emit(key, cols, ctx)
         kc = f"(u64)__double_as_longlong({kc})" if key.kind == "f" else f"(u64)({kc})"
-        return ctx.hoist(("probe", t, kc), "i64", f"dryad_probe(tk{t}, th{t}, tc{t}, {kc})")
+        want = "true" if op == "probe_slot" else "false"
+        return ctx.hoist((op, t, kc), "i64", f"dryad_probe<{want}>(tk{t}, th{t}, tc{t}, {kc})")
     if op == "gather":
         if ctx is None or e.args[0] not in ctx.arrays:
             raise TraceError(f"gather from unknown array {e.args[0]!r}")

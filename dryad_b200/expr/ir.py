@@ -221,6 +221,12 @@ def probe(table: str, key) -> Expr:
     return Expr("probe", (table, wrap(key)), "i")
 
 
+def probe_slot(table: str, key) -> Expr:
+    """Like `probe`, but returns the table SLOT of the key (or -1): side arrays permuted into slot
+    order (`BroadcastJoin.slot_payload`) are then gathered without the extra slot -> row hop."""
+    return Expr("probe_slot", (table, wrap(key)), "i")
+
+
 def gather(array: str, index, kind: str = "i") -> Expr:
     """array[index] for a side array that is not row-aligned with the inputs (0 where index < 0)."""
     return Expr("gather", (array, wrap(index)), kind)

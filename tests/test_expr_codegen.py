@@ -47,7 +47,7 @@ def test_fused_probe_gather_reduce_source_compiles():
     src = codegen._source({"r": where(keep, col("v") * gather("attr", hit), 0), "f": gather("w", hit, "f") * 2.0}, keep,
                           ["k", "v"], [torch.int64, torch.int64], tables=["dim"],
                           arrays=[("attr", torch.int64), ("w", torch.float64)], reduce={"r": "sum", "f": "max"}, count_flags=True)
-    assert src.count("dryad_probe(tk0") == 1
+    assert src.count("dryad_probe<false>(tk0") == 1
     err, prog = nvrtc.nvrtcCreateProgram(src.encode(), b"t.cu", 0, [], [])
     opts = [b"--gpu-architecture=sm_100a"]
     (err,) = nvrtc.nvrtcCompileProgram(prog, len(opts), opts)
