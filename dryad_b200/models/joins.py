@@ -19,7 +19,7 @@ def generate(n_fact: int, n_dim: int, seed: int, device, rank: int = 0, world: i
 
 def bench(rank, world, dev, n_fact, n_dim, steps, warmup, max_over_ranks, barrier, threshold=500):
     import os
-    from ..expr import col, gather, probe, where
+    from ..expr import col, gather, probe_slot, where
     from ..expr.compile import run_on_gpu
     from ..ops import core as K
     from ..parallel.djoin import BroadcastJoin
@@ -35,10 +35,13 @@ def bench(rank, world, dev, n_fact, n_dim, steps, warmup, max_over_ranks, barrie
         if fused:
             # probe + payload gather + Where + Select + Sum in ONE generated kernel: the fact side is
             # read once and nothing per-row is written (expr.probe / expr.gather, expr/codegen.py)
-            hit = probe("dim", col("k"))
+            # the payload column is permuted into slot order once per build (1 Mi elements), so the
+            # probe kernel touches two L2 sectors per fact row (key bucket, payload) instead of three
+            attr_slot = bj.slot_payload(bj.cols[0])
+            hit = probe_slot("dim", col("k"))
             keep = (col("v") >= threshold) & (hit >= 0)
             out, cnt = run_on_gpu({"r": where(keep, col("v") * gather("attr", hit), 0)}, {"k": fk, "v": fv}, n_fact,
-                                  predicate=keep, tables={"dim": bj}, arrays={"attr": bj.cols[0]},
+                                  predicate=keep, tables={"dim": bj}, arrays={"attr": attr_slot},
                                   reduce={"r": "sum"}, count_flags=True)
             return out["r"], cnt
         di, matched = bj.probe_unique(fk)                             # local probe: the fact side never moves

@@ -92,6 +92,13 @@ class BroadcastJoin:
                                      self.nrows, K.ptr(self.status), K.stream()), "join_build")
         K._count(2)
 
+    def slot_payload(self, col: torch.Tensor) -> torch.Tensor:
+        """`col` (one value per small-side row) permuted into TABLE-SLOT order: out[s] = col[head[s]]
+        for occupied slots.  A fused probe that returns the slot (`expr.probe_slot`) then reads the
+        payload with ONE more memory request per row instead of two (head[slot], then col[row])."""
+        idx = self.head.clamp(min=0)
+        return K.gather_rows(col.contiguous(), idx.contiguous())
+
     def build_remote_atomics(self, keys_local: torch.Tensor, cols_local: Sequence[torch.Tensor], row_base: int) -> None:
         """Alternative single-kernel form: insert into every rank's table with system-scope atomics
         over NVLink (kept for comparison; slower at 8 GPUs than replicate + local build)."""
