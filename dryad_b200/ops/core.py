@@ -432,6 +432,11 @@ class JoinTable:
             self._unique = st == 0
         return self._unique
 
+    def slot_payload(self, col: torch.Tensor) -> torch.Tensor:
+        """`col` (one value per build row) permuted into table-slot order: out[s] = col[head[s]]
+        (unique-key tables; pairs with `expr.probe_slot`)."""
+        return gather_rows(col.contiguous(), self.head.clamp(min=0).contiguous())
+
     def probe(self, probe_keys: torch.Tensor):
         """Returns (probe_idx, build_idx) int32 index pairs of all matches."""
         require_cuda(probe_keys)

@@ -603,7 +603,7 @@ def _join_fused(be, jt, outer: ColumnBatch, inner: ColumnBatch, ok: torch.Tensor
         if not jt.unique:
             return None
         proj = res if isinstance(res, dict) else {"value": res}
-        hit = X.probe("jt", X.col("__okey"))
+        hit = X.probe_slot("jt", X.col("__okey"))          # slot, not row: payloads are permuted to slot order below
         sub = {}
         arrays = {}
         for k, v in inner.cols.items():
@@ -612,7 +612,7 @@ def _join_fused(be, jt, outer: ColumnBatch, inner: ColumnBatch, ok: torch.Tensor
             kind = "f" if v.dtype in (torch.float32, torch.float64) else ("b" if v.dtype == torch.bool else "i")
             g = X.gather("i." + k, hit, "f" if kind == "f" else "i")
             sub["i." + k] = X.cast(g, "b") if kind == "b" else g
-            arrays["i." + k] = (v.view(torch.uint8) if v.dtype == torch.bool else v).contiguous()
+            arrays["i." + k] = (v if v.element_size() in (4, 8) else v.to(torch.int64)).contiguous()   # slot_payload gathers 4/8-byte elements
         outs = {}
         for name, e in proj.items():
             e = X.wrap(e)
@@ -626,7 +626,7 @@ def _join_fused(be, jt, outer: ColumnBatch, inner: ColumnBatch, ok: torch.Tensor
         for e in outs.values():
             need |= {a for a in arrays if _mentions_array(e, a)}
         out, flags = run_on_gpu(outs, cols, outer.n, predicate=hit >= 0, tables={"jt": jt},
-                                arrays={a: arrays[a] for a in need})
+                                arrays={a: jt.slot_payload(arrays[a]) for a in need})
     except (CompileError, X.TraceError):
         return None
     idx, m = K.compact_flags(flags)
