@@ -80,15 +80,6 @@ __device__ __forceinline__ void tma_load_2d(void* smem_dst, const CUtensorMap* m
       "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];"
       ::"r"(smem_u32(smem_dst)), "l"(map), "r"(smem_u32(bar)), "r"(x), "r"(y) : "memory");
 }
-__device__ __forceinline__ void tma_load_2d_mc(void* smem_dst, const CUtensorMap* map, int x, int y, uint64_t* bar, uint16_t mask) {
-  asm volatile(
-      "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes.multicast::cluster [%0], [%1, {%3, %4}], [%2], %5;"
-      ::"r"(smem_u32(smem_dst)), "l"(map), "r"(smem_u32(bar)), "r"(x), "r"(y), "h"(mask) : "memory");
-}
-__device__ __forceinline__ void tc_commit_mc(uint64_t* bar, uint16_t mask) {
-  asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;"
-               ::"r"(smem_u32(bar)), "h"(mask) : "memory");
-}
 // TMA reduce-add of one 128-byte shared-memory row segment into a global fp32 tensor (the
 // per-centroid sums): one L2 reduction transaction of 32 floats instead of eight 16-byte REDs.
 __device__ __forceinline__ void tma_reduce_add_2d(const CUtensorMap* map, int x, int y, const void* smem_src) {
@@ -148,7 +139,6 @@ struct Bars {
   uint32_t tmem_base;
 };
 
-template <int CLUSTER>
 __global__ void __launch_bounds__(THREADS, 1)
 km_assign(const __grid_constant__ CUtensorMap map_x, const __grid_constant__ CUtensorMap map_c,
           const __grid_constant__ CUtensorMap map_s,
@@ -164,17 +154,13 @@ km_assign(const __grid_constant__ CUtensorMap map_x, const __grid_constant__ CUt
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int nchunks = k / BN;
   const int64_t ntiles_real = (n + BM - 1) / BM;
-  // every CTA of a cluster runs the same number of tiles (out-of-range tiles load zeros and are
-  // skipped by the epilogue), so the shared centroid pipeline stays in lock-step
-  const int64_t ntiles = CLUSTER > 1 ? ((ntiles_real + gridDim.x - 1) / gridDim.x) * gridDim.x : ntiles_real;
-  const uint32_t crank = CLUSTER > 1 ? cluster_rank() : 0;
-  constexpr uint16_t CMASK = (uint16_t)((1u << CLUSTER) - 1);
+  const int64_t ntiles = ntiles_real;
 
   for (int i = threadIdx.x; i < k; i += THREADS) s_cn[i] = cnorm[i];
   if (threadIdx.x == 0) {
     for (int i = 0; i < 2; ++i) { mbar_init(&bars->a_full[i], 1); mbar_init(&bars->a_empty[i], 256);
                                   mbar_init(&bars->t_full[i], 1); mbar_init(&bars->t_empty[i], 256); }
-    for (int i = 0; i < B_STAGES; ++i) { mbar_init(&bars->b_full[i], 1); mbar_init(&bars->b_empty[i], CLUSTER); }
+    for (int i = 0; i < B_STAGES; ++i) { mbar_init(&bars->b_full[i], 1); mbar_init(&bars->b_empty[i], 1); }
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
   if (warp == 1) {
@@ -183,7 +169,6 @@ km_assign(const __grid_constant__ CUtensorMap map_x, const __grid_constant__ CUt
   }
   tc_fence_before();
   __syncthreads();
-  if (CLUSTER > 1) cluster_sync_all();          // peers' barriers are initialised before any multicast
   tc_fence_after();
   const uint32_t tmem_base = bars->tmem_base;
 
@@ -199,16 +184,9 @@ km_assign(const __grid_constant__ CUtensorMap map_x, const __grid_constant__ CUt
           tma_load_2d(sA + ab * A_BYTES + kb * A_KB_BYTES, &map_x, kb * KB, (int)(tile * BM), &bars->a_full[ab]);
         for (int c = 0; c < nchunks; ++c)
           for (int kb = 0; kb < NKB; ++kb) {
-            mbar_wait(&bars->b_empty[bs], bphase ^ 1);          // every CTA of the cluster freed the slot
+            mbar_wait(&bars->b_empty[bs], bphase ^ 1);
             mbar_expect_tx(&bars->b_full[bs], B_STAGE_BYTES);
-            if (CLUSTER == 1) {
-              tma_load_2d(sB + bs * B_STAGE_BYTES, &map_c, kb * KB, c * BN, &bars->b_full[bs]);
-            } else {
-              // this CTA fetches 1/CLUSTER of the centroid rows and multicasts them to all peers
-              constexpr int ROWS = BN / CLUSTER;
-              tma_load_2d_mc(sB + bs * B_STAGE_BYTES + crank * (ROWS * KB * 4), &map_c, kb * KB, c * BN + (int)crank * ROWS,
-                             &bars->b_full[bs], CMASK);
-            }
+            tma_load_2d(sB + bs * B_STAGE_BYTES, &map_c, kb * KB, c * BN, &bars->b_full[bs]);
             if (++bs == B_STAGES) { bs = 0; bphase ^= 1; }
           }
       }
@@ -232,7 +210,7 @@ km_assign(const __grid_constant__ CUtensorMap map_x, const __grid_constant__ CUt
 #pragma unroll
             for (int kk = 0; kk < KB / 8; ++kk)   // K = 8 tf32 = 32 bytes per instruction
               tc_mma_tf32(tmem_base + tb * BN, ad + (uint64_t)(kk * 2), bd + (uint64_t)(kk * 2), IDESC, (kb | kk) != 0);
-            if (CLUSTER == 1) tc_commit(&bars->b_empty[bs]); else tc_commit_mc(&bars->b_empty[bs], CMASK);
+            tc_commit(&bars->b_empty[bs]);
             if (kb == NKB - 1) tc_commit(&bars->t_full[tb]);
           }
           __syncwarp();
@@ -331,7 +309,6 @@ km_assign(const __grid_constant__ CUtensorMap map_x, const __grid_constant__ CUt
 
   tc_fence_before();
   __syncthreads();
-  if (CLUSTER > 1) cluster_sync_all();          // nobody exits while a peer may still write its smem / barriers
   if (warp == 1) {
     tc_fence_after();
     asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "n"(TMEM_COLS) : "memory");
@@ -756,24 +733,9 @@ int dryad_kmeans_assign(const float* points, int64_t n, const float* centroids, 
     DRYAD_LAUNCH_CHECK();
     return DRYAD_OK;
   }
-  const char* cenv = getenv("DRYAD_KM_CLUSTER");
-  int cluster = cenv ? atoi(cenv) : 1;   // multicast clusters measured no faster: shared-memory operand reads bound the SS-mode MMA
-  if (cluster != 1 && cluster != 2 && cluster != 4) cluster = 2;
-  if (cluster > 1) {
-    // TMA multicast loads here read only this GPU's memory, since on B200 a TMA multicast load from
-    // another GPU's memory hung the GPU: the multicast variant runs only when the centroid array is
-    // an ordinary allocation of the CURRENT device; any other pointer takes the plain loads.
-    int cur = -1;
-    cudaPointerAttributes pa;
-    if (cudaGetDevice(&cur) != cudaSuccess || cudaPointerGetAttributes(&pa, centroids) != cudaSuccess ||
-        pa.type != cudaMemoryTypeDevice || pa.device != cur) {
-      cudaGetLastError();
-      cluster = 1;
-    }
-  }
   CUtensorMap mx, mc;
   int rc = make_map(&mx, points, (uint64_t)n); if (rc) return rc;
-  rc = make_map(&mc, centroids, (uint64_t)k, (uint32_t)(BN / cluster)); if (rc) return rc;
+  rc = make_map(&mc, centroids, (uint64_t)k, (uint32_t)BN); if (rc) return rc;
   CUtensorMap ms;
   rc = make_map(&ms, sums, (uint64_t)k, 1u); if (rc) return rc;
   int dev = 0, sms = 148;
@@ -782,26 +744,11 @@ int dryad_kmeans_assign(const float* points, int64_t n, const float* centroids, 
   int64_t ntiles = (n + BM - 1) / BM;
   int grid = (int)(ntiles < sms ? ntiles : sms);
   if (max_ctas > 0 && grid > max_ctas) grid = max_ctas;
-  grid = (grid / cluster) * cluster;
-  if (grid == 0) { grid = cluster; }
+  if (grid == 0) grid = 1;
   const char* dbg = getenv("DRYAD_KM_DEBUG");
   const int dbgv = dbg ? atoi(dbg) : 0;
-  cudaLaunchConfig_t cfg = {};
-  cfg.gridDim = dim3((unsigned)grid); cfg.blockDim = dim3(THREADS); cfg.dynamicSmemBytes = SMEM_BYTES; cfg.stream = (cudaStream_t)stream;
-  cudaLaunchAttribute attr[1];
-  attr[0].id = cudaLaunchAttributeClusterDimension;
-  attr[0].val.clusterDim.x = (unsigned)cluster; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
-  cfg.attrs = attr; cfg.numAttrs = 1;
-  if (cluster == 1) {
-    DRYAD_CUDA_TRY(cudaFuncSetAttribute(km_assign<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SMEM_BYTES));
-    DRYAD_CUDA_TRY(cudaLaunchKernelEx(&cfg, km_assign<1>, mx, mc, ms, cnorm, n, k, assign, sums, counts, inertia, dbgv));
-  } else if (cluster == 2) {
-    DRYAD_CUDA_TRY(cudaFuncSetAttribute(km_assign<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SMEM_BYTES));
-    DRYAD_CUDA_TRY(cudaLaunchKernelEx(&cfg, km_assign<2>, mx, mc, ms, cnorm, n, k, assign, sums, counts, inertia, dbgv));
-  } else {
-    DRYAD_CUDA_TRY(cudaFuncSetAttribute(km_assign<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SMEM_BYTES));
-    DRYAD_CUDA_TRY(cudaLaunchKernelEx(&cfg, km_assign<4>, mx, mc, ms, cnorm, n, k, assign, sums, counts, inertia, dbgv));
-  }
+  DRYAD_CUDA_TRY(cudaFuncSetAttribute(km_assign, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SMEM_BYTES));
+  km_assign<<<grid, THREADS, SMEM_BYTES, (cudaStream_t)stream>>>(mx, mc, ms, cnorm, n, k, assign, sums, counts, inertia, dbgv);
   DRYAD_LAUNCH_CHECK();
   return DRYAD_OK;
 }
