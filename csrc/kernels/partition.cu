@@ -51,6 +51,8 @@ struct Params {
   uint32_t* block_counts;  // [nparts][nblocks]
   int32_t* status;
   int max_width;
+  uint64_t* key_out;       // optional: the count pass also writes every row's derived key here
+  int filter_mod, filter_rem;   // filter_mod > 0: this scatter pass moves only partitions p with p % filter_mod == filter_rem
 };
 
 __device__ __forceinline__ uint64_t load_key(const Params& P, int64_t row) {
@@ -112,7 +114,9 @@ __global__ void __launch_bounds__(THREADS) sh_count(Params P) {
     const bool in = r < row1;
     const uint32_t amask = __ballot_sync(0xffffffffu, in);
     if (in) {
-      uint32_t p = part_of(load_key(P, r), P.mode, P.nparts, s_seps);
+      const uint64_t key = load_key(P, r);
+      if (P.key_out) P.key_out[r] = key;
+      uint32_t p = part_of(key, P.mode, P.nparts, s_seps);
       uint32_t peers = __match_any_sync(amask, p);
       if ((peers >> lane_id()) <= 1u) atomicAdd(&s_cnt[p], (uint32_t)__popc(peers));
     }
@@ -166,6 +170,7 @@ __global__ void __launch_bounds__(256) sh_publish(Params P, uint32_t* done_count
 
 __global__ void __launch_bounds__(THREADS) sh_scatter(Params P) {
   extern __shared__ __align__(16) unsigned char smem[];
+  const int vb = (int)blockIdx.x;
   // layout: in[TILE*maxw] | out[TILE*maxw + 32*nparts + 16] | small arrays
   const int maxw = P.max_width;
   unsigned char* s_in = smem;
@@ -200,7 +205,7 @@ __global__ void __launch_bounds__(THREADS) sh_scatter(Params P) {
       total += c;
     }
     if (total > P.capacity[p]) s_abort = 1;
-    s_gbase[p] = before + (int64_t)P.block_counts[(size_t)p * P.nblocks + blockIdx.x];
+    s_gbase[p] = before + (int64_t)P.block_counts[(size_t)p * P.nblocks + vb];
   }
   if (P.mode == DRYAD_PART_RANGE_ASC || P.mode == DRYAD_PART_RANGE_DESC)
     for (int i = tid; i < np - 1; i += THREADS) s_seps[i] = P.separators[i];
@@ -212,7 +217,7 @@ __global__ void __launch_bounds__(THREADS) sh_scatter(Params P) {
   const int total_cols = P.ncols + (P.emit_key ? 1 : 0);
 
   for (int t = 0; t < P.tiles_per_block; ++t) {
-    int64_t row0 = ((int64_t)blockIdx.x * P.tiles_per_block + t) * TILE;
+    int64_t row0 = ((int64_t)vb * P.tiles_per_block + t) * TILE;
     if (row0 >= P.n) break;
     const int valid = (int)min((int64_t)TILE, P.n - row0);
 
@@ -236,10 +241,11 @@ __global__ void __launch_bounds__(THREADS) sh_scatter(Params P) {
     __syncthreads();
 
     uint64_t key = 0; uint32_t part = 0, rank = 0;
-    const bool active = tid < valid;
+    bool active = tid < valid;
     if (active) {
       key = key_from_smem(P, s_in + (size_t)tid * kw);
       part = part_of(key, P.mode, np, s_seps);
+      if (P.filter_mod > 0 && (int)(part % (uint32_t)P.filter_mod) != P.filter_rem) active = false;   // another pass moves it
     }
     {
       uint32_t amask = __ballot_sync(0xffffffffu, active);
@@ -408,50 +414,63 @@ __global__ void __launch_bounds__(THREADS) sh_scatter_tma(Params P) {
                   asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory"); }
   __syncthreads();
 
-  // prefetch the first tile while waiting for the peers' counts
-  const int64_t tile0 = (int64_t)blockIdx.x * P.tiles_per_block;
+  // Persistent form: the grid may be smaller than the number of row blocks the count pass used
+  // (a capped CTA count leaves SMs to kernels on other streams while this link-bound kernel
+  // runs); every CTA walks the virtual blocks vb = blockIdx.x, blockIdx.x + gridDim.x, ...
   const int64_t ntiles_total = (P.n + TILE - 1) / TILE;
-  int my_tiles = (int)min((int64_t)P.tiles_per_block, ntiles_total - tile0);
-  if (my_tiles < 0) my_tiles = 0;
-  auto issue_load = [&](int t) {
-    const int64_t row0 = (tile0 + t) * TILE;
+  uint32_t g = 0;                       // tiles processed by this CTA so far: buffer = g & 1
+  auto issue_load = [&](int64_t tile, uint32_t gi) {
+    const int64_t row0 = tile * TILE;
     const int valid = (int)min((int64_t)TILE, P.n - row0);
     const uint32_t bytes = ((uint32_t)valid * w) & ~15u;
-    uint64_t* bar = &s_full[t & 1];
+    uint64_t* bar = &s_full[gi & 1];
     mbar_expect_tx(bar, bytes);
-    if (bytes) bulk_load(s_in + (t & 1) * in_bytes, P.src[0] + (size_t)row0 * w, bytes, bar);
+    if (bytes) bulk_load(s_in + (gi & 1) * in_bytes, P.src[0] + (size_t)row0 * w, bytes, bar);
   };
-  if (tid == 0 && my_tiles > 0) issue_load(0);
+  auto tiles_of = [&](int vb) {
+    int mt = (int)min((int64_t)P.tiles_per_block, ntiles_total - (int64_t)vb * P.tiles_per_block);
+    return mt < 0 ? 0 : mt;
+  };
+  // prefetch the first tile while waiting for the peers' counts
+  const int vb0 = (int)blockIdx.x;
+  const bool have_first = vb0 < P.nblocks && tiles_of(vb0) > 0;
+  if (tid == 0 && have_first) issue_load((int64_t)vb0 * P.tiles_per_block, 0);
 
   if (tid < P.world) {
     if (!spin_until_ge(&P.flags_local[tid], P.epoch, SPIN_CYCLES)) { s_abort = 2; }
   }
   __syncthreads();
-  if (s_abort) { if (tid == 0) atomicMax(P.status, 2); if (tid == 0 && my_tiles > 0) mbar_wait(&s_full[0], 0); return; }
+  if (s_abort) { if (tid == 0) atomicMax(P.status, 2); if (tid == 0 && have_first) mbar_wait(&s_full[0], 0); return; }
   for (int p = tid; p < np; p += THREADS) {
-    int64_t before = 0, total = 0;
-    for (int r = 0; r < P.world; ++r) {
-      int64_t c = reinterpret_cast<const volatile int64_t*>(P.counts_local)[(size_t)r * np + p];
-      if (r < P.rank) before += c;
-      total += c;
-    }
+    int64_t total = 0;
+    for (int r = 0; r < P.world; ++r) total += reinterpret_cast<const volatile int64_t*>(P.counts_local)[(size_t)r * np + p];
     if (total > P.capacity[p]) s_abort = 1;
-    s_gbase[p] = before + (int64_t)P.block_counts[(size_t)p * P.nblocks + blockIdx.x];
   }
   if (P.mode == DRYAD_PART_RANGE_ASC || P.mode == DRYAD_PART_RANGE_DESC)
     for (int i = tid; i < np - 1; i += THREADS) s_seps[i] = P.separators[i];
   __syncthreads();
-  if (s_abort) { if (tid == 0) atomicMax(P.status, 1); if (tid == 0 && my_tiles > 0) mbar_wait(&s_full[0], 0); return; }
+  if (s_abort) { if (tid == 0) atomicMax(P.status, 1); if (tid == 0 && have_first) mbar_wait(&s_full[0], 0); return; }
 
-  for (int t = 0; t < my_tiles; ++t) {
-    const int buf = t & 1;
+  for (int vb = vb0; vb < P.nblocks; vb += gridDim.x) {
+  const int64_t tile0 = (int64_t)vb * P.tiles_per_block;
+  const int my_tiles = tiles_of(vb);
+  if (vb != vb0 && tid == 0 && my_tiles > 0) issue_load(tile0, g);   // in[g&1] was released at the end of the previous tile
+  for (int p = tid; p < np; p += THREADS) {
+    int64_t before = 0;
+    for (int r = 0; r < P.rank; ++r) before += reinterpret_cast<const volatile int64_t*>(P.counts_local)[(size_t)r * np + p];
+    s_gbase[p] = before + (int64_t)P.block_counts[(size_t)p * P.nblocks + vb];
+  }
+  __syncthreads();
+
+  for (int t = 0; t < my_tiles; ++t, ++g) {
+    const int buf = g & 1;
     const int64_t row0 = (tile0 + t) * TILE;
     const int valid = (int)min((int64_t)TILE, P.n - row0);
     unsigned char* in = s_in + buf * in_bytes;
     unsigned char* out = s_out + buf * out_bytes;
     unsigned char* kout = s_kout + buf * kout_bytes;
-    if (tid == 0 && t + 1 < my_tiles) issue_load(t + 1);       // in[buf^1] was released at the end of t-1
-    mbar_wait(&s_full[buf], (t >> 1) & 1);
+    if (tid == 0 && t + 1 < my_tiles) issue_load(tile0 + t + 1, g + 1);       // in[buf^1] was released at the end of the previous tile
+    mbar_wait(&s_full[buf], (g >> 1) & 1);
     {   // tail bytes that are not a multiple of 16 (last partial tile only)
       const uint32_t total_b = (uint32_t)valid * w, bulk_b = total_b & ~15u;
       for (uint32_t b = bulk_b + 4 * tid; b < total_b; b += 4 * THREADS)
@@ -461,8 +480,11 @@ __global__ void __launch_bounds__(THREADS) sh_scatter_tma(Params P) {
     __syncthreads();
 
     uint64_t key = 0; uint32_t part = 0, rank = 0;
-    const bool active = tid < valid;
-    if (active) { key = key_from_smem(P, in + (size_t)tid * w); part = part_of(key, P.mode, np, s_seps); }
+    bool active = tid < valid;
+    if (active) {
+      key = key_from_smem(P, in + (size_t)tid * w); part = part_of(key, P.mode, np, s_seps);
+      if (P.filter_mod > 0 && (int)(part % (uint32_t)P.filter_mod) != P.filter_rem) active = false;   // another pass moves it
+    }
     {
       uint32_t amask = __ballot_sync(0xffffffffu, active);
       if (active) {
@@ -543,6 +565,7 @@ __global__ void __launch_bounds__(THREADS) sh_scatter_tma(Params P) {
     // it must have drained the reads of tile t; warp leaders wait here, one tile late
     if (lane == 0) asm volatile("cp.async.bulk.wait_group.read 1;" ::: "memory");
     __syncthreads();
+  }
   }
   if (lane == 0) asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");   // writes performed
   __threadfence_system();
@@ -631,32 +654,47 @@ int dryad_shuffle_run(const DryadShuffleDesc* d, void* stream) {
   P.flags_local = d->flags_local; P.flags_peers = d->flags_peers; P.epoch = d->epoch;
   P.status = d->status;
   P.nblocks = pick_blocks(d->n, &P.tiles_per_block);
+  P.key_out = d->key_out;
+  P.filter_mod = d->filter_mod; P.filter_rem = d->filter_rem;
+  if (d->filter_mod < 0 || (d->filter_mod > 0 && (d->filter_rem < 0 || d->filter_rem >= d->filter_mod))) return DRYAD_ERR_BAD_ARG;
+  const int vblocks = P.nblocks;
   size_t counts_bytes = (((size_t)P.nparts * P.nblocks * 4) + 255) & ~(size_t)255;
   if (!d->scratch || d->scratch_bytes < counts_bytes + 256) return DRYAD_ERR_SCRATCH;
   P.block_counts = (uint32_t*)d->scratch;
   uint32_t* done_counter = (uint32_t*)((unsigned char*)d->scratch + counts_bytes);
-  DRYAD_CUDA_TRY(cudaMemsetAsync(done_counter, 0, 4, st));
+  const int phases = d->phases ? d->phases : (DRYAD_SHUFFLE_PLAN | DRYAD_SHUFFLE_SCATTER | DRYAD_SHUFFLE_BARRIER);
+  const int slot = d->barrier_slot ? d->barrier_slot : 1;
+  if (slot < 0 || slot >= DRYAD_FLAG_SLOTS) return DRYAD_ERR_BAD_ARG;
 
-  sh_count<<<P.nblocks, THREADS, 0, st>>>(P);
-  DRYAD_LAUNCH_CHECK();
-  sh_publish<<<P.nparts, 256, 0, st>>>(P, done_counter);
-  DRYAD_LAUNCH_CHECK();
-  const char* no_tma = getenv("DRYAD_SHUFFLE_NO_TMA");
-  const bool tma_ok = d->ncols == 1 && d->width[0] >= 16 && (((uintptr_t)d->src[0]) & 15) == 0 &&
-                      scatter_tma_smem((int)d->width[0], P.nparts, d->emit_key) <= 200 * 1024 && !(no_tma && no_tma[0] == '1');
-  if (tma_ok) {
-    size_t smem = scatter_tma_smem((int)d->width[0], P.nparts, d->emit_key);
-    DRYAD_CUDA_TRY(cudaFuncSetAttribute(sh_scatter_tma, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    sh_scatter_tma<<<P.nblocks, THREADS, smem, st>>>(P);
-  } else {
-    size_t smem = scatter_smem(maxw, P.nparts);
-    DRYAD_CUDA_TRY(cudaFuncSetAttribute(sh_scatter, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    sh_scatter<<<P.nblocks, THREADS, smem, st>>>(P);
+  if (phases & DRYAD_SHUFFLE_PLAN) {
+    DRYAD_CUDA_TRY(cudaMemsetAsync(done_counter, 0, 4, st));
+    sh_count<<<P.nblocks, THREADS, 0, st>>>(P);
+    DRYAD_LAUNCH_CHECK();
+    sh_publish<<<P.nparts, 256, 0, st>>>(P, done_counter);
+    DRYAD_LAUNCH_CHECK();
   }
-  DRYAD_LAUNCH_CHECK();
-  sh_barrier<<<1, 32, 0, st>>>(d->flags_peers, d->flags_local, d->rank, d->world, 1, d->epoch,
-                               d->status);
-  DRYAD_LAUNCH_CHECK();
+  if (phases & DRYAD_SHUFFLE_SCATTER) {
+    const char* no_tma = getenv("DRYAD_SHUFFLE_NO_TMA");
+    const bool tma_ok = d->ncols == 1 && d->width[0] >= 16 && (((uintptr_t)d->src[0]) & 15) == 0 &&
+                        scatter_tma_smem((int)d->width[0], P.nparts, d->emit_key) <= 200 * 1024 && !(no_tma && no_tma[0] == '1');
+    if (tma_ok) {
+      size_t smem = scatter_tma_smem((int)d->width[0], P.nparts, d->emit_key);
+      DRYAD_CUDA_TRY(cudaFuncSetAttribute(sh_scatter_tma, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+      int grid = vblocks;
+      if (d->max_ctas > 0 && grid > d->max_ctas) grid = d->max_ctas;   // persistent CTAs walk the row blocks
+      if (grid > 0) sh_scatter_tma<<<grid, THREADS, smem, st>>>(P);
+    } else {
+      size_t smem = scatter_smem(maxw, P.nparts);
+      DRYAD_CUDA_TRY(cudaFuncSetAttribute(sh_scatter, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+      if (vblocks > 0) sh_scatter<<<vblocks, THREADS, smem, st>>>(P);
+    }
+    DRYAD_LAUNCH_CHECK();
+  }
+  if (phases & DRYAD_SHUFFLE_BARRIER) {
+    sh_barrier<<<1, 32, 0, st>>>(d->flags_peers, d->flags_local, d->rank, d->world, slot,
+                                 d->barrier_epoch ? d->barrier_epoch : d->epoch, d->status);
+    DRYAD_LAUNCH_CHECK();
+  }
   return DRYAD_OK;
 }
 

@@ -39,11 +39,17 @@ __global__ void extract_be64_kernel(const unsigned char* __restrict__ rowsp, int
                                     int key_off, uint64_t* __restrict__ out) {
   int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   int64_t stride = (int64_t)gridDim.x * blockDim.x;
+  const bool aligned = ((reinterpret_cast<uintptr_t>(rowsp) | (uintptr_t)width | (uintptr_t)key_off) & 3) == 0;
   for (; i < n; i += stride) {
     const unsigned char* k = rowsp + (size_t)i * width + key_off;
     uint64_t v = 0;
+    if (aligned) {          // two word loads + byte swaps instead of eight byte loads
+      const uint32_t* w = reinterpret_cast<const uint32_t*>(k);
+      v = ((uint64_t)__byte_perm(__ldg(w), 0, 0x0123) << 32) | (uint64_t)__byte_perm(__ldg(w + 1), 0, 0x0123);
+    } else {
 #pragma unroll
-    for (int b = 0; b < 8; ++b) v = (v << 8) | (uint64_t)k[b];
+      for (int b = 0; b < 8; ++b) v = (v << 8) | (uint64_t)k[b];
+    }
     out[i] = v;
   }
 }
@@ -109,6 +115,26 @@ __global__ void select_separators_kernel(const uint64_t* __restrict__ sorted, in
                                          int pcount, int descending, uint64_t* __restrict__ seps) {
   int i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= pcount - 1) return;
+  if (cnt == 0) { seps[i] = descending ? 0ull : ~0ull; return; }
+  if (cnt < pcount) {
+    if (descending) seps[i] = (i < cnt) ? sorted[cnt - 1 - i] : sorted[0];
+    else seps[i] = (i < cnt) ? sorted[i] : sorted[cnt - 1];
+    return;
+  }
+  int64_t intv = cnt / pcount;
+  seps[i] = descending ? sorted[cnt - intv * (i + 1)] : sorted[intv * (i + 1)];
+}
+
+// Same pick with the sample count still on the device: cnt = sum over r of min(counts[r], cap_each).
+// `sorted` holds every rank's fixed-size sample slab (unused slots pre-filled with ~0, so they sort
+// behind the real samples) — no host round trip between sampling and the shuffle.
+__global__ void select_separators_dev_kernel(const uint64_t* __restrict__ sorted, const int64_t* __restrict__ counts,
+                                             int ncounts, int64_t cap_each, int pcount, int descending,
+                                             uint64_t* __restrict__ seps) {
+  int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= pcount - 1) return;
+  int64_t cnt = 0;
+  for (int r = 0; r < ncounts; ++r) { int64_t c = counts[r]; cnt += c < cap_each ? c : cap_each; }
   if (cnt == 0) { seps[i] = descending ? 0ull : ~0ull; return; }
   if (cnt < pcount) {
     if (descending) seps[i] = (i < cnt) ? sorted[cnt - 1 - i] : sorted[0];
@@ -265,6 +291,41 @@ __global__ void fix_ties32_kernel(const uint32_t* __restrict__ keys, uint32_t* _
   }
 }
 
+// Tie repair that needs no rows: runs of equal 32-bit windows are ordered by the full 64-bit key
+// prefix of each slot (keys64[idx]), then by slot (stable).  Pairs whose 64-bit prefixes are equal
+// cannot be decided without the remaining key bytes: they are counted in `unresolved` when the key
+// is wider than the prefix (`wide_key`), so the caller can fall back to the row-based repair.
+__global__ void fix_ties32_keys_kernel(const uint32_t* __restrict__ keys, uint32_t* __restrict__ idx, int64_t n,
+                                       const uint64_t* __restrict__ keys64, int max_run, int wide_key,
+                                       int32_t* __restrict__ long_runs, int32_t* __restrict__ unresolved) {
+  int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  int64_t stride = (int64_t)gridDim.x * blockDim.x;
+  for (; i < n; i += stride) {
+    const uint32_t k = keys[i];
+    if (i + 1 >= n || keys[i + 1] != k) continue;
+    if (i > 0 && keys[i - 1] == k) continue;
+    int64_t e = i + 1;
+    while (e < n && keys[e] == k) ++e;
+    if (e - i > max_run) { atomicAdd(long_runs, 1); continue; }
+    int eq = 0;
+    for (int64_t a = i + 1; a < e; ++a) {
+      const uint32_t ia = idx[a];
+      const uint64_t ka = keys64[ia];
+      int64_t b = a - 1;
+      while (b >= i) {
+        const uint32_t ib = idx[b];
+        const uint64_t kb = keys64[ib];
+        if (kb == ka) eq = 1;
+        if (kb < ka || (kb == ka && ib < ia)) break;
+        idx[b + 1] = ib;
+        --b;
+      }
+      idx[b + 1] = ia;
+    }
+    if (eq && wide_key) atomicAdd(unresolved, 1);
+  }
+}
+
 // Element gather for 4- and 8-byte columns.
 template <typename T>
 __global__ void gather_elems_kernel(const T* __restrict__ in, const uint32_t* __restrict__ idx,
@@ -366,6 +427,15 @@ int dryad_select_separators(const uint64_t* sorted, int64_t cnt, int pcount, int
   return DRYAD_OK;
 }
 
+int dryad_select_separators_dev(const uint64_t* sorted, const int64_t* counts, int ncounts, int64_t cap_each,
+                                int pcount, int descending, uint64_t* seps, void* stream) {
+  if (pcount < 1 || ncounts < 1 || cap_each < 0) return DRYAD_ERR_BAD_ARG;
+  if (pcount == 1) return DRYAD_OK;
+  select_separators_dev_kernel<<<(pcount + 254) / 256, 256, 0, (cudaStream_t)stream>>>(sorted, counts, ncounts, cap_each, pcount, descending, seps);
+  DRYAD_LAUNCH_CHECK();
+  return DRYAD_OK;
+}
+
 int dryad_fix_ties(const uint64_t* keys, uint32_t* idx, int64_t n, const uint8_t* rowsp, int width,
                    int extra_off, int extra, int max_run, int descending, uint64_t prefix_mask,
                    int32_t* long_runs, void* stream) {
@@ -423,6 +493,14 @@ int dryad_fix_ties32(const uint32_t* keys, uint32_t* idx, int64_t n, const uint8
   if (n <= 1 || extra <= 0) return DRYAD_OK;
   if (extra_off < 0 || extra_off + extra > width) return DRYAD_ERR_BAD_ARG;
   fix_ties32_kernel<<<grid_for(n, 256), 256, 0, (cudaStream_t)stream>>>(keys, idx, n, rowsp, width, extra_off, extra, max_run, descending, long_runs);
+  DRYAD_LAUNCH_CHECK();
+  return DRYAD_OK;
+}
+
+int dryad_fix_ties32_keys(const uint32_t* keys, uint32_t* idx, int64_t n, const uint64_t* keys64, int max_run,
+                          int wide_key, int32_t* long_runs, int32_t* unresolved, void* stream) {
+  if (n <= 1) return DRYAD_OK;
+  fix_ties32_keys_kernel<<<grid_for(n, 256), 256, 0, (cudaStream_t)stream>>>(keys, idx, n, keys64, max_run, wide_key, long_runs, unresolved);
   DRYAD_LAUNCH_CHECK();
   return DRYAD_OK;
 }

@@ -17,7 +17,7 @@ _kernels = None
 _host = None
 
 MAX_PEERS = 8
-FLAG_SLOTS = 4
+FLAG_SLOTS = 8
 MAX_LANES = 8
 EXPR_MAX_INSTR = 64
 EXPR_MAX_COLS = 16
@@ -42,7 +42,12 @@ class ShuffleDesc(C.Structure):
         ("epoch", c_uint64),
         ("scratch", c_void_p), ("scratch_bytes", c_size_t),
         ("status", c_void_p),
+        ("key_out", c_void_p), ("phases", c_int32), ("barrier_slot", c_int32), ("max_ctas", c_int32),
+        ("filter_mod", c_int32), ("filter_rem", c_int32), ("barrier_epoch", c_uint64),
     ]
+
+
+SHUFFLE_PLAN, SHUFFLE_SCATTER, SHUFFLE_BARRIER = 1, 2, 4
 
 
 class ExprInstr(C.Structure):
@@ -89,9 +94,11 @@ def _declare_kernels(lib):
     _sig(lib, "dryad_sample_rows", c_int, [P, c_int, c_int, c_int64, c_uint64, c_double, P, P,
                                            c_int64, P])
     _sig(lib, "dryad_select_separators", c_int, [P, c_int64, c_int, c_int, P, P])
+    _sig(lib, "dryad_select_separators_dev", c_int, [P, P, c_int, c_int64, c_int, c_int, P, P])
     _sig(lib, "dryad_extract_be64", c_int, [P, c_int64, c_int, c_int, P, P])
     _sig(lib, "dryad_fix_ties", c_int, [P, P, c_int64, P, c_int, c_int, c_int, c_int, c_int, c_uint64, P, P])
     _sig(lib, "dryad_gather_rows", c_int, [P, P, P, c_int64, c_int, P])
+    _sig(lib, "dryad_fix_ties32_keys", c_int, [P, P, c_int64, P, c_int, c_int, P, P, P])
     _sig(lib, "dryad_extract_be_window", c_int, [P, c_int64, c_int, c_int, c_int, P, P])
     _sig(lib, "dryad_shift_u64_to_u32", c_int, [P, c_int64, c_int, P, P])
     _sig(lib, "dryad_fix_ties32", c_int, [P, P, c_int64, P, c_int, c_int, c_int, c_int, c_int, P, P])

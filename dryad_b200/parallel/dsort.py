@@ -1,12 +1,14 @@
-"""Distributed OrderBy over fixed-width rows: sample → separators → fused range shuffle → local
-radix sort → tie repair → payload gather.
+"""Distributed OrderBy over fixed-width rows: sample → separators → range exchange → local radix
+sort → tie repair → payload gather.
 
 Mirrors the reference's OrderBy plan (LinqToDryad/DryadLinqQueryGen.cs:2362-2521): Phase1Sampling
 per partition, a single RangeSampler producing `pcount-1` separators that are broadcast to every
 distributor, RangePartition with CrossProduct edges into a Merge, then a per-partition Sort.
-Here the sampler output crosses GPUs as small P2P copies, the RangePartition+Merge is the fused
-shuffle kernel, and the sort is the one-sweep radix sort on (64-bit key prefix, row index) followed
-by one payload gather, so each 100-byte row crosses NVLink once and HBM three times.
+Here the sampler output crosses GPUs as small P2P copies, the RangePartition+Merge is the sort
+exchange of csrc/kernels/sortx.cu (ascending order; keys first, then the rows one key sub-range per
+round, so the receiver sorts the keys and gathers finished sub-ranges while later rounds are still
+on NVLink) or the fused shuffle kernel (descending order), and the sort is the one-sweep radix sort
+on (key window, slot) followed by a payload gather: each 100-byte row crosses NVLink once.
 """
 from __future__ import annotations
 
@@ -14,6 +16,7 @@ from typing import Optional
 
 import torch
 
+from .. import _native as N
 from ..ops import core as K
 from .shuffle import ColSpec, FusedShuffle
 from .symm import SymmetricArena, tensor_from_ptr
@@ -28,7 +31,7 @@ class RowSorter:
 
     def __init__(self, arena: SymmetricArena, max_rows: int, width: int, *, key_off: int = 0,
                  key_len: int = 10, slack: float = 1.12, sample_rate: float = SAMPLE_RATE,
-                 descending: bool = False):
+                 descending: bool = False, passes: Optional[int] = None):
         if key_len < 8:
             raise ValueError("RowSorter needs at least 8 key bytes (pad shorter keys)")
         self.arena, self.width, self.key_off, self.key_len = arena, width, key_off, key_len
@@ -39,13 +42,27 @@ class RowSorter:
         self.sample_rate = sample_rate
         self.sample_cap = max(1024, min(MAX_SAMPLES // self.world, int(max_rows * sample_rate * 2) + 1024))
         if self.world > 1:
-            self.cap_rows = int(max_rows * slack) + 4096
             import os
-            # DRYAD_SORT_EMIT_KEY=0: do not ship the 8-byte key prefix next to each row; the receiver
-            # re-extracts it from the rows (7 % fewer NVLink bytes, one more pass over row heads)
-            self.emit_key = os.environ.get("DRYAD_SORT_EMIT_KEY", "1") != "0"
-            self.shuffle = FusedShuffle(arena, [ColSpec(width, torch.uint8, width)], self.cap_rows,
-                                        emit_key=self.emit_key, max_rows_in=max_rows)
+            # every destination's key range can be cut into R sub-ranges with their own receive
+            # buffers (FusedShuffle parts_per_rank): the rows then travel one sub-range per pass and a
+            # sub-range is gathered while later passes are still on NVLink.  Measured on 2 and 8
+            # B200s each extra pass costs more SM time re-reading the rows than the overlap returns
+            # (profiles/README.md), so the default is one pass.
+            R = passes if passes is not None else int(os.environ.get("DRYAD_SORT_PASSES", "1"))
+            self.R = max(1, min(16, R, 256 // self.world))
+            # keys first / rows behind on a side stream (ascending order); 0 = one fused shuffle
+            self.split = os.environ.get("DRYAD_SORT_SPLIT", "1") != "0" and not descending
+            # the row transfer is link-bound: a capped number of persistent CTAs leaves SM resources
+            # to the key sort and the gathers that run concurrently on the main stream
+            self.payload_ctas = int(os.environ.get("DRYAD_SORT_PAYLOAD_CTAS", "148"))
+            self.cap_part = int(max_rows * slack / self.R) + 4096
+            self.cap_rows = self.cap_part * self.R
+            self.emit_key = True
+            self.shuffle = FusedShuffle(arena, [ColSpec(width, torch.uint8, width)], self.cap_part,
+                                        parts_per_rank=self.R, emit_key=True, max_rows_in=max_rows)
+            self.side = torch.cuda.Stream(device=dev) if self.split else None
+            self._peek_buf = torch.empty(1024, dtype=torch.int64).pin_memory()
+            self._peek_ev = torch.cuda.Event()
             self.all_samples, self.all_samples_off = arena.alloc((self.world, self.sample_cap), torch.int64)
             self.all_counts, self.all_counts_off = arena.alloc((self.world,), torch.int64)
             self._peer_sample_views = []
@@ -56,15 +73,23 @@ class RowSorter:
                 cp = tensor_from_ptr(arena.peer_ptr(r, self.all_counts_off + self.rank * 8), 8, dev).view(torch.int64)
                 self._peer_sample_views.append(sp)
                 self._peer_count_views.append(cp)
+            self._samples = torch.empty(self.sample_cap, dtype=torch.int64, device=dev)
+            self._sample_cnt = torch.zeros(1, dtype=torch.int64, device=dev)
+            self._sorted_alt = torch.empty(self.world * self.sample_cap, dtype=torch.int64, device=dev)
+            self._seps = torch.empty(self.world * self.R - 1, dtype=torch.int64, device=dev)
+            self._tie_flags = torch.zeros((self.R, 2), dtype=torch.int32, device=dev)   # per sub-range: [long runs, unresolved]
         else:
-            self.cap_rows = self.max_rows
+            self.R = 1
+            self.cap_part = self.cap_rows = self.max_rows
             self.shuffle = None
+            self.split = False
         n = self.cap_rows
         self.keys_a = torch.empty(n, dtype=torch.int64, device=dev)
         self.keys_b = torch.empty(n, dtype=torch.int64, device=dev)
         self.idx_a = torch.empty(n, dtype=torch.int32, device=dev)
         self.idx_b = torch.empty(n, dtype=torch.int32, device=dev)
         self.out = torch.empty((n, width), dtype=torch.uint8, device=dev)
+        self._runs = torch.zeros(1, dtype=torch.int32, device=dev)
         self.last_long_runs: Optional[torch.Tensor] = None
         self.profile = False                  # diagnostic: record per-phase device times in self.timing
         self.timing: dict = {}
@@ -83,24 +108,42 @@ class RowSorter:
             self._marks = []
 
     # -- separators ----------------------------------------------------------------------------
+    def _peek(self, t: torch.Tensor) -> list:
+        """Read a small device tensor on the host without draining the stream behind it: async copy
+        into pinned memory, then wait for THAT copy only (work queued later, or on the side
+        stream, keeps running)."""
+        k = t.numel()
+        self._peek_buf[:k].copy_(t, non_blocking=True)
+        self._peek_ev.record()
+        self._peek_ev.synchronize()
+        return self._peek_buf[:k].tolist()
+
     def _separators(self, rows: torch.Tensor) -> torch.Tensor:
-        samples, cnt = K.sample_rows(rows, self.key_off, seed=self.rank, rate=self.sample_rate,
-                                     cap=self.sample_cap)
-        cnt = torch.clamp(cnt, max=self.sample_cap)
-        # publish my samples + count into every rank's table (P2P copies), then barrier
+        """Phase1Sampling + RangeSampler (DryadLinqSampler.cs:42-106, 139-246) with no host round
+        trip: every rank writes a fixed-size sample slab (unused slots = ~0, which sort last) and its
+        count into every rank's table; each rank sorts the whole table and picks the world*R - 1
+        separators from the first sum(counts) entries."""
+        lib = N.kernels()
+        self._samples.fill_(-1)
+        self._sample_cnt.zero_()
+        N.check(lib.dryad_sample_rows(K.ptr(rows), rows.shape[1], self.key_off, rows.shape[0], self.rank,
+                                      self.sample_rate, K.ptr(self._samples), K.ptr(self._sample_cnt),
+                                      self.sample_cap, K.stream()), "sample_rows")
+        K._count()
         for r in range(self.world):
-            self._peer_sample_views[r].copy_(samples, non_blocking=True)
-            self._peer_count_views[r].copy_(cnt, non_blocking=True)
+            self._peer_sample_views[r].copy_(self._samples, non_blocking=True)
+            self._peer_count_views[r].copy_(self._sample_cnt, non_blocking=True)
         self.arena.barrier(slot=2)
-        counts = self.all_counts.tolist()                      # host sync (tiny)
-        parts = [self.all_samples[r, :int(counts[r])] for r in range(self.world)]
-        allk = torch.cat(parts) if parts else samples[:0]
-        total = allk.numel()
-        skeys, _ = K.radix_sort_pairs(allk.contiguous(), None)   # ascending; the picker handles descending
-        return K.select_separators(skeys, total, self.world, self.descending)
+        allk = self.all_samples.view(-1)
+        skeys, _ = K.radix_sort_pairs(allk, None, keys_alt=self._sorted_alt)   # ascending; the picker handles descending
+        N.check(lib.dryad_select_separators_dev(K.ptr(skeys), K.ptr(self.all_counts), self.world, self.sample_cap,
+                                                self.world * self.R, int(self.descending), K.ptr(self._seps), K.stream()),
+                "select_separators_dev")
+        K._count()
+        return self._seps
 
     # -- the sort ------------------------------------------------------------------------------
-    WINDOW_BITS = 32          # radix passes cover this many key bits; ties are repaired from the rows
+    WINDOW_BITS = 32          # radix passes cover this many key bits; ties are repaired afterwards
     WINDOW_MAX_RUN = 64
 
     @staticmethod
@@ -110,26 +153,28 @@ class RowSorter:
         top = max((lo ^ hi).bit_length(), RowSorter.WINDOW_BITS)
         return top - RowSorter.WINDOW_BITS, top
 
-    def _local_sort(self, keys, m: int, src_rows: torch.Tensor, lo: int, hi: int):
-        """Sort permutation of the first m rows of src_rows.  `keys`: the rows' 64-bit key prefixes
-        (int64 bits) when the shuffle delivered them, else None.  Fast path: a 32-bit window of the
-        prefix (leading bits shared by the whole partition are skipped) sorted as (u32, u32) pairs in
-        4 radix passes + tie repair on the remaining key bytes; a partition with long runs of equal
-        windows (not TeraSort-like) falls back to all 8 passes over the 64-bit prefix."""
-        from .. import _native as N
+    def _local_sort(self, keys, m: int, src_rows: torch.Tensor, lo: int, hi: int, o: int = 0):
+        """Sort permutation of the first m rows of src_rows, computed in the work buffers at offset
+        `o`.  `keys`: the rows' 64-bit key prefixes (int64 bits) when the shuffle delivered them,
+        else None.  Fast path: a 32-bit window of the prefix (leading bits shared by the whole
+        partition are skipped) sorted as (u32, u32) pairs in 4 radix passes + tie repair on the
+        remaining key bytes read from the rows; a partition with long runs of equal windows (not
+        TeraSort-like) falls back to all 8 passes over the 64-bit prefix."""
         lib = N.kernels()
         b0, b1 = self._window(lo, hi)
-        k32 = self.keys_a.view(torch.int32)[:m]
+        k32a, k32b = self.keys_a.view(torch.int32), self.keys_b.view(torch.int32)
         if not self.descending:
+            k32 = k32a[o:o + m]
             if keys is None:
                 N.check(lib.dryad_extract_be_window(K.ptr(src_rows), m, self.width, self.key_off, b0, K.ptr(k32), K.stream()), "extract_be_window")
             else:
                 N.check(lib.dryad_shift_u64_to_u32(K.ptr(keys), m, b0, K.ptr(k32), K.stream()), "shift_u64_to_u32")
             K._count()
-            skeys, sidx = K.radix_sort_pairs(k32, self.idx_a[:m], iota=True, keys_alt=self.keys_b.view(torch.int32)[:m],
-                                             vals_alt=self.idx_b[:m])
+            skeys, sidx = K.radix_sort_pairs(k32, self.idx_a[o:o + m], iota=True, keys_alt=k32b[o:o + m],
+                                             vals_alt=self.idx_b[o:o + m])
             first_byte = (64 - b0) // 8               # key bytes before this are equal inside a run
-            runs = torch.zeros(1, dtype=torch.int32, device=src_rows.device)
+            runs = self._runs
+            runs.zero_()
             N.check(lib.dryad_fix_ties32(K.ptr(skeys), K.ptr(sidx), m, K.ptr(src_rows), self.width, self.key_off + first_byte,
                                          self.key_len - first_byte, self.WINDOW_MAX_RUN, 0, K.ptr(runs), K.stream()), "fix_ties32")
             K._count()
@@ -137,51 +182,117 @@ class RowSorter:
                 self.last_long_runs = runs
                 return sidx
         # general path (descending order, or long runs of equal windows): full 64-bit prefix
-        k64 = K.extract_be64(src_rows[:m], self.key_off, out=self.keys_a)[:m]
+        k64 = K.extract_be64(src_rows[:m], self.key_off, out=self.keys_a[o:o + m])
         if self.descending:
             k64 = ~k64
-        skeys, sidx = K.radix_sort_pairs(k64, self.idx_a[:m], iota=True, keys_alt=self.keys_b[:m], vals_alt=self.idx_b[:m])
+        skeys, sidx = K.radix_sort_pairs(k64, self.idx_a[o:o + m], iota=True, keys_alt=self.keys_b[o:o + m],
+                                         vals_alt=self.idx_b[o:o + m])
         if self.key_len > 8:
             self.last_long_runs = K.fix_ties(skeys, sidx, src_rows, self.key_off + 8, self.key_len - 8,
                                              descending=self.descending)
         return sidx
 
+    def _sort_keys(self, keys, m: int, lo: int, hi: int, o: int, flags: torch.Tensor):
+        """Sort permutation from the received key prefixes ALONE (32-bit window + key-only tie
+        repair), so it can run before the rows have arrived.  flags[0] / flags[1] count what the
+        keys cannot decide (long runs of equal windows / equal 64-bit prefixes under a wider key)."""
+        lib = N.kernels()
+        b0, _ = self._window(lo, hi)
+        k32 = self.keys_a.view(torch.int32)[o:o + m]
+        N.check(lib.dryad_shift_u64_to_u32(K.ptr(keys), m, b0, K.ptr(k32), K.stream()), "shift_u64_to_u32")
+        skeys, sidx = K.radix_sort_pairs(k32, self.idx_a[o:o + m], iota=True,
+                                         keys_alt=self.keys_b.view(torch.int32)[o:o + m], vals_alt=self.idx_b[o:o + m])
+        N.check(lib.dryad_fix_ties32_keys(K.ptr(skeys), K.ptr(sidx), m, K.ptr(keys), self.WINDOW_MAX_RUN,
+                                          1 if self.key_len > 8 else 0, flags.data_ptr(), flags.data_ptr() + 4, K.stream()),
+                "fix_ties32_keys")
+        K._count(2)
+        return sidx
+
     def sort(self, rows: torch.Tensor):
         """rows: [n, width] uint8 on this rank.  Returns (sorted_rows_view, m): this rank's slice
-        of the global order (rank r holds keys between separators r-1 and r)."""
+        of the global order (rank r holds keys between separators r*R-1 and (r+1)*R-1)."""
         n = rows.shape[0]
         if n > self.max_rows:
             raise ValueError("RowSorter: more rows than the sorter was sized for")
         M64 = (1 << 64) - 1
         self._mark("start")
-        if self.world > 1:
-            seps = self._separators(rows)
-            self._mark("sample+separators")
-            mode = "range_desc" if self.descending else "range_asc"
-            self.shuffle.run([rows], mode=mode, key_col=0, key_kind=1, key_off=self.key_off, separators=seps)
-            self._mark("shuffle")
-            sl = [x & M64 for x in seps.tolist()]              # host sync (tiny): this rank's key range
-            m = self.shuffle.received_rows()[0]               # host sync: sizes the local sort
-            self._mark("host sync")
-            src_rows = self.shuffle.recv[0][0]
-            keys = self.shuffle.recv_key[0][:m] if self.emit_key else None
-            r = self.rank
-            if self.descending:
-                lo = sl[r] if r < len(sl) else 0
-                hi = sl[r - 1] if r > 0 else M64
-                lo, hi = (~hi) & M64, (~lo) & M64              # keys are complemented before sorting
-            else:
-                lo = sl[r - 1] if r > 0 else 0
-                hi = sl[r] if r < len(sl) else M64
+        if self.world == 1:
+            sidx = self._local_sort(None, n, rows, 0, M64)
+            self._mark("local sort + ties")
+            out = self.out[:n]
+            K.gather_rows(rows, sidx, out)
+            self._mark("gather")
+            self._finish_marks()
+            return out, n
+
+        W, r, R = self.world, self.rank, self.R
+        sh = self.shuffle
+        main = torch.cuda.current_stream()
+        seps = self._separators(rows)
+        self._mark("sample+separators")
+        mode = "range_desc" if self.descending else "range_asc"
+        events = None
+        if self.split:
+            events = sh.run_passes(rows, mode=mode, key_off=self.key_off, separators=seps, side=self.side,
+                                   payload_ctas=self.payload_ctas)
+            self._mark("plan + key stream")
         else:
-            m = n
-            src_rows = rows
-            keys = None
-            lo, hi = 0, M64
-        sidx = self._local_sort(keys, m, src_rows, lo, hi)
-        self._mark("local sort + ties")
-        out = self.out[:m]
-        K.gather_rows(src_rows, sidx, out)
-        self._mark("gather")
+            sh.run([rows], mode=mode, key_col=0, key_kind=1, key_off=self.key_off, separators=seps)
+            self._mark("shuffle")
+        # ONE small read-back: status, rows received per (source, my sub-range), the separators
+        info = self._peek(torch.cat([sh.status.to(torch.int64), sh.counts[:, r * R:(r + 1) * R].reshape(-1), seps]))
+        st = int(info[0])
+        if st == 1:
+            raise N.NativeError("shuffle: a destination partition overflowed its receive buffer")
+        if st == 2:
+            raise N.NativeError("shuffle: peer did not signal within the timeout")
+        cnt = info[1:1 + W * R]
+        mj = [int(sum(cnt[s * R + j] for s in range(W))) for j in range(R)]
+        sl = [x & M64 for x in info[1 + W * R:]]
+        self._mark("host sync")
+        base = [0]
+        for j in range(R):
+            base.append(base[-1] + mj[j])
+        m = base[R]
+
+        def key_range(j: int):
+            p = r * R + j                               # my j-th partition in the global order
+            if self.descending:
+                lo = sl[p] if p < len(sl) else 0
+                hi = sl[p - 1] if p > 0 else M64
+                return (~hi) & M64, (~lo) & M64          # keys are complemented before sorting
+            return (sl[p - 1] if p > 0 else 0), (sl[p] if p < len(sl) else M64)
+
+        if events is not None:
+            # all key sorts first (they need the keys only), then each sub-range's gather as soon as
+            # its pass has landed
+            self._tie_flags.zero_()
+            perms = []
+            for j in range(R):
+                lo, hi = key_range(j)
+                perms.append(self._sort_keys(sh.recv_key[j][:mj[j]], mj[j], lo, hi, j * self.cap_part, self._tie_flags[j])
+                             if mj[j] else None)
+            self._mark("key sorts")
+            bad = self._peek(self._tie_flags.reshape(-1))
+            for j in range(R):
+                main.wait_event(events[j])
+                if not mj[j]:
+                    continue
+                src = sh.recv[0][j]
+                sidx = perms[j]
+                if bad[2 * j] or bad[2 * j + 1]:            # the keys alone could not decide: row-based path
+                    lo, hi = key_range(j)
+                    sidx = self._local_sort(sh.recv_key[j][:mj[j]], mj[j], src, lo, hi, j * self.cap_part)
+                K.gather_rows(src, sidx, self.out[base[j]:base[j + 1]])
+            self._mark("row passes + gathers")
+        else:
+            for j in range(R):
+                if not mj[j]:
+                    continue
+                lo, hi = key_range(j)
+                src = sh.recv[0][j]
+                sidx = self._local_sort(sh.recv_key[j][:mj[j]], mj[j], src, lo, hi, j * self.cap_part)
+                K.gather_rows(src, sidx, self.out[base[j]:base[j + 1]])
+            self._mark("local sorts + gathers")
         self._finish_marks()
-        return out, m
+        return self.out[:m], m

@@ -54,11 +54,13 @@ class KMeans:
         centroids in self.centroids (identical bits on every rank), assignments in self.assign."""
         n = points.shape[0]
         lib = N.kernels()
+        if self.world > 1:
+            # every rank has finished the previous iteration's update (which reads all peers'
+            # partials in the P2P form): only now may the partials be cleared
+            self.arena.barrier(slot=2)
         self.sums.zero_()
         self.counts.zero_()
         self.inertia.zero_()
-        if self.world > 1:
-            self.arena.barrier(slot=2)         # nobody is still reading last iteration's partials
         N.check(lib.dryad_kmeans_assign(K.ptr(points), n, K.ptr(self.centroids), K.ptr(self.cnorm), self.k,
                                         K.ptr(self.assign), K.ptr(self.sums), K.ptr(self.counts),
                                         K.ptr(self.inertia), max_ctas, K.stream()), "kmeans_assign")

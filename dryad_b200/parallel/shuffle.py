@@ -75,6 +75,7 @@ class FusedShuffle:
         self.capacity = torch.full((self.nparts,), self.cap_rows, dtype=torch.int64, device=dev)
         self.status = torch.zeros(1, dtype=torch.int32, device=dev)
         self._scratch = None
+        self._key_tmp = None
         if max_rows_in is not None:
             self._ensure_scratch(max_rows_in)
 
@@ -84,32 +85,30 @@ class FusedShuffle:
             self._scratch = torch.empty(need, dtype=torch.uint8, device=self.arena.device)
         return self._scratch
 
-    def run(self, srcs: Sequence[torch.Tensor], *, mode: str, key_col: int = 0, key_kind: int = 0,
-            key_off: int = 0, separators: Optional[torch.Tensor] = None) -> None:
-        """Launch the fused shuffle on the current stream.  No host synchronisation.  Afterwards
-        `self.counts[src_rank, part]` (device) holds the row counts and the receive buffers hold
-        the rows, ordered by source rank then source order."""
+    def _desc(self, srcs: Sequence[torch.Tensor], widths: Sequence[int], *, mode: str, key_col: int, key_kind: int,
+              key_off: int, separators: Optional[torch.Tensor], epoch: int, dst_table: torch.Tensor,
+              emit_key: bool) -> "N.ShuffleDesc":
         a = self.arena
         n = srcs[0].shape[0]
         K.require_cuda(*srcs)
         d = N.ShuffleDesc()
-        d.ncols = len(self.cols)
+        d.ncols = len(srcs)
         d.nparts = self.nparts
         d.mode = K.PART[mode]
         d.key_col, d.key_kind, d.key_off = key_col, key_kind, key_off
-        d.emit_key = 1 if self.emit_key else 0
+        d.emit_key = 1 if emit_key else 0
         d.rank, d.world = a.rank, a.world
         d.n = n
-        for c, (cs, t) in enumerate(zip(self.cols, srcs)):
+        for c, (w, t) in enumerate(zip(widths, srcs)):
             if t.shape[0] != n:
                 raise ValueError("shuffle columns must have equal row counts")
             row_bytes = t.element_size() * (t.shape[1] if t.dim() > 1 else 1)
-            if row_bytes != cs.width:
-                raise ValueError(f"column {c}: row width {row_bytes} != spec {cs.width}")
+            if row_bytes != w:
+                raise ValueError(f"column {c}: row width {row_bytes} != spec {w}")
             d.src[c] = t.data_ptr()
-            d.width[c] = cs.width
-        d.dst_table = self.dst_table.data_ptr()
-        d.dst_key_table = self.dst_key_table.data_ptr() if self.emit_key else None
+            d.width[c] = w
+        d.dst_table = dst_table.data_ptr()
+        d.dst_key_table = self.dst_key_table.data_ptr() if emit_key else None
         if mode.startswith("range"):
             if separators is None or separators.numel() != self.nparts - 1:
                 raise ValueError("range shuffle needs nparts-1 separators")
@@ -119,12 +118,74 @@ class FusedShuffle:
         d.counts_peers = self.counts_peers.data_ptr()
         d.flags_local = a.flags_local_ptr()
         d.flags_peers = a.flags_peers_table().data_ptr()
-        d.epoch = a.next_epoch()
+        d.epoch = epoch
         sc = self._ensure_scratch(n)
         d.scratch, d.scratch_bytes = sc.data_ptr(), sc.numel()
         d.status = self.status.data_ptr()
+        return d
+
+    def run(self, srcs: Sequence[torch.Tensor], *, mode: str, key_col: int = 0, key_kind: int = 0,
+            key_off: int = 0, separators: Optional[torch.Tensor] = None) -> None:
+        """Launch the fused shuffle on the current stream.  No host synchronisation.  Afterwards
+        `self.counts[src_rank, part]` (device) holds the row counts and the receive buffers hold
+        the rows, ordered by source rank then source order."""
+        d = self._desc(srcs, [cs.width for cs in self.cols], mode=mode, key_col=key_col, key_kind=key_kind,
+                       key_off=key_off, separators=separators, epoch=self.arena.next_epoch(),
+                       dst_table=self.dst_table, emit_key=self.emit_key)
         N.check(N.kernels().dryad_shuffle_run(C.byref(d), K.stream()), "shuffle_run")
         K._count(4)
+
+    def run_passes(self, rows: torch.Tensor, *, mode: str, key_off: int = 0,
+                   separators: Optional[torch.Tensor] = None, side: "torch.cuda.Stream" = None,
+                   payload_ctas: int = 0) -> list:
+        """Key stream first, then the wide rows one key sub-range per pass (single payload column,
+        emit_key=True buffers, range mode with parts_per_rank = R sub-ranges per destination).
+
+        Current stream: count + publish (the count pass also writes the rows' 64-bit key prefixes as
+        a compact column), then the 8-byte keys of ALL partitions are scattered into `recv_key` and
+        barrier slot 1 closes the key stream.  `side` stream: R passes of the TMA scatter over the
+        rows with the SAME offsets (slot i of recv_key[j] is row i of recv[0][j]); pass j moves only
+        the partitions of sub-range j and is closed by its own barrier (slot 4).  Returns one event
+        per pass: after event j every destination's sub-range-j buffer is complete, so the consumer
+        can sort keys while the link-bound row transfer runs and finish sub-range j while pass j+1
+        is still in flight.  Re-reading the rows R times is free where the link is the limit."""
+        if not self.emit_key or len(self.cols) != 1:
+            raise ValueError("run_passes needs one payload column and emit_key=True")
+        n = rows.shape[0]
+        a = self.arena
+        if self._key_tmp is None or self._key_tmp.numel() < max(n, 1):
+            self._key_tmp = torch.empty(max(n, 1), dtype=torch.int64, device=a.device)
+        epoch = a.next_epoch()
+        lib = N.kernels()
+        cur = torch.cuda.current_stream()
+        w = self.cols[0].width
+        d = self._desc([rows], [w], mode=mode, key_col=0, key_kind=1, key_off=key_off, separators=separators,
+                       epoch=epoch, dst_table=self.dst_table, emit_key=False)
+        d.key_out = self._key_tmp.data_ptr()
+        d.phases = N.SHUFFLE_PLAN
+        N.check(lib.dryad_shuffle_run(C.byref(d), K.stream()), "shuffle_plan")
+        planned = torch.cuda.Event()
+        planned.record(cur)
+        dk = self._desc([self._key_tmp[:n]], [8], mode=mode, key_col=0, key_kind=0, key_off=0, separators=separators,
+                        epoch=epoch, dst_table=self.dst_key_table, emit_key=False)
+        dk.phases = N.SHUFFLE_SCATTER | N.SHUFFLE_BARRIER
+        dk.barrier_slot = 1
+        N.check(lib.dryad_shuffle_run(C.byref(dk), K.stream()), "shuffle_keys")
+        side.wait_event(planned)
+        d.key_out = None
+        d.phases = N.SHUFFLE_SCATTER | N.SHUFFLE_BARRIER
+        d.barrier_slot = 4
+        d.max_ctas = int(payload_ctas)
+        events = []
+        for j in range(self.ppr):
+            d.filter_mod, d.filter_rem = (self.ppr, j) if self.ppr > 1 else (0, 0)
+            d.barrier_epoch = a.next_epoch()
+            N.check(lib.dryad_shuffle_run(C.byref(d), side.cuda_stream), "shuffle_payload")
+            ev = torch.cuda.Event()
+            ev.record(side)
+            events.append(ev)
+        K._count(4 + 2 * self.ppr)
+        return events
 
     def received_rows(self) -> List[int]:
         """Rows received per local partition (host sync)."""

@@ -19,7 +19,7 @@ extern "C" {
 #endif
 
 #define DRYAD_MAX_PEERS_C 8
-#define DRYAD_FLAG_SLOTS 4      /* flags buffer = uint64[DRYAD_FLAG_SLOTS][8] per rank */
+#define DRYAD_FLAG_SLOTS 8      /* flags buffer = uint64[DRYAD_FLAG_SLOTS][8] per rank */
 #define DRYAD_MAX_LANES 8
 #define DRYAD_EXPR_MAX_INSTR 64
 #define DRYAD_EXPR_MAX_COLS 16
@@ -114,7 +114,23 @@ typedef struct DryadShuffleDesc {
   uint64_t epoch;                  /* strictly increasing per shuffle on this flag set */
   void* scratch; size_t scratch_bytes;
   int32_t* status;                 /* device: 0 ok, 1 capacity overflow, 2 peer timeout */
+  /* Split execution (all optional; zero = the whole chain on one stream, barrier slot 1).
+   * A shuffle can run as PLAN once and then several SCATTER|BARRIER calls that reuse the plan's
+   * block offsets (same n, nparts, mode, separators, scratch and epoch) for different columns on
+   * different streams: the key stream first, the wide payload behind it, each with its own barrier
+   * slot.  Row i of every column lands in slot i of its destination buffer. */
+  uint64_t* key_out;               /* PLAN also writes each row's derived uint64 key here (n entries) */
+  int32_t phases;                  /* DRYAD_SHUFFLE_* bits */
+  int32_t barrier_slot;            /* flag slot of the closing barrier */
+  int32_t max_ctas;                /* cap on the scatter grid (persistent CTAs); 0 = one CTA per row block */
+  /* Passes: a SCATTER call with filter_mod > 0 moves only the partitions p with p % filter_mod ==
+   * filter_rem (the other rows are read and skipped).  With parts_per_rank = R key sub-ranges per
+   * destination, pass j fills every destination's sub-range-j buffer; give each pass's closing
+   * barrier its own barrier_epoch. */
+  int32_t filter_mod, filter_rem;
+  uint64_t barrier_epoch;          /* 0 = epoch */
 } DryadShuffleDesc;
+enum { DRYAD_SHUFFLE_PLAN = 1, DRYAD_SHUFFLE_SCATTER = 2, DRYAD_SHUFFLE_BARRIER = 4 };
 
 size_t dryad_shuffle_scratch_bytes(int64_t n, int nparts);
 int dryad_shuffle_run(const DryadShuffleDesc* desc, void* stream);
@@ -127,6 +143,10 @@ int dryad_sample_rows(const uint8_t* rows, int width, int key_off, int64_t n, ui
                       void* stream);
 int dryad_select_separators(const uint64_t* sorted, int64_t cnt, int pcount, int descending,
                             uint64_t* seps, void* stream);
+/* Same, the count stays on the device: cnt = sum_r min(counts[r], cap_each); `sorted` is the sorted
+ * concatenation of fixed-size sample slabs whose unused slots were pre-filled with ~0. */
+int dryad_select_separators_dev(const uint64_t* sorted, const int64_t* counts, int ncounts, int64_t cap_each,
+                                int pcount, int descending, uint64_t* seps, void* stream);
 
 /* ---- row helpers for OrderBy on wide records ----------------------------------------------- */
 int dryad_extract_be64(const uint8_t* rows, int64_t n, int width, int key_off, uint64_t* out,
@@ -142,6 +162,11 @@ int dryad_fix_ties32(const uint32_t* keys, uint32_t* idx, int64_t n, const uint8
                      int extra, int max_run, int descending, int32_t* long_runs, void* stream);
 int dryad_gather_rows(const void* in, const uint32_t* idx, void* out, int64_t n, int width,
                       void* stream);
+/* Key-only tie repair for the split (keys first) exchange: runs of equal 32-bit windows are ordered
+ * by keys64[idx] then idx; `unresolved` counts runs holding equal 64-bit prefixes when wide_key != 0
+ * (they need the rows' remaining key bytes: fall back to dryad_fix_ties32 once the payload is in). */
+int dryad_fix_ties32_keys(const uint32_t* keys, uint32_t* idx, int64_t n, const uint64_t* keys64, int max_run,
+                          int wide_key, int32_t* long_runs, int32_t* unresolved, void* stream);
 int dryad_check_sorted_rows(const uint8_t* rows, int64_t n, int width, int key_off, int key_len,
                             int descending, unsigned long long* result2, void* stream);
 

@@ -176,6 +176,17 @@ def gpu_checks(rank, world):
     dist.all_gather(allc, km.centroids)
     assert all(torch.equal(allc[0], c) for c in allc)
     assert int(km.total_counts.sum().item()) == 200_000 * world
+    # same with the peer-load all-reduce (no NVLS): partials may only be cleared after every rank
+    # has read them, so centroids stay bit-identical across ranks over several iterations
+    km2 = KMeans(arena, 256, 200_000, use_nvls=False)
+    km2.set_centroids(centres + 0.05)
+    for _ in range(6):
+        km2.iterate(pts)
+    torch.cuda.synchronize()
+    allc = [torch.zeros_like(km2.centroids) for _ in range(world)]
+    dist.all_gather(allc, km2.centroids)
+    assert all(torch.equal(allc[0], c) for c in allc), "P2P k-means all-reduce diverged across ranks"
+    assert int(km2.total_counts.sum().item()) == 200_000 * world
 
     # 3d. streamed channel between GPUs (NCCL p2p on a side stream, overlapped with the producer)
     from dryad_b200.channel.pipe import PipeReader, PipeWriter
