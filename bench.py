@@ -79,6 +79,7 @@ def main():
     ap.add_argument("--groupby-keys", type=int, default=1 << 20)
     ap.add_argument("--skip-e2e", action="store_true")
     ap.add_argument("--skip-groupby", action="store_true")
+    ap.add_argument("--skip-baseline", action="store_true", help="do not time the PyTorch+NCCL comparison arm")
     a = ap.parse_args()
 
     if a.impl == "reference":
@@ -173,13 +174,42 @@ def main():
     ok = int(g[:, 0].sum()) == 0 and int(g[:, 1].sum()) == world * n and \
         (int(g[:, 2].sum()) - int(g[:, 3].sum())) % (1 << 64) == 0
 
+    def timed(fn, steps, warmup):
+        """ms per call: device-timed with CUDA events, barrier + synchronize on both sides, max over ranks."""
+        for _ in range(warmup):
+            fn()
+        barrier()
+        t0, t1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        t0.record()
+        for _ in range(steps):
+            fn()
+        t1.record()
+        barrier()
+        return max_over_ranks(t0.elapsed_time(t1)) / steps
+
+    # ---- the comparison arm the bench line carries itself: PyTorch + NCCL (+cuBLAS) on the same box ---
+    # (dryad_b200/baseline/torch_nccl.py: all_to_all_single / torch.sort / unique / index_add_ /
+    # all_gather / all_reduce / matmul; it calls none of this repo's kernels)
+    from dryad_b200.baseline import torch_nccl as B
+    base = {"impl": "pytorch+nccl(+cublas), same process, same box, same data", "steps": None}
+    bsteps, bwarm = max(2, min(a.steps, 3)), 1
+    base["steps"], base["warmup"] = bsteps, bwarm
+    if not a.skip_baseline:
+        try:
+            del out
+            b_ms = timed(lambda: B.terasort_step(rows, world, rank), bsteps, bwarm)
+            base["terasort"] = {"ms_per_step": b_ms, "GB_per_s": world * n * W / (b_ms * 1e-3) / 1e9}
+        except Exception as ex:  # noqa: BLE001
+            base["terasort"] = {"error": f"{type(ex).__name__}: {ex}"}
+        torch.cuda.empty_cache()
+
     # ---- end to end through the public API -------------------------------------------------------
     e2e = None
     if not a.skip_e2e:
         try:
             host_rows = torch.empty((n, W), dtype=torch.uint8).pin_memory()
             host_rows.copy_(rows)
-            del sorter, arena, out
+            del sorter, arena
             torch.cuda.empty_cache()
             ctx = DryadLinqContext(world, platform="B200" if world > 1 else "LOCAL", device=f"cuda:{local_rank}")
 
@@ -209,8 +239,33 @@ def main():
             barrier()
             e_ms = max_over_ranks(s0.elapsed_time(s1)) / a.steps
             e2e = {"value": world * n * W / (e_ms * 1e-3) / 1e9, "unit": "GB/s", "ms_per_step": e_ms,
+                   "what": "load + sort: rows H2D from pinned memory, sorted rows stay in HBM, a 24-byte validation summary comes back",
                    "h2d_bytes_per_step": n * W, "d2h_bytes_per_step": 24, "cpus_bound": len(bound) if bound else 0, "box_h2d_GBps_per_gpu": round(h2d_rate, 1),
                    "violations": int(summ[0]), "rows_out_local": int(summ[2])}
+            # variant that also stores: the sorted rows are copied back to pinned host memory every step
+            host_out = torch.empty((int(n * 1.13) + 8192, W), dtype=torch.uint8).pin_memory()
+
+            def e2e_rows_back():
+                q = ctx.from_rows(host_rows, key_off=0, key_len=terasort.KEY_BYTES).order_by(RowKey(0, terasort.KEY_BYTES))
+                res = q.submit_and_wait()
+                r_ = terasort.result_rows(res)
+                host_out[:r_.shape[0]].copy_(r_, non_blocking=True)
+                torch.cuda.current_stream().synchronize()
+                return r_.shape[0]
+
+            rb_ms = timed(e2e_rows_back, max(2, a.steps // 2), 1)
+            e2e["rows_back"] = {"value": world * n * W / (rb_ms * 1e-3) / 1e9, "unit": "GB/s", "ms_per_step": rb_ms,
+                                "what": "load + sort + store: the sorted rows are also copied to pinned host memory",
+                                "h2d_bytes_per_step": n * W, "d2h_bytes_per_step": n * W}
+            if not a.skip_baseline:
+                def base_e2e():
+                    r_ = host_rows.to(dev, non_blocking=True)
+                    o_ = B.terasort_step(r_, world, rank)
+                    return o_[0, :8].cpu()                      # D2H: 8 bytes
+                be_ms = timed(base_e2e, bsteps, bwarm)
+                base["terasort_e2e"] = {"ms_per_step": be_ms, "GB_per_s": world * n * W / (be_ms * 1e-3) / 1e9,
+                                        "h2d_bytes_per_step": n * W, "d2h_bytes_per_step": 8}
+            del host_out
         except Exception as ex:  # noqa: BLE001
             e2e = {"error": f"{type(ex).__name__}: {ex}"}
 
@@ -219,10 +274,29 @@ def main():
     if not a.skip_groupby:
         try:
             from dryad_b200.models import groupby as gbm
+            # headline: general (sparse 64-bit) keys on the hashed table; the dense-id case, where the
+            # table is direct-addressed, is the second field
             groupby = gbm.bench(rank, world, dev, a.groupby_rows_per_gpu, a.groupby_keys, steps=a.steps,
-                                warmup=a.warmup, max_over_ranks=max_over_ranks, barrier=barrier)
+                                warmup=a.warmup, max_over_ranks=max_over_ranks, barrier=barrier, sparse=True)
+            torch.cuda.empty_cache()
+            groupby["dense_ids"] = gbm.bench(rank, world, dev, a.groupby_rows_per_gpu, a.groupby_keys, steps=a.steps,
+                                             warmup=a.warmup, max_over_ranks=max_over_ranks, barrier=barrier, sparse=False)
+            torch.cuda.empty_cache()
+            if not a.skip_baseline:
+                g_n = a.groupby_rows_per_gpu
+                gk_, gv_ = gbm.generate(g_n, a.groupby_keys, 11, dev, rank, sparse=True)
+                ms_ = timed(lambda: B.groupby_hashed_step(gk_, gv_, world), bsteps, bwarm)
+                base["groupby_sparse_keys"] = {"ms_per_step": ms_, "rows_per_s": world * g_n / (ms_ * 1e-3),
+                                               "how": "unique + index_add_ partials, all_to_all_single by key hash, unique + index_add_"}
+                del gk_, gv_
+                gk_, gv_ = gbm.generate(g_n, a.groupby_keys, 11, dev, rank, sparse=False)
+                ms_ = timed(lambda: B.groupby_step(gk_, gv_, a.groupby_keys, world), bsteps, bwarm)
+                base["groupby_dense_ids"] = {"ms_per_step": ms_, "rows_per_s": world * g_n / (ms_ * 1e-3),
+                                             "how": "index_add_ / bincount on the dense id + all_reduce"}
+                del gk_, gv_
+                torch.cuda.empty_cache()
         except Exception as ex:  # noqa: BLE001
-            groupby = {"error": f"{type(ex).__name__}: {ex}"}
+            groupby = {"error": f"{type(ex).__name__}: {ex}"} if groupby is None else dict(groupby, baseline_error=f"{type(ex).__name__}: {ex}")
         if not a.skip_e2e and isinstance(groupby, dict) and "error" not in groupby:
             try:
                 torch.cuda.empty_cache()
@@ -238,8 +312,18 @@ def main():
             from dryad_b200.models import joins
             extra["broadcast_join"] = joins.bench(rank, world, dev, 50_000_000, 1 << 20, steps=a.steps, warmup=a.warmup,
                                                   max_over_ranks=max_over_ranks, barrier=barrier)
+            if not a.skip_baseline:
+                torch.cuda.empty_cache()
+                fk_, fv_, dk_, da_, _ = joins.generate(50_000_000, 1 << 20, 13, dev, rank, world)
+                ms_ = timed(lambda: B.join_step(fk_, fv_, dk_, da_, 1 << 20, world), bsteps, bwarm)
+                base["broadcast_join"] = {"ms_per_step": ms_, "rows_per_s": world * 50_000_000 / (ms_ * 1e-3),
+                                          "how": "all_gather of the dimension table, dense table[key] gather, masked multiply, sum"}
+                del fk_, fv_, dk_, da_
+            extra["shuffle_hash_join"] = joins.bench_shuffle_join(rank, world, dev, 20_000_000, 4_000_000, steps=max(2, a.steps // 2),
+                                                                  warmup=1, max_over_ranks=max_over_ranks, barrier=barrier)
         except Exception as ex:  # noqa: BLE001
-            extra["broadcast_join"] = {"error": f"{type(ex).__name__}: {ex}"}
+            extra.setdefault("broadcast_join", {"error": f"{type(ex).__name__}: {ex}"})
+            extra.setdefault("shuffle_hash_join", {"error": f"{type(ex).__name__}: {ex}"})
         try:
             from dryad_b200.models import kmeans as KM
             from dryad_b200.parallel.kmeans import KMeans
@@ -263,13 +347,36 @@ def main():
                                "points_per_gpu": npts, "dims": 128, "k": kk, "points_per_s": world * npts / (kms * 1e-3),
                                "tf32_tflops_per_gpu": 2.0 * npts * kk * 128 / (kms * 1e-3) / 1e12,
                                "total_count_ok": int(km.total_counts.sum().item()) == world * npts}
+            if not a.skip_baseline:
+                c0 = centres + 0.05
+                ms_ = timed(lambda: B.kmeans_step(pts, c0, world), 2, 1)
+                base["kmeans"] = {"ms_per_iteration": ms_, "how": "cuBLAS TF32 matmul + argmin + index_add_ + all_reduce"}
+                ms_ = timed(lambda: B.gemm_tf32_only(pts, c0), 3, 1)
+                base["kmeans_gemm_only_cublas_tf32"] = {"ms": ms_, "tflops": 2.0 * npts * kk * 128 / (ms_ * 1e-3) / 1e12,
+                                                        "what": "the distance GEMM alone (8 M x 128 x 1024), no argmin, no sums, no all-reduce"}
         except Exception as ex:  # noqa: BLE001
             extra["kmeans"] = {"error": f"{type(ex).__name__}: {ex}"}
 
+    def ratio(x, y):
+        return (x / y) if (x and y) else None
+
+    vs = None
+    if not a.skip_baseline:
+        bt = base.get("terasort", {}).get("GB_per_s")
+        vs = ratio(gbs, bt)
+        base["ratios_ours_over_baseline"] = {
+            "terasort_kernel_path": vs,
+            "terasort_e2e": ratio((e2e or {}).get("value"), base.get("terasort_e2e", {}).get("GB_per_s")),
+            "groupby_sparse_keys": ratio((groupby or {}).get("value"), base.get("groupby_sparse_keys", {}).get("rows_per_s")),
+            "groupby_dense_ids": ratio(((groupby or {}).get("dense_ids") or {}).get("value"), base.get("groupby_dense_ids", {}).get("rows_per_s")),
+            "broadcast_join": ratio((extra.get("broadcast_join") or {}).get("value"), base.get("broadcast_join", {}).get("rows_per_s")),
+            "kmeans_iteration": ratio(base.get("kmeans", {}).get("ms_per_iteration"), ((extra.get("kmeans") or {}).get("value") or 0) * 1e3),
+        }
     if rank == 0:
         line = {
             "metric": METRIC, "value": gbs, "unit": "GB/s", "n_gpus": world, "steps": a.steps, "warmup": a.warmup,
-            "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": vs,
+            "vs_baseline_note": "the reference publishes no numbers (BASELINE.md); this is value / the PyTorch+NCCL implementation of the same sort timed in this run (BASELINE.json names it as the baseline)",
             "dtype": "exact (uint8 records, 80-bit keys); no reduced precision", "data": "synthetic",
             "impl": "ours", "valid": bool(ok),
             "config": {"model": "TeraSort-style RangePartition+OrderBy, 100-byte records, 10-byte keys",
@@ -277,6 +384,7 @@ def main():
                        "parallelism": f"dp{world} (range-partitioned, one partition per GPU)",
                        "l2_policy": f"inputs exceed L2 ({n * W / 1e9:.1f} GB per GPU vs 126 MB)"},
             "clocks": clocks, "gpu_launches": launches, "e2e": e2e, "groupby_agg": groupby, "extra": extra,
+            "baseline": None if a.skip_baseline else base,
         }
         print(json.dumps(line))
     if world > 1:

@@ -150,6 +150,81 @@ __global__ void __launch_bounds__(256) flag_count_kernel(const uint8_t* __restri
   }
 }
 
+// Exclusive scan of n int64 values (join match counts -> output offsets), three small kernels:
+// per-block scan (4096 values per block, in place) + block totals, single-block scan of the totals,
+// add-back.  total[0] receives the grand total.
+constexpr int SCAN_ITEMS = 4;
+__global__ void __launch_bounds__(1024) scan_i64_block_kernel(int64_t* __restrict__ x, int64_t n, int64_t* __restrict__ bsum) {
+  __shared__ int64_t s_warp[32];
+  const int64_t base = (int64_t)blockIdx.x * 1024 * SCAN_ITEMS + (int64_t)threadIdx.x * SCAN_ITEMS;
+  int64_t v[SCAN_ITEMS];
+  int64_t sum = 0;
+#pragma unroll
+  for (int k = 0; k < SCAN_ITEMS; ++k) { v[k] = (base + k < n) ? x[base + k] : 0; sum += v[k]; }
+  int64_t incl = sum;
+#pragma unroll
+  for (int o = 1; o < 32; o <<= 1) {
+    int64_t a = __shfl_up_sync(0xffffffffu, incl, o);
+    if (lane_id() >= (uint32_t)o) incl += a;
+  }
+  if (lane_id() == 31) s_warp[threadIdx.x >> 5] = incl;
+  __syncthreads();
+  if (threadIdx.x < 32) {
+    int64_t w = s_warp[threadIdx.x], wi = w;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      int64_t a = __shfl_up_sync(0xffffffffu, wi, o);
+      if (lane_id() >= (uint32_t)o) wi += a;
+    }
+    s_warp[threadIdx.x] = wi - w;
+    if (threadIdx.x == 31) bsum[blockIdx.x] = wi;
+  }
+  __syncthreads();
+  int64_t run = s_warp[threadIdx.x >> 5] + incl - sum;
+#pragma unroll
+  for (int k = 0; k < SCAN_ITEMS; ++k) { if (base + k < n) x[base + k] = run; run += v[k]; }
+}
+__global__ void __launch_bounds__(1024) scan_i64_totals_kernel(int64_t* __restrict__ bsum, int64_t nb, int64_t* __restrict__ total) {
+  __shared__ int64_t s_warp[32];
+  __shared__ int64_t s_carry;
+  if (threadIdx.x == 0) s_carry = 0;
+  __syncthreads();
+  for (int64_t base = 0; base < nb; base += 1024) {
+    const int64_t i = base + threadIdx.x;
+    const int64_t v = (i < nb) ? bsum[i] : 0;
+    int64_t incl = v;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      int64_t a = __shfl_up_sync(0xffffffffu, incl, o);
+      if (lane_id() >= (uint32_t)o) incl += a;
+    }
+    if (lane_id() == 31) s_warp[threadIdx.x >> 5] = incl;
+    __syncthreads();
+    if (threadIdx.x < 32) {
+      int64_t w = s_warp[threadIdx.x], wi = w;
+#pragma unroll
+      for (int o = 1; o < 32; o <<= 1) {
+        int64_t a = __shfl_up_sync(0xffffffffu, wi, o);
+        if (lane_id() >= (uint32_t)o) wi += a;
+      }
+      s_warp[threadIdx.x] = wi - w;
+    }
+    __syncthreads();
+    const int64_t carry = s_carry;
+    if (i < nb) bsum[i] = carry + s_warp[threadIdx.x >> 5] + incl - v;
+    __syncthreads();
+    if (threadIdx.x == 1023) s_carry = carry + s_warp[31] + incl;
+    __syncthreads();
+  }
+  if (threadIdx.x == 0) total[0] = s_carry;
+}
+__global__ void __launch_bounds__(1024) scan_i64_add_kernel(int64_t* __restrict__ x, int64_t n, const int64_t* __restrict__ boff) {
+  const int64_t base = (int64_t)blockIdx.x * 1024 * SCAN_ITEMS + (int64_t)threadIdx.x * SCAN_ITEMS;
+  const int64_t add = boff[blockIdx.x];
+#pragma unroll
+  for (int k = 0; k < SCAN_ITEMS; ++k) if (base + k < n) x[base + k] += add;
+}
+
 // Single-block exclusive scan of m uint32 values into int64 offsets (+ total at out[m]).
 __global__ void __launch_bounds__(1024) scan_u32_kernel(const uint32_t* __restrict__ in, int64_t m,
                                                         int64_t* __restrict__ out) {
@@ -422,6 +497,28 @@ int dryad_compact_flags(const uint8_t* flags, int64_t n, uint32_t* out_idx, int6
 int dryad_exclusive_scan_u32(const uint32_t* in, int64_t m, int64_t* out_m_plus_1, void* stream) {
   if (m < 0) return DRYAD_ERR_BAD_ARG;
   scan_u32_kernel<<<1, 1024, 0, (cudaStream_t)stream>>>(in, m, out_m_plus_1);
+  DRYAD_LAUNCH_CHECK();
+  return DRYAD_OK;
+}
+
+size_t dryad_scan_i64_scratch_bytes(int64_t n) {
+  int64_t nb = (n + 1024 * SCAN_ITEMS - 1) / (1024 * SCAN_ITEMS);
+  return (size_t)(nb < 1 ? 1 : nb) * 8 + 256;
+}
+
+// In place: x[i] <- sum of x[0..i); total_dev[0] <- sum of all.
+int dryad_exclusive_scan_i64(int64_t* x, int64_t n, int64_t* total_dev, void* scratch, size_t scratch_bytes, void* stream) {
+  if (n < 0) return DRYAD_ERR_BAD_ARG;
+  cudaStream_t st = (cudaStream_t)stream;
+  if (scratch_bytes < dryad_scan_i64_scratch_bytes(n)) return DRYAD_ERR_SCRATCH;
+  if (n == 0) { DRYAD_CUDA_TRY(cudaMemsetAsync(total_dev, 0, 8, st)); return DRYAD_OK; }
+  const int64_t nb = (n + 1024 * SCAN_ITEMS - 1) / (1024 * SCAN_ITEMS);
+  int64_t* bsum = (int64_t*)scratch;
+  scan_i64_block_kernel<<<(unsigned)nb, 1024, 0, st>>>(x, n, bsum);
+  DRYAD_LAUNCH_CHECK();
+  scan_i64_totals_kernel<<<1, 1024, 0, st>>>(bsum, nb, total_dev);
+  DRYAD_LAUNCH_CHECK();
+  scan_i64_add_kernel<<<(unsigned)nb, 1024, 0, st>>>(x, n, bsum);
   DRYAD_LAUNCH_CHECK();
   return DRYAD_OK;
 }

@@ -116,6 +116,8 @@ def _declare_kernels(lib):
     _sig(lib, "dryad_compact_scratch_bytes", c_size_t, [c_int64])
     _sig(lib, "dryad_compact_flags", c_int, [P, c_int64, P, P, P, c_size_t, P])
     _sig(lib, "dryad_exclusive_scan_u32", c_int, [P, c_int64, P, P])
+    _sig(lib, "dryad_scan_i64_scratch_bytes", c_size_t, [c_int64])
+    _sig(lib, "dryad_exclusive_scan_i64", c_int, [P, c_int64, P, P, c_size_t, P])
     _sig(lib, "dryad_reduce_scratch_bytes", c_size_t, [])
     _sig(lib, "dryad_reduce", c_int, [P, c_int, c_int64, c_int, P, P, c_size_t, P])
     _sig(lib, "dryad_tokenize_scratch_bytes", c_size_t, [c_int64])

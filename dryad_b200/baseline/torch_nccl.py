@@ -68,6 +68,37 @@ def groupby_step(keys: torch.Tensor, vals: torch.Tensor, nkeys: int, world: int)
     return s, c
 
 
+def groupby_hashed_step(keys: torch.Tensor, vals: torch.Tensor, world: int):
+    """The same GroupBy for general (sparse 64-bit) keys, the way a PyTorch + NCCL user writes it:
+    local partial aggregate (unique + index_add_/bincount), all_to_all of the partials by key hash,
+    final aggregate (unique + index_add_).  Returns (keys, sums, counts) of the groups this rank owns."""
+    uk, inv = torch.unique(keys, return_inverse=True)
+    s = torch.zeros(uk.numel(), dtype=torch.int64, device=keys.device).index_add_(0, inv, vals)
+    c = torch.bincount(inv, minlength=uk.numel())
+    if world == 1:
+        return uk, s, c
+    dest = ((uk * -7046029254386353131) >> 40) % world       # multiplicative hash of the key bits
+    part = _a2a_rows(torch.stack([uk, s, c], dim=1), dest, world)
+    fk, finv = torch.unique(part[:, 0], return_inverse=True)
+    fs = torch.zeros(fk.numel(), dtype=torch.int64, device=keys.device).index_add_(0, finv, part[:, 1])
+    fc = torch.zeros(fk.numel(), dtype=torch.int64, device=keys.device).index_add_(0, finv, part[:, 2])
+    return fk, fs, fc
+
+
+def gemm_tf32_only(points: torch.Tensor, centroids: torch.Tensor, chunk: int = 1 << 20):
+    """cuBLAS TF32 GEMM of the k-means distance shape and NOTHING else (no argmin, no sums): the
+    library's time for the tensor-core part of one iteration, in row chunks so the product fits."""
+    prev = torch.backends.cuda.matmul.allow_tf32
+    torch.backends.cuda.matmul.allow_tf32 = True
+    ct = centroids.t().contiguous()
+    out = torch.empty((min(chunk, points.shape[0]), centroids.shape[0]), dtype=torch.float32, device=points.device)
+    for i in range(0, points.shape[0], chunk):
+        blk = points[i:i + chunk]
+        torch.matmul(blk, ct, out=out[:blk.shape[0]])
+    torch.backends.cuda.matmul.allow_tf32 = prev
+    return out
+
+
 def join_step(fk, fv, dk, da, n_dim, world, threshold=500):
     """Broadcast join: all_gather the dimension table, filter, gather-by-key, multiply, sum."""
     if world > 1:

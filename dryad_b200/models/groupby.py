@@ -5,19 +5,52 @@ from __future__ import annotations
 import torch
 
 
-def generate(n: int, nkeys: int, seed: int, device, rank: int = 0):
+def generate(n: int, nkeys: int, seed: int, device, rank: int = 0, sparse: bool = False):
+    """(key, value) columns with `nkeys` distinct keys.  sparse=False: dense ids 0..nkeys-1 (dictionary
+    codes).  sparse=True: the ids pushed through the 64-bit mixer (a bijection), i.e. general 64-bit
+    keys spread over the whole range, which no dense array can index."""
     g = torch.Generator(device=device)
     g.manual_seed(seed * 7919 + rank)
     keys = torch.randint(0, nkeys, (n,), dtype=torch.int64, device=device, generator=g)
     vals = torch.randint(0, 1000, (n,), dtype=torch.int64, device=device, generator=g)
+    if sparse:
+        from ..ops import core as K
+        keys = K.hash_u64(keys)
     return keys, vals
 
 
-def bench(rank, world, dev, n, nkeys, steps, warmup, max_over_ranks, barrier):
+def validate_sample(rank, world, dev, keys, vals, gk, gl, nsample: int = 2048) -> bool:
+    """Per-key check on a sample: for `nsample` key values drawn from the data, the (sum, count) this
+    framework returned (each key lives on exactly one rank) equals a plain torch reduction over ALL
+    ranks' rows of that key.  Catches a wrong key -> owner mapping that totals alone would not."""
+    import torch.distributed as dist
+    sample = keys[:: max(1, keys.numel() // nsample)][:nsample].clone()
+    if world > 1:
+        dist.broadcast(sample, 0)
+    sample = torch.unique(sample)
+    ns = sample.numel()
+    sel = torch.isin(keys, sample)
+    pos = torch.searchsorted(sample, keys[sel])
+    want = torch.zeros((2, ns), dtype=torch.int64, device=dev)
+    want[0].index_add_(0, pos, vals[sel])
+    want[1].index_add_(0, pos, torch.ones_like(pos))
+    got = torch.zeros((3, ns), dtype=torch.int64, device=dev)
+    gsel = torch.isin(gk, sample)
+    gpos = torch.searchsorted(sample, gk[gsel])
+    got[0].index_add_(0, gpos, gl[0][gsel])
+    got[1].index_add_(0, gpos, gl[1][gsel])
+    got[2].index_add_(0, gpos, torch.ones_like(gpos))          # every sampled key on exactly ONE rank
+    if world > 1:
+        dist.all_reduce(want)
+        dist.all_reduce(got)
+    return bool(torch.equal(want, got[:2]) and bool((got[2] == 1).all()))
+
+
+def bench(rank, world, dev, n, nkeys, steps, warmup, max_over_ranks, barrier, sparse: bool = False):
     from ..ops import core as K
     from ..parallel.dagg import DistributedHashAggregate
     from ..parallel.symm import SymmetricArena
-    keys, vals = generate(n, nkeys, 11, dev, rank)
+    keys, vals = generate(n, nkeys, 11, dev, rank, sparse=sparse)
     # owner tables hold ~nkeys/world groups (1.25x for hash imbalance), the local partial table all nkeys
     fcap = K.agg_capacity(int(1.25 * nkeys) // world + 1024)
     arena = SymmetricArena(fcap * 8 * 3 + (fcap // 3 + 1024) * world * 24 + (16 << 20), rank, world, None, dev)
@@ -38,10 +71,13 @@ def bench(rank, world, dev, n, nkeys, steps, warmup, max_over_ranks, barrier):
     if world > 1:
         import torch.distributed as dist
         dist.all_reduce(tot)
-    ok = int(tot[0]) == world * n and int(tot[1]) == int(tot[2])
+    ok = int(tot[0]) == world * n and int(tot[1]) == int(tot[2]) and 0 < int(tot[3]) <= nkeys
+    ok = ok and validate_sample(rank, world, dev, keys, vals, gk, gl)
     return {"metric": "groupby_sum_count_rows_per_s", "value": world * n / (ms * 1e-3), "unit": "rows/s",
             "ms_per_step": ms, "rows_per_gpu": n, "distinct_keys": nkeys, "groups_out": int(tot[3]),
-            "valid": bool(ok), "gpu_launches": K.launch_count() - l0}
+            "keys": "sparse 64-bit (mix64 of ids): hashed table" if sparse else "dense ids: direct-addressed table",
+            "valid": bool(ok), "validation": "totals + per-key sum/count on a 2048-key sample against torch",
+            "gpu_launches": K.launch_count() - l0}
 
 
 def bench_api(rank, world, dev, n, nkeys, steps, warmup, max_over_ranks, barrier):

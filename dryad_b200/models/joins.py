@@ -69,3 +69,49 @@ def bench(rank, world, dev, n_fact, n_dim, steps, warmup, max_over_ranks, barrie
     return {"metric": "broadcast_join_fact_rows_per_s", "value": world * n_fact / (ms * 1e-3), "unit": "rows/s",
             "ms_per_step": ms, "fact_rows_per_gpu": n_fact, "dim_rows": n_dim, "matches_local": m, "valid": bool(ok), "fused_probe_pipeline": fused,
             "gpu_launches": K.launch_count() - l0}
+
+
+def bench_shuffle_join(rank, world, dev, n_fact, n_dim_per_gpu, steps, warmup, max_over_ranks, barrier):
+    """Hash join where NEITHER side fits a broadcast: fact (key, value) and a dimension table with
+    `n_dim_per_gpu` unique keys per GPU are both hash-partitioned to the key's owner with the fused
+    shuffle, joined there, and Select(v * attr) is reduced to a checksum."""
+    from ..ops import core as K
+    from ..parallel.djoin import ShuffleHashJoin
+    from ..parallel.symm import SymmetricArena
+    n_dim = n_dim_per_gpu * world
+    g = torch.Generator(device=dev)
+    g.manual_seed(977 + rank)
+    fk = K.hash_u64(torch.randint(0, n_dim, (n_fact,), dtype=torch.int64, device=dev, generator=g))   # sparse 64-bit keys
+    fv = torch.randint(0, 1000, (n_fact,), dtype=torch.int64, device=dev, generator=g)
+    ids = torch.arange(rank * n_dim_per_gpu, (rank + 1) * n_dim_per_gpu, dtype=torch.int64, device=dev)
+    dk = K.hash_u64(ids)
+    da = (ids * 2654435761) % 97
+    capl, capr = int(n_fact * 1.15) + 65536, int(n_dim_per_gpu * 1.15) + 65536
+    arena = SymmetricArena((capl + capr) * 16 + world * 8192 * 16 + (64 << 20), rank, world, None, dev)
+    shj = ShuffleHashJoin(arena, 2, 2, capl, capr, n_fact, n_dim_per_gpu)
+
+    def step():
+        lc, rc, rows, matched = shj.run_unique([fk, fv], [dk, da])
+        attr = K.gather_rows(rc[1], rows.clamp_(min=0))
+        return (lc[1] * attr * matched).sum(), matched.sum(dtype=torch.int64)
+
+    for _ in range(max(warmup, 1)):
+        s_, m_ = step()
+    barrier()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(steps):
+        s_, m_ = step()
+    e1.record()
+    barrier()
+    ms = max_over_ranks(e0.elapsed_time(e1)) / steps
+    # reference: attr is a function of the id, which the mixer (a bijection) hides from the join
+    idsf = torch.randint(0, n_dim, (n_fact,), dtype=torch.int64, device=dev, generator=torch.Generator(device=dev).manual_seed(977 + rank))
+    want = (fv * ((idsf * 2654435761) % 97)).sum()
+    tot = torch.stack([s_, m_, want])
+    if world > 1:
+        import torch.distributed as dist
+        dist.all_reduce(tot)
+    ok = int(tot[0]) == int(tot[2]) and int(tot[1]) == world * n_fact
+    return {"metric": "shuffle_hash_join_fact_rows_per_s", "value": world * n_fact / (ms * 1e-3), "unit": "rows/s",
+            "ms_per_step": ms, "fact_rows_per_gpu": n_fact, "dim_rows_per_gpu": n_dim_per_gpu, "valid": bool(ok)}

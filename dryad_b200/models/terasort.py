@@ -40,6 +40,16 @@ def validate_sorted(rows_cpu: torch.Tensor) -> bool:
     return all(x <= y for x, y in zip(keys, keys[1:]))
 
 
+def result_rows(result_query) -> torch.Tensor:
+    """The sorted rows this process holds after `order_by(...).submit_and_wait()` as ONE device
+    tensor [m, RECORD_BYTES] (the partitions of a row table are views of the sorter's output)."""
+    t = result_query.expr.params["table"]
+    parts = [p.cols["row"] for p in t.partitions if p is not None and len(p)]
+    if not parts:
+        return torch.empty((0, RECORD_BYTES), dtype=torch.uint8)
+    return parts[0] if len(parts) == 1 else torch.cat(parts)
+
+
 def validate(result_query) -> list:
     """TeraValidate-style summary of a sorted result held by this process: [order violations,
     wrapping key checksum, row count].  Reads 24 bytes back from the device."""

@@ -447,8 +447,8 @@ class JoinTable:
         N.check(lib.dryad_join_probe(ptr(self.keys), ptr(self.head), self.cap, ptr(self.next),
                                      ptr(probe_keys), n, 0, ptr(counts), None, None, stream()), "join_probe")
         _count()
-        offs = torch.cumsum(counts, 0) - counts  # tiny bookkeeping; the probe itself is ours
-        total = int((offs[-1] + counts[-1]).item()) if n else 0
+        offs, tot = exclusive_scan_i64(counts)                 # counts -> output offsets, in place
+        total = int(tot.item()) if n else 0
         op = torch.empty(total, dtype=torch.int32, device=dev)
         ob = torch.empty(total, dtype=torch.int32, device=dev)
         if total:
@@ -465,6 +465,18 @@ class JoinTable:
                                                probe_keys.numel(), ptr(out), stream()), "set_contains")
         _count()
         return out
+
+
+def exclusive_scan_i64(x: torch.Tensor):
+    """In-place exclusive prefix sum of an int64 column (K16); returns (x, total[1])."""
+    require_cuda(x)
+    n = x.numel()
+    lib = N.kernels()
+    total = torch.zeros(1, dtype=torch.int64, device=x.device)
+    sc = scratch(lib.dryad_scan_i64_scratch_bytes(n), x.device, "scan64")
+    N.check(lib.dryad_exclusive_scan_i64(ptr(x), n, ptr(total), ptr(sc), sc.numel(), stream()), "exclusive_scan_i64")
+    _count(3)
+    return x, total
 
 
 # ---- K12 -------------------------------------------------------------------------------------

@@ -125,8 +125,8 @@ class BroadcastJoin:
         counts = torch.empty(n, dtype=torch.int64, device=dev)
         N.check(lib.dryad_join_probe(K.ptr(self.keys), K.ptr(self.head), self.cap, K.ptr(self.next), K.ptr(probe_keys),
                                      n, 0, K.ptr(counts), None, None, K.stream()), "join_probe")
-        offs = torch.cumsum(counts, 0) - counts
-        total = int((offs[-1] + counts[-1]).item()) if n else 0
+        offs, tot = K.exclusive_scan_i64(counts)
+        total = int(tot.item()) if n else 0
         op = torch.empty(total, dtype=torch.int32, device=dev)
         ob = torch.empty(total, dtype=torch.int32, device=dev)
         if total:
@@ -145,6 +145,47 @@ class BroadcastJoin:
                                                     K.ptr(rows), K.ptr(matched), K.stream()), "join_probe_unique")
         K._count()
         return rows, matched
+
+
+class ShuffleHashJoin:
+    """Both sides hash-partitioned by key to their owner rank with the fused shuffle, then joined
+    locally (K1 + C1 + K8; reference: HashPartition x2 -> Merge -> HashJoin,
+    LinqToDryad/DryadLinqQueryGen.cs:1419-1610).  The two FusedShuffle objects (receive buffers,
+    pointer tables, scratch) live as long as this object and are reused by every `run`; the received
+    columns are handed out as views of the receive buffers, valid until the next `run`."""
+
+    def __init__(self, arena: SymmetricArena, ncols_left: int, ncols_right: int, cap_left: int, cap_right: int,
+                 max_left: int, max_right: int):
+        self.arena = arena
+        self.shl = FusedShuffle(arena, [ColSpec(8, torch.int64)] * ncols_left, cap_left, max_rows_in=max_left)
+        self.shr = FusedShuffle(arena, [ColSpec(8, torch.int64)] * ncols_right, cap_right, max_rows_in=max_right)
+
+    def exchange(self, left: Sequence[torch.Tensor], right: Sequence[torch.Tensor]):
+        self.shl.run(list(left), mode="hash", key_col=0)
+        self.shr.run(list(right), mode="hash", key_col=0)
+        ml, mr = self.shl.received_rows()[0], self.shr.received_rows()[0]
+        lc = [self.shl.recv[c][0][:ml] for c in range(len(left))]
+        rc = [self.shr.recv[c][0][:mr] for c in range(len(right))]
+        return lc, rc
+
+    def run(self, left: Sequence[torch.Tensor], right: Sequence[torch.Tensor]):
+        """Returns (left_cols_received, right_cols_received, left_idx, right_idx): all matching pairs."""
+        lc, rc = self.exchange(left, right)
+        jt = K.JoinTable(rc[0])
+        li, ri = jt.probe(lc[0])
+        return lc, rc, li, ri
+
+    def run_unique(self, left: Sequence[torch.Tensor], right: Sequence[torch.Tensor]):
+        """Right side with unique keys: (left_cols, right_cols, right_row int32 [ml], matched uint8 [ml])."""
+        lc, rc = self.exchange(left, right)
+        jt = K.JoinTable(rc[0])
+        ml = lc[0].numel()
+        rows = torch.empty(ml, dtype=torch.int32, device=lc[0].device)
+        matched = torch.empty(ml, dtype=torch.uint8, device=lc[0].device)
+        N.check(N.kernels().dryad_join_probe_unique(K.ptr(jt.keys), K.ptr(jt.head), jt.cap, K.ptr(lc[0]), ml,
+                                                    K.ptr(rows), K.ptr(matched), K.stream()), "join_probe_unique")
+        K._count()
+        return lc, rc, rows, matched
 
 
 def shuffle_hash_join(arena: SymmetricArena, left: Sequence[torch.Tensor], right: Sequence[torch.Tensor],

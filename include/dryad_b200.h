@@ -348,6 +348,10 @@ int dryad_compact_flags(const uint8_t* flags, int64_t n, uint32_t* out_idx, int6
                         void* scratch, size_t scratch_bytes, void* stream);
 /* K16: exclusive scan of m counts into m+1 int64 offsets (LinqToDryad/DryadLinqEnumerable.cs:1131). */
 int dryad_exclusive_scan_u32(const uint32_t* in, int64_t m, int64_t* out_m_plus_1, void* stream);
+/* K16: exclusive scan of n int64 values in place (join match counts -> output offsets, partition
+ * counts -> global indices; LinqToDryad/DryadLinqEnumerable.cs:1131 Offsets); total_dev[0] = sum. */
+size_t dryad_scan_i64_scratch_bytes(int64_t n);
+int dryad_exclusive_scan_i64(int64_t* x, int64_t n, int64_t* total_dev, void* scratch, size_t scratch_bytes, void* stream);
 
 /* ---- K11 scalar aggregates: LinqToDryad/DryadLinqVertex.cs:1673-4704 ------------------------ */
 enum { DRYAD_RED_SUM = 0, DRYAD_RED_MIN = 1, DRYAD_RED_MAX = 2 };

@@ -114,6 +114,24 @@ def gpu_checks(rank, world):
     ne = [b for b in bounds if b[2]]
     assert all(a[1] <= b[0] for a, b in zip(ne, ne[1:])), "partitions are not globally ordered"
 
+    # 2a. the same with the rows travelling in two key sub-range passes (filtered scatter passes into
+    #     per-sub-range receive buffers), and in descending order (one fused shuffle, no side stream)
+    for kw in ({"passes": 2}, {"descending": True}):
+        mark = arena.mark()
+        s2 = RowSorter(arena, nr, 100, key_len=10, **kw)
+        out2, m2 = s2.sort(rows)
+        desc = bool(kw.get("descending"))
+        r2 = K.check_sorted_rows(out2, 0, 10, descending=desc).cpu()
+        tt = torch.tensor([int(r2[0]), m2, int(r2[1]) & ((1 << 56) - 1), int(cs_in) & ((1 << 56) - 1)], dtype=torch.int64, device=dev)
+        dist.all_reduce(tt)
+        assert int(tt[0]) == 0 and int(tt[1]) == nr * world, (kw, tt)
+        assert (int(tt[2]) - int(tt[3])) % (1 << 56) == 0, kw
+        if not desc:
+            assert torch.equal(out2[:m2], out[:mm]), "two-pass sort differs from the one-pass sort"
+        torch.cuda.synchronize()
+        dist.barrier()
+        arena.release_to(mark)
+
     # 3. fused GroupBy reduce-scatter
     nk = 50_000
     gk = torch.randint(0, nk, (2_000_000,), dtype=torch.int64, device=dev, generator=g)

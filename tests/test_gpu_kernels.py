@@ -493,3 +493,40 @@ def test_packed_row_extract_and_update_round_trip(K):
     assert torch.equal(gl[0][order], torch.zeros(m, dtype=torch.int64, device=dev).index_add_(0, inv, vals))
     assert torch.equal(gl[1][order], torch.bincount(inv, minlength=m))
     assert torch.equal(gl[2][order], torch.full((m,), -(1 << 62), dtype=torch.int64, device=dev).scatter_reduce_(0, inv, vals, "amax"))
+
+
+@pytest.mark.parametrize("n", [0, 1, 4095, 4096, 4097, 1_000_003])
+def test_exclusive_scan_i64_matches_cumsum(K, n):
+    x = torch.randint(0, 1 << 40, (n,), dtype=torch.int64, device="cuda")
+    ref = torch.cumsum(x, 0) - x
+    want_total = int(x.sum().item())
+    got, total = K.exclusive_scan_i64(x.clone())
+    assert torch.equal(got, ref) and int(total.item()) == want_total
+
+
+def test_key_only_tie_repair_orders_equal_windows_by_full_prefix(K):
+    """dryad_fix_ties32_keys: runs of equal 32-bit windows are ordered by keys64[idx], then idx; equal
+    64-bit prefixes are reported as unresolved when the key is wider than the prefix."""
+    from dryad_b200 import _native as N
+    n = 200_000
+    g = torch.Generator(device="cuda").manual_seed(5)
+    hi = torch.randint(0, 50_000, (n,), dtype=torch.int64, device="cuda", generator=g)       # many equal windows
+    lo = torch.randint(0, 1 << 20, (n,), dtype=torch.int64, device="cuda", generator=g)
+    keys64 = (hi << 20) | lo
+    keys64[1000] = keys64[2000]                                                                # one exact 64-bit tie
+    k32 = (keys64 >> 20).to(torch.int32)
+    sk, sidx = K.radix_sort_pairs(k32.clone(), None, iota=True)
+    flags = torch.zeros(2, dtype=torch.int32, device="cuda")
+    N.check(N.kernels().dryad_fix_ties32_keys(K.ptr(sk), K.ptr(sidx), n, K.ptr(keys64), 64, 1, flags.data_ptr(),
+                                              flags.data_ptr() + 4, K.stream()), "fix_ties32_keys")
+    torch.cuda.synchronize()
+    ku = keys64.cpu().numpy()
+    order = np.lexsort((np.arange(n), ku))                  # by key, then index (stable)
+    assert int(flags[0]) == 0 and int(flags[1]) >= 1
+    assert np.array_equal(sidx.cpu().numpy().astype(np.int64), order)
+    # no wide key: the same tie is not an error
+    flags.zero_()
+    sk, sidx = K.radix_sort_pairs(k32.clone(), None, iota=True)
+    N.check(N.kernels().dryad_fix_ties32_keys(K.ptr(sk), K.ptr(sidx), n, K.ptr(keys64), 64, 0, flags.data_ptr(),
+                                              flags.data_ptr() + 4, K.stream()), "fix_ties32_keys")
+    assert flags.tolist() == [0, 0]
