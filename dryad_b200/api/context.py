@@ -357,6 +357,9 @@ class DryadLinqContext:
             arena = self._spmd_arena()
             if cur is not None:
                 arena.release_to(cur._arena_mark)
+                # everything allocated above the old sorter goes with it
+                for name in ("_exchange_cache", "_dagg_cache", "_bjoin_cache"):
+                    self.__dict__.pop(name, None)
             mark = arena.mark()
             cur = RowSorter(arena, max_rows, width, key_off=key_off, key_len=key_len, descending=descending)
             cur._arena_mark = mark

@@ -60,6 +60,7 @@ class RowSorter:
             self.emit_key = True
             self.shuffle = FusedShuffle(arena, [ColSpec(width, torch.uint8, width)], self.cap_part,
                                         parts_per_rank=self.R, emit_key=True, max_rows_in=max_rows)
+            self.regrown = 0
             self.side = torch.cuda.Stream(device=dev) if self.split else None
             self._peek_buf = torch.empty(1024, dtype=torch.int64).pin_memory()
             self._peek_ev = torch.cuda.Event()
@@ -83,17 +84,35 @@ class RowSorter:
             self.cap_part = self.cap_rows = self.max_rows
             self.shuffle = None
             self.split = False
-        n = self.cap_rows
-        self.keys_a = torch.empty(n, dtype=torch.int64, device=dev)
-        self.keys_b = torch.empty(n, dtype=torch.int64, device=dev)
-        self.idx_a = torch.empty(n, dtype=torch.int32, device=dev)
-        self.idx_b = torch.empty(n, dtype=torch.int32, device=dev)
-        self.out = torch.empty((n, width), dtype=torch.uint8, device=dev)
+        self._alloc_work()
         self._runs = torch.zeros(1, dtype=torch.int32, device=dev)
         self.last_long_runs: Optional[torch.Tensor] = None
         self.profile = False                  # diagnostic: record per-phase device times in self.timing
         self.timing: dict = {}
         self._marks: list = []
+
+    def _alloc_work(self) -> None:
+        n, dev = self.cap_rows, self.arena.device
+        self.keys_a = torch.empty(n, dtype=torch.int64, device=dev)
+        self.keys_b = torch.empty(n, dtype=torch.int64, device=dev)
+        self.idx_a = torch.empty(n, dtype=torch.int32, device=dev)
+        self.idx_b = torch.empty(n, dtype=torch.int32, device=dev)
+        self.out = torch.empty((n, self.width), dtype=torch.uint8, device=dev)
+
+    def _grow(self, need_rows: int) -> None:
+        """Skew: one key range received more rows than its buffer holds (duplicate-heavy keys put a
+        whole run of equal keys into ONE partition, whatever the separators).  The exact per-partition
+        totals are known to every rank before any row moves (the shuffle's published count matrix),
+        so all ranks take the same decision: re-create the receive side with room for the largest
+        partition and run the exchange again.  Reference: consumers sized from the measured data
+        (GraphManager/stagemanager/DrDynamicDistributor.h:25-124); file channels absorb any skew."""
+        self.cap_part = int(need_rows * 1.05) + 4096
+        self.cap_rows = self.cap_part * self.R
+        self.keys_a = self.keys_b = self.idx_a = self.idx_b = self.out = None
+        self.shuffle = FusedShuffle(self.arena, [ColSpec(self.width, torch.uint8, self.width)], self.cap_part,
+                                    parts_per_rank=self.R, emit_key=True, max_rows_in=self.max_rows)
+        self._alloc_work()
+        self.regrown += 1
 
     def _mark(self, name: str) -> None:
         if self.profile:
@@ -243,7 +262,16 @@ class RowSorter:
         info = self._peek(torch.cat([sh.status.to(torch.int64), sh.counts[:, r * R:(r + 1) * R].reshape(-1), seps]))
         st = int(info[0])
         if st == 1:
-            raise N.NativeError("shuffle: a destination partition overflowed its receive buffer")
+            # every rank sees the same count matrix, so every rank grows and re-runs together
+            if events is not None:
+                main.wait_event(events[-1])
+            need = int(sh.counts.sum(dim=0).max().item())
+            if need <= self.cap_part or self.regrown >= 4:
+                raise N.NativeError("shuffle: a destination partition overflowed its receive buffer")
+            sh.status.zero_()
+            self._marks = []
+            self._grow(need)
+            return self.sort(rows)
         if st == 2:
             raise N.NativeError("shuffle: peer did not signal within the timeout")
         cnt = info[1:1 + W * R]

@@ -197,7 +197,7 @@ def _key_column(src: ColumnBatch, lam) -> Optional[torch.Tensor]:
         out, _ = run_on_gpu({"k": ir}, src.cols, src.n)
         t = out["k"]
     if t.dtype == torch.float64:
-        return t.view(torch.int64)
+        return _canonical_zero(t.view(torch.int64))          # -0.0 == 0.0 as a key
     return t.to(torch.int64) if t.dtype != torch.int64 else t
 
 
@@ -244,34 +244,11 @@ def _group_by(be, node, part, inputs, env):
     src = be._cat(inputs[0])
     mode = p["mode"]
     n = src.n
-    if mode == "final_acc":
-        if "key" not in src.cols:
-            return NotImplemented
-        keys = src.cols["key"]
-        key_is_f = keys.dtype == torch.float64
-        kbits = keys.view(torch.int64) if key_is_f else keys
-        in_cols = [src.cols[f"agg{i}"] for i in range(len(lanes))]
-        combine = True
-    else:
-        if not isinstance(p["key"].ir, X.Expr):
-            return NotImplemented
-        key_is_f = p["key"].ir.kind == "f"
-        proj = {"__k": p["key"].ir}
-        for i, a in enumerate(dec.aggs):
-            if a.kind != "count":
-                sel = a.selector.ir if a.selector is not None else None
-                if not isinstance(sel, X.Expr):
-                    return NotImplemented
-                proj[f"__v{i}"] = sel
-        if n:
-            out, _ = run_on_gpu(proj, src.cols, n)
-        else:
-            out = {k: torch.empty(0, dtype=torch.int64, device=be.device) for k in proj}
-        kbits = out["__k"].view(torch.int64) if out["__k"].dtype == torch.float64 else out["__k"].to(torch.int64)
-        in_cols = [None if a.kind == "count" else out[f"__v{i}"] for i, a in enumerate(dec.aggs)]
-        combine = False
+    pre = _group_by_inputs(be, node, src)
+    if pre is NotImplemented:
+        return NotImplemented
+    kbits, in_views, key_is_f, combine = pre
     cap = max(1024, min(2 * n + 64, be.context.group_capacity_hint))
-    in_views = [None if c is None else (c.view(torch.int64) if c.dtype == torch.float64 else c.to(torch.int64)) for c in in_cols]
     # dense integer key range (ids, codes): direct-addressed table, one reduction request per row
     if n >= (1 << 16) and not combine and not key_is_f and len(lanes) < 8:
         lo, hi = K.minmax_i64(kbits.contiguous()).tolist()
@@ -304,11 +281,66 @@ def _group_by(be, node, part, inputs, env):
             raise
         except OverflowError as ex:
             raise DryadLinqException(ErrorCode.FailureInHashGroupBy, "Arithmetic operation resulted in an overflow.") from ex
+    return [_group_result_batch(dec, lanes, gk, gl, key_is_f)]
+
+
+def _group_result_batch(dec, lanes, gk, gl, key_is_f) -> ColumnBatch:
+    """(group keys, accumulator lanes) -> the partial-aggregate ColumnBatch layout (key, agg0, ...)."""
     cols: Dict[str, torch.Tensor] = {"key": gk.view(torch.float64) if key_is_f else gk}
     for i, a in enumerate(dec.aggs):
         lane = gl[i].contiguous()
         cols[f"agg{i}"] = lane.view(torch.float64) if lanes[i].endswith("f64") else lane
-    return [ColumnBatch(cols, gk.numel(), acc_lanes=len(dec.aggs))]
+    return ColumnBatch(cols, gk.numel(), acc_lanes=len(dec.aggs))
+
+
+def _group_by_inputs(be, node, src: ColumnBatch):
+    """Key bits and one int64-bits column per accumulator lane for a decomposable GroupBy vertex
+    (`mode` partial_acc / full_acc: from the source rows through the traced key and selector
+    expressions; final_acc: the (key, agg...) columns of partials).  NotImplemented when a lambda
+    did not trace."""
+    p = node.params
+    dec = p["decomp"]
+    lanes = dec.gpu_lanes()
+    n = src.n
+    if p["mode"] == "final_acc":
+        if "key" not in src.cols:
+            return NotImplemented
+        keys = src.cols["key"]
+        key_is_f = keys.dtype == torch.float64
+        kbits = keys.view(torch.int64) if key_is_f else keys
+        in_cols = [src.cols[f"agg{i}"] for i in range(len(lanes))]
+        combine = True
+    else:
+        if not isinstance(p["key"].ir, X.Expr):
+            return NotImplemented
+        key_is_f = p["key"].ir.kind == "f"
+        proj = {"__k": p["key"].ir}
+        for i, a in enumerate(dec.aggs):
+            if a.kind != "count":
+                sel = a.selector.ir if a.selector is not None else None
+                if not isinstance(sel, X.Expr):
+                    return NotImplemented
+                proj[f"__v{i}"] = sel
+        if n:
+            out, _ = run_on_gpu(proj, src.cols, n)
+        else:
+            out = {k: torch.empty(0, dtype=torch.int64, device=be.device) for k in proj}
+        kbits = out["__k"].view(torch.int64) if out["__k"].dtype == torch.float64 else out["__k"].to(torch.int64)
+        if key_is_f:
+            kbits = _canonical_zero(kbits)
+        in_cols = [None if a.kind == "count" else out[f"__v{i}"] for i, a in enumerate(dec.aggs)]
+        combine = False
+    in_views = [None if c is None else (c.view(torch.int64) if c.dtype == torch.float64 else c.to(torch.int64)) for c in in_cols]
+    return kbits, in_views, key_is_f, combine
+
+
+_NEG_ZERO_BITS = -0x8000000000000000
+
+
+def _canonical_zero(bits: torch.Tensor) -> torch.Tensor:
+    """Float keys are compared by bit pattern on the GPU; -0.0 and +0.0 are EQUAL keys, so the sign
+    of zero is cleared before the bits are used as a key."""
+    return torch.where(bits == _NEG_ZERO_BITS, torch.zeros_like(bits), bits)
 
 
 def _arena_for(be: GpuBackend, nbytes: int):
@@ -374,15 +406,34 @@ def _partition_exchange(be, src: ColumnBatch, names, cols, specs, mode: str, sep
     cap = total + 16                                   # skew-proof when it is affordable
     if cap * row_bytes > (2 << 30):
         cap = max(4096, 2 * total // ctx.world + 4096)   # else 2x the mean; overflow is reported, not silent
-    arena = ctx._spmd_arena()
-    mark = arena.mark()
+    # one FusedShuffle per column layout lives as long as the context (receive buffers, pointer
+    # tables and scratch are built once, not per vertex); it is replaced by a larger one on demand
+    cache = ctx.__dict__.setdefault("_exchange_cache", {})
+    sig = (tuple((sp.width, str(sp.dtype), sp.inner) for sp in specs), mode.startswith("range"))
+    sh = cache.get(sig)
+    if sh is None or sh.cap_rows < cap or sh._max_in < n_max:
+        arena = ctx._spmd_arena()
+        grow = 1 if sh is None else 2
+        sh = FusedShuffle(arena, specs, cap * grow, parts_per_rank=1, emit_key=False, max_rows_in=max(n_max * grow, 1))
+        sh._max_in = max(n_max * grow, 1)
+        cache[sig] = sh
+    sh.run(cols, mode=mode, key_col=0, key_kind=0, separators=seps)
     try:
-        sh = FusedShuffle(arena, specs, cap, parts_per_rank=1, emit_key=False, max_rows_in=max(n_max, 1))
+        m = sh.received_rows()[0]
+    except K.N.NativeError as ex:
+        if "overflow" not in str(ex):
+            raise
+        # skew: the published count matrix (identical on every rank) says how much the fullest owner
+        # receives; every rank re-creates the receive side with that room and runs the exchange again
+        need = int(sh.counts.sum(dim=0).max().item())
+        sh = FusedShuffle(ctx._spmd_arena(), specs, need + 16, parts_per_rank=1, emit_key=False, max_rows_in=sh._max_in)
+        sh._max_in = cache[sig]._max_in
+        cache[sig] = sh
         sh.run(cols, mode=mode, key_col=0, key_kind=0, separators=seps)
         m = sh.received_rows()[0]
-        d = {k: sh.recv[c + 1][0][:m].clone() for c, k in enumerate(names)}
-    finally:
-        arena.release_to(mark)
+        be.skew_regrows = getattr(be, "skew_regrows", 0) + 1
+    # the receive buffers are reused by the next exchange of this layout: hand out copies
+    d = {k: sh.recv[c + 1][0][:m].clone() for c, k in enumerate(names)}
     for k in names:
         if src.cols[k].dtype == torch.bool:
             d[k] = d[k].view(torch.bool) if d[k].dtype == torch.uint8 else d[k]
@@ -565,6 +616,10 @@ def _join(be, node, part, inputs, env):
         return NotImplemented
     ok, ik = _key_column(outer, p["outer_key"]), _key_column(inner, p["inner_key"])
     if ok is None or ik is None:
+        return NotImplemented
+    if p["outer_key"].ir.kind != p["inner_key"].ir.kind:
+        # keys are matched by bit pattern: a float key never equals an int key's bits, while the
+        # host path compares values (1.0 == 1); mixed kinds run there
         return NotImplemented
     if outer.n == 0 or inner.n == 0:
         proj = res if isinstance(res, dict) else {"value": res}

@@ -10,9 +10,15 @@ over the symmetric arena:
   1:N broadcast (side inputs)          small control-plane broadcast from rank 0
   OrderBy over byte rows               the whole sample → separators → range shuffle → sort subplan
                                        is executed by the fused `RowSorter` (parallel/dsort.py)
-(The decomposable GroupBy plan runs through these edges: its HashPartition stage is the fused
-shuffle; the single-kernel NVLink reduce-scatter form of the same plan is `parallel/dagg.py`,
-driven directly by models/groupby.py.)
+  decomposable GroupBy                 partial GroupBy → HashPartition → Merge → final GroupBy runs as
+                                       ONE DistributedHashAggregate (local table + NVLink reduce-scatter
+                                       into the key owners' tables, parallel/dagg.py)
+  Join(broadcast=True)                 to-one Merge → Tee → CrossProduct → Merge feeding the Join runs as
+                                       BroadcastJoin (NVLS / P2P replication fused with the build) and the
+                                       generated probe kernel (parallel/djoin.py)
+Columnar payloads never travel as pickled objects: the remaining 1:N / N:1 / all-to-all edges move
+tensors (padded all_gather / broadcast).  `object_collectives` counts the object exchanges a job
+needed (host records only).
 
 Reference roles: GraphBuilder.ConnectPointwise/ConnectCrossProduct (DryadLinqGraphManager/
 GraphBuilder.cs:420-504) and the GM run loop; the reference gets these edges from files + HTTP.
@@ -47,6 +53,8 @@ class SpmdExecutor(JobExecutor):
         self.arena = None                      # created lazily: host-backend SPMD needs no GPU arena
         self._skip: set = set()
         self._fused: Dict[int, Any] = {}
+        self.object_collectives = 0            # data-carrying *_object collectives (host records)
+        self.tensor_collectives = 0            # columnar edges moved as tensors
 
     # ---- pattern detection ---------------------------------------------------------------------
     def _find_row_sort_patterns(self):
@@ -75,6 +83,64 @@ class SpmdExecutor(JobExecutor):
             self._skip.update(x.uid for x in chain)
             self._skip.add(rp.uid)
 
+    def _find_groupby_patterns(self):
+        """[... | GroupBy(partial_acc) | HashPartition] ×→ [Merge | GroupBy(final_acc) | ...] with GPU
+        lanes: producer and consumer are executed as one DistributedHashAggregate
+        (reference plan: LinqToDryad/DryadLinqQueryGen.cs:2094-2183)."""
+        for c in self.plan.nodes:
+            cm = c.members if c.type == NodeType.Super else [c]
+            if len(cm) < 2 or cm[0].type != NodeType.Merge or cm[1].type != NodeType.GroupBy:
+                continue
+            if cm[1].params.get("mode") != "final_acc" or len(c.children) != 1 or c.children[0][1] != ConnOp.CrossProduct:
+                continue
+            n = c.children[0][0]
+            nm = n.members if n.type == NodeType.Super else [n]
+            if len(nm) < 2 or nm[-1].type != NodeType.HashPartition or nm[-2].type != NodeType.GroupBy:
+                continue
+            gb = nm[-2]
+            dec = gb.params.get("decomp")
+            if gb.params.get("mode") != "partial_acc" or dec is None or gb.params.get("elem") is not None:
+                continue
+            if dec.gpu_lanes() is None or gb.params.get("comparer") is not None:
+                continue
+            if n.partition_count != self.world or c.partition_count != self.world:
+                continue
+            if sum(1 for x in self.plan.nodes for ch, _ in x.children if ch is n) != 1:
+                continue                                   # the partials feed something else too
+            self._fused[n.uid] = ("gb_producer", nm[:-2], gb, c)
+            self._fused[c.uid] = ("gb_consumer", n, cm[1], cm[2:])
+
+    def _find_broadcast_join_patterns(self):
+        """Join(broadcast=True) whose inner side is Merge(world) ×← Tee ← Merge(1) ← X: X's local
+        partition goes straight into BroadcastJoin (LinqToDryad/DryadLinqQueryGen.cs:2957-3001)."""
+        for j in self.plan.nodes:
+            jm = j.members if j.type == NodeType.Super else [j]
+            jn = jm[0]
+            if jn.type != NodeType.Join or not jn.params.get("broadcast") or len(j.children) != 2:
+                continue
+            bc = j.children[1][0]
+            if bc.type != NodeType.Merge or not bc.children or bc.children[0][1] != ConnOp.CrossProduct:
+                continue
+            tee = bc.children[0][0]
+            if _tail(tee).type != NodeType.Tee or tee.partition_count != 1 or not tee.children:
+                continue
+            chain = [bc, tee]
+            one = tee if tee.type == NodeType.Super else None
+            src = tee.children[0][0]
+            if one is None:
+                if src.type != NodeType.Merge or src.partition_count != 1 or not src.children:
+                    continue
+                chain.append(src)
+                src = src.children[0][0]
+            elif _head(tee).type != NodeType.Merge:
+                continue
+            if src.partition_count != self.world:
+                continue
+            if any(sum(1 for x in self.plan.nodes for ch, _ in x.children if ch is y) != 1 for y in chain):
+                continue
+            self._fused[j.uid] = ("bjoin", src, jn, jm[1:])
+            self._skip.update(x.uid for x in chain)
+
     # ---- run -----------------------------------------------------------------------------------
     def run(self):
         ctx = self.context
@@ -82,6 +148,9 @@ class SpmdExecutor(JobExecutor):
             raise DryadLinqException(ErrorCode.Internal,
                                      "SPMD execution needs every stage to have 1 or world partitions")
         self._find_row_sort_patterns()
+        if getattr(self.backend, "name", "") == "gpu" and self.world > 1:
+            self._find_groupby_patterns()
+            self._find_broadcast_join_patterns()
         # GPU backend: distributor stages (HashPartition / RangePartition into `world` ports) run
         # the fused partition + all-to-all kernel over the symmetric arena instead of emitting ports
         if getattr(self.backend, "name", "") == "gpu":
@@ -113,6 +182,8 @@ class SpmdExecutor(JobExecutor):
                 self.out[node.uid][mine] = ports
                 rep.vertex_event(node, mine, 0, "completed", seconds=time.perf_counter() - t0)
         results = self._commit_local()
+        ctx.__dict__["last_object_collectives"] = self.object_collectives
+        ctx.__dict__["last_tensor_collectives"] = self.tensor_collectives
         self._flush_timeline()
         rep.job_stop(True, "", seconds=time.perf_counter() - t_job)
         return results
@@ -124,11 +195,58 @@ class SpmdExecutor(JobExecutor):
                 self._gather_to_zero(child)
 
     # ---- edges -----------------------------------------------------------------------------------
+    _DT = {"i": torch.int64, "f": torch.float64, "b": torch.bool}
+
+    def _all_columnar(self, payloads, schema) -> bool:
+        """Collective decision (one tiny all-reduce): every rank that holds a payload for this edge
+        holds it as a ColumnBatch with a known numeric schema.  A rank whose vertex fell back to host
+        records makes the whole edge take the object path, so no rank waits in the wrong collective."""
+        from .gpu_backend import _numeric_schema
+        ok = _numeric_schema(schema) and all(isinstance(p, ColumnBatch) and not p.is_rows and p.acc_lanes is None
+                                             for p in payloads if p is not None)
+        dev = self.backend.device if getattr(self.backend, "name", "") == "gpu" else torch.device("cpu")
+        flag = torch.tensor([1 if ok else 0], dtype=torch.int64, device=dev)
+        dist.all_reduce(flag, op=dist.ReduceOp.MIN)
+        return bool(int(flag.item()))
+
+    def _allgather_batches(self, mine: Optional[ColumnBatch], schema, tuple_like=False) -> List[ColumnBatch]:
+        """All-gather of one ColumnBatch per rank as tensors: sizes first, then every column padded
+        to the largest partition (one all_gather_into_tensor per column)."""
+        names = list(schema)
+        dev = self.backend.device if getattr(self.backend, "name", "") == "gpu" else torch.device("cpu")
+        n = mine.n if mine is not None else 0
+        sizes = torch.zeros(self.world, dtype=torch.int64, device=dev)
+        dist.all_gather_into_tensor(sizes, torch.tensor([n], dtype=torch.int64, device=dev))
+        sz = sizes.tolist()
+        cap = max(max(sz), 1)
+        cols: Dict[str, torch.Tensor] = {}
+        for k in names:
+            dt = self._DT[schema[k]]
+            wire = torch.uint8 if dt == torch.bool else dt
+            buf = torch.zeros(cap, dtype=wire, device=dev)
+            if n:
+                buf[:n] = mine.cols[k].to(dev).to(wire)
+            out = torch.empty(self.world * cap, dtype=wire, device=dev)
+            dist.all_gather_into_tensor(out, buf)
+            cols[k] = out
+        self.tensor_collectives += 1
+        res = []
+        for r in range(self.world):
+            d = {k: (cols[k][r * cap:r * cap + sz[r]].to(torch.bool) if self._DT[schema[k]] == torch.bool
+                     else cols[k][r * cap:r * cap + sz[r]]) for k in names}
+            res.append(ColumnBatch(d, sz[r], tuple_like))
+        return res
+
     def _gather_to_zero(self, child) -> Optional[List]:
         local = self.out[child.uid][self.rank]
-        payload = self.backend.to_records(local[0]) if local is not None else []
+        payload = local[0] if local is not None else None
+        if self._all_columnar([payload], child.schema):
+            parts = self._allgather_batches(payload, child.schema, getattr(payload, "tuple_like", False))
+            return parts if self.rank == 0 else None
+        recs = self.backend.to_records(payload) if payload is not None else []
         bucket: Optional[List] = [None] * self.world if self.rank == 0 else None
-        dist.gather_object(payload, bucket, dst=0)
+        dist.gather_object(recs, bucket, dst=0)
+        self.object_collectives += 1
         return bucket
 
     def _spmd_inputs(self, node, i) -> List[List]:
@@ -142,17 +260,33 @@ class SpmdExecutor(JobExecutor):
             w = head.params["window"]
             child = node.children[0][0]
             own = self.out[child.uid][self.rank][0]
+            if w > 1 and self._all_columnar([own], child.schema):
+                tail = own.slice(max(0, own.n - (w - 1)), own.n)
+                tails = self._allgather_batches(tail, child.schema, getattr(own, "tuple_like", False))
+                halo_parts: List[ColumnBatch] = []
+                have = 0
+                s = self.rank - 1
+                while s >= 0 and have < w - 1:
+                    seg = tails[s]
+                    take = min(seg.n, (w - 1) - have)
+                    if take:
+                        halo_parts.insert(0, seg.slice(seg.n - take, seg.n))
+                        have += take
+                    s -= 1
+                halo = ColumnBatch.concat(halo_parts) if halo_parts else own.slice(0, 0)
+                return [[own], [halo if self.rank > 0 else own.slice(0, 0)]]
             recs = self.backend.to_records(own)
-            tails: List = [None] * self.world
-            dist.all_gather_object(tails, list(recs[-(w - 1):]) if w > 1 else [])
-            halo: List = []
+            tails_o: List = [None] * self.world
+            dist.all_gather_object(tails_o, list(recs[-(w - 1):]) if w > 1 else [])
+            self.object_collectives += 1
+            halo_r: List = []
             s = self.rank - 1
-            while s >= 0 and len(halo) < w - 1:
-                seg = tails[s]
-                take = (w - 1) - len(halo)
-                halo = list(seg[-take:]) + halo if take > 0 and seg else halo
+            while s >= 0 and len(halo_r) < w - 1:
+                seg = tails_o[s]
+                take = (w - 1) - len(halo_r)
+                halo_r = list(seg[-take:]) + halo_r if take > 0 and seg else halo_r
                 s -= 1
-            return [[own], [halo if self.rank > 0 else []]]
+            return [[own], [halo_r if self.rank > 0 else []]]
         for child, op in node.children:
             cpc = child.partition_count
             if op == ConnOp.CrossProduct:
@@ -160,15 +294,29 @@ class SpmdExecutor(JobExecutor):
                 if ports is not None and len(ports) == 1 and getattr(ports[0], "_exchanged", False):
                     ins.append([ports[0]])                # the distributor already ran the fused all-to-all
                     continue
+                if cpc == 1 and _tail(child).type == NodeType.Tee and _tail(child).params.get("replicate") \
+                        and self._all_columnar(ports or [], child.schema):
+                    # replicated Tee ports are the same batch: broadcast it once as tensors
+                    got = self._allgather_batches(ports[0] if ports else None, child.schema,
+                                                  getattr(ports[0], "tuple_like", False) if ports else False)
+                    ins.append([got[0]])
+                    continue
                 recs = [self.backend.to_records(p) for p in ports] if ports is not None else None
                 everyone: List = [None] * self.world
                 dist.all_gather_object(everyone, recs)
+                self.object_collectives += 1
                 ins.append([everyone[s][i] for s in range(self.world) if everyone[s] is not None])
             elif cpc == node.partition_count:
                 ins.append([self.out[child.uid][i][0]])
             elif cpc == 1:                                    # 1:N broadcast from rank 0
-                box = [self.backend.to_records(self.out[child.uid][0][0]) if self.rank == 0 else None]
+                payload = self.out[child.uid][0][0] if self.rank == 0 else None
+                if self._all_columnar([payload], child.schema):
+                    got = self._allgather_batches(payload, child.schema, getattr(payload, "tuple_like", False))
+                    ins.append([got[0]])
+                    continue
+                box = [self.backend.to_records(payload) if self.rank == 0 else None]
                 dist.broadcast_object_list(box, src=0)
+                self.object_collectives += 1
                 ins.append([box[0]])
             elif node.partition_count == 1:                   # N:1 gather (only rank 0 gets here)
                 ins.append(self._gather_to_zero(child))
@@ -178,8 +326,17 @@ class SpmdExecutor(JobExecutor):
 
     # ---- fused stages ----------------------------------------------------------------------------
     def _run_fused(self, node):
+        kind = self._fused[node.uid][0]
+        if kind == "rowsort":
+            return self._run_rowsort(node)
+        if kind == "gb_producer":
+            return self._run_gb_producer(node)
+        if kind == "gb_consumer":
+            return self._run_gb_consumer(node)
+        return self._run_bjoin(node)
+
+    def _run_rowsort(self, node):
         kind, base, ob, rest = self._fused[node.uid]
-        from ..parallel.dsort import RowSorter
         batch: ColumnBatch = self.out[base.uid][self.rank][0]
         rows = batch.cols[ROW_COL]
         if rows.device.type != "cuda":
@@ -191,11 +348,184 @@ class SpmdExecutor(JobExecutor):
                                           bool(ob.params["descending"]))
         out, m = sorter.sort(rows.contiguous())
         res = ColumnBatch.rows(out[:m], rk.offset, rk.length)
-        ports = [res]
+        return self._run_rest([res], node, rest)
+
+    def _run_rest(self, ports, node, rest):
         env = VertexEnv(self.context, node.uid, self.rank, 0)
-        for mnode in rest:                                     # e.g. the OutputTable member
+        for mnode in rest:                                     # e.g. Select_FinalReduce, OutputTable
             ports = self.backend._run_one(mnode, self.rank, [[ports[0]]], env)
         return ports
+
+    # -- decomposable GroupBy as one DistributedHashAggregate ------------------------------------
+    def _run_gb_producer(self, node):
+        """Runs the members ahead of the partial GroupBy, then only PREPARES the aggregate inputs
+        (key bits + one column per lane).  All ranks agree (one all-reduce) whether the fused form
+        applies; if not, the GroupBy and HashPartition members run as planned."""
+        from . import gpu_backend as G
+        kind, prefix, gb, consumer = self._fused[node.uid]
+        be = self.backend
+        env = VertexEnv(self.context, node.uid, self.rank, 0)
+        cur = self._spmd_inputs(node, self.rank)
+        for mnode in prefix:
+            out = be._run_one(mnode, self.rank, cur, env)
+            cur = [[out[0]]]
+        pre = NotImplemented
+        if all(isinstance(p, ColumnBatch) and not p.is_rows for ps in cur for p in ps):
+            try:
+                pre = G._group_by_inputs(be, gb, be._cat(cur[0]))
+            except G.CompileError:
+                pre = NotImplemented
+        ok = pre is not NotImplemented and not G._has_reserved_key(pre[0])
+        flag = torch.tensor([1 if ok else 0], dtype=torch.int64, device=be.device)
+        dist.all_reduce(flag, op=dist.ReduceOp.MIN)
+        if int(flag.item()):
+            self._gb_ready = (node.uid, pre)
+            return [None]
+        # planned path: partial table, fused hash shuffle, final table
+        self._fused[consumer.uid] = ("plain",)
+        members = (node.members if node.type == NodeType.Super else [node])[len(prefix):]
+        for mnode in members:
+            out = be._run_one(mnode, self.rank, cur, env)
+            cur = [[out[0]]]
+        return out
+
+    def _dagg(self, lanes):
+        """One DistributedHashAggregate per lane signature for the life of the context (tables in
+        the symmetric arena, peer pointer tables built once)."""
+        from ..ops import core as K
+        from ..parallel.dagg import DistributedHashAggregate
+        ctx = self.context
+        cache = ctx.__dict__.setdefault("_dagg_cache", {})
+        hint = int(ctx.group_capacity_hint)
+        sig = (tuple(lanes), hint)
+        agg = cache.get(sig)
+        if agg is None:
+            fcap = K.agg_capacity(int(1.25 * hint) // self.world + 1024)
+            agg = DistributedHashAggregate(ctx._spmd_arena(), list(lanes), K.agg_capacity(hint), fcap)
+            cache[sig] = agg
+        return agg
+
+    def _run_gb_consumer(self, node):
+        from . import gpu_backend as G
+        info = self._fused[node.uid]
+        if info[0] == "plain":                                 # the producer took the planned path
+            ins = self._spmd_inputs(node, self.rank)
+            return self.backend.run_vertex(node, self.rank, ins, VertexEnv(self.context, node.uid, self.rank, 0))
+        kind, producer, gb, rest = info
+        uid, (kbits, in_views, key_is_f, _combine) = self._gb_ready
+        assert uid == producer.uid
+        dec = gb.params["decomp"]
+        lanes = dec.gpu_lanes()
+        try:
+            gk, gl = self._dagg(lanes).run(kbits.contiguous(), [None if c is None else c.contiguous() for c in in_views])
+        except OverflowError as ex:
+            raise DryadLinqException(ErrorCode.FailureInHashGroupBy, "Arithmetic operation resulted in an overflow.") from ex
+        self.backend.fused_aggregates = getattr(self.backend, "fused_aggregates", 0) + 1
+        batch = G._group_result_batch(dec, lanes, gk, gl, key_is_f)
+        return self._run_rest([batch], node, rest)
+
+    # -- broadcast join ---------------------------------------------------------------------------
+    def _run_bjoin(self, node):
+        """Join(broadcast=True): this rank's slice of the small side is replicated to every GPU and
+        built into each GPU's table by BroadcastJoin (NVLS multicast stores when the box has them,
+        else P2P stores); the outer side is probed where it is by the generated kernel."""
+        from . import gpu_backend as G
+        from ..expr import ir as X
+        from ..parallel.djoin import BroadcastJoin
+        kind, src, jn, rest = self._fused[node.uid]
+        be, ctx = self.backend, self.context
+        p = jn.params
+        env = VertexEnv(ctx, node.uid, self.rank, 0)
+        outer_ports = self.out[node.children[0][0].uid][self.rank]
+        outer = be._columnar(outer_ports[0], node.children[0][0].schema)
+        inner = be._columnar(self.out[src.uid][self.rank][0], src.schema)
+        res = p["result"].ir
+        ok = (isinstance(outer, ColumnBatch) and isinstance(inner, ColumnBatch) and not outer.is_rows and not inner.is_rows
+              and isinstance(res, (dict, X.Expr)) and p.get("comparer") is None
+              and isinstance(p["outer_key"].ir, X.Expr) and isinstance(p["inner_key"].ir, X.Expr)
+              and p["outer_key"].ir.kind == p["inner_key"].ir.kind
+              and all(v.dim() == 1 for v in inner.cols.values()))
+        okb = ikb = None
+        if ok:
+            okb, ikb = G._key_column(outer, p["outer_key"]), G._key_column(inner, p["inner_key"])
+            ok = okb is not None and ikb is not None and not G._has_reserved_key(okb, ikb)
+        dev = be.device
+        t = torch.tensor([1 if ok else 0, inner.n if ok else 0], dtype=torch.int64, device=dev)
+        sizes = torch.zeros(self.world * 2, dtype=torch.int64, device=dev)
+        dist.all_gather_into_tensor(sizes, t)
+        sz = sizes.view(self.world, 2).tolist()
+        if not all(f for f, _ in sz):
+            return self._bjoin_unfused(node, src, outer_ports)
+        total = sum(n for _, n in sz)
+        base = sum(n for _, n in sz[:self.rank])
+        names = list(inner.cols)
+        cache = ctx.__dict__.setdefault("_bjoin_cache", {})
+        sig = (len(names),)
+        bj = cache.get(sig)
+        if bj is None or bj.nrows < total:
+            bj = BroadcastJoin(ctx._spmd_arena(), max(total, 1024) if bj is None else 2 * total, len(names))
+            cache[sig] = bj
+        nrows_saved, bj.nrows = bj.nrows, total               # build over the rows actually present
+        batch = None
+        try:
+            if total == 0:
+                raise G.CompileError("empty broadcast side")
+            wire = [(v.view(torch.int64) if v.dtype == torch.float64 else v.to(torch.int64)).contiguous() for v in inner.cols.values()]
+            bj.build(ikb.contiguous(), wire, base)
+            uniq = bool(int((bj.next[:total] >= 0).sum().item()) == 0) if total else True
+            if not uniq:
+                raise G.CompileError("duplicate keys on the broadcast side")
+            proj = res if isinstance(res, dict) else {"value": res}
+            hit = X.probe_slot("jt", X.col("__okey"))
+            sub, arrays = {}, {}
+            for k, v, wcol in zip(names, inner.cols.values(), bj.cols):
+                kind_k = "f" if v.dtype == torch.float64 else ("b" if v.dtype == torch.bool else "i")
+                g = X.gather("i." + k, hit, "f" if kind_k == "f" else "i")
+                sub["i." + k] = X.cast(g, "b") if kind_k == "b" else g
+                col = wcol[:max(total, 1)]
+                arrays["i." + k] = col.view(torch.float64) if kind_k == "f" else col
+            outs = {}
+            for name, e in proj.items():
+                e = X.wrap(e)
+                used = {c for c in e.columns() if c.startswith("i.")}
+                outs[name] = e.substitute({c: sub[c] for c in used})
+            cols = {("o." + k): v for k, v in outer.cols.items()}
+            cols["__okey"] = okb.contiguous()
+            need = {a for e in outs.values() for a in arrays if G._mentions_array(e, a)}
+            if outer.n:
+                out, flags = G.run_on_gpu(outs, cols, outer.n, predicate=hit >= 0, tables={"jt": bj},
+                                          arrays={a: bj.slot_payload(arrays[a].contiguous()) for a in need})
+                idx, m = G.K.compact_flags(flags)
+                batch = ColumnBatch(out, outer.n, tuple_like=G._tuple_cls(res)).take(idx)
+            else:
+                batch = ColumnBatch({k: torch.empty(0, dtype=self._DT[X.wrap(e).kind], device=dev) for k, e in proj.items()}, 0,
+                                    tuple_like=G._tuple_cls(res))
+        except (G.CompileError, X.TraceError):
+            batch = None
+        bj.nrows = nrows_saved
+        # every rank must take the same path from here on (the unfused form is a collective)
+        done = torch.tensor([0 if batch is None else 1], dtype=torch.int64, device=dev)
+        dist.all_reduce(done, op=dist.ReduceOp.MIN)
+        if not int(done.item()):
+            return self._bjoin_unfused(node, src, outer_ports)
+        be.fused_broadcast_joins = getattr(be, "fused_broadcast_joins", 0) + 1
+        return self._run_rest([batch], node, rest)
+
+    def _bjoin_unfused(self, node, src, outer_ports):
+        """The planned form without pickles: the small side is all-gathered as tensors and the Join
+        vertex runs on (outer partition, full small side)."""
+        payload = self.out[src.uid][self.rank][0]
+        if self._all_columnar([payload], src.schema):
+            parts = self._allgather_batches(payload, src.schema, getattr(payload, "tuple_like", False))
+            inner_all = [ColumnBatch.concat(parts)]
+        else:
+            recs = self.backend.to_records(payload)
+            everyone: List = [None] * self.world
+            dist.all_gather_object(everyone, recs)
+            self.object_collectives += 1
+            inner_all = [sum(everyone, [])]
+        env = VertexEnv(self.context, node.uid, self.rank, 0)
+        return self.backend.run_vertex(node, self.rank, [[outer_ports[0]], inner_all], env)
 
     def _commit_local(self):
         results = {}
