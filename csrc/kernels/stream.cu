@@ -416,6 +416,46 @@ __global__ void __launch_bounds__(256) tok_write_kernel(const unsigned char* __r
   }
 }
 
+// ---- variable-length (string) columns ---------------------------------------------------------
+// A string column inside the engine is a set of VIEWS into a byte buffer: (start, length) per row
+// (reference: strings on the wire are length-prefixed UTF-8, LinqToDryad/DryadLinqBinaryWriter.cs:
+// 523-546; LineRecord, LinqToDryad/LineRecord.cs:30-176).  Keys are the 64-bit hash of the bytes —
+// FNV-1a then the 64-bit mixer, the same function the tokenizer and hash_bytes use — and every use
+// of a hash as a key is followed by a byte-for-byte check against the group's representative.
+__global__ void hash_views_kernel(const unsigned char* __restrict__ buf, const int64_t* __restrict__ starts,
+                                  const int32_t* __restrict__ lens, int64_t n, uint64_t* __restrict__ out) {
+  int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+  for (; i < n; i += stride) {
+    const unsigned char* p = buf + starts[i];
+    const int32_t l = lens[i];
+    uint64_t h = 0xcbf29ce484222325ULL;
+    for (int32_t j = 0; j < l; ++j) { h ^= p[j]; h *= 0x100000001b3ULL; }
+    out[i] = mix64(h);
+  }
+}
+
+// Strings -> fixed-width slots (zero padded) so they can ride the fixed-width fused shuffle:
+// out[i*W .. i*W+W) = bytes of string i.  W is a multiple of 4; lens[i] <= W is the caller's check.
+__global__ void str_pack_kernel(const unsigned char* __restrict__ buf, const int64_t* __restrict__ starts,
+                                const int32_t* __restrict__ lens, int64_t n, int W, unsigned char* __restrict__ out) {
+  const int words = W >> 2;
+  int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+  for (; t < n * words; t += stride) {
+    const int64_t i = t / words;
+    const int w = (int)(t - i * words);
+    const unsigned char* p = buf + starts[i] + 4 * w;
+    const int rem = lens[i] - 4 * w;
+    uint32_t v = 0;
+    if (rem > 0) v |= (uint32_t)p[0];
+    if (rem > 1) v |= (uint32_t)p[1] << 8;
+    if (rem > 2) v |= (uint32_t)p[2] << 16;
+    if (rem > 3) v |= (uint32_t)p[3] << 24;
+    reinterpret_cast<uint32_t*>(out)[t] = v;
+  }
+}
+
 // Verify that every token equals the representative token of its group (hash-collision check).
 __global__ void tok_verify_kernel(const unsigned char* __restrict__ text,
                                   const int64_t* __restrict__ starts, const int32_t* __restrict__ lens,
@@ -571,6 +611,21 @@ int dryad_tokenize_write(const uint8_t* text, int64_t n, int delim, int keep_emp
   int64_t blocks = (n + CTILE - 1) / CTILE;
   int64_t* bo = (int64_t*)((char*)scratch + ((blocks * 4 + 255) & ~255ll));
   tok_write_kernel<<<(unsigned)blocks, 256, 0, (cudaStream_t)stream>>>(text, n, (unsigned char)delim, keep_empty, bo, starts, lens, hashes);
+  DRYAD_LAUNCH_CHECK();
+  return DRYAD_OK;
+}
+
+int dryad_hash_views(const uint8_t* buf, const int64_t* starts, const int32_t* lens, int64_t n, uint64_t* out, void* stream) {
+  if (n <= 0) return DRYAD_OK;
+  hash_views_kernel<<<grid_for(n), 256, 0, (cudaStream_t)stream>>>(buf, starts, lens, n, out);
+  DRYAD_LAUNCH_CHECK();
+  return DRYAD_OK;
+}
+
+int dryad_str_pack(const uint8_t* buf, const int64_t* starts, const int32_t* lens, int64_t n, int width, uint8_t* out, void* stream) {
+  if (width <= 0 || (width & 3)) return DRYAD_ERR_BAD_ARG;
+  if (n <= 0) return DRYAD_OK;
+  str_pack_kernel<<<grid_for(n * (width >> 2)), 256, 0, (cudaStream_t)stream>>>(buf, starts, lens, n, width, out);
   DRYAD_LAUNCH_CHECK();
   return DRYAD_OK;
 }

@@ -123,6 +123,8 @@ def _declare_kernels(lib):
     _sig(lib, "dryad_tokenize_scratch_bytes", c_size_t, [c_int64])
     _sig(lib, "dryad_tokenize_count", c_int, [P, c_int64, c_int, c_int, P, P, c_size_t, P])
     _sig(lib, "dryad_tokenize_write", c_int, [P, c_int64, c_int, c_int, P, P, P, P, c_size_t, P])
+    _sig(lib, "dryad_hash_views", c_int, [P, P, P, c_int64, P, P])
+    _sig(lib, "dryad_str_pack", c_int, [P, P, P, c_int64, c_int, P, P])
     _sig(lib, "dryad_tokenize_verify", c_int, [P, P, P, P, P, c_int64, P, P])
     _sig(lib, "dryad_replicate_slice", c_int, [c_int, c_int, P, P, c_int64, c_int64, P])
     _sig(lib, "dryad_join_table_init", c_int, [P, P, c_uint64, P])

@@ -261,8 +261,28 @@ class DryadLinqContext:
         not distinct whatever they were when written (DryadLinqQuery.cs:547-551)."""
         self._check_not_disposed()
         from ..channel import store
-        t = store.open_table(uri)
-        return self._from_table(Table(t.partitions, t.schema, None, uri, False), uri)
+        t = store.open_table(uri, text_partitions=self.world if self.world > 1 else 1)
+        parts = t.partitions
+        if self.world > 1 and len(parts) == self.world and parts and isinstance(parts[0], store.TextPartition):
+            parts = [p if i == self.rank else None for i, p in enumerate(parts)]   # SPMD: every rank keeps its own byte range
+        return self._from_table(Table(parts, t.schema, None, uri, False), uri)
+
+    def from_text(self, text) -> Query:
+        """Text ingress without a file: `text` is bytes or a 1-D uint8 tensor (host, pinned or already
+        in HBM) holding '\\n'-separated lines; the result is a table of LineRecords (schema
+        {"value": "s"}).  SPMD: `text` is THIS rank's byte range (whole lines)."""
+        self._check_not_disposed()
+        from ..channel.store import TextPartition
+        import torch
+        if isinstance(text, torch.Tensor):
+            part = TextPartition(b"", device_buf=text.contiguous().view(torch.uint8))
+        else:
+            part = TextPartition(bytes(text))
+        parts: List[Any] = [part]
+        if self.world > 1:
+            parts = [None] * self.world
+            parts[self.rank] = part
+        return self._from_table(Table(parts, {"value": "s"}, None, None, True))
 
     def from_columns(self, columns: Dict[str, Any], num_partitions: Optional[int] = None) -> Query:
         """Columnar ingress: dict name -> 1-D numpy array / torch tensor (equal lengths)."""
@@ -295,7 +315,9 @@ class DryadLinqContext:
         rows = None
         if table.partitions is not None:
             try:
-                rows = sum(len(p) for p in table.partitions if p is not None)
+                # text partitions are raw bytes: estimate instead of splitting them into lines here
+                rows = sum((max(len(p.data), 0 if p.device_buf is None else int(p.device_buf.numel())) // 32 + 1) if hasattr(p, "data") else len(p)
+                           for p in table.partitions if p is not None)
             except TypeError:
                 rows = None
         e = QExpr("source", [], table.schema, table=table, partition_count=pc, uri=uri,

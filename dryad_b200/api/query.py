@@ -99,7 +99,14 @@ class Query:
     long_where = where_indexed
 
     def select_many(self, fn, result: Optional[Callable] = None) -> "Query":
-        return self._new("select_many", schema=None, fn=Lam(fn, None, 1),
+        # `l => l.Split(' ')` over a string column traces to a `split` expression: the GPU backend runs
+        # it as the tokenizer kernel and the result is again a string column
+        ir, schema = None, None
+        if result is None and self.schema is not None and all(k != "o" for k in self.schema.values()):
+            t = X.trace(fn, self.schema)
+            if isinstance(t, X.Expr) and t.op == "split":
+                ir, schema = t, {"value": "s"}
+        return self._new("select_many", schema=schema, fn=Lam(fn, ir, 1),
                          result=Lam(result, None, 2) if result else None, indexed=False)
 
     def select_many_indexed(self, fn, result: Optional[Callable] = None) -> "Query":

@@ -149,15 +149,59 @@ def read_partition_file(p: str) -> List:
     return out
 
 
-def open_table(uri: str) -> StoredTable:
+class TextPartition:
+    """The lines of (a byte range of) a text file, kept as raw bytes.  The GPU backend uploads the
+    bytes as they are (the string column is views into them); LineRecords are only materialised when
+    host code iterates (host backend, LocalDebug, enumeration).
+    Reference: LinqToDryad/DryadLinqTextReader.cs:36-280."""
+
+    def __init__(self, data, device_buf=None):
+        self.data = data                     # bytes (host copy; b"" when only the device copy exists)
+        self.device_buf = device_buf         # optional uint8 tensor already holding the same bytes
+        self._lines: Optional[List[LineRecord]] = None
+
+    def to_records(self) -> List[LineRecord]:
+        if self._lines is None:
+            from ..oracle.text import split_lines
+            data = self.data if (self.data or self.device_buf is None) else bytes(self.device_buf.cpu().numpy())
+            self._lines = [LineRecord(l.decode("utf-8")) for l in split_lines(data)]
+        return self._lines
+
+    def __len__(self):
+        return len(self.to_records())
+
+    def __iter__(self):
+        return iter(self.to_records())
+
+    def __getitem__(self, i):
+        return self.to_records()[i]
+
+
+def split_text(data: bytes, n: int) -> List[bytes]:
+    """Cut text into n byte ranges of about equal size, each ending at a line boundary."""
+    if n <= 1:
+        return [data]
+    out, pos, total = [], 0, len(data)
+    for i in range(n):
+        if i == n - 1:
+            out.append(data[pos:])
+            break
+        end = max(pos, min(total, (total * (i + 1)) // n))
+        nl = data.find(b"\n", end)
+        end = total if nl < 0 else nl + 1
+        out.append(data[pos:end])
+        pos = end
+    return out
+
+
+def open_table(uri: str, text_partitions: int = 1) -> StoredTable:
     scheme, path = parse_uri(uri)
     if not os.path.exists(path):
         raise DryadLinqException(ErrorCode.StreamDoesNotExist, f"{uri} does not exist")
     if scheme == "file" or not path.endswith(".pt"):
         with open(path, "rb") as f:                       # plain text: one LineRecord per line
-            from ..oracle.text import split_lines
-            lines = [LineRecord(l.decode("utf-8")) for l in split_lines(f.read())]
-        return StoredTable([lines], None)
+            data = f.read()
+        return StoredTable([TextPartition(d) for d in split_text(data, text_partitions)], {"value": "s"})
     base, n, _ = _read_meta(path)
     schema = None
     if os.path.exists(path + ".schema"):

@@ -28,8 +28,9 @@ _BIT = {"band", "bor", "bxor", "shl", "shr"}
 
 
 class Expr:
-    """Immutable expression node.  `kind` is 'i' (int64), 'f' (float64), 'b' (bool) or 'o'
-    (opaque/object: strings etc., host only)."""
+    """Immutable expression node.  `kind` is 'i' (int64), 'f' (float64), 'b' (bool), 's' (string
+    column: views into a byte buffer, runtime/columnar.py StrColumn), 'S' (sequence of strings per
+    row: the result of `split`) or 'o' (opaque object, host only)."""
 
     __slots__ = ("op", "args", "kind", "_key")
 
@@ -117,6 +118,13 @@ class Expr:
         return self._bin(o, "or" if self.kind == "b" and o.kind == "b" else "bor")
     def __ror__(self, o): return wrap(o).__or__(self)
     def __xor__(self, o): return self._bin(o, "bxor")
+    def split(self, sep: str = " "):
+        """`line.split(" ")` on a string column: a sequence of strings per row (kind 'S'), the
+        SelectMany body of WordCount (samples/WordCount.cs.pp:72).  One single-byte separator."""
+        if self.kind != "s" or not isinstance(sep, str) or len(sep.encode("utf-8")) != 1:
+            raise TraceError("split needs a string column and a one-byte separator")
+        return Expr("split", (self, sep), "S")
+
     def __lshift__(self, o): return self._bin(o, "shl")
     def __rshift__(self, o): return self._bin(o, "shr")
     def __invert__(self):

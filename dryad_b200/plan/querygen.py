@@ -201,7 +201,7 @@ class QueryGen:
                 part = self._node(NodeType.GroupBy, [(child, PW)], pc, None, None, key=key, elem=p.get("elem"),
                                   decomp=dec, mode="partial_acc", comparer=comparer)
                 part.dynamic_manager = DynamicManagerType.PartialAggregator if (SC.DYNAMIC_OPT_LEVEL & SC.DYN_AGGREGATE) else DynamicManagerType.NoManager
-                kir = X.col("key", key.ir.kind) if isinstance(key.ir, X.Expr) and key.ir.kind in "ifb" else None
+                kir = X.col("key", key.ir.kind) if isinstance(key.ir, X.Expr) and key.ir.kind in "ifbs" else None
                 pkey = Lam(lambda kv: kv[0], kir, 1, "Key")
                 merged = self._hash_shuffle(part, pkey, pc, comparer)
                 g = self._node(NodeType.GroupBy, [(merged, PW)], pc, out_info, None, key=pkey, decomp=dec,

@@ -17,7 +17,7 @@ from ..expr.compile import CompileError, run_on_gpu
 from ..ops import core as K
 from ..plan.qnodes import DLinqQueryNode, NodeType
 from . import vertex_ops
-from .columnar import ROW_COL, ColumnBatch
+from .columnar import ROW_COL, ColumnBatch, StrColumn
 
 
 def _tuple_cls(ir):
@@ -96,6 +96,8 @@ class GpuBackend:
     def _run_one(self, node, part, inputs, env):
         fn = _GPU_OPS.get(node.type)
         all_col = all(isinstance(p, ColumnBatch) for payloads in inputs for p in payloads)
+        if all_col and node.type not in _STR_AWARE and any(p.has_strings for payloads in inputs for p in payloads):
+            fn = None                      # operators without a string-column form run on the host path
         if fn is not None and (all_col or node.type == NodeType.InputTable):
             try:
                 r = fn(self, node, part, inputs, env)
@@ -114,10 +116,62 @@ class GpuBackend:
         return ColumnBatch.concat(list(payloads))
 
 
+def _numeric_cols(b: ColumnBatch) -> Dict[str, torch.Tensor]:
+    return {k: v for k, v in b.cols.items() if not isinstance(v, StrColumn)}
+
+
+def _str_col(src: ColumnBatch, lam) -> Optional[StrColumn]:
+    """The string column a traced key / selector names directly (`w => w`, `r => r.word`), else None."""
+    ir = getattr(lam, "ir", None)
+    if isinstance(ir, X.Expr) and ir.op == "col" and ir.kind == "s":
+        c = src.cols.get(ir.args[0])
+        return c if isinstance(c, StrColumn) else None
+    return None
+
+
 # ---- operators -----------------------------------------------------------------------------------
 def _input(be: GpuBackend, node, part, inputs, env):
     p = node.params["table"].partitions[part]
+    data = getattr(p, "data", None)
+    if isinstance(data, (bytes, bytearray)):
+        # text partition: the bytes go to HBM as they are; the string column is views into them
+        # (LinqToDryad/DryadLinqTextReader.cs:36-280 decodes lines on the CPU instead)
+        dbuf = getattr(p, "device_buf", None)
+        if dbuf is not None:
+            dbuf = dbuf if dbuf.device.type == "cuda" else dbuf.to(be.device, non_blocking=True)
+            if dbuf.numel() and bool((dbuf == 13).any().item()):
+                return NotImplemented
+            return [ColumnBatch({"value": StrColumn(dbuf, None, None, None, whole_lines=True)})]
+        if b"\r" in data:
+            return NotImplemented          # CRLF text: the host reader strips the '\r'
+        if len(data) == 0:
+            return [ColumnBatch({"value": StrColumn(torch.empty(0, dtype=torch.uint8, device=be.device),
+                                                   torch.empty(0, dtype=torch.int64, device=be.device),
+                                                   torch.empty(0, dtype=torch.int32, device=be.device))}, 0)]
+        import warnings
+        with warnings.catch_warnings():
+            warnings.simplefilter("ignore")                # read-only buffer: it is only copied from
+            host = torch.frombuffer(data, dtype=torch.uint8)
+        return [ColumnBatch({"value": StrColumn(host.to(be.device, non_blocking=True), None, None, None, whole_lines=True)})]
     return [be._columnar(p, node.schema)]
+
+
+def _select_many(be, node, part, inputs, env):
+    """SelectMany(l => l.Split(c)) over the lines of a text buffer = the tokenizer kernel (K13): the
+    result is a string column of views into the SAME buffer, with the tokens' key hashes."""
+    p = node.params
+    ir = p["fn"].ir
+    if p["indexed"] or p.get("result") is not None or not isinstance(ir, X.Expr) or ir.op != "split":
+        return NotImplemented
+    src = be._cat(inputs[0])
+    a = ir.args[0]
+    sc = src.cols.get(a.args[0]) if a.op == "col" else None
+    if not isinstance(sc, StrColumn) or not sc.whole_lines or sc.device.type != "cuda":
+        return NotImplemented
+    if sc.buf.numel() == 0:
+        return [src]
+    starts, lens, hashes = K.tokenize(sc.buf, ir.args[1], True)
+    return [ColumnBatch({"value": StrColumn(sc.buf, starts, lens, hashes)}, starts.numel())]
 
 
 def _passthrough(be, node, part, inputs, env):
@@ -163,8 +217,17 @@ def _select(be, node, part, inputs, env):
         kinds = [a.out_kind for a in dec.aggs]
         res = dec.result
         proj = {k: _bind_leaves(e, kinds) for k, e in res.items()} if isinstance(res, dict) else {"value": _bind_leaves(res, kinds)}
-        out, _ = run_on_gpu(proj, src.cols, src.n)
-        return [ColumnBatch(out, src.n, tuple_like=_tuple_cls(res))]
+        # string columns can only be passed through (the key of a string GroupBy); the rest is computed
+        passed = {k: src.cols[e.args[0]] for k, e in proj.items()
+                  if e.op == "col" and isinstance(src.cols.get(e.args[0]), StrColumn)}
+        calc = {k: e for k, e in proj.items() if k not in passed}
+        if any(isinstance(src.cols.get(c), StrColumn) for e in calc.values() for c in e.columns()):
+            return NotImplemented
+        out = run_on_gpu(calc, _numeric_cols(src), src.n)[0] if (calc and src.n) else \
+            {k: torch.empty(0, dtype={"i": torch.int64, "f": torch.float64, "b": torch.bool}[e.kind], device=be.device) for k, e in calc.items()}
+        return [ColumnBatch({k: (passed[k] if k in passed else out[k]) for k in proj}, src.n, tuple_like=_tuple_cls(res))]
+    if src.has_strings:
+        return NotImplemented
     if p["indexed"]:
         return NotImplemented
     proj = _proj_of(p["fn"])
@@ -244,6 +307,11 @@ def _group_by(be, node, part, inputs, env):
     src = be._cat(inputs[0])
     mode = p["mode"]
     n = src.n
+    skey = src.cols.get("key") if mode == "final_acc" else _str_col(src, p["key"])
+    if isinstance(skey, StrColumn):
+        return _group_by_str(be, node, src, skey, lanes)
+    if src.has_strings:
+        return NotImplemented
     pre = _group_by_inputs(be, node, src)
     if pre is NotImplemented:
         return NotImplemented
@@ -282,6 +350,76 @@ def _group_by(be, node, part, inputs, env):
         except OverflowError as ex:
             raise DryadLinqException(ErrorCode.FailureInHashGroupBy, "Arithmetic operation resulted in an overflow.") from ex
     return [_group_result_batch(dec, lanes, gk, gl, key_is_f)]
+
+
+def _group_by_str(be, node, src: ColumnBatch, sc: StrColumn, lanes):
+    """Decomposable GroupBy on a STRING key: the table is keyed by the 64-bit hash of the bytes, an
+    extra Min(row index) lane elects a representative string per group, and every row is then
+    compared byte for byte with its group's representative (`tok_verify`), so two different strings
+    that share a hash are detected (the vertex then runs on the host path) instead of merged.
+    Reference: ParallelHashGroupByPartialAccumulate over string keys with the default comparer
+    (LinqToDryad/DryadLinqVertex.cs:5718-6033)."""
+    p = node.params
+    dec = p["decomp"]
+    n = src.n
+    combine = p["mode"] == "final_acc"
+    if len(lanes) >= 8 or sc.device.type != "cuda":
+        return NotImplemented
+    if n == 0:
+        z = lambda dt: torch.empty(0, dtype=dt, device=be.device)   # noqa: E731
+        cols0: Dict[str, Any] = {"key": StrColumn(sc.buf, z(torch.int64), z(torch.int32), z(torch.int64))}
+        for i, ln in enumerate(lanes):
+            cols0[f"agg{i}"] = z(torch.float64 if ln.endswith("f64") else torch.int64)
+        return [ColumnBatch(cols0, 0, acc_lanes=len(dec.aggs))]
+    hashes = sc.key_hashes().contiguous()
+    if _has_reserved_key(hashes):
+        return NotImplemented
+    if combine:
+        in_cols = [src.cols[f"agg{i}"] for i in range(len(lanes))]
+    else:
+        proj = {}
+        for i, a in enumerate(dec.aggs):
+            if a.kind != "count":
+                sel = a.selector.ir if a.selector is not None else None
+                if not isinstance(sel, X.Expr) or any(isinstance(src.cols.get(c), StrColumn) for c in sel.columns()):
+                    return NotImplemented
+                proj[f"__v{i}"] = sel
+        out = run_on_gpu(proj, _numeric_cols(src), n)[0] if proj else {}
+        in_cols = [None if a.kind == "count" else out[f"__v{i}"] for i, a in enumerate(dec.aggs)]
+    in_views = [None if c is None else (c.view(torch.int64) if c.dtype == torch.float64 else c.to(torch.int64)).contiguous() for c in in_cols]
+    row_idx = torch.arange(n, dtype=torch.int64, device=be.device)
+    cap = max(1024, min(2 * n + 64, be.context.group_capacity_hint))
+    while True:
+        tbl = K.HashAggTable(cap, list(lanes) + ["min_i64"], be.device)
+        tbl.update(hashes, in_views + [row_idx], combine=combine)
+        try:
+            gk, gl = tbl.extract()
+            break
+        except K.N.NativeError as ex:
+            if "full" in str(ex) and cap < 4 * n + 1024:
+                cap *= 4
+                continue
+            raise
+        except OverflowError as ex:
+            raise DryadLinqException(ErrorCode.FailureInHashGroupBy, "Arithmetic operation resulted in an overflow.") from ex
+    rep = gl[len(lanes)]
+    rep_start, rep_len = sc.starts[rep].contiguous(), sc.lens[rep].contiguous()
+    # full-key verification: row i must equal the representative of the group its hash fell into
+    jt = K.JoinTable(gk.contiguous())
+    grp = torch.empty(n, dtype=torch.int32, device=be.device)
+    matched = torch.empty(n, dtype=torch.uint8, device=be.device)
+    K.N.check(K.N.kernels().dryad_join_probe_unique(K.ptr(jt.keys), K.ptr(jt.head), jt.cap, K.ptr(hashes), n,
+                                                    K.ptr(grp), K.ptr(matched), K.stream()), "join_probe_unique")
+    K._count()
+    collisions = K.tokenize_verify(sc.buf, sc.starts.contiguous(), sc.lens.contiguous(),
+                                   K.gather_rows(rep_start, grp), K.gather_rows(rep_len, grp))
+    if collisions:
+        return NotImplemented
+    cols: Dict[str, Any] = {"key": StrColumn(sc.buf, rep_start, rep_len, gk)}
+    for i in range(len(dec.aggs)):
+        lane = gl[i].contiguous()
+        cols[f"agg{i}"] = lane.view(torch.float64) if lanes[i].endswith("f64") else lane
+    return [ColumnBatch(cols, gk.numel(), acc_lanes=len(dec.aggs))]
 
 
 def _group_result_batch(dec, lanes, gk, gl, key_is_f) -> ColumnBatch:
@@ -353,20 +491,48 @@ def _partition_generic(be, node, src: ColumnBatch, kbits: torch.Tensor, mode: st
     live on this GPU.  Exact sizes come from a count-only launch, then the scatter runs."""
     from ..parallel.shuffle import ColSpec, FusedShuffle
     nports = node.params["nports"]
-    names = [k for k in src.cols]
-    cols = [kbits.contiguous()] + [src.cols[k].contiguous() for k in names]
+    spmd = getattr(be, "spmd_exchange", False) and nports == be.context.world and be.context.world > 1
+    # a string column travels as three fixed-width physical columns: key hash, length, and the
+    # bytes in zero-padded slots as wide as the longest string (lengths first, bytes behind them)
+    phys: Dict[str, torch.Tensor] = {}
+    strs = {}
+    for k, v in src.cols.items():
+        if isinstance(v, StrColumn):
+            mx = int(v.lens.max().item()) if src.n else 0
+            if spmd:
+                import torch.distributed as dist
+                t = torch.tensor([mx], dtype=torch.int64, device=be.device)
+                dist.all_reduce(t, op=dist.ReduceOp.MAX)      # every rank must use the same slot width
+                mx = int(t.item())
+            w = max(4, (mx + 3) // 4 * 4)
+            if w > 512:
+                return None
+            strs[k] = w
+            phys[k + "#h"] = v.key_hashes()
+            phys[k + "#l"] = v.lens.to(torch.int64)
+            phys[k + "#b"] = v.pack(w)
+        else:
+            phys[k] = v
+    names = [k for k in phys]
+    cols = [kbits.contiguous()] + [phys[k].contiguous() for k in names]
     specs = [ColSpec(8, torch.int64, 1)]
     for k in names:
-        t = src.cols[k]
+        t = phys[k]
         if t.dtype == torch.bool:
             t = t.to(torch.uint8)
         w = t.element_size() * (t.shape[1] if t.dim() > 1 else 1)
         if w % 4:
             return None
         specs.append(ColSpec(w, t.dtype, t.shape[1] if t.dim() > 1 else 1))
+
+    def rebuild(d: Dict[str, torch.Tensor]) -> Dict[str, Any]:
+        out: Dict[str, Any] = {}
+        for k in src.cols:
+            out[k] = StrColumn.from_packed(d[k + "#b"], d[k + "#l"], d[k + "#h"]) if k in strs else d[k]
+        return out
     n = src.n
-    if getattr(be, "spmd_exchange", False) and nports == be.context.world and be.context.world > 1:
-        return _partition_exchange(be, src, names, cols, specs, mode, seps)
+    if spmd:
+        return _partition_exchange(be, src, names, cols, specs, mode, seps, rebuild)
     cap = n + 16                      # worst case: everything lands in one partition
     total = sum(s.width for s in specs) * cap * nports
     if total > (8 << 30):
@@ -380,14 +546,14 @@ def _partition_generic(be, node, src: ColumnBatch, kbits: torch.Tensor, mode: st
     ports = []
     for j in range(nports):
         m = counts[j]
-        d = {k: sh.recv[c + 1][j][:m] for c, k in enumerate(names)}
-        b = ColumnBatch(d, m, src.tuple_like, src.key_spec)
+        d = rebuild({k: sh.recv[c + 1][j][:m] for c, k in enumerate(names)})
+        b = ColumnBatch(d, m, src.tuple_like, src.key_spec, src.acc_lanes)
         b._keepalive = (arena, sh)
         ports.append(b)
     return ports
 
 
-def _partition_exchange(be, src: ColumnBatch, names, cols, specs, mode: str, seps):
+def _partition_exchange(be, src: ColumnBatch, names, cols, specs, mode: str, seps, rebuild=None):
     """SPMD form of a distributor stage (one process per GPU, partition p lives on rank p): the
     partition function, the all-to-all and the consumer's Merge are ONE fused kernel chain writing
     straight into the owners' receive buffers over NVLink (parallel/shuffle.py).  The vertex's
@@ -435,9 +601,11 @@ def _partition_exchange(be, src: ColumnBatch, names, cols, specs, mode: str, sep
     # the receive buffers are reused by the next exchange of this layout: hand out copies
     d = {k: sh.recv[c + 1][0][:m].clone() for c, k in enumerate(names)}
     for k in names:
-        if src.cols[k].dtype == torch.bool:
+        if k in src.cols and src.cols[k].dtype == torch.bool:
             d[k] = d[k].view(torch.bool) if d[k].dtype == torch.uint8 else d[k]
-    b = ColumnBatch(d, m, src.tuple_like, src.key_spec)
+    if rebuild is not None:
+        d = rebuild(d)
+    b = ColumnBatch(d, m, src.tuple_like, src.key_spec, src.acc_lanes)
     b._exchanged = True
     be.fused_exchanges = getattr(be, "fused_exchanges", 0) + 1
     return [b]
@@ -447,7 +615,9 @@ def _hash_partition(be, node, part, inputs, env):
     src = be._cat(inputs[0])
     if src.is_rows or node.params.get("comparer") is not None:
         return NotImplemented
-    kb = _key_column(src, node.params["key"])
+    sk = _str_col(src, node.params["key"])
+    kb = sk.key_hashes() if sk is not None else (None if src.has_strings and not isinstance(node.params["key"].ir, X.Expr)
+                                                 else _key_column(src, node.params["key"]))
     if kb is None:
         return NotImplemented
     r = _partition_generic(be, node, src, kb, "hash", None)
@@ -727,7 +897,12 @@ def _set_operation(be, node, part, inputs, env):
     return [ColumnBatch({"value": r.view(torch.float64) if f else r}, r.numel())]
 
 
+# operators that understand string columns (StrColumn); the others see them only through the host path
+_STR_AWARE = {NodeType.InputTable, NodeType.OutputTable, NodeType.Dummy, NodeType.Merge, NodeType.Concat, NodeType.Tee,
+              NodeType.ForkBranch, NodeType.Select, NodeType.SelectMany, NodeType.GroupBy, NodeType.HashPartition}
+
 _GPU_OPS = {
+    NodeType.SelectMany: _select_many,
     NodeType.InputTable: _input, NodeType.OutputTable: _passthrough, NodeType.Dummy: _passthrough,
     NodeType.Merge: _passthrough, NodeType.Concat: _passthrough, NodeType.ForkBranch: _passthrough,
     NodeType.Tee: _tee, NodeType.Select: _select, NodeType.Where: _where, NodeType.GroupBy: _group_by,

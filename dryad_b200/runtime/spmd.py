@@ -331,7 +331,7 @@ class SpmdExecutor(JobExecutor):
             return self._run_rowsort(node)
         if kind == "gb_producer":
             return self._run_gb_producer(node)
-        if kind == "gb_consumer":
+        if kind in ("gb_consumer", "plain"):
             return self._run_gb_consumer(node)
         return self._run_bjoin(node)
 

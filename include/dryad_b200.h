@@ -366,6 +366,11 @@ int dryad_tokenize_count(const uint8_t* text, int64_t n, int delim, int keep_emp
 int dryad_tokenize_write(const uint8_t* text, int64_t n, int delim, int keep_empty, int64_t* starts,
                          int32_t* lens, uint64_t* hashes, void* scratch, size_t scratch_bytes,
                          void* stream);
+/* String columns as (start, length) views into a byte buffer: key hashes (same function as the
+ * tokenizer's) and packing into zero-padded fixed-width slots for the fused shuffle
+ * (LinqToDryad/DryadLinqBinaryWriter.cs:523-546, LinqToDryad/LineRecord.cs:30-176). */
+int dryad_hash_views(const uint8_t* buf, const int64_t* starts, const int32_t* lens, int64_t n, uint64_t* out, void* stream);
+int dryad_str_pack(const uint8_t* buf, const int64_t* starts, const int32_t* lens, int64_t n, int width, uint8_t* out, void* stream);
 int dryad_tokenize_verify(const uint8_t* text, const int64_t* starts, const int32_t* lens,
                           const int64_t* rep_start, const int32_t* rep_len, int64_t ntok,
                           unsigned long long* mismatches, void* stream);

@@ -336,6 +336,38 @@ def gpu_checks(rank, world):
     torch.cuda.synchronize()
 
 
+def wordcount_checks(rank, world, dev):
+    """WordCount through the API on `world` GPUs: every rank reads its own byte range of the text
+    file, tokenizes on the GPU, partial-aggregates on token hashes, the partials (hash, length,
+    padded bytes, count) cross NVLink in the fused hash shuffle, owners aggregate and verify."""
+    import tempfile
+    from dryad_b200.models import wordcount as WC
+    path = os.path.join(tempfile.gettempdir(), "dryad_wc_corpus.txt")
+    if rank == 0:
+        with open(path, "wb") as f:
+            f.write(WC.generate_text(20_000, words_per_line=10, seed=11, vocab=3000))
+    dist.barrier()
+    ctx = D.DryadLinqContext(platform="B200", device=str(dev))
+    q = (ctx.from_store("file://" + path).select_many(lambda l: l.split(" ")).group_by(lambda w: w)
+         .select(lambda g: D.Pair(g.key, g.count())))
+    mine = dict(q.partitions()[0])
+    be = ctx._backend()
+    assert be.host_fallbacks == 0, be.host_fallbacks
+    assert ctx.last_object_collectives == 0
+    everyone = [None] * world
+    dist.all_gather_object(everyone, mine)
+    merged = {}
+    for d_ in everyone:
+        assert not (set(d_) & set(merged)), "a word is owned by two ranks"
+        merged.update(d_)
+    if rank == 0:
+        from collections import Counter
+        with open(path, "rb") as f:
+            want = Counter(w.decode() for line in f.read().split(b"\n")[:-1] for w in line.split(b" "))
+        assert merged == dict(want), (len(merged), len(want))
+    dist.barrier()
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--mode", default="cpu")
@@ -350,6 +382,7 @@ def main():
         torch.cuda.set_device(dev)
         dist.init_process_group("nccl", device_id=dev)
         gpu_checks(rank, world)
+        wordcount_checks(rank, world, dev)
     dist.barrier()
     if rank == 0:
         print(f"SPMD {a.mode} checks passed on {world} ranks")
