@@ -140,6 +140,7 @@ class DryadLinqContext:
         # engine knobs (GraphManager/graph/DrGraphParameters.cpp:50-69)
         self.max_failures_per_vertex = 6
         self.fail_fast_on_deterministic_errors = False
+        self.spmd_control_timeout = 120.0      # seconds a rank waits for the graph manager / the manager for a rank
         self.retain_intermediate = True
         self.sample_rate = SC.SAMPLE_RATE
         self.group_capacity_hint = 1 << 26     # max initial hash-aggregate table slots per vertex
@@ -171,6 +172,9 @@ class DryadLinqContext:
     def dispose(self):
         self._disposed = True
         self._tables.clear()
+        cp = self.__dict__.pop("_control_plane", None)
+        if cp is not None:
+            cp.close()                       # the graph manager's mailbox service (SPMD jobs)
 
     Dispose = dispose
 

@@ -79,6 +79,58 @@ def _read_meta(path: str):
     return base.value.decode(), n, [sizes[i] for i in range(min(n, 65536))]
 
 
+def write_part(uri: str, index: int, part, compression: Optional[str] = None):
+    """Write ONE partition of a table as an uncommitted version file (SPMD: every rank writes its own
+    partition).  Returns (tmp_path, final_path, stored_bytes); nothing is visible until
+    `commit_part` renames it and `finish_table` publishes the metadata file
+    (GraphManager/filesystem/DrPartitionFile.cpp:561-580, DrGraph::FinalizeGraph)."""
+    scheme, path = parse_uri(uri)
+    lib = N.host()
+    os.makedirs(os.path.dirname(os.path.abspath(path)) or ".", exist_ok=True)
+    base = os.path.splitext(path)[0]
+    comp = 1 if str(compression or "None").lower() in ("gzip", "1", "true") else 0
+    final = _part_path(base, index)
+    tmp = final + ".v0.tmp"
+    try:
+        w = lib.dh_writer_open(tmp.encode(), comp, 0)
+        if not w:
+            raise DryadLinqException(ErrorCode.FailedToCreateStream, f"cannot create {tmp}")
+        recs = part.to_records() if hasattr(part, "to_records") else part
+        for rec in recs:
+            b = R.encode_record(rec)
+            lib.dh_write_bytes(w, b, len(b))
+            rc = lib.dh_writer_end_record(w)
+            if rc:
+                raise DryadLinqException(ErrorCode.WriteFileError, f"write failed ({rc})")
+        raw, stored, nrec = C.c_int64(), C.c_int64(), C.c_int64()
+        rc = lib.dh_writer_close(w, C.byref(raw), C.byref(stored), C.byref(nrec))
+        if rc:
+            raise DryadLinqException(ErrorCode.WriteFileError, f"close failed ({rc})")
+    except BaseException:
+        if os.path.exists(tmp):
+            os.remove(tmp)
+        raise
+    return tmp, final, stored.value
+
+
+def commit_part(tmp: str, final: str) -> None:
+    if N.host().dh_commit_part(tmp.encode(), final.encode()):
+        raise DryadLinqException(ErrorCode.WriteFileError, f"cannot commit {final}")
+
+
+def finish_table(uri: str, sizes: Sequence[int], schema=None, compression: Optional[str] = None) -> None:
+    """Publish the metadata of a table whose partitions have all been committed."""
+    scheme, path = parse_uri(uri)
+    base = os.path.splitext(path)[0]
+    comp = 1 if str(compression or "None").lower() in ("gzip", "1", "true") else 0
+    arr = (C.c_int64 * max(len(sizes), 1))(*sizes)
+    rc = N.host().dh_partfile_write(path.encode(), base.encode(), len(sizes), arr, b"")
+    if rc:
+        raise DryadLinqException(ErrorCode.WriteFileError, f"cannot write {path} ({rc})")
+    with open(path + ".schema", "w") as f:
+        json.dump({"schema": schema, "compression": "Gzip" if comp else "None"}, f)
+
+
 def write_table(uri: str, parts: Sequence[Sequence], schema=None, compression: Optional[str] = None) -> None:
     scheme, path = parse_uri(uri)
     lib = N.host()

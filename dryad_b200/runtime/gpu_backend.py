@@ -501,6 +501,9 @@ def _partition_generic(be, node, src: ColumnBatch, kbits: torch.Tensor, mode: st
             mx = int(v.lens.max().item()) if src.n else 0
             if spmd:
                 import torch.distributed as dist
+                sync = be.context.__dict__.get("_spmd_sync")
+                if sync is not None:
+                    sync()
                 t = torch.tensor([mx], dtype=torch.int64, device=be.device)
                 dist.all_reduce(t, op=dist.ReduceOp.MAX)      # every rank must use the same slot width
                 mx = int(t.item())
@@ -563,6 +566,9 @@ def _partition_exchange(be, src: ColumnBatch, names, cols, specs, mode: str, sep
     from ..parallel.shuffle import FusedShuffle
     ctx = be.context
     n = src.n
+    sync = ctx.__dict__.get("_spmd_sync")
+    if sync is not None:
+        sync()                                           # agreement point before the collective (spmd_control)
     t = torch.tensor([n, -n], dtype=torch.int64, device=be.device)
     tot = torch.tensor([n], dtype=torch.int64, device=be.device)
     dist.all_reduce(t, op=dist.ReduceOp.MAX)

@@ -35,6 +35,7 @@ from ..api.errors import DryadLinqException, ErrorCode
 from ..plan.qnodes import ConnOp, DLinqQueryNode, NodeType
 from .columnar import ROW_COL, ColumnBatch
 from .executor import JobExecutor
+from .spmd_control import StageAborted
 from .vertex_ops import VertexEnv
 
 
@@ -53,6 +54,7 @@ class SpmdExecutor(JobExecutor):
         self.arena = None                      # created lazily: host-backend SPMD needs no GPU arena
         self._skip: set = set()
         self._fused: Dict[int, Any] = {}
+        self._cp = None
         self.object_collectives = 0            # data-carrying *_object collectives (host records)
         self.tensor_collectives = 0            # columnar edges moved as tensors
 
@@ -142,6 +144,41 @@ class SpmdExecutor(JobExecutor):
             self._skip.update(x.uid for x in chain)
 
     # ---- run -----------------------------------------------------------------------------------
+    def _control(self):
+        ctx = self.context
+        cp = ctx.__dict__.get("_control_plane")
+        if cp is None:
+            from .spmd_control import ControlPlane
+            dev = self.backend.device if getattr(self.backend, "name", "") == "gpu" else torch.device("cpu")
+            cp = ControlPlane(ctx, dev)
+            ctx.__dict__["_control_plane"] = cp
+        return cp
+
+    def _sync(self) -> None:
+        """Agreement point, called before every collective of a stage attempt (see spmd_control)."""
+        if self._cp is not None and not self._cp.agree(True):
+            raise StageAborted()
+
+    def _build_gm(self):
+        """One GM vertex per executed plan stage (an SPMD stage is a gang), chained in plan order on
+        top of the plan's own edges so the manager hands the stages out in an order every rank can
+        follow with the inputs it retained."""
+        from ..sched.gm import GraphManager
+        ctx = self.context
+        gm = GraphManager(max_failures=ctx.max_failures_per_vertex, speculative=False)
+        self._gm_node = {}
+        prev = None
+        sid = {}
+        for node in self.plan.nodes:
+            if node.uid in self._skip:
+                continue
+            sid[node.uid] = gm.add_stage(f"{node.name}#{node.uid}", 1)
+            self._gm_node[sid[node.uid]] = node
+            if prev is not None:
+                gm.connect(prev, sid[node.uid])
+            prev = sid[node.uid]
+        return gm
+
     def run(self):
         ctx = self.context
         if any(n.partition_count not in (1, self.world) for n in self.plan.nodes):
@@ -160,33 +197,122 @@ class SpmdExecutor(JobExecutor):
         t_job = time.perf_counter()
         for node in self.plan.nodes:
             self.out[node.uid] = [None] * node.partition_count
-            if node.uid in self._skip:
-                continue
-            mine = self.rank if node.partition_count == self.world else (0 if self.rank == 0 else None)
-            t0 = time.perf_counter()
-            import contextlib
-            span = self.timeline.span(f"{node.name}#{node.uid}[{mine}]", stage=node.uid, part=mine, rank=self.rank) \
-                if (self.timeline is not None and mine is not None) else contextlib.nullcontext()
-            if node.uid in self._fused:
-                with span:
-                    ports = self._run_fused(node)
-            elif mine is None:
-                self._participate_only(node)
-                continue
+        self._cp = self._control() if self.world > 1 else None
+        ctx.__dict__["_spmd_sync"] = self._sync
+        nodes = {n.uid: n for n in self.plan.nodes}
+        try:
+            if self._cp is None:
+                for node in self.plan.nodes:
+                    if node.uid not in self._skip:
+                        self._run_stage(node, 0)
+                ok, message = True, ""
             else:
-                ins = self._spmd_inputs(node, mine)
-                env = VertexEnv(ctx, node.uid, mine, 0)
-                with span:
-                    ports = self.backend.run_vertex(node, mine, ins, env)
-            if mine is not None:
-                self.out[node.uid][mine] = ports
-                rep.vertex_event(node, mine, 0, "completed", seconds=time.perf_counter() - t0)
-        results = self._commit_local()
+                ok, message = self._run_controlled(nodes, rep)
+        finally:
+            ctx.__dict__.pop("_spmd_sync", None)
         ctx.__dict__["last_object_collectives"] = self.object_collectives
         ctx.__dict__["last_tensor_collectives"] = self.tensor_collectives
+        if not ok:
+            self.out.clear()                               # nothing is committed
+            rep.job_stop(False, message)
+            raise DryadLinqException(ErrorCode.DidNotCompleteSuccessfully, message)
+        results = self._commit_local()
         self._flush_timeline()
         rep.job_stop(True, "", seconds=time.perf_counter() - t_job)
         return results
+
+    def _run_controlled(self, nodes, rep):
+        """The job under the control plane: rank 0 asks the native graph manager for the next stage
+        attempt and posts its launch descriptor into every rank's mailbox; every rank (rank 0
+        included) runs the attempt and reports; a failed attempt is re-run by all ranks from the
+        inputs they retained; when the failure budget of a stage is spent (or the error is
+        deterministic) every rank receives `abort`; outputs are committed only on `commit`."""
+        import traceback
+        from .command import CMD_START, VertexCommand
+        from .spmd_control import terminate_command
+        ctx, cp = self.context, self._cp
+        gm = self._build_gm() if self.rank == 0 else None
+        self.gm = gm
+        if gm is not None:
+            gm.start()
+        t_job = time.perf_counter()
+        self.stage_attempts = 0
+        while True:
+            if gm is not None:                             # ---- graph manager (rank 0) ----
+                nxt = gm.next_ready(time.perf_counter() - t_job)
+                if nxt is None:
+                    done = gm.state == "Succeeded"
+                    cp.post_command(terminate_command(done, "" if done else f"job ended in state {gm.state}: {gm.error()}"))
+                else:
+                    v, version = nxt
+                    node = self._gm_node[gm.vertex(v)["stage"]]
+                    cp.post_command(VertexCommand(CMD_START, node.uid, version, args=[node.name, str(self.world)]))
+            cmd = cp.next_command()                        # ---- worker (every rank) ----
+            if cmd.command != CMD_START:
+                commit = bool(cmd.args) and cmd.args[0] == "commit"
+                return commit, (cmd.args[1] if len(cmd.args) > 1 else "")
+            node, version = nodes[cmd.vertex_id], cmd.version
+            self.stage_attempts += 1
+            t0 = time.perf_counter()
+            ok, text, deterministic = True, "", False
+            try:
+                if ctx.fault_injector is not None:
+                    ctx.fault_injector(node, self.rank, version)
+                self._run_stage(node, version)
+                if not cp.agree(True):                     # end-of-attempt agreement
+                    ok, text = False, "aborted: another rank failed"
+            except StageAborted:
+                ok, text = False, "aborted: another rank failed"
+            except Exception as ex:  # noqa: BLE001  (vertex code is user code)
+                cp.agree(False)                            # pairs with the healthy ranks' next agreement point
+                ok = False
+                text = "".join(traceback.format_exception_only(type(ex), ex)).strip()
+                deterministic = isinstance(ex, DryadLinqException) and not getattr(ex, "transient", False)
+                if deterministic and ctx.fail_fast_on_deterministic_errors:
+                    text = "deterministic: " + text
+            if not ok:
+                self.out[node.uid] = [None] * node.partition_count
+            rep.vertex_event(node, self.rank, version, "completed" if ok else "failed",
+                             **({"seconds": time.perf_counter() - t0} if ok else {"error": text}))
+            cp.report(node.uid, version, ok, text)
+            if gm is not None:                             # ---- graph manager: account the attempt ----
+                all_ok, err = cp.collect(node.uid, version)
+                v = next(k for k, n_ in self._gm_node.items() if n_ is node)
+                gv = gm.stage_vertices(v)[0]
+                if all_ok:
+                    gm.completed(gv, version, time.perf_counter() - t0)
+                else:
+                    rc = gm.failed(gv, version, err or "stage attempt failed")
+                    if rc == 1 or "deterministic: " in err or "rank lost" in err:
+                        msg = gm.error() or err
+                        if "deterministic: " in err:
+                            msg = err.replace("deterministic: ", "")
+                        cp.post_command(terminate_command(False, msg))
+                        gm = None                          # the next command every rank sees is `abort`
+
+    def _run_stage(self, node, version: int):
+        """One attempt of one plan stage on this rank."""
+        ctx, rep = self.context, self.reporter
+        mine = self.rank if node.partition_count == self.world else (0 if self.rank == 0 else None)
+        t0 = time.perf_counter()
+        import contextlib
+        span = self.timeline.span(f"{node.name}#{node.uid}[{mine}]", stage=node.uid, part=mine, rank=self.rank) \
+            if (self.timeline is not None and mine is not None) else contextlib.nullcontext()
+        if node.uid in self._fused:
+            with span:
+                ports = self._run_fused(node)
+        elif mine is None:
+            self._participate_only(node)
+            return
+        else:
+            ins = self._spmd_inputs(node, mine)
+            env = VertexEnv(ctx, node.uid, mine, version)
+            with span:
+                ports = self.backend.run_vertex(node, mine, ins, env)
+        if mine is not None:
+            self.out[node.uid][mine] = ports
+            if self._cp is None:
+                rep.vertex_event(node, mine, version, "completed", seconds=time.perf_counter() - t0)
 
     def _participate_only(self, node):
         """Ranks without a vertex in a single-partition stage still take part in its gathers."""
@@ -202,6 +328,7 @@ class SpmdExecutor(JobExecutor):
         holds it as a ColumnBatch with a known numeric schema.  A rank whose vertex fell back to host
         records makes the whole edge take the object path, so no rank waits in the wrong collective."""
         from .gpu_backend import _numeric_schema
+        self._sync()
         ok = _numeric_schema(schema) and all(isinstance(p, ColumnBatch) and not p.is_rows and p.acc_lanes is None
                                              for p in payloads if p is not None)
         dev = self.backend.device if getattr(self.backend, "name", "") == "gpu" else torch.device("cpu")
@@ -245,6 +372,7 @@ class SpmdExecutor(JobExecutor):
             return parts if self.rank == 0 else None
         recs = self.backend.to_records(payload) if payload is not None else []
         bucket: Optional[List] = [None] * self.world if self.rank == 0 else None
+        self._sync()
         dist.gather_object(recs, bucket, dst=0)
         self.object_collectives += 1
         return bucket
@@ -277,6 +405,7 @@ class SpmdExecutor(JobExecutor):
                 return [[own], [halo if self.rank > 0 else own.slice(0, 0)]]
             recs = self.backend.to_records(own)
             tails_o: List = [None] * self.world
+            self._sync()
             dist.all_gather_object(tails_o, list(recs[-(w - 1):]) if w > 1 else [])
             self.object_collectives += 1
             halo_r: List = []
@@ -303,6 +432,7 @@ class SpmdExecutor(JobExecutor):
                     continue
                 recs = [self.backend.to_records(p) for p in ports] if ports is not None else None
                 everyone: List = [None] * self.world
+                self._sync()
                 dist.all_gather_object(everyone, recs)
                 self.object_collectives += 1
                 ins.append([everyone[s][i] for s in range(self.world) if everyone[s] is not None])
@@ -315,6 +445,7 @@ class SpmdExecutor(JobExecutor):
                     ins.append([got[0]])
                     continue
                 box = [self.backend.to_records(payload) if self.rank == 0 else None]
+                self._sync()
                 dist.broadcast_object_list(box, src=0)
                 self.object_collectives += 1
                 ins.append([box[0]])
@@ -342,6 +473,7 @@ class SpmdExecutor(JobExecutor):
         if rows.device.type != "cuda":
             rows = rows.to(self.backend.device, non_blocking=True)
         rk = ob.params["key"].fn
+        self._sync()
         nmax = torch.tensor([rows.shape[0]], dtype=torch.int64, device=rows.device)
         dist.all_reduce(nmax, op=dist.ReduceOp.MAX)           # control plane: size the receive side
         sorter = self.context._row_sorter(int(nmax.item()), rows.shape[1], rk.offset, max(8, rk.length),
@@ -376,6 +508,7 @@ class SpmdExecutor(JobExecutor):
             except G.CompileError:
                 pre = NotImplemented
         ok = pre is not NotImplemented and not G._has_reserved_key(pre[0])
+        self._sync()
         flag = torch.tensor([1 if ok else 0], dtype=torch.int64, device=be.device)
         dist.all_reduce(flag, op=dist.ReduceOp.MIN)
         if int(flag.item()):
@@ -412,6 +545,7 @@ class SpmdExecutor(JobExecutor):
             ins = self._spmd_inputs(node, self.rank)
             return self.backend.run_vertex(node, self.rank, ins, VertexEnv(self.context, node.uid, self.rank, 0))
         kind, producer, gb, rest = info
+        self._sync()                                           # before the device-side barriers of the aggregate
         uid, (kbits, in_views, key_is_f, _combine) = self._gb_ready
         assert uid == producer.uid
         dec = gb.params["decomp"]
@@ -450,6 +584,7 @@ class SpmdExecutor(JobExecutor):
             okb, ikb = G._key_column(outer, p["outer_key"]), G._key_column(inner, p["inner_key"])
             ok = okb is not None and ikb is not None and not G._has_reserved_key(okb, ikb)
         dev = be.device
+        self._sync()
         t = torch.tensor([1 if ok else 0, inner.n if ok else 0], dtype=torch.int64, device=dev)
         sizes = torch.zeros(self.world * 2, dtype=torch.int64, device=dev)
         dist.all_gather_into_tensor(sizes, t)
@@ -528,12 +663,47 @@ class SpmdExecutor(JobExecutor):
         return self.backend.run_vertex(node, self.rank, [[outer_ports[0]], inner_all], env)
 
     def _commit_local(self):
+        """Output commit, reached only after the graph manager's `commit` command (every stage
+        succeeded on every rank).  A table with a store URI is written by all ranks together: each
+        rank writes its own partition as an uncommitted version file, the ranks agree that all
+        writes succeeded, then every rank renames its part and rank 0 publishes the metadata — a
+        failure anywhere removes the version files, so a failed job leaves no part files."""
+        import os
+        from ..channel import store
         results = {}
         for root in self.plan.roots:
             node = _tail(root)
             mine = self.rank if root.partition_count == self.world else 0
             payload = self.out[root.uid][mine]
             parts = [payload[0]] if payload is not None else [[]]
-            table = self.context._commit_table(None, parts, root.schema, root.info, None, True)
+            uri = node.params.get("uri")
+            if uri and self.world > 1:
+                tmp = final = None
+                size, err = 0, None
+                writes = payload is not None and (root.partition_count == self.world or self.rank == 0)
+                try:
+                    if writes:
+                        tmp, final, size = store.write_part(uri, mine, payload[0], node.params.get("compression"))
+                except Exception as ex:  # noqa: BLE001
+                    err = ex
+                ok = self._cp.agree(err is None) if self._cp is not None else err is None
+                if not ok:
+                    if tmp and os.path.exists(tmp):
+                        os.remove(tmp)
+                    raise DryadLinqException(ErrorCode.WriteFileError,
+                                             f"output {uri} was not committed: {err or 'another rank could not write its partition'}")
+                if writes:
+                    store.commit_part(tmp, final)
+                nparts = root.partition_count
+                sizes: List = [None] * self.world
+                dist.all_gather_object(sizes, size)                    # control plane: one integer per rank
+                if self.rank == 0:
+                    store.finish_table(uri, sizes[:nparts], root.schema, node.params.get("compression"))
+                dist.barrier()
+                table = self.context._commit_table(None, parts, root.schema, root.info, None, node.params.get("temporary", False))
+                table.uri = uri
+            else:
+                table = self.context._commit_table(uri if self.world == 1 else None, parts, root.schema, root.info,
+                                                   node.params.get("compression"), node.params.get("temporary", True))
             results[node.params["qexpr_id"]] = table
         return results
