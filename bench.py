@@ -79,6 +79,7 @@ def main():
     ap.add_argument("--groupby-keys", type=int, default=1 << 20)
     ap.add_argument("--skip-e2e", action="store_true")
     ap.add_argument("--skip-groupby", action="store_true")
+    ap.add_argument("--kmeans-points", type=int, default=125_000_000, help="points per GPU of the named-size k-means run (0 = skip)")
     ap.add_argument("--skip-baseline", action="store_true", help="do not time the PyTorch+NCCL comparison arm")
     a = ap.parse_args()
 
@@ -343,10 +344,48 @@ def main():
             k1.record()
             barrier()
             kms = max_over_ranks(k0.elapsed_time(k1)) / a.steps
+            queued, changed = km.ucount.tolist()
             extra["kmeans"] = {"metric": "kmeans_seconds_per_iteration", "value": kms * 1e-3, "unit": "s",
                                "points_per_gpu": npts, "dims": 128, "k": kk, "points_per_s": world * npts / (kms * 1e-3),
                                "tf32_tflops_per_gpu": 2.0 * npts * kk * 128 / (kms * 1e-3) / 1e12,
+                               "assignments": "fp32-exact: TF32 tensor-core choice certified per point in the assign kernel, "
+                                              "uncertified points re-evaluated in fp32",
+                               "uncertified_points_last_iteration": int(queued), "moved_by_recheck": int(changed),
                                "total_count_ok": int(km.total_counts.sum().item()) == world * npts}
+            # the same iteration without the certificate (TF32 choice taken as is), for the cost of exactness
+            km_t = KMeans(karena, kk, npts, exact=False)
+            km_t.set_centroids(centres + 0.05)
+            extra["kmeans"]["tf32_only_ms_per_iteration"] = timed(lambda: km_t.iterate(pts), a.steps, 2)
+            del km_t
+            # ... and as a query: do_while over apply_per_partition(KMeansStep) through the public API
+            try:
+                kctx = DryadLinqContext(world, platform="B200" if world > 1 else "LOCAL", device=f"cuda:{local_rank}")
+                kstep = KM.KMeansStep(kctx)
+                pq, cq = kctx.from_columns({"x": pts}), kctx.from_columns({"c": centres + 0.05})
+
+                class _Budget:
+                    device = True
+
+                    def __init__(self):
+                        self.left = 0
+
+                    def __call__(self, new_c, old_c):
+                        self.left -= 1
+                        return {"value": torch.tensor([self.left > 0], device=dev)}
+                bud = _Budget()
+
+                def api_loop(iters):
+                    bud.left = iters
+                    return cq.do_while(lambda cur: pq.apply_per_partition(kstep, cur),
+                                       lambda cur, nxt: nxt.apply_per_partition(bud, cur))
+                api_loop(2)
+                barrier()
+                t_api = time.perf_counter()
+                api_loop(5)
+                barrier()
+                extra["kmeans"]["api_do_while_s_per_iteration"] = max_over_ranks((time.perf_counter() - t_api) / 5)
+            except Exception as ex:  # noqa: BLE001
+                extra["kmeans"]["api_do_while_error"] = f"{type(ex).__name__}: {ex}"
             if not a.skip_baseline:
                 c0 = centres + 0.05
                 ms_ = timed(lambda: B.kmeans_step(pts, c0, world), 2, 1)
@@ -354,6 +393,24 @@ def main():
                 ms_ = timed(lambda: B.gemm_tf32_only(pts, c0), 3, 1)
                 base["kmeans_gemm_only_cublas_tf32"] = {"ms": ms_, "tflops": 2.0 * npts * kk * 128 / (ms_ * 1e-3) / 1e12,
                                                         "what": "the distance GEMM alone (8 M x 128 x 1024), no argmin, no sums, no all-reduce"}
+            # BASELINE.json config 5 at its named size: 1 B points x 128 over 8 GPUs = 125 M points per GPU
+            # (64 GB of fp32 points per GPU); same per-GPU size at every N (weak scaling)
+            if a.kmeans_points > npts:
+                try:
+                    del pts, km
+                    torch.cuda.empty_cache()
+                    bigp, centres = KM.generate(a.kmeans_points, kk, 5, dev, rank)
+                    kmb = KMeans(karena, kk, a.kmeans_points)
+                    kmb.set_centroids(centres + 0.05)
+                    bms = timed(lambda: kmb.iterate(bigp), 3, 1)
+                    extra["kmeans_named_size"] = {"metric": "kmeans_seconds_per_iteration", "value": bms * 1e-3, "unit": "s",
+                                                  "points_per_gpu": a.kmeans_points, "points_total": world * a.kmeans_points,
+                                                  "dims": 128, "k": kk, "tf32_tflops_per_gpu": 2.0 * a.kmeans_points * kk * 128 / (bms * 1e-3) / 1e12,
+                                                  "total_count_ok": int(kmb.total_counts.sum().item()) == world * a.kmeans_points}
+                    del bigp, kmb
+                    torch.cuda.empty_cache()
+                except Exception as ex:  # noqa: BLE001
+                    extra["kmeans_named_size"] = {"error": f"{type(ex).__name__}: {ex}"}
         except Exception as ex:  # noqa: BLE001
             extra["kmeans"] = {"error": f"{type(ex).__name__}: {ex}"}
 

@@ -400,7 +400,9 @@ template <int EW>      // epilogue warps per CTA: 8 or 16
 __global__ void __launch_bounds__((2 + EW) * 32, 1)
 km_assign_pair(const __grid_constant__ CUtensorMap map_x, const __grid_constant__ CUtensorMap map_c,
                const float* __restrict__ cnorm, int64_t n, int k, int32_t* __restrict__ assign,
-               float* __restrict__ sums, unsigned long long* __restrict__ counts, float* __restrict__ inertia, int dbg) {
+               float* __restrict__ sums, unsigned long long* __restrict__ counts, float* __restrict__ inertia, int dbg,
+               const float* __restrict__ cent, const float* __restrict__ sep2, uint32_t* __restrict__ ulist,
+               unsigned int* __restrict__ ucount) {
   extern __shared__ unsigned char smem_raw[];
   unsigned char* smem = reinterpret_cast<unsigned char*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
   unsigned char* sA = smem + OFF_A;
@@ -602,8 +604,19 @@ km_assign_pair(const __grid_constant__ CUtensorMap map_x, const __grid_constant_
           }
           if (row0 + rr < n) {
             const float4 x = lds_f4(smem_u32(sA + ab * A_BYTES + kb * A_KB_BYTES + (rr >> 3) * 1024 + (rr & 7) * 128 + ((ch ^ (rr & 7)) << 4)));
-            xn += x.x * x.x + x.y * x.y + x.z * x.z + x.w * x.w;
+            const float x2 = x.x * x.x + x.y * x.y + x.z * x.z + x.w * x.w;
+            xn += x2;
             if (!(dbg & 1)) red_add_v4(sums + (size_t)wi * D + kb * KB + ch * 4, x);
+            if (sep2) {
+              // Certificate (Elkan's first lemma): the TF32 products picked centroid wi; if the EXACT
+              // fp32 distance to it is at most half the distance to wi's nearest other centroid, no
+              // other centroid can be closer, so the choice equals the fp32 argmin.  Everything else
+              // is queued for the fp32 re-check kernel.
+              const float4 c4 = __ldg(reinterpret_cast<const float4*>(cent + (size_t)wi * D + kb * KB + ch * 4));
+              float dp = x2 - 2.f * (x.x * c4.x + x.y * c4.y + x.z * c4.z + x.w * c4.w);
+              dp = warp_sum(dp);
+              if (lane == 0 && !(dp + s_cn[wi] <= sep2[wi])) ulist[atomicAdd(ucount, 1u)] = (uint32_t)(row0 + rr);
+            }
           }
         }
         local_inertia += xn;
@@ -620,6 +633,124 @@ km_assign_pair(const __grid_constant__ CUtensorMap map_x, const __grid_constant_
   if (warp == 1) {
     tc_fence_after();
     asm volatile("tcgen05.dealloc.cta_group::2.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "n"(TMEM_COLS2) : "memory");
+  }
+}
+
+// sep2[b] = (1/4) * min over j != b of |c_b - c_j|^2, shaved by a relative 1e-4 so that fp32 rounding in
+// either side of the certificate can only make it MORE conservative.  One block per centroid.
+__global__ void __launch_bounds__(256) km_sep(const float* __restrict__ c, int k, float* __restrict__ sep2) {
+  __shared__ float s_c[D];
+  __shared__ float s_min[8];
+  const int b = blockIdx.x;
+  if (threadIdx.x < D) s_c[threadIdx.x] = c[(size_t)b * D + threadIdx.x];
+  __syncthreads();
+  float best = 3.4e38f;
+  for (int j = threadIdx.x; j < k; j += 256) {
+    if (j == b) continue;
+    float d2 = 0.f;
+    const float4* cj = reinterpret_cast<const float4*>(c + (size_t)j * D);
+#pragma unroll 8
+    for (int q = 0; q < D / 4; ++q) {
+      const float4 v = __ldg(cj + q);
+      const float a0 = v.x - s_c[4 * q], a1 = v.y - s_c[4 * q + 1], a2 = v.z - s_c[4 * q + 2], a3 = v.w - s_c[4 * q + 3];
+      d2 += a0 * a0 + a1 * a1 + a2 * a2 + a3 * a3;
+    }
+    best = fminf(best, d2);
+  }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) best = fminf(best, __shfl_xor_sync(0xffffffffu, best, o));
+  if (lane_id() == 0) s_min[threadIdx.x >> 5] = best;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    float m = s_min[0];
+    for (int w = 1; w < 8; ++w) m = fminf(m, s_min[w]);
+    sep2[b] = (k > 1) ? 0.25f * m * (1.f - 1e-4f) : 3.4e38f;
+  }
+}
+
+// Certificate pass: one warp per point (four points in flight per warp), exact fp32 distance to the
+// assigned centroid against sep2.  Measured on 8 M x 128 x 1024: 0.8 ms as its own streaming pass
+// over the points, against +2.8 ms when the same arithmetic sits in the tcgen05 kernel's epilogue
+// (where it lengthens the critical path of every tile).
+__global__ void __launch_bounds__(256) km_certify(const float* __restrict__ pts, int64_t n, const float* __restrict__ cent,
+                                                  const float* __restrict__ cnorm, const float* __restrict__ sep2,
+                                                  const int32_t* __restrict__ assign, uint32_t* __restrict__ ulist,
+                                                  unsigned int* __restrict__ ucount) {
+  const int lane = threadIdx.x & 31;
+  const int64_t w0 = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  const int64_t nw = ((int64_t)gridDim.x * blockDim.x) >> 5;
+  constexpr int U = 4;
+  for (int64_t base = w0 * U; base < n; base += nw * U) {
+    int b[U];
+    float4 x[U], c4[U];
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      const int64_t r = base + u;
+      b[u] = (r < n) ? assign[r] : 0;
+      x[u] = (r < n) ? __ldg(reinterpret_cast<const float4*>(pts + (size_t)r * D) + lane) : make_float4(0.f, 0.f, 0.f, 0.f);
+    }
+#pragma unroll
+    for (int u = 0; u < U; ++u) c4[u] = __ldg(reinterpret_cast<const float4*>(cent + (size_t)b[u] * D) + lane);
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      float dp = x[u].x * x[u].x + x[u].y * x[u].y + x[u].z * x[u].z + x[u].w * x[u].w -
+                 2.f * (x[u].x * c4[u].x + x[u].y * c4[u].y + x[u].z * c4[u].z + x[u].w * c4[u].w);
+      dp = warp_sum(dp);
+      if (lane == 0 && base + u < n && !(dp + cnorm[b[u]] <= sep2[b[u]])) ulist[atomicAdd(ucount, 1u)] = (uint32_t)(base + u);
+    }
+  }
+}
+
+// fp32 re-check of the queued points: exact argmin of cnorm[j] - 2 x.c_j over ALL centroids in fp32
+// FMA arithmetic (ties -> lowest index).  When it differs from the tensor-core choice the point is
+// moved: assignment, counts and the centroid sums (exact fp32 rows) are corrected in place.
+__global__ void __launch_bounds__(256) km_recheck(const float* __restrict__ pts, const float* __restrict__ cent,
+                                                  const float* __restrict__ cnorm, int k, int32_t* __restrict__ assign,
+                                                  float* __restrict__ sums, unsigned long long* __restrict__ counts,
+                                                  const uint32_t* __restrict__ ulist, const unsigned int* __restrict__ ucount,
+                                                  unsigned int* __restrict__ changed) {
+  __shared__ __align__(16) float s_x[8][D];
+  const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
+  const unsigned int total = *ucount;
+  unsigned int w = blockIdx.x * 8 + wib;
+  const unsigned int nw = gridDim.x * 8;
+  for (; w < total; w += nw) {
+    const uint32_t row = ulist[w];
+    const float4 xv = __ldg(reinterpret_cast<const float4*>(pts + (size_t)row * D) + lane);
+    reinterpret_cast<float4*>(s_x[wib])[lane] = xv;
+    __syncwarp();
+    float best = 3.4e38f;
+    int bi = 0x7fffffff;
+    for (int j = lane; j < k; j += 32) {
+      const float4* cj = reinterpret_cast<const float4*>(cent + (size_t)j * D);
+      float dot = 0.f;
+#pragma unroll 8
+      for (int q = 0; q < D / 4; ++q) {
+        const float4 c4 = __ldg(cj + q);
+        const float4 x4 = reinterpret_cast<const float4*>(s_x[wib])[q];
+        dot = fmaf(x4.x, c4.x, dot); dot = fmaf(x4.y, c4.y, dot); dot = fmaf(x4.z, c4.z, dot); dot = fmaf(x4.w, c4.w, dot);
+      }
+      const float d = fmaf(-2.f, dot, cnorm[j]);
+      if (d < best || (d == best && j < bi)) { best = d; bi = j; }
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+      const float ob = __shfl_xor_sync(0xffffffffu, best, o);
+      const int oi = __shfl_xor_sync(0xffffffffu, bi, o);
+      if (ob < best || (ob == best && oi < bi)) { best = ob; bi = oi; }
+    }
+    const int old = assign[row];
+    if (bi != old) {
+      red_add_v4(sums + (size_t)bi * D + lane * 4, xv);
+      red_add_v4(sums + (size_t)old * D + lane * 4, make_float4(-xv.x, -xv.y, -xv.z, -xv.w));
+      if (lane == 0) {
+        assign[row] = bi;
+        atomicAdd(&counts[bi], 1ull);
+        atomicAdd(&counts[old], ~0ull);              // -1 in two's complement
+        if (changed) atomicAdd(changed, 1u);
+      }
+    }
+    __syncwarp();
   }
 }
 
@@ -697,9 +828,9 @@ int dryad_kmeans_norms(const float* centroids, int k, float* cnorm, void* stream
 // points [n,128] fp32, centroids [k,128] fp32 (k multiple of 128, <= 2048), cnorm [k].
 // Outputs: assign[n] int32; sums[k,128] and counts[k] are ACCUMULATED into (zero them per
 // iteration); inertia (optional, 1 float) accumulates sum of squared distances.
-int dryad_kmeans_assign(const float* points, int64_t n, const float* centroids, const float* cnorm, int k,
-                        int32_t* assign, float* sums, unsigned long long* counts, float* inertia,
-                        int max_ctas, void* stream) {
+static int kmeans_assign_impl(const float* points, int64_t n, const float* centroids, const float* cnorm, int k,
+                              int32_t* assign, float* sums, unsigned long long* counts, float* inertia,
+                              int max_ctas, const float* sep2, uint32_t* ulist, unsigned int* ucount, void* stream) {
   if (n < 0 || k <= 0 || k % BN != 0 || k > MAX_K) return DRYAD_ERR_BAD_ARG;
   if (n == 0) return DRYAD_OK;
   if (((uintptr_t)points & 15) || ((uintptr_t)centroids & 15) || ((uintptr_t)sums & 15)) return DRYAD_ERR_BAD_ARG;
@@ -729,8 +860,17 @@ int dryad_kmeans_assign(const float* points, int64_t n, const float* centroids, 
     attr[0].val.clusterDim.x = 2; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
     cfg.attrs = attr; cfg.numAttrs = 1;
     DRYAD_CUDA_TRY(cudaFuncSetAttribute(km_assign_pair<8>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SMEM_BYTES2));
-    DRYAD_CUDA_TRY(cudaLaunchKernelEx(&cfg, km_assign_pair<8>, mx, mc, cnorm, n, k, assign, sums, counts, inertia, dbgv));
+    const char* fenv = getenv("DRYAD_KM_FUSED_CERT");
+    const bool fused_cert = sep2 && fenv && atoi(fenv) != 0;      // certificate inside the epilogue (slower, see km_certify)
+    DRYAD_CUDA_TRY(cudaLaunchKernelEx(&cfg, km_assign_pair<8>, mx, mc, cnorm, n, k, assign, sums, counts, inertia, dbgv,
+                                      centroids, fused_cert ? sep2 : (const float*)nullptr, ulist, ucount));
     DRYAD_LAUNCH_CHECK();
+    if (sep2 && !fused_cert) {
+      int64_t cg = (n + 31) / 32;
+      if (cg > 148 * 16) cg = 148 * 16;
+      km_certify<<<(int)cg, 256, 0, (cudaStream_t)stream>>>(points, n, centroids, cnorm, sep2, assign, ulist, ucount);
+      DRYAD_LAUNCH_CHECK();
+    }
     return DRYAD_OK;
   }
   CUtensorMap mx, mc;
@@ -749,6 +889,40 @@ int dryad_kmeans_assign(const float* points, int64_t n, const float* centroids, 
   const int dbgv = dbg ? atoi(dbg) : 0;
   DRYAD_CUDA_TRY(cudaFuncSetAttribute(km_assign, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SMEM_BYTES));
   km_assign<<<grid, THREADS, SMEM_BYTES, (cudaStream_t)stream>>>(mx, mc, ms, cnorm, n, k, assign, sums, counts, inertia, dbgv);
+  DRYAD_LAUNCH_CHECK();
+  if (sep2) {                          // this kernel does not certify in its epilogue: one extra pass over the points
+    int64_t cg = (n + 31) / 32;
+    if (cg > 148 * 16) cg = 148 * 16;
+    km_certify<<<(int)cg, 256, 0, (cudaStream_t)stream>>>(points, n, centroids, cnorm, sep2, assign, ulist, ucount);
+    DRYAD_LAUNCH_CHECK();
+  }
+  return DRYAD_OK;
+}
+
+int dryad_kmeans_assign(const float* points, int64_t n, const float* centroids, const float* cnorm, int k,
+                        int32_t* assign, float* sums, unsigned long long* counts, float* inertia,
+                        int max_ctas, void* stream) {
+  return kmeans_assign_impl(points, n, centroids, cnorm, k, assign, sums, counts, inertia, max_ctas, nullptr, nullptr, nullptr, stream);
+}
+
+int dryad_kmeans_sep(const float* centroids, int k, float* sep2, void* stream) {
+  if (k <= 0) return DRYAD_ERR_BAD_ARG;
+  km_sep<<<k, 256, 0, (cudaStream_t)stream>>>(centroids, k, sep2);
+  DRYAD_LAUNCH_CHECK();
+  return DRYAD_OK;
+}
+
+int dryad_kmeans_assign_exact(const float* points, int64_t n, const float* centroids, const float* cnorm, const float* sep2,
+                              int k, int32_t* assign, float* sums, unsigned long long* counts, float* inertia,
+                              uint32_t* uncertain, unsigned int* uncertain_count, unsigned int* changed, int max_ctas,
+                              void* stream) {
+  if (!sep2 || !uncertain || !uncertain_count || n >= (1ll << 32)) return DRYAD_ERR_BAD_ARG;
+  int rc = kmeans_assign_impl(points, n, centroids, cnorm, k, assign, sums, counts, inertia, max_ctas, sep2, uncertain,
+                              uncertain_count, stream);
+  if (rc) return rc;
+  if (n == 0) return DRYAD_OK;
+  km_recheck<<<148 * 4, 256, 0, (cudaStream_t)stream>>>(points, centroids, cnorm, k, assign, sums, counts, uncertain,
+                                                       uncertain_count, changed);
   DRYAD_LAUNCH_CHECK();
   return DRYAD_OK;
 }

@@ -135,6 +135,8 @@ def _declare_kernels(lib):
     _sig(lib, "dryad_emit_ranges", c_int, [P, P, P, c_int64, P, P, P])
     _sig(lib, "dryad_kmeans_norms", c_int, [P, c_int, P, P])
     _sig(lib, "dryad_kmeans_assign", c_int, [P, c_int64, P, P, c_int, P, P, P, P, c_int, P])
+    _sig(lib, "dryad_kmeans_sep", c_int, [P, c_int, P, P])
+    _sig(lib, "dryad_kmeans_assign_exact", c_int, [P, c_int64, P, P, P, c_int, P, P, P, P, P, P, P, c_int, P])
     _sig(lib, "dryad_kmeans_update", c_int, [P, P, c_int, c_int, P, P, P, P])
     _sig(lib, "dryad_radix_sort_pairs_u64_noalloc", c_int, [P, P, P, P, c_int64, c_int, c_int, c_int,
                                                             C.POINTER(c_int), P])

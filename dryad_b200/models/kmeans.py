@@ -35,3 +35,42 @@ def reference_iteration(points: torch.Tensor, centroids: torch.Tensor, chunk: in
         counts += torch.bincount(a, minlength=k)
     new_c = torch.where(counts[:, None] > 0, sums / counts.clamp(min=1)[:, None].to(sums.dtype), centroids)
     return assign, sums, counts, new_c
+
+
+class KMeansStep:
+    """One Lloyd iteration as a DEVICE function for `apply_per_partition`: called with this
+    partition's points (column "x": [n, 128] fp32) and the current centroids (column "c": [k, 128]
+    fp32, one replica per partition), returns the new centroids (identical bits on every partition).
+    The kernels are the tcgen05 assign + certificate + fp32 re-check and the cross-GPU all-reduce of
+    parallel/kmeans.py.  With `do_while` this is BASELINE.json config 5 expressed as a query
+    (Apply loop; LinqToDryad/DryadLinqQueryable.cs:1280-1306):
+
+        step = KMeansStep(ctx)
+        cents = cents0.do_while(lambda cur: points.apply_per_partition(step, cur), cond)
+    """
+
+    device = True
+
+    def __init__(self, context, exact: bool = True):
+        self.context, self.exact = context, exact
+        self._km = None
+        self.iterations = 0
+
+    def _engine(self, k: int, n: int, dev):
+        from ..parallel.kmeans import KMeans
+        from ..parallel.symm import SymmetricArena
+        km = self._km
+        if km is None or km.k != k or km.assign.numel() < n:
+            ctx = self.context
+            arena = ctx._spmd_arena() if ctx.world > 1 else SymmetricArena(4 << 20, 0, 1, None, dev)
+            km = self._km = KMeans(arena, k, n, exact=self.exact)
+        return km
+
+    def __call__(self, points, cents):
+        x = points.cols["x"]
+        c = cents.cols["c"]
+        km = self._engine(c.shape[0], x.shape[0], x.device)
+        km.set_centroids(c.to(torch.float32))
+        km.iterate(x.contiguous())
+        self.iterations += 1
+        return {"c": km.centroids.clone()}

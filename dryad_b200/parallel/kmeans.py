@@ -19,7 +19,7 @@ D = 128
 
 
 class KMeans:
-    def __init__(self, arena: SymmetricArena, k: int, n_local_max: int, use_nvls: bool = True):
+    def __init__(self, arena: SymmetricArena, k: int, n_local_max: int, use_nvls: bool = True, exact: bool = True):
         if k % 128 or k > 2048:
             raise ValueError("k must be a multiple of 128 and at most 2048")
         self.arena, self.k = arena, k
@@ -43,11 +43,24 @@ class KMeans:
         self.total_counts = torch.zeros(k, dtype=torch.int64, device=dev)
         self.assign = torch.empty(max(n_local_max, 1), dtype=torch.int32, device=dev)
         self.inertia = torch.zeros(1, dtype=torch.float32, device=dev)
+        # fp32-exact assignments: tensor-core (TF32) choice certified per point in the assign kernel,
+        # uncertified points re-evaluated in fp32 (csrc/kernels/kmeans.cu km_recheck)
+        self.exact = exact
+        if exact:
+            self.sep2 = torch.empty(k, dtype=torch.float32, device=dev)
+            self.uncertain = torch.empty(max(n_local_max, 1), dtype=torch.int32, device=dev)
+            self.ucount = torch.zeros(2, dtype=torch.int32, device=dev)       # [queued for re-check, changed by it]
 
     def set_centroids(self, c: torch.Tensor) -> None:
         self.centroids.copy_(c)
         N.check(N.kernels().dryad_kmeans_norms(K.ptr(self.centroids), self.k, K.ptr(self.cnorm), K.stream()), "kmeans_norms")
         K._count()
+        self._refresh_sep()
+
+    def _refresh_sep(self) -> None:
+        if self.exact:
+            N.check(N.kernels().dryad_kmeans_sep(K.ptr(self.centroids), self.k, K.ptr(self.sep2), K.stream()), "kmeans_sep")
+            K._count()
 
     def iterate(self, points: torch.Tensor, max_ctas: int = 0) -> None:
         """One Lloyd iteration on this rank's shard ([n,128] fp32, contiguous).  Leaves the new
@@ -61,10 +74,18 @@ class KMeans:
         self.sums.zero_()
         self.counts.zero_()
         self.inertia.zero_()
-        N.check(lib.dryad_kmeans_assign(K.ptr(points), n, K.ptr(self.centroids), K.ptr(self.cnorm), self.k,
-                                        K.ptr(self.assign), K.ptr(self.sums), K.ptr(self.counts),
-                                        K.ptr(self.inertia), max_ctas, K.stream()), "kmeans_assign")
-        K._count()
+        if self.exact:
+            self.ucount.zero_()
+            N.check(lib.dryad_kmeans_assign_exact(K.ptr(points), n, K.ptr(self.centroids), K.ptr(self.cnorm), K.ptr(self.sep2),
+                                                  self.k, K.ptr(self.assign), K.ptr(self.sums), K.ptr(self.counts),
+                                                  K.ptr(self.inertia), K.ptr(self.uncertain), K.ptr(self.ucount),
+                                                  self.ucount.data_ptr() + 4, max_ctas, K.stream()), "kmeans_assign_exact")
+            K._count(2)
+        else:
+            N.check(lib.dryad_kmeans_assign(K.ptr(points), n, K.ptr(self.centroids), K.ptr(self.cnorm), self.k,
+                                            K.ptr(self.assign), K.ptr(self.sums), K.ptr(self.counts),
+                                            K.ptr(self.inertia), max_ctas, K.stream()), "kmeans_assign")
+            K._count()
         if self.world > 1:
             self.arena.barrier(slot=3)         # every rank's partials are complete and visible
         if self.nvls is not None:
@@ -76,6 +97,7 @@ class KMeans:
                                         K.ptr(self.centroids), K.ptr(self.cnorm), K.ptr(self.total_counts),
                                         K.stream()), "kmeans_update")
         K._count()
+        self._refresh_sep()
 
     def iterate_graph(self, points: torch.Tensor) -> None:
         """Single-GPU iterations as a CUDA graph (sub-graph vertex, runtime/graph_vertex.py): the five

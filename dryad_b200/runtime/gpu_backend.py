@@ -156,6 +156,22 @@ def _input(be: GpuBackend, node, part, inputs, env):
     return [be._columnar(p, node.schema)]
 
 
+def _apply(be, node, part, inputs, env):
+    """Apply / ApplyPerPartition with a DEVICE function: a callable marked `device = True` receives
+    the ColumnBatches of its inputs as they are (tensors in HBM) and returns a ColumnBatch or a dict
+    of tensors — user code that launches its own kernels, e.g. models.kmeans.KMeansStep.  Ordinary
+    Python functions over records take the host path (LinqToDryad/DryadLinqVertex.cs:4726-4785)."""
+    p = node.params
+    fn = p["fn"].fn
+    if not getattr(fn, "device", False) or p.get("with_index"):
+        return NotImplemented
+    args = [be._cat(payloads) for payloads in inputs]
+    out = fn(*args)
+    if isinstance(out, dict):
+        out = ColumnBatch(out)
+    return [out]
+
+
 def _select_many(be, node, part, inputs, env):
     """SelectMany(l => l.Split(c)) over the lines of a text buffer = the tokenizer kernel (K13): the
     result is a string column of views into the SAME buffer, with the tokens' key hashes."""
@@ -904,11 +920,11 @@ def _set_operation(be, node, part, inputs, env):
 
 
 # operators that understand string columns (StrColumn); the others see them only through the host path
-_STR_AWARE = {NodeType.InputTable, NodeType.OutputTable, NodeType.Dummy, NodeType.Merge, NodeType.Concat, NodeType.Tee,
+_STR_AWARE = {NodeType.Apply, NodeType.InputTable, NodeType.OutputTable, NodeType.Dummy, NodeType.Merge, NodeType.Concat, NodeType.Tee,
               NodeType.ForkBranch, NodeType.Select, NodeType.SelectMany, NodeType.GroupBy, NodeType.HashPartition}
 
 _GPU_OPS = {
-    NodeType.SelectMany: _select_many,
+    NodeType.SelectMany: _select_many, NodeType.Apply: _apply,
     NodeType.InputTable: _input, NodeType.OutputTable: _passthrough, NodeType.Dummy: _passthrough,
     NodeType.Merge: _passthrough, NodeType.Concat: _passthrough, NodeType.ForkBranch: _passthrough,
     NodeType.Tee: _tee, NodeType.Select: _select, NodeType.Where: _where, NodeType.GroupBy: _group_by,

@@ -392,6 +392,18 @@ int dryad_kmeans_assign(const float* points, int64_t n, const float* centroids, 
                         int k, int32_t* assign, float* sums, unsigned long long* counts,
                         float* inertia, int max_ctas, void* stream);
 /* All-reduce of the partials over peer-mapped memory + centroid update (no NCCL). */
+/* fp32-exact assignments.  dryad_kmeans_sep: sep2[b] = 1/4 of the squared distance from centroid b to its
+ * nearest other centroid (recompute whenever the centroids change).  dryad_kmeans_assign_exact: the
+ * tensor-core assignment, certified per point in the same kernel (exact fp32 distance to the chosen
+ * centroid <= sep2 proves it is the fp32 argmin); points without a certificate are queued in
+ * `uncertain` (capacity n, count in *uncertain_count, which the caller zeroes) and re-evaluated over
+ * all centroids in fp32 FMA arithmetic; assignment, counts and sums are corrected where the choice
+ * changes (*changed counts those, may be NULL).  n < 2^32. */
+int dryad_kmeans_sep(const float* centroids, int k, float* sep2, void* stream);
+int dryad_kmeans_assign_exact(const float* points, int64_t n, const float* centroids, const float* cnorm, const float* sep2,
+                              int k, int32_t* assign, float* sums, unsigned long long* counts, float* inertia,
+                              uint32_t* uncertain, unsigned int* uncertain_count, unsigned int* changed, int max_ctas,
+                              void* stream);
 int dryad_kmeans_update(float* const* peer_sums, unsigned long long* const* peer_counts, int world,
                         int k, float* centroids, float* cnorm, unsigned long long* total_counts,
                         void* stream);

@@ -291,3 +291,39 @@ def test_string_columns_partition_and_concat_round_trip():
     assert t.cols["w"].to_list() == ["gamma-delta-epsilon", "alpha", "z"] and t.cols["i"].tolist() == [3, 0, 249]
     c = ColumnBatch.concat([ColumnBatch({"w": back}), ColumnBatch({"w": sc})])
     assert c.n == 500 and c.cols["w"].to_list() == sc.to_list() * 2
+
+
+def test_kmeans_as_a_do_while_query_matches_the_direct_engine():
+    """BASELINE config 5 through the API: `do_while` submits one job per iteration whose body is
+    `points.apply_per_partition(KMeansStep, centroids)` — a device function on the GPU backend."""
+    from dryad_b200.models import kmeans as KM
+    from dryad_b200.parallel.kmeans import KMeans
+    from dryad_b200.parallel.symm import SymmetricArena
+    n, k, iters = 50_000, 256, 3
+    pts, centres = KM.generate(n, k, seed=4, device="cuda")
+    init = centres + 0.05
+    ctx = D.DryadLinqContext(1, device="cuda")
+    step = KM.KMeansStep(ctx)
+    points = ctx.from_columns({"x": pts})
+    cents0 = ctx.from_columns({"c": init})
+
+    class Budget:
+        device = True
+
+        def __init__(self, limit):
+            self.left = limit
+
+        def __call__(self, new_c, old_c):
+            self.left -= 1
+            return {"value": torch.tensor([self.left > 0], device=new_c.cols["c"].device)}
+    budget = Budget(iters)
+    final = cents0.do_while(lambda cur: points.apply_per_partition(step, cur),
+                            lambda cur, nxt: nxt.apply_per_partition(budget, cur))
+    got = final.to_columns()["c"]
+    assert step.iterations == iters and ctx._backend().host_fallbacks == 0
+    km = KMeans(SymmetricArena(8 << 20), k, n)
+    km.set_centroids(init)
+    for _ in range(iters):
+        km.iterate(pts)
+    torch.cuda.synchronize()
+    assert torch.allclose(got, km.centroids, rtol=1e-5, atol=1e-5)

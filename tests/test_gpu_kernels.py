@@ -220,15 +220,51 @@ def test_row_sorter_window_path_and_fallback(K):
         assert (int(res[1]) & ((1 << 64) - 1)) == terasort.key_checksum(r), variant
 
 
+@pytest.mark.parametrize("n,k,spread", [(1000, 128, 0.35), (70_001, 1024, 0.35), (60_000, 256, 3.0), (40_000, 384, 1.5)])
+def test_kmeans_assignments_equal_the_fp32_argmin(K, n, k, spread):
+    """Exact mode: the tensor-core (TF32) choice is certified per point and uncertified points are
+    re-evaluated in fp32, so every assignment equals the argmin of an fp64 reference except where
+    the two best centroids are within fp32 rounding of each other.  spread=3.0 makes the blobs
+    overlap heavily (most points fail the certificate and go through the fp32 re-check); k=384 takes
+    the one-CTA kernel with the separate certificate pass."""
+    from dryad_b200.models import kmeans as KM
+    from dryad_b200.parallel.kmeans import KMeans
+    from dryad_b200.parallel.symm import SymmetricArena
+    pts, centres = KM.generate(n, k, seed=3, device="cuda", spread=spread)
+    init = centres + 0.05 * torch.randn_like(centres)
+    km = KMeans(SymmetricArena(8 << 20), k, n)
+    km.set_centroids(init)
+    km.iterate(pts)
+    torch.cuda.synchronize()
+    a = km.assign[:n].long()
+    p64, c64 = pts.double(), init.double()
+    d = (c64 * c64).sum(1)[None, :] - 2.0 * (p64 @ c64.T)
+    top2 = d.topk(2, dim=1, largest=False).values
+    margin = (top2[:, 1] - top2[:, 0]) / ((p64 * p64).sum(1) + top2[:, 0].abs() + 1.0)
+    decided = margin > 1e-6                                  # beyond fp32 rounding of the distance itself
+    assert bool((a[decided] == d.argmin(1)[decided]).all()), int((a[decided] != d.argmin(1)[decided]).sum())
+    assert int(decided.sum()) >= n - 5
+    queued, changed = km.ucount.tolist()
+    if spread >= 3.0:
+        assert queued > n // 10                               # the re-check path really ran
+    # sums / counts follow the FINAL assignment (the re-check moves points between centroids)
+    ref_sums = torch.zeros((k, 128), dtype=torch.float64, device="cuda").index_add_(0, a, p64)
+    ref_cnt = torch.bincount(a, minlength=k)
+    assert torch.equal(km.total_counts, ref_cnt)
+    new_ref = torch.where(ref_cnt[:, None] > 0, ref_sums / ref_cnt.clamp(min=1)[:, None], c64)
+    assert torch.allclose(km.centroids.double(), new_ref, rtol=1e-4, atol=1e-4)
+
+
 @pytest.mark.parametrize("n,k", [(1000, 128), (70_001, 1024)])
 def test_kmeans_tcgen05_iteration(K, n, k):
-    """tcgen05/TMEM/TMA assign+accumulate vs an fp64 PyTorch reference of the same iteration."""
+    """tcgen05/TMEM/TMA assign+accumulate (TF32 products, no certificate) vs an fp64 PyTorch
+    reference of the same iteration."""
     from dryad_b200.models import kmeans as KM
     from dryad_b200.parallel.kmeans import KMeans
     from dryad_b200.parallel.symm import SymmetricArena
     pts, centres = KM.generate(n, k, seed=3, device="cuda")
     init = centres + 0.05 * torch.randn_like(centres)
-    km = KMeans(SymmetricArena(8 << 20), k, n)
+    km = KMeans(SymmetricArena(8 << 20), k, n, exact=False)
     km.set_centroids(init)
     km.iterate(pts)
     torch.cuda.synchronize()
