@@ -38,6 +38,33 @@ def _lam(fn, schema: Schema, nargs: int = 1) -> Lam:
     return Lam.traced(fn, schema, nargs)
 
 
+IDX = "__idx"          # symbolic GLOBAL record index in traced two-argument lambdas ((x, i) => ...)
+
+
+def _lam_indexed(fn, schema: Schema) -> Lam:
+    """(x, i) => ... : traced with the index as the column `__idx`; the GPU backend binds it to
+    rowid + the partition's start offset (device count -> scan, K16)."""
+    ir = None
+    if schema is not None and callable(fn) and all(k != "o" for k in schema.values()):
+        ir = X.trace(fn, schema, X.col(IDX, "i"))
+    return Lam(fn, ir, 2)
+
+
+def _lam_pair(fn, sa: Schema, sb: Schema) -> Lam:
+    """(a, b) => ... over two row-aligned datasets (Zip): columns are prefixed `a.` / `b.`."""
+    ir = None
+    if sa is not None and sb is not None and callable(fn) and all(k != "o" for k in list(sa.values()) + list(sb.values())):
+        def sym(schema, prefix):
+            if list(schema) == ["value"]:
+                return X.col(prefix + "value", schema["value"])
+            return X.RowProxy(schema, prefix=prefix)
+        try:
+            ir = X.normalise_traced(fn(sym(sa, "a."), sym(sb, "b.")))
+        except Exception:  # noqa: BLE001  (opaque lambda: host path)
+            ir = None
+    return Lam(fn, ir, 2)
+
+
 def _fn_from_ir(ir):
     from .types import Record
 
@@ -86,7 +113,8 @@ class Query:
 
     def select_indexed(self, fn) -> "Query":
         """Select((x, i) => …) with the GLOBAL record index."""
-        return self._new("select", schema=None, fn=Lam(fn, None, 2), indexed=True)
+        lam = _lam_indexed(fn, self.schema)
+        return self._new("select", schema=lam.out_schema(), fn=lam, indexed=True)
 
     long_select = select_indexed
 
@@ -94,7 +122,7 @@ class Query:
         return self._new("where", schema=self.schema, fn=_lam(pred, self.schema), indexed=False)
 
     def where_indexed(self, pred) -> "Query":
-        return self._new("where", schema=self.schema, fn=Lam(pred, None, 2), indexed=True)
+        return self._new("where", schema=self.schema, fn=_lam_indexed(pred, self.schema), indexed=True)
 
     long_where = where_indexed
 
@@ -155,8 +183,13 @@ class Query:
                          result=rlam, comparer=comparer)
 
     def group_join(self, inner: "Query", outer_key, inner_key, result, comparer=None) -> "Query":
-        return self._new("group_join", [inner], schema=None, outer_key=_lam(outer_key, self.schema),
-                         inner_key=_lam(inner_key, inner.schema), result=Lam(result, None, 2), comparer=comparer)
+        # (outer, group) => ... selectors that use the group only through decomposable aggregates are
+        # traced: the GPU backend then aggregates the inner side by key and probes it once per outer row
+        from ..plan.decomposition import try_decompose_group_join
+        dec = try_decompose_group_join(result, self.schema, inner.schema) if callable(result) else None
+        return self._new("group_join", [inner], schema=dec.out_schema() if dec is not None else None,
+                         outer_key=_lam(outer_key, self.schema), inner_key=_lam(inner_key, inner.schema),
+                         result=Lam(result, None, 2), comparer=comparer, gj_decomp=dec)
 
     def concat(self, other: "Query") -> "Query":
         return self._new("concat", [other], schema=self.schema if self.schema == other.schema else None)
@@ -171,7 +204,8 @@ class Query:
         return self._new("except", [other], schema=self.schema, comparer=comparer)
 
     def zip(self, other: "Query", fn) -> "Query":
-        return self._new("zip", [other], schema=None, fn=Lam(fn, None, 2))
+        lam = _lam_pair(fn, self.schema, other.schema)
+        return self._new("zip", [other], schema=lam.out_schema(), fn=lam)
 
     # ---- prefix operators ------------------------------------------------------------------
     def take(self, n: int) -> "Query":
@@ -181,16 +215,16 @@ class Query:
         return self._new("skip", schema=self.schema, n=int(n))
 
     def take_while(self, pred) -> "Query":
-        return self._new("take_while", schema=self.schema, fn=Lam(pred, None, 1), indexed=False)
+        return self._new("take_while", schema=self.schema, fn=_lam(pred, self.schema), indexed=False)
 
     def skip_while(self, pred) -> "Query":
-        return self._new("skip_while", schema=self.schema, fn=Lam(pred, None, 1), indexed=False)
+        return self._new("skip_while", schema=self.schema, fn=_lam(pred, self.schema), indexed=False)
 
     def take_while_indexed(self, pred) -> "Query":
-        return self._new("take_while", schema=self.schema, fn=Lam(pred, None, 2), indexed=True)
+        return self._new("take_while", schema=self.schema, fn=_lam_indexed(pred, self.schema), indexed=True)
 
     def skip_while_indexed(self, pred) -> "Query":
-        return self._new("skip_while", schema=self.schema, fn=Lam(pred, None, 2), indexed=True)
+        return self._new("skip_while", schema=self.schema, fn=_lam_indexed(pred, self.schema), indexed=True)
 
     long_take_while, long_skip_while = take_while_indexed, skip_while_indexed
 
@@ -243,7 +277,22 @@ class Query:
                          with_index=True)
 
     def sliding_window(self, fn, window: int) -> "Query":
-        return self._new("sliding_window", schema=None, fn=Lam(fn, None, 1), window=int(window))
+        # the window function sees a sequence of `window` records; it is traced with one symbolic
+        # record per window slot (columns w0.*, w1.*, ...), so `lambda w: sum(w)` or
+        # `lambda w: w[-1] - w[0]` become one fused kernel over shifted views of the column
+        w = int(window)
+        ir = None
+        if self.schema is not None and w > 0 and all(k != "o" for k in self.schema.values()):
+            if list(self.schema) == ["value"]:
+                syms = [X.col(f"w{j}.value", self.schema["value"]) for j in range(w)]
+            else:
+                syms = [X.RowProxy(self.schema, prefix=f"w{j}.") for j in range(w)]
+            try:
+                ir = X.normalise_traced(fn(syms))
+            except Exception:  # noqa: BLE001  (opaque lambda: host path)
+                ir = None
+        lam = Lam(fn, ir, 1)
+        return self._new("sliding_window", schema=lam.out_schema(), fn=lam, window=w)
 
     def fork(self, fn, n: int = 2) -> "MultiQuery":
         """Mapper returns a tuple of n optional values; branch i receives the non-None i-th values.
@@ -290,19 +339,19 @@ class Query:
     def _agg(self, kind: str, **params) -> "Query":
         return self._new("aggregate", schema=None, kind=kind, **params)
 
-    def count_as_query(self, pred=None): return self._agg("count", fn=Lam(pred, None, 1) if pred else None)
+    def count_as_query(self, pred=None): return self._agg("count", fn=_lam(pred, self.schema) if pred else None)
     def long_count_as_query(self, pred=None): return self.count_as_query(pred)
     def sum_as_query(self, sel=None): return self._agg("sum", fn=_lam(sel, self.schema) if sel else None)
     def min_as_query(self, sel=None): return self._agg("min", fn=_lam(sel, self.schema) if sel else None)
     def max_as_query(self, sel=None): return self._agg("max", fn=_lam(sel, self.schema) if sel else None)
     def average_as_query(self, sel=None): return self._agg("average", fn=_lam(sel, self.schema) if sel else None)
-    def any_as_query(self, pred=None): return self._agg("any", fn=Lam(pred, None, 1) if pred else None)
-    def all_as_query(self, pred): return self._agg("all", fn=Lam(pred, None, 1))
+    def any_as_query(self, pred=None): return self._agg("any", fn=_lam(pred, self.schema) if pred else None)
+    def all_as_query(self, pred): return self._agg("all", fn=_lam(pred, self.schema))
     def contains_as_query(self, value): return self._agg("contains", value=value)
-    def first_as_query(self, pred=None): return self._agg("first", fn=Lam(pred, None, 1) if pred else None, default=False)
-    def first_or_default_as_query(self, pred=None): return self._agg("first", fn=Lam(pred, None, 1) if pred else None, default=True)
-    def last_as_query(self, pred=None): return self._agg("last", fn=Lam(pred, None, 1) if pred else None, default=False)
-    def last_or_default_as_query(self, pred=None): return self._agg("last", fn=Lam(pred, None, 1) if pred else None, default=True)
+    def first_as_query(self, pred=None): return self._agg("first", fn=_lam(pred, self.schema) if pred else None, default=False)
+    def first_or_default_as_query(self, pred=None): return self._agg("first", fn=_lam(pred, self.schema) if pred else None, default=True)
+    def last_as_query(self, pred=None): return self._agg("last", fn=_lam(pred, self.schema) if pred else None, default=False)
+    def last_or_default_as_query(self, pred=None): return self._agg("last", fn=_lam(pred, self.schema) if pred else None, default=True)
     def single_as_query(self, pred=None): return self._agg("single", fn=Lam(pred, None, 1) if pred else None, default=False)
     def single_or_default_as_query(self, pred=None): return self._agg("single", fn=Lam(pred, None, 1) if pred else None, default=True)
 

@@ -215,7 +215,8 @@ def group_join(outer, inner, okey, ikey, result):
     lookup: Dict[Any, List] = {}
     for y in inner:
         lookup.setdefault(_hashable(ikey(y)), []).append(y)
-    return [result(x, list(lookup.get(_hashable(okey(x)), ()))) for x in outer]
+    # the group is an IEnumerable with the LINQ aggregates (g.count(), g.sum(sel), ...), like a GroupBy group
+    return [result(x, Grouping(okey(x), lookup.get(_hashable(okey(x)), ()))) for x in outer]
 
 
 # ---- aggregates -------------------------------------------------------------------------------

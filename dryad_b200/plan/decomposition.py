@@ -306,6 +306,30 @@ def try_decompose(fn: Callable, elem_schema: Schema, key_lam: Lam, two_arg: bool
     return DecompositionInfo(aggs, norm, key_schema)
 
 
+def try_decompose_group_join(fn: Callable, outer_schema: Schema, inner_schema: Schema) -> Optional[DecompositionInfo]:
+    """Trace a GroupJoin result selector (outer, group) => ...: outer fields appear as columns
+    `o.<name>` (`o.value` for scalars), the matching inner records only through decomposable
+    aggregates of the group.  None when the selector enumerates the group or is opaque."""
+    if outer_schema is None or inner_schema is None:
+        return None
+    if any(k == "o" for k in list(outer_schema.values()) + list(inner_schema.values())):
+        return None
+    aggs: List[AggSpec] = []
+    g = GroupProxy(inner_schema, None, aggs)
+    osym = X.col("o.value", outer_schema["value"]) if list(outer_schema) == ["value"] else X.RowProxy(outer_schema, prefix="o.")
+    try:
+        out = fn(osym, g)
+    except Exception:  # noqa: BLE001  (TraceError or anything the lambda does to a symbol)
+        return None
+    norm = X.normalise_traced(out)
+    if norm is None or not aggs:
+        return None
+    exprs = norm.values() if isinstance(norm, dict) else [norm]
+    if any(c == "key" or c.startswith("key.") for e in exprs for c in e.columns()):
+        return None
+    return DecompositionInfo(aggs, norm, None)
+
+
 def _uses_only_key(norm) -> bool:
     exprs = norm.values() if isinstance(norm, dict) else [norm]
     return all(all(c == "key" or c.startswith("key.") for c in e.columns()) for e in exprs)

@@ -358,7 +358,8 @@ class QueryGen:
         pc = outer.partition_count
         return self._node(ntype, [(outer, PW), (inner, PW)], pc, DataSetInfo(RandomPartition(pc)), e.schema,
                           outer_key=okey, inner_key=ikey, result=p["result"], algorithm=algo, broadcast=False,
-                          comparer=comparer, descending=(outer.info.order.descending if algo == "merge" else False))
+                          comparer=comparer, descending=(outer.info.order.descending if algo == "merge" else False),
+                          gj_decomp=p.get("gj_decomp"))
 
     def _visit_group_join(self, e: QExpr):
         return self._visit_join(e, NodeType.GroupJoin)

@@ -84,6 +84,21 @@ class JobExecutor:
                     return [[self.out[child.uid][i - acc][0]]]
                 acc += child.partition_count
         if t == NodeType.Zip:
+            lp = [p[0] for p in self.out[node.children[0][0].uid]]
+            rp = [p[0] for p in self.out[node.children[1][0].uid]]
+            if all(hasattr(b, "cols") and not b.is_rows for b in lp + rp):
+                # columnar re-alignment: slices of the right side's partitions, no records
+                from .columnar import ColumnBatch
+                start = sum(b.n for b in lp[:i])
+                need = lp[i].n
+                segs, pos = [], 0
+                for b in rp:
+                    lo, hi = max(start, pos), min(start + need, pos + b.n)
+                    if lo < hi:
+                        segs.append(b.slice(lo - pos, hi - pos))
+                    pos += b.n
+                right = ColumnBatch.concat(segs) if segs else rp[0].slice(0, 0)
+                return [[lp[i]], [right]]
             tr = self.backend.to_records
             left = [[tr(p[0])] for p in self.out[node.children[0][0].uid]]
             right = [[tr(p[0])] for p in self.out[node.children[1][0].uid]]
@@ -100,6 +115,19 @@ class JobExecutor:
             return [[left[i][0]], [flat]]
         if t == NodeType.SlidingWindow:
             w = (node.members[0] if node.type == NodeType.Super else node).params["window"]
+            cb = [p[0] for p in self.out[node.children[0][0].uid]]
+            if all(hasattr(b, "cols") and not b.is_rows for b in cb):
+                # columnar halo: the last w-1 rows that precede partition i, as slices
+                from .columnar import ColumnBatch
+                parts_h, have, s = [], 0, i - 1
+                while s >= 0 and have < w - 1:
+                    take = min(cb[s].n, (w - 1) - have)
+                    if take:
+                        parts_h.insert(0, cb[s].slice(cb[s].n - take, cb[s].n))
+                        have += take
+                    s -= 1
+                ins.append([ColumnBatch.concat(parts_h) if parts_h else cb[i].slice(0, 0)])
+                return ins
             co = [[self.backend.to_records(p[0])] for p in self.out[node.children[0][0].uid]]
             halo: List = []
             s = i - 1

@@ -215,6 +215,134 @@ def _tee(be, node, part, inputs, env):
     return [b for _ in range(node.n_out_ports)] if node.params.get("replicate") else [b]
 
 
+IDX = "__idx"
+
+
+def _start_offset(be, inputs) -> int:
+    """Global index of this partition's first record: the side input of an indexed operator, produced
+    by the count -> exclusive scan stage (K16; LinqToDryad/DryadLinqQueryGen.cs:1225-1248)."""
+    if len(inputs) < 2:
+        return 0
+    side = be._cat(inputs[1])
+    return int(side.cols["value"][0].item()) if side.n else 0
+
+
+def _bind_index(proj: Dict[str, Any], start: int) -> Dict[str, Any]:
+    """Replace the symbolic global index of a traced (x, i) lambda by rowid + partition start."""
+    gi = X.rowid() + X.lit(int(start))
+    return {k: X.wrap(e).substitute({IDX: gi}) for k, e in proj.items()}
+
+
+def _offsets(be, node, part, inputs, env):
+    """Per-partition counts -> exclusive scan -> one start offset per consumer partition (K16)."""
+    src = be._cat(inputs[0])
+    n = node.params["nports"]
+    if "value" not in src.cols or src.cols["value"].dtype != torch.int64:
+        return NotImplemented
+    counts = torch.zeros(n, dtype=torch.int64, device=be.device)
+    counts[:min(n, src.n)] = src.cols["value"][:n]
+    offs, _tot = K.exclusive_scan_i64(counts)
+    return [ColumnBatch({"value": offs[i:i + 1]}, 1) for i in range(n)]
+
+
+def _first_false(be, src: ColumnBatch, pred) -> int:
+    """Index of the first row for which the predicate is false (src.n when none): one generated
+    kernel computes min(rowid where !pred) — no flag column, no scan."""
+    if src.n == 0:
+        return 0
+    big = (1 << 62)
+    out, _ = run_on_gpu({"p": X.where(pred, X.lit(big), X.rowid())}, src.cols, src.n, reduce={"p": "min"})
+    v = int(out["p"].item())
+    return src.n if v >= big else v
+
+
+def _partition_op(be, node, part, inputs, env):
+    """Take / Skip / TakeWhile / SkipWhile on columns (LinqToDryad/DryadLinqVertex.cs:222-289)."""
+    p = node.params
+    src = be._cat(inputs[0])
+    op = p["op"]
+    if op == "take":
+        return [src.slice(0, max(0, int(p["n"])))]
+    if op == "skip":
+        return [src.slice(min(src.n, max(0, int(p["n"]))), src.n)]
+    lam = p["fn"]
+    if src.is_rows or src.has_strings or not isinstance(lam.ir, X.Expr):
+        return NotImplemented
+    pred = lam.ir
+    if p.get("indexed"):
+        pred = _bind_index({"p": pred}, 0)["p"]          # stage 2 runs on ONE partition: index = rowid
+    cut = _first_false(be, src, pred)
+    return [src.slice(0, cut)] if op == "take_while" else [src.slice(cut, src.n)]
+
+
+def _reverse(be, node, part, inputs, env):
+    src = be._cat(inputs[0])
+    if src.n <= 1:
+        return [src]
+    idx = torch.arange(src.n - 1, -1, -1, dtype=torch.int32, device=be.device)
+    return [src.take(idx)]
+
+
+def _zip(be, node, part, inputs, env):
+    """Zip over row-aligned partitions (the executor re-aligns the right side to the left side's
+    boundaries, LinqToDryad/DryadLinqQueryGen.cs:2626-2717): one fused kernel over both column sets."""
+    ir = node.params["fn"].ir
+    proj = ir if isinstance(ir, dict) else ({"value": ir} if isinstance(ir, X.Expr) else None)
+    if proj is None:
+        return NotImplemented
+    a, b = be._cat(inputs[0]), be._cat(inputs[1])
+    if a.is_rows or b.is_rows or a.has_strings or b.has_strings:
+        return NotImplemented
+    n = min(a.n, b.n)
+    cols = {("a." + k): v[:n].contiguous() for k, v in a.cols.items()}
+    cols.update({("b." + k): v[:n].contiguous() for k, v in b.cols.items()})
+    if n == 0:
+        dt = {"i": torch.int64, "f": torch.float64, "b": torch.bool}
+        return [ColumnBatch({k: torch.empty(0, dtype=dt[X.wrap(e).kind], device=be.device) for k, e in proj.items()}, 0,
+                            tuple_like=_tuple_cls(ir))]
+    out, _ = run_on_gpu(proj, cols, n)
+    return [ColumnBatch(out, n, tuple_like=_tuple_cls(ir))]
+
+
+def _sliding_window(be, node, part, inputs, env):
+    """SlidingWindow (LinqToDryad/DryadLinqQueryGen.cs:3234-3293): inputs[1] is the halo — the w-1
+    records preceding this partition, delivered by the neighbour (C6).  Window slot j of output row i
+    is row i + j of (halo ++ partition): w shifted VIEWS of each column feed one fused kernel."""
+    p = node.params
+    w = int(p["window"])
+    ir = p["fn"].ir
+    proj = ir if isinstance(ir, dict) else ({"value": ir} if isinstance(ir, X.Expr) else None)
+    if proj is None or w < 1:
+        return NotImplemented
+    own = be._cat(inputs[0])
+    halo = be._cat(inputs[1]) if len(inputs) > 1 and inputs[1] else None
+    if own.is_rows or own.has_strings or (halo is not None and not isinstance(halo, ColumnBatch)):
+        return NotImplemented
+    data = ColumnBatch.concat([halo, own]) if (halo is not None and halo.n) else own
+    n_out = max(0, data.n - w + 1)
+    dt = {"i": torch.int64, "f": torch.float64, "b": torch.bool}
+    if n_out == 0:
+        return [ColumnBatch({k: torch.empty(0, dtype=dt[X.wrap(e).kind], device=be.device) for k, e in proj.items()}, 0,
+                            tuple_like=_tuple_cls(ir))]
+    cols = {}
+    for j in range(w):
+        for k, v in data.cols.items():
+            cols[f"w{j}.{k}"] = v[j:j + n_out]
+    out, _ = run_on_gpu(proj, cols, n_out)
+    return [ColumnBatch(out, n_out, tuple_like=_tuple_cls(ir))]
+
+
+def _contains(be, node, part, inputs, env):
+    src = be._cat(inputs[0])
+    v = node.params["value"]
+    if list(src.cols) != ["value"] or src.has_strings or isinstance(v, (str, bytes)) or not isinstance(v, (int, float, bool)):
+        return NotImplemented
+    if src.n == 0:
+        return [ColumnBatch({"value": torch.zeros(1, dtype=torch.bool, device=be.device)}, 1)]
+    out, _ = run_on_gpu({"h": X.where(X.col("value", src.schema["value"]) == X.lit(v), 1, 0)}, src.cols, src.n, reduce={"h": "max"})
+    return [ColumnBatch({"value": out["h"].reshape(1) > 0}, 1)]
+
+
 def _proj_of(lam):
     if isinstance(lam.ir, X.Expr):
         return {"value": lam.ir}
@@ -244,11 +372,15 @@ def _select(be, node, part, inputs, env):
         return [ColumnBatch({k: (passed[k] if k in passed else out[k]) for k in proj}, src.n, tuple_like=_tuple_cls(res))]
     if src.has_strings:
         return NotImplemented
-    if p["indexed"]:
-        return NotImplemented
     proj = _proj_of(p["fn"])
     if proj is None:
         return NotImplemented
+    if p["indexed"]:
+        proj = _bind_index(proj, _start_offset(be, inputs))
+    if src.n == 0:
+        dt = {"i": torch.int64, "f": torch.float64, "b": torch.bool}
+        return [ColumnBatch({k: torch.empty(0, dtype=dt[X.wrap(e).kind], device=be.device) for k, e in proj.items()}, 0,
+                            tuple_like=_tuple_cls(p["fn"].ir))]
     out, _ = run_on_gpu(proj, src.cols, src.n)
     return [ColumnBatch(out, src.n, tuple_like=_tuple_cls(p["fn"].ir))]
 
@@ -256,11 +388,14 @@ def _select(be, node, part, inputs, env):
 def _where(be, node, part, inputs, env):
     p = node.params
     src = be._cat(inputs[0])
-    if p["indexed"] or not isinstance(p["fn"].ir, X.Expr) or src.is_rows:
+    if not isinstance(p["fn"].ir, X.Expr) or src.is_rows:
         return NotImplemented
     if src.n == 0:
         return [src]
-    _, flags = run_on_gpu({}, src.cols, src.n, predicate=p["fn"].ir)
+    pred = p["fn"].ir
+    if p["indexed"]:
+        pred = _bind_index({"p": pred}, _start_offset(be, inputs))["p"]
+    _, flags = run_on_gpu({}, src.cols, src.n, predicate=pred)
     idx, m = K.compact_flags(flags)
     return [src.take(idx)]
 
@@ -748,51 +883,128 @@ def _order_by(be, node, part, inputs, env):
     return [src.take(idx)]
 
 
+def _checked_sum_i64(col: torch.Tensor) -> int:
+    """Exact Sum of an int64 column with C# checked-arithmetic semantics (LinqToDryad/
+    DryadLinqDecomposition.cs:312-315): the low and high 32-bit halves are summed separately in ONE
+    generated kernel (neither partial sum can wrap for n < 2^31), recombined as an exact integer on
+    the host, and an OverflowException is raised when the result leaves the int64 range."""
+    n = col.numel()
+    if n == 0:
+        return 0
+    if n >= (1 << 31):
+        raise CompileError("column too long for the split checked sum")
+    c = X.col("v", "i")
+    out, _ = run_on_gpu({"lo": c & X.lit(0xFFFFFFFF), "hi": c >> X.lit(32)}, {"v": col.contiguous()}, n,
+                        reduce={"lo": "sum", "hi": "sum"})
+    total = (int(out["hi"].item()) << 32) + int(out["lo"].item())
+    if not -(1 << 63) <= total < (1 << 63):
+        raise DryadLinqException(ErrorCode.FailureInOperator, "Arithmetic operation resulted in an overflow.")
+    return total
+
+
+def _scalar(be, v, dtype) -> ColumnBatch:
+    return ColumnBatch({"value": torch.tensor([v], dtype=dtype, device=be.device)}, 1)
+
+
 def _basic_aggregate(be, node, part, inputs, env):
+    """Scalar aggregates on columns (K11; LinqToDryad/DryadLinqVertex.cs:1673-4704): stage 1 reduces
+    a partition to one partial, stage 2 combines the partials of all partitions."""
     p = node.params
     kind, stage = p["kind"], p["stage"]
-    if kind not in ("count", "sum", "min", "max"):
+    if kind not in ("count", "sum", "min", "max", "average", "any", "all", "first", "last", "any_true"):
         return NotImplemented
     src = be._cat(inputs[0])
     if src.is_rows:
         if kind == "count" and stage == 1 and p.get("fn") is None:
-            return [ColumnBatch({"value": torch.tensor([src.n], dtype=torch.int64, device=be.device)}, 1)]
+            return [_scalar(be, src.n, torch.int64)]
+        return NotImplemented
+    if src.has_strings:
         return NotImplemented
     fn = p.get("fn")
+    if fn is not None and not isinstance(fn.ir, X.Expr):
+        return NotImplemented
+    if kind == "any_true":                                  # stage 2 of Contains
+        if "value" not in src.cols:
+            return NotImplemented
+        return [_scalar(be, bool(src.n and bool(src.cols["value"].any().item())), torch.bool)]
     if stage == 1:
-        if kind == "count":
-            if fn is not None:
-                return NotImplemented
-            return [ColumnBatch({"value": torch.tensor([src.n], dtype=torch.int64, device=be.device)}, 1)]
+        n = src.n
+        if kind in ("count", "any", "all"):
+            if fn is None:
+                hits = n
+            elif n == 0:
+                hits = 0
+            else:
+                _, cnt = run_on_gpu({}, src.cols, n, predicate=fn.ir, count_flags=True)
+                hits = int(cnt.item())
+            if kind == "count":
+                return [_scalar(be, hits, torch.int64)]
+            return [_scalar(be, hits > 0 if kind == "any" else hits == n, torch.bool)]
+        if kind in ("first", "last"):
+            if n == 0:
+                return [src]
+            if fn is None:
+                return [src.slice(0, 1) if kind == "first" else src.slice(n - 1, n)]
+            big = 1 << 62
+            if kind == "first":
+                out, _ = run_on_gpu({"p": X.where(fn.ir, X.rowid(), X.lit(big))}, src.cols, n, reduce={"p": "min"})
+                i = int(out["p"].item())
+                return [src.slice(i, i + 1) if i < big else src.slice(0, 0)]
+            out, _ = run_on_gpu({"p": X.where(fn.ir, X.rowid(), X.lit(-1))}, src.cols, n, reduce={"p": "max"})
+            i = int(out["p"].item())
+            return [src.slice(i, i + 1) if i >= 0 else src.slice(0, 0)]
+        # sum / min / max / average over a value column or a traced selector
         if fn is not None:
-            if not isinstance(fn.ir, X.Expr):
-                return NotImplemented
-            out, _ = run_on_gpu({"v": fn.ir}, src.cols, src.n) if src.n else ({"v": torch.empty(0, dtype=torch.int64, device=be.device)}, None)
+            out, _ = run_on_gpu({"v": fn.ir}, src.cols, n) if n else ({"v": torch.empty(0, dtype=torch.int64, device=be.device)}, None)
             col = out["v"]
         else:
             if "value" not in src.cols:
                 return NotImplemented
             col = src.cols["value"]
-        if src.n == 0:
+        if col.dtype == torch.bool:
+            return NotImplemented
+        if n == 0:
             if kind == "sum":
                 return [ColumnBatch({"value": torch.zeros(1, dtype=col.dtype, device=be.device)}, 1)]
             return [ColumnBatch({"value": col[:0]}, 0)]
-        if kind == "sum" and col.dtype == torch.int64:
-            # checked arithmetic: detect overflow with a float shadow sum
-            approx = float(col.to(torch.float64).sum().item())
-            if abs(approx) > 9.2e18:
-                raise DryadLinqException(ErrorCode.FailureInOperator, "Arithmetic operation resulted in an overflow.")
-        return [ColumnBatch({"value": K.reduce(col.contiguous(), kind)}, 1)]
-    # stage 2 over the per-partition partials
+        if kind in ("sum", "average"):
+            tot = _checked_sum_i64(col) if col.dtype == torch.int64 else K.reduce(col.contiguous(), "sum")
+            if kind == "sum":
+                return [_scalar(be, tot, torch.int64) if col.dtype == torch.int64 else ColumnBatch({"value": tot.reshape(1)}, 1)]
+            pair = ColumnBatch({"item1": torch.tensor([tot], dtype=torch.int64, device=be.device) if col.dtype == torch.int64 else tot.reshape(1),
+                                "item2": torch.tensor([n], dtype=torch.int64, device=be.device)}, 1, tuple_like=True)
+            return [pair]
+        return [ColumnBatch({"value": K.reduce(col.contiguous(), kind).reshape(1)}, 1)]
+    # ---- stage 2 over the per-partition partials --------------------------------------------------
+    if kind in ("first", "last"):
+        if src.n == 0:
+            return NotImplemented                              # default / typed "no elements" error: host
+        return [src.slice(0, 1) if kind == "first" else src.slice(src.n - 1, src.n)]
+    if kind == "average":
+        if src.n == 0 or "item1" not in src.cols:
+            return NotImplemented
+        s_col, c_col = src.cols["item1"], src.cols["item2"]
+        cnt = int(K.reduce(c_col.contiguous(), "sum").item())
+        if cnt == 0:
+            return NotImplemented
+        tot = _checked_sum_i64(s_col) if s_col.dtype == torch.int64 else float(K.reduce(s_col.contiguous(), "sum").item())
+        return [_scalar(be, tot / cnt, torch.float64)]
     if "value" not in src.cols:
         return NotImplemented
     col = src.cols["value"]
+    if kind in ("any", "all"):
+        if src.n == 0:
+            return [_scalar(be, kind == "all", torch.bool)]
+        v = bool(col.any().item()) if kind == "any" else bool(col.all().item())
+        return [_scalar(be, v, torch.bool)]
     if src.n == 0:
         if kind in ("count", "sum"):
-            return [ColumnBatch({"value": torch.zeros(1, dtype=torch.int64, device=be.device)}, 1)]
+            return [_scalar(be, 0, torch.int64)]
         return NotImplemented          # host raises the typed "no elements" error
+    if kind in ("count", "sum") and col.dtype == torch.int64:
+        return [_scalar(be, _checked_sum_i64(col), torch.int64)]
     op = "sum" if kind in ("count", "sum") else kind
-    return [ColumnBatch({"value": K.reduce(col.contiguous(), op)}, 1)]
+    return [ColumnBatch({"value": K.reduce(col.contiguous(), op).reshape(1)}, 1)]
 
 
 def _join(be, node, part, inputs, env):
@@ -840,6 +1052,86 @@ def _join(be, node, part, inputs, env):
         dt = {"i": torch.int64, "f": torch.float64, "b": torch.bool}
         out = {k: torch.empty(0, dtype=dt[e.kind], device=be.device) for k, e in proj.items()}
     return [ColumnBatch(out, op.numel(), tuple_like=_tuple_cls(res))]
+
+
+def _group_join(be, node, part, inputs, env):
+    """GroupJoin whose result selector uses the group through decomposable aggregates
+    (ParallelHashGroupJoin, LinqToDryad/DryadLinqVertex.cs:7316-7761): the inner side is aggregated
+    by key in the hash-aggregate table, every outer row probes the group table once, and the selector
+    runs as one fused kernel over the outer columns and the gathered aggregates.  Outer rows without
+    a match see the empty group (Count 0, Sum 0)."""
+    p = node.params
+    dec = p.get("gj_decomp")
+    if dec is None or p.get("comparer") is not None or p.get("algorithm") == "merge":
+        return NotImplemented
+    lanes = dec.gpu_lanes()
+    if lanes is None or len(lanes) >= 8:
+        return NotImplemented
+    outer, inner = be._cat(inputs[0]), be._cat(inputs[1])
+    if outer.is_rows or inner.is_rows or outer.has_strings or inner.has_strings:
+        return NotImplemented
+    if not isinstance(p["outer_key"].ir, X.Expr) or not isinstance(p["inner_key"].ir, X.Expr) or \
+            p["outer_key"].ir.kind != p["inner_key"].ir.kind:
+        return NotImplemented
+    ok, ik = _key_column(outer, p["outer_key"]), _key_column(inner, p["inner_key"])
+    if ok is None or ik is None or _has_reserved_key(ok, ik):
+        return NotImplemented
+    res = dec.result
+    kinds = [a.out_kind for a in dec.aggs]
+    proj = {k: _bind_leaves(e, kinds) for k, e in res.items()} if isinstance(res, dict) else {"value": _bind_leaves(res, kinds)}
+    dt = {"i": torch.int64, "f": torch.float64, "b": torch.bool}
+    if outer.n == 0:
+        return [ColumnBatch({k: torch.empty(0, dtype=dt[e.kind], device=be.device) for k, e in proj.items()}, 0,
+                            tuple_like=_tuple_cls(res))]
+    # 1. aggregate the inner side by key
+    sel_proj = {}
+    for i, a in enumerate(dec.aggs):
+        if a.kind != "count":
+            sel = a.selector.ir if a.selector is not None else None
+            if not isinstance(sel, X.Expr):
+                return NotImplemented
+            sel_proj[f"__v{i}"] = sel
+    empty_ok = all(a.kind in ("count", "sum") for a in dec.aggs)
+    cols = {("o." + k): v for k, v in outer.cols.items()}
+    if inner.n:
+        vals = run_on_gpu(sel_proj, inner.cols, inner.n)[0] if sel_proj else {}
+        in_views = []
+        for i, a in enumerate(dec.aggs):
+            if a.kind == "count":
+                in_views.append(None)
+            else:
+                c = vals[f"__v{i}"]
+                in_views.append((c.view(torch.int64) if c.dtype == torch.float64 else c.to(torch.int64)).contiguous())
+        tbl = K.HashAggTable(max(1024, 2 * inner.n + 64), lanes, be.device)
+        try:
+            tbl.update(ik.contiguous(), in_views)
+            gk, gl = tbl.extract()
+        except OverflowError as ex:
+            raise DryadLinqException(ErrorCode.FailureInHashGroupBy, "Arithmetic operation resulted in an overflow.") from ex
+        # 2. one probe per outer row, 3. gather the group's aggregates (identity where unmatched)
+        jt = K.JoinTable(gk.contiguous())
+        rows = torch.empty(outer.n, dtype=torch.int32, device=be.device)
+        matched = torch.empty(outer.n, dtype=torch.uint8, device=be.device)
+        K.N.check(K.N.kernels().dryad_join_probe_unique(K.ptr(jt.keys), K.ptr(jt.head), jt.cap, K.ptr(ok.contiguous()), outer.n,
+                                                        K.ptr(rows), K.ptr(matched), K.stream()), "join_probe_unique")
+        K._count()
+        if not empty_ok and not bool(matched.all().item()):
+            return NotImplemented                             # Min/Max/Average of an empty group: host semantics
+        rows = rows.clamp_(min=0)
+        m64 = matched.to(torch.int64)
+        for i, ln in enumerate(lanes):
+            lane = K.gather_rows(gl[i].contiguous(), rows)
+            if ln.endswith("f64"):
+                cols[f"agg{i}"] = lane.view(torch.float64) * matched.to(torch.float64)
+            else:
+                cols[f"agg{i}"] = lane * m64
+    else:
+        if not empty_ok:
+            return NotImplemented
+        for i, ln in enumerate(lanes):
+            cols[f"agg{i}"] = torch.zeros(outer.n, dtype=torch.float64 if ln.endswith("f64") else torch.int64, device=be.device)
+    out, _ = run_on_gpu(proj, cols, outer.n)
+    return [ColumnBatch(out, outer.n, tuple_like=_tuple_cls(res))]
 
 
 def _join_fused(be, jt, outer: ColumnBatch, inner: ColumnBatch, ok: torch.Tensor, res):
@@ -924,12 +1216,13 @@ _STR_AWARE = {NodeType.Apply, NodeType.InputTable, NodeType.OutputTable, NodeTyp
               NodeType.ForkBranch, NodeType.Select, NodeType.SelectMany, NodeType.GroupBy, NodeType.HashPartition}
 
 _GPU_OPS = {
-    NodeType.SelectMany: _select_many, NodeType.Apply: _apply,
+    NodeType.SelectMany: _select_many, NodeType.Apply: _apply, NodeType.Offsets: _offsets, NodeType.PartitionOp: _partition_op,
+    NodeType.Reverse: _reverse, NodeType.Zip: _zip, NodeType.Contains: _contains, NodeType.SlidingWindow: _sliding_window,
     NodeType.InputTable: _input, NodeType.OutputTable: _passthrough, NodeType.Dummy: _passthrough,
     NodeType.Merge: _passthrough, NodeType.Concat: _passthrough, NodeType.ForkBranch: _passthrough,
     NodeType.Tee: _tee, NodeType.Select: _select, NodeType.Where: _where, NodeType.GroupBy: _group_by,
     NodeType.HashPartition: _hash_partition, NodeType.RangePartition: _range_partition,
     NodeType.Sampler: _sampler, NodeType.RangeSampler: _range_sampler, NodeType.OrderBy: _order_by,
-    NodeType.BasicAggregate: _basic_aggregate, NodeType.Join: _join, NodeType.Distinct: _distinct,
+    NodeType.BasicAggregate: _basic_aggregate, NodeType.Join: _join, NodeType.GroupJoin: _group_join, NodeType.Distinct: _distinct,
     NodeType.SetOperation: _set_operation,
 }

@@ -364,6 +364,49 @@ class SpmdExecutor(JobExecutor):
             res.append(ColumnBatch(d, sz[r], tuple_like))
         return res
 
+    def _halo_p2p(self, own: ColumnBatch, w: int, schema) -> Optional[ColumnBatch]:
+        """C6 neighbour shift over NVLink: every rank stores the last w-1 rows of its partition into
+        the NEXT rank's halo slot in the symmetric arena (plain P2P stores), one device barrier, and
+        the receiver reads its slot locally.  Applies when every partition holds at least w-1 rows
+        (otherwise a halo spans several ranks and the all-gather form is used).  GPU backend only."""
+        if getattr(self.backend, "name", "") != "gpu" or own.device.type != "cuda":
+            return None
+        dev = self.backend.device
+        nmin = torch.tensor([own.n], dtype=torch.int64, device=dev)
+        dist.all_reduce(nmin, op=dist.ReduceOp.MIN)
+        if int(nmin.item()) < w - 1:
+            return None
+        from ..parallel.symm import tensor_from_ptr
+        ctx = self.context
+        arena = ctx._spmd_arena()
+        names = list(schema)
+        cache = ctx.__dict__.setdefault("_halo_cache", {})
+        sig = (len(names), w)
+        slot = cache.get(sig)
+        if slot is None:
+            buf, off = arena.alloc((len(names), w - 1), torch.int64)
+            slot = cache[sig] = (buf, off)
+        buf, off = slot
+        h = w - 1
+        arena.barrier(slot=2)                          # the neighbour has consumed its previous halo
+        if self.rank + 1 < self.world:
+            for c, k in enumerate(names):
+                v = own.cols[k][own.n - h:]
+                wire = v.view(torch.int64) if v.dtype == torch.float64 else v.to(torch.int64)
+                dst = tensor_from_ptr(arena.peer_ptr(self.rank + 1, off + c * h * 8), h * 8, dev).view(torch.int64)
+                dst.copy_(wire, non_blocking=True)
+        arena.barrier(slot=3)                          # every halo has landed
+        self.p2p_halos = getattr(self, "p2p_halos", 0) + 1
+        ctx.__dict__["last_p2p_halos"] = self.p2p_halos
+        if self.rank == 0:
+            return own.slice(0, 0)
+        cols = {}
+        for c, k in enumerate(names):
+            raw = buf[c].clone()
+            kind = schema[k]
+            cols[k] = raw.view(torch.float64) if kind == "f" else (raw != 0 if kind == "b" else raw)
+        return ColumnBatch(cols, h, getattr(own, "tuple_like", False))
+
     def _gather_to_zero(self, child) -> Optional[List]:
         local = self.out[child.uid][self.rank]
         payload = local[0] if local is not None else None
@@ -389,6 +432,9 @@ class SpmdExecutor(JobExecutor):
             child = node.children[0][0]
             own = self.out[child.uid][self.rank][0]
             if w > 1 and self._all_columnar([own], child.schema):
+                halo_p2p = self._halo_p2p(own, w, child.schema)
+                if halo_p2p is not None:
+                    return [[own], [halo_p2p]]
                 tail = own.slice(max(0, own.n - (w - 1)), own.n)
                 tails = self._allgather_batches(tail, child.schema, getattr(own, "tuple_like", False))
                 halo_parts: List[ColumnBatch] = []

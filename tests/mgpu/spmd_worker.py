@@ -366,6 +366,14 @@ def gpu_checks(rank, world):
     dist.all_reduce(tot_hp)
     assert int(tot_hp.item()) == nrec * world
 
+    # sliding window on columns: the w-1 boundary rows move as one P2P neighbour write into the arena
+    seq = torch.arange(1000 * rank, 1000 * rank + 1000, dtype=torch.int64)
+    win = ctx.from_columns({"value": seq}).sliding_window(lambda w_: w_[0] + w_[1] + w_[2], 3).to_columns()["value"].cpu()
+    lo = 1000 * rank - (2 if rank > 0 else 0)
+    full = torch.arange(lo, 1000 * rank + 1000, dtype=torch.int64)
+    assert torch.equal(win, full[:-2] + full[1:-1] + full[2:]), (rank, win[:4])
+    assert ctx.__dict__.get("last_p2p_halos", 0) >= 1 and ctx.last_object_collectives == 0 and be.host_fallbacks == 0
+
     # 5a. dimension join through the API: the planner picks the broadcast join (small inner side), the
     #     SPMD executor runs it as BroadcastJoin + generated probe; no object collectives
     nd = 3000                                            # dimension rows in total, sliced over the ranks

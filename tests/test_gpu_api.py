@@ -327,3 +327,84 @@ def test_kmeans_as_a_do_while_query_matches_the_direct_engine():
         km.iterate(pts)
     torch.cuda.synchronize()
     assert torch.allclose(got, km.centroids, rtol=1e-5, atol=1e-5)
+
+
+def _same_order(build, data, parts=(1, 3)):
+    """Exact (ordered) agreement with the LocalDebug oracle; returns the last GPU context."""
+    ld = D.DryadLinqContext(1, local_debug=True)
+    want = build(ld.from_enumerable(data, 1)).to_list()
+    for p in parts:
+        ctx = D.DryadLinqContext(p, device="cuda")
+        got = build(ctx.from_enumerable(data, p)).to_list()
+        assert got == want, f"partitions={p}: {got[:8]} vs {want[:8]}"
+        assert ctx._backend().host_fallbacks == 0, f"partitions={p}: {ctx._backend().host_fallbacks} host fallbacks"
+    return ctx
+
+
+def test_order_dependent_operators_run_on_the_gpu():
+    """Global index (count -> scan -> offsets, K16), Take/Skip(While), Reverse and Zip on columns."""
+    data = [(i * 7919) % 5003 for i in range(4001)]
+    _same_order(lambda q: q.select_indexed(lambda x, i: x * 2 + i), data)
+    _same_order(lambda q: q.where_indexed(lambda x, i: (x + i) % 3 == 0), data)
+    _same_order(lambda q: q.take(37), data)
+    _same_order(lambda q: q.skip(3950), data)
+    _same_order(lambda q: q.take_while(lambda x: x != 2500), data)
+    _same_order(lambda q: q.skip_while(lambda x: x != 2500), data)
+    _same_order(lambda q: q.take_while_indexed(lambda x, i: i < 1234), data)
+    _same_order(lambda q: q.reverse(), data)
+    _same_order(lambda q: q.zip(q.select(lambda x: x * 3), lambda a, b: a + b), data)
+    recs = [{"k": i % 11, "v": i} for i in range(3000)]
+    _same_order(lambda q: q.zip(q.select(lambda r: r.v + 1), lambda r, w: {"k": r.k, "s": r.v + w}), recs)
+
+
+def test_scalar_aggregates_run_on_the_gpu_and_sum_is_checked_exactly():
+    data = [(i * 104729) % 100003 - 50000 for i in range(6000)]
+    for build in (lambda q: q.sum_as_query(), lambda q: q.average_as_query(), lambda q: q.min_as_query(),
+                  lambda q: q.max_as_query(), lambda q: q.count_as_query(lambda x: x % 7 == 0),
+                  lambda q: q.any_as_query(lambda x: x == data[4321]), lambda q: q.any_as_query(lambda x: x > 10**9),
+                  lambda q: q.all_as_query(lambda x: x > -60000), lambda q: q.all_as_query(lambda x: x > 0),
+                  lambda q: q.first_as_query(), lambda q: q.last_as_query(),
+                  lambda q: q.first_as_query(lambda x: x % 1000 == 0), lambda q: q.last_as_query(lambda x: x % 1000 == 0),
+                  lambda q: q.contains_as_query(data[17]), lambda q: q.contains_as_query(123456789),
+                  lambda q: q.select(lambda x: x * 0.5).average_as_query()):
+        _same_order(build, data)
+    # checked arithmetic is exact at the int64 boundary (no float shadow)
+    top = (1 << 63) - 1
+    ctx = D.DryadLinqContext(2, device="cuda")
+    assert ctx.from_enumerable([top - 5, 2, 3], 2).sum_as_query().to_list() == [top]
+    with pytest.raises(D.DryadLinqException):
+        ctx.from_enumerable([top - 5, 2, 4], 2).sum_as_query().to_list()
+    with pytest.raises(D.DryadLinqException):
+        ctx.from_enumerable([-(1 << 63), -1], 1).sum_as_query().to_list()
+    assert ctx.from_enumerable([1 << 62, 1 << 62, -(1 << 62), -(1 << 62), 7], 2).sum_as_query().to_list() == [7]
+
+
+def test_float_zero_keys_and_mixed_key_kinds_agree_with_the_oracle():
+    """-0.0 and 0.0 are one key; a float outer key joined with an int inner key compares values."""
+    vals = [0.0, -0.0, 1.5, -0.0, 0.0, 1.5, 2.0]
+    _both(lambda q: q.group_by(lambda x: x).select(lambda g: (g.key + 0.0, g.count())), vals, parts=(1, 2))
+    left = [float(i % 5) for i in range(40)]
+    ld = D.DryadLinqContext(1, local_debug=True)
+    want = sorted(ld.from_enumerable(left, 1).join(ld.from_enumerable([1, 3], 1), lambda a: a, lambda b: b, lambda a, b: (a, b)).to_list())
+    ctx = D.DryadLinqContext(2, device="cuda")
+    got = sorted(ctx.from_enumerable(left, 2).join(ctx.from_enumerable([1, 3], 1), lambda a: a, lambda b: b, lambda a, b: (a, b)).to_list())
+    assert got == want and len(got) == 16
+
+
+def test_group_join_and_sliding_window_run_on_the_gpu():
+    outer = [{"id": i, "w": i % 5} for i in range(300)]
+    inner = [{"fk": (i * 7) % 330, "v": i} for i in range(4000)]        # ids 300..329 have no outer row; some outers have no match
+
+    def gj(c, parts):
+        o, n = c.from_enumerable(outer, parts), c.from_enumerable(inner, parts)
+        return o.group_join(n, lambda r: r.id, lambda s: s.fk,
+                            lambda r, g: {"id": r.id, "n": g.count(), "s": g.sum(lambda s: s.v) + r.w})
+    want = sorted(gj(D.DryadLinqContext(1, local_debug=True), 1).to_list(), key=repr)
+    for parts in (1, 3):
+        ctx = D.DryadLinqContext(parts, device="cuda")
+        got = sorted(gj(ctx, parts).to_list(), key=repr)
+        assert got == want and ctx._backend().host_fallbacks == 0, parts
+    data = [(i * 31) % 97 for i in range(2000)]
+    _same_order(lambda q: q.sliding_window(lambda w: sum(w), 4), data)
+    _same_order(lambda q: q.sliding_window(lambda w: w[-1] - w[0], 7), data)
+    _same_order(lambda q: q.sliding_window(lambda w: (w[0], w[1] * 2), 2), data)
