@@ -44,6 +44,7 @@ struct Pump {
   void* user = nullptr;
   bool stop = false;
   int64_t delivered = 0;
+  int64_t notifiers = 0;          // stream-completion callbacks created and not yet fired (guarded by mu)
 };
 
 void pump_worker(Pump* p) {
@@ -130,10 +131,19 @@ void pump_post(void* h, int64_t listener, int64_t message, double delay_seconds)
 // graph-manager event loop without any thread blocking in a stream synchronize
 // (GraphManager/kernel/DrMessagePump.h:81-87 delivers process/vertex state changes the same way).
 struct Notifier { Pump* p; int64_t listener, message; };
-void* pump_make_notifier(void* h, int64_t listener, int64_t message) { return new Notifier{(Pump*)h, listener, message}; }
+void* pump_make_notifier(void* h, int64_t listener, int64_t message) {
+  Pump* p = (Pump*)h;
+  { std::lock_guard<std::mutex> l(p->mu); ++p->notifiers; }
+  return new Notifier{p, listener, message};
+}
+// Runs on a CUDA driver thread when the stream reaches the callback.  pump_destroy waits until every
+// outstanding notifier has fired, so `n->p` is alive here even when the job is torn down with GPU
+// work still in flight.
 static void pump_notifier_fire(void* arg) {
   Notifier* n = (Notifier*)arg;
   pump_post(n->p, n->listener, n->message, 0.0);
+  { std::lock_guard<std::mutex> l(n->p->mu); --n->p->notifiers; }
+  n->p->cv.notify_all();
   delete n;
 }
 void* pump_notifier_fn() { return (void*)&pump_notifier_fire; }
@@ -146,7 +156,20 @@ int64_t pump_wait_delivered(void* h, int64_t count, double timeout_seconds) {
 }
 void pump_destroy(void* h) {
   Pump* p = (Pump*)h;
-  { std::lock_guard<std::mutex> l(p->mu); p->stop = true; }
+  {
+    // callbacks queued on CUDA streams still point at this pump: let them fire first (bounded wait:
+    // a stream that never reaches its callback must not hang the teardown; such a notifier is leaked
+    // together with the pump rather than left to post into freed memory)
+    std::unique_lock<std::mutex> l(p->mu);
+    if (!p->cv.wait_for(l, std::chrono::seconds(30), [&] { return p->notifiers == 0; })) {
+      p->stop = true;
+      l.unlock();
+      p->cv.notify_all();
+      for (auto& t : p->workers) t.join();
+      return;                                            // pump intentionally not freed
+    }
+    p->stop = true;
+  }
   p->cv.notify_all();
   for (auto& t : p->workers) t.join();
   for (auto& kv : p->listener_locks) delete kv.second;

@@ -12,6 +12,11 @@
 //
 // One push / pop = one kernel launch on the caller's stream.  Producer and consumer must be
 // different GPUs (two kernels that wait on each other must never share a device).
+//
+// A timeout is FATAL for the ring: the status word becomes non-zero, and because the completion
+// counters count CTAs per block, a push or pop that timed out leaves them out of step for good.
+// Every later push / pop on a ring whose status is non-zero returns at once without touching the
+// ring; the owner (parallel/ring.py HbmRing) refuses further use once it has seen the status.
 #include "common.cuh"
 #include "../../include/dryad_b200.h"
 
@@ -35,14 +40,21 @@ __global__ void __launch_bounds__(256) push_kernel(const uint4* __restrict__ src
                                                    const uint64_t* tail_local, unsigned long long* done_local,
                                                    uint64_t seq, int slots, uint64_t slot_bytes, int32_t* status) {
   __shared__ int ok;
-  if (threadIdx.x == 0) ok = wait_ge(tail_local, seq + 1 >= (uint64_t)slots ? seq + 1 - slots : 0) ? 1 : 0;
+  if (threadIdx.x == 0)
+    ok = (*reinterpret_cast<volatile int32_t*>(status) == 0) &&
+         wait_ge(tail_local, seq + 1 >= (uint64_t)slots ? seq + 1 - slots : 0) ? 1 : 0;
   __syncthreads();
   if (!ok) { if (threadIdx.x == 0) atomicMax(status, 2); return; }
   const int slot = (int)(seq % slots);
   uint4* dst = reinterpret_cast<uint4*>(ring_peer + (size_t)slot * slot_bytes);
-  const uint64_t n16 = (nbytes + 15) / 16;
+  const uint64_t n16 = nbytes / 16;                    // whole 16-byte units; the tail goes bytewise:
   for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n16; i += (uint64_t)gridDim.x * blockDim.x)
     dst[i] = __ldcs(src + i);
+  if (blockIdx.x == 0) {                                // the source is never read past nbytes
+    const unsigned char* sb = reinterpret_cast<const unsigned char*>(src);
+    unsigned char* db = reinterpret_cast<unsigned char*>(dst);
+    for (uint64_t b = n16 * 16 + threadIdx.x; b < nbytes; b += blockDim.x) db[b] = sb[b];
+  }
   __threadfence_system();
   __syncthreads();
   if (threadIdx.x == 0) {
@@ -61,7 +73,7 @@ __global__ void __launch_bounds__(256) pop_kernel(uint4* __restrict__ dst, uint6
                                                   unsigned long long* done_local, uint64_t seq, int slots,
                                                   uint64_t slot_bytes, int32_t* status) {
   __shared__ int ok;
-  if (threadIdx.x == 0) ok = wait_ge(head_local, seq + 1) ? 1 : 0;
+  if (threadIdx.x == 0) ok = (*reinterpret_cast<volatile int32_t*>(status) == 0) && wait_ge(head_local, seq + 1) ? 1 : 0;
   __syncthreads();
   if (!ok) { if (threadIdx.x == 0) atomicMax(status, 2); return; }
   const int slot = (int)(seq % slots);

@@ -133,13 +133,16 @@ class DryadLinqContext:
         self.graph_manager_node: Optional[str] = None
         self.select_order_preserving = False
         self.partition_unc_path: Optional[str] = None
-        self.job_environment_variables: Dict[str, str] = {}
-        self.resources_to_add: List[str] = []
-        self.resources_to_remove: List[str] = []
+        # read-only once a job was submitted (DryadLinqStringDictionary / DryadLinqStringList)
+        from ..utils.collections import ReadOnlyAfterSubmitDict, ReadOnlyAfterSubmitList
+        self.job_environment_variables: Dict[str, str] = ReadOnlyAfterSubmitDict()
+        self.resources_to_add: List[str] = ReadOnlyAfterSubmitList()
+        self.resources_to_remove: List[str] = ReadOnlyAfterSubmitList()
         self.exec_host_args: List[str] = []
         # engine knobs (GraphManager/graph/DrGraphParameters.cpp:50-69)
         self.max_failures_per_vertex = 6
         self.fail_fast_on_deterministic_errors = False
+        self.schedule_vertices = True          # place every vertex through the cluster interface + delay scheduler
         self.spmd_control_timeout = 120.0      # seconds a rank waits for the graph manager / the manager for a rank
         self.retain_intermediate = True
         self.sample_rate = SC.SAMPLE_RATE
@@ -169,6 +172,16 @@ class DryadLinqContext:
         self.last_plan = None
 
     # ---- lifecycle ---------------------------------------------------------------------------
+    @property
+    def client_log(self):
+        """`DryadLinqClient.log` in the work directory (LinqToDryad/DryadLinqLog.cs:30-190)."""
+        log = self.__dict__.get("_client_log")
+        if log is None:
+            from ..utils.log import DryadLinqLog
+            log = DryadLinqLog.client(self.work_dir, getattr(self.runtime_logging_level, "name", None))
+            self.__dict__["_client_log"] = log
+        return log
+
     def dispose(self):
         self._disposed = True
         self._tables.clear()
@@ -411,6 +424,10 @@ class DryadLinqContext:
                 raise DryadLinqException(ErrorCode.MustStartFromContext, "queries of one job must share one context")
         job = DryadLinqJobInfo(self, qs)
         object.__setattr__(self, "_frozen", True)
+        for coll in (self.job_environment_variables, self.resources_to_add, self.resources_to_remove):
+            if hasattr(coll, "freeze"):
+                coll.freeze()
+        self.client_log.info("submit: {0} quer{1}", len(qs), "y" if len(qs) == 1 else "ies")
         already = [q for q in qs if q._job is not None]
         if len(already) == len(qs):          # re-submitting an executed query returns the existing job
             return qs[0]._job

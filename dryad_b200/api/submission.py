@@ -64,8 +64,17 @@ class LocalJobSubmission(IDryadLinqJobSubmission):
     def get_job_id(self):
         return os.path.basename(self.job_dir)
 
+    def resource_files(self) -> List[str]:
+        """The job's file set: the script, files added with add_local_file and every imported module
+        that is not part of the interpreter's own library trees (PeloponneseJobSubmission computes the
+        GM / worker file sets by dependency listing, LinqToDryad/PeloponneseJobSubmission.cs:36-179)."""
+        from ..plan.type_system import loaded_non_system_modules
+        return sorted(set([os.path.abspath(self.script)] + [os.path.abspath(f) for f in self.files] + loaded_non_system_modules()))
+
     def submit_job(self):
         os.makedirs(os.path.join(self.job_dir, "log"), exist_ok=True)
+        with open(os.path.join(self.job_dir, "resources.txt"), "w") as f:
+            f.write("\n".join(self.resource_files()) + "\n")
         cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={self.n}",
                "--master-addr", "127.0.0.1", "--master-port", str(self.port), self.script, *self.args]
         out = open(os.path.join(self.job_dir, "log", "stdout.txt"), "wb")

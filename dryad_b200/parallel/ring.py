@@ -28,6 +28,7 @@ class HbmRing:
         arena.barrier()                                 # every rank's control words are zero before any push
         self.pushed = 0
         self.popped = 0
+        self.dead = False                               # set by check(): a timed-out ring is never used again
         self.status = torch.zeros(1, dtype=torch.int32, device=arena.device)
         self.out_len = torch.zeros(1, dtype=torch.int64, device=arena.device)
 
@@ -38,6 +39,8 @@ class HbmRing:
         """Producer side: enqueue the copy of `block` (contiguous, <= slot_bytes) into the ring."""
         if self.arena.rank != self.src:
             raise RuntimeError("push is for the producer rank")
+        if self.dead:
+            raise N.NativeError("HbmRing: the ring failed earlier (timeout or oversized block) and cannot be used again")
         K.require_cuda(block)
         nbytes = block.numel() * block.element_size()
         a = self.arena
@@ -52,6 +55,8 @@ class HbmRing:
         bytes); returns the device word that will hold the block's byte length."""
         if self.arena.rank != self.dst:
             raise RuntimeError("pop is for the consumer rank")
+        if self.dead:
+            raise N.NativeError("HbmRing: the ring failed earlier (timeout or oversized block) and cannot be used again")
         K.require_cuda(out)
         a = self.arena
         cap = out.numel() * out.element_size()
@@ -65,6 +70,8 @@ class HbmRing:
 
     def check(self) -> None:
         st = int(self.status.item())
+        if st:
+            self.dead = True            # fatal: the per-block completion counters are out of step from here on
         if st == 2:
             raise N.NativeError("HbmRing: the peer did not move within the timeout")
         if st == 1:

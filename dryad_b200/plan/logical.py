@@ -94,10 +94,11 @@ def infer_schema(sample: Any) -> Schema:
     """Schema of python records: numbers -> scalar 'value' column; dict / Record / namedtuple of
     numbers -> one column per field; anything else is opaque."""
     import numbers
+    from .type_system import kind_of_value
 
     def kind(v):
-        if isinstance(v, bool):
-            return "b"
+        if isinstance(v, (bool, int, float)):
+            return kind_of_value(v)          # ints outside int64 are opaque (host path)
         if isinstance(v, numbers.Integral):
             return "i"
         if isinstance(v, numbers.Real):

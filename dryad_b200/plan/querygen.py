@@ -194,13 +194,18 @@ class QueryGen:
         partitioned = child.info.partition.is_partitioned_by(ks, comparer) or pc == 1
         out_info = DataSetInfo(HashPartition(KeySelector(None, None, "key"), pc, comparer))
         if dec is not None:
+            if not partitioned and not SC.GROUP_BY_LOCAL_AGGREGATION_IS_PARTIAL:
+                # no local pre-aggregation: shuffle the rows by key, then one full aggregation
+                child = self._hash_shuffle(child, key, pc, comparer)
+                partitioned = True
             if partitioned:
                 g = self._node(NodeType.GroupBy, [(child, PW)], pc, child.info.keep_partition_only(), None,
                                key=key, elem=p.get("elem"), decomp=dec, mode="full_acc", comparer=comparer)
             else:
                 part = self._node(NodeType.GroupBy, [(child, PW)], pc, None, None, key=key, elem=p.get("elem"),
                                   decomp=dec, mode="partial_acc", comparer=comparer)
-                part.dynamic_manager = DynamicManagerType.PartialAggregator if (SC.DYNAMIC_OPT_LEVEL & SC.DYN_AGGREGATE) else DynamicManagerType.NoManager
+                part.dynamic_manager = DynamicManagerType.PartialAggregator \
+                    if ((SC.DYNAMIC_OPT_LEVEL & SC.DYN_AGGREGATE) or SC.GROUP_BY_DYNAMIC_REDUCE) else DynamicManagerType.NoManager
                 kir = X.col("key", key.ir.kind) if isinstance(key.ir, X.Expr) and key.ir.kind in "ifbs" else None
                 pkey = Lam(lambda kv: kv[0], kir, 1, "Key")
                 merged = self._hash_shuffle(part, pkey, pc, comparer)
@@ -317,10 +322,17 @@ class QueryGen:
             return outer, self._hash_shuffle(inner, ikey, op.count, comparer)
         if i_ok and isinstance(ip, HashPartition):
             return self._hash_shuffle(outer, okey, ip.count, comparer), inner
+        def co_range(side, key, part):
+            # the other side is re-partitioned with the SAME separators (co-range); with DYN_CO_RANGE
+            # the distributor is tagged so the runtime may re-balance both sides together
+            merged = self._range_shuffle(side, key, part.count, part.descending, comparer, list(part.separators))
+            if SC.DYNAMIC_OPT_LEVEL & SC.DYN_CO_RANGE and merged.children:
+                merged.children[0][0].dynamic_manager = DynamicManagerType.RangeDistributor
+            return merged
         if o_ok and isinstance(op, RangePartition) and op.has_keys():
-            return outer, self._range_shuffle(inner, ikey, op.count, op.descending, comparer, list(op.separators))
+            return outer, co_range(inner, ikey, op)
         if i_ok and isinstance(ip, RangePartition) and ip.has_keys():
-            return self._range_shuffle(outer, okey, ip.count, ip.descending, comparer, list(ip.separators)), inner
+            return co_range(outer, okey, ip), inner
         pc = max(outer.partition_count, inner.partition_count)
         if pc == 1:
             return outer, inner
@@ -634,55 +646,86 @@ class QueryGen:
                 lines.append(f"      {n.describe()}")
         return "\n".join(lines)
 
+    def _collect_objects(self):
+        """Closure objects a plan refers to by index (comparers, explicit range keys, aggregate seeds):
+        DryadLinqObjectStore role — the client puts them, the plan carries the indices, the job
+        directory carries the serialised store (LinqToDryad/DryadLinqObjectStore.cs:43-173)."""
+        from .object_store import ObjectStore
+        store = ObjectStore()
+        refs = {}
+        for n in self.nodes:
+            members = n.members if n.type == NodeType.Super else [n]
+            for m in members:
+                for name in ("comparer", "range_keys", "seed"):
+                    v = m.params.get(name)
+                    if v is not None:
+                        refs.setdefault(n.uid, []).append((name, store.put(v)))
+        self.object_store, self.object_refs = store, refs
+        return store, refs
+
+    def save_object_store(self, path: str) -> bool:
+        """Serialise the plan's closure objects next to the plan file; False when one of them cannot be
+        pickled (a lambda comparer), in which case the closures only live in this process."""
+        store, _ = self._collect_objects()
+        if not len(store):
+            return False
+        try:
+            store.save(path)
+            return True
+        except Exception:  # noqa: BLE001
+            return False
+
     def to_xml(self) -> str:
+        from .query_doc import QueryDoc
         self.build()
         ctx = self.context
-        out = ['<?xml version="1.0" encoding="utf-8"?>', "<Query>",
-               f"  <DryadLinqVersion>{escape(ctx.version)}</DryadLinqVersion>",
-               f"  <ClusterName>{escape(str(ctx.cluster_name))}</ClusterName>",
-               "  <Visualization>none</Visualization>",
-               f"  <IntermediateDataCompression>{ctx.intermediate_data_compression_scheme}</IntermediateDataCompression>",
-               f"  <EnableSpeculativeDuplication>{str(ctx.enable_speculative_duplication).lower()}</EnableSpeculativeDuplication>",
-               "  <XmlExecHostArgs>" + "".join(f"<Argument>{escape(a)}</Argument>" for a in ctx.exec_host_args) + "</XmlExecHostArgs>",
-               "  <QueryPlan>"]
+        _store, refs = self._collect_objects()
+        doc = QueryDoc("Query")
+        doc.element("DryadLinqVersion", ctx.version).element("ClusterName", ctx.cluster_name)
+        doc.element("Visualization", "none")
+        doc.element("IntermediateDataCompression", ctx.intermediate_data_compression_scheme)
+        doc.element("EnableSpeculativeDuplication", str(ctx.enable_speculative_duplication).lower())
+        doc.open("XmlExecHostArgs")
+        for a in ctx.exec_host_args:
+            doc.element("Argument", a)
+        doc.close("XmlExecHostArgs")
+        doc.element("ObjectStoreCount", len(_store))
+        doc.open("QueryPlan")
         for n in self.nodes:
-            t = XML_VERTEX_TYPE.get(n.type, "WHERE")
-            out.append("    <Vertex>")
-            out.append(f"      <UniqueId>{n.uid}</UniqueId>")
-            out.append(f"      <Type>{t}</Type>")
-            out.append(f"      <Name>{escape(n.name)}</Name>")
-            out.append(f"      <Explain><![CDATA[{n.describe() if n.type != NodeType.Super else ' | '.join(m.describe() for m in n.members)}]]></Explain>")
-            out.append(f"      <Partitions>{n.partition_count}</Partitions>")
-            out.append(f"      <ChannelType>{n.channel_type.value.upper()}</ChannelType>")
+            doc.open("Vertex")
+            doc.element("UniqueId", n.uid).element("Type", XML_VERTEX_TYPE.get(n.type, "WHERE")).element("Name", n.name)
+            doc.cdata("Explain", n.describe() if n.type != NodeType.Super else " | ".join(m.describe() for m in n.members))
+            doc.element("Partitions", n.partition_count).element("ChannelType", n.channel_type.value.upper())
             conn = CP if any(op == CP for _, op in n.children) else PW
-            out.append(f"      <ConnectionOperator>{conn.value.upper()}</ConnectionOperator>")
-            out.append("      <DynamicManager>")
-            out.append(f"        <Type>{n.dynamic_manager.value}</Type>")
+            doc.element("ConnectionOperator", conn.value.upper())
+            doc.open("DynamicManager").element("Type", n.dynamic_manager.value)
             if n.dynamic_manager in (DynamicManagerType.PartialAggregator, DynamicManagerType.FullAggregator):
-                out.append(f"        <AggregationLevels>{n.aggregation_levels}</AggregationLevels>")
+                doc.element("AggregationLevels", n.aggregation_levels)
             if n.dynamic_manager == DynamicManagerType.RangeDistributor:
-                out.append(f"        <SampleRate>{SC.SAMPLE_RATE}</SampleRate>")
-            out.append("      </DynamicManager>")
+                doc.element("SampleRate", SC.SAMPLE_RATE)
+            doc.close("DynamicManager")
             if n.type in (NodeType.InputTable, NodeType.OutputTable):
                 uri = n.params.get("uri") or ""
-                tag = "SourceURI" if n.type == NodeType.InputTable else "SinkURI"
-                out.append("      <StorageSet>")
-                out.append(f"        <Type>{'PartitionedFile' if uri else 'Memory'}</Type>")
-                out.append(f"        <{tag}>{escape(uri)}</{tag}>")
+                doc.open("StorageSet").element("Type", "PartitionedFile" if uri else "Memory")
+                doc.element("SourceURI" if n.type == NodeType.InputTable else "SinkURI", uri)
                 if n.type == NodeType.OutputTable:
-                    out.append(f"        <IsTemporary>{str(bool(n.params.get('temporary'))).lower()}</IsTemporary>")
-                    out.append(f"        <OutputCompressionScheme>{n.params.get('compression') or 'None'}</OutputCompressionScheme>")
-                out.append("      </StorageSet>")
+                    doc.element("IsTemporary", str(bool(n.params.get("temporary"))).lower())
+                    doc.element("OutputCompressionScheme", n.params.get("compression") or "None")
+                doc.close("StorageSet")
             else:
-                out.append("      <Entry>")
-                out.append("        <AssemblyName>dryad_b200.runtime.vertex_ops</AssemblyName>")
-                out.append("        <ClassName>DryadLinq__Vertex</ClassName>")
-                out.append(f"        <MethodName>{escape(n.type.value)}__{n.uid}</MethodName>")
-                out.append("      </Entry>")
-            out.append("      <Children>")
+                doc.open("Entry").element("AssemblyName", "dryad_b200.runtime.vertex_ops")
+                doc.element("ClassName", "DryadLinq__Vertex").element("MethodName", f"{n.type.value}__{n.uid}")
+                doc.close("Entry")
+            if n.uid in refs:
+                doc.open("ObjectStoreRefs")
+                for name, idx in refs[n.uid]:
+                    doc.element("Ref", idx, {"name": name})
+                doc.close("ObjectStoreRefs")
+            doc.open("Children")
             for c, op in n.children:
-                out.append(f"        <Child><UniqueId>{c.uid}</UniqueId><ConnectionOperator>{op.value.upper()}</ConnectionOperator><AffinityConstraint>UseDefault</AffinityConstraint></Child>")
-            out.append("      </Children>")
-            out.append("    </Vertex>")
-        out += ["  </QueryPlan>", "</Query>"]
-        return "\n".join(out)
+                doc.open("Child").element("UniqueId", c.uid).element("ConnectionOperator", op.value.upper())
+                doc.element("AffinityConstraint", "UseDefault").close("Child")
+            doc.close("Children")
+            doc.close("Vertex")
+        doc.close("QueryPlan")
+        return '<?xml version="1.0" encoding="utf-8"?>\n' + doc.to_string()

@@ -47,6 +47,13 @@ def simple_rewrite(root: QExpr) -> QExpr:
         srcs = [rw(s) for s in e.sources]
         out = e if all(a is b for a, b in zip(srcs, e.sources)) else _clone(e, srcs)
         s0 = out.sources[0] if out.sources else None
+        if out.op == "select" and not out.params.get("indexed") and s0 is not None:
+            # Select(x => x) does nothing: the planner never sees it (IdentityFunction, TypeSystem.cs)
+            from .type_system import is_identity_ir
+            lam = out.params.get("fn")
+            if lam is not None and is_identity_ir(getattr(lam, "ir", None), s0.schema):
+                memo[e.id] = s0
+                return s0
         if out.op == "where" and not out.params.get("indexed") and s0 is not None and single(e.sources[0]):
             # Where below OrderBy / Distinct / partition operators
             if s0.op in ("order_by", "distinct", "hash_partition", "range_partition") and \

@@ -40,6 +40,19 @@ def is_identity_function(fn: Optional[Callable]) -> bool:
         return False
 
 
+def is_identity_ir(ir: Any, schema: Optional[Dict[str, str]]) -> bool:
+    """True when a TRACED selector returns its argument unchanged: the `value` column for scalar
+    datasets, or a record whose every field is the same-named input column."""
+    from ..expr import ir as X
+    if schema is None:
+        return False
+    if isinstance(ir, X.Expr):
+        return list(schema) == ["value"] and ir.op == "col" and ir.args[0] == "value"
+    if isinstance(ir, dict) and not isinstance(ir, X.TupleFields):
+        return list(ir) == list(schema) and all(isinstance(e, X.Expr) and e.op == "col" and e.args[0] == k for k, e in ir.items())
+    return False
+
+
 def is_anonymous_type(v: Any) -> bool:
     """`new { a, b }` in the reference = a plain dict / Record here."""
     return isinstance(v, dict)

@@ -45,6 +45,8 @@ class JobExecutor:
         self.stats: List[dict] = []
         self.backend = context._backend()
         from ..utils import trace
+        self._placement: Dict[Tuple[int, int], int] = {}          # (stage uid, partition) -> computer its output lives on
+        self.cluster = None
         self.timeline = trace.GpuTimeline() if (trace.enabled(context) and getattr(self.backend, "name", "") == "gpu") else None
         self.gpu_timeline: List[dict] = []
 
@@ -139,6 +141,48 @@ class JobExecutor:
             ins.append([halo if i > 0 else []])
         return ins
 
+    # ---- placement (ClusterInterface + LocalScheduler roles) ---------------------------------------
+    def _place(self, v: int, node: DLinqQueryNode, i: int, ins) -> Dict[str, Any]:
+        """Choose the computer (GPU / worker slot) for one vertex: every input partition votes for the
+        computer that holds it with its record count (DrResources affinity), the votes are merged into
+        a computer-, rack- or cluster-level preference (`affinity_merge`), and the native delay
+        scheduler matches the vertex with an idle computer (LocalScheduler/LocalScheduler.cs:132-268).
+        Returns what the vertex record keeps: where it ran, at which locality, and per input channel
+        how many records came from which computer (GraphManager/vertex/DrVertexRecord.cpp)."""
+        from ..sched.cluster import Affinity, LocalCluster, Process
+        from .command import affinity_merge
+        ctx = self.context
+        if self.cluster is None:
+            n = max(1, min(int(getattr(ctx, "job_max_nodes", 0) or 0) or max(x.partition_count for x in self.plan.nodes), 64))
+            self.cluster = LocalCluster(n, getattr(ctx, "work_dir", "/tmp"), rack_delay=0.0, cluster_delay=0.0)
+        ncomp = len(self.cluster.computers)
+        votes: Dict[int, int] = {}
+        channels = []
+        for (uid, part), payloads in zip(self._gm_inputs.get(v, []), [p for inp in ins for p in inp]):
+            where = self._placement.get((uid, part))
+            recs = self.backend.count(payloads)
+            channels.append({"from": f"{uid}.{part}", "records": recs, "computer": where})
+            if where is not None and recs:
+                votes[where] = votes.get(where, 0) + recs
+        if votes:
+            level, choice = affinity_merge(sorted(votes.items()), [0] * ncomp)
+            prefer = [choice] if level == "computer" else []
+        else:
+            level, prefer = "cluster", [i % ncomp]                    # sources: spread by partition index
+        proc = Process(v, f"{node.name}#{node.uid}[{i}]", Affinity(prefer, sum(votes.values()), False))
+        self.cluster.schedule_process(proc)
+        got = None
+        for c in (prefer + [x for x in range(ncomp) if x not in prefer]):
+            got = self.cluster.computer_idle(c, age_bias=1e9)
+            if got is not None:
+                break
+        comp = got.computer.index if got is not None and got.computer is not None else (prefer[0] if prefer else 0)
+        self._placement[(node.uid, i)] = comp
+        local = sum(ch["records"] for ch in channels if ch["computer"] == comp)
+        total = sum(ch["records"] for ch in channels)
+        return {"computer": comp, "locality": level if votes else "source", "channels": channels,
+                "records_local": local, "records_remote": total - local}
+
     # ---- graph manager wiring -------------------------------------------------------------------
     def _build_gm(self):
         """Mirror the physical plan into the native graph manager: one GM stage per plan node, one
@@ -203,6 +247,7 @@ class JobExecutor:
                 t0 = time.perf_counter()
                 try:
                     ins = self._inputs(node, i)
+                    placed = self._place(v, node, i, ins) if ctx.schedule_vertices else None
                     if ctx.fault_injector is not None:
                         ctx.fault_injector(node, i, version)
                     env = VertexEnv(ctx, node.uid, i, version)
@@ -215,10 +260,15 @@ class JobExecutor:
                     self.out[node.uid][i] = ports
                     n_in = sum(self.backend.count(p) for inp in ins for p in inp)
                     n_out = sum(self.backend.count(p) for p in ports)
-                    self.stats.append({"stage": node.uid, "stage_name": node.name, "part": i, "version": version,
-                                       "seconds": dt, "records_in": n_in, "records_out": n_out})
+                    rec = {"stage": node.uid, "stage_name": node.name, "part": i, "version": version,
+                           "seconds": dt, "records_in": n_in, "records_out": n_out}
+                    if placed is not None:
+                        rec.update(placed)
+                    self.stats.append(rec)
                     gm.completed(v, version, dt, float(n_in))
-                    rep.vertex_event(node, i, version, "completed", seconds=dt, records_in=n_in, records_out=n_out)
+                    rep.vertex_event(node, i, version, "completed", seconds=dt, records_in=n_in, records_out=n_out,
+                                     **({"computer": placed["computer"], "locality": placed["locality"],
+                                         "local": placed["records_local"], "remote": placed["records_remote"]} if placed else {}))
                     self._release_finished_children(node)
                 except Exception as ex:  # noqa: BLE001  (vertex code is user code)
                     text = "".join(traceback.format_exception_only(type(ex), ex)).strip()
@@ -267,9 +317,13 @@ class JobExecutor:
         later failure could re-run a consumer without re-running the producer."""
         if self.context.retain_intermediate:
             return
-        done = {n.uid for n in self.plan.nodes if n.uid in self.out and all(x is not None for x in self.out[n.uid])}
+        from ..utils.collections import BitVector
+        done = BitVector(max((n.uid for n in self.plan.nodes), default=0) + 1)       # finished stages, by uid
+        for n in self.plan.nodes:
+            if n.uid in self.out and all(x is not None for x in self.out[n.uid]):
+                done.set(n.uid)
         for child, _ in node.children:
-            if child.parents and all(p.uid in done for p in child.parents):
+            if child.parents and all(done[p.uid] for p in child.parents):
                 self.out[child.uid] = [None] * child.partition_count
 
     # ---- atomic output commit (DrGraph::FinalizeGraph) ----------------------------------------

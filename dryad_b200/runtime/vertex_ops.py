@@ -43,7 +43,20 @@ class VertexEnv:
                  use_large_buffer: bool = False):
         self.context, self.vertex_id, self.part, self.version = context, vertex_id, part, version
         self.n_outputs = max(1, n_outputs)
-        self.use_large_buffer = use_large_buffer
+        from ..plan import static_config as SC
+        self.use_large_buffer = use_large_buffer or SC.USE_LARGE_BUFFER
+        self._log = None
+
+    @property
+    def log(self):
+        """`vertex-<id>-<version>-LinqLog.txt` (LinqToDryad/DryadLinqLog.cs:30-190), created on first use."""
+        if self._log is None:
+            import os
+            from ..utils.log import DryadLinqLog
+            level = getattr(getattr(self.context, "runtime_logging_level", None), "name", None)
+            self._log = DryadLinqLog.for_vertex(os.path.join(getattr(self.context, "work_dir", "."), "log"),
+                                                self.vertex_id, self.version, level)
+        return self._log
 
     @property
     def threads_per_worker(self) -> int:
@@ -80,6 +93,7 @@ class VertexEnv:
         with open(path, "w", encoding="utf-8") as f:
             f.write(f"vertex {self.vertex_id} partition {self.part} version {self.version}\n")
             f.write("".join(traceback.format_exception(type(exc), exc, exc.__traceback__)))
+        self.log.error("vertex {0}[{1}] v{2} failed: {3}", self.vertex_id, self.part, self.version, repr(exc))
         return path
 
 

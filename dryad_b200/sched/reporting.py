@@ -31,6 +31,9 @@ class CalypsoReporter:
             f.write(plan.to_xml())
         with open(os.path.join(self.job_dir, "QueryGraph__0.txt"), "w") as f:
             f.write(plan.explain())
+        # closure objects the plan refers to by index travel with the job (DryadLinqObjectStore role)
+        if hasattr(plan, "save_object_store"):
+            plan.save_object_store(os.path.join(self.job_dir, "DryadLinqObjectStore__0.bin"))
 
     def vertex_event(self, node, part, version, state, **kv):
         self._emit("vertex", vertex=f"{node.uid}.{part}", version=version, stagename=node.name, stage=node.uid,

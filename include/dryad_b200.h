@@ -253,6 +253,9 @@ int dryad_stream_host_func(void* stream, void* fn, void* arg);
  * `done_local` is one zero-initialised u64 of scratch per direction and per side.  seq = number of
  * blocks pushed (popped) before this call.  status 2: the peer did not move within the timeout,
  * 1: block larger than the destination.  Producer and consumer must be different GPUs. */
+/* status != 0 (1 = block larger than the destination, 2 = peer timeout) is fatal for the ring: later
+ * pushes and pops return immediately without moving data; create a new ring.  `src` is read for exactly
+ * nbytes (whole 16-byte units vectorised, the tail bytewise); src must be 16-byte aligned. */
 int dryad_ring_push(const void* src, uint64_t nbytes, void* ring_peer, uint64_t* len_peer,
                     uint64_t* head_peer, const uint64_t* tail_local, uint64_t* done_local,
                     uint64_t seq, int slots, uint64_t slot_bytes, int32_t* status, void* stream);

@@ -148,3 +148,96 @@ def test_fork_value_type_system_and_query_doc():
     doc = QueryDoc("Query").element("ClusterName", "local").open("Vertex", {"id": 3}).cdata("Explain", "x => x < 3 && y ]]> 0").close("Vertex")
     root = ET.fromstring(doc.to_string())
     assert root.find("ClusterName").text == "local" and root.find("Vertex/Explain").text == "x => x < 3 && y ]]> 0"
+
+
+def test_golden_plans_of_dataset_info_elision_rules():
+    """The DataSetInfo subtleties: which shuffles and sorts the planner skips
+    because the data is already suitably partitioned / ordered, the broadcast-join rule, Fork / Tee,
+    Assume*, Concat, and Where pushed below OrderBy (SimpleRewriter)."""
+    ctx = D.DryadLinqContext(4)
+    ctx.broadcast_join_rows = 0                      # size rule off unless a case turns it on
+    src = lambda: ctx.from_enumerable([{"k": i % 7, "v": i} for i in range(100)], 4)   # noqa: E731
+    K = lambda r: r.k                                # noqa: E731
+    J = lambda a, b: {"k": a.k, "s": a.v + b.v}      # noqa: E731
+    shuffled = ["InputTable", "HashPartition", "Merge"]
+    # Join: neither side partitioned on the key -> both shuffled (QueryGen.cs:1483-1608)
+    assert _shape(src().join(src(), K, K, J)) == shuffled + shuffled + ["Super[Join,OutputTable]"]
+    # both sides already hash-partitioned on the key into the same count: NO further shuffle
+    assert _shape(src().hash_partition(K, 4).join(src().hash_partition(K, 4), K, K, J)) == \
+        shuffled + shuffled + ["Super[Join,OutputTable]"]
+    # one side partitioned: only the OTHER side is shuffled, into the same partition count
+    one = _plan(src().hash_partition(K, 4).join(src(), K, K, J))
+    assert [n.type.value for n in one.nodes].count("HashPartition") == 2 and one.nodes[-1].partition_count == 4
+    # set operations hash both sides on the element; Distinct after a matching HashPartition adds nothing
+    setop = ["InputTable", "Super[Select,HashPartition]", "Merge"]
+    assert _shape(src().select(lambda r: r.k).union(src().select(lambda r: r.v))) == setop + setop + ["Super[SetOperation,OutputTable]"]
+    assert _shape(src().select(lambda r: r.k).hash_partition(lambda x: x, 4).distinct()) == [
+        "InputTable", "Super[Select,HashPartition]", "Super[Merge,Distinct,OutputTable]"]
+    # GroupBy over data already hash-partitioned on the key: one full aggregation, no partial stage, no shuffle
+    assert _shape(src().hash_partition(K, 4).group_by(K).select(lambda g: {"k": g.key, "c": g.count()})) == [
+        "InputTable", "HashPartition", "Super[Merge,GroupBy,Select,OutputTable]"]
+    assert _shape(src().assume_hash_partition(K).group_by(K).select(lambda g: {"k": g.key, "c": g.count()})) == [
+        "InputTable", "Dummy", "Super[GroupBy,Select,OutputTable]"]
+    # OrderBy over data already range-partitioned on the key: only the per-partition sort is added;
+    # a second OrderBy on the same key is dropped altogether
+    ranged = ["InputTable", "Sampler", "Super[Merge,RangeSampler]", "RangePartition", "Super[Merge,OrderBy,OutputTable]"]
+    assert _shape(src().range_partition(K, 4).order_by(K)) == ranged
+    assert _shape(src().order_by(K).order_by(K)) == ranged
+    # AssumeOrderBy: Take keeps the order (ordered merge to one partition), no sort is planned
+    assert _shape(src().assume_order_by(K).take(5)) == ["InputTable", "Dummy", "PartitionOp", "Super[Merge,PartitionOp,OutputTable]"]
+    # Where moves below OrderBy (and the shared input of sampler and distributor becomes a Tee)
+    assert _shape(src().order_by(K).where(lambda r: r.v > 3)) == [
+        "InputTable", "Where", "Tee", "Sampler", "Super[Merge,RangeSampler]", "RangePartition", "Super[Merge,OrderBy,OutputTable]"]
+    # Concat keeps the partitions of both inputs side by side; a GroupBy after it re-partitions
+    assert _shape(src().concat(src())) == ["InputTable", "InputTable", "Concat", "OutputTable"]
+    assert _plan(src().concat(src())).nodes[2].partition_count == 8
+    assert _shape(src().concat(src()).group_by(K).select(lambda g: {"k": g.key, "c": g.count()})) == [
+        "InputTable", "InputTable", "Concat", "Super[GroupBy,HashPartition]", "Super[Merge,GroupBy,Select,OutputTable]"]
+    # broadcast-join rule: a small inner source is replicated (Tee x CrossProduct Merge), the big side stays put
+    ctx2 = D.DryadLinqContext(4)
+    big = ctx2.from_enumerable([{"k": i % 7, "v": i} for i in range(100)], 4)
+    small = ctx2.from_enumerable([{"k": i, "v": i * 2} for i in range(7)], 1)
+    bplan = _plan(big.join(small, K, K, J))
+    assert _shape(big.join(small, K, K, J)) == ["InputTable", "InputTable", "Tee", "Merge", "Super[Join,OutputTable]"]
+    join = bplan.nodes[-1].members[0]
+    assert join.params["broadcast"] and bplan.nodes[2].dynamic_manager.value == "Broadcast"
+    # Fork: one Fork vertex, one ForkBranch per consumer; a dataset used by two queries of one job is a Tee
+    f = src().fork(lambda r: (r.v if r.v % 2 == 0 else None, r.k if r.v % 2 else None), 2)
+    multi = QueryGen(ctx, [f.first.select(lambda x: x + 1).materialize_lazy(), f.second.materialize_lazy()]).build()
+    assert [n.type.value if not n.members else "Super[" + ",".join(m.type.value for m in n.members) + "]" for n in multi.nodes] == [
+        "InputTable", "Fork", "Super[ForkBranch,Select,OutputTable]", "Super[ForkBranch,OutputTable]"]
+    t = src().select(lambda r: r.v)
+    tee = QueryGen(ctx, [t.where(lambda x: x > 5).materialize_lazy(), t.select(lambda x: x * 2).materialize_lazy()]).build()
+    assert [n.type.value if not n.members else "Super[" + ",".join(m.type.value for m in n.members) + "]" for n in tee.nodes] == [
+        "InputTable", "Select", "Tee", "Super[Where,OutputTable]", "Super[Select,OutputTable]"]
+
+
+def test_plan_carries_its_closure_objects_and_static_config_switches(tmp_path):
+    """ObjectStore in the plan writer (comparers / range keys by index), QueryDoc-built XML, and the
+    GroupBy planner switch that turns local pre-aggregation off."""
+    from dryad_b200.plan import static_config as SC
+    ctx = D.DryadLinqContext(2, work_dir=str(tmp_path))
+    q = ctx.from_enumerable(range(50), 2).range_partition(lambda x: x, 2, range_keys=[25])
+    gen = _plan(q)
+    xml = gen.to_xml()
+    assert "<ObjectStoreCount>1</ObjectStoreCount>" in xml and '<Ref name="range_keys">0</Ref>' in xml
+    assert gen.object_store.get(0) == [25]
+    assert gen.save_object_store(str(tmp_path / "os.bin")) and ObjectStore.load(str(tmp_path / "os.bin")).get(0) == [25]
+    assert xmlplan.parse_query_xml(xml).version == ctx.version
+    q.to_list()                                              # the job directory carries the store too
+    import os
+    assert os.path.exists(os.path.join(str(tmp_path), "LocalJobs", "1", "DryadLinqObjectStore__0.bin"))
+    assert os.path.exists(os.path.join(str(tmp_path), "DryadLinqClient.log")) or ctx.client_log.level < 4
+    old = SC.GROUP_BY_LOCAL_AGGREGATION_IS_PARTIAL
+    try:
+        SC.GROUP_BY_LOCAL_AGGREGATION_IS_PARTIAL = False
+        c2 = D.DryadLinqContext(3)
+        shape = _shape(c2.from_enumerable(range(30), 3).group_by(lambda x: x % 4).select(lambda g: (g.key, g.count())))
+        assert shape == ["InputTable", "HashPartition", "Super[Merge,GroupBy,Select,OutputTable]"]
+        got = sorted(c2.from_enumerable(range(30), 3).group_by(lambda x: x % 4).select(lambda g: (g.key, g.count())).to_list())
+        assert got == [(0, 8), (1, 8), (2, 7), (3, 7)]
+    finally:
+        SC.GROUP_BY_LOCAL_AGGREGATION_IS_PARTIAL = old
+    # settings collections become read-only once a job was submitted
+    with pytest.raises(D.DryadLinqException):
+        ctx.job_environment_variables["X"] = "1"

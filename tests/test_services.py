@@ -59,3 +59,20 @@ def test_local_job_submission_runs_spmd_workers(tmp_path):
     bad = LocalJobSubmission(os.path.join(HERE, "mgpu", "does_not_exist.py"), num_processes=1, dryad_home=str(tmp_path))
     bad.submit_job()
     assert bad.wait_for_completion(timeout=120) == JobStatus.Failure
+
+
+def test_vertices_are_placed_by_the_delay_scheduler_and_records_keep_locality(tmp_path):
+    """ClusterInterface + LocalScheduler on the path of a job: every vertex is matched with a computer
+    through affinity votes of its inputs; the vertex record keeps where it ran and how many records
+    were local (DrVertexRecord per-channel statistics)."""
+    import os
+    import dryad_b200 as D
+    ctx = D.DryadLinqContext(3, work_dir=str(tmp_path))
+    got = ctx.from_enumerable(list(range(90)), 3).select(lambda x: x + 1).where(lambda x: x % 2 == 0).to_list()
+    assert sorted(got) == [x + 1 for x in range(90) if (x + 1) % 2 == 0]
+    log = open(os.path.join(str(tmp_path), "LocalJobs", "1", "calypso.log")).read()
+    placed = [l for l in log.splitlines() if ",vertex," in l and "state=completed" in l]
+    assert placed and all("computer=" in l and "locality=" in l for l in placed)
+    # pointwise stages follow their input: everything they read is local to the computer they ran on
+    follow = [l for l in placed if "locality=computer" in l]
+    assert follow and all("remote=0" in l for l in follow)
