@@ -142,6 +142,7 @@ class DryadLinqContext:
         # engine knobs (GraphManager/graph/DrGraphParameters.cpp:50-69)
         self.max_failures_per_vertex = 6
         self.fail_fast_on_deterministic_errors = False
+        self.spmd_pipe = os.environ.get("DRYAD_SPMD_PIPE", "nccl")   # streamed N:1 edges: "nccl" p2p pipe or "ring" (HBM ring FIFO)
         self.schedule_vertices = True          # place every vertex through the cluster interface + delay scheduler
         self.spmd_control_timeout = 120.0      # seconds a rank waits for the graph manager / the manager for a rank
         self.retain_intermediate = True

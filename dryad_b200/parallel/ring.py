@@ -76,3 +76,41 @@ class HbmRing:
             raise N.NativeError("HbmRing: the peer did not move within the timeout")
         if st == 1:
             raise N.NativeError("HbmRing: block larger than the destination buffer")
+
+
+def ring_send_batch(ring: HbmRing, batch, names) -> None:
+    """Stream a ColumnBatch through the ring: one header block (row count), then every column in
+    slot-sized chunks.  Names, dtypes and order are known to both ends from the plan's schema."""
+    dev = ring.arena.device
+    n = batch.n
+    hdr = torch.tensor([n, 0], dtype=torch.int64, device=dev)
+    ring.push(hdr)
+    for k in names:
+        col = batch.cols[k].contiguous().view(torch.uint8) if n else None
+        if col is None:
+            continue
+        flat = col.reshape(-1)
+        for a in range(0, flat.numel(), ring.slot_bytes):
+            blk = flat[a:a + ring.slot_bytes]
+            if blk.data_ptr() % 16:
+                blk = blk.clone()
+            ring.push(blk)
+
+
+def ring_recv_batch(ring: HbmRing, names, dtypes) -> dict:
+    """Inverse of ring_send_batch; returns dict name -> tensor."""
+    dev = ring.arena.device
+    hdr = torch.zeros(2, dtype=torch.int64, device=dev)
+    ring.pop(hdr)
+    n = int(hdr[0].item())                           # sizes the receives that follow
+    out = {}
+    for k in names:
+        dt = dtypes[k]
+        esz = torch.empty(0, dtype=dt).element_size()
+        total = n * esz
+        buf = torch.empty((total + 15) // 16 * 16 + ring.slot_bytes, dtype=torch.uint8, device=dev)
+        for a in range(0, total, ring.slot_bytes):
+            ring.pop(buf[a:a + ring.slot_bytes])
+        out[k] = buf[:total].view(dt)
+    ring.check()
+    return out

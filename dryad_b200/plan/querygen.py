@@ -240,9 +240,11 @@ class QueryGen:
             return self._merge(rp, pc, CP, info)
         desc = bool(descending)
         # branch A: sample -> one vertex -> separators (broadcast to every distributor)
-        smp = self._node(NodeType.Sampler, [(child, PW)], child.partition_count, None, None, key=key)
+        # sampled keys and separators are a `value` column of the key's kind when the key is traced
+        kschema = {"value": key.ir.kind} if isinstance(key.ir, X.Expr) and key.ir.kind in "if" and comparer is None else None
+        smp = self._node(NodeType.Sampler, [(child, PW)], child.partition_count, None, kschema, key=key)
         one = self._to_one(smp)
-        rs = self._node(NodeType.RangeSampler, [(one, PW)], 1, None, None, pcount=pc, descending=desc, comparer=comparer)
+        rs = self._node(NodeType.RangeSampler, [(one, PW)], 1, None, kschema, pcount=pc, descending=desc, comparer=comparer)
         # branch B: distribute with the separators as a side input
         rp = self._node(NodeType.RangePartition, [(child, PW), (rs, PW)], child.partition_count, None, child.schema,
                         key=key, nports=pc, descending=desc, comparer=comparer, range_keys=None)
@@ -487,13 +489,32 @@ class QueryGen:
             return self._node(NodeType.Aggregate, [(one, PW)], 1, None, None, fn=p["fn"], stage=0, has_seed=p["has_seed"],
                               seed=p.get("seed"), seed_fn=p.get("seed_fn"), result=p.get("result"))
         if kind == "contains":
-            s1 = self._node(NodeType.Contains, [(child, PW)], pc, None, None, value=p["value"], stage=1)
+            s1 = self._node(NodeType.Contains, [(child, PW)], pc, None, {"value": "b"}, value=p["value"], stage=1)
             one = self._to_one(s1)
-            return self._node(NodeType.BasicAggregate, [(one, PW)], 1, None, None, kind="any_true", stage=2)
-        s1 = self._node(NodeType.BasicAggregate, [(child, PW)], pc, None, None, kind=kind, stage=1, fn=p.get("fn"),
+            return self._node(NodeType.BasicAggregate, [(one, PW)], 1, None, {"value": "b"}, kind="any_true", stage=2)
+        # schemas of the partials and of the result, where the types are known: they let the partials
+        # travel between ranks as tensors and the scalar come back as a column
+        fn = p.get("fn")
+        vk = None
+        if fn is not None and isinstance(getattr(fn, "ir", None), X.Expr):
+            vk = fn.ir.kind
+        elif fn is None and child.schema is not None and list(child.schema) == ["value"]:
+            vk = child.schema["value"]
+        s1_schema = s2_schema = None
+        if kind == "count":
+            s1_schema = s2_schema = {"value": "i"}
+        elif kind in ("any", "all"):
+            s1_schema = s2_schema = {"value": "b"}
+        elif kind in ("sum", "min", "max") and vk in ("i", "f"):
+            s1_schema = s2_schema = {"value": vk}
+        elif kind == "average" and vk in ("i", "f"):
+            s1_schema, s2_schema = {"item1": vk, "item2": "i"}, {"value": "f"}
+        elif kind in ("first", "last") and child.schema is not None:
+            s1_schema = s2_schema = dict(child.schema)
+        s1 = self._node(NodeType.BasicAggregate, [(child, PW)], pc, None, s1_schema, kind=kind, stage=1, fn=p.get("fn"),
                         default=p.get("default", False))
         one = self._to_one(s1)
-        return self._node(NodeType.BasicAggregate, [(one, PW)], 1, None, None, kind=kind, stage=2, fn=p.get("fn"),
+        return self._node(NodeType.BasicAggregate, [(one, PW)], 1, None, s2_schema, kind=kind, stage=2, fn=p.get("fn"),
                           default=p.get("default", False))
 
     # apply / fork (VisitApply :2925-3081, VisitFork :3083-3100)

@@ -55,6 +55,7 @@ class GpuBackend:
         self.device = torch.device(context.device)
         K.N.kernels()                      # fail loudly when the CUDA library is missing
         self.host_fallbacks = 0
+        self.fallback_log: List[str] = []
         self._arena = None
 
     # ---- plumbing ------------------------------------------------------------------------------
@@ -106,6 +107,7 @@ class GpuBackend:
             if r is not NotImplemented:
                 return r
         self.host_fallbacks += 1
+        self.fallback_log.append(f"{node.type.value}#{node.uid}")     # which vertices ran on the host path
         ins = [[self.to_records(p) for p in payloads] for payloads in inputs]
         ports = vertex_ops.run(node, part, ins, env)
         if node.n_out_ports == 1 and node.type not in (NodeType.GroupBy,):

@@ -407,12 +407,54 @@ class SpmdExecutor(JobExecutor):
             cols[k] = raw.view(torch.float64) if kind == "f" else (raw != 0 if kind == "b" else raw)
         return ColumnBatch(cols, h, getattr(own, "tuple_like", False))
 
+    def _pipe_to_zero(self, payload: Optional[ColumnBatch], schema) -> Optional[List]:
+        """N:1 merge of columnar partitions as STREAMED rank-to-rank channels (C7): every rank r > 0
+        streams its partition to rank 0 in blocks — `channel/pipe.py` (point-to-point sends on a side
+        stream, bounded depth) or, with context.spmd_pipe == "ring", the HBM ring FIFO of
+        `parallel/ring.py` (P2P stores + release/acquire flags, no NCCL) — while rank 0 receives them in
+        rank order.  Only rank 0 ends up with the data (the all-gather form gave it to everyone)."""
+        names = sorted(schema)
+        dts = {k: self._DT[schema[k]] for k in names}
+        dev = self.backend.device if getattr(self.backend, "name", "") == "gpu" else torch.device("cpu")
+        tl = getattr(payload, "tuple_like", False) if payload is not None else False
+        mode = getattr(self.context, "spmd_pipe", "nccl")
+        self.tensor_collectives += 1
+        self.streamed_edges = getattr(self, "streamed_edges", 0) + 1
+        self.context.__dict__["last_streamed_edges"] = self.streamed_edges
+        if mode == "ring" and dev.type == "cuda":
+            from ..parallel.ring import HbmRing, ring_recv_batch, ring_send_batch
+            ctx = self.context
+            rings = ctx.__dict__.get("_gather_rings")
+            if rings is None:
+                arena = ctx._spmd_arena()
+                rings = ctx.__dict__["_gather_rings"] = [None] + [HbmRing(arena, r, 0, slots=4, slot_bytes=1 << 20)
+                                                                  for r in range(1, self.world)]
+            if self.rank == 0:
+                parts = [payload if payload is not None else ColumnBatch({k: torch.empty(0, dtype=dts[k], device=dev) for k in names}, 0)]
+                for r in range(1, self.world):
+                    cols = ring_recv_batch(rings[r], names, dts)
+                    parts.append(ColumnBatch({k: cols[k] for k in schema}, None, tl))
+                return parts
+            ring_send_batch(rings[self.rank], payload, names)
+            rings[self.rank].check()
+            return None
+        from ..channel.pipe import PipeReader, PipeWriter, recv_batch, send_batch
+        if self.rank == 0:
+            parts = [payload if payload is not None else ColumnBatch({k: torch.empty(0, dtype=dts[k], device=dev) for k in names}, 0)]
+            for r in range(1, self.world):
+                cols = recv_batch(PipeReader(r, dev, tag=7), names)
+                parts.append(ColumnBatch({k: cols[k].to(dts[k]) if cols[k].numel() == 0 else cols[k] for k in schema}, None, tl))
+            return parts
+        if payload is None:
+            payload = ColumnBatch({k: torch.empty(0, dtype=dts[k], device=dev) for k in names}, 0)
+        send_batch(PipeWriter(0, dev, tag=7), payload)
+        return None
+
     def _gather_to_zero(self, child) -> Optional[List]:
         local = self.out[child.uid][self.rank]
         payload = local[0] if local is not None else None
         if self._all_columnar([payload], child.schema):
-            parts = self._allgather_batches(payload, child.schema, getattr(payload, "tuple_like", False))
-            return parts if self.rank == 0 else None
+            return self._pipe_to_zero(payload, child.schema)
         recs = self.backend.to_records(payload) if payload is not None else []
         bucket: Optional[List] = [None] * self.world if self.rank == 0 else None
         self._sync()

@@ -374,6 +374,19 @@ def gpu_checks(rank, world):
     assert torch.equal(win, full[:-2] + full[1:-1] + full[2:]), (rank, win[:4])
     assert ctx.__dict__.get("last_p2p_halos", 0) >= 1 and ctx.last_object_collectives == 0 and be.host_fallbacks == 0
 
+    # N:1 merges of columnar partials are streamed rank-to-rank channels: the p2p pipe, then the HBM ring
+    for pipe in ("nccl", "ring"):
+        ctx.spmd_pipe = pipe
+        tot = tbl.select(lambda r: r.v).sum_as_query().to_columns()
+        if rank == 0:
+            assert int(tot["value"][0].item()) == int(fv.sum()), (pipe, tot)
+        assert ctx.__dict__.get("last_streamed_edges", 0) >= 1 and ctx.last_object_collectives == 0, pipe
+        top = tbl.select(lambda r: r.v).order_by(lambda x: x).take(5).to_columns()
+        if rank == 0:
+            assert top["value"].cpu().tolist() == sorted(fv.tolist())[:5], pipe
+    ctx.spmd_pipe = "nccl"
+    assert be.host_fallbacks == 0, be.fallback_log
+
     # 5a. dimension join through the API: the planner picks the broadcast join (small inner side), the
     #     SPMD executor runs it as BroadcastJoin + generated probe; no object collectives
     nd = 3000                                            # dimension rows in total, sliced over the ranks
