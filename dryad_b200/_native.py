@@ -135,6 +135,16 @@ def _declare_kernels(lib):
     _sig(lib, "dryad_emit_ranges", c_int, [P, P, P, c_int64, P, P, P])
     _sig(lib, "dryad_kmeans_norms", c_int, [P, c_int, P, P])
     _sig(lib, "dryad_kmeans_assign", c_int, [P, c_int64, P, P, c_int, P, P, P, P, c_int, P])
+    _sig(lib, "dryad_chan_control_bytes", c_size_t, [c_int])
+    _sig(lib, "dryad_chan_create", c_int, [P, c_size_t, c_int, c_int, P, C.POINTER(c_void_p)])
+    _sig(lib, "dryad_chan_destroy", c_int, [P])
+    _sig(lib, "dryad_chan_alloc_block", c_int, [P, c_size_t, c_double, C.POINTER(c_void_p)])
+    _sig(lib, "dryad_chan_write_block", c_int, [P, P, c_size_t, P])
+    _sig(lib, "dryad_chan_close_writer", c_int, [P])
+    _sig(lib, "dryad_chan_read_block", c_int, [P, C.POINTER(c_void_p), C.POINTER(c_size_t), c_double, P])
+    _sig(lib, "dryad_chan_release_block", c_int, [P, P, P])
+    _sig(lib, "dryad_chan_total_length", c_int64, [P])
+    _sig(lib, "dryad_chan_stats", c_int, [P, C.POINTER(c_int64)])
     _sig(lib, "dryad_kmeans_sep", c_int, [P, c_int, P, P])
     _sig(lib, "dryad_kmeans_assign_exact", c_int, [P, c_int64, P, P, P, c_int, P, P, P, P, P, P, P, c_int, P])
     _sig(lib, "dryad_kmeans_update", c_int, [P, P, c_int, c_int, P, P, P, P])

@@ -141,6 +141,49 @@ class JobExecutor:
             ins.append([halo if i > 0 else []])
         return ins
 
+    # ---- restart descriptors (DumpRestartCommand, dvertexpncontrol.h:72; LocalDebuggingAndProfiling.cs) ----
+    def _dump_restart(self, node: DLinqQueryNode, part: int, version: int, ins, error: str) -> Optional[str]:
+        """A failed vertex leaves everything needed to run it ALONE again: its start command on the
+        native TLV wire format (stage, partition, version, input channel URIs) and its inputs as
+        partition files, under <job dir>/restart/.  `tools/rerun.py` replays it."""
+        import os
+        from ..channel import store
+        from .command import CMD_START, STATE_FAILED, VertexCommand
+        job_dir = getattr(self.reporter, "job_dir", None)
+        if not job_dir:
+            return None
+        d = os.path.join(job_dir, "restart")
+        os.makedirs(d, exist_ok=True)
+        stem = os.path.join(d, f"vertex-{node.uid}-{part}")
+        uris = []
+        try:
+            for k, payloads in enumerate(ins):
+                uri = f"partfile://{stem}-in{k}.pt"
+                store.write_table(uri, [self.backend.to_records(p) for p in payloads])
+                uris.append((uri, sum(self.backend.count(p) for p in payloads)))
+        except Exception:  # noqa: BLE001  (records that the wire format cannot carry: keep the command only)
+            uris = []
+        cmd = VertexCommand(CMD_START, node.uid, version, args=[node.name, str(part), str(len(ins))], inputs=uris,
+                            state=STATE_FAILED, exit_code=1, message=error[:4000])
+        with open(stem + ".cmd", "wb") as f:
+            f.write(cmd.serialize())
+        return stem + ".cmd"
+
+    def run_single_vertex(self, uid: int, part: int, inputs=None, restart_file: Optional[str] = None):
+        """Run ONE vertex of this plan outside the graph manager — from explicit inputs or from a
+        restart descriptor written by a failed job — and return its output ports."""
+        from ..channel import store
+        from .command import VertexCommand
+        node = next(n for n in self.plan.nodes if n.uid == uid)
+        version = 0
+        if inputs is None:
+            with open(restart_file, "rb") as f:
+                cmd = VertexCommand.parse(f.read())
+            version = cmd.version + 1
+            inputs = [[list(p) for p in store.open_table(u).partitions] for u, _ in cmd.inputs]
+        env = VertexEnv(self.context, node.uid, part, version)
+        return self.backend.run_vertex(node, part, inputs, env)
+
     # ---- placement (ClusterInterface + LocalScheduler roles) ---------------------------------------
     def _place(self, v: int, node: DLinqQueryNode, i: int, ins) -> Dict[str, Any]:
         """Choose the computer (GPU / worker slot) for one vertex: every input partition votes for the
@@ -245,6 +288,7 @@ class JobExecutor:
                 node, i = self._gm_stage_node[info["stage"]], info["part"]
                 rep.vertex_event(node, i, version, "starting")
                 t0 = time.perf_counter()
+                ins = []
                 try:
                     ins = self._inputs(node, i)
                     placed = self._place(v, node, i, ins) if ctx.schedule_vertices else None
@@ -272,13 +316,19 @@ class JobExecutor:
                     self._release_finished_children(node)
                 except Exception as ex:  # noqa: BLE001  (vertex code is user code)
                     text = "".join(traceback.format_exception_only(type(ex), ex)).strip()
-                    rep.vertex_event(node, i, version, "failed", error=text)
+                    rep.vertex_event(node, i, version, "failed", error=text,
+                                     **({"computer": self._placement.get((node.uid, i))} if (node.uid, i) in self._placement else {}))
                     bad = -1
                     if isinstance(ex, InputReadError):
                         want = (ex.producer_uid, ex.producer_part)
                         edges = self._gm_inputs.get(v, [])
                         bad = edges.index(want) if want in edges else -1
                     rc = gm.failed(v, version, text, bad_input=bad)
+                    if rc == 1 or ctx.compile_for_vertex_debugging:
+                        try:
+                            self._dump_restart(node, i, version, ins, text)
+                        except Exception:  # noqa: BLE001  (diagnostics must never mask the failure)
+                            pass
                     deterministic = isinstance(ex, DryadLinqException) and not getattr(ex, "transient", False)
                     if rc == 2:                      # producer revoked: it will be re-executed
                         self.out[ex.producer_uid][ex.producer_part] = None

@@ -51,6 +51,8 @@ def build_job(job_dir: str) -> Dict[str, Any]:
                                           "part": int(e.get("partInStage", 0)), "state": None, "start": None,
                                           "end": None, "error": None})
             a["state"] = e["state"]
+            if "computer" in e:
+                a["computer"] = e["computer"]
             if e["state"] == "starting":
                 a["start"] = e["ts"]
             else:
@@ -74,34 +76,75 @@ def build_job(job_dir: str) -> Dict[str, Any]:
                     job[k] = int(e[k])
     job["stages"] = sorted(stages.values(), key=lambda s: s["id"])
     job["attempts"] = sorted(attempts.values(), key=lambda a: (a["start"] or "", a["vertex"]))
+    # static plan as written by the client: a job whose plan file cannot be parsed never had a graph
+    plan_file = os.path.join(job_dir, "DryadLinqProgram__0.xml")
+    job["plan_error"] = None
+    if os.path.exists(plan_file):
+        try:
+            from ..plan import xmlplan
+            xmlplan.parse_query_xml(open(plan_file).read())
+        except Exception as ex:  # noqa: BLE001
+            job["plan_error"] = f"{type(ex).__name__}: {ex}"
     job["diagnosis"] = diagnose(job)
     return job
 
 
 def diagnose(job: Dict[str, Any]) -> List[str]:
-    """Post-mortem rules in the spirit of Diagnosis.cs."""
+    """Post-mortem rules, one per failure family of the reference's diagnosis engine
+    (JobBrowser/JobBrowser/Diagnosis.cs: stack overflow :441, serialization error :545, failed when
+    reading :573, XML plan parse error :673, correlated machine failures :749, deterministic input
+    failure :807, correlated read failures :858), plus the families this engine adds (checked
+    arithmetic, memory, lost rank, stage-wide operator failure)."""
     out: List[str] = []
+    if job.get("plan_error"):
+        out.append(f"the XML query plan cannot be parsed ({job['plan_error']}): the graph manager never built a graph — "
+                   "client and graph manager disagree on the plan format")
     failed = [a for a in job["attempts"] if a["state"] == "failed"]
     if not failed and job.get("success"):
-        return ["job succeeded; no failed vertex attempts"]
+        return out + ["job succeeded; no failed vertex attempts"]
     by_vertex = defaultdict(list)
     for a in failed:
         by_vertex[a["vertex"]].append(a)
+    read_fail = lambda m: "cannot read" in m.lower() or "ReadFileError" in m or "StreamDoesNotExist" in m   # noqa: E731
+    readers = []
     for v, atts in by_vertex.items():
         errs = {(a["error"] or "").split(":")[0] for a in atts}
         msg = (atts[-1]["error"] or "")
-        if len(atts) >= 2 and len(errs) == 1:
+        same = len(atts) >= 2 and len(errs) == 1
+        if same and not read_fail(msg):
             out.append(f"vertex {v} failed {len(atts)} times with the same error ({msg[:120]}): deterministic failure — "
                        "most likely a bug in the user function or bad input records, not the cluster")
+        if "RecursionError" in msg or "stack overflow" in msg.lower() or "maximum recursion depth" in msg:
+            out.append(f"vertex {v}: stack overflow — unbounded recursion in the user function (or a very deep expression)")
         if "TypeNotSerializable" in msg or "FailedToDeserialize" in msg or "pickle" in msg.lower():
             out.append(f"vertex {v}: serialization error — a record type cannot be (de)serialised")
-        if "cannot read" in msg.lower() or "ReadFileError" in msg or "StreamDoesNotExist" in msg:
-            out.append(f"vertex {v}: failed while READING its input — the producer's output was lost or is corrupt; "
-                       "the graph manager re-executes the producer")
-        if "overflow" in msg.lower():
+        if read_fail(msg):
+            readers.append(v)
+            if same:
+                out.append(f"vertex {v} failed {len(atts)} times READING the same input: deterministic input failure — the "
+                           "stored data itself is bad (corrupt partition file or a record the reader cannot decode); "
+                           "re-running the producer will not help")
+            else:
+                out.append(f"vertex {v}: failed while READING its input — the producer's output was lost or is corrupt; "
+                           "the graph manager re-executes the producer")
+        if "overflow" in msg.lower() and "stack" not in msg.lower():
             out.append(f"vertex {v}: checked arithmetic overflow in an aggregate")
         if "MemoryError" in msg or "out of memory" in msg.lower():
             out.append(f"vertex {v}: ran out of memory — increase the partition count")
+        if "rank lost" in msg or "did not report" in msg:
+            out.append(f"stage {v.split('.')[0]}: a rank stopped answering the graph manager (process died or hung); the job was aborted on every rank")
+    if len(readers) >= 2:
+        out.append(f"correlated read failures: {len(readers)} vertices ({', '.join(sorted(readers)[:6])}) failed reading their inputs — "
+                   "look at the storage / the producing stage they share, not at the readers")
+    machines = defaultdict(set)
+    for a in failed:
+        if a.get("computer") is not None:
+            machines[a["computer"]].add(a["vertex"])
+    all_machines = {a.get("computer") for a in job["attempts"] if a.get("computer") is not None}
+    for m, vs in machines.items():
+        if len(vs) >= 2 and len(all_machines) > 1 and sum(len(x) for x in machines.values()) == len(vs):
+            out.append(f"correlated machine failures: all {len(vs)} failed vertices ran on computer {m} while the other "
+                       f"{len(all_machines) - 1} computers had none — suspect that GPU / worker, not the program")
     stages_failed = {a["stage"] for a in failed}
     if len(by_vertex) >= 3 and len(stages_failed) == 1:
         out.append(f"{len(by_vertex)} different vertices of stage {next(iter(stages_failed))} failed: the stage's "

@@ -264,6 +264,28 @@ int dryad_ring_pop(void* dst, uint64_t dst_cap, uint64_t* out_len, const void* r
                    uint64_t* done_local, uint64_t seq, int slots, uint64_t slot_bytes,
                    int32_t* status, void* stream);
 
+/* ---- Block channel over device partitions (the C ABI between a vertex and the engine):
+ *      DryadVertex/VertexHost/vertex/include/wrappernativeinfo.h:103-150, LinqToDryad/DryadLinqNative.cs:76-145,
+ *      bounded FIFO with throttling: DryadVertex/VertexHost/system/channel/src/channelfifo.cpp -----------------
+ * The pool is a caller-provided device buffer of nblocks * block_bytes bytes (for instance a slice of the
+ * symmetric arena): nothing is allocated.  alloc_block waits (up to timeout_s, then DRYAD_ERR_OVERFLOW) while
+ * every block is in use: a writer is at most nblocks blocks ahead of the reader.  write_block publishes a block
+ * with an event on the writer's stream; read_block returns 0 and the next block (the reader's stream waits for
+ * that event), 1 at end of stream, DRYAD_ERR_OVERFLOW on timeout; release_block returns the block to the pool
+ * once the work queued on the reader's stream has finished.  checksum != 0 adds an integrity check of every
+ * block (checksum kernel on both sides, mismatches counted in stats[4]); it needs `control`, device memory of
+ * dryad_chan_control_bytes(nblocks) bytes.  Thread-safe: one writer thread and one reader thread may stream. */
+size_t dryad_chan_control_bytes(int nblocks);
+int dryad_chan_create(void* buffer, size_t block_bytes, int nblocks, int checksum, void* control, void** out);
+int dryad_chan_destroy(void* chan);
+int dryad_chan_alloc_block(void* chan, size_t bytes, double timeout_s, void** dev_ptr);
+int dryad_chan_write_block(void* chan, void* dev_ptr, size_t nbytes, void* stream);
+int dryad_chan_close_writer(void* chan);
+int dryad_chan_read_block(void* chan, void** dev_ptr, size_t* nbytes, double timeout_s, void* stream);
+int dryad_chan_release_block(void* chan, void* dev_ptr, void* stream);
+int64_t dryad_chan_total_length(void* chan);
+int dryad_chan_stats(void* chan, int64_t* out5);
+
 /* ---- NVLS (NVSwitch multicast / in-switch reduction) ----------------------------------------------
  * `mc` is the multicast address of a symmetric buffer (every GPU of the group has a copy at the same
  * offset; the mapping is made by the caller, e.g. torch's symmetric-memory rendezvous).

@@ -126,3 +126,65 @@ def test_memory_fifo_channels_form_start_cliques_and_results_are_unchanged(monke
     assert sorted(q.to_list()) == want
     gm = ctx.last_executor.gm
     assert any(len(gm.clique(v)) > 1 for v in range(gm.live_vertices))
+
+
+def test_failed_vertex_leaves_a_restart_descriptor_and_can_be_rerun_alone(tmp_path):
+    """DumpRestartCommand + local re-run of one failed vertex (LocalDebuggingAndProfiling role)."""
+    from dryad_b200.tools import rerun
+    ctx = _ctx(tmp_path, parts=2)
+    state = {"broken": True}
+
+    def f(x):
+        if state["broken"] and x == 37:
+            raise ValueError("bad record 37")
+        return x * 10
+    q = ctx.from_enumerable(DATA, 2).select(lambda x: x + 0).where(lambda x: x >= 0).select(f)
+    with pytest.raises(DryadLinqException):
+        q.to_list()
+    job_dir = os.path.join(str(tmp_path), "LocalJobs", "1")
+    found = rerun.list_restarts(job_dir)
+    assert len(found) == 1 and "bad record 37" in found[0]["error"] and found[0]["inputs"]
+    tag = f"{found[0]['stage']}.{found[0]['partition']}"
+    assert rerun.main([job_dir]) == 0
+    with pytest.raises(ValueError):                      # same inputs, same code: same failure, now under a debugger
+        rerun.replay(q, job_dir, tag)
+    state["broken"] = False                              # "fix the bug", replay only that vertex
+    ports = rerun.replay(q, job_dir, tag, profile=True)
+    half = DATA[:50] if found[0]["partition"] == 0 else DATA[50:]
+    assert list(ports[0]) == [x * 10 for x in half]
+    # the diagnosis names the failure family
+    job = jobreport.build_job(job_dir)
+    assert any("deterministic failure" in d for d in job["diagnosis"])
+
+
+def test_diagnosis_rule_families(tmp_path):
+    """One synthetic event log per failure family of the diagnosis engine (Diagnosis.cs rule set)."""
+    def job(events, plan="<Query><DryadLinqVersion>x</DryadLinqVersion><QueryPlan></QueryPlan></Query>"):
+        d = tmp_path / f"job{len(list(tmp_path.iterdir()))}"
+        (d / "log").mkdir(parents=True)
+        lines = ["t0,start,job=j,stages=2", "t0,topology,stage=1,stagename=Select,type=Select,partitions=4,children="]
+        for i, (vertex, version, state, kv) in enumerate(events):
+            body = ",".join(f"{k}={v}" for k, v in kv.items())
+            lines.append(f"t{i + 1},vertex,vertex={vertex},version={version},stagename=Select,stage=1,partInStage={vertex.split('.')[1]},state={state}" + ("," + body if body else ""))
+        lines.append("tz,stop,success=False,error=boom")
+        (d / "calypso.log").write_text("\n".join(lines) + "\n")
+        if plan is not None:
+            (d / "DryadLinqProgram__0.xml").write_text(plan)
+        return jobreport.build_job(str(d))["diagnosis"]
+    so = job([("1.0", 0, "failed", {"error": "RecursionError: maximum recursion depth exceeded"})])
+    assert any("stack overflow" in x for x in so)
+    ser = job([("1.0", 0, "failed", {"error": "PicklingError: cannot pickle lambda"})])
+    assert any("serialization error" in x for x in ser)
+    rd = job([("1.0", 0, "failed", {"error": "InputReadError: cannot read output of stage 0[0]"}), ("1.0", 1, "completed", {})])
+    assert any("failed while READING" in x for x in rd)
+    det_in = job([("1.0", v, "failed", {"error": "InputReadError: cannot read output of stage 0[0]"}) for v in range(3)])
+    assert any("deterministic input failure" in x for x in det_in)
+    corr = job([("1.0", 0, "failed", {"error": "ReadFileError: x"}), ("1.1", 0, "failed", {"error": "ReadFileError: y"})])
+    assert any("correlated read failures" in x for x in corr)
+    mach = job([("1.0", 0, "failed", {"error": "RuntimeError: a", "computer": 2}), ("1.1", 0, "failed", {"error": "RuntimeError: b", "computer": 2}),
+                ("1.2", 0, "completed", {"computer": 0}), ("1.3", 0, "completed", {"computer": 1})])
+    assert any("correlated machine failures" in x and "computer 2" in x for x in mach)
+    bad_plan = job([("1.0", 0, "failed", {"error": "RuntimeError: a"})], plan="<Query><Broken")
+    assert any("XML query plan cannot be parsed" in x for x in bad_plan)
+    lost = job([("1.0", 0, "failed", {"error": "rank 1 did not report stage 1 v0 within 60 s (rank lost)"})])
+    assert any("stopped answering" in x for x in lost)
