@@ -355,6 +355,8 @@ class DryadLinqContext:
 
     def _read_table_partition(self, table: Table, i: int):
         p = table.partitions[i]
+        if hasattr(p, "data") and hasattr(p, "to_records"):
+            return p              # raw text partition: lines are materialised only if a vertex iterates it
         if hasattr(p, "to_records"):
             return p.to_records() if self._backend().wants_records else p
         return p

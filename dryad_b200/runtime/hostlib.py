@@ -114,6 +114,12 @@ _d("cache_put", c_int, [P, c_char_p, c_char_p, c_int64])
 _d("cache_get", c_int64, [P, c_char_p, c_char_p, c_int64])
 _d("cache_stats", c_int, [P] + [C.POINTER(c_int64)] * 4)
 _d("fprint64", c_uint64, [c_uint64, c_char_p, c_int64])
+_d("hv_split_count", P, [c_char_p, c_int64, c_int, c_int, c_int])
+_d("hv_groups", c_int64, [P])
+_d("hv_word_bytes", c_int64, [P])
+_d("hv_total", c_int64, [P])
+_d("hv_export", None, [P, c_char_p, C.POINTER(c_int64), C.POINTER(c_int64)])
+_d("hv_free", None, [P])
 _d("cpu_wordcount", c_int64, [c_char_p, c_int64, c_int, c_int, C.POINTER(c_int64)])
 _d("cpu_sort_rows", c_int, [P, c_int64, c_int, c_int, c_int, P])
 _d("cpu_groupby_sum_count", c_int64, [P, P, c_int64, c_int, C.POINTER(c_int64)])

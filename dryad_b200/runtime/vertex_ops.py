@@ -97,11 +97,68 @@ class VertexEnv:
         return path
 
 
+def _native_split_count(members, inputs, env):
+    """Traced pipeline [SelectMany(l => l.Split(c)), GroupBy(w => w, partial, Count only)] over raw text
+    partitions: the whole vertex body runs in the native host library (csrc/host/vertex_native.cpp
+    `hv_split_count`) instead of over Python records.  Returns the partial-aggregate records
+    [(word, [count])] and the number of members consumed, or None when the pattern does not apply."""
+    from ..expr import ir as X
+    if len(members) < 2 or members[0].type != NodeType.SelectMany or members[1].type != NodeType.GroupBy:
+        return None
+    sm, gb = members[0].params, members[1].params
+    ir = sm["fn"].ir
+    if sm.get("indexed") or sm.get("result") is not None or not isinstance(ir, X.Expr) or ir.op != "split":
+        return None
+    dec = gb.get("decomp")
+    key_ir = getattr(gb.get("key"), "ir", None)
+    if dec is None or gb.get("mode") not in ("partial_acc", "full_acc") or gb.get("elem") is not None or gb.get("comparer") is not None:
+        return None
+    if not (isinstance(key_ir, X.Expr) and key_ir.op == "col" and key_ir.kind == "s"):
+        return None
+    if len(dec.aggs) != 1 or dec.aggs[0].kind != "count":
+        return None
+    parts = [p for p in inputs[0]]
+    if not parts or not all(isinstance(getattr(p, "data", None), (bytes, bytearray)) and getattr(p, "device_buf", None) is None
+                            for p in parts):
+        return None
+    if any(b"\r" in p.data for p in parts):
+        return None                                   # CRLF text: the record reader strips the '\r'
+    import ctypes as C
+    from .. import _native as N
+    lib = N.host()
+    delim = ir.args[1].encode("utf-8")
+    merged: dict = {}
+    for p in parts:
+        h = lib.hv_split_count(p.data, len(p.data), delim[0], 1, env.threads_per_worker)
+        try:
+            g, nb = lib.hv_groups(h), lib.hv_word_bytes(h)
+            words = C.create_string_buffer(max(nb, 1))
+            offs = (C.c_int64 * (g + 1))()
+            cnts = (C.c_int64 * max(g, 1))()
+            lib.hv_export(h, words, offs, cnts)
+        finally:
+            lib.hv_free(h)
+        raw = words.raw
+        for i in range(g):
+            w = raw[offs[i]:offs[i + 1]].decode("utf-8")
+            merged[w] = merged.get(w, 0) + cnts[i]
+    return [(w, [c]) for w, c in merged.items()], 2
+
+
 def run(node: DLinqQueryNode, part: int, inputs: List[List], env: VertexEnv) -> List[List]:
     if node.type == NodeType.Super:
         cur = inputs
         out: List[List] = []
-        for m in node.members:
+        members = list(node.members)
+        fast = _native_split_count(members, inputs, env)
+        if fast is not None:
+            recs, used = fast
+            out = [recs]
+            cur = [[recs]]
+            members = members[used:]
+            env.native_vertices = getattr(env, "native_vertices", 0) + 1
+            env.context.__dict__["native_host_vertices"] = env.context.__dict__.get("native_host_vertices", 0) + 1
+        for m in members:
             out = run(m, part, cur, env)
             cur = [[out[0]]]
         return out

@@ -141,6 +141,16 @@ int affinity_merge(int n, const int32_t* computer, const int64_t* weight, const 
                    double threshold, int32_t* choice);
 
 /* ---- timed CPU baselines (multi-threaded restatements of the benchmark queries) ------------------ */
+/* Native host vertex operators for traced string pipelines (csrc/host/vertex_native.cpp):
+ * SelectMany(line.Split(delim)) -> GroupBy(word) with Count(), from raw text bytes (LinqToDryad/
+ * DryadLinqVertex.cs:5718-6032, samples/WordCount.cs.pp:72-75).  The handle owns the group table. */
+void* hv_split_count(const char* text, int64_t n, int delim, int keep_empty, int threads);
+int64_t hv_groups(void* h);
+int64_t hv_word_bytes(void* h);
+int64_t hv_total(void* h);
+void hv_export(void* h, char* words, int64_t* offsets, int64_t* counts);
+void hv_free(void* h);
+
 int64_t cpu_wordcount(const char* text, int64_t n, int threads, int keep_empty, int64_t* total_tokens);
 int cpu_sort_rows(const uint8_t* rows, int64_t n, int width, int key_len, int threads, uint8_t* out);
 int64_t cpu_groupby_sum_count(const int64_t* keys, const int64_t* vals, int64_t n, int threads, int64_t* checksum);
