@@ -114,3 +114,62 @@ class ChannelReader:
             return
         else:
             raise ValueError(f"unknown channel scheme {self.scheme!r}")
+
+
+class VertexReader:
+    """Multi-port input of a vertex (DryadLinqVertexReader, LinqToDryad/DryadLinqVertexReader.cs:41-257):
+    one record reader per input channel, read one port after the other.  Unless `keep_port_order` the
+    ports are visited in a random permutation, so that the consumers of a CrossProduct edge do not all
+    pull from producer 0 first (`VertexReader.cs:67-83`); the permutation is seeded by the vertex id,
+    which makes a retried vertex read in the same order."""
+
+    def __init__(self, uris: List[str], keep_port_order: bool = True, seed: int = 0):
+        self.ports = [ChannelReader(u) for u in uris]
+        self.order = list(range(len(self.ports)))
+        if not keep_port_order and len(self.order) > 1:
+            import random
+            random.Random(seed).shuffle(self.order)
+
+    def port(self, i: int) -> ChannelReader:
+        return self.ports[i]
+
+    def __iter__(self) -> Iterator:
+        for i in self.order:
+            yield from self.ports[i]
+
+
+class VertexWriter:
+    """Multi-port output of a vertex (DryadLinqVertexWriter, LinqToDryad/DryadLinqVertexWriter.cs:41-187):
+    distributors write each record to the port its partition function picked (`WriteItem(item, port)`),
+    Fork hands one record writer per branch (`GetRecordWriter(port)`)."""
+
+    def __init__(self, uris: List[str]):
+        self.ports = [ChannelWriter(u) for u in uris]
+
+    def write_item(self, item, port: int) -> None:
+        self.ports[port].write(item)
+
+    def write_item_sequence(self, items, port: int = 0) -> None:
+        w = self.ports[port]
+        for it in items:
+            w.write(it)
+
+    def get_record_writer(self, port: int) -> ChannelWriter:
+        return self.ports[port]
+
+    @property
+    def records(self) -> List[int]:
+        return [w.records for w in self.ports]
+
+    def close(self) -> None:
+        for w in self.ports:
+            w.close()
+
+
+def port_order(nports: int, keep_port_order: bool, seed: int) -> List[int]:
+    """The order in which a vertex visits its input ports (see VertexReader)."""
+    order = list(range(nports))
+    if not keep_port_order and nports > 1:
+        import random
+        random.Random(seed).shuffle(order)
+    return order

@@ -188,7 +188,12 @@ def _merge(node, part, inputs, env):
         key = _kfn(p["sort_key"])
         runs = [list(r) for r in inputs[0]]
         return [list(heapq.merge(*runs, key=key, reverse=bool(p.get("descending"))))]
-    return [_cat(inputs[0])]           # port order is preserved (keepPortOrder)
+    if p.get("keep_port_order", True):
+        return [_cat(inputs[0])]       # port order is preserved (keepPortOrder)
+    # unordered merge: ports are read in a permutation seeded by the vertex id (VertexReader.cs:67-83)
+    from ..channel.factory import port_order
+    ports = list(inputs[0])
+    return [_cat([ports[i] for i in port_order(len(ports), False, env.vertex_id * 7919 + part)])]
 
 
 def _tee(node, part, inputs, env):

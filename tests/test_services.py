@@ -76,3 +76,25 @@ def test_vertices_are_placed_by_the_delay_scheduler_and_records_keep_locality(tm
     # pointwise stages follow their input: everything they read is local to the computer they ran on
     follow = [l for l in placed if "locality=computer" in l]
     assert follow and all("remote=0" in l for l in follow)
+
+
+def test_multi_port_vertex_reader_and_writer(tmp_path):
+    """WriteItem(item, port) / per-port record writers / permuted multi-port reads over file and FIFO channels."""
+    from dryad_b200.channel.factory import VertexReader, VertexWriter, port_order
+    uris = [f"file://{tmp_path}/p{i}.bin" for i in range(3)] + ["fifo://32/mp_test_3"]
+    w = VertexWriter(uris)
+    for x in range(40):
+        w.write_item((x, f"v{x}"), x % 4)
+    w.get_record_writer(0).write((999, "extra"))
+    assert w.records == [11, 10, 10, 10]
+    w.close()
+    ordered = list(VertexReader(uris, keep_port_order=True))
+    assert [r[0] for r in ordered[:11]] == [0, 4, 8, 12, 16, 20, 24, 28, 32, 36, 999]
+    assert sorted(r[0] for r in ordered) == sorted(list(range(40)) + [999])
+    w2 = VertexWriter(uris[:3])
+    w2.write_item_sequence([1, 2, 3], port=2)
+    w2.close()
+    assert port_order(8, False, 5) == port_order(8, False, 5) != list(range(8))     # seeded: retries read in the same order
+    assert port_order(8, True, 5) == list(range(8))
+    shuffled = VertexReader(uris[:3], keep_port_order=False, seed=5)
+    assert sorted(shuffled.order) == [0, 1, 2] and list(shuffled) == [1, 2, 3]
