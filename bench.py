@@ -267,6 +267,7 @@ def main():
                 base["terasort_e2e"] = {"ms_per_step": be_ms, "GB_per_s": world * n * W / (be_ms * 1e-3) / 1e9,
                                         "h2d_bytes_per_step": n * W, "d2h_bytes_per_step": 8}
             del host_out
+            ctx.dispose()                        # frees this context's symmetric arena (a third of HBM) for what follows
         except Exception as ex:  # noqa: BLE001
             e2e = {"error": f"{type(ex).__name__}: {ex}"}
 
@@ -384,6 +385,7 @@ def main():
                 api_loop(5)
                 barrier()
                 extra["kmeans"]["api_do_while_s_per_iteration"] = max_over_ranks((time.perf_counter() - t_api) / 5)
+                kctx.dispose()
             except Exception as ex:  # noqa: BLE001
                 extra["kmeans"]["api_do_while_error"] = f"{type(ex).__name__}: {ex}"
             if not a.skip_baseline:

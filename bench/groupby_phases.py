@@ -21,7 +21,7 @@ dev = torch.device("cuda", lr)
 if world > 1:
     os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
     dist.init_process_group("nccl", device_id=dev)
-keys, vals = groupby.generate(n, nkeys, 11, dev, rank)
+keys, vals = groupby.generate(n, nkeys, 11, dev, rank, sparse=(len(sys.argv) > 3 and sys.argv[3] == "sparse"))
 fcap = K.agg_capacity(int(1.25 * nkeys) // world + 1024)
 arena = SymmetricArena(fcap * 8 * 3 + (fcap // 3 + 1024) * world * 24 + (16 << 20), rank, world, None, dev)
 agg = DistributedHashAggregate(arena, ["sum_i64", "count"], K.agg_capacity(nkeys), fcap)

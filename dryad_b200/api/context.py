@@ -189,6 +189,18 @@ class DryadLinqContext:
         cp = self.__dict__.pop("_control_plane", None)
         if cp is not None:
             cp.close()                       # the graph manager's mailbox service (SPMD jobs)
+        for name in ("_exchange_cache", "_dagg_cache", "_bjoin_cache", "_halo_cache", "_gather_rings"):
+            self.__dict__.pop(name, None)
+        self._sorters.clear()
+        if self._arena is not None:          # the symmetric arena (IPC-mapped by the peers): a collective teardown
+            arena, self._arena = self._arena, None
+            try:
+                if self.world > 1:
+                    import torch.distributed as dist
+                    dist.barrier()           # nobody still reads a peer's arena
+                arena.close()
+            except Exception:  # noqa: BLE001
+                pass
 
     Dispose = dispose
 
@@ -500,10 +512,13 @@ class DryadLinqContext:
         out: List = []
         for i in range(t.partition_count):
             p = t.partitions[i]
+            if p is None:
+                continue                       # SPMD: a partition that lives on another rank
             out.extend(p.to_records() if hasattr(p, "to_records") else p)
         return out
 
     def _execute_to_partitions(self, q: Query) -> List[List]:
         res = self._execute(q)
         t: Table = res.expr.params["table"]
-        return [list(p.to_records() if hasattr(p, "to_records") else p) for p in t.partitions]
+        # SPMD tables hold None for the partitions of other ranks: only the local ones are returned
+        return [list(p.to_records() if hasattr(p, "to_records") else p) for p in t.partitions if p is not None]

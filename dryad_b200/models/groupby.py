@@ -116,6 +116,8 @@ def bench_api(rank, world, dev, n, nkeys, steps, warmup, max_over_ranks, barrier
     if world > 1:
         import torch.distributed as dist
         dist.all_reduce(tot)
-    return {"value": world * n / (ms * 1e-3), "unit": "rows/s", "ms_per_step": ms, "h2d_bytes_per_step": 16 * n,
-            "d2h_bytes_per_step": 16, "groups_out": int(tot[0]), "valid": int(tot[1]) == world * n,
-            "host_fallbacks": ctx._backend().host_fallbacks}
+    res = {"value": world * n / (ms * 1e-3), "unit": "rows/s", "ms_per_step": ms, "h2d_bytes_per_step": 16 * n,
+           "d2h_bytes_per_step": 16, "groups_out": int(tot[0]), "valid": int(tot[1]) == world * n,
+           "host_fallbacks": ctx._backend().host_fallbacks}
+    ctx.dispose()
+    return res

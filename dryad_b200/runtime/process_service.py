@@ -30,12 +30,27 @@ class ProcessService:
         svc = self
 
         class Handler(BaseHTTPRequestHandler):
+            protocol_version = "HTTP/1.1"       # keep-alive: a worker keeps ONE connection for all its polls and reports
+
             def log_message(self, *a):
                 pass
 
+            def setup(self):
+                super().setup()
+                import socket
+                self.request.setsockopt(socket.IPPROTO_TCP, socket.TCP_NODELAY, 1)   # small messages: no 40 ms delayed-ACK stalls
+
+            def end_headers(self):
+                if not any(h.lower().startswith(b"content-length") for h in getattr(self, "_headers_buffer", [])):
+                    self.send_header("Content-Length", "0")
+                super().end_headers()
+
             def _mb(self, pid: str) -> Mailbox:
                 with svc._lock:
-                    return svc.mailboxes.setdefault(pid, Mailbox())
+                    m = svc.mailboxes.get(pid)
+                    if m is None:
+                        m = svc.mailboxes[pid] = Mailbox()
+                    return m
 
             def do_PUT(self):
                 u = urllib.parse.urlparse(self.path)
@@ -43,10 +58,22 @@ class ProcessService:
                 parts = u.path.strip("/").split("/")
                 body = self.rfile.read(int(self.headers.get("Content-Length", 0) or 0))
                 if len(parts) == 3 and parts[0] == "process" and parts[2] == "setvalue":
-                    v = self._mb(parts[1]).set(q["key"][0], q.get("status", [""])[0], body)
+                    mb = self._mb(parts[1])
+                    v = mb.set(q["key"][0], q.get("status", [""])[0], body)
+                    got = None
+                    if "wait" in q:
+                        # report-and-wait: the same exchange long-polls another key (a worker hands in its
+                        # status and receives its next command in one round trip)
+                        got = mb.block_on_status(q["wait"][0], int(q.get("version", ["0"])[0]), float(q.get("timeout", ["1"])[0]))
                     self.send_response(200)
-                    self.send_header(H_VERSION, str(v))
+                    self.send_header(H_VERSION, str(got[0] if got else v))
+                    if got:
+                        self.send_header(H_STATUS, got[1])
+                        self.send_header("X-Dryad-Waited", "1")
+                        self.send_header("Content-Length", str(len(got[2])))
                     self.end_headers()
+                    if got:
+                        self.wfile.write(got[2])
                 elif len(parts) == 3 and parts[0] == "process" and parts[2] == "launch":
                     cmd = body.decode().split("\x00")
                     log = open(os.path.join(svc.root, f"process-{parts[1]}-stdout.txt"), "wb")
@@ -80,6 +107,8 @@ class ProcessService:
                         self.send_header(H_STATUS, got[1])
                     if p is not None and p.poll() is not None:
                         self.send_header(H_EXIT, str(p.returncode))
+                    if got:
+                        self.send_header("Content-Length", str(len(got[2])))
                     self.end_headers()
                     if got:
                         self.wfile.write(got[2])
@@ -107,7 +136,13 @@ class ProcessService:
                     self.send_response(404)
                     self.end_headers()
 
-        self.httpd = ThreadingHTTPServer((host, port), Handler)
+        class Server(ThreadingHTTPServer):
+            # every worker of a job long-polls and reports at the same instant: the default listen
+            # backlog of 5 drops connections (1 s SYN retransmits) from 8 ranks on
+            request_queue_size = 256
+            daemon_threads = True
+
+        self.httpd = Server((host, port), Handler)
         self.port = self.httpd.server_address[1]
         self.uri = f"http://{host}:{self.port}"
         self._thread = threading.Thread(target=self.httpd.serve_forever, daemon=True)

@@ -763,7 +763,13 @@ class SpmdExecutor(JobExecutor):
             node = _tail(root)
             mine = self.rank if root.partition_count == self.world else 0
             payload = self.out[root.uid][mine]
-            parts = [payload[0]] if payload is not None else [[]]
+            if root.partition_count == self.world:
+                # a distributed table: every rank holds ITS partition, the others are None (the same
+                # layout from_columns / from_rows build), so a later query sees `world` partitions
+                parts = [None] * self.world
+                parts[self.rank] = payload[0] if payload is not None else []
+            else:
+                parts = [payload[0]] if payload is not None else [[]]
             uri = node.params.get("uri")
             if uri and self.world > 1:
                 tmp = final = None

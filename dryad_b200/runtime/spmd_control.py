@@ -65,12 +65,42 @@ class ControlPlane:
         dist.broadcast_object_list(uri, src=0)            # bootstrap only: where the mailbox lives
         self.uri = uri[0]
         self.commands_delivered = 0
+        self._conn = None                     # persistent HTTP connection of a worker rank
+        self._prefetched = None               # next command, when it arrived with the last status report
 
     # ---- mailbox access: rank 0 talks to the native mailboxes directly, the others over HTTP ------
     def _mbox(self, r: int):
         from .services import Mailbox
         with self.service._lock:
-            return self.service.mailboxes.setdefault(f"rank-{r}", Mailbox())
+            m = self.service.mailboxes.get(f"rank-{r}")
+            if m is None:
+                m = self.service.mailboxes[f"rank-{r}"] = Mailbox()
+            return m
+
+    def _request(self, method: str, path: str, body: bytes = b"", timeout: float = 30.0):
+        """One HTTP exchange on the rank's keep-alive connection (reconnects once when it was dropped)."""
+        import http.client
+        u = urllib.parse.urlparse(self.uri)
+        for attempt in (0, 1):
+            try:
+                if self._conn is None:
+                    import socket
+                    self._conn = http.client.HTTPConnection(u.hostname, u.port, timeout=timeout)
+                    self._conn.connect()
+                    self._conn.sock.setsockopt(socket.IPPROTO_TCP, socket.TCP_NODELAY, 1)
+                self._conn.sock.settimeout(timeout)
+                self._conn.request(method, path, body=body or None, headers={"Content-Length": str(len(body))} if body else {})
+                resp = self._conn.getresponse()
+                data = resp.read()
+                return resp.status, resp.headers, data
+            except (http.client.HTTPException, OSError) as ex:
+                try:
+                    self._conn.close()
+                except Exception:  # noqa: BLE001
+                    pass
+                self._conn = None
+                if attempt:
+                    raise RankLost(f"rank {self.rank}: the graph manager's mailbox is unreachable ({ex})") from ex
 
     def post_command(self, cmd: VertexCommand) -> None:
         """GM side: deliver one launch descriptor to every rank's mailbox."""
@@ -87,10 +117,14 @@ class ControlPlane:
             if left <= 0:
                 raise RankLost(f"rank {self.rank}: no command from the graph manager for {self.timeout:.0f} s")
             poll = min(left, 5.0)
-            if self.rank == 0:
+            if self._prefetched is not None:                  # delivered together with the last status report
+                got, self._prefetched = self._prefetched, None
+            elif self.rank == 0:
                 got = self._mbox(0).block_on_status("cmd", self._seen["cmd"], poll)
             else:
                 got = self._http_get(f"rank-{self.rank}", "cmd", self._seen["cmd"], poll)
+            if got and got[0] <= self._seen["cmd"]:
+                got = None
             if got:
                 self._seen["cmd"] = got[0]
                 cmd = VertexCommand.parse(got[2])
@@ -105,9 +139,12 @@ class ControlPlane:
         if self.rank == 0:
             self._mbox(0).set("status", "completed" if ok else "failed", data)
         else:
-            q = urllib.parse.urlencode({"key": "status", "status": "completed" if ok else "failed"})
-            req = urllib.request.Request(f"{self.uri}/process/rank-{self.rank}/setvalue?{q}", data=data, method="PUT")
-            urllib.request.urlopen(req, timeout=self.timeout).read()
+            # report and long-poll the next command in ONE exchange
+            q = urllib.parse.urlencode({"key": "status", "status": "completed" if ok else "failed", "wait": "cmd",
+                                        "version": self._seen["cmd"], "timeout": 5.0})
+            status, headers, body = self._request("PUT", f"/process/rank-{self.rank}/setvalue?{q}", data, self.timeout)
+            if status == 200 and headers.get("X-Dryad-Waited") == "1":
+                self._prefetched = (int(headers.get(H_VERSION, "0")), headers.get(H_STATUS, ""), body)
 
     def collect(self, uid: int, version: int) -> Tuple[bool, str]:
         """GM side: wait for every rank's status block of (stage, version).  A rank that does not
@@ -135,13 +172,10 @@ class ControlPlane:
 
     def _http_get(self, pid: str, key: str, seen: int, timeout: float):
         q = urllib.parse.urlencode({"key": key, "version": seen, "timeout": timeout})
-        try:
-            with urllib.request.urlopen(f"{self.uri}/process/{pid}/status?{q}", timeout=timeout + 10.0) as resp:
-                if resp.status != 200:
-                    return None
-                return int(resp.headers.get(H_VERSION, "0")), resp.headers.get(H_STATUS, ""), resp.read()
-        except urllib.error.URLError as ex:
-            raise RankLost(f"rank {self.rank}: the graph manager's mailbox is unreachable ({ex})") from ex
+        status, headers, data = self._request("GET", f"/process/{pid}/status?{q}", b"", timeout + 10.0)
+        if status != 200:
+            return None
+        return int(headers.get(H_VERSION, "0")), headers.get(H_STATUS, ""), data
 
     # ---- agreement point ------------------------------------------------------------------------
     def agree(self, ok: bool = True) -> bool:
@@ -151,6 +185,9 @@ class ControlPlane:
         return bool(int(t.item()))
 
     def close(self) -> None:
+        if self._conn is not None:
+            self._conn.close()
+            self._conn = None
         if self.service is not None:
             self.service.close()
             self.service = None
