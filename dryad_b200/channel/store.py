@@ -19,8 +19,9 @@ from .. import _native as N
 from ..api.errors import DryadLinqException, ErrorCode
 from ..api.types import LineRecord
 from . import records as R
+from .provider import DataProvider, StreamInfo
 
-SCHEMES = ("partfile", "file", "hdfs", "wasb", "azureblob", "hpcdsc")
+SCHEMES = ("partfile", "file", "hdfs", "wasb", "azureblob", "hpcdsc")      # the reference's scheme names
 
 
 class StoredTable:
@@ -32,21 +33,17 @@ def parse_uri(uri: str):
     if "://" not in uri:
         return "partfile", uri
     scheme, rest = uri.split("://", 1)
-    if scheme not in SCHEMES:
-        raise DryadLinqException(ErrorCode.UnrecognizedDataSource, f"unknown storage scheme {scheme!r}")
-    if scheme in ("hdfs", "wasb", "azureblob", "hpcdsc"):
-        raise DryadLinqException(ErrorCode.UnrecognizedDataSource,
-                                 f"{scheme}:// needs a cluster file system; this build has none (single box)")
+    DataProvider.get(scheme)               # raises UnrecognizedDataSource for a scheme nobody serves
     path = "/" + rest.lstrip("/") if rest.startswith("/") else rest
     return scheme, path
 
 
-def exists(uri: str) -> bool:
+def _pf_exists(uri: str) -> bool:
     _, path = parse_uri(uri)
     return os.path.exists(path)
 
 
-def delete(uri: str) -> None:
+def _pf_delete(uri: str) -> None:
     _, path = parse_uri(uri)
     if not os.path.exists(path):
         return
@@ -79,7 +76,7 @@ def _read_meta(path: str):
     return base.value.decode(), n, [sizes[i] for i in range(min(n, 65536))]
 
 
-def write_part(uri: str, index: int, part, compression: Optional[str] = None):
+def _pf_write_part(uri: str, index: int, part, compression: Optional[str] = None):
     """Write ONE partition of a table as an uncommitted version file (SPMD: every rank writes its own
     partition).  Returns (tmp_path, final_path, stored_bytes); nothing is visible until
     `commit_part` renames it and `finish_table` publishes the metadata file
@@ -113,12 +110,12 @@ def write_part(uri: str, index: int, part, compression: Optional[str] = None):
     return tmp, final, stored.value
 
 
-def commit_part(tmp: str, final: str) -> None:
+def _pf_commit_part(tmp: str, final: str) -> None:
     if N.host().dh_commit_part(tmp.encode(), final.encode()):
         raise DryadLinqException(ErrorCode.WriteFileError, f"cannot commit {final}")
 
 
-def finish_table(uri: str, sizes: Sequence[int], schema=None, compression: Optional[str] = None) -> None:
+def _pf_finish_table(uri: str, sizes: Sequence[int], schema=None, compression: Optional[str] = None) -> None:
     """Publish the metadata of a table whose partitions have all been committed."""
     scheme, path = parse_uri(uri)
     base = os.path.splitext(path)[0]
@@ -131,7 +128,7 @@ def finish_table(uri: str, sizes: Sequence[int], schema=None, compression: Optio
         json.dump({"schema": schema, "compression": "Gzip" if comp else "None"}, f)
 
 
-def write_table(uri: str, parts: Sequence[Sequence], schema=None, compression: Optional[str] = None) -> None:
+def _pf_write_table(uri: str, parts: Sequence[Sequence], schema=None, compression: Optional[str] = None) -> None:
     scheme, path = parse_uri(uri)
     lib = N.host()
     os.makedirs(os.path.dirname(os.path.abspath(path)) or ".", exist_ok=True)
@@ -246,7 +243,7 @@ def split_text(data: bytes, n: int) -> List[bytes]:
     return out
 
 
-def open_table(uri: str, text_partitions: int = 1) -> StoredTable:
+def _pf_open_table(uri: str, text_partitions: int = 1) -> StoredTable:
     scheme, path = parse_uri(uri)
     if not os.path.exists(path):
         raise DryadLinqException(ErrorCode.StreamDoesNotExist, f"{uri} does not exist")
@@ -261,3 +258,95 @@ def open_table(uri: str, text_partitions: int = 1) -> StoredTable:
             schema = json.load(f).get("schema")
     parts = [read_partition_file(_part_path(base, i)) for i in range(n)]
     return StoredTable(parts, schema)
+
+
+# ---- providers and the public entry points ---------------------------------------------------------
+class PartitionedFileProvider(DataProvider):
+    """`partfile://` (and bare paths): metadata file + one block-stream file per partition
+    (LinqToDryad/DataProvider.cs:378-538)."""
+    scheme = "partfile"
+    supports_part_commit = True
+
+    def exists(self, uri):
+        return _pf_exists(uri)
+
+    def delete(self, uri):
+        _pf_delete(uri)
+
+    def open_table(self, uri, text_partitions=1):
+        return _pf_open_table(uri, text_partitions)
+
+    def write_table(self, uri, parts, schema=None, compression=None):
+        _pf_write_table(uri, parts, schema, compression)
+
+    def write_part(self, uri, index, part, compression=None):
+        return _pf_write_part(uri, index, part, compression)
+
+    def commit_part(self, tmp, final):
+        _pf_commit_part(tmp, final)
+
+    def finish_table(self, uri, sizes, schema=None, compression=None):
+        _pf_finish_table(uri, sizes, schema, compression)
+
+    def get_stream_info(self, uri):
+        _, path = parse_uri(uri)
+        if not path.endswith(".pt"):
+            return StreamInfo(1, os.path.getsize(path))
+        _, n, sizes = _read_meta(path)
+        return StreamInfo(n, sum(sizes))
+
+    def get_metadata(self, uri):
+        _, path = parse_uri(uri)
+        if os.path.exists(path + ".schema"):
+            with open(path + ".schema") as f:
+                return json.load(f)
+        return {"schema": None, "compression": "None"}
+
+    def temporary_uri(self, context, path):
+        return f"partfile://{os.path.join(context.work_dir, 'tmp', path)}.pt"
+
+
+class TextFileProvider(PartitionedFileProvider):
+    """`file://`: plain text, one LineRecord per line; writes go to a partfile-format table."""
+    scheme = "file"
+
+
+DataProvider.register(PartitionedFileProvider(), replace=True)
+DataProvider.register(TextFileProvider(), replace=True)
+
+
+def exists(uri: str) -> bool:
+    return DataProvider.for_uri(uri).exists(uri)
+
+
+def delete(uri: str) -> None:
+    DataProvider.for_uri(uri).delete(uri)
+
+
+def open_table(uri: str, text_partitions: int = 1):
+    return DataProvider.for_uri(uri).open_table(uri, text_partitions)
+
+
+def write_table(uri: str, parts: Sequence[Sequence], schema=None, compression: Optional[str] = None) -> None:
+    DataProvider.for_uri(uri).write_table(uri, parts, schema, compression)
+
+
+def supports_part_commit(uri: str) -> bool:
+    return DataProvider.for_uri(uri).supports_part_commit
+
+
+def write_part(uri: str, index: int, part, compression: Optional[str] = None):
+    return DataProvider.for_uri(uri).write_part(uri, index, part, compression)
+
+
+def commit_part(tmp: str, final: str, uri: Optional[str] = None) -> None:
+    (DataProvider.for_uri(uri) if uri else DataProvider.get("partfile")).commit_part(tmp, final)
+
+
+def finish_table(uri: str, sizes: Sequence[int], schema=None, compression: Optional[str] = None) -> None:
+    DataProvider.for_uri(uri).finish_table(uri, sizes, schema, compression)
+
+
+def stream_info(uri: str) -> StreamInfo:
+    return DataProvider.for_uri(uri).get_stream_info(uri)
+

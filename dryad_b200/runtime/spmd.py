@@ -771,7 +771,20 @@ class SpmdExecutor(JobExecutor):
             else:
                 parts = [payload[0]] if payload is not None else [[]]
             uri = node.params.get("uri")
-            if uri and self.world > 1:
+            if uri and self.world > 1 and not store.supports_part_commit(uri):
+                # a provider without per-partition commit: rank 0 collects the partitions and publishes the table
+                mine_recs = self.backend.to_records(payload[0]) if payload is not None else []
+                gathered: List = [None] * self.world
+                dist.all_gather_object(gathered, list(mine_recs))
+                self.object_collectives += 1
+                if self.rank == 0:
+                    n_out = root.partition_count
+                    store.write_table(uri, gathered[:n_out] if n_out == self.world else [gathered[0]], root.schema,
+                                      node.params.get("compression"))
+                dist.barrier()
+                table = self.context._commit_table(None, parts, root.schema, root.info, None, node.params.get("temporary", False))
+                table.uri = uri
+            elif uri and self.world > 1:
                 tmp = final = None
                 size, err = 0, None
                 writes = payload is not None and (root.partition_count == self.world or self.rank == 0)
