@@ -29,6 +29,7 @@ VERSION = "0.2.1-b200"
 class PlatformKind(str, Enum):
     LOCAL = "LOCAL"
     B200 = "B200"            # one NVSwitch domain (replaces YARN_NATIVE / YARN_AZURE)
+    LOCAL_CLUSTER = "LOCAL_CLUSTER"   # a graph-manager process + vertex-host processes on this box (CPU vertices)
 
 
 class ExecutorKind(str, Enum):
@@ -467,6 +468,8 @@ class DryadLinqContext:
                     data = interp.run(r.expr)
                     tables[r.expr.id] = Table([list(data)], r.expr.schema, None, r.expr.params.get("uri"),
                                               r.expr.params.get("temporary", False))
+            elif self.platform == PlatformKind.LOCAL_CLUSTER:
+                tables = self._run_cluster_job(job, roots)
             else:
                 from ..plan.querygen import QueryGen
                 from ..runtime.executor import JobExecutor
@@ -493,6 +496,37 @@ class DryadLinqContext:
             job.status = JobStatus.Failure
             job.error = ex
             raise
+
+    def _run_cluster_job(self, job: "DryadLinqJobInfo", roots) -> Dict[int, "Table"]:
+        """Ship the job package to a graph-manager process and wait for its verdict (SURVEY §3.1:
+        client -> job package -> job manager -> vertex hosts)."""
+        from ..channel import store
+        from ..runtime import jobpackage
+        from .submission import ClusterJobSubmission
+        self._job_counter += 1
+        job_dir = os.path.join(self.work_dir, "ClusterJobs", str(self._job_counter))
+        jobpackage.write(job_dir, self, roots)
+        sub = ClusterJobSubmission(job_dir, workers=int(self.job_max_nodes or 0))
+        for f in self.resources_to_add:
+            sub.add_local_file(f)
+        job.submission = sub
+        sub.submit_job()
+        limit = float(self.job_runtime_limit) + 30.0 if self.job_runtime_limit else None
+        st = sub.wait_for_completion(limit)
+        if st == JobStatus.Running:
+            sub.terminate_job()
+            raise DryadLinqException(ErrorCode.DidNotCompleteSuccessfully, "job exceeded its runtime limit")
+        rec = sub.status_record()
+        self.last_job_stats = rec.get("vertices", [])
+        self.last_cluster_status = rec
+        if st != JobStatus.Success:
+            raise DryadLinqException(ErrorCode.DidNotCompleteSuccessfully, sub.error_text() or "job failed")
+        tables: Dict[int, Table] = {}
+        for r in roots:
+            t = rec["tables"][str(r.expr.id)]
+            stored = store.open_table(t["uri"])
+            tables[r.expr.id] = Table(stored.partitions, stored.schema or r.expr.schema, None, t["uri"], t["temporary"])
+        return tables
 
     def _execute(self, q: Query) -> Query:
         res = getattr(q, "_result", None)

@@ -112,3 +112,87 @@ class LocalJobSubmission(IDryadLinqJobSubmission):
             return open(err).read()
         out = os.path.join(self.job_dir, "log", "stdout.txt")
         return open(out, errors="replace").read()[-2000:] if os.path.exists(out) else ""
+
+
+class ClusterJobSubmission(IDryadLinqJobSubmission):
+    """Cluster mode on one box: a graph-manager PROCESS (`python -m dryad_b200.sched.jm`) that starts
+    vertex-host processes through its process service and runs the job package in `job_dir`
+    (the role of YarnJobSubmission / PeloponneseJobSubmission: LinqToDryad/YarnJobSubmission.cs,
+    PeloponneseJobSubmission.cs:36-179 — stage resources, start the job manager, poll its status)."""
+
+    def __init__(self, job_dir: str, workers: int = 0):
+        self.job_dir, self.workers = job_dir, workers
+        self.options: Dict[str, str] = {}
+        self.files: List[str] = []
+        self.proc: Optional[subprocess.Popen] = None
+        self.status = JobStatus.NotSubmitted
+
+    def add_job_option(self, name, value):
+        self.options[name] = str(value)
+
+    def add_local_file(self, path):
+        self.files.append(path)
+
+    def get_job_id(self):
+        return os.path.basename(self.job_dir.rstrip("/"))
+
+    def submit_job(self):
+        os.makedirs(os.path.join(self.job_dir, "log"), exist_ok=True)
+        if self.files:
+            import shutil
+            res = os.path.join(self.job_dir, "resources")
+            os.makedirs(res, exist_ok=True)
+            for f in self.files:
+                shutil.copy(f, res)
+        cmd = [sys.executable, "-m", "dryad_b200.sched.jm", self.job_dir]
+        if self.workers:
+            cmd += ["--workers", str(self.workers)]
+        env = {**os.environ, **{"DRYAD_OPT_" + k.upper(): v for k, v in self.options.items()}}
+        root = os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+        env["PYTHONPATH"] = root + os.pathsep + env.get("PYTHONPATH", "")
+        out = open(os.path.join(self.job_dir, "log", "jm-stdout.txt"), "wb")
+        self.proc = subprocess.Popen(cmd, stdout=out, stderr=subprocess.STDOUT, env=env)
+        self.status = JobStatus.Running
+
+    def status_record(self) -> dict:
+        import json
+        p = os.path.join(self.job_dir, "status.json")
+        if not os.path.exists(p):
+            return {}
+        with open(p) as f:
+            return json.load(f)
+
+    def get_status(self):
+        if self.proc is None or self.status == JobStatus.Cancelled:
+            return self.status
+        rc = self.proc.poll()
+        if rc is None:
+            return JobStatus.Running
+        rec = self.status_record()
+        self.status = JobStatus.Success if rc == 0 and rec.get("state") == "Success" else JobStatus.Failure
+        return self.status
+
+    def terminate_job(self):
+        if self.proc is not None and self.proc.poll() is None:
+            self.proc.terminate()          # SIGTERM to the graph manager we started: it stops its vertex hosts
+            try:
+                self.proc.wait(10)
+            except subprocess.TimeoutExpired:
+                self.proc.kill()
+            self.status = JobStatus.Cancelled
+
+    def wait_for_completion(self, timeout=None):
+        if self.proc is not None:
+            try:
+                self.proc.wait(timeout)
+            except subprocess.TimeoutExpired:
+                return JobStatus.Running
+        return self.get_status()
+
+    def error_text(self) -> str:
+        rec = self.status_record()
+        if rec.get("error"):
+            return rec["error"]
+        out = os.path.join(self.job_dir, "log", "jm-stdout.txt")
+        return open(out, errors="replace").read()[-3000:] if os.path.exists(out) else ""
+

@@ -76,6 +76,37 @@ def _read_meta(path: str):
     return base.value.decode(), n, [sizes[i] for i in range(min(n, 65536))]
 
 
+def write_records_file(path: str, part, compression=None) -> int:
+    """One block-stream file of records (the format of table partitions and of file channels between
+    vertices).  Returns the stored size; on error the file is removed."""
+    lib = N.host()
+    comp = compression if isinstance(compression, int) else (1 if str(compression or "None").lower() in ("gzip", "1", "true") else 0)
+    try:
+        w = lib.dh_writer_open(path.encode(), comp, 0)
+        if not w:
+            raise DryadLinqException(ErrorCode.FailedToCreateStream, f"cannot create {path}")
+        try:
+            recs = part.to_records() if hasattr(part, "to_records") else part
+            for rec in recs:
+                b = R.encode_record(rec)
+                lib.dh_write_bytes(w, b, len(b))
+                rc = lib.dh_writer_end_record(w)
+                if rc:
+                    raise DryadLinqException(ErrorCode.WriteFileError, f"write failed ({rc})")
+        except BaseException:
+            lib.dh_writer_close(w, None, None, None)
+            raise
+        raw, stored, nrec = C.c_int64(), C.c_int64(), C.c_int64()
+        rc = lib.dh_writer_close(w, C.byref(raw), C.byref(stored), C.byref(nrec))
+        if rc:
+            raise DryadLinqException(ErrorCode.WriteFileError, f"close failed ({rc})")
+    except BaseException:
+        if os.path.exists(path):
+            os.remove(path)
+        raise
+    return stored.value
+
+
 def _pf_write_part(uri: str, index: int, part, compression: Optional[str] = None):
     """Write ONE partition of a table as an uncommitted version file (SPMD: every rank writes its own
     partition).  Returns (tmp_path, final_path, stored_bytes); nothing is visible until
@@ -88,26 +119,8 @@ def _pf_write_part(uri: str, index: int, part, compression: Optional[str] = None
     comp = 1 if str(compression or "None").lower() in ("gzip", "1", "true") else 0
     final = _part_path(base, index)
     tmp = final + ".v0.tmp"
-    try:
-        w = lib.dh_writer_open(tmp.encode(), comp, 0)
-        if not w:
-            raise DryadLinqException(ErrorCode.FailedToCreateStream, f"cannot create {tmp}")
-        recs = part.to_records() if hasattr(part, "to_records") else part
-        for rec in recs:
-            b = R.encode_record(rec)
-            lib.dh_write_bytes(w, b, len(b))
-            rc = lib.dh_writer_end_record(w)
-            if rc:
-                raise DryadLinqException(ErrorCode.WriteFileError, f"write failed ({rc})")
-        raw, stored, nrec = C.c_int64(), C.c_int64(), C.c_int64()
-        rc = lib.dh_writer_close(w, C.byref(raw), C.byref(stored), C.byref(nrec))
-        if rc:
-            raise DryadLinqException(ErrorCode.WriteFileError, f"close failed ({rc})")
-    except BaseException:
-        if os.path.exists(tmp):
-            os.remove(tmp)
-        raise
-    return tmp, final, stored.value
+    stored = write_records_file(tmp, part, comp)
+    return tmp, final, stored
 
 
 def _pf_commit_part(tmp: str, final: str) -> None:

@@ -77,6 +77,11 @@ class VertexCommand:
             lib.vc_destroy(h)
 
 
+def terminate_command(commit: bool = True, message: str = "") -> VertexCommand:
+    """The Terminate command of the vertex-host protocol (dvertexpncontrol.h:34-106)."""
+    return VertexCommand(CMD_TERMINATE, 0, 0, args=["commit" if commit else "abort", message[:4000]])
+
+
 def affinity_merge(weights: List[Tuple[int, int]], rack_of: List[int], threshold: float = 0.5) -> Tuple[str, int]:
     """(level, id): where a vertex should run given (computer, input bytes) affinities."""
     n = len(weights)

@@ -156,3 +156,85 @@ class ProcessService:
                 p.kill()
         for m in self.mailboxes.values():
             m.close()
+
+
+class MailboxClient:
+    """A process's side of the mailbox protocol: ONE keep-alive HTTP connection to the node daemon
+    for all its long-polls and reports (ClusterInterface/HttpScheduler.cs:34-126 is the GM-side
+    counterpart in the reference; the vertex host's side is dvertexpncontrol.cpp's status loop)."""
+
+    def __init__(self, uri: str, who: str = "client"):
+        self.uri, self.who = uri, who
+        self._conn = None
+
+    def request(self, method: str, path: str, body: bytes = b"", timeout: float = 30.0):
+        """One exchange; reconnects once when the connection was dropped.  Raises ConnectionError when
+        the daemon cannot be reached at all."""
+        import http.client
+        import socket
+        u = urllib.parse.urlparse(self.uri)
+        for attempt in (0, 1):
+            try:
+                if self._conn is None:
+                    self._conn = http.client.HTTPConnection(u.hostname, u.port, timeout=timeout)
+                    self._conn.connect()
+                    self._conn.sock.setsockopt(socket.IPPROTO_TCP, socket.TCP_NODELAY, 1)
+                self._conn.sock.settimeout(timeout)
+                self._conn.request(method, path, body=body or None,
+                                   headers={"Content-Length": str(len(body))} if body else {})
+                resp = self._conn.getresponse()
+                return resp.status, resp.headers, resp.read()
+            except (http.client.HTTPException, OSError) as ex:
+                try:
+                    self._conn.close()
+                except Exception:  # noqa: BLE001
+                    pass
+                self._conn = None
+                if attempt:
+                    raise ConnectionError(f"{self.who}: the process service at {self.uri} is unreachable ({ex})") from ex
+
+    def get(self, pid: str, key: str, seen: int, timeout: float):
+        """Long-poll: (version, status, data) of `key` once its version exceeds `seen`, else None."""
+        q = urllib.parse.urlencode({"key": key, "version": seen, "timeout": timeout})
+        status, headers, data = self.request("GET", f"/process/{pid}/status?{q}", b"", timeout + 10.0)
+        if status != 200:
+            return None
+        return int(headers.get(H_VERSION, "0")), headers.get(H_STATUS, ""), data
+
+    def set(self, pid: str, key: str, status: str, data: bytes = b"", wait: Optional[str] = None, seen: int = 0,
+            wait_timeout: float = 5.0, timeout: float = 30.0):
+        """Set a value; with `wait`, the same exchange long-polls another key and returns its
+        (version, status, data) when it changed within wait_timeout, else None."""
+        q = {"key": key, "status": status}
+        if wait:
+            q.update({"wait": wait, "version": seen, "timeout": wait_timeout})
+        st, headers, body = self.request("PUT", f"/process/{pid}/setvalue?{urllib.parse.urlencode(q)}", data,
+                                         timeout + (wait_timeout if wait else 0.0))
+        if wait and st == 200 and headers.get("X-Dryad-Waited") == "1":
+            return int(headers.get(H_VERSION, "0")), headers.get(H_STATUS, ""), body
+        return None
+
+    def fetch_file(self, rel_path: str, start: int = 0, end: Optional[int] = None, timeout: float = 30.0) -> bytes:
+        """Ranged GET from the daemon's file server (a channel file that lives on another computer)."""
+        import http.client
+        u = urllib.parse.urlparse(self.uri)
+        c = http.client.HTTPConnection(u.hostname, u.port, timeout=timeout)
+        try:
+            hdr = {"Range": f"bytes={start}-{'' if end is None else end}"} if (start or end is not None) else {}
+            c.request("GET", "/file/" + rel_path.lstrip("/"), headers=hdr)
+            r = c.getresponse()
+            data = r.read()
+            if r.status not in (200, 206):
+                raise FileNotFoundError(rel_path)
+            return data
+        finally:
+            c.close()
+
+    def close(self):
+        if self._conn is not None:
+            try:
+                self._conn.close()
+            except Exception:  # noqa: BLE001
+                pass
+            self._conn = None
+

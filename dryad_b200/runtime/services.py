@@ -17,7 +17,8 @@ class MessagePump:
         self.h = self.lib.pump_create(threads, self._cb, None)
 
     def post(self, listener: int, message: int, delay: float = 0.0) -> None:
-        self.lib.pump_post(self.h, listener, message, delay)
+        if self.h:
+            self.lib.pump_post(self.h, listener, message, delay)
 
     def post_on_stream_completion(self, listener: int, message: int, stream: Optional[int] = None) -> None:
         """Post (listener, message) when all GPU work enqueued so far on `stream` (default: the

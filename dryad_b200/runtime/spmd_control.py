@@ -23,19 +23,13 @@ rank will never enter.
 from __future__ import annotations
 
 import time
-import urllib.error
-import urllib.parse
-import urllib.request
 from typing import List, Optional, Tuple
 
 import torch
 import torch.distributed as dist
 
 from ..api.errors import DryadLinqException, ErrorCode
-from .command import CMD_START, CMD_TERMINATE, STATE_COMPLETED, STATE_FAILED, VertexCommand
-
-H_VERSION, H_STATUS = "X-Dryad-ValueVersion", "X-Dryad-ProcessStatus"
-
+from .command import CMD_START, CMD_TERMINATE, STATE_COMPLETED, STATE_FAILED, VertexCommand, terminate_command  # noqa: F401
 
 class StageAborted(Exception):
     """Another rank failed in this stage attempt: unwind, the GM decides what happens next."""
@@ -77,30 +71,11 @@ class ControlPlane:
                 m = self.service.mailboxes[f"rank-{r}"] = Mailbox()
             return m
 
-    def _request(self, method: str, path: str, body: bytes = b"", timeout: float = 30.0):
-        """One HTTP exchange on the rank's keep-alive connection (reconnects once when it was dropped)."""
-        import http.client
-        u = urllib.parse.urlparse(self.uri)
-        for attempt in (0, 1):
-            try:
-                if self._conn is None:
-                    import socket
-                    self._conn = http.client.HTTPConnection(u.hostname, u.port, timeout=timeout)
-                    self._conn.connect()
-                    self._conn.sock.setsockopt(socket.IPPROTO_TCP, socket.TCP_NODELAY, 1)
-                self._conn.sock.settimeout(timeout)
-                self._conn.request(method, path, body=body or None, headers={"Content-Length": str(len(body))} if body else {})
-                resp = self._conn.getresponse()
-                data = resp.read()
-                return resp.status, resp.headers, data
-            except (http.client.HTTPException, OSError) as ex:
-                try:
-                    self._conn.close()
-                except Exception:  # noqa: BLE001
-                    pass
-                self._conn = None
-                if attempt:
-                    raise RankLost(f"rank {self.rank}: the graph manager's mailbox is unreachable ({ex})") from ex
+    def _client(self):
+        if self._conn is None:
+            from .process_service import MailboxClient
+            self._conn = MailboxClient(self.uri, f"rank {self.rank}")
+        return self._conn
 
     def post_command(self, cmd: VertexCommand) -> None:
         """GM side: deliver one launch descriptor to every rank's mailbox."""
@@ -140,11 +115,11 @@ class ControlPlane:
             self._mbox(0).set("status", "completed" if ok else "failed", data)
         else:
             # report and long-poll the next command in ONE exchange
-            q = urllib.parse.urlencode({"key": "status", "status": "completed" if ok else "failed", "wait": "cmd",
-                                        "version": self._seen["cmd"], "timeout": 5.0})
-            status, headers, body = self._request("PUT", f"/process/rank-{self.rank}/setvalue?{q}", data, self.timeout)
-            if status == 200 and headers.get("X-Dryad-Waited") == "1":
-                self._prefetched = (int(headers.get(H_VERSION, "0")), headers.get(H_STATUS, ""), body)
+            try:
+                self._prefetched = self._client().set(f"rank-{self.rank}", "status", "completed" if ok else "failed", data,
+                                                      wait="cmd", seen=self._seen["cmd"], wait_timeout=5.0, timeout=self.timeout)
+            except ConnectionError as ex:
+                raise RankLost(str(ex)) from ex
 
     def collect(self, uid: int, version: int) -> Tuple[bool, str]:
         """GM side: wait for every rank's status block of (stage, version).  A rank that does not
@@ -171,11 +146,10 @@ class ControlPlane:
         return ok, first_error
 
     def _http_get(self, pid: str, key: str, seen: int, timeout: float):
-        q = urllib.parse.urlencode({"key": key, "version": seen, "timeout": timeout})
-        status, headers, data = self._request("GET", f"/process/{pid}/status?{q}", b"", timeout + 10.0)
-        if status != 200:
-            return None
-        return int(headers.get(H_VERSION, "0")), headers.get(H_STATUS, ""), data
+        try:
+            return self._client().get(pid, key, seen, timeout)
+        except ConnectionError as ex:
+            raise RankLost(str(ex)) from ex
 
     # ---- agreement point ------------------------------------------------------------------------
     def agree(self, ok: bool = True) -> bool:
@@ -191,7 +165,3 @@ class ControlPlane:
         if self.service is not None:
             self.service.close()
             self.service = None
-
-
-def terminate_command(commit: bool, message: str = "") -> VertexCommand:
-    return VertexCommand(CMD_TERMINATE, 0, 0, args=["commit" if commit else "abort", message[:4000]])

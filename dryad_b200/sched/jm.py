@@ -1,0 +1,396 @@
+"""Graph-manager process of a cluster-mode job.
+
+    python -m dryad_b200.sched.jm <job dir> [--workers N]
+
+Role of the reference's job manager executable (DryadLinqGraphManager/Program.cs:30-131 +
+LinqToDryadJM.cs:79-259: read the plan, build the graph, run it, exit code = job outcome) with the
+pieces it drives: the native graph (csrc/host/sched.cpp: versions, retries, upstream invalidation,
+duplicates), the cluster interface + delay scheduler that match vertices with idle computers
+(ClusterInterface/Interfaces.cs, LocalScheduler/LocalScheduler.cs:132-268), the process service
+whose mailbox carries start commands and status blocks (ProcessService/ProcessService.cs:674-746),
+and the message pump that serialises every state change of the graph
+(GraphManager/kernel/DrMessagePump.h:23-135).
+
+Threads: one watcher per vertex-host process blocks on that host's status key and on the process
+itself; whatever it sees becomes a MESSAGE posted to the pump.  The pump's handler is the only code
+that touches the graph: it applies the status (completed / failed / host died), asks the graph for
+newly runnable vertices, queues them with the scheduler under their input affinities, and lets idle
+hosts claim work.  Channel data never passes through this process: producers write block-stream files
+under <job dir>/channels, consumers read them (or their own cache); output tables are written by the
+output vertices as uncommitted versions and published here, atomically, only when the whole job
+succeeded (DrGraph::FinalizeGraph, GraphManager/filesystem/DrPartitionFile.cpp:561-597).
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import signal
+import subprocess
+import sys
+import threading
+import time
+from collections import deque
+from typing import Any, Deque, Dict, List, Optional, Tuple
+
+EV_DISPATCH, EV_STATUS, EV_EXIT, EV_TICK, EV_HELLO = range(5)
+STATUS_FILE = "status.json"
+
+
+class _Host:
+    """One vertex-host process slot (a 'computer')."""
+
+    def __init__(self, index: int):
+        self.index = index
+        self.incarnation = -1
+        self.name = ""
+        self.proc: Optional[subprocess.Popen] = None
+        self.ready = False
+        self.busy: Optional[Tuple[int, int, float]] = None      # (gm vertex, version, start time)
+        self.restarts = 0
+        self.vertices_run = 0
+
+
+class JobManager:
+    def __init__(self, job_dir: str, workers: int = 0, max_host_restarts: int = 8):
+        from ..runtime import jobpackage
+        from ..runtime.executor import JobExecutor
+        from ..runtime.process_service import ProcessService
+        from ..runtime.services import MessagePump
+        from .cluster import LocalCluster
+        from .reporting import CalypsoReporter
+        self.job_dir = os.path.abspath(job_dir)
+        self.ctx, self.plan = jobpackage.load(self.job_dir)
+        self.reporter = CalypsoReporter(self.job_dir, level=self.ctx.runtime_logging_level.value)
+        self.ex = JobExecutor(self.ctx, self.plan, reporter=self.reporter)
+        self.gm = self.ex._build_gm()
+        self.nodes = self.ex._gm_stage_node                                   # gm stage id -> plan node
+        width = max(n.partition_count for n in self.plan.nodes)
+        want = workers or int(self.ctx.job_max_nodes or 0) or min(width, os.cpu_count() or 1)
+        self.nhosts = max(1, max(int(self.ctx.job_min_nodes or 0), want))
+        self.service = ProcessService(self.job_dir)
+        self.cluster = LocalCluster(self.nhosts, self.job_dir, rack_delay=0.02, cluster_delay=0.05)
+        self.hosts = [_Host(i) for i in range(self.nhosts)]
+        self.max_host_restarts = max_host_restarts
+        self.lock = threading.RLock()
+        self.inbox: Dict[int, Deque[Tuple[int, bytes]]] = {i: deque() for i in range(self.nhosts)}
+        self.pending: Dict[int, Tuple[int, int]] = {}                         # scheduler process id -> (gm vertex, version)
+        self._next_pid = 1
+        self.versions: Dict[Tuple[int, int], int] = {}                        # (stage uid, part) -> completed version
+        self.where: Dict[Tuple[int, int], int] = {}                           # (stage uid, part) -> host that holds it in cache
+        self.records: Dict[Tuple[int, int], int] = {}                         # (stage uid, part) -> output records
+        self.part_files: Dict[Tuple[int, int], Tuple[str, str, int]] = {}     # root (uid, part) -> (tmp, final, size)
+        self.done = threading.Event()
+        self.ok = False
+        self.error = ""
+        self.stopping = False
+        self.t0 = time.perf_counter()
+        self.stats: List[dict] = []
+        self.messages = 0
+        self._watchers: List[threading.Thread] = []
+        self.pump = MessagePump(self._on_message, threads=1)                  # ONE consumer: graph changes are serialised
+
+    # ---- vertex hosts -----------------------------------------------------------------------------
+    def _launch(self, h: _Host) -> None:
+        h.incarnation += 1
+        h.name = f"w{h.index}.{h.incarnation}"
+        h.ready, h.busy = False, None
+        log = open(os.path.join(self.job_dir, "log", f"host-{h.name}.txt"), "wb")
+        env = dict(os.environ)
+        env["DRYAD_JOB_DIR"] = self.job_dir
+        cmd = [sys.executable, "-m", "dryad_b200.runtime.vertex_host", "--service", self.service.uri, "--id", h.name,
+               "--job-dir", self.job_dir]
+        h.proc = subprocess.Popen(cmd, stdout=log, stderr=subprocess.STDOUT, env=env, cwd=self.job_dir)
+        with self.service._lock:
+            self.service.procs[h.name] = h.proc
+        self.reporter._emit("process", host=h.name, pid=h.proc.pid, state="created")
+        t = threading.Thread(target=self._watch, args=(h, h.incarnation), daemon=True, name=f"watch-{h.name}")
+        self._watchers.append(t)
+        t.start()
+
+    def _mbox(self, name: str):
+        from ..runtime.services import Mailbox
+        with self.service._lock:
+            m = self.service.mailboxes.get(name)
+            if m is None:
+                m = self.service.mailboxes[name] = Mailbox()
+            return m
+
+    def _watch(self, h: _Host, incarnation: int) -> None:
+        """Blocks on the host's keys; turns what it sees into pump messages.  Never touches the graph."""
+        mb = self._mbox(f"w{h.index}.{incarnation}")
+        seen, hello = 0, False
+        proc = h.proc
+        while not self.done.is_set():
+            if not hello:
+                got = mb.block_on_status("hello", 0, 0.05)
+                if got:
+                    hello = True
+                    self.pump.post(EV_HELLO, h.index * 1000 + incarnation)
+            got = mb.block_on_status("status", seen, 0.2 if hello else 0.05)
+            if got:
+                seen = got[0]
+                self.inbox[h.index].append((incarnation, got[2]))
+                self.pump.post(EV_STATUS, h.index * 1000 + incarnation)
+                continue
+            if proc.poll() is not None:
+                self.pump.post(EV_EXIT, h.index * 1000 + incarnation)
+                return
+
+    # ---- the pump handler: the only place the graph changes -----------------------------------------
+    def _on_message(self, listener: int, message: int) -> None:
+        try:
+            with self.lock:
+                self.messages += 1
+                if self.done.is_set():
+                    return
+                if listener in (EV_HELLO, EV_STATUS, EV_EXIT):
+                    h = self.hosts[message // 1000]
+                    data = self.inbox[h.index].popleft()[1] if listener == EV_STATUS else b""   # one entry per status message
+                    if h.incarnation != message % 1000:
+                        return                                                # news of a replaced incarnation
+                    if listener == EV_HELLO:
+                        h.ready = True
+                        self.reporter._emit("process", host=h.name, state="started")
+                    elif listener == EV_STATUS:
+                        self._on_status(h, data)
+                    else:
+                        self._on_exit(h)
+                elif listener == EV_TICK:
+                    self.gm.check_duplicates(time.perf_counter() - self.t0)
+                    limit = self.ctx.job_runtime_limit
+                    if limit and time.perf_counter() - self.t0 > float(limit):
+                        self._finish(False, f"job exceeded its runtime limit of {limit} s")
+                        return
+                    self.pump.post(EV_TICK, 0, 0.25)
+                self._dispatch()
+                st = self.gm.state
+                if st == "Succeeded":
+                    self._commit()
+                elif st == "Failed":
+                    self._finish(False, self.error or self.gm.error() or "job failed")
+        except Exception as ex:  # noqa: BLE001  (a bug here must end the job, not hang it)
+            import traceback
+            self._finish(False, "graph manager error: " + "".join(traceback.format_exception(type(ex), ex, ex.__traceback__))[-3000:])
+
+    def _vertex(self, v: int):
+        info = self.gm.vertex(v)
+        return self.nodes[info["stage"]], info["part"]
+
+    def _on_status(self, h: _Host, data: bytes) -> None:
+        from ..runtime.command import STATE_COMPLETED, VertexCommand
+        st = VertexCommand.parse(data)
+        if st is None or h.busy is None:
+            return
+        v, version, t_start = h.busy
+        if int(st.args[1]) != v or st.version != version:
+            return                                                            # stale
+        h.busy = None
+        h.vertices_run += 1
+        node, part = self._vertex(v)
+        n_in, n_out, seconds, hits = int(st.args[2]), int(st.args[3]), float(st.args[4]), int(st.args[5])
+        if st.state == STATE_COMPLETED:
+            won = self.gm.completed(v, version, seconds, float(sum(b for b, _ in st.channel_status)))
+            if won:
+                self.versions[(node.uid, part)] = version
+                self.where[(node.uid, part)] = h.index
+                self.records[(node.uid, part)] = n_out
+                for path, size in st.outputs:
+                    if "|" in path:
+                        tmp, final = path.split("|", 1)
+                        self.part_files[(node.uid, part)] = (tmp, final, size)
+            ins = self.ex._gm_inputs.get(v, [])
+            local = sum(self.records.get(e, 0) for e in ins if self.where.get(e) == h.index)
+            total = sum(self.records.get(e, 0) for e in ins)
+            rec = {"stage": node.uid, "stage_name": node.name, "part": part, "version": version, "seconds": seconds,
+                   "records_in": n_in, "records_out": n_out, "computer": h.index, "host": h.name, "won": bool(won),
+                   "records_local": local, "records_remote": total - local, "cache_hits": hits,
+                   "bytes_in": [b for b, _ in st.channel_status], "bytes_out": [s for _, s in st.outputs]}
+            self.stats.append(rec)
+            self.reporter.vertex_event(node, part, version, "completed" if won else "completed_duplicate", seconds=seconds,
+                                       records_in=n_in, records_out=n_out, computer=h.index, local=local,
+                                       remote=total - local, cache_hits=hits)
+        else:
+            bad = next((k for k, (_b, err) in enumerate(st.channel_status) if err), -1)
+            self.reporter.vertex_event(node, part, version, "failed", error=st.message, computer=h.index)
+            rc = self.gm.failed(v, version, st.message, bad_input=bad)
+            if rc == 2 and bad >= 0:
+                prod = self.ex._gm_inputs[v][bad]
+                self.versions.pop(prod, None)
+                self.where.pop(prod, None)
+            elif rc == 1 or (st.exit_code == 2 and self.ctx.fail_fast_on_deterministic_errors):
+                self.error = st.message
+                if rc != 1:
+                    self._finish(False, st.message)
+
+    def _on_exit(self, h: _Host) -> None:
+        code = h.proc.poll() if h.proc is not None else None
+        self.reporter._emit("process", host=h.name, state="exited", exitcode=code)
+        if self.stopping:
+            return
+        if h.busy is not None:
+            v, version, _ = h.busy
+            node, part = self._vertex(v)
+            msg = f"vertex host {h.name} exited with code {code} while running {node.name}#{node.uid}[{part}] v{version}"
+            self.reporter.vertex_event(node, part, version, "failed", error=msg, computer=h.index)
+            if self.gm.failed(v, version, msg) == 1:
+                self.error = msg
+            h.busy = None
+        for key in [k for k, w in self.where.items() if w == h.index]:          # its cache died with it; the files remain
+            del self.where[key]
+        h.restarts += 1
+        if h.restarts > self.max_host_restarts:
+            self.error = f"vertex host slot {h.index} died {h.restarts} times"
+            self._finish(False, self.error)
+            return
+        self._launch(h)
+
+    def _dispatch(self) -> None:
+        from ..runtime.command import CMD_START, VertexCommand, affinity_merge
+        from .cluster import Affinity, Process
+        now = time.perf_counter() - self.t0
+        while True:
+            nxt = self.gm.next_ready(now)
+            if nxt is None:
+                break
+            v, version = nxt
+            node, part = self._vertex(v)
+            votes: Dict[int, int] = {}
+            for e in self.ex._gm_inputs.get(v, []):
+                w = self.where.get(e)
+                if w is not None:
+                    votes[w] = votes.get(w, 0) + max(1, self.records.get(e, 0))
+            prefer: List[int] = []
+            if votes:
+                level, choice = affinity_merge(sorted(votes.items()), [0] * self.nhosts)
+                if level == "computer":
+                    prefer = [choice]
+            pid = self._next_pid
+            self._next_pid += 1
+            self.pending[pid] = (v, version)
+            self.cluster.schedule_process(Process(pid, f"{node.name}#{node.uid}[{part}]", Affinity(prefer, sum(votes.values()), False)))
+            self.reporter.vertex_event(node, part, version, "created", prefer=prefer[0] if prefer else None)
+        waiting = self.cluster.scheduler.waiting
+        if not waiting:
+            return
+        idle = [h for h in self.hosts if h.ready and h.busy is None and h.proc is not None and h.proc.poll() is None]
+        for h in idle:
+            p = self.cluster.computer_idle(h.index)
+            if p is None:
+                continue
+            v, version = self.pending.pop(p.id)
+            node, part = self._vertex(v)
+            inputs = [(f"chan://{uid}/{s}/{self.versions.get((uid, s), 0)}", self.records.get((uid, s), 0))
+                      for uid, s in self.ex._gm_inputs.get(v, [])]
+            cmd = VertexCommand(CMD_START, node.uid, version, args=[node.name, str(part), str(v)], inputs=inputs,
+                                outputs=[(f"chan://{node.uid}/{part}/{version}", 0)])
+            h.busy = (v, version, time.perf_counter())
+            self._mbox(h.name).set("cmd", "start", cmd.serialize())
+            self.reporter.vertex_event(node, part, version, "starting", computer=h.index)
+        if self.cluster.scheduler.waiting and any(h.ready and h.busy is None for h in self.hosts):
+            self.pump.post(EV_DISPATCH, 0, 0.03)                              # delay scheduling: let preferences age
+
+    # ---- end of job ---------------------------------------------------------------------------------
+    def _commit(self) -> None:
+        """Every vertex completed: publish the output tables (rename the winning part versions, then the
+        metadata), write the job's status file."""
+        from ..channel import store
+        from ..runtime.vertex_host import read_channel, temp_output_uri
+        tables: Dict[str, Any] = {}
+        try:
+            for root in self.plan.roots:
+                onode = root if root.type.value == "OutputTable" else root.members[-1]
+                uri = onode.params.get("uri") or temp_output_uri(self.job_dir, onode.params["qexpr_id"])
+                comp = onode.params.get("compression") or self.ctx.output_data_compression_scheme
+                if store.supports_part_commit(uri):
+                    sizes = []
+                    for i in range(root.partition_count):
+                        tmp, final, size = self.part_files[(root.uid, i)]
+                        store.commit_part(tmp, final, uri)
+                        sizes.append(size)
+                    store.finish_table(uri, sizes, root.schema, comp)
+                else:
+                    parts = [read_channel(self.job_dir, root.uid, i, 0, self.versions[(root.uid, i)])[0]
+                             for i in range(root.partition_count)]
+                    store.write_table(uri, parts, root.schema, comp)
+                tables[str(onode.params["qexpr_id"])] = {"uri": uri, "temporary": bool(onode.params.get("temporary", False)),
+                                                         "partitions": root.partition_count}
+        except Exception as ex:  # noqa: BLE001
+            self._finish(False, f"output commit failed: {type(ex).__name__}: {ex}")
+            return
+        self._finish(True, "", tables)
+
+    def _finish(self, ok: bool, error: str, tables: Optional[dict] = None) -> None:
+        if self.done.is_set():
+            return
+        self.stopping = True
+        if not ok:
+            for tmp, _final, _ in self.part_files.values():                  # failed jobs leave no partial outputs
+                try:
+                    os.remove(tmp)
+                except OSError:
+                    pass
+        counters = self.gm.counters()
+        self.reporter.job_stop(ok, error, seconds=time.perf_counter() - self.t0, **counters)
+        status = {"state": "Success" if ok else "Failure", "error": error, "tables": tables or {}, "counters": counters,
+                  "hosts": self.nhosts, "host_restarts": sum(h.restarts for h in self.hosts),
+                  "pump_messages": self.messages, "seconds": time.perf_counter() - self.t0, "vertices": self.stats}
+        tmp = os.path.join(self.job_dir, STATUS_FILE + ".tmp")
+        with open(tmp, "w") as f:
+            json.dump(status, f)
+        os.replace(tmp, os.path.join(self.job_dir, STATUS_FILE))
+        self.ok = ok
+        self.done.set()
+
+    def run(self) -> int:
+        os.makedirs(os.path.join(self.job_dir, "log"), exist_ok=True)
+        self.reporter.job_start(self.plan)
+        for h in self.hosts:
+            self._launch(h)
+        self.gm.start()
+        self.pump.post(EV_DISPATCH, 0)
+        self.pump.post(EV_TICK, 0, 0.25)
+        try:
+            self.done.wait()
+        finally:
+            self.shutdown()
+        return 0 if self.ok else 1
+
+    def cancel(self, why: str = "cancelled") -> None:
+        with self.lock:
+            self._finish(False, why)
+
+    def shutdown(self) -> None:
+        from ..runtime.command import terminate_command
+        self.stopping = True
+        data = terminate_command().serialize()
+        for h in self.hosts:
+            if h.proc is not None and h.proc.poll() is None:
+                self._mbox(h.name).set("cmd", "terminate", data)
+        deadline = time.monotonic() + 5.0
+        for h in self.hosts:
+            if h.proc is None:
+                continue
+            try:
+                h.proc.wait(max(0.05, deadline - time.monotonic()))
+            except subprocess.TimeoutExpired:
+                h.proc.kill()                                                 # the exact process we started
+        for t in self._watchers:                                              # nobody may post to a pump that is gone
+            t.join(5.0)
+        self.pump.close()
+        self.service.close()
+        self.reporter.close()
+
+
+def main(argv: Optional[List[str]] = None) -> int:
+    ap = argparse.ArgumentParser(prog="jm")
+    ap.add_argument("job_dir")
+    ap.add_argument("--workers", type=int, default=0)
+    a = ap.parse_args(argv)
+    jm = JobManager(a.job_dir, a.workers)
+    signal.signal(signal.SIGTERM, lambda *_: jm.cancel("cancelled (SIGTERM)"))
+    return jm.run()
+
+
+if __name__ == "__main__":
+    sys.exit(main())

@@ -1,0 +1,141 @@
+"""Cluster mode: a graph-manager process + vertex-host processes (reference roles:
+DryadLinqGraphManager/Program.cs, DryadVertex/VertexHost/vertexHost/main.cpp, dvertexpncontrol.cpp,
+ProcessService, LocalScheduler).  Everything here runs on CPU."""
+import json
+import os
+
+import pytest
+
+from dryad_b200.api.context import DryadLinqContext, PlatformKind
+from dryad_b200.api.errors import DryadLinqException
+
+
+def _ctx(tmp_path, n=3, **kw):
+    ctx = DryadLinqContext(n, platform=PlatformKind.LOCAL_CLUSTER, work_dir=str(tmp_path))
+    ctx.job_max_nodes = kw.pop("hosts", 2)
+    for k, v in kw.items():
+        setattr(ctx, k, v)
+    return ctx
+
+
+def test_cluster_queries_match_oracle(tmp_path):
+    ctx = _ctx(tmp_path)
+    oracle = DryadLinqContext(3, local_debug=True)
+    data = [(i * 7919) % 1000 for i in range(3000)]
+    other = [(k, f"name{k}") for k in range(0, 1000, 3)]
+
+    def build(c):
+        a = c.from_enumerable(data, 3)
+        b = c.from_enumerable(other, 2)
+        g = a.group_by(lambda x: x % 11).select(lambda g: (g.key, g.count(), sum(g)))
+        j = a.join(b, lambda x: x, lambda t: t[0], lambda x, t: (x, t[1]))
+        o = a.where(lambda x: x % 2 == 0).order_by(lambda x: x)
+        return g, j, o
+
+    g1, j1, o1 = build(ctx)
+    g0, j0, o0 = build(oracle)
+    ctx.submit_and_wait(g1, j1, o1)                        # three queries, ONE job
+    assert sorted(g1) == sorted(g0)
+    assert sorted(j1) == sorted(j0)
+    assert list(o1) == list(o0)
+    st = ctx.last_cluster_status
+    assert st["state"] == "Success" and st["hosts"] == 2 and st["pump_messages"] > 0
+    # every vertex ran in a vertex-host process, and locality was tracked per vertex
+    hosts = {v["host"] for v in st["vertices"]}
+    assert hosts and all(h.startswith("w") for h in hosts)
+    assert any(v["cache_hits"] > 0 for v in st["vertices"])
+    job_dir = os.path.join(str(tmp_path), "ClusterJobs", "1")
+    assert os.path.exists(os.path.join(job_dir, "calypso.log"))
+    assert any(f.endswith(".chan") for f in os.listdir(os.path.join(job_dir, "channels")))
+
+
+def test_cluster_store_roundtrip_and_text(tmp_path):
+    ctx = _ctx(tmp_path)
+    uri = f"partfile://{tmp_path}/squares.pt"
+    ctx.submit_and_wait(ctx.from_enumerable(range(100), 3).select(lambda x: (x, x * x)).to_store(uri))
+    assert not [f for f in os.listdir(tmp_path) if f.endswith(".tmp")]
+    back = sorted(ctx.from_store(uri).where(lambda t: t[0] < 5))
+    assert back == [(i, i * i) for i in range(5)]
+    text = tmp_path / "words.txt"
+    text.write_text("a b a\nc b a\n" * 50)
+    wc = dict(ctx.from_store(f"file://{text}").select_many(lambda l: l.line.split(" "))
+              .group_by(lambda w: w).select(lambda g: (g.key, g.count())))
+    assert wc == {"a": 150, "b": 100, "c": 50}
+
+
+def test_cluster_host_death_and_vertex_retry(tmp_path):
+    marker = str(tmp_path / "killed")
+
+    def inject(node, part, version):
+        # the first attempt of partition 1 of the grouping stage takes its whole host process down;
+        # the first attempt of partition 0 fails with an ordinary exception
+        if "GroupBy" in node.name and version == 0:
+            if part == 1 and not os.path.exists(marker):
+                open(marker, "w").close()
+                os._exit(7)
+            if part == 0:
+                raise RuntimeError("injected vertex failure")
+
+    ctx = _ctx(tmp_path, fault_injector=inject)
+    out = sorted(ctx.from_enumerable(range(600), 3).group_by(lambda x: x % 5).select(lambda g: (g.key, g.count())))
+    assert out == [(k, 120) for k in range(5)]
+    st = ctx.last_cluster_status
+    assert st["host_restarts"] >= 1 and st["counters"]["failures"] >= 2
+    log = open(os.path.join(str(tmp_path), "ClusterJobs", "1", "calypso.log")).read()
+    assert "exited" in log and "injected vertex failure" in log
+
+
+def test_cluster_unreadable_channel_reruns_producer(tmp_path):
+    from dryad_b200.runtime.executor import InputReadError
+
+    def inject(node, part, version):
+        if "GroupBy" in node.name and part == 0 and version == 0:
+            prod = node.children[0][0]
+            raise InputReadError(prod.uid, 1, "injected: channel file lost")
+
+    ctx = _ctx(tmp_path, fault_injector=inject)
+    out = sorted(ctx.from_enumerable(range(300), 3).group_by(lambda x: x % 3).select(lambda g: (g.key, g.count())))
+    assert out == [(0, 100), (1, 100), (2, 100)]
+    st = ctx.last_cluster_status
+    assert st["counters"]["invalidations"] >= 1
+    reruns = [v for v in st["vertices"] if v["version"] > 0]
+    assert any("HashPartition" in v["stage_name"] or "InputTable" in v["stage_name"] for v in reruns)     # the producer ran again
+
+
+def test_cluster_job_failure_publishes_nothing(tmp_path):
+    def inject(node, part, version):
+        if "Select" in node.name and part == 0:
+            raise ValueError("always broken")
+
+    ctx = _ctx(tmp_path, fault_injector=inject, max_failures_per_vertex=2)
+    uri = f"partfile://{tmp_path}/never.pt"
+    with pytest.raises(DryadLinqException) as e:
+        ctx.submit_and_wait(ctx.from_enumerable(range(30), 3).select(lambda x: x + 1).to_store(uri))
+    assert "always broken" in str(e.value)
+    assert not os.path.exists(tmp_path / "never.pt")
+    assert not [f for f in os.listdir(tmp_path) if f.startswith("never")]
+    st = json.load(open(os.path.join(str(tmp_path), "ClusterJobs", "1", "status.json")))
+    assert st["state"] == "Failure"
+
+
+def test_cluster_submission_cancel(tmp_path):
+    import time
+    from dryad_b200.api.context import JobStatus
+    from dryad_b200.api.submission import ClusterJobSubmission
+    from dryad_b200.runtime import jobpackage
+
+    def slow(node, part, version):
+        time.sleep(30)
+
+    ctx = DryadLinqContext(2, work_dir=str(tmp_path))
+    ctx.fault_injector = slow
+    q = ctx.from_enumerable(range(10), 2).select(lambda x: x).to_store(f"partfile://{tmp_path}/slow.pt")
+    job_dir = str(tmp_path / "job")
+    jobpackage.write(job_dir, ctx, [q.materialize_lazy()])
+    sub = ClusterJobSubmission(job_dir, workers=2)
+    sub.submit_job()
+    assert sub.get_status() == JobStatus.Running
+    time.sleep(3.0)
+    sub.terminate_job()
+    assert sub.get_status() == JobStatus.Cancelled
+    assert not os.path.exists(tmp_path / "slow.pt")
