@@ -326,6 +326,78 @@ int gm_resize_stage(void* h, int stage, int new_parts, int follow) {
   return (int)todo.size();
 }
 
+// Graph rewrite WHILE THE JOB RUNS (DrDynamicAggregateManager: an internal vertex takes over a group
+// of one consumer's inputs; DrDynamicBroadcastManager: a copy vertex stands between a producer and a
+// group of its consumers).  Adds ONE vertex to `stage` (a stage made with 0 partitions for this
+// purpose) whose inputs are `inputs`; in every listed consumer, the file edges from those inputs are
+// replaced by one edge from the new vertex (appended at the end of the consumer's input list).
+// Consumers must not have started.  Returns the new vertex id, or <0 and leaves the graph untouched.
+int gm_splice(void* h, int stage, const int* inputs, int n_in, const int* consumers, int n_cons) {
+  GM* g = (GM*)h;
+  std::lock_guard<std::mutex> l(g->mu);
+  if (stage < 0 || stage >= (int)g->stages.size() || n_in < 1 || n_cons < 1) return -1;
+  if (g->jstate != J_RUNNING && g->jstate != J_NOT_STARTED) return -1;
+  const int nv = (int)g->verts.size();
+  for (int i = 0; i < n_in; ++i) {
+    if (inputs[i] < 0 || inputs[i] >= nv || g->verts[inputs[i]].removed) return -2;
+  }
+  for (int c = 0; c < n_cons; ++c) {
+    if (consumers[c] < 0 || consumers[c] >= nv) return -3;
+    const Vertex& cv = g->verts[consumers[c]];
+    if (cv.removed || cv.clique >= 0 || (cv.state != V_WAITING && cv.state != V_READY) || !cv.running.empty()) return -4;
+    std::vector<int> left = cv.inputs;                    // every input must be an edge of every consumer
+    for (int i = 0; i < n_in; ++i) {
+      bool found = false;
+      for (size_t k = 0; k < left.size(); ++k)
+        if (left[k] == inputs[i] && !cv.input_fifo[k]) { left[k] = -1; found = true; break; }
+      if (!found) return -5;
+    }
+  }
+  {
+    Vertex v; v.id = nv; v.stage = stage; v.part = g->stages[stage].nparts;
+    g->verts.push_back(v);
+  }
+  g->stages[stage].vids.push_back(nv); g->stages[stage].nparts++; g->live++;
+  for (int i = 0; i < n_in; ++i) {
+    Vertex& up = g->verts[inputs[i]];
+    Vertex& me = g->verts[nv];
+    me.inputs.push_back(up.id); me.input_fifo.push_back(0);
+    if (up.state != V_COMPLETED) me.pending_inputs++;
+    up.consumers.push_back(nv); up.consumer_fifo.push_back(0);
+  }
+  for (int c = 0; c < n_cons; ++c) {
+    Vertex& cv = g->verts[consumers[c]];
+    for (int i = 0; i < n_in; ++i) {
+      Vertex& up = g->verts[inputs[i]];
+      for (size_t k = 0; k < cv.inputs.size(); ++k)
+        if (cv.inputs[k] == up.id && !cv.input_fifo[k]) {
+          cv.inputs.erase(cv.inputs.begin() + k); cv.input_fifo.erase(cv.input_fifo.begin() + k);
+          if (up.state != V_COMPLETED && cv.pending_inputs > 0) cv.pending_inputs--;
+          break;
+        }
+      for (size_t k = 0; k < up.consumers.size(); ++k)
+        if (up.consumers[k] == cv.id && !up.consumer_fifo[k]) {
+          up.consumers.erase(up.consumers.begin() + k); up.consumer_fifo.erase(up.consumer_fifo.begin() + k);
+          break;
+        }
+    }
+    cv.inputs.push_back(nv); cv.input_fifo.push_back(0); cv.pending_inputs++;
+    if (cv.state == V_READY) cv.state = V_WAITING;
+    g->verts[nv].consumers.push_back(cv.id); g->verts[nv].consumer_fifo.push_back(0);
+  }
+  if (g->jstate == J_RUNNING) make_ready_if_possible(g, g->verts[nv]);
+  return nv;
+}
+
+// Producer vertex ids of a vertex, in input order (what `bad_input` of gm_report_failed indexes).
+int gm_vertex_inputs(void* h, int vertex, int* out, int cap) {
+  GM* g = (GM*)h; std::lock_guard<std::mutex> l(g->mu);
+  if (vertex < 0 || vertex >= (int)g->verts.size()) return -1;
+  const Vertex& v = g->verts[vertex];
+  for (int i = 0; i < (int)v.inputs.size() && i < cap; ++i) out[i] = v.inputs[i];
+  return (int)v.inputs.size();
+}
+
 int gm_stage_vertices(void* h, int stage, int* out, int cap) {
   GM* g = (GM*)h; std::lock_guard<std::mutex> l(g->mu);
   if (stage < 0 || stage >= (int)g->stages.size()) return -1;

@@ -147,6 +147,11 @@ class DryadLinqContext:
         self.schedule_vertices = True          # place every vertex through the cluster interface + delay scheduler
         self.spmd_control_timeout = 120.0      # seconds a rank waits for the graph manager / the manager for a rank
         self.retain_intermediate = True
+        # run-time graph rewriting (cluster mode; DryadLinqGlobals.cs:40-52 DynamicOptLevel + the GM's thresholds)
+        self.dynamic_opt_level = SC.DYNAMIC_OPT_LEVEL      # which stages the planner tags for a dynamic manager
+        self.aggregation_tree_fan_in = 128                 # inputs per internal vertex (DrDynamicAggregateManager)
+        self.broadcast_tree_min_consumers = 5              # copy vertices for >= this many consumers (DrDynamicBroadcast)
+        self.dynamic_data_per_vertex = 0                   # bytes per consumer of a dynamic distributor; 0 = planned widths
         self.sample_rate = SC.SAMPLE_RATE
         self.group_capacity_hint = 1 << 26     # max initial hash-aggregate table slots per vertex
         self.broadcast_join_rows = 1 << 20     # planner rule: inner side at most this many rows -> broadcast join

@@ -41,6 +41,8 @@ class QueryGen:
             if e.op != "to_store":
                 raise DryadLinqException(ErrorCode.Internal, "plan roots must be outputs")
         self._memo: Dict[int, DLinqQueryNode] = {}
+        # DynamicOptLevel (DryadLinqGlobals.cs:40-52): which stages get a dynamic-manager tag
+        self._dyn_level = int(getattr(context, "dynamic_opt_level", SC.DYNAMIC_OPT_LEVEL))
         self.roots: List[DLinqQueryNode] = []
         self.nodes: List[DLinqQueryNode] = []
         self._built = False
@@ -119,7 +121,7 @@ class QueryGen:
         hp = self._node(NodeType.HashPartition, [(child, PW)], child.partition_count, None, child.schema,
                         key=key, nports=pc, comparer=comparer)
         hp.n_out_ports = pc
-        if SC.DYNAMIC_OPT_LEVEL & SC.DYN_HASH_PARTITION:
+        if self._dyn_level & SC.DYN_HASH_PARTITION:
             hp.dynamic_manager = DynamicManagerType.HashDistributor
         info = DataSetInfo(HashPartition(_ks(key), pc, comparer))
         return self._merge(hp, pc, CP, info)
@@ -205,7 +207,7 @@ class QueryGen:
                 part = self._node(NodeType.GroupBy, [(child, PW)], pc, None, None, key=key, elem=p.get("elem"),
                                   decomp=dec, mode="partial_acc", comparer=comparer)
                 part.dynamic_manager = DynamicManagerType.PartialAggregator \
-                    if ((SC.DYNAMIC_OPT_LEVEL & SC.DYN_AGGREGATE) or SC.GROUP_BY_DYNAMIC_REDUCE) else DynamicManagerType.NoManager
+                    if ((self._dyn_level & SC.DYN_AGGREGATE) or SC.GROUP_BY_DYNAMIC_REDUCE) else DynamicManagerType.NoManager
                 kir = X.col("key", key.ir.kind) if isinstance(key.ir, X.Expr) and key.ir.kind in "ifbs" else None
                 pkey = Lam(lambda kv: kv[0], kir, 1, "Key")
                 merged = self._hash_shuffle(part, pkey, pc, comparer)
@@ -249,7 +251,7 @@ class QueryGen:
         rp = self._node(NodeType.RangePartition, [(child, PW), (rs, PW)], child.partition_count, None, child.schema,
                         key=key, nports=pc, descending=desc, comparer=comparer, range_keys=None)
         rp.n_out_ports = pc
-        if SC.DYNAMIC_OPT_LEVEL & SC.DYN_RANGE_PARTITION:
+        if self._dyn_level & SC.DYN_RANGE_PARTITION:
             rp.dynamic_manager = DynamicManagerType.RangeDistributor
         info = DataSetInfo(RangePartition(ks, pc, None, desc, comparer))
         return self._merge(rp, pc, CP, info)
@@ -328,7 +330,7 @@ class QueryGen:
             # the other side is re-partitioned with the SAME separators (co-range); with DYN_CO_RANGE
             # the distributor is tagged so the runtime may re-balance both sides together
             merged = self._range_shuffle(side, key, part.count, part.descending, comparer, list(part.separators))
-            if SC.DYNAMIC_OPT_LEVEL & SC.DYN_CO_RANGE and merged.children:
+            if self._dyn_level & SC.DYN_CO_RANGE and merged.children:
                 merged.children[0][0].dynamic_manager = DynamicManagerType.RangeDistributor
             return merged
         if o_ok and isinstance(op, RangePartition) and op.has_keys():
@@ -383,7 +385,7 @@ class QueryGen:
         one = self._to_one(child)
         tee = self._node(NodeType.Tee, [(one, PW)], 1, one.info, one.schema, nports=pc, replicate=True)
         tee.n_out_ports = pc
-        tee.dynamic_manager = DynamicManagerType.Broadcast if (SC.DYNAMIC_OPT_LEVEL & SC.DYN_BROADCAST) else DynamicManagerType.NoManager
+        tee.dynamic_manager = DynamicManagerType.Broadcast if (self._dyn_level & SC.DYN_BROADCAST) else DynamicManagerType.NoManager
         return self._merge(tee, pc, CP)
 
     def _visit_broadcast(self, e: QExpr):
@@ -482,7 +484,7 @@ class QueryGen:
             assoc = is_associative(p["fn"].fn) and not p["has_seed"] and p.get("result") is None
             if assoc and pc > 1:
                 s1 = self._node(NodeType.Aggregate, [(child, PW)], pc, None, None, fn=p["fn"], stage=1, has_seed=False)
-                s1.dynamic_manager = DynamicManagerType.FullAggregator if (SC.DYNAMIC_OPT_LEVEL & SC.DYN_AGGREGATE) else DynamicManagerType.NoManager
+                s1.dynamic_manager = DynamicManagerType.FullAggregator if (self._dyn_level & SC.DYN_AGGREGATE) else DynamicManagerType.NoManager
                 one = self._to_one(s1)
                 return self._node(NodeType.Aggregate, [(one, PW)], 1, None, None, fn=p["fn"], stage=2, has_seed=False)
             one = self._to_one(child)
@@ -513,6 +515,8 @@ class QueryGen:
             s1_schema = s2_schema = dict(child.schema)
         s1 = self._node(NodeType.BasicAggregate, [(child, PW)], pc, None, s1_schema, kind=kind, stage=1, fn=p.get("fn"),
                         default=p.get("default", False))
+        if self._dyn_level & SC.DYN_AGGREGATE:
+            s1.dynamic_manager = DynamicManagerType.FullAggregator
         one = self._to_one(s1)
         return self._node(NodeType.BasicAggregate, [(one, PW)], 1, None, s2_schema, kind=kind, stage=2, fn=p.get("fn"),
                           default=p.get("default", False))

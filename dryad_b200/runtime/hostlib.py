@@ -64,6 +64,8 @@ _d("gm_add_stage", c_int, [P, c_char_p, c_int])
 _d("gm_connect", c_int, [P, c_int, c_int, c_int])
 _d("gm_connect_ex", c_int, [P, c_int, c_int, c_int, c_int])
 _d("gm_resize_stage", c_int, [P, c_int, c_int, c_int])
+_d("gm_splice", c_int, [P, c_int, C.POINTER(c_int), c_int, C.POINTER(c_int), c_int])
+_d("gm_vertex_inputs", c_int, [P, c_int, C.POINTER(c_int), c_int])
 _d("gm_stage_vertices", c_int, [P, c_int, C.POINTER(c_int), c_int])
 _d("gm_vertex_clique", c_int, [P, c_int, C.POINTER(c_int), c_int])
 _d("gm_live_vertex_count", c_int, [P])

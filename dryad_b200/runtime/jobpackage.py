@@ -26,7 +26,8 @@ _CTX_FIELDS = ("num_partitions", "storage_scheme", "intermediate_data_compressio
                "job_min_nodes", "job_max_nodes", "threads_per_worker", "enable_speculative_duplication",
                "select_order_preserving", "max_failures_per_vertex", "fail_fast_on_deterministic_errors",
                "retain_intermediate", "sample_rate", "group_capacity_hint", "broadcast_join_rows", "fault_injector",
-               "job_runtime_limit")
+               "job_runtime_limit", "dynamic_opt_level", "aggregation_tree_fan_in", "broadcast_tree_min_consumers",
+               "dynamic_data_per_vertex")
 
 
 def write(job_dir: str, context, roots) -> str:

@@ -136,6 +136,7 @@ class VertexHost:
         self.roots = {r.uid: r for r in self.plan.roots}
         self.compression = self.ctx.intermediate_data_compression_scheme
         self._versions: Dict[Tuple[int, int], int] = {}
+        self._subst: Dict[str, Optional[str]] = {}
         self._input_index: Dict[Tuple[int, int], int] = {}
         self._input_bytes: List[int] = []
         self._cache_hits = 0
@@ -152,6 +153,13 @@ class VertexHost:
     # ---- channels -------------------------------------------------------------------------------
     def load_input(self, uid: int, part: int, port: int):
         from .executor import InputReadError
+        hops = 0
+        while f"{uid}/{part}" in self._subst and hops < 64:       # run-time rewrites: follow the splice chain
+            t = self._subst[f"{uid}/{part}"]
+            if t is None:
+                return []                                          # folded into an internal vertex's output
+            uid, part, port = int(t.split("/")[0]), int(t.split("/")[1]), 0
+            hops += 1
         ver = self._versions.get((uid, part))
         if ver is None:
             raise InputReadError(uid, part, f"stage {uid}[{part}] is not an input of this vertex")
@@ -191,7 +199,14 @@ class VertexHost:
         from .vertex_ops import VertexEnv
         uid, version = cmd.vertex_id, cmd.version
         part, gmv = int(cmd.args[1]), int(cmd.args[2])
-        node = self.nodes[uid]
+        extra = cmd.args[3:]
+        internal = extra[1:4] if extra and extra[0] == "internal" else None     # [kind, consumer uid, port]
+        self._subst = {}
+        for a in extra:
+            if a.startswith("subst="):
+                import json
+                self._subst = json.loads(a[6:])
+        node = self.nodes[uid] if internal is None else None
         self._versions, self._input_index = {}, {}
         for k, (u, _len) in enumerate(cmd.inputs):                     # chan://<uid>/<part>/<version>
             a = u.split("://", 1)[1].split("/")
@@ -203,13 +218,23 @@ class VertexHost:
         t0 = time.perf_counter()
         outputs: List[Tuple[str, int]] = []
         try:
-            ins = self.ex._inputs(node, part)
-            # channels open lazily: touch every payload now so that a read error is an INPUT error
-            ins = [[p for p in payloads] for payloads in ins]
-            if self.ctx.fault_injector is not None:
-                self.ctx.fault_injector(node, part, version)
             env = VertexEnv(self.ctx, uid, part, version)
-            ports = self.backend.run_vertex(node, part, ins, env)
+            if internal is not None:
+                # an internal vertex of a run-time rewrite: fold / copy exactly the channels named in the command
+                from . import vertex_ops
+                subst, self._subst = self._subst, {}
+                payloads = [self.load_input(u, s, int(internal[2])) for (u, s) in self._input_index]
+                self._subst = subst
+                ins = [payloads]
+                if internal[0] == "copy":
+                    ports = [payloads[0]]
+                else:
+                    ports = [vertex_ops.internal_combine(self.nodes[int(internal[1])], [self.backend.to_records(p) for p in payloads], env)]
+            else:
+                ins = self.ex._inputs(node, part)
+                if self.ctx.fault_injector is not None:
+                    self.ctx.fault_injector(node, part, version)
+                ports = self.backend.run_vertex(node, part, ins, env)
             n_in = sum(self.backend.count(p) for inp in ins for p in inp)
             n_out = 0
             for k, payload in enumerate(ports):

@@ -585,6 +585,66 @@ def _basic_aggregate(node, part, inputs, env):
     raise DryadLinqException(ErrorCode.AggregateOperatorNotSupported, kind)
 
 
+# ---- internal vertices of a run-time aggregation tree -----------------------------------------------------------
+_COMMUTATIVE_KINDS = ("count", "sum", "min", "max", "any", "all", "average", "any_true")
+
+
+def combiner_of(node):
+    """The member of an N:1 consumer that combines per-partition partials — stage 2 of an Aggregate or
+    BasicAggregate directly behind the consumer's Merge — or None.  With it: (member, commutative)."""
+    members = node.members if node.type == NodeType.Super else [node]
+    for m in members:
+        if m.type == NodeType.Merge and m.params.get("sort_key") is None:
+            continue
+        if m.type == NodeType.BasicAggregate and m.params.get("stage") == 2 and m.params["kind"] != "sequence_equal":
+            return m, m.params["kind"] in _COMMUTATIVE_KINDS
+        if m.type == NodeType.Aggregate and m.params.get("stage") == 2:
+            return m, False                     # associative, not known to be commutative: contiguous groups only
+        return None
+    return None
+
+
+def internal_combine(node, payloads, env) -> List:
+    """What an internal vertex of the aggregation tree computes (the reference copies the consumer
+    stage's vertex as the internal vertex, GraphManager/stagemanager/DrDynamicAggregateManager.h:
+    24-179): it folds SOME of the consumer's partial inputs into ONE partial of the same shape, so the
+    consumer — or another internal vertex — can take it in their place."""
+    found = combiner_of(node)
+    if found is None:
+        raise DryadLinqException(ErrorCode.Internal, f"{node.name} has no combiner for an aggregation tree")
+    m = found[0]
+    src = _cat(payloads)
+    p = m.params
+    if m.type == NodeType.Aggregate:
+        return [L.aggregate(src, p["fn"].fn)] if src else []
+    kind = p["kind"]
+    if kind in ("count", "sum"):
+        return [L.sum_(src)]
+    if kind in ("any", "any_true"):
+        return [any(src)]
+    if kind == "all":
+        return [all(src)]
+    if not src:
+        return []
+    if kind == "min":
+        return [min(src)]
+    if kind == "max":
+        return [max(src)]
+    if kind == "average":
+        s, c = 0, 0
+        for ps, pc in src:
+            s = L.checked_add(s, ps) if isinstance(ps, int) else s + ps
+            c += pc
+        return [(s, c)]
+    if kind == "first":
+        return src[:1]
+    if kind == "last":
+        return src[-1:]
+    if kind == "single":
+        return src[:2]
+    raise DryadLinqException(ErrorCode.AggregateOperatorNotSupported, kind)
+
+
 def _contains(node, part, inputs, env):
     return [[L.contains(_cat(inputs[0]), node.params["value"])]]
 

@@ -54,6 +54,25 @@ class GraphManager:
             raise ValueError(f"stage {stage} cannot be resized to {new_parts} (rc {rc})")
         return rc
 
+    def splice(self, stage: int, inputs: List[int], consumers: List[int]) -> int:
+        """Run-time graph rewrite: ONE new vertex in `stage` (made with `add_stage(name, 0)`) reads
+        `inputs`; in every consumer the edges from those inputs become one edge from the new vertex
+        (DrDynamicAggregateManager internal vertices, DrDynamicBroadcastManager copy vertices).
+        Returns the new vertex id."""
+        a = (C.c_int * len(inputs))(*inputs)
+        b = (C.c_int * len(consumers))(*consumers)
+        v = self.lib.gm_splice(self.h, stage, a, len(inputs), b, len(consumers))
+        if v < 0:
+            raise ValueError(f"cannot splice a vertex into stage {stage} (rc {v})")
+        self._nverts = max(self._nverts, v + 1)
+        return v
+
+    def vertex_inputs(self, vertex: int) -> List[int]:
+        n = self.lib.gm_vertex_inputs(self.h, vertex, None, 0)
+        out = (C.c_int * max(n, 1))()
+        self.lib.gm_vertex_inputs(self.h, vertex, out, n)
+        return list(out)[:n]
+
     def stage_vertices(self, stage: int) -> List[int]:
         n = self.lib.gm_stage_vertices(self.h, stage, None, 0)
         out = (C.c_int * max(n, 1))()

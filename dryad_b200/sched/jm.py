@@ -65,6 +65,14 @@ class JobManager:
         self.ex = JobExecutor(self.ctx, self.plan, reporter=self.reporter)
         self.gm = self.ex._build_gm()
         self.nodes = self.ex._gm_stage_node                                   # gm stage id -> plan node
+        self.node_by_uid = {n.uid: n for n in self.plan.nodes}
+        self.vid: Dict[Tuple[int, int], int] = {}                             # (stage uid, part) -> gm vertex
+        self.vkey: Dict[int, Tuple[int, int]] = {}                            # gm vertex -> (stage uid, part)
+        for st, n in self.nodes.items():
+            first = self.gm.stage_first_vertex[st]
+            for p_ in range(n.partition_count):
+                self.vid[(n.uid, p_)] = first + p_
+                self.vkey[first + p_] = (n.uid, p_)
         width = max(n.partition_count for n in self.plan.nodes)
         want = workers or int(self.ctx.job_max_nodes or 0) or min(width, os.cpu_count() or 1)
         self.nhosts = max(1, max(int(self.ctx.job_min_nodes or 0), want))
@@ -88,6 +96,8 @@ class JobManager:
         self.stats: List[dict] = []
         self.messages = 0
         self._watchers: List[threading.Thread] = []
+        from .dynamic import DynamicManagers
+        self.dyn = DynamicManagers(self)
         self.pump = MessagePump(self._on_message, threads=1)                  # ONE consumer: graph changes are serialised
 
     # ---- vertex hosts -----------------------------------------------------------------------------
@@ -199,6 +209,7 @@ class JobManager:
                     if "|" in path:
                         tmp, final = path.split("|", 1)
                         self.part_files[(node.uid, part)] = (tmp, final, size)
+                self.dyn.on_completed(v, h.index)                             # run-time rewrites, before anything is dispatched
             ins = self.ex._gm_inputs.get(v, [])
             local = sum(self.records.get(e, 0) for e in ins if self.where.get(e) == h.index)
             total = sum(self.records.get(e, 0) for e in ins)
@@ -282,7 +293,7 @@ class JobManager:
             node, part = self._vertex(v)
             inputs = [(f"chan://{uid}/{s}/{self.versions.get((uid, s), 0)}", self.records.get((uid, s), 0))
                       for uid, s in self.ex._gm_inputs.get(v, [])]
-            cmd = VertexCommand(CMD_START, node.uid, version, args=[node.name, str(part), str(v)], inputs=inputs,
+            cmd = VertexCommand(CMD_START, node.uid, version, args=[node.name, str(part), str(v)] + self.dyn.command_args(v), inputs=inputs,
                                 outputs=[(f"chan://{node.uid}/{part}/{version}", 0)])
             h.busy = (v, version, time.perf_counter())
             self._mbox(h.name).set("cmd", "start", cmd.serialize())
@@ -334,7 +345,7 @@ class JobManager:
         self.reporter.job_stop(ok, error, seconds=time.perf_counter() - self.t0, **counters)
         status = {"state": "Success" if ok else "Failure", "error": error, "tables": tables or {}, "counters": counters,
                   "hosts": self.nhosts, "host_restarts": sum(h.restarts for h in self.hosts),
-                  "pump_messages": self.messages, "seconds": time.perf_counter() - self.t0, "vertices": self.stats}
+                  "pump_messages": self.messages, "dynamic": dict(self.dyn.spliced), "seconds": time.perf_counter() - self.t0, "vertices": self.stats}
         tmp = os.path.join(self.job_dir, STATUS_FILE + ".tmp")
         with open(tmp, "w") as f:
             json.dump(status, f)

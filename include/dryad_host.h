@@ -57,6 +57,9 @@ int gm_connect_ex(void* h, int src_stage, int dst_stage, int kind, int channel);
 /* Dynamic resize of a not-yet-started stage; follow != 0 propagates the new width to the pointwise
  * stages downstream of equal width (DrPipelineSplitManager).  Returns stages resized or < 0. */
 int gm_resize_stage(void* h, int stage, int new_parts, int follow);
+/* run-time rewrite: one new vertex in `stage` takes over the edges inputs -> consumers; returns its id */
+int gm_splice(void* h, int stage, const int* inputs, int n_in, const int* consumers, int n_cons);
+int gm_vertex_inputs(void* h, int vertex, int* out, int cap);
 int gm_stage_vertices(void* h, int stage, int* out, int cap);
 int gm_vertex_clique(void* h, int vertex, int* out, int cap);
 int gm_live_vertex_count(void* h);

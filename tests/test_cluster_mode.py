@@ -139,3 +139,45 @@ def test_cluster_submission_cancel(tmp_path):
     sub.terminate_job()
     assert sub.get_status() == JobStatus.Cancelled
     assert not os.path.exists(tmp_path / "slow.pt")
+
+
+def test_cluster_runtime_aggregation_tree(tmp_path):
+    """DYN_AGGREGATE: internal vertices are spliced into the RUNNING graph between the partial
+    aggregates and their N:1 consumer (DrDynamicAggregateManager)."""
+    import operator
+    from dryad_b200.plan import static_config as SC
+    ctx = _ctx(tmp_path, n=12, hosts=3, dynamic_opt_level=SC.DYN_BROADCAST | SC.DYN_AGGREGATE, aggregation_tree_fan_in=3)
+    data = list(range(1, 1201))
+    q = ctx.from_enumerable(data, 12)
+    assert q.sum() == sum(data)
+    st = ctx.last_cluster_status
+    assert st["dynamic"]["aggregate"] >= 3                 # 12 partials, at most 3 inputs per vertex
+    internal = [v for v in st["vertices"] if v["stage_name"].startswith("Agg__")]
+    assert len(internal) == st["dynamic"]["aggregate"] and all(v["records_out"] == 1 for v in internal)
+    final = [v for v in st["vertices"] if "BasicAggregate" in v["stage_name"] and v["stage"] < 1_000_000 and v["part"] == 0
+             and v["records_in"] and len(v["bytes_in"]) <= 3 + 1][-1:]
+    assert final                                           # the consumer read at most fan-in inputs (+ none folded)
+    log = open(os.path.join(str(tmp_path), "ClusterJobs", "1", "calypso.log")).read()
+    assert "dynamic,manager=aggregate" in log
+    # average and max through the same trees
+    assert q.average() == sum(data) / len(data)
+    assert q.max() == 1200
+    # an associative function that is NOT commutative: groups are contiguous runs, the order of the partials is kept
+    words = [chr(ord("a") + i % 26) for i in range(120)]
+    cat = ctx.from_enumerable(words, 12).aggregate(operator.add)
+    assert cat == "".join(words)
+    assert ctx.last_cluster_status["dynamic"]["aggregate"] >= 3
+
+
+def test_cluster_runtime_broadcast_copies(tmp_path):
+    """DYN_BROADCAST (on by default, like the reference): a broadcast to >= 5 consumers goes through
+    floor(sqrt(n)) copy vertices spliced in when the producer completes (DrDynamicBroadcast)."""
+    ctx = _ctx(tmp_path, n=6, hosts=3)
+    big = ctx.from_enumerable(range(600), 6)
+    small = ctx.from_enumerable([(k, k * k) for k in range(0, 600, 50)], 2)
+    out = sorted(big.join(small, lambda x: x, lambda t: t[0], lambda x, t: (x, t[1])))   # small inner side: broadcast join
+    assert out == [(k, k * k) for k in range(0, 600, 50)]
+    st = ctx.last_cluster_status
+    assert st["dynamic"]["copy"] == 2                      # floor(sqrt(6))
+    copies = [v for v in st["vertices"] if v["stage_name"].startswith("CP__")]
+    assert len(copies) == 2 and all(v["records_out"] == 12 for v in copies)

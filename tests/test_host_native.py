@@ -404,3 +404,65 @@ def test_vertex_env_buffer_sizing_threads_and_error_report(tmp_path, monkeypatch
         path = env.report_vertex_error(ex, str(tmp_path))
     text = open(path).read()
     assert path.endswith("VertexException.txt") and "vertex 7 partition 2 version 1" in text and "bad record" in text
+
+
+def test_gm_splice_rewrites_a_running_graph():
+    """Run-time rewrite (DrDynamicAggregateManager / DrDynamicBroadcast): a new vertex takes over edges
+    of vertices that have not started; retries and upstream invalidation keep working through it."""
+    from dryad_b200.sched.gm import GraphManager
+    gm = GraphManager(max_failures=4, speculative=False)
+    a = gm.add_stage("partial", 4)
+    b = gm.add_stage("final", 1)
+    dyn = gm.add_stage("Agg__final", 0)
+    gm.connect(a, b)
+    gm.start()
+    started = {}
+    while True:
+        nxt = gm.next_ready(0.0)
+        if nxt is None:
+            break
+        started[nxt[0]] = nxt[1]
+    assert sorted(started) == [0, 1, 2, 3]
+    gm.completed(0, 0, 0.1)
+    gm.completed(1, 0, 0.1)
+    x = gm.splice(dyn, [0, 1], [4])                       # both inputs complete: the internal vertex is runnable at once
+    assert gm.vertex(x)["stage"] == dyn and gm.vertex(x)["part"] == 0
+    assert gm.vertex_inputs(4) == [2, 3, x] and gm.vertex_inputs(x) == [0, 1]
+    assert gm.next_ready(0.0) == (x, 0)
+    gm.completed(2, 0, 0.1)
+    gm.completed(3, 0, 0.1)
+    assert gm.next_ready(0.0) is None and gm.vertex(4)["state"] == "Waiting"      # the consumer waits for the new vertex
+    with pytest.raises(ValueError):
+        gm.splice(dyn, [0], [4])                           # 0 is no longer an input of the consumer
+    gm.completed(x, 0, 0.1)
+    assert gm.next_ready(0.0) == (4, 0)
+    # the consumer cannot read the internal vertex's output: it is revoked and runs again from ITS inputs
+    assert gm.failed(4, 0, "cannot read", bad_input=2) == 2
+    assert gm.next_ready(0.0) == (x, 1)
+    gm.completed(x, 1, 0.1)
+    v, ver = gm.next_ready(0.0)
+    assert v == 4
+    with pytest.raises(ValueError):
+        gm.splice(dyn, [2], [4])                           # a started consumer cannot be rewired
+    gm.completed(4, ver, 0.1)
+    assert gm.state == "Succeeded" and gm.counters()["completed"] == 6
+    # copy vertex between one producer and several consumers
+    g2 = GraphManager(speculative=False)
+    p = g2.add_stage("tee", 1)
+    c = g2.add_stage("join", 6)
+    cp = g2.add_stage("CP__tee", 0)
+    g2.connect(p, c)
+    g2.start()
+    assert g2.next_ready(0.0) == (0, 0)
+    g2.completed(0, 0, 0.1)
+    x1 = g2.splice(cp, [0], [1, 2, 3])
+    x2 = g2.splice(cp, [0], [4, 5, 6])
+    ready = []
+    while (n := g2.next_ready(0.0)) is not None:
+        ready.append(n[0])
+    assert sorted(ready) == [x1, x2]
+    g2.completed(x1, 0, 0.1)
+    ready = []
+    while (n := g2.next_ready(0.0)) is not None:
+        ready.append(n[0])
+    assert sorted(ready) == [1, 2, 3]
