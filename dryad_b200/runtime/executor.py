@@ -227,12 +227,25 @@ class JobExecutor:
                 "records_local": local, "records_remote": total - local}
 
     # ---- graph manager wiring -------------------------------------------------------------------
+    @staticmethod
+    def edge_is_cross_product(node: DLinqQueryNode, child: DLinqQueryNode, op) -> bool:
+        """How the edge child -> node is expanded in the graph manager: cross product when the plan
+        says so, and conservatively for the operators whose vertices read neighbouring partitions."""
+        special = (NodeType.Concat, NodeType.Zip, NodeType.Reverse, NodeType.SlidingWindow)
+        head = node.members[0].type if node.type == NodeType.Super else node.type
+        cpc, pc = child.partition_count, node.partition_count
+        conservative = head in special or not (cpc == pc or cpc == 1 or pc == 1 or (pc and cpc % pc == 0))
+        return op == ConnOp.CrossProduct or conservative
+
     def _build_gm(self):
         """Mirror the physical plan into the native graph manager: one GM stage per plan node, one
         GM vertex per partition, edges expanded by the same connection rules the data follows."""
         from ..sched.gm import CHANNEL_FIFO, CHANNEL_FILE, CROSS_PRODUCT, POINTWISE, GraphManager
         ctx = self.context
         gm = GraphManager(max_failures=ctx.max_failures_per_vertex, speculative=ctx.enable_speculative_duplication)
+        # straggler thresholds (DrGraphParameters.cpp:50-69: default outlier threshold 10 min, never below 10 s)
+        gm.set_outlier_params(float(getattr(ctx, "duplicate_default_seconds", 600.0)),
+                              float(getattr(ctx, "duplicate_min_seconds", 10.0)))
         sid = {}
         self._gm_inputs: Dict[int, List[Tuple[int, int]]] = {}       # gm vertex -> [(producer uid, part)]
         special = (NodeType.Concat, NodeType.Zip, NodeType.Reverse, NodeType.SlidingWindow)
@@ -243,8 +256,7 @@ class JobExecutor:
             first = gm.stage_first_vertex[sid[node.uid]]
             for child, op in node.children:
                 cpc, pc = child.partition_count, node.partition_count
-                conservative = head in special or not (cpc == pc or cpc == 1 or pc == 1 or (pc and cpc % pc == 0))
-                kind = CROSS_PRODUCT if (op == ConnOp.CrossProduct or conservative) else POINTWISE
+                kind = CROSS_PRODUCT if self.edge_is_cross_product(node, child, op) else POINTWISE
                 # a MemoryFIFO edge streams: producer and consumer vertices form one start clique
                 fifo = kind == POINTWISE and cpc == pc and getattr(child.channel_type, "value", "") == "MemoryFIFO"
                 gm.connect(sid[child.uid], sid[node.uid], kind, CHANNEL_FIFO if fifo else CHANNEL_FILE)

@@ -206,6 +206,16 @@ class VertexHost:
             if a.startswith("subst="):
                 import json
                 self._subst = json.loads(a[6:])
+            elif a.startswith("widths="):
+                import json
+                w = json.loads(a[7:])                   # widths decided at run time by the dynamic distributor
+                for k, n in w.get("widths", {}).items():
+                    self.nodes[int(k)].partition_count = int(n)
+                for k, n in w.get("nports", {}).items():
+                    d = self.nodes[int(k)]
+                    tail = d.members[-1] if getattr(d, "members", None) else d
+                    tail.params["nports"] = int(n)
+                    d.n_out_ports = int(n)
         node = self.nodes[uid] if internal is None else None
         self._versions, self._input_index = {}, {}
         for k, (u, _len) in enumerate(cmd.inputs):                     # chan://<uid>/<part>/<version>

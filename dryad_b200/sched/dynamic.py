@@ -48,8 +48,11 @@ class DynamicManagers:
         self.subst: Dict[int, Dict[str, Optional[str]]] = {}   # consumer gm vertex -> {"U/s": "X/p" | None}
         self.spliced = {"aggregate": 0, "copy": 0, "resized": 0}
         self._bcast_done: set = set()
-        self._dist_done: set = set()
+        self.dist: Dict[int, dict] = {}             # distributor stage uid -> state
+        self.widths: Dict[int, int] = {}            # stage uid -> partition count decided at run time
+        self.nports: Dict[int, int] = {}            # distributor stage uid -> output ports decided at run time
         self._find_candidates()
+        self._find_distributors()
 
     # ---- which vertices are eligible --------------------------------------------------------------
     def _find_candidates(self) -> None:
@@ -111,6 +114,87 @@ class DynamicManagers:
         """Called after vertex v's completion was applied to the graph and before anything is dispatched."""
         self._aggregate(v, host)
         self._broadcast(v)
+        self._distribute()
+
+    # ---- dynamic distributor ------------------------------------------------------------------------
+    def _find_distributors(self) -> None:
+        from ..plan.qnodes import ConnOp
+        from ..runtime.executor import JobExecutor
+        jm = self.jm
+        if not self.data_per_vertex:
+            return
+        xp = JobExecutor.edge_is_cross_product
+        for node in jm.plan.nodes:
+            tail = node.members[-1] if node.type == NodeType.Super else node
+            if tail.type != NodeType.HashPartition or node.dynamic_manager != DynamicManagerType.HashDistributor:
+                continue
+            if not node.children or len(node.parents) != 1:
+                continue
+            cons = node.parents[0]
+            op = next(o for c, o in cons.children if c is node)
+            if op != ConnOp.CrossProduct or cons.partition_count != tail.params.get("nports") or len(cons.children) != 1:
+                continue
+            # the stages that change width with the consumer (pointwise, same width), as the native resize follows them
+            old = cons.partition_count
+            follow = [cons]
+            ok = True
+            for n in follow:
+                for par in n.parents:
+                    pop = next(o for c, o in par.children if c is n)
+                    if xp(par, n, pop):
+                        continue                                      # cross product: any widths connect
+                    if par.partition_count == old:
+                        if par not in follow:
+                            follow.append(par)
+                    elif par.partition_count != 1:
+                        ok = False                                    # grouped pointwise edge: widths must divide
+            for n in follow[1:]:
+                for c, o in n.children:
+                    if c not in follow and not xp(n, c, o) and c.partition_count != 1:
+                        ok = False                                    # a second same-width input (co-partitioned join)
+            if ok:
+                self.dist[node.uid] = {"node": node, "tail": tail, "consumer": cons, "follow": follow, "decided": False,
+                                       "held": []}
+
+    def hold(self, v: int, version: int) -> bool:
+        """A distributor vertex is not dispatched before its stage's output width has been decided."""
+        key = self.jm.vkey.get(v)
+        st = self.dist.get(key[0]) if key else None
+        if st is None or st["decided"]:
+            return False
+        st["held"].append((v, version))
+        return True
+
+    def _distribute(self) -> None:
+        from .gm import consumer_count
+        jm = self.jm
+        for uid, st in self.dist.items():
+            if st["decided"]:
+                continue
+            node = st["node"]
+            ups = [(c.uid, i) for c, _ in node.children for i in range(c.partition_count)]
+            if any(k not in jm.versions for k in ups):
+                continue
+            st["decided"] = True
+            total = sum(jm.out_bytes.get(k, 0) for k in ups)
+            old = st["consumer"].partition_count
+            new = consumer_count(total, self.data_per_vertex, 1, 20000)
+            if new != old:
+                stage = jm.stage_of_uid[st["consumer"].uid]
+                n = jm.gm.resize_stage(stage, new, follow=True)
+                for f in st["follow"]:
+                    f.partition_count = new
+                    self.widths[f.uid] = new
+                st["tail"].params["nports"] = new
+                node.n_out_ports = new
+                self.nports[uid] = new
+                jm.rebuild_maps()
+                self.spliced["resized"] += n
+                jm.reporter._emit("dynamic", manager="distributor", stage=uid, bytes=total, consumers_before=old,
+                                  consumers=new, stages_resized=n)
+            held, st["held"] = st["held"], []
+            for v, version in held:
+                jm.enqueue(v, version)
 
     def _aggregate(self, v: int, host: int) -> None:
         jm = self.jm
@@ -225,4 +309,6 @@ class DynamicManagers:
         sub = self.subst.get(v)
         if sub:
             out.append("subst=" + json.dumps(sub))
+        if self.widths or self.nports:
+            out.append("widths=" + json.dumps({"widths": self.widths, "nports": self.nports}))
         return out

@@ -87,6 +87,8 @@ class JobManager:
         self.versions: Dict[Tuple[int, int], int] = {}                        # (stage uid, part) -> completed version
         self.where: Dict[Tuple[int, int], int] = {}                           # (stage uid, part) -> host that holds it in cache
         self.records: Dict[Tuple[int, int], int] = {}                         # (stage uid, part) -> output records
+        self.out_bytes: Dict[Tuple[int, int], int] = {}                       # (stage uid, part) -> channel bytes written
+        self.stage_of_uid = {n.uid: st for st, n in self.nodes.items()}
         self.part_files: Dict[Tuple[int, int], Tuple[str, str, int]] = {}     # root (uid, part) -> (tmp, final, size)
         self.done = threading.Event()
         self.ok = False
@@ -205,6 +207,7 @@ class JobManager:
                 self.versions[(node.uid, part)] = version
                 self.where[(node.uid, part)] = h.index
                 self.records[(node.uid, part)] = n_out
+                self.out_bytes[(node.uid, part)] = sum(sz for pth, sz in st.outputs if "|" not in pth)
                 for path, size in st.outputs:
                     if "|" in path:
                         tmp, final = path.split("|", 1)
@@ -256,31 +259,49 @@ class JobManager:
             return
         self._launch(h)
 
-    def _dispatch(self) -> None:
-        from ..runtime.command import CMD_START, VertexCommand, affinity_merge
+    def enqueue(self, v: int, version: int) -> None:
+        """Queue one vertex attempt with the scheduler, with its input affinities."""
+        from ..runtime.command import affinity_merge
         from .cluster import Affinity, Process
+        node, part = self._vertex(v)
+        votes: Dict[int, int] = {}
+        for e in self.ex._gm_inputs.get(v, []):
+            w = self.where.get(e)
+            if w is not None:
+                votes[w] = votes.get(w, 0) + max(1, self.records.get(e, 0))
+        prefer: List[int] = []
+        if votes:
+            level, choice = affinity_merge(sorted(votes.items()), [0] * self.nhosts)
+            if level == "computer":
+                prefer = [choice]
+        pid = self._next_pid
+        self._next_pid += 1
+        self.pending[pid] = (v, version)
+        self.cluster.schedule_process(Process(pid, f"{node.name}#{node.uid}[{part}]", Affinity(prefer, sum(votes.values()), False)))
+        self.reporter.vertex_event(node, part, version, "created", prefer=prefer[0] if prefer else None)
+
+    def rebuild_maps(self) -> None:
+        """After a run-time resize the native graph is the truth: vertex ids and input lists are re-read."""
+        self.stage_of_uid = {n.uid: st for st, n in self.nodes.items()}
+        for st, n in self.nodes.items():
+            for idx, vid in enumerate(self.gm.stage_vertices(st)):
+                self.vid[(n.uid, idx)] = vid
+                self.vkey[vid] = (n.uid, idx)
+        for vid in list(self.vkey):
+            if self.vid.get(self.vkey[vid]) == vid:
+                self.ex._gm_inputs[vid] = [self.vkey[p] for p in self.gm.vertex_inputs(vid)]
+
+    def _dispatch(self) -> None:
+        from ..runtime.command import CMD_START, VertexCommand
         now = time.perf_counter() - self.t0
         while True:
             nxt = self.gm.next_ready(now)
             if nxt is None:
                 break
             v, version = nxt
-            node, part = self._vertex(v)
-            votes: Dict[int, int] = {}
-            for e in self.ex._gm_inputs.get(v, []):
-                w = self.where.get(e)
-                if w is not None:
-                    votes[w] = votes.get(w, 0) + max(1, self.records.get(e, 0))
-            prefer: List[int] = []
-            if votes:
-                level, choice = affinity_merge(sorted(votes.items()), [0] * self.nhosts)
-                if level == "computer":
-                    prefer = [choice]
-            pid = self._next_pid
-            self._next_pid += 1
-            self.pending[pid] = (v, version)
-            self.cluster.schedule_process(Process(pid, f"{node.name}#{node.uid}[{part}]", Affinity(prefer, sum(votes.values()), False)))
-            self.reporter.vertex_event(node, part, version, "created", prefer=prefer[0] if prefer else None)
+            if self.dyn.hold(v, version):
+                continue
+            self.enqueue(v, version)
         waiting = self.cluster.scheduler.waiting
         if not waiting:
             return
@@ -353,6 +374,24 @@ class JobManager:
         self.ok = ok
         self.done.set()
 
+    def _remove_uncommitted(self) -> None:
+        """Failed and cancelled jobs leave no partial outputs: drop every uncommitted part version."""
+        import glob
+        from ..channel import store
+        from ..runtime.vertex_host import temp_output_uri
+        for root in self.plan.roots:
+            onode = root if root.type.value == "OutputTable" else root.members[-1]
+            uri = onode.params.get("uri") or temp_output_uri(self.job_dir, onode.params["qexpr_id"])
+            try:
+                _, path = store.parse_uri(uri)
+            except Exception:  # noqa: BLE001
+                continue
+            for f in glob.glob(glob.escape(os.path.splitext(path)[0]) + ".*.tmp"):
+                try:
+                    os.remove(f)
+                except OSError:
+                    pass
+
     def run(self) -> int:
         os.makedirs(os.path.join(self.job_dir, "log"), exist_ok=True)
         self.reporter.job_start(self.plan)
@@ -386,6 +425,8 @@ class JobManager:
                 h.proc.wait(max(0.05, deadline - time.monotonic()))
             except subprocess.TimeoutExpired:
                 h.proc.kill()                                                 # the exact process we started
+        if not self.ok:
+            self._remove_uncommitted()                                        # a host may have written a part after the verdict
         for t in self._watchers:                                              # nobody may post to a pump that is gone
             t.join(5.0)
         self.pump.close()

@@ -181,3 +181,50 @@ def test_cluster_runtime_broadcast_copies(tmp_path):
     assert st["dynamic"]["copy"] == 2                      # floor(sqrt(6))
     copies = [v for v in st["vertices"] if v["stage_name"].startswith("CP__")]
     assert len(copies) == 2 and all(v["records_out"] == 12 for v in copies)
+
+
+def test_cluster_runtime_distributor_resizes_consumers(tmp_path):
+    """DYN_HASH_PARTITION: the number of consumers of a hash repartitioning is decided from the data
+    volume once the upstream stage has finished; the distributor's vertices are held until then and the
+    pointwise stages downstream follow the new width (DrDynamicDistributionManager, DrPipelineSplitManager)."""
+    from dryad_b200.channel import store
+    from dryad_b200.plan import static_config as SC
+    ctx = _ctx(tmp_path, n=4, hosts=2, dynamic_opt_level=SC.DYN_BROADCAST | SC.DYN_HASH_PARTITION, dynamic_data_per_vertex=1500)
+    uri = f"partfile://{tmp_path}/groups.pt"
+    q = ctx.from_enumerable(range(1000), 4).group_by(lambda x: x % 13).select(lambda g: (g.key, g.count())).to_store(uri)
+    ctx.submit_and_wait(q)
+    st = ctx.last_cluster_status
+    assert st["dynamic"]["resized"] >= 1
+    info = store.stream_info(uri)
+    assert info.partition_count != 4 and info.partition_count == st["tables"][list(st["tables"])[0]]["partitions"]
+    assert sorted(ctx.from_store(uri)) == sorted((k, len([x for x in range(1000) if x % 13 == k])) for k in range(13))
+    finals = [v for v in st["vertices"] if "GroupBy" in v["stage_name"]]
+    assert len({v["part"] for v in finals}) == info.partition_count
+    log = open(os.path.join(str(tmp_path), "ClusterJobs", "1", "calypso.log")).read()
+    assert "dynamic,manager=distributor" in log
+    # a co-partitioned join must NOT be resized on one side only: the manager leaves it alone
+    a = ctx.from_enumerable(range(200), 4)
+    b = ctx.from_enumerable([(k, -k) for k in range(0, 200, 2)], 4)
+    ctx.broadcast_join_rows = 0
+    j = sorted(a.join(b, lambda x: x, lambda t: t[0], lambda x, t: (x, t[1])))
+    assert j == [(k, -k) for k in range(0, 200, 2)]
+
+
+def test_cluster_speculative_duplicate_beats_a_straggler(tmp_path):
+    """A vertex that runs far beyond its stage's model gets a duplicate on another host; the first
+    version to finish wins (DrDefaultManager / DrStageStatistics; GraphManager/stagemanager/DrStageManager.cpp)."""
+    import time
+
+    def straggle(node, part, version):
+        if "Select" in node.name and part == 3 and version == 0:
+            time.sleep(25)
+
+    ctx = _ctx(tmp_path, n=4, hosts=3, fault_injector=straggle, duplicate_default_seconds=1.0, duplicate_min_seconds=0.5)
+    t0 = time.time()
+    out = sorted(ctx.from_enumerable(range(40), 4).select(lambda x: x * 3))
+    assert out == [x * 3 for x in range(40)]
+    assert time.time() - t0 < 20                                  # did not wait for the sleeping attempt
+    st = ctx.last_cluster_status
+    assert st["counters"]["duplicates"] >= 1
+    winners = [v for v in st["vertices"] if "Select" in v["stage_name"] and v["part"] == 3 and v["won"]]
+    assert winners and winners[0]["version"] >= 1
