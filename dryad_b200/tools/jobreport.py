@@ -40,7 +40,22 @@ def build_job(job_dir: str) -> Dict[str, Any]:
     stages: Dict[str, Dict[str, Any]] = {}
     attempts: Dict[tuple, Dict[str, Any]] = {}
     job: Dict[str, Any] = {"dir": job_dir, "success": None, "error": None, "seconds": None}
+    processes: Dict[str, Dict[str, Any]] = {}       # cluster mode: vertex-host processes
+    rewrites: List[Dict[str, Any]] = []             # run-time graph rewrites (dynamic managers)
     for e in events:
+        if e["event"] == "process":
+            p = processes.setdefault(e.get("host", "?"), {"host": e.get("host", "?"), "pid": None, "created": None, "started": None,
+                                                       "exited": None, "exitcode": None, "vertices": 0})
+            if e.get("pid"):
+                p["pid"] = int(e["pid"])
+            if e.get("state") in ("created", "started", "exited"):
+                p[e["state"]] = e["ts"]
+            if e.get("exitcode") not in (None, "None"):
+                p["exitcode"] = int(e["exitcode"])
+            continue
+        if e["event"] == "dynamic":
+            rewrites.append({k: v for k, v in e.items() if k != "event"})
+            continue
         if e["event"] == "topology":
             stages[e["stage"]] = {"id": int(e["stage"]), "name": e.get("stagename", ""), "type": e.get("type", ""),
                                   "partitions": int(e.get("partitions", 0)), "children": e.get("children", "").split(),
@@ -53,6 +68,8 @@ def build_job(job_dir: str) -> Dict[str, Any]:
             a["state"] = e["state"]
             if "computer" in e:
                 a["computer"] = e["computer"]
+            if e["state"] == "created":
+                continue
             if e["state"] == "starting":
                 a["start"] = e["ts"]
             else:
@@ -74,6 +91,8 @@ def build_job(job_dir: str) -> Dict[str, Any]:
             for k in ("completed", "failures", "duplicates", "invalidations"):
                 if k in e:
                     job[k] = int(e[k])
+    job["processes"] = sorted(processes.values(), key=lambda p: p["host"])
+    job["rewrites"] = rewrites
     job["stages"] = sorted(stages.values(), key=lambda s: s["id"])
     job["attempts"] = sorted(attempts.values(), key=lambda a: (a["start"] or "", a["vertex"]))
     # static plan as written by the client: a job whose plan file cannot be parsed never had a graph
@@ -100,7 +119,7 @@ def diagnose(job: Dict[str, Any]) -> List[str]:
         out.append(f"the XML query plan cannot be parsed ({job['plan_error']}): the graph manager never built a graph — "
                    "client and graph manager disagree on the plan format")
     failed = [a for a in job["attempts"] if a["state"] == "failed"]
-    if not failed and job.get("success"):
+    if not failed and job.get("success") and not any(p.get("exitcode") not in (None, 0) for p in job.get("processes", [])):
         return out + ["job succeeded; no failed vertex attempts"]
     by_vertex = defaultdict(list)
     for a in failed:
@@ -145,6 +164,14 @@ def diagnose(job: Dict[str, Any]) -> List[str]:
         if len(vs) >= 2 and len(all_machines) > 1 and sum(len(x) for x in machines.values()) == len(vs):
             out.append(f"correlated machine failures: all {len(vs)} failed vertices ran on computer {m} while the other "
                        f"{len(all_machines) - 1} computers had none — suspect that GPU / worker, not the program")
+    died = [p for p in job.get("processes", []) if p.get("exitcode") not in (None, 0)]
+    if died:
+        slots = defaultdict(int)
+        for p in died:
+            slots[p["host"].split(".")[0]] += 1
+        worst = max(slots.items(), key=lambda kv: kv[1])
+        out.append(f"{len(died)} vertex-host process(es) died (exit codes {sorted({p['exitcode'] for p in died})}); the graph manager "
+                   f"restarted them and re-ran their vertices" + (f" — slot {worst[0]} died {worst[1]} times: suspect that worker" if worst[1] >= 2 else ""))
     stages_failed = {a["stage"] for a in failed}
     if len(by_vertex) >= 3 and len(stages_failed) == 1:
         out.append(f"{len(by_vertex)} different vertices of stage {next(iter(stages_failed))} failed: the stage's "
@@ -171,6 +198,14 @@ def render(job: Dict[str, Any]) -> str:
     lines.append("Schedule (attempt order):")
     for a in job["attempts"][:200]:
         lines.append(f"  {a['start'] or '-':<28} v{a['vertex']:<8} ver {a['version']} -> {a['state']}")
+    if job.get("processes"):
+        lines.append("Vertex hosts:")
+        for p in job["processes"]:
+            lines.append(f"  {p['host']:<8} pid {p['pid'] or '-':<8} created {p['created'] or '-':<28} exit {p['exitcode'] if p['exitcode'] is not None else '-'}")
+    if job.get("rewrites"):
+        lines.append("Run-time graph rewrites:")
+        for r in job["rewrites"]:
+            lines.append("  " + " ".join(f"{k}={v}" for k, v in r.items() if k != "ts"))
     lines.append("Diagnosis:")
     lines += ["  - " + d for d in job["diagnosis"]]
     plan = os.path.join(job["dir"], "QueryGraph__0.txt")

@@ -83,6 +83,10 @@ def test_cluster_host_death_and_vertex_retry(tmp_path):
     assert st["host_restarts"] >= 1 and st["counters"]["failures"] >= 2
     log = open(os.path.join(str(tmp_path), "ClusterJobs", "1", "calypso.log")).read()
     assert "exited" in log and "injected vertex failure" in log
+    from dryad_b200.tools.jobreport import build_job, render
+    job = build_job(os.path.join(str(tmp_path), "ClusterJobs", "1"))
+    assert any("vertex-host process" in d for d in job["diagnosis"])
+    assert any(p["exitcode"] == 7 for p in job["processes"]) and "Vertex hosts:" in render(job)
 
 
 def test_cluster_unreadable_channel_reruns_producer(tmp_path):
