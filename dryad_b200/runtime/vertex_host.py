@@ -216,6 +216,9 @@ class VertexHost:
                     tail = d.members[-1] if getattr(d, "members", None) else d
                     tail.params["nports"] = int(n)
                     d.n_out_ports = int(n)
+                for k, n in w.get("pcount", {}).items():
+                    d = self.nodes[int(k)]
+                    (d.members[-1] if getattr(d, "members", None) else d).params["pcount"] = int(n)
         node = self.nodes[uid] if internal is None else None
         self._versions, self._input_index = {}, {}
         for k, (u, _len) in enumerate(cmd.inputs):                     # chan://<uid>/<part>/<version>

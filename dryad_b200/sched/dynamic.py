@@ -51,6 +51,8 @@ class DynamicManagers:
         self.dist: Dict[int, dict] = {}             # distributor stage uid -> state
         self.widths: Dict[int, int] = {}            # stage uid -> partition count decided at run time
         self.nports: Dict[int, int] = {}            # distributor stage uid -> output ports decided at run time
+        self.pcount: Dict[int, int] = {}            # range-sampler stage uid -> number of ranges decided at run time
+        self._hold_by_uid: Dict[int, int] = {}      # stage whose vertices are held -> distributor stage uid
         self._find_candidates()
         self._find_distributors()
 
@@ -126,10 +128,20 @@ class DynamicManagers:
         xp = JobExecutor.edge_is_cross_product
         for node in jm.plan.nodes:
             tail = node.members[-1] if node.type == NodeType.Super else node
-            if tail.type != NodeType.HashPartition or node.dynamic_manager != DynamicManagerType.HashDistributor:
+            is_hash = tail.type == NodeType.HashPartition and node.dynamic_manager == DynamicManagerType.HashDistributor
+            is_range = (tail.type == NodeType.RangePartition and node.dynamic_manager == DynamicManagerType.RangeDistributor
+                        and tail.params.get("range_keys") is None and node.type != NodeType.Super and len(node.children) == 2)
+            if not (is_hash or is_range):
                 continue
             if not node.children or len(node.parents) != 1:
                 continue
+            sampler = None
+            if is_range:
+                # the separators come from a one-vertex stage that must produce (new width - 1) of them: IT is held
+                sampler = node.children[1][0]
+                stail = sampler.members[-1] if sampler.type == NodeType.Super else sampler
+                if stail.type != NodeType.RangeSampler or sampler.partition_count != 1:
+                    continue
             cons = node.parents[0]
             op = next(o for c, o in cons.children if c is node)
             if op != ConnOp.CrossProduct or cons.partition_count != tail.params.get("nports") or len(cons.children) != 1:
@@ -153,13 +165,16 @@ class DynamicManagers:
                     if c not in follow and not xp(n, c, o) and c.partition_count != 1:
                         ok = False                                    # a second same-width input (co-partitioned join)
             if ok:
+                data = [c for c, _ in node.children if c is not sampler]
                 self.dist[node.uid] = {"node": node, "tail": tail, "consumer": cons, "follow": follow, "decided": False,
-                                       "held": []}
+                                       "held": [], "hold_uid": sampler.uid if sampler is not None else node.uid,
+                                       "data": data, "sampler": sampler}
+                self._hold_by_uid[self.dist[node.uid]["hold_uid"]] = node.uid
 
     def hold(self, v: int, version: int) -> bool:
         """A distributor vertex is not dispatched before its stage's output width has been decided."""
         key = self.jm.vkey.get(v)
-        st = self.dist.get(key[0]) if key else None
+        st = self.dist.get(self._hold_by_uid.get(key[0], -1)) if key else None
         if st is None or st["decided"]:
             return False
         st["held"].append((v, version))
@@ -172,7 +187,7 @@ class DynamicManagers:
             if st["decided"]:
                 continue
             node = st["node"]
-            ups = [(c.uid, i) for c, _ in node.children for i in range(c.partition_count)]
+            ups = [(c.uid, i) for c in st["data"] for i in range(c.partition_count)]
             if any(k not in jm.versions for k in ups):
                 continue
             st["decided"] = True
@@ -188,6 +203,10 @@ class DynamicManagers:
                 st["tail"].params["nports"] = new
                 node.n_out_ports = new
                 self.nports[uid] = new
+                if st["sampler"] is not None:
+                    smp = st["sampler"]
+                    (smp.members[-1] if smp.type == NodeType.Super else smp).params["pcount"] = new
+                    self.pcount[smp.uid] = new
                 jm.rebuild_maps()
                 self.spliced["resized"] += n
                 jm.reporter._emit("dynamic", manager="distributor", stage=uid, bytes=total, consumers_before=old,
@@ -310,5 +329,5 @@ class DynamicManagers:
         if sub:
             out.append("subst=" + json.dumps(sub))
         if self.widths or self.nports:
-            out.append("widths=" + json.dumps({"widths": self.widths, "nports": self.nports}))
+            out.append("widths=" + json.dumps({"widths": self.widths, "nports": self.nports, "pcount": self.pcount}))
         return out

@@ -232,3 +232,22 @@ def test_cluster_speculative_duplicate_beats_a_straggler(tmp_path):
     assert st["counters"]["duplicates"] >= 1
     winners = [v for v in st["vertices"] if "Select" in v["stage_name"] and v["part"] == 3 and v["won"]]
     assert winners and winners[0]["version"] >= 1
+
+
+def test_cluster_runtime_range_distributor(tmp_path):
+    """DYN_RANGE_PARTITION: the range count of an OrderBy follows the data volume — the separator
+    vertex computes (new width - 1) separators, the bucketizers get that many ports, the sort stage is
+    resized (DrDynamicRangeDistributor)."""
+    from dryad_b200.channel import store
+    from dryad_b200.plan import static_config as SC
+    ctx = _ctx(tmp_path, n=3, hosts=2, dynamic_opt_level=SC.DYN_BROADCAST | SC.DYN_RANGE_PARTITION, dynamic_data_per_vertex=2500)
+    data = [(i * 7919) % 5000 for i in range(3000)]
+    uri = f"partfile://{tmp_path}/sorted.pt"
+    ctx.submit_and_wait(ctx.from_enumerable(data, 3).order_by(lambda x: x).to_store(uri))
+    st = ctx.last_cluster_status
+    assert st["dynamic"]["resized"] >= 1
+    n = store.stream_info(uri).partition_count
+    assert n > 3
+    parts = store.open_table(uri).partitions
+    assert [x for p in parts for x in p] == sorted(data)          # globally sorted across the NEW partitions
+    assert sum(1 for p in parts if p) >= 3
