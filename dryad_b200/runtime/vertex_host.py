@@ -32,6 +32,7 @@ import traceback
 from typing import Any, Dict, List, Optional, Tuple
 
 CHAN_DIR = "channels"
+DYN_UID_BASE = 1_000_000          # stage ids of vertices created at run time (sched/dynamic.py)
 
 
 def channel_path(job_dir: str, uid: int, part: int, port: int, version: int, kind: str = "chan") -> str:
@@ -236,7 +237,8 @@ class VertexHost:
                 # an internal vertex of a run-time rewrite: fold / copy exactly the channels named in the command
                 from . import vertex_ops
                 subst, self._subst = self._subst, {}
-                payloads = [self.load_input(u, s, int(internal[2])) for (u, s) in self._input_index]
+                # producers of the plan are read at the consumer's port, outputs of other internal vertices at port 0
+                payloads = [self.load_input(u, s, int(internal[2]) if u < DYN_UID_BASE else 0) for (u, s) in self._input_index]
                 self._subst = subst
                 ins = [payloads]
                 if internal[0] == "copy":

@@ -600,6 +600,8 @@ def combiner_of(node):
             return m, m.params["kind"] in _COMMUTATIVE_KINDS
         if m.type == NodeType.Aggregate and m.params.get("stage") == 2:
             return m, False                     # associative, not known to be commutative: contiguous groups only
+        if m.type == NodeType.GroupBy and m.params.get("mode") == "final_acc":
+            return m, True                      # (key, accumulators) pairs in, the same shape out
         return None
     return None
 
@@ -615,6 +617,8 @@ def internal_combine(node, payloads, env) -> List:
     m = found[0]
     src = _cat(payloads)
     p = m.params
+    if m.type == NodeType.GroupBy:
+        return _group_by(m, 0, [[src]], env)[0]
     if m.type == NodeType.Aggregate:
         return [L.aggregate(src, p["fn"].fn)] if src else []
     kind = p["kind"]

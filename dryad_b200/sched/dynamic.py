@@ -20,7 +20,7 @@ from typing import Dict, List, Optional, Tuple
 
 from ..plan.qnodes import DynamicManagerType, NodeType
 
-DYN_UID_BASE = 1_000_000
+from ..runtime.vertex_host import DYN_UID_BASE  # noqa: E402
 
 
 class DynNode:
@@ -62,18 +62,26 @@ class DynamicManagers:
         jm = self.jm
         if not self.fan_in:
             return
+        from ..plan.qnodes import ConnOp
+        agg_tags = (DynamicManagerType.FullAggregator, DynamicManagerType.PartialAggregator)
         for node in jm.plan.nodes:
-            if node.partition_count != 1 or len(node.children) != 1:
+            if len(node.children) != 1:
                 continue
-            child = node.children[0][0]
-            tagged = child.dynamic_manager in (DynamicManagerType.FullAggregator, DynamicManagerType.PartialAggregator)
+            child, op = node.children[0]
+            # a stage's tag is its tail's; the partial aggregate sits before the HashPartition in its super node
+            tagged = child.dynamic_manager in agg_tags or any(m.dynamic_manager in agg_tags for m in (child.members or []))
             if child.partition_count <= self.fan_in or not (tagged or getattr(jm.ctx, "aggregation_tree_all", False)):
                 continue
+            cross = op == ConnOp.CrossProduct
+            if not cross and node.partition_count != 1:
+                continue                                  # N:1 gather, or N:M where consumer j reads port j of every producer
             found = combiner_of(node)
             if found is None:
                 continue
-            v = jm.vid[(node.uid, 0)]
-            self.agg[v] = {"node": node, "commutative": found[1], "done": False, "level": 0}
+            for j in range(node.partition_count):
+                v = jm.vid[(node.uid, j)]
+                self.agg[v] = {"node": node, "part": j, "port": j if cross else 0, "commutative": found[1], "done": False,
+                               "level": 0}
 
     def _dyn_stage(self, kind: str, key_uid: int, name: str, consumer=None, port: int = 0) -> int:
         jm = self.jm
@@ -90,7 +98,7 @@ class DynamicManagers:
         """One internal vertex over `members` (gm vertex ids, inputs of consumer `cv`)."""
         jm = self.jm
         node = state["node"]
-        st = self._dyn_stage("combine", node.uid, f"Agg__{node.name}", node, 0)
+        st = self._dyn_stage("combine", node.uid, f"Agg__{node.name}", node, state["port"])
         dyn = jm.nodes[st]
         x = jm.gm.splice(st, members, [cv])
         xp = jm.gm.vertex(x)["part"]
@@ -109,7 +117,7 @@ class DynamicManagers:
         jm.ex._gm_inputs[x] = list(keys)
         state["grouped"] = state.get("grouped", set()) | set(members)
         self.spliced["aggregate"] += 1
-        jm.reporter._emit("dynamic", manager="aggregate", consumer=f"{node.uid}.0", vertex=f"{dyn.uid}.{xp}",
+        jm.reporter._emit("dynamic", manager="aggregate", consumer=f"{node.uid}.{state['part']}", vertex=f"{dyn.uid}.{xp}",
                           inputs=" ".join(f"{a}.{b}" for a, b in keys), level=state["level"])
 
     def on_completed(self, v: int, host: int) -> None:

@@ -251,3 +251,19 @@ def test_cluster_runtime_range_distributor(tmp_path):
     parts = store.open_table(uri).partitions
     assert [x for p in parts for x in p] == sorted(data)          # globally sorted across the NEW partitions
     assert sum(1 for p in parts if p) >= 3
+
+
+def test_cluster_aggregation_tree_for_decomposed_group_by(tmp_path):
+    """GroupBy with decomposable aggregates: consumer j of the hash edge gets internal vertices that
+    fold port j of a group of producers with the GroupBy's own combiner (GroupByDynamicReduce)."""
+    from dryad_b200.plan import static_config as SC
+    ctx = _ctx(tmp_path, n=8, hosts=2, dynamic_opt_level=SC.DYN_BROADCAST | SC.DYN_AGGREGATE, aggregation_tree_fan_in=3)
+    ctx.num_partitions = 2
+    q = ctx.from_enumerable(range(2000), 8).hash_partition(lambda x: x, 8) \
+           .group_by(lambda x: x % 13).select(lambda g: (g.key, g.count(), g.sum()))
+    out = sorted(q)
+    assert out == sorted((k, len(range(k, 2000, 13)), sum(range(k, 2000, 13))) for k in range(13))
+    st = ctx.last_cluster_status
+    assert st["dynamic"]["aggregate"] >= 2
+    internal = [v for v in st["vertices"] if v["stage_name"].startswith("Agg__")]
+    assert internal and all("GroupBy" in v["stage_name"] for v in internal)
