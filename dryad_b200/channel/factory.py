@@ -32,7 +32,8 @@ def fifo_uri(vertex_id: int, port: int, version: int, blocking: bool = True) -> 
 
 
 class ChannelWriter:
-    def __init__(self, uri: str):
+    def __init__(self, uri: str, compression=None):
+        """`compression`: gzip the blocks of a file channel (the intermediate-data compression setting)."""
         self.uri = uri
         self.scheme, _, rest = uri.partition("://")
         self.records = 0
@@ -40,7 +41,8 @@ class ChannelWriter:
         self._buf: List[bytes] = []
         self._w = None
         if self.scheme == "file":
-            self._w = N.host().dh_writer_open(("/" + rest.lstrip("/")).encode(), 0, 0)
+            comp = compression if isinstance(compression, int) else (1 if str(compression or "None").lower() in ("gzip", "1", "true") else 0)
+            self._w = N.host().dh_writer_open(("/" + rest.lstrip("/")).encode(), comp, 0)
             if not self._w:
                 raise OSError(f"cannot create {uri}")
         elif self.scheme == "fifo":
@@ -74,7 +76,13 @@ class ChannelWriter:
 
     def close(self) -> None:
         if self.scheme == "file":
-            N.host().dh_writer_close(self._w, None, None, None)
+            if self._w:
+                stored = C.c_int64()
+                rc = N.host().dh_writer_close(self._w, None, C.byref(stored), None)
+                self._w = None
+                self.stored_bytes = stored.value
+                if rc:
+                    raise OSError(f"closing {self.uri} failed ({rc})")
         elif self.scheme == "fifo":
             self._flush_fifo()
             self._fifo.close_writer()
@@ -143,8 +151,8 @@ class VertexWriter:
     distributors write each record to the port its partition function picked (`WriteItem(item, port)`),
     Fork hands one record writer per branch (`GetRecordWriter(port)`)."""
 
-    def __init__(self, uris: List[str]):
-        self.ports = [ChannelWriter(u) for u in uris]
+    def __init__(self, uris: List[str], compression=None):
+        self.ports = [ChannelWriter(u, compression) for u in uris]
 
     def write_item(self, item, port: int) -> None:
         self.ports[port].write(item)

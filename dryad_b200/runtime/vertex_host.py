@@ -40,38 +40,51 @@ def channel_path(job_dir: str, uid: int, part: int, port: int, version: int, kin
     return os.path.join(job_dir, CHAN_DIR, f"{uid}_{part}_{port}.v{version}.{kind}")
 
 
-def write_channel(job_dir: str, uid: int, part: int, port: int, version: int, payload, compression) -> Tuple[str, int, int]:
-    """-> (path, stored bytes, records).  Records that the wire format carries go out as a block
-    stream (optionally gzip, the intermediate-data compression setting); anything else is pickled."""
+def write_ports(job_dir: str, uid: int, part: int, version: int, ports, compression) -> List[Tuple[str, int, int]]:
+    """Write every output port of a vertex through ONE multi-port writer (channel/factory.VertexWriter,
+    the reference's DryadLinqVertexWriter): per port (path, stored bytes, records).  Records that the wire
+    format carries go out as block streams (optionally gzip, the intermediate-data compression setting);
+    a port whose records it cannot carry, or that holds raw text, is pickled instead.  Files appear under
+    their final names only when complete (write to *.tmp, rename)."""
     from ..api.errors import DryadLinqException
-    from ..channel import store
+    from ..channel.factory import VertexWriter
     os.makedirs(os.path.join(job_dir, CHAN_DIR), exist_ok=True)
-    raw = hasattr(payload, "data") and hasattr(payload, "to_records")        # raw text partition: keep the bytes
-    if not raw:
-        recs = payload.to_records() if hasattr(payload, "to_records") else payload
-        final = channel_path(job_dir, uid, part, port, version, "chan")
-        tmp = final + ".tmp"
+    finals = [channel_path(job_dir, uid, part, k, version, "chan") for k in range(len(ports))]
+    w = VertexWriter([f"file://{f}.tmp" for f in finals], compression)
+    out: List[Tuple[str, int, int]] = []
+    pickled: Dict[int, Any] = {}
+    for k, payload in enumerate(ports):
+        raw = hasattr(payload, "data") and hasattr(payload, "to_records")     # raw text partition: keep the bytes
+        if raw:
+            pickled[k] = payload
+            continue
         try:
-            size = store.write_records_file(tmp, recs, compression)
-            # tuples and lists both decode as written, but user classes without a serializer do not
-            os.replace(tmp, final)
-            return final, size, _count(recs)
+            w.write_item_sequence(payload.to_records() if hasattr(payload, "to_records") else payload, k)
         except DryadLinqException:
-            pass                                  # TypeNotSerializable: fall through to pickle
-    final = channel_path(job_dir, uid, part, port, version, "pkl")
-    tmp = final + ".tmp"
-    with open(tmp, "wb") as f:
-        pickle.dump(payload, f, protocol=pickle.HIGHEST_PROTOCOL)
-    os.replace(tmp, final)
-    return final, os.path.getsize(final), _count(payload)
+            pickled[k] = payload                  # TypeNotSerializable: user classes without a serializer
+    w.close()
+    for k, payload in enumerate(ports):
+        tmp = finals[k] + ".tmp"
+        if k in pickled:
+            os.remove(tmp)
+            final = channel_path(job_dir, uid, part, k, version, "pkl")
+            import cloudpickle                    # classes defined inside a function travel by value
+            with open(final + ".tmp", "wb") as f:
+                cloudpickle.dump(payload, f, protocol=pickle.HIGHEST_PROTOCOL)
+            os.replace(final + ".tmp", final)
+            out.append((final, os.path.getsize(final), _count(payload)))
+        else:
+            os.replace(tmp, finals[k])
+            out.append((finals[k], getattr(w.ports[k], "stored_bytes", 0), w.ports[k].records))
+    return out
 
 
 def read_channel(job_dir: str, uid: int, part: int, port: int, version: int):
     """-> (payload, stored bytes); FileNotFoundError / a decode error mean the channel is unreadable."""
-    from ..channel import store
+    from ..channel.factory import ChannelReader
     p = channel_path(job_dir, uid, part, port, version, "chan")
     if os.path.exists(p):
-        return store.read_partition_file(p), os.path.getsize(p)
+        return list(ChannelReader(f"file://{p}")), os.path.getsize(p)
     p = channel_path(job_dir, uid, part, port, version, "pkl")
     with open(p, "rb") as f:
         return pickle.load(f), os.path.getsize(p)
@@ -252,9 +265,8 @@ class VertexHost:
                 ports = self.backend.run_vertex(node, part, ins, env)
             n_in = sum(self.backend.count(p) for inp in ins for p in inp)
             n_out = 0
-            for k, payload in enumerate(ports):
-                path, size, nrec = write_channel(self.job_dir, uid, part, k, version, payload, self.compression)
-                self._cache_put(f"{uid}_{part}_{k}.v{version}", payload)
+            for k, (path, size, nrec) in enumerate(write_ports(self.job_dir, uid, part, version, ports, self.compression)):
+                self._cache_put(f"{uid}_{part}_{k}.v{version}", ports[k])
                 outputs.append((path, size))
                 n_out += nrec
             root = self.roots.get(uid)

@@ -267,3 +267,24 @@ def test_cluster_aggregation_tree_for_decomposed_group_by(tmp_path):
     assert st["dynamic"]["aggregate"] >= 2
     internal = [v for v in st["vertices"] if v["stage_name"].startswith("Agg__")]
     assert internal and all("GroupBy" in v["stage_name"] for v in internal)
+
+
+def test_cluster_channels_gzip_and_custom_records(tmp_path):
+    """Intermediate channels honour the compression setting; records the wire format cannot carry
+    (a user class without a registered serializer) still travel between vertex hosts."""
+    class P:                                               # local class: pickled by value with the job
+        def __init__(self, k, v):
+            self.k, self.v = k, v
+
+    ctx = _ctx(tmp_path, n=3, hosts=2, intermediate_data_compression_scheme="Gzip")
+    q = ctx.from_enumerable(range(3000), 3).select(lambda x: (x % 10, "v" * 40)).hash_partition(lambda t: t[0], 3) \
+           .select(lambda t: t[0])
+    assert sorted(q) == sorted(x % 10 for x in range(3000))
+    chans = os.path.join(str(tmp_path), "ClusterJobs", "1", "channels")
+    sizes = [os.path.getsize(os.path.join(chans, f)) for f in os.listdir(chans) if f.endswith(".chan")]
+    assert sizes and max(sizes) < 3000 * 20                # 44-byte records, highly repetitive: gzip shrinks them
+    q2 = ctx.from_enumerable(range(60), 3).select(lambda x: P(x % 4, x)).hash_partition(lambda p: p.k, 2) \
+            .select(lambda p: (p.k, p.v))
+    assert sorted(q2) == sorted((x % 4, x) for x in range(60))
+    chans2 = os.path.join(str(tmp_path), "ClusterJobs", "2", "channels")
+    assert any(f.endswith(".pkl") for f in os.listdir(chans2))
