@@ -32,9 +32,11 @@ def fifo_uri(vertex_id: int, port: int, version: int, blocking: bool = True) -> 
 
 
 class ChannelWriter:
-    def __init__(self, uri: str, compression=None):
-        """`compression`: gzip the blocks of a file channel (the intermediate-data compression setting)."""
+    def __init__(self, uri: str, compression=None, timeout: float = 60.0):
+        """`compression`: gzip the blocks of a file channel (the intermediate-data compression setting);
+        `timeout`: how long a FIFO writer waits for the reader to make room."""
         self.uri = uri
+        self.timeout = timeout
         self.scheme, _, rest = uri.partition("://")
         self.records = 0
         self.bytes = 0
@@ -71,7 +73,7 @@ class ChannelWriter:
 
     def _flush_fifo(self):
         if self._buf:
-            self._fifo.write(b"".join(self._buf), timeout=60.0)
+            self._fifo.write(b"".join(self._buf), timeout=self.timeout)
             self._buf = []
 
     def close(self) -> None:
@@ -92,8 +94,9 @@ class ChannelWriter:
 
 
 class ChannelReader:
-    def __init__(self, uri: str):
+    def __init__(self, uri: str, timeout: float = 60.0):
         self.uri = uri
+        self.timeout = timeout
         self.scheme, _, rest = uri.partition("://")
         self._rest = rest
 
@@ -106,7 +109,7 @@ class ChannelReader:
             with _lock:
                 f = _fifos.setdefault(name, Fifo(32))
             while True:
-                blk = f.read(timeout=60.0)
+                blk = f.read(timeout=self.timeout)
                 if blk is None:
                     break
                 buf = memoryview(blk)
@@ -172,6 +175,24 @@ class VertexWriter:
     def close(self) -> None:
         for w in self.ports:
             w.close()
+
+
+def drop_fifo(name: str, abort: bool = False) -> None:
+    """Forget a named FIFO once both ends are done with it (or abort it: both ends fail fast)."""
+    with _lock:
+        f = _fifos.pop(name, None)
+    if f is not None:
+        if abort:
+            f.abort()
+        else:
+            f.close()
+
+
+def abort_fifo(name: str) -> None:
+    with _lock:
+        f = _fifos.get(name)
+    if f is not None:
+        f.abort()
 
 
 def port_order(nports: int, keep_port_order: bool, seed: int) -> List[int]:

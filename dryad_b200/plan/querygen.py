@@ -625,7 +625,7 @@ class QueryGen:
         producer and consumer into one start clique of the graph manager."""
         from . import static_config
         from .qnodes import ChannelType
-        if not static_config.USE_MEMORY_FIFO:
+        if not getattr(self.context, "use_memory_fifo", static_config.USE_MEMORY_FIFO):
             return
         multi = (NodeType.Join, NodeType.GroupJoin, NodeType.SetOperation, NodeType.Apply)
         for n in self._all_nodes():

@@ -108,19 +108,19 @@ class _NoReport:
 
 
 class _LazyPorts:
-    def __init__(self, host, uid, part):
-        self.host, self.uid, self.part = host, uid, part
+    def __init__(self, run, uid, part):
+        self.run, self.uid, self.part = run, uid, part
 
     def __getitem__(self, port):
-        return self.host.load_input(self.uid, self.part, port)
+        return self.run.load_input(self.uid, self.part, port)
 
 
 class _LazyStage:
     """Stands where the in-process executor keeps `out[stage uid]`: a list of partitions, each a list
     of ports — here every access opens the channel on demand."""
 
-    def __init__(self, host, uid, nparts):
-        self.host, self.uid, self.nparts = host, uid, nparts
+    def __init__(self, run, uid, nparts):
+        self.run, self.uid, self.nparts = run, uid, nparts
 
     def __len__(self):
         return self.nparts
@@ -130,10 +130,71 @@ class _LazyStage:
             part += self.nparts
         if not 0 <= part < self.nparts:
             raise IndexError(part)
-        return _LazyPorts(self.host, self.uid, part)
+        return _LazyPorts(self.run, self.uid, part)
 
     def __iter__(self):
         return (self[i] for i in range(self.nparts))
+
+
+class _Run:
+    """ONE vertex attempt: which channel versions it reads, what a run-time rewrite substituted, which
+    inputs and outputs are in-process FIFOs (members of a sub-graph vertex run concurrently, so nothing
+    of this may live on the host object)."""
+
+    def __init__(self, host, member: dict, subst: Dict[str, Optional[str]], internal=None):
+        self.host = host
+        self.uid, self.part = int(member["uid"]), int(member["part"])
+        self.gmv, self.version = int(member["gmv"]), int(member["version"])
+        self.subst = subst
+        self.internal = internal
+        self.versions: Dict[Tuple[int, int], int] = {}
+        self.input_index: Dict[Tuple[int, int], int] = {}
+        for k, (u, sp, ver) in enumerate(member["inputs"]):
+            self.versions[(int(u), int(sp))] = int(ver)
+            self.input_index[(int(u), int(sp))] = k
+        self.input_bytes = [0] * len(member["inputs"])
+        self.cache_hits = 0
+        self.fifo_in: Dict[Tuple[int, int], str] = {}        # (producer uid, part) -> fifo name
+        self.fifo_out: List[str] = []
+        self._fifo_payload: Dict[Tuple[int, int], Any] = {}
+
+    def load_input(self, uid: int, part: int, port: int):
+        from .executor import InputReadError
+        host = self.host
+        hops = 0
+        while f"{uid}/{part}" in self.subst and hops < 64:         # run-time rewrites: follow the splice chain
+            t = self.subst[f"{uid}/{part}"]
+            if t is None:
+                return []                                          # folded into an internal vertex's output
+            uid, part, port = int(t.split("/")[0]), int(t.split("/")[1]), 0
+            hops += 1
+        name = self.fifo_in.get((uid, part))
+        if name is not None:
+            if (uid, part) not in self._fifo_payload:
+                self._fifo_payload[(uid, part)] = host.read_fifo(name, uid, part)
+            return self._fifo_payload[(uid, part)]
+        ver = self.versions.get((uid, part))
+        if ver is None:
+            raise InputReadError(uid, part, f"stage {uid}[{part}] is not an input of this vertex")
+        key = f"{uid}_{part}_{port}.v{ver}"
+        idx = self.input_index.get((uid, part), -1)
+        n = host._cached.get(key)
+        if n is not None:
+            import ctypes as C
+            buf = C.create_string_buffer(n)
+            got = host._hostlib.cache_get(host._cache, key.encode(), buf, n)
+            if got == n:
+                self.cache_hits += 1
+                if idx >= 0:
+                    self.input_bytes[idx] += n
+                return pickle.loads(buf.raw)
+        try:
+            payload, size = read_channel(host.job_dir, uid, part, port, ver)
+        except Exception as ex:  # noqa: BLE001  (missing, truncated or corrupt: all "cannot read")
+            raise InputReadError(uid, part, f"cannot read channel {key}: {type(ex).__name__}: {ex}") from ex
+        if idx >= 0:
+            self.input_bytes[idx] += size
+        return payload
 
 
 class VertexHost:
@@ -149,11 +210,7 @@ class VertexHost:
         self.backend = self.ex.backend
         self.roots = {r.uid: r for r in self.plan.roots}
         self.compression = self.ctx.intermediate_data_compression_scheme
-        self._versions: Dict[Tuple[int, int], int] = {}
-        self._subst: Dict[str, Optional[str]] = {}
-        self._input_index: Dict[Tuple[int, int], int] = {}
-        self._input_bytes: List[int] = []
-        self._cache_hits = 0
+        self._handoff: Dict[str, Any] = {}
         # channel cache with spill: outputs of vertices that ran HERE are served from memory
         from .. import _native as N
         self._hostlib = N.host()
@@ -163,112 +220,102 @@ class VertexHost:
         os.makedirs(spill, exist_ok=True)
         self._cache = self._hostlib.cache_create(spill.encode(), low, high)
         self._cached: Dict[str, int] = {}
+        import threading
+        self._cache_lock = threading.Lock()
 
     # ---- channels -------------------------------------------------------------------------------
-    def load_input(self, uid: int, part: int, port: int):
-        from .executor import InputReadError
-        hops = 0
-        while f"{uid}/{part}" in self._subst and hops < 64:       # run-time rewrites: follow the splice chain
-            t = self._subst[f"{uid}/{part}"]
-            if t is None:
-                return []                                          # folded into an internal vertex's output
-            uid, part, port = int(t.split("/")[0]), int(t.split("/")[1]), 0
-            hops += 1
-        ver = self._versions.get((uid, part))
-        if ver is None:
-            raise InputReadError(uid, part, f"stage {uid}[{part}] is not an input of this vertex")
-        key = f"{uid}_{part}_{port}.v{ver}"
-        idx = self._input_index.get((uid, part), -1)
-        n = self._cached.get(key)
-        if n is not None:
-            import ctypes as C
-            buf = C.create_string_buffer(n)
-            got = self._hostlib.cache_get(self._cache, key.encode(), buf, n)
-            if got == n:
-                self._cache_hits += 1
-                if idx >= 0:
-                    self._input_bytes[idx] += n
-                return pickle.loads(buf.raw)
-        try:
-            payload, size = read_channel(self.job_dir, uid, part, port, ver)
-        except Exception as ex:  # noqa: BLE001  (missing, truncated or corrupt: all "cannot read")
-            raise InputReadError(uid, part, f"cannot read channel {key}: {type(ex).__name__}: {ex}") from ex
-        if idx >= 0:
-            self._input_bytes[idx] += size
-        return payload
-
     def _cache_put(self, key: str, payload) -> None:
         try:
             b = pickle.dumps(payload, protocol=pickle.HIGHEST_PROTOCOL)
         except Exception:  # noqa: BLE001
             return
-        if len(b) <= (32 << 20) and self._hostlib.cache_put(self._cache, key.encode(), b, len(b)) == 0:
-            self._cached[key] = len(b)
+        with self._cache_lock:
+            if len(b) <= (32 << 20) and self._hostlib.cache_put(self._cache, key.encode(), b, len(b)) == 0:
+                self._cached[key] = len(b)
+
+    def write_fifo(self, name: str, payload) -> None:
+        """Stream one output to a member of the same sub-graph vertex through a bounded in-process FIFO
+        (fifo://32/..., channelfifo.cpp: the writer blocks while 32 blocks are outstanding)."""
+        from ..api.errors import DryadLinqException
+        from ..channel.factory import ChannelWriter
+        w = ChannelWriter(f"fifo://32/{name}", timeout=3600.0)
+        try:
+            for rec in (payload.to_records() if hasattr(payload, "to_records") else payload):
+                w.write(rec)
+        except DryadLinqException:
+            self._handoff[name] = payload          # records the wire format cannot carry: handed over as objects
+        finally:
+            w.close()
+
+    def read_fifo(self, name: str, uid: int, part: int):
+        from ..channel.factory import ChannelReader
+        from .executor import InputReadError
+        try:
+            got = list(ChannelReader(f"fifo://32/{name}", timeout=3600.0))
+        except (BrokenPipeError, TimeoutError) as ex:
+            raise InputReadError(uid, part, f"aborted: the producer of FIFO {name} failed ({type(ex).__name__})") from ex
+        return self._handoff.pop(name, got)
+
+    def _apply_widths(self, w: dict) -> None:
+        """Widths decided at run time by the dynamic distributor."""
+        for k, n in w.get("widths", {}).items():
+            self.nodes[int(k)].partition_count = int(n)
+        for k, n in w.get("nports", {}).items():
+            d = self.nodes[int(k)]
+            tail = d.members[-1] if getattr(d, "members", None) else d
+            tail.params["nports"] = int(n)
+            d.n_out_ports = int(n)
+        for k, n in w.get("pcount", {}).items():
+            d = self.nodes[int(k)]
+            (d.members[-1] if getattr(d, "members", None) else d).params["pcount"] = int(n)
 
     # ---- one vertex -----------------------------------------------------------------------------
-    def run_vertex(self, cmd):
+    def run_member(self, run: _Run) -> dict:
+        """Run one vertex attempt; returns its result record (what the status block carries)."""
+        import copy
         from ..channel import store
-        from .command import CMD_START, STATE_COMPLETED, STATE_FAILED, VertexCommand
+        from ..channel.factory import abort_fifo
         from .executor import InputReadError
         from .vertex_ops import VertexEnv
-        uid, version = cmd.vertex_id, cmd.version
-        part, gmv = int(cmd.args[1]), int(cmd.args[2])
-        extra = cmd.args[3:]
-        internal = extra[1:4] if extra and extra[0] == "internal" else None     # [kind, consumer uid, port]
-        self._subst = {}
-        for a in extra:
-            if a.startswith("subst="):
-                import json
-                self._subst = json.loads(a[6:])
-            elif a.startswith("widths="):
-                import json
-                w = json.loads(a[7:])                   # widths decided at run time by the dynamic distributor
-                for k, n in w.get("widths", {}).items():
-                    self.nodes[int(k)].partition_count = int(n)
-                for k, n in w.get("nports", {}).items():
-                    d = self.nodes[int(k)]
-                    tail = d.members[-1] if getattr(d, "members", None) else d
-                    tail.params["nports"] = int(n)
-                    d.n_out_ports = int(n)
-                for k, n in w.get("pcount", {}).items():
-                    d = self.nodes[int(k)]
-                    (d.members[-1] if getattr(d, "members", None) else d).params["pcount"] = int(n)
-        node = self.nodes[uid] if internal is None else None
-        self._versions, self._input_index = {}, {}
-        for k, (u, _len) in enumerate(cmd.inputs):                     # chan://<uid>/<part>/<version>
-            a = u.split("://", 1)[1].split("/")
-            self._versions[(int(a[0]), int(a[1]))] = int(a[2])
-            self._input_index[(int(a[0]), int(a[1]))] = k
-        self._input_bytes = [0] * len(cmd.inputs)
-        self._cache_hits = 0
-        self.ex.out = {n.uid: _LazyStage(self, n.uid, n.partition_count) for n in self.plan.nodes}
+        uid, part, version = run.uid, run.part, run.version
+        internal = run.internal
+        res = {"uid": uid, "part": part, "gmv": run.gmv, "version": version, "ok": False, "n_in": 0, "n_out": 0,
+               "seconds": 0.0, "hits": 0, "bytes_in": [], "bad": -1, "message": "", "out_bytes": 0, "out_sizes": [],
+               "part_file": None, "deterministic": False}
+        ex = copy.copy(self.ex)                                    # its `out` is this attempt's view of the channels
+        ex.out = {n.uid: _LazyStage(run, n.uid, n.partition_count) for n in self.plan.nodes}
         t0 = time.perf_counter()
-        outputs: List[Tuple[str, int]] = []
         try:
             env = VertexEnv(self.ctx, uid, part, version)
             if internal is not None:
                 # an internal vertex of a run-time rewrite: fold / copy exactly the channels named in the command
                 from . import vertex_ops
-                subst, self._subst = self._subst, {}
+                subst, run.subst = run.subst, {}
                 # producers of the plan are read at the consumer's port, outputs of other internal vertices at port 0
-                payloads = [self.load_input(u, s, int(internal[2]) if u < DYN_UID_BASE else 0) for (u, s) in self._input_index]
-                self._subst = subst
+                payloads = [run.load_input(u, sp, int(internal[2]) if u < DYN_UID_BASE else 0) for (u, sp) in run.input_index]
+                run.subst = subst
                 ins = [payloads]
                 if internal[0] == "copy":
                     ports = [payloads[0]]
                 else:
                     ports = [vertex_ops.internal_combine(self.nodes[int(internal[1])], [self.backend.to_records(p) for p in payloads], env)]
             else:
-                ins = self.ex._inputs(node, part)
+                node = self.nodes[uid]
+                ins = ex._inputs(node, part)
                 if self.ctx.fault_injector is not None:
                     self.ctx.fault_injector(node, part, version)
                 ports = self.backend.run_vertex(node, part, ins, env)
-            n_in = sum(self.backend.count(p) for inp in ins for p in inp)
-            n_out = 0
-            for k, (path, size, nrec) in enumerate(write_ports(self.job_dir, uid, part, version, ports, self.compression)):
-                self._cache_put(f"{uid}_{part}_{k}.v{version}", ports[k])
-                outputs.append((path, size))
-                n_out += nrec
+            res["n_in"] = sum(self.backend.count(p) for inp in ins for p in inp)
+            for name in run.fifo_out:                              # streamed edges first: the consumer is waiting
+                self.write_fifo(name, ports[0])
+            if run.fifo_out and not self._needs_file(uid):
+                res["n_out"] = sum(_count(p) for p in ports)
+            else:
+                for k, (path, size, nrec) in enumerate(write_ports(self.job_dir, uid, part, version, ports, self.compression)):
+                    self._cache_put(f"{uid}_{part}_{k}.v{version}", ports[k])
+                    res["out_sizes"].append(size)
+                    res["out_bytes"] += size
+                    res["n_out"] += nrec
             root = self.roots.get(uid)
             if root is not None:
                 onode = root if root.type.value == "OutputTable" else root.members[-1]
@@ -278,24 +325,95 @@ class VertexHost:
                                                         or self.ctx.output_data_compression_scheme)
                     tmp_v = f"{final}.v{version}.tmp"
                     os.replace(tmp, tmp_v)
-                    outputs.append((f"{tmp_v}|{final}", size))
-            dt = time.perf_counter() - t0
-            return VertexCommand(CMD_START, uid, version, state=STATE_COMPLETED, outputs=outputs,
-                                 args=[str(part), str(gmv), str(n_in), str(n_out), f"{dt:.6f}", str(self._cache_hits)],
-                                 channel_status=[(b, 0) for b in self._input_bytes])
-        except BaseException as ex:  # noqa: BLE001  (vertex code is user code; SystemExit must pass)
-            if isinstance(ex, (SystemExit, KeyboardInterrupt)):
+                    res["part_file"] = [tmp_v, final, size]
+            res["ok"] = True
+        except BaseException as ex_:  # noqa: BLE001  (vertex code is user code; SystemExit must pass)
+            if isinstance(ex_, (SystemExit, KeyboardInterrupt)):
                 raise
-            text = "".join(traceback.format_exception_only(type(ex), ex)).strip()
-            chans = [(b, 0) for b in self._input_bytes]
-            if isinstance(ex, InputReadError):
-                k = self._input_index.get((ex.producer_uid, ex.producer_part), -1)
-                if k >= 0:
-                    chans[k] = (chans[k][0], 1)
-            deterministic = getattr(ex, "code", None) is not None and not getattr(ex, "transient", False)
-            return VertexCommand(CMD_START, uid, version, state=STATE_FAILED, exit_code=2 if deterministic else 1,
-                                 message=text[:4000], channel_status=chans,
-                                 args=[str(part), str(gmv), "0", "0", f"{time.perf_counter() - t0:.6f}", "0"])
+            for name in run.fifo_out:
+                abort_fifo(name)                                   # the consumers of the streamed edges fail fast
+            res["message"] = "".join(traceback.format_exception_only(type(ex_), ex_)).strip()[:3000]
+            if isinstance(ex_, InputReadError):
+                res["bad"] = run.input_index.get((ex_.producer_uid, ex_.producer_part), -1)
+            res["deterministic"] = getattr(ex_, "code", None) is not None and not getattr(ex_, "transient", False)
+        res["seconds"] = time.perf_counter() - t0
+        res["hits"] = run.cache_hits
+        res["bytes_in"] = list(run.input_bytes)
+        return res
+
+    def _is_fifo_edge(self, child, parent) -> bool:
+        from ..plan.qnodes import ConnOp
+        op = next((o for c, o in parent.children if c is child), None)
+        return (getattr(child.channel_type, "value", "") == "MemoryFIFO" and op is not None
+                and not self.ex.edge_is_cross_product(parent, child, op) and child.partition_count == parent.partition_count)
+
+    def _needs_file(self, uid: int) -> bool:
+        """False when every consumer of the stage reads it through a FIFO (a streamed edge keeps nothing)."""
+        node = self.nodes[uid]
+        return uid in self.roots or not node.parents or any(not self._is_fifo_edge(node, p) for p in node.parents)
+
+    def run_command(self, cmd):
+        """-> status block.  A plain START runs one vertex; a `subgraph` START runs the members of a start
+        clique concurrently, wired by in-process FIFOs (DryadSubGraphVertex, subgraphvertex.cpp)."""
+        import json
+        from .command import CMD_START, STATE_COMPLETED, STATE_FAILED, VertexCommand
+        extra = cmd.args[3:]
+        subst: Dict[str, Optional[str]] = {}
+        for a in extra:
+            if a.startswith("subst="):
+                subst = json.loads(a[6:])
+            elif a.startswith("widths="):
+                self._apply_widths(json.loads(a[7:]))
+        if extra and extra[0] == "subgraph":
+            results = self.run_subgraph(json.loads(extra[1]), subst)
+            ok = all(r["ok"] for r in results)
+            slim = [{k: r[k] for k in ("uid", "part", "gmv", "version", "ok", "n_in", "n_out", "seconds", "hits", "bad",
+                                        "out_bytes", "part_file", "deterministic")} | {"message": r["message"][:600]}
+                    for r in results]
+            return VertexCommand(CMD_START, cmd.vertex_id, cmd.version, state=STATE_COMPLETED if ok else STATE_FAILED,
+                                 args=["subgraph", json.dumps(slim)])
+        internal = extra[1:4] if extra and extra[0] == "internal" else None     # [kind, consumer uid, port]
+        member = {"uid": cmd.vertex_id, "part": int(cmd.args[1]), "gmv": int(cmd.args[2]), "version": cmd.version,
+                  "inputs": [u.split("://", 1)[1].split("/") for u, _len in cmd.inputs]}     # chan://<uid>/<part>/<version>
+        r = self.run_member(_Run(self, member, subst, internal))
+        outputs = [(f"port{k}", sz) for k, sz in enumerate(r["out_sizes"])]
+        if r["part_file"]:
+            outputs.append((f"{r['part_file'][0]}|{r['part_file'][1]}", r["part_file"][2]))
+        chans = [(b, 1 if k == r["bad"] else 0) for k, b in enumerate(r["bytes_in"])]
+        return VertexCommand(CMD_START, r["uid"], r["version"], state=STATE_COMPLETED if r["ok"] else STATE_FAILED,
+                             exit_code=0 if r["ok"] else (2 if r["deterministic"] else 1), message=r["message"],
+                             outputs=outputs, channel_status=chans,
+                             args=[str(r["part"]), str(r["gmv"]), str(r["n_in"]), str(r["n_out"]), f"{r['seconds']:.6f}", str(r["hits"])])
+
+    def run_subgraph(self, members: List[dict], subst) -> List[dict]:
+        import threading
+        from ..channel.factory import drop_fifo
+        runs = [_Run(self, m, subst) for m in members]
+        here = {(r.uid, r.part): r for r in runs}
+        names: List[str] = []
+        for r in runs:
+            node = self.nodes[r.uid]
+            for child, _op in node.children:
+                p = here.get((child.uid, r.part))
+                if p is not None and self._is_fifo_edge(child, node):
+                    name = f"{child.uid}_{r.part}_to_{r.uid}_v{r.version}"
+                    r.fifo_in[(child.uid, r.part)] = name
+                    p.fifo_out.append(name)
+                    names.append(name)
+        results: List[Optional[dict]] = [None] * len(runs)
+
+        def work(i):
+            results[i] = self.run_member(runs[i])
+
+        threads = [threading.Thread(target=work, args=(i,), name=f"member-{r.uid}.{r.part}") for i, r in enumerate(runs)]
+        for t in threads:
+            t.start()
+        for t in threads:
+            t.join()
+        for n in names:
+            drop_fifo(n)
+            self._handoff.pop(n, None)
+        return [r for r in results if r is not None]
 
     # ---- command loop ---------------------------------------------------------------------------
     def serve(self, idle_timeout: float = 300.0) -> int:
@@ -323,7 +441,7 @@ class VertexHost:
                 continue
             if cmd.command == CMD_TERMINATE:
                 return 0
-            st = self.run_vertex(cmd)
+            st = self.run_command(cmd)
             try:
                 got = self.client.set(self.id, "status", "completed" if st.state == STATE_COMPLETED else "failed",
                                       st.serialize(), wait="cmd", seen=seen, wait_timeout=2.0)

@@ -100,7 +100,11 @@ class DynamicManagers:
         node = state["node"]
         st = self._dyn_stage("combine", node.uid, f"Agg__{node.name}", node, state["port"])
         dyn = jm.nodes[st]
-        x = jm.gm.splice(st, members, [cv])
+        try:
+            x = jm.gm.splice(st, members, [cv])
+        except ValueError:
+            state["done"] = True                     # the consumer belongs to a start clique or has started: leave it alone
+            return
         xp = jm.gm.vertex(x)["part"]
         dyn.partition_count = xp + 1
         jm.vid[(dyn.uid, xp)] = x
@@ -221,7 +225,7 @@ class DynamicManagers:
                                   consumers=new, stages_resized=n)
             held, st["held"] = st["held"], []
             for v, version in held:
-                jm.enqueue(v, version)
+                jm.enqueue([(v, version)])
 
     def _aggregate(self, v: int, host: int) -> None:
         jm = self.jm
@@ -311,7 +315,10 @@ class DynamicManagers:
                 mine = [c for c, which in zip(cons, copy_of) if which == cpy]
                 if not mine:
                     continue
-                x = jm.gm.splice(st, [v], mine)
+                try:
+                    x = jm.gm.splice(st, [v], mine)
+                except ValueError:
+                    continue                         # a consumer in a start clique: it keeps reading the producer directly
                 xp = jm.gm.vertex(x)["part"]
                 dyn.partition_count = xp + 1
                 jm.vid[(dyn.uid, xp)] = x

@@ -46,7 +46,7 @@ class _Host:
         self.name = ""
         self.proc: Optional[subprocess.Popen] = None
         self.ready = False
-        self.busy: Optional[Tuple[int, int, float]] = None      # (gm vertex, version, start time)
+        self.busy: Optional[Tuple[List[Tuple[int, int]], float]] = None      # ([(gm vertex, version), ...], start time)
         self.restarts = 0
         self.vertices_run = 0
 
@@ -190,28 +190,55 @@ class JobManager:
         return self.nodes[info["stage"]], info["part"]
 
     def _on_status(self, h: _Host, data: bytes) -> None:
+        import json
         from ..runtime.command import STATE_COMPLETED, VertexCommand
         st = VertexCommand.parse(data)
         if st is None or h.busy is None:
             return
-        v, version, t_start = h.busy
+        attempts, _t_start = h.busy
+        if st.args and st.args[0] == "subgraph":
+            results = json.loads(st.args[1])
+            if {(r["gmv"], r["version"]) for r in results} != set(attempts):
+                return                                                        # stale
+            h.busy = None
+            # a streamed edge keeps nothing to re-read: one member's failure restarts the gang, so the failure is
+            # applied first and the completions of the same attempt then lose (they are no longer running)
+            failed = [r for r in results if not r["ok"]]
+            own = [r for r in failed if not r["message"].startswith("dryad_b200.runtime.executor.InputReadError: aborted")]
+            for r in (own or failed)[:1]:
+                self._apply_result(h, r)
+            for r in results:
+                if r["ok"]:
+                    self._apply_result(h, r)
+            return
+        v, version = attempts[0]
         if int(st.args[1]) != v or st.version != version:
             return                                                            # stale
         h.busy = None
+        part_file = next(((pth.split("|", 1)[0], pth.split("|", 1)[1], sz) for pth, sz in st.outputs if "|" in pth), None)
+        self._apply_result(h, {
+            "gmv": v, "version": version, "ok": st.state == STATE_COMPLETED, "n_in": int(st.args[2]), "n_out": int(st.args[3]),
+            "seconds": float(st.args[4]), "hits": int(st.args[5]), "bytes_in": [b for b, _ in st.channel_status],
+            "bad": next((k for k, (_b, err) in enumerate(st.channel_status) if err), -1), "message": st.message,
+            "out_bytes": sum(sz for pth, sz in st.outputs if "|" not in pth), "out_sizes": [sz for pth, sz in st.outputs if "|" not in pth],
+            "part_file": part_file, "deterministic": st.exit_code == 2})
+
+    def _apply_result(self, h: _Host, r: dict) -> None:
+        """One vertex attempt's outcome -> the graph, the bookkeeping, the event log."""
+        v, version = int(r["gmv"]), int(r["version"])
         h.vertices_run += 1
         node, part = self._vertex(v)
-        n_in, n_out, seconds, hits = int(st.args[2]), int(st.args[3]), float(st.args[4]), int(st.args[5])
-        if st.state == STATE_COMPLETED:
-            won = self.gm.completed(v, version, seconds, float(sum(b for b, _ in st.channel_status)))
+        n_in, n_out, seconds, hits = r["n_in"], r["n_out"], r["seconds"], r["hits"]
+        if r["ok"]:
+            won = self.gm.completed(v, version, seconds, float(sum(r.get("bytes_in", []))))
             if won:
                 self.versions[(node.uid, part)] = version
                 self.where[(node.uid, part)] = h.index
                 self.records[(node.uid, part)] = n_out
-                self.out_bytes[(node.uid, part)] = sum(sz for pth, sz in st.outputs if "|" not in pth)
-                for path, size in st.outputs:
-                    if "|" in path:
-                        tmp, final = path.split("|", 1)
-                        self.part_files[(node.uid, part)] = (tmp, final, size)
+                self.out_bytes[(node.uid, part)] = r["out_bytes"]
+                if r.get("part_file"):
+                    tmp, final, size = r["part_file"]
+                    self.part_files[(node.uid, part)] = (tmp, final, size)
                 self.dyn.on_completed(v, h.index)                             # run-time rewrites, before anything is dispatched
             ins = self.ex._gm_inputs.get(v, [])
             local = sum(self.records.get(e, 0) for e in ins if self.where.get(e) == h.index)
@@ -219,23 +246,23 @@ class JobManager:
             rec = {"stage": node.uid, "stage_name": node.name, "part": part, "version": version, "seconds": seconds,
                    "records_in": n_in, "records_out": n_out, "computer": h.index, "host": h.name, "won": bool(won),
                    "records_local": local, "records_remote": total - local, "cache_hits": hits,
-                   "bytes_in": [b for b, _ in st.channel_status], "bytes_out": [s for _, s in st.outputs]}
+                   "bytes_in": r.get("bytes_in", []), "bytes_out": r.get("out_sizes", [r["out_bytes"]])}
             self.stats.append(rec)
             self.reporter.vertex_event(node, part, version, "completed" if won else "completed_duplicate", seconds=seconds,
                                        records_in=n_in, records_out=n_out, computer=h.index, local=local,
                                        remote=total - local, cache_hits=hits)
         else:
-            bad = next((k for k, (_b, err) in enumerate(st.channel_status) if err), -1)
-            self.reporter.vertex_event(node, part, version, "failed", error=st.message, computer=h.index)
-            rc = self.gm.failed(v, version, st.message, bad_input=bad)
+            bad = r["bad"]
+            self.reporter.vertex_event(node, part, version, "failed", error=r["message"], computer=h.index)
+            rc = self.gm.failed(v, version, r["message"], bad_input=bad)
             if rc == 2 and bad >= 0:
                 prod = self.ex._gm_inputs[v][bad]
                 self.versions.pop(prod, None)
                 self.where.pop(prod, None)
-            elif rc == 1 or (st.exit_code == 2 and self.ctx.fail_fast_on_deterministic_errors):
-                self.error = st.message
+            elif rc == 1 or (r["deterministic"] and self.ctx.fail_fast_on_deterministic_errors):
+                self.error = r["message"]
                 if rc != 1:
-                    self._finish(False, st.message)
+                    self._finish(False, r["message"])
 
     def _on_exit(self, h: _Host) -> None:
         code = h.proc.poll() if h.proc is not None else None
@@ -243,12 +270,14 @@ class JobManager:
         if self.stopping:
             return
         if h.busy is not None:
-            v, version, _ = h.busy
-            node, part = self._vertex(v)
-            msg = f"vertex host {h.name} exited with code {code} while running {node.name}#{node.uid}[{part}] v{version}"
-            self.reporter.vertex_event(node, part, version, "failed", error=msg, computer=h.index)
-            if self.gm.failed(v, version, msg) == 1:
-                self.error = msg
+            attempts, _ = h.busy
+            # members of a sub-graph vertex are one gang: failing one restarts them all
+            for v, version in (attempts[:1] if len(attempts) > 1 else attempts):
+                node, part = self._vertex(v)
+                msg = f"vertex host {h.name} exited with code {code} while running {node.name}#{node.uid}[{part}] v{version}"
+                self.reporter.vertex_event(node, part, version, "failed", error=msg, computer=h.index)
+                if self.gm.failed(v, version, msg) == 1:
+                    self.error = msg
             h.busy = None
         for key in [k for k, w in self.where.items() if w == h.index]:          # its cache died with it; the files remain
             del self.where[key]
@@ -259,16 +288,20 @@ class JobManager:
             return
         self._launch(h)
 
-    def enqueue(self, v: int, version: int) -> None:
-        """Queue one vertex attempt with the scheduler, with its input affinities."""
+    def enqueue(self, attempts) -> None:
+        """Queue vertex attempts with the scheduler as ONE process — a single vertex, or the members of a
+        start clique that run together as a sub-graph vertex — with the input affinities of all of them."""
         from ..runtime.command import affinity_merge
         from .cluster import Affinity, Process
-        node, part = self._vertex(v)
+        if isinstance(attempts, tuple):
+            attempts = [attempts]
+        members = {self.vkey.get(v) for v, _ in attempts}
         votes: Dict[int, int] = {}
-        for e in self.ex._gm_inputs.get(v, []):
-            w = self.where.get(e)
-            if w is not None:
-                votes[w] = votes.get(w, 0) + max(1, self.records.get(e, 0))
+        for v, _version in attempts:
+            for e in self.ex._gm_inputs.get(v, []):
+                w = self.where.get(e)
+                if w is not None and e not in members:
+                    votes[w] = votes.get(w, 0) + max(1, self.records.get(e, 0))
         prefer: List[int] = []
         if votes:
             level, choice = affinity_merge(sorted(votes.items()), [0] * self.nhosts)
@@ -276,9 +309,14 @@ class JobManager:
                 prefer = [choice]
         pid = self._next_pid
         self._next_pid += 1
-        self.pending[pid] = (v, version)
-        self.cluster.schedule_process(Process(pid, f"{node.name}#{node.uid}[{part}]", Affinity(prefer, sum(votes.values()), False)))
-        self.reporter.vertex_event(node, part, version, "created", prefer=prefer[0] if prefer else None)
+        self.pending[pid] = list(attempts)
+        node, part = self._vertex(attempts[0][0])
+        label = f"{node.name}#{node.uid}[{part}]" + (f" +{len(attempts) - 1}" if len(attempts) > 1 else "")
+        self.cluster.schedule_process(Process(pid, label, Affinity(prefer, sum(votes.values()), False)))
+        for v, version in attempts:
+            n_, p_ = self._vertex(v)
+            self.reporter.vertex_event(n_, p_, version, "created", prefer=prefer[0] if prefer else None,
+                                       gang=len(attempts) if len(attempts) > 1 else None)
 
     def rebuild_maps(self) -> None:
         """After a run-time resize the native graph is the truth: vertex ids and input lists are re-read."""
@@ -294,6 +332,7 @@ class JobManager:
     def _dispatch(self) -> None:
         from ..runtime.command import CMD_START, VertexCommand
         now = time.perf_counter() - self.t0
+        gangs: Dict[int, List[Tuple[int, int]]] = {}
         while True:
             nxt = self.gm.next_ready(now)
             if nxt is None:
@@ -301,7 +340,13 @@ class JobManager:
             v, version = nxt
             if self.dyn.hold(v, version):
                 continue
-            self.enqueue(v, version)
+            clique = self.gm.clique(v)
+            if len(clique) > 1:
+                gangs.setdefault(min(clique), []).append((v, version))       # a start clique runs as ONE sub-graph vertex
+            else:
+                self.enqueue([(v, version)])
+        for members in gangs.values():
+            self.enqueue(sorted(members))
         waiting = self.cluster.scheduler.waiting
         if not waiting:
             return
@@ -310,15 +355,30 @@ class JobManager:
             p = self.cluster.computer_idle(h.index)
             if p is None:
                 continue
-            v, version = self.pending.pop(p.id)
+            attempts = self.pending.pop(p.id)
+            v, version = attempts[0]
             node, part = self._vertex(v)
-            inputs = [(f"chan://{uid}/{s}/{self.versions.get((uid, s), 0)}", self.records.get((uid, s), 0))
-                      for uid, s in self.ex._gm_inputs.get(v, [])]
-            cmd = VertexCommand(CMD_START, node.uid, version, args=[node.name, str(part), str(v)] + self.dyn.command_args(v), inputs=inputs,
+            if len(attempts) == 1:
+                inputs = [(f"chan://{uid}/{s}/{self.versions.get((uid, s), 0)}", self.records.get((uid, s), 0))
+                          for uid, s in self.ex._gm_inputs.get(v, [])]
+                args = [node.name, str(part), str(v)] + self.dyn.command_args(v)
+            else:
+                import json
+                members, inputs = [], []
+                for mv, mver in attempts:
+                    mn, mp = self._vertex(mv)
+                    mins = [[uid, s, self.versions.get((uid, s), 0)] for uid, s in self.ex._gm_inputs.get(mv, [])]
+                    members.append({"uid": mn.uid, "part": mp, "gmv": mv, "version": mver, "inputs": mins})
+                    inputs += [(f"chan://{u}/{s}/{ver}", self.records.get((u, s), 0)) for u, s, ver in mins]
+                args = [node.name, str(part), str(v), "subgraph", json.dumps(members)] + \
+                       [a for a in self.dyn.command_args(v) if a.startswith("widths=")]
+            cmd = VertexCommand(CMD_START, node.uid, version, args=args, inputs=inputs,
                                 outputs=[(f"chan://{node.uid}/{part}/{version}", 0)])
-            h.busy = (v, version, time.perf_counter())
+            h.busy = (list(attempts), time.perf_counter())
             self._mbox(h.name).set("cmd", "start", cmd.serialize())
-            self.reporter.vertex_event(node, part, version, "starting", computer=h.index)
+            for mv, mver in attempts:
+                mn, mp = self._vertex(mv)
+                self.reporter.vertex_event(mn, mp, mver, "starting", computer=h.index)
         if self.cluster.scheduler.waiting and any(h.ready and h.busy is None for h in self.hosts):
             self.pump.post(EV_DISPATCH, 0, 0.03)                              # delay scheduling: let preferences age
 

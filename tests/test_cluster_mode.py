@@ -288,3 +288,30 @@ def test_cluster_channels_gzip_and_custom_records(tmp_path):
     assert sorted(q2) == sorted((x % 4, x) for x in range(60))
     chans2 = os.path.join(str(tmp_path), "ClusterJobs", "2", "channels")
     assert any(f.endswith(".pkl") for f in os.listdir(chans2))
+
+
+def test_cluster_subgraph_vertex_streams_over_fifos(tmp_path):
+    """UseMemoryFIFO: the inputs of a join stream through in-process FIFOs, so producer and consumer
+    vertices form a start clique that runs as ONE sub-graph vertex on one host; a member's failure
+    restarts the gang (DryadSubGraphVertex, channelfifo.cpp, DrClique.h, DrCohort.cpp:852-929)."""
+    def inject(node, part, version):
+        if "Join" in node.name and part == 1 and version == 0:
+            raise RuntimeError("injected failure inside the gang")
+
+    ctx = _ctx(tmp_path, n=3, hosts=2, use_memory_fifo=True, broadcast_join_rows=0, fault_injector=inject)
+    a = ctx.from_enumerable(range(300), 3).select(lambda x: x * 2)
+    b = ctx.from_enumerable([(k, str(k)) for k in range(0, 600, 3)], 3)
+    out = sorted(a.join(b, lambda x: x, lambda t: t[0], lambda x, t: (x, t[1])))
+    assert out == [(k, str(k)) for k in range(0, 600, 6)]
+    st = ctx.last_cluster_status
+    log = open(os.path.join(str(tmp_path), "ClusterJobs", "1", "calypso.log")).read()
+    assert "gang=3" in log                                          # merge(outer)[i] + merge(inner)[i] + join[i] start together
+    assert "injected failure inside the gang" in log
+    # the gang of partition 1 ran twice, and its members did not leave channel files for the streamed edges
+    joins = [v for v in st["vertices"] if "Join" in v["stage_name"] and v["part"] == 1 and v["won"]]
+    assert joins and joins[0]["version"] >= 1
+    merges = [v for v in st["vertices"] if v["stage_name"] == "Merge" and v["part"] == 1 and v["won"]]
+    assert merges and all(v["version"] >= 1 for v in merges)
+    merge_uids = {v["stage"] for v in st["vertices"] if v["stage_name"] == "Merge"}
+    chans = os.listdir(os.path.join(str(tmp_path), "ClusterJobs", "1", "channels"))
+    assert not [f for f in chans if int(f.split("_")[0]) in merge_uids]
