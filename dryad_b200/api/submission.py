@@ -147,7 +147,9 @@ class ClusterJobSubmission(IDryadLinqJobSubmission):
         cmd = [sys.executable, "-m", "dryad_b200.sched.jm", self.job_dir]
         if self.workers:
             cmd += ["--workers", str(self.workers)]
-        env = {**os.environ, **{"DRYAD_OPT_" + k.upper(): v for k, v in self.options.items()}}
+        for k, v in self.options.items():                  # graph-manager options: -mai 64, -at 512MB, -nca ...
+            cmd += ["-" + k.lstrip("-")] + ([str(v)] if v not in ("", None, True) else [])
+        env = dict(os.environ)
         root = os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
         env["PYTHONPATH"] = root + os.pathsep + env.get("PYTHONPATH", "")
         out = open(os.path.join(self.job_dir, "log", "jm-stdout.txt"), "wb")

@@ -41,6 +41,8 @@ class DynamicManagers:
         self.jm = jm
         ctx = jm.ctx
         self.fan_in = int(getattr(ctx, "aggregation_tree_fan_in", 0) or 0)          # 0 = aggregation tree off
+        if self.fan_in and jm.app.max_aggregate_inputs != type(jm.app)().max_aggregate_inputs:
+            self.fan_in = jm.app.max_aggregate_inputs                               # -mai on the manager's command line wins
         self.broadcast_min = int(getattr(ctx, "broadcast_tree_min_consumers", 0) or 0)   # 0 = copy vertices off
         self.data_per_vertex = int(getattr(ctx, "dynamic_data_per_vertex", 0) or 0)      # 0 = distributor off
         self.agg: Dict[int, dict] = {}              # consumer gm vertex -> state of its tree
@@ -254,12 +256,12 @@ class DynamicManagers:
                 continue
             state["level"] += 1
             if state["commutative"]:
-                from .gm import aggregate_groups
-                sizes = [max(1, jm.records.get(jm.vkey[i], 0)) for i in ins]
+                sizes = [max(1, jm.out_bytes.get(jm.vkey[i], 0)) for i in ins]
                 chunks = []
                 for by_machine in (True, False):     # same machine first, then anywhere (one pod on this box)
                     machine = [jm.where.get(jm.vkey[i], -1) if by_machine else 0 for i in ins]
-                    gids = aggregate_groups(sizes, machine, [0] * len(ins), max_inputs=self.fan_in)
+                    jm.app.max_aggregate_inputs = self.fan_in
+                    gids = jm.app.aggregate_groups(sizes, machine, [0] * len(ins))     # -at / -nca apply here
                     groups: Dict[int, List[int]] = {}
                     for i, g in zip(ins, gids):
                         groups.setdefault(g, []).append(i)

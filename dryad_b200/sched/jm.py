@@ -52,7 +52,7 @@ class _Host:
 
 
 class JobManager:
-    def __init__(self, job_dir: str, workers: int = 0, max_host_restarts: int = 8):
+    def __init__(self, job_dir: str, workers: int = 0, max_host_restarts: int = 8, app=None):
         from ..runtime import jobpackage
         from ..runtime.executor import JobExecutor
         from ..runtime.process_service import ProcessService
@@ -61,6 +61,8 @@ class JobManager:
         from .reporting import CalypsoReporter
         self.job_dir = os.path.abspath(job_dir)
         self.ctx, self.plan = jobpackage.load(self.job_dir)
+        from .app import DryadLinqApp
+        self.app = app or DryadLinqApp()                  # the graph manager's own option table (-mai, -at, -nca, ...)
         self.reporter = CalypsoReporter(self.job_dir, level=self.ctx.runtime_logging_level.value)
         self.ex = JobExecutor(self.ctx, self.plan, reporter=self.reporter)
         self.gm = self.ex._build_gm()
@@ -455,6 +457,10 @@ class JobManager:
     def run(self) -> int:
         os.makedirs(os.path.join(self.job_dir, "log"), exist_ok=True)
         self.reporter.job_start(self.plan)
+        # which plan vertex became which graph-manager stage (DryadLinqApplication.cs identity map, `<plan>.map`)
+        self.app.open_identity_map(os.path.join(self.job_dir, "DryadLinqProgram__0.xml"))
+        for st, n in sorted(self.nodes.items()):
+            self.app.record_identity(n.uid, st, n.name)
         for h in self.hosts:
             self._launch(h)
         self.gm.start()
@@ -498,8 +504,14 @@ def main(argv: Optional[List[str]] = None) -> int:
     ap = argparse.ArgumentParser(prog="jm")
     ap.add_argument("job_dir")
     ap.add_argument("--workers", type=int, default=0)
-    a = ap.parse_args(argv)
-    jm = JobManager(a.job_dir, a.workers)
+    a, rest = ap.parse_known_args(argv)
+    from .app import DryadLinqApp
+    try:
+        app = DryadLinqApp.parse(rest)                    # -mai / -mafi / -at / -nca and the legacy switches
+    except ValueError as ex:
+        print(f"{ex}\noptions:\n{DryadLinqApp.usage()}", file=sys.stderr)
+        return 2
+    jm = JobManager(a.job_dir, a.workers, app=app)
     signal.signal(signal.SIGTERM, lambda *_: jm.cancel("cancelled (SIGTERM)"))
     return jm.run()
 

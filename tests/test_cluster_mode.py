@@ -315,3 +315,29 @@ def test_cluster_subgraph_vertex_streams_over_fifos(tmp_path):
     merge_uids = {v["stage"] for v in st["vertices"] if v["stage_name"] == "Merge"}
     chans = os.listdir(os.path.join(str(tmp_path), "ClusterJobs", "1", "channels"))
     assert not [f for f in chans if int(f.split("_")[0]) in merge_uids]
+
+
+def test_cluster_graph_manager_options_and_identity_map(tmp_path):
+    """The graph-manager process has its own option table (DryadLinqApplication.cs:34-409): -mai bounds the
+    inputs of an aggregation vertex; the identity map records plan vertex -> graph stage."""
+    import subprocess, sys
+    from dryad_b200.api.submission import ClusterJobSubmission
+    from dryad_b200.plan import static_config as SC
+    from dryad_b200.runtime import jobpackage
+    from dryad_b200.sched.app import DryadLinqApp
+    ctx = DryadLinqContext(8, work_dir=str(tmp_path))
+    ctx.dynamic_opt_level = SC.DYN_BROADCAST | SC.DYN_AGGREGATE
+    q = ctx.from_enumerable(range(800), 8).select(lambda x: x + 1).count_as_query().to_store(f"partfile://{tmp_path}/n.pt")
+    job_dir = str(tmp_path / "job")
+    jobpackage.write(job_dir, ctx, [q.materialize_lazy()])
+    sub = ClusterJobSubmission(job_dir, workers=2)
+    sub.add_job_option("mai", 2)
+    sub.submit_job()
+    assert sub.wait_for_completion(120).value == "Success", sub.error_text()
+    st = sub.status_record()
+    assert st["dynamic"]["aggregate"] >= 4                      # 8 partials, 2 inputs per internal vertex
+    assert list(ctx.from_store(f"partfile://{tmp_path}/n.pt")) == [800]
+    ident = DryadLinqApp.read_identity_map(os.path.join(job_dir, "DryadLinqProgram__0.xml.map"))
+    assert ident and all(isinstance(v[0], int) for v in ident.values())
+    bad = subprocess.run([sys.executable, "-m", "dryad_b200.sched.jm", job_dir, "-nosuchoption"], capture_output=True, text=True)
+    assert bad.returncode == 2 and "maxaggregateinputs" in bad.stderr
