@@ -154,6 +154,7 @@ class _Run:
             self.input_index[(int(u), int(sp))] = k
         self.input_bytes = [0] * len(member["inputs"])
         self.cache_hits = 0
+        self.remote_reads = 0
         self.fifo_in: Dict[Tuple[int, int], str] = {}        # (producer uid, part) -> fifo name
         self.fifo_out: List[str] = []
         self._fifo_payload: Dict[Tuple[int, int], Any] = {}
@@ -189,7 +190,11 @@ class _Run:
                     self.input_bytes[idx] += n
                 return pickle.loads(buf.raw)
         try:
-            payload, size = read_channel(host.job_dir, uid, part, port, ver)
+            if host.remote_reads:
+                payload, size = host.fetch_channel(uid, part, port, ver)
+                self.remote_reads += 1
+            else:
+                payload, size = read_channel(host.job_dir, uid, part, port, ver)
         except Exception as ex:  # noqa: BLE001  (missing, truncated or corrupt: all "cannot read")
             raise InputReadError(uid, part, f"cannot read channel {key}: {type(ex).__name__}: {ex}") from ex
         if idx >= 0:
@@ -211,6 +216,9 @@ class VertexHost:
         self.roots = {r.uid: r for r in self.plan.roots}
         self.compression = self.ctx.intermediate_data_compression_scheme
         self._handoff: Dict[str, Any] = {}
+        # channels produced on ANOTHER computer are fetched from that node's daemon over HTTP, in ranges
+        # (managedchannel HttpReader + ProcessService file server); on one box a shared directory serves as well
+        self.remote_reads = bool(getattr(self.ctx, "remote_channel_reads", False))
         # channel cache with spill: outputs of vertices that ran HERE are served from memory
         from .. import _native as N
         self._hostlib = N.host()
@@ -232,6 +240,35 @@ class VertexHost:
         with self._cache_lock:
             if len(b) <= (32 << 20) and self._hostlib.cache_put(self._cache, key.encode(), b, len(b)) == 0:
                 self._cached[key] = len(b)
+
+    def fetch_channel(self, uid: int, part: int, port: int, version: int, piece: int = 4 << 20):
+        """Read a channel through the process service's file server: ranged GETs into a scratch file."""
+        scratch = os.path.join(self.job_dir, "spill", self.id)
+        for kind in ("chan", "pkl"):
+            name = os.path.basename(channel_path(self.job_dir, uid, part, port, version, kind))
+            local = os.path.join(scratch, f"fetch-{name}")
+            try:
+                size = 0
+                with open(local, "wb") as f:
+                    while True:
+                        data = self.client.fetch_file(f"{CHAN_DIR}/{name}", size, size + piece - 1)
+                        f.write(data)
+                        size += len(data)
+                        if len(data) < piece:
+                            break
+            except FileNotFoundError:
+                if os.path.exists(local):
+                    os.remove(local)
+                continue
+            try:
+                if kind == "chan":
+                    from ..channel.factory import ChannelReader
+                    return list(ChannelReader(f"file://{local}")), size
+                with open(local, "rb") as f:
+                    return pickle.load(f), size
+            finally:
+                os.remove(local)
+        raise FileNotFoundError(f"channel {uid}_{part}_{port}.v{version} is not served by {self.client.uri}")
 
     def write_fifo(self, name: str, payload) -> None:
         """Stream one output to a member of the same sub-graph vertex through a bounded in-process FIFO
@@ -338,6 +375,7 @@ class VertexHost:
             res["deterministic"] = getattr(ex_, "code", None) is not None and not getattr(ex_, "transient", False)
         res["seconds"] = time.perf_counter() - t0
         res["hits"] = run.cache_hits
+        res["remote_reads"] = run.remote_reads
         res["bytes_in"] = list(run.input_bytes)
         return res
 
@@ -368,7 +406,7 @@ class VertexHost:
             results = self.run_subgraph(json.loads(extra[1]), subst)
             ok = all(r["ok"] for r in results)
             slim = [{k: r[k] for k in ("uid", "part", "gmv", "version", "ok", "n_in", "n_out", "seconds", "hits", "bad",
-                                        "out_bytes", "part_file", "deterministic")} | {"message": r["message"][:600]}
+                                        "out_bytes", "part_file", "deterministic", "remote_reads")} | {"message": r["message"][:600]}
                     for r in results]
             return VertexCommand(CMD_START, cmd.vertex_id, cmd.version, state=STATE_COMPLETED if ok else STATE_FAILED,
                                  args=["subgraph", json.dumps(slim)])
@@ -383,7 +421,8 @@ class VertexHost:
         return VertexCommand(CMD_START, r["uid"], r["version"], state=STATE_COMPLETED if r["ok"] else STATE_FAILED,
                              exit_code=0 if r["ok"] else (2 if r["deterministic"] else 1), message=r["message"],
                              outputs=outputs, channel_status=chans,
-                             args=[str(r["part"]), str(r["gmv"]), str(r["n_in"]), str(r["n_out"]), f"{r['seconds']:.6f}", str(r["hits"])])
+                             args=[str(r["part"]), str(r["gmv"]), str(r["n_in"]), str(r["n_out"]), f"{r['seconds']:.6f}", str(r["hits"]),
+                                   str(r["remote_reads"])])
 
     def run_subgraph(self, members: List[dict], subst) -> List[dict]:
         import threading

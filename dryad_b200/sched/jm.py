@@ -220,7 +220,7 @@ class JobManager:
         part_file = next(((pth.split("|", 1)[0], pth.split("|", 1)[1], sz) for pth, sz in st.outputs if "|" in pth), None)
         self._apply_result(h, {
             "gmv": v, "version": version, "ok": st.state == STATE_COMPLETED, "n_in": int(st.args[2]), "n_out": int(st.args[3]),
-            "seconds": float(st.args[4]), "hits": int(st.args[5]), "bytes_in": [b for b, _ in st.channel_status],
+            "seconds": float(st.args[4]), "hits": int(st.args[5]), "remote_reads": int(st.args[6]) if len(st.args) > 6 else 0, "bytes_in": [b for b, _ in st.channel_status],
             "bad": next((k for k, (_b, err) in enumerate(st.channel_status) if err), -1), "message": st.message,
             "out_bytes": sum(sz for pth, sz in st.outputs if "|" not in pth), "out_sizes": [sz for pth, sz in st.outputs if "|" not in pth],
             "part_file": part_file, "deterministic": st.exit_code == 2})
@@ -248,7 +248,7 @@ class JobManager:
             rec = {"stage": node.uid, "stage_name": node.name, "part": part, "version": version, "seconds": seconds,
                    "records_in": n_in, "records_out": n_out, "computer": h.index, "host": h.name, "won": bool(won),
                    "records_local": local, "records_remote": total - local, "cache_hits": hits,
-                   "bytes_in": r.get("bytes_in", []), "bytes_out": r.get("out_sizes", [r["out_bytes"]])}
+                   "remote_reads": r.get("remote_reads", 0), "bytes_in": r.get("bytes_in", []), "bytes_out": r.get("out_sizes", [r["out_bytes"]])}
             self.stats.append(rec)
             self.reporter.vertex_event(node, part, version, "completed" if won else "completed_duplicate", seconds=seconds,
                                        records_in=n_in, records_out=n_out, computer=h.index, local=local,

@@ -341,3 +341,21 @@ def test_cluster_graph_manager_options_and_identity_map(tmp_path):
     assert ident and all(isinstance(v[0], int) for v in ident.values())
     bad = subprocess.run([sys.executable, "-m", "dryad_b200.sched.jm", job_dir, "-nosuchoption"], capture_output=True, text=True)
     assert bad.returncode == 2 and "maxaggregateinputs" in bad.stderr
+
+
+def test_cluster_remote_channel_reads_over_http(tmp_path):
+    """Channels that are not in the reading host's own cache are fetched from the process service's
+    file server with ranged GETs (managedchannel HttpReader, ProcessService/HttpServer.cs ranged file GET)."""
+    import time
+
+    def slow_producers(node, part, version):
+        if "HashPartition" in node.name:
+            time.sleep(0.4)                      # long enough for the second host to take its share of the stage
+
+    ctx = _ctx(tmp_path, n=4, hosts=2, remote_channel_reads=True, fault_injector=slow_producers)
+    out = sorted(ctx.from_enumerable(range(4000), 4).select(lambda x: (x % 9, x)).group_by(lambda t: t[0])
+                 .select(lambda g: (g.key, g.count())))
+    assert out == sorted((k, len(range(k, 4000, 9))) for k in range(9))
+    st = ctx.last_cluster_status
+    assert sum(v["remote_reads"] for v in st["vertices"]) > 0
+    assert any(v["cache_hits"] > 0 for v in st["vertices"])          # what a host produced itself never crosses HTTP
