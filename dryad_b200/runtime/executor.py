@@ -54,6 +54,36 @@ class JobExecutor:
     def _inputs(self, node: DLinqQueryNode, i: int) -> List[List]:
         ins: List[List] = []
         t = node.type if node.type != NodeType.Super else node.members[0].type
+        if t == NodeType.Zip:
+            lp = [p[0] for p in self.out[node.children[0][0].uid]]
+            rp = [p[0] for p in self.out[node.children[1][0].uid]]
+            if all(hasattr(b, "cols") and not b.is_rows for b in lp + rp):
+                # columnar re-alignment: slices of the right side's partitions, no records
+                from .columnar import ColumnBatch
+                start = sum(b.n for b in lp[:i])
+                need = lp[i].n
+                segs, pos = [], 0
+                for b in rp:
+                    lo, hi = max(start, pos), min(start + need, pos + b.n)
+                    if lo < hi:
+                        segs.append(b.slice(lo - pos, hi - pos))
+                    pos += b.n
+                right = ColumnBatch.concat(segs) if segs else rp[0].slice(0, 0)
+                return [[lp[i]], [right]]
+            tr = self.backend.to_records
+            left = [[tr(p[0])] for p in self.out[node.children[0][0].uid]]
+            right = [[tr(p[0])] for p in self.out[node.children[1][0].uid]]
+            start = sum(len(left[s][0]) for s in range(i))
+            need = len(left[i][0])
+            flat: List = []
+            pos = 0
+            for s in range(node.children[1][0].partition_count):   # re-align right to left's boundaries
+                seg = right[s][0]
+                lo, hi = max(start, pos), min(start + need, pos + len(seg))
+                if lo < hi:
+                    flat.extend(seg[lo - pos:hi - pos])
+                pos += len(seg)
+            return [[left[i][0]], [flat]]
         for k, (child, op) in enumerate(node.children):
             co = self.out[child.uid]
             cpc = child.partition_count
@@ -85,36 +115,6 @@ class JobExecutor:
                 if i < acc + child.partition_count:
                     return [[self.out[child.uid][i - acc][0]]]
                 acc += child.partition_count
-        if t == NodeType.Zip:
-            lp = [p[0] for p in self.out[node.children[0][0].uid]]
-            rp = [p[0] for p in self.out[node.children[1][0].uid]]
-            if all(hasattr(b, "cols") and not b.is_rows for b in lp + rp):
-                # columnar re-alignment: slices of the right side's partitions, no records
-                from .columnar import ColumnBatch
-                start = sum(b.n for b in lp[:i])
-                need = lp[i].n
-                segs, pos = [], 0
-                for b in rp:
-                    lo, hi = max(start, pos), min(start + need, pos + b.n)
-                    if lo < hi:
-                        segs.append(b.slice(lo - pos, hi - pos))
-                    pos += b.n
-                right = ColumnBatch.concat(segs) if segs else rp[0].slice(0, 0)
-                return [[lp[i]], [right]]
-            tr = self.backend.to_records
-            left = [[tr(p[0])] for p in self.out[node.children[0][0].uid]]
-            right = [[tr(p[0])] for p in self.out[node.children[1][0].uid]]
-            start = sum(len(left[s][0]) for s in range(i))
-            need = len(left[i][0])
-            flat: List = []
-            pos = 0
-            for s in range(node.children[1][0].partition_count):   # re-align right to left's boundaries
-                seg = right[s][0]
-                lo, hi = max(start, pos), min(start + need, pos + len(seg))
-                if lo < hi:
-                    flat.extend(seg[lo - pos:hi - pos])
-                pos += len(seg)
-            return [[left[i][0]], [flat]]
         if t == NodeType.SlidingWindow:
             w = (node.members[0] if node.type == NodeType.Super else node).params["window"]
             cb = [p[0] for p in self.out[node.children[0][0].uid]]

@@ -30,6 +30,8 @@ def test_order_take_skip_reverse_zip():
     check_both(lambda c, src: src(DATA).take(5), sort=False)
     check_both(lambda c, src: src(DATA).reverse(), sort=False)
     check_both(lambda c, src: src(DATA).zip(src(DATA).select(lambda x: x * x), lambda a, b: (a, b)), sort=False)
+    # the two sides of a Zip may be partitioned differently: the right side is re-aligned to the left's boundaries
+    check_both(lambda c, src: c.from_enumerable(DATA, 4).zip(c.from_enumerable([x * x for x in DATA], 3), lambda a, b: (a, b)), sort=False)
     check_both(lambda c, src: src(DATA).take_while(lambda x: x < 6), sort=False)
     check_both(lambda c, src: src(DATA).skip_while(lambda x: x < 6), sort=False)
 

@@ -359,3 +359,52 @@ def test_cluster_remote_channel_reads_over_http(tmp_path):
     st = ctx.last_cluster_status
     assert sum(v["remote_reads"] for v in st["vertices"]) > 0
     assert any(v["cache_hits"] > 0 for v in st["vertices"])          # what a host produced itself never crosses HTTP
+
+
+def test_cluster_operator_sweep_matches_oracle(tmp_path):
+    """The operators whose vertices read neighbouring partitions or several ports (Zip, SlidingWindow,
+    Reverse, Concat, Fork, Take/Skip, indexed Select, set operations, Distinct, Apply, GroupJoin, OrderBy
+    descending, scalar aggregates) through vertex-host processes and file channels, against LocalDebug."""
+    data = [(i * 37) % 101 for i in range(500)]
+    other = [(i * 13) % 71 for i in range(300)]
+
+    def build(c):
+        a = c.from_enumerable(data, 4)
+        b = c.from_enumerable(other, 3)
+        qs = {
+            "zip": a.zip(c.from_enumerable(list(range(500)), 3), lambda x, y: x * 1000 + y),
+            "window": a.sliding_window(lambda w: sum(w), 3),
+            "reverse": a.reverse(),
+            "concat": a.concat(b),
+            "take": a.take(17),
+            "skip": a.skip(480),
+            "indexed": a.select_indexed(lambda x, i: x + i),
+            "union": a.union(b),
+            "intersect": a.intersect(b),
+            "except": a.except_(b),
+            "distinct": a.distinct(),
+            "apply": a.apply(lambda xs: [x for x in xs if x % 5 == 0]),
+            "groupjoin": a.distinct().group_join(b, lambda x: x, lambda y: y, lambda x, ys: (x, len(list(ys)))),
+            "orderdesc": a.order_by_descending(lambda x: x),
+            "where_sel": a.where(lambda x: x % 3 == 1).select(lambda x: x * 2),
+            "selmany": a.select_many(lambda x: [x, -x] if x % 10 == 0 else []),
+        }
+        return qs
+
+    ctx = _ctx(tmp_path, n=4, hosts=3)
+    oracle = DryadLinqContext(4, local_debug=True)
+    mine, ref = build(ctx), build(oracle)
+    ctx.submit_and_wait(*mine.values())                       # one job, sixteen outputs
+    ordered = {"zip", "window", "reverse", "concat", "take", "skip", "indexed", "orderdesc", "where_sel", "selmany", "apply"}
+    for name in mine:
+        got, want = list(mine[name]), list(ref[name])
+        if name in ordered:
+            assert got == want, name
+        else:
+            assert sorted(got) == sorted(want), name
+    # scalar aggregates: each is its own small job
+    a = ctx.from_enumerable(data, 4)
+    assert a.count() == 500 and a.sum() == sum(data) and a.min() == min(data) and a.max() == max(data)
+    assert a.any(lambda x: x == 100) == (100 in data) and a.all(lambda x: x >= 0)
+    assert a.first() == data[0] and a.last() == data[-1] and a.contains(data[7])
+    assert abs(a.average() - sum(data) / len(data)) < 1e-9
