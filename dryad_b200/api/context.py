@@ -529,7 +529,14 @@ class DryadLinqContext:
         self.last_job_stats = rec.get("vertices", [])
         self.last_cluster_status = rec
         if st != JobStatus.Success:
-            raise DryadLinqException(ErrorCode.DidNotCompleteSuccessfully, sub.error_text() or "job failed")
+            text = sub.error_text() or "job failed"
+            # a vertex that failed with one of the API's own errors (empty-sequence aggregate, user function
+            # failure, ...) keeps its error code on the client side, as in the in-process executor
+            import re
+            m = re.search(r"DryadLinqException: \[(\w+)\] ?(.*)", text, re.S)
+            if m and isinstance(getattr(ErrorCode, m.group(1), None), int) and m.group(1) != "DidNotCompleteSuccessfully":
+                raise DryadLinqException(getattr(ErrorCode, m.group(1)), m.group(2).strip() or text)
+            raise DryadLinqException(ErrorCode.DidNotCompleteSuccessfully, text)
         tables: Dict[int, Table] = {}
         for r in roots:
             t = rec["tables"][str(r.expr.id)]

@@ -372,7 +372,7 @@ class VertexHost:
             res["message"] = "".join(traceback.format_exception_only(type(ex_), ex_)).strip()[:3000]
             if isinstance(ex_, InputReadError):
                 res["bad"] = run.input_index.get((ex_.producer_uid, ex_.producer_part), -1)
-            res["deterministic"] = getattr(ex_, "code", None) is not None and not getattr(ex_, "transient", False)
+            res["deterministic"] = getattr(ex_, "error_code", None) is not None and not getattr(ex_, "transient", False)
         res["seconds"] = time.perf_counter() - t0
         res["hits"] = run.cache_hits
         res["remote_reads"] = run.remote_reads

@@ -408,3 +408,14 @@ def test_cluster_operator_sweep_matches_oracle(tmp_path):
     assert a.any(lambda x: x == 100) == (100 in data) and a.all(lambda x: x >= 0)
     assert a.first() == data[0] and a.last() == data[-1] and a.contains(data[7])
     assert abs(a.average() - sum(data) / len(data)) < 1e-9
+
+
+def test_cluster_api_errors_keep_their_code(tmp_path):
+    from dryad_b200.api.errors import ErrorCode
+    ctx = _ctx(tmp_path, n=2, hosts=1, max_failures_per_vertex=1)
+    with pytest.raises(DryadLinqException) as e:
+        ctx.from_enumerable([], 2).select(lambda x: x).min()
+    assert e.value.error_code == ErrorCode.MinNoElements
+    with pytest.raises(DryadLinqException) as e:
+        ctx.from_enumerable([1, 2, 3], 2).apply(lambda xs: [1 // 0 for _ in xs]).count()
+    assert e.value.error_code == ErrorCode.FailureInUserApplyFunction
