@@ -90,7 +90,13 @@ class DryadLinqJobInfo:
 
     def cancel_job(self) -> None:
         self._cancel.set()
-        if self.status in (JobStatus.NotSubmitted, JobStatus.Waiting):
+        sub = getattr(self, "submission", None)
+        if sub is not None and self.status in (JobStatus.Waiting, JobStatus.Running):
+            sub.terminate_job()              # the graph-manager process stops its vertex hosts and publishes nothing
+            if self._thread is not None:
+                self._thread.join(30)
+            self.status = JobStatus.Cancelled
+        elif self.status in (JobStatus.NotSubmitted, JobStatus.Waiting):
             self.status = JobStatus.Cancelled
 
     Wait, CancelJob = wait, cancel_job
@@ -456,6 +462,18 @@ class DryadLinqContext:
         already = [q for q in qs if q._job is not None]
         if len(already) == len(qs):          # re-submitting an executed query returns the existing job
             return qs[0]._job
+        if self.platform == PlatformKind.LOCAL_CLUSTER:
+            # the job runs in other processes: Submit returns at once, Wait / CancelJob act on the handle
+            # (DryadLinqJobInfo.Wait / CancelJob, LinqToDryad/DryadLinqJobInfo.cs)
+            def run():
+                try:
+                    self._run_job(job)
+                except BaseException:  # noqa: BLE001  (kept in job.error; Wait re-raises it)
+                    pass
+            job.status = JobStatus.Waiting
+            job._thread = threading.Thread(target=run, name="dryad-job", daemon=True)
+            job._thread.start()
+            return job
         self._run_job(job)
         return job
 
@@ -502,7 +520,7 @@ class DryadLinqContext:
                 job.results.append(res)
             job.status = JobStatus.Success
         except BaseException as ex:  # noqa: BLE001
-            job.status = JobStatus.Failure
+            job.status = JobStatus.Cancelled if job._cancel.is_set() else JobStatus.Failure
             job.error = ex
             raise
 
@@ -519,6 +537,8 @@ class DryadLinqContext:
         for f in self.resources_to_add:
             sub.add_local_file(f)
         job.submission = sub
+        if job._cancel.is_set():
+            raise DryadLinqException(ErrorCode.DidNotCompleteSuccessfully, "job was cancelled")
         sub.submit_job()
         limit = float(self.job_runtime_limit) + 30.0 if self.job_runtime_limit else None
         st = sub.wait_for_completion(limit)

@@ -419,3 +419,28 @@ def test_cluster_api_errors_keep_their_code(tmp_path):
     with pytest.raises(DryadLinqException) as e:
         ctx.from_enumerable([1, 2, 3], 2).apply(lambda xs: [1 // 0 for _ in xs]).count()
     assert e.value.error_code == ErrorCode.FailureInUserApplyFunction
+
+
+def test_cluster_submit_is_asynchronous_and_cancellable(tmp_path):
+    """Submit returns a job handle at once; Wait blocks; CancelJob stops the graph manager and its hosts."""
+    import time
+    from dryad_b200.api.context import JobStatus
+
+    def slow(node, part, version):
+        time.sleep(20)
+
+    ctx = _ctx(tmp_path, n=2, hosts=2)
+    job = ctx.submit(ctx.from_enumerable(range(100), 2).select(lambda x: x + 1).to_store(f"partfile://{tmp_path}/fast.pt"))
+    assert job.status in (JobStatus.Waiting, JobStatus.Running, JobStatus.Success)
+    res = job.wait()
+    assert job.status == JobStatus.Success and sorted(res[0]) == list(range(1, 101))
+    ctx2 = _ctx(tmp_path / "b", n=2, hosts=2, fault_injector=slow)
+    t0 = time.time()
+    job2 = ctx2.submit(ctx2.from_enumerable(range(10), 2).select(lambda x: x).to_store(f"partfile://{tmp_path}/slow.pt"))
+    assert time.time() - t0 < 5                          # did not wait for the 20 s vertices
+    time.sleep(3.0)
+    job2.cancel_job()
+    assert job2.status == JobStatus.Cancelled
+    with pytest.raises(DryadLinqException):
+        job2.wait()
+    assert not os.path.exists(tmp_path / "slow.pt")
