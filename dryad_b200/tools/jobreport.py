@@ -8,7 +8,7 @@ rules for serialization errors :545, failed-when-reading :573, plan parse errors
 machine failures :749, deterministic input failure :807).  The WinForms GUI itself is out of scope
 (no windowing here); this produces the same information as text / JSON.
 
-    python -m dryad_b200.tools.jobreport <job_dir> [--json]
+    python -m dryad_b200.tools.jobreport <job_dir> [--json | --html [out.html]]
 """
 from __future__ import annotations
 
@@ -215,12 +215,99 @@ def render(job: Dict[str, Any]) -> str:
     return "\n".join(lines)
 
 
+def _ts(text: str) -> float:
+    import datetime
+    return datetime.datetime.strptime(text, "%Y-%m-%dT%H:%M:%S.%fZ").replace(tzinfo=datetime.timezone.utc).timestamp()
+
+
+def render_html(job: Dict[str, Any]) -> str:
+    """Self-contained HTML page with two inline SVG drawings — the stage graph with per-stage progress and
+    the schedule (one lane per computer, one bar per vertex attempt) — followed by the text report.
+    The information content of the reference's job browser views (JobBrowser/JobBrowser: static / dynamic
+    plan drawing, `jobschedule.cs` Gantt view, diagnosis pane), without a window system."""
+    import html
+    stages = job["stages"]
+    by_id = {str(s["id"]): s for s in stages}
+    level: Dict[str, int] = {}
+
+    def depth(sid: str) -> int:
+        if sid not in level:
+            level[sid] = 0
+            kids = [c for c in by_id[sid]["children"] if c in by_id]
+            level[sid] = 1 + max((depth(c) for c in kids), default=-1)
+        return level[sid]
+
+    for sid in by_id:
+        depth(sid)
+    rows: Dict[int, List[str]] = defaultdict(list)
+    for sid, lv in level.items():
+        rows[lv].append(sid)
+    bw, bh, gx, gy = 210, 44, 30, 36
+    pos = {}
+    for lv, ids in rows.items():
+        for k, sid in enumerate(sorted(ids, key=int)):
+            pos[sid] = (20 + k * (bw + gx), 20 + lv * (bh + gy))
+    gw = max((x for x, _ in pos.values()), default=0) + bw + 20
+    gh = max((y for _, y in pos.values()), default=0) + bh + 20
+    g = [f'<svg xmlns="http://www.w3.org/2000/svg" width="{gw}" height="{gh}" font-family="monospace" font-size="11">']
+    for sid, s in by_id.items():
+        x, y = pos[sid]
+        for c in s["children"]:
+            if c in pos:
+                cx, cy = pos[c]
+                g.append(f'<line x1="{cx + bw / 2}" y1="{cy + bh}" x2="{x + bw / 2}" y2="{y}" stroke="#888"/>')
+    for sid, s in by_id.items():
+        x, y = pos[sid]
+        done = s["completed"] >= s["partitions"] > 0
+        fill = "#f6c7c7" if s["failed"] and not done else ("#cfe8cf" if done else "#eeeeee")
+        g.append(f'<rect x="{x}" y="{y}" width="{bw}" height="{bh}" rx="5" fill="{fill}" stroke="#444"/>')
+        g.append(f'<text x="{x + 6}" y="{y + 16}">#{sid} {html.escape(s["name"][:28])}</text>')
+        g.append(f'<text x="{x + 6}" y="{y + 32}">x{s["partitions"]}  done {s["completed"]}  failed {s["failed"]}</text>')
+    g.append("</svg>")
+    # schedule
+    atts = [a for a in job["attempts"] if a.get("start") and a.get("end")]
+    sched = ["<p>(no timed attempts)</p>"]
+    if atts:
+        t0 = min(_ts(a["start"]) for a in atts)
+        t1 = max(_ts(a["end"]) for a in atts)
+        span = max(t1 - t0, 1e-6)
+        lanes = sorted({str(a.get("computer", "-")) for a in atts}, key=lambda v: (len(v), v))
+        lw, lh, left = 900, 22, 90
+        sched = [f'<svg xmlns="http://www.w3.org/2000/svg" width="{lw + left + 20}" height="{len(lanes) * (lh + 6) + 40}" '
+                 f'font-family="monospace" font-size="10">']
+        for k, lane in enumerate(lanes):
+            y = 10 + k * (lh + 6)
+            sched.append(f'<text x="4" y="{y + 15}">computer {html.escape(lane)}</text>')
+            sched.append(f'<rect x="{left}" y="{y}" width="{lw}" height="{lh}" fill="#fafafa" stroke="#ddd"/>')
+        for a in atts:
+            k = lanes.index(str(a.get("computer", "-")))
+            x = left + (_ts(a["start"]) - t0) / span * lw
+            w = max(1.5, (_ts(a["end"]) - _ts(a["start"])) / span * lw)
+            color = {"completed": "#4c9f4c", "failed": "#c0392b", "completed_duplicate": "#d4a017"}.get(a["state"], "#999")
+            tip = f'v{a["vertex"]} ver {a["version"]} {a["state"]}' + (f' — {a["error"][:80]}' if a.get("error") else "")
+            sched.append(f'<rect x="{x:.1f}" y="{10 + k * (lh + 6) + 2}" width="{w:.1f}" height="{lh - 4}" fill="{color}">'
+                         f'<title>{html.escape(tip)}</title></rect>')
+        sched.append(f'<text x="{left}" y="{len(lanes) * (lh + 6) + 26}">0 s</text>')
+        sched.append(f'<text x="{left + lw - 60}" y="{len(lanes) * (lh + 6) + 26}">{span:.3f} s</text>')
+        sched.append("</svg>")
+    return ("<!doctype html><html><head><meta charset='utf-8'><title>" + html.escape(job["dir"]) + "</title></head><body>"
+            "<h2>Stage graph</h2>" + "".join(g) + "<h2>Schedule</h2>" + "".join(sched) +
+            "<h2>Report</h2><pre>" + html.escape(render(job)) + "</pre></body></html>")
+
+
 def main(argv=None):
     argv = argv or sys.argv[1:]
     if not argv:
         print(__doc__)
         return 2
     job = build_job(argv[0])
+    if "--html" in argv:
+        i = argv.index("--html")
+        out = argv[i + 1] if i + 1 < len(argv) and not argv[i + 1].startswith("--") else os.path.join(argv[0], "report.html")
+        with open(out, "w") as f:
+            f.write(render_html(job))
+        print(out)
+        return 0
     print(json.dumps(job, indent=1) if "--json" in argv else render(job))
     return 0
 

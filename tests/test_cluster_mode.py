@@ -87,6 +87,14 @@ def test_cluster_host_death_and_vertex_retry(tmp_path):
     job = build_job(os.path.join(str(tmp_path), "ClusterJobs", "1"))
     assert any("vertex-host process" in d for d in job["diagnosis"])
     assert any(p["exitcode"] == 7 for p in job["processes"]) and "Vertex hosts:" in render(job)
+    # the browser views as one self-contained page: stage graph + schedule lanes per computer, as inline SVG
+    import re
+    import xml.dom.minidom
+    from dryad_b200.tools.jobreport import render_html
+    page = render_html(job)
+    svgs = re.findall(r"<svg.*?</svg>", page, re.S)
+    assert len(svgs) == 2 and all(xml.dom.minidom.parseString(x) for x in svgs)
+    assert page.count("#c0392b") >= 1                         # failed attempts are drawn in red on the schedule
 
 
 def test_cluster_unreadable_channel_reruns_producer(tmp_path):
