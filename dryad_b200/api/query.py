@@ -18,7 +18,7 @@ from typing import Dict, Any, Callable, Iterable, List, Optional, Sequence
 
 from ..expr import ir as X
 from ..plan.decomposition import try_decompose
-from ..plan.logical import Lam, QExpr, Schema
+from ..plan.logical import Lam, QExpr, Schema, _records_out
 from .errors import DryadLinqException, ErrorCode
 
 
@@ -47,7 +47,7 @@ def _lam_indexed(fn, schema: Schema) -> Lam:
     ir = None
     if schema is not None and callable(fn) and all(k != "o" for k in schema.values()):
         ir = X.trace(fn, schema, X.col(IDX, "i"))
-    return Lam(fn, ir, 2)
+    return Lam(_records_out(fn) if callable(fn) else fn, ir, 2)
 
 
 def _lam_pair(fn, sa: Schema, sb: Schema) -> Lam:
@@ -62,7 +62,7 @@ def _lam_pair(fn, sa: Schema, sb: Schema) -> Lam:
             ir = X.normalise_traced(fn(sym(sa, "a."), sym(sb, "b.")))
         except Exception:  # noqa: BLE001  (opaque lambda: host path)
             ir = None
-    return Lam(fn, ir, 2)
+    return Lam(_records_out(fn), ir, 2)
 
 
 def _fn_from_ir(ir):
@@ -189,7 +189,7 @@ class Query:
         dec = try_decompose_group_join(result, self.schema, inner.schema) if callable(result) else None
         return self._new("group_join", [inner], schema=dec.out_schema() if dec is not None else None,
                          outer_key=_lam(outer_key, self.schema), inner_key=_lam(inner_key, inner.schema),
-                         result=Lam(result, None, 2), comparer=comparer, gj_decomp=dec)
+                         result=Lam(_records_out(result) if callable(result) else result, None, 2), comparer=comparer, gj_decomp=dec)
 
     def concat(self, other: "Query") -> "Query":
         return self._new("concat", [other], schema=self.schema if self.schema == other.schema else None)
@@ -485,7 +485,7 @@ def _join_result_lam(result, outer_schema: Schema, inner_schema: Schema) -> Lam:
             ir = X.normalise_traced(result(o, i))
         except Exception:
             ir = None
-    return Lam(result, ir, 2)
+    return Lam(_records_out(result), ir, 2)       # a selector that builds `{...}` yields Records on the host path too
 
 
 class MultiQuery:

@@ -2,7 +2,9 @@
 
   python samples/wordcount.py --mode local  [input.txt]      # LocalJobSubmission-style, host CPU
   python samples/wordcount.py --mode debug  [input.txt]      # LocalDebug (LINQ-to-objects oracle)
+  python samples/wordcount.py --mode cluster [input.txt]     # a graph-manager process + vertex-host processes
   python samples/wordcount.py --mode gpu    [input.txt]      # one B200: tokenizer + hash-aggregate kernels
+  python samples/wordcount.py --mode gpu-api [input.txt]     # one B200, through the query API (text stays in HBM)
 
 The query is the reference's:  lines.SelectMany(l => l.Split(' ')).GroupBy(w => w)
                                     .Select(g => new Pair(g.Key, g.Count())).OrderByDescending(count).Take(20)
@@ -22,7 +24,7 @@ SAMPLE = ("the quick brown fox jumps over the lazy dog\n" * 200 +
 
 def main(argv=None):
     ap = argparse.ArgumentParser()
-    ap.add_argument("--mode", choices=["local", "debug", "gpu"], default="local")
+    ap.add_argument("--mode", choices=["local", "debug", "cluster", "gpu", "gpu-api"], default="local")
     ap.add_argument("--partitions", type=int, default=4)
     ap.add_argument("input", nargs="?")
     a = ap.parse_args(argv)
@@ -42,7 +44,9 @@ def main(argv=None):
         d = wordcount.gpu_result_to_dict(raw, rep_start, rep_len, counts)
         top = sorted(((w.decode(), c) for w, c in d.items()), key=lambda wc: (-wc[1], wc[0]))[:20]
     else:
-        ctx = D.DryadLinqContext(a.partitions, local_debug=(a.mode == "debug"))
+        from dryad_b200.api.context import PlatformKind
+        ctx = D.DryadLinqContext(a.partitions, local_debug=(a.mode == "debug"), device="cuda:0" if a.mode == "gpu-api" else "cpu",
+                                 platform=PlatformKind.LOCAL_CLUSTER if a.mode == "cluster" else PlatformKind.LOCAL)
         lines = ctx.from_store(f"file://{path}") if hasattr(ctx, "from_store") else ctx.from_enumerable(open(path).read().splitlines(), a.partitions)
         q = (lines.select_many(lambda l: str(l).split(" "))
                   .where(lambda w: w != "")
