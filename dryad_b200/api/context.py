@@ -66,6 +66,19 @@ class Table:
     def partition_count(self) -> int:
         return len(self.partitions) if self.partitions is not None else 0
 
+    # A job package must not carry the DATA of a stored table: processes that load the package open the
+    # partitions they need from the store themselves (the reference's vertices get input channel URIs).
+    by_reference = threading.local()
+
+    def __getstate__(self):
+        st = dict(self.__dict__)
+        if getattr(Table.by_reference, "on", False) and self.uri and self.partitions is not None:
+            from ..channel.store import LazyPartitions
+            lazy = LazyPartitions.describe(self.uri, self.partitions)
+            if lazy is not None:
+                st["partitions"] = lazy
+        return st
+
 
 class DryadLinqJobInfo:
     """Job handle: ids, Wait() (raises on failure), CancelJob()."""
@@ -307,7 +320,9 @@ class DryadLinqContext:
         not distinct whatever they were when written (DryadLinqQuery.cs:547-551)."""
         self._check_not_disposed()
         from ..channel import store
-        t = store.open_table(uri, text_partitions=self.world if self.world > 1 else 1)
+        # a text file is cut into byte ranges at line boundaries: one per rank (SPMD) or per partition (cluster mode)
+        cuts = self.world if self.world > 1 else (self.num_partitions if self.platform == PlatformKind.LOCAL_CLUSTER else 1)
+        t = store.open_table(uri, text_partitions=cuts)
         parts = t.partitions
         if self.world > 1 and len(parts) == self.world and parts and isinstance(parts[0], store.TextPartition):
             parts = [p if i == self.rank else None for i, p in enumerate(parts)]   # SPMD: every rank keeps its own byte range
@@ -362,7 +377,7 @@ class DryadLinqContext:
         if table.partitions is not None:
             try:
                 # text partitions are raw bytes: estimate instead of splitting them into lines here
-                rows = sum((max(len(p.data), 0 if p.device_buf is None else int(p.device_buf.numel())) // 32 + 1) if hasattr(p, "data") else len(p)
+                rows = sum((p.nbytes // 32 + 1) if hasattr(p, "nbytes") else len(p)
                            for p in table.partitions if p is not None)
             except TypeError:
                 rows = None
@@ -383,7 +398,7 @@ class DryadLinqContext:
 
     def _read_table_partition(self, table: Table, i: int):
         p = table.partitions[i]
-        if hasattr(p, "data") and hasattr(p, "to_records"):
+        if getattr(p, "is_text_partition", False):
             return p              # raw text partition: lines are materialised only if a vertex iterates it
         if hasattr(p, "to_records"):
             return p.to_records() if self._backend().wants_records else p

@@ -217,10 +217,37 @@ class TextPartition:
     host code iterates (host backend, LocalDebug, enumeration).
     Reference: LinqToDryad/DryadLinqTextReader.cs:36-280."""
 
-    def __init__(self, data, device_buf=None):
-        self.data = data                     # bytes (host copy; b"" when only the device copy exists)
+    is_text_partition = True                 # cheap type test that does not touch (and so does not load) `data`
+
+    def __init__(self, data, device_buf=None, source=None):
+        self._data = data                    # bytes (host copy; b"" when only the device copy exists); None = not read yet
         self.device_buf = device_buf         # optional uint8 tensor already holding the same bytes
+        self.source = source                 # (path, lo, hi): the byte range of a file this partition stands for
         self._lines: Optional[List[LineRecord]] = None
+
+    @classmethod
+    def from_file(cls, path: str, lo: int, hi: int) -> "TextPartition":
+        """A byte range of a text file, read when first used (a vertex that never runs here never reads it)."""
+        return cls(None, None, (path, lo, hi))
+
+    @property
+    def data(self):
+        if self._data is None:
+            path, lo, hi = self.source
+            with open(path, "rb") as f:
+                f.seek(lo)
+                self._data = f.read(hi - lo)
+        return self._data
+
+    @data.setter
+    def data(self, value):
+        self._data = value
+
+    @property
+    def nbytes(self) -> int:
+        if self._data is None:
+            return self.source[2] - self.source[1]
+        return max(len(self._data), 0 if self.device_buf is None else int(self.device_buf.numel()))
 
     def to_records(self) -> List[LineRecord]:
         if self._lines is None:
@@ -237,6 +264,84 @@ class TextPartition:
 
     def __getitem__(self, i):
         return self.to_records()[i]
+
+
+class LazyPartitions:
+    """The partitions of a stored table, opened on demand: what a job package carries instead of the data.
+    Text: (path, byte ranges); partfile: (path of the metadata file).  Indexing loads ONE partition."""
+
+    def __init__(self, uri: str, kind: str, ranges=None, count: int = 0):
+        self.uri, self.kind, self.ranges, self.count = uri, kind, ranges, count
+
+    @staticmethod
+    def describe(uri: str, partitions):
+        try:
+            scheme, path = parse_uri(uri)
+        except Exception:  # noqa: BLE001
+            return None
+        if not isinstance(DataProvider.for_uri(uri), PartitionedFileProvider) or not os.path.exists(path):
+            return None                                    # other providers: the data travels with the package
+        if all(isinstance(p, TextPartition) for p in partitions) and partitions:
+            if all(p.source is not None and p.source[0] == path for p in partitions):
+                return LazyPartitions(uri, "text", [(p.source[1], p.source[2]) for p in partitions], len(partitions))
+            return None
+        if path.endswith(".pt") and not any(isinstance(p, TextPartition) for p in partitions):
+            return LazyPartitions(uri, "partfile", None, len(partitions))
+        return None
+
+    def __len__(self):
+        return self.count
+
+    def nbytes(self, i: int) -> int:
+        """Stored size of partition i, without reading it."""
+        if self.kind == "text":
+            return self.ranges[i][1] - self.ranges[i][0]
+        _, path = parse_uri(self.uri)
+        _, _, sizes = _read_meta(path)
+        return int(sizes[i]) if i < len(sizes) else 0
+
+    def __getitem__(self, i):
+        if isinstance(i, slice):
+            return [self[k] for k in range(*i.indices(self.count))]
+        if i < 0:
+            i += self.count
+        if not 0 <= i < self.count:
+            raise IndexError(i)
+        _, path = parse_uri(self.uri)
+        if self.kind == "text":
+            lo, hi = self.ranges[i]
+            return TextPartition.from_file(path, lo, hi)
+        base, n, _ = _read_meta(path)
+        return read_partition_file(_part_path(base, i))
+
+    def __iter__(self):
+        return (self[i] for i in range(self.count))
+
+
+def split_text_file(path: str, n: int) -> List[tuple]:
+    """Byte ranges [(lo, hi)] that cut a text FILE into n parts of about equal size at line boundaries,
+    reading only a little around each cut."""
+    total = os.path.getsize(path)
+    if n <= 1 or total == 0:
+        return [(0, total)]
+    cuts = [0]
+    with open(path, "rb") as f:
+        for i in range(1, n):
+            pos = max(cuts[-1], (total * i) // n)
+            f.seek(pos)
+            end = total
+            while pos < total:
+                chunk = f.read(1 << 16)
+                if not chunk:
+                    break
+                k = chunk.find(b"\n")
+                if k >= 0:
+                    end = pos + k + 1
+                    break
+                pos += len(chunk)
+            cuts.append(min(end, total))
+    cuts.append(total)
+    return [(cuts[i], cuts[i + 1]) for i in range(n)]
 
 
 def split_text(data: bytes, n: int) -> List[bytes]:
@@ -261,9 +366,9 @@ def _pf_open_table(uri: str, text_partitions: int = 1) -> StoredTable:
     if not os.path.exists(path):
         raise DryadLinqException(ErrorCode.StreamDoesNotExist, f"{uri} does not exist")
     if scheme == "file" or not path.endswith(".pt"):
-        with open(path, "rb") as f:                       # plain text: one LineRecord per line
-            data = f.read()
-        return StoredTable([TextPartition(d) for d in split_text(data, text_partitions)], {"value": "s"})
+        # plain text, one LineRecord per line: byte ranges of the file, read when a vertex first touches them
+        return StoredTable([TextPartition.from_file(path, lo, hi) for lo, hi in split_text_file(path, text_partitions)],
+                           {"value": "s"})
     base, n, _ = _read_meta(path)
     schema = None
     if os.path.exists(path + ".schema"):

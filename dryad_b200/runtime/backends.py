@@ -20,12 +20,12 @@ class HostBackend:
     def run_vertex(self, node, part, inputs, env):
         # raw text partitions stay raw: a native vertex operator may consume the bytes directly, and
         # they turn into LineRecords only when a vertex iterates them
-        ins = [[p if hasattr(p, "data") else self.to_records(p) for p in payloads] for payloads in inputs]
+        ins = [[p if getattr(p, "is_text_partition", False) else self.to_records(p) for p in payloads] for payloads in inputs]
         return vertex_ops.run(node, part, ins, env)
 
     @staticmethod
     def count(payload) -> int:
-        if hasattr(payload, "data") and getattr(payload, "_lines", 1) is None:
+        if getattr(payload, "is_text_partition", False) and getattr(payload, "_lines", 1) is None:
             return payload.data.count(b"\n")          # raw text: count lines without materialising them
         try:
             return len(payload)

@@ -44,7 +44,12 @@ def write(job_dir: str, context, roots) -> str:
         # two pickles: the module search path first, because functions pickled by reference need the
         # client's modules importable BEFORE the second pickle is loaded
         pickle.dump({"sys_path": [p for p in sys.path if p], "cwd": os.getcwd()}, f)
-        cloudpickle.dump(pkg, f, protocol=pickle.HIGHEST_PROTOCOL)
+        from ..api.context import Table
+        Table.by_reference.on = True                  # stored tables travel as (URI, ranges), not as data
+        try:
+            cloudpickle.dump(pkg, f, protocol=pickle.HIGHEST_PROTOCOL)
+        finally:
+            Table.by_reference.on = False
     os.replace(tmp, path)
     return path
 

@@ -54,7 +54,7 @@ def write_ports(job_dir: str, uid: int, part: int, version: int, ports, compress
     out: List[Tuple[str, int, int]] = []
     pickled: Dict[int, Any] = {}
     for k, payload in enumerate(ports):
-        raw = hasattr(payload, "data") and hasattr(payload, "to_records")     # raw text partition: keep the bytes
+        raw = getattr(payload, "is_text_partition", False)                    # raw text partition: keep the bytes
         if raw:
             pickled[k] = payload
             continue
@@ -91,7 +91,9 @@ def read_channel(job_dir: str, uid: int, part: int, port: int, version: int):
 
 
 def _count(payload) -> int:
-    if hasattr(payload, "data") and getattr(payload, "_lines", 1) is None:
+    if getattr(payload, "is_text_partition", False) and getattr(payload, "_lines", 1) is None:
+        if getattr(payload, "_data", b"") is None:
+            return payload.nbytes // 32 + 1           # not read yet: an estimate is enough for placement weights
         return payload.data.count(b"\n")
     try:
         return len(payload)
@@ -169,6 +171,14 @@ class _Run:
                 return []                                          # folded into an internal vertex's output
             uid, part, port = int(t.split("/")[0]), int(t.split("/")[1]), 0
             hops += 1
+        src = host.nodes.get(uid)
+        if src is not None and src.type.value == "InputTable":
+            # a stored (or packaged) table is read where it is consumed: no channel file between the source and its reader
+            payload = host.ctx._read_table_partition(src.params["table"], part)
+            idx = self.input_index.get((uid, part), -1)
+            if idx >= 0:
+                self.input_bytes[idx] += payload.nbytes if getattr(payload, "is_text_partition", False) else 0
+            return payload
         name = self.fifo_in.get((uid, part))
         if name is not None:
             if (uid, part) not in self._fifo_payload:
@@ -336,6 +346,28 @@ class VertexHost:
                     ports = [payloads[0]]
                 else:
                     ports = [vertex_ops.internal_combine(self.nodes[int(internal[1])], [self.backend.to_records(p) for p in payloads], env)]
+            elif self.nodes[uid].type.value == "InputTable":
+                # a source is read where it is consumed; its vertex only reports the partition's size and
+                # record count (estimated for data that has not been read), which the manager uses for
+                # placement weights and for sizing dynamic distributors
+                table = self.nodes[uid].params["table"]
+                parts_ = table.partitions
+                if hasattr(parts_, "nbytes"):
+                    size = parts_.nbytes(part)
+                    res["n_out"] = size // 32 + 1
+                else:
+                    payload = self.ctx._read_table_partition(table, part)
+                    if getattr(payload, "is_text_partition", False):
+                        size = payload.nbytes
+                    else:
+                        try:
+                            size = len(pickle.dumps(payload, protocol=pickle.HIGHEST_PROTOCOL))
+                        except Exception:  # noqa: BLE001
+                            size = 64 * _count(payload)
+                    res["n_out"] = _count(payload)
+                res["out_bytes"], res["out_sizes"], res["ok"] = size, [size], True
+                res["seconds"], res["remote_reads"] = time.perf_counter() - t0, 0
+                return res
             else:
                 node = self.nodes[uid]
                 ins = ex._inputs(node, part)
@@ -346,7 +378,7 @@ class VertexHost:
             for name in run.fifo_out:                              # streamed edges first: the consumer is waiting
                 self.write_fifo(name, ports[0])
             if run.fifo_out and not self._needs_file(uid):
-                res["n_out"] = sum(_count(p) for p in ports)
+                res["n_out"] = sum(_count(p) for p in ports)      # streamed edges keep nothing
             else:
                 for k, (path, size, nrec) in enumerate(write_ports(self.job_dir, uid, part, version, ports, self.compression)):
                     self._cache_put(f"{uid}_{part}_{k}.v{version}", ports[k])

@@ -112,6 +112,9 @@ class JobManager:
         log = open(os.path.join(self.job_dir, "log", f"host-{h.name}.txt"), "wb")
         env = dict(os.environ)
         env["DRYAD_JOB_DIR"] = self.job_dir
+        if "DRYAD_THREADS_PER_WORKER" not in self.ctx.job_environment_variables:
+            # the hosts share this box: split its cores between them (DRYAD_THREADS_PER_WORKER, VertexEnv.cs:72-86)
+            env["DRYAD_THREADS_PER_WORKER"] = str(max(1, (os.cpu_count() or 1) // self.nhosts))
         cmd = [sys.executable, "-m", "dryad_b200.runtime.vertex_host", "--service", self.service.uri, "--id", h.name,
                "--job-dir", self.job_dir]
         h.proc = subprocess.Popen(cmd, stdout=log, stderr=subprocess.STDOUT, env=env, cwd=self.job_dir)

@@ -210,7 +210,7 @@ def test_cluster_runtime_distributor_resizes_consumers(tmp_path):
     info = store.stream_info(uri)
     assert info.partition_count != 4 and info.partition_count == st["tables"][list(st["tables"])[0]]["partitions"]
     assert sorted(ctx.from_store(uri)) == sorted((k, len([x for x in range(1000) if x % 13 == k])) for k in range(13))
-    finals = [v for v in st["vertices"] if "GroupBy" in v["stage_name"]]
+    finals = [v for v in st["vertices"] if "Merge_GroupBy" in v["stage_name"]]
     assert len({v["part"] for v in finals}) == info.partition_count
     log = open(os.path.join(str(tmp_path), "ClusterJobs", "1", "calypso.log")).read()
     assert "dynamic,manager=distributor" in log
@@ -452,3 +452,23 @@ def test_cluster_submit_is_asynchronous_and_cancellable(tmp_path):
     with pytest.raises(DryadLinqException):
         job2.wait()
     assert not os.path.exists(tmp_path / "slow.pt")
+
+
+def test_cluster_job_package_references_stored_tables(tmp_path):
+    """A stored input travels as (URI, byte ranges): the package stays small and every vertex host opens
+    only the partitions it runs (the reference hands input channel URIs to the vertices)."""
+    text = tmp_path / "big.txt"
+    line = "alpha beta gamma delta alpha\n"
+    text.write_text(line * 40000)                                   # ~1.1 MB
+    ctx = _ctx(tmp_path, n=4, hosts=2)
+    lines = ctx.from_store(f"file://{text}")
+    assert lines.expr.params["partition_count"] == 4                # cut into byte ranges at line boundaries
+    wc = dict(lines.select_many(lambda l: l.line.split(" ")).group_by(lambda w: w).select(lambda g: (g.key, g.count())))
+    assert wc == {"alpha": 80000, "beta": 40000, "gamma": 40000, "delta": 40000}
+    pkg = os.path.join(str(tmp_path), "ClusterJobs", "1", "job.pkl")
+    assert os.path.getsize(pkg) < 200_000                           # not the megabyte of text
+    uri = f"partfile://{tmp_path}/nums.pt"
+    ctx.submit_and_wait(ctx.from_enumerable(range(50000), 4).to_store(uri))
+    assert ctx.from_store(uri).select(lambda x: x % 7).sum() == sum(x % 7 for x in range(50000))
+    pkg3 = os.path.join(str(tmp_path), "ClusterJobs", "3", "job.pkl")
+    assert os.path.getsize(pkg3) < 100_000
