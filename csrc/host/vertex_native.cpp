@@ -20,36 +20,54 @@
 
 namespace {
 
-struct Entry { const char* p; uint32_t n; uint64_t h; int64_t c; };
+// A slot keeps the word's first 8 bytes and its length next to the hash: words of up to 8 bytes are
+// compared without touching the text they were first seen in (that text is cold by then — comparing
+// through the pointer cost one DRAM miss per token).
+struct Entry { const char* p; uint64_t h; int64_t c; uint64_t prefix; uint32_t n; };
+
+inline uint64_t load_prefix(const char* p, size_t n, const char* end) {
+  uint64_t v = 0;
+  if (p + 8 <= end) memcpy(&v, p, 8); else memcpy(&v, p, (size_t)(end - p));
+  return n >= 8 ? v : (v & ((1ULL << (8 * n)) - 1));
+}
+
+inline uint64_t mix64(uint64_t x) {
+  x ^= x >> 33; x *= 0xff51afd7ed558ccdULL; x ^= x >> 33; x *= 0xc4ceb9fe1a85ec53ULL; x ^= x >> 33;
+  return x;
+}
 
 struct Table {
   std::vector<Entry> slots;
   size_t used = 0, mask = 0;
-  explicit Table(size_t cap = 1 << 12) { slots.assign(cap, Entry{nullptr, 0, 0, 0}); mask = cap - 1; }
-  static uint64_t hash(const char* p, size_t n) {
-    uint64_t h = 0xcbf29ce484222325ULL;
-    for (size_t i = 0; i < n; ++i) { h ^= (unsigned char)p[i]; h *= 0x100000001b3ULL; }
-    h ^= h >> 32;
+  explicit Table(size_t cap = 1 << 12) { slots.assign(cap, Entry{nullptr, 0, 0, 0, 0}); mask = cap - 1; }
+  // 8 bytes at a time; `prefix` is the (masked) first word, already loaded by the caller
+  static uint64_t hash(const char* p, size_t n, uint64_t prefix) {
+    uint64_t h = mix64(prefix ^ (0x9E3779B97F4A7C15ULL * (uint64_t)(n + 1)));
+    for (size_t i = 8; i < n; i += 8) {
+      uint64_t v = 0;
+      memcpy(&v, p + i, n - i >= 8 ? 8 : n - i);
+      h = mix64(h ^ v);
+    }
     return h | 1;                                   // never 0: 0 marks an empty slot
   }
   void grow() {
     std::vector<Entry> old;
     old.swap(slots);
-    slots.assign(old.size() * 2, Entry{nullptr, 0, 0, 0});
+    slots.assign(old.size() * 2, Entry{nullptr, 0, 0, 0, 0});
     mask = slots.size() - 1;
     for (const Entry& e : old)
       if (e.h) { size_t i = e.h & mask; while (slots[i].h) i = (i + 1) & mask; slots[i] = e; }
   }
-  void add(const char* p, size_t n, uint64_t h, int64_t c) {
+  void add(const char* p, size_t n, uint64_t h, uint64_t prefix, int64_t c) {
     size_t i = h & mask;
     for (;;) {
       Entry& e = slots[i];
       if (!e.h) {
-        e = Entry{p, (uint32_t)n, h, c};
+        e = Entry{p, h, c, prefix, (uint32_t)n};
         if (++used * 2 > slots.size()) grow();
         return;
       }
-      if (e.h == h && e.n == n && memcmp(e.p, p, n) == 0) { e.c += c; return; }
+      if (e.h == h && e.n == n && e.prefix == prefix && (n <= 8 || memcmp(e.p + 8, p + 8, n - 8) == 0)) { e.c += c; return; }
       i = (i + 1) & mask;
     }
   }
@@ -78,20 +96,28 @@ void* hv_split_count(const char* text, int64_t n, int delim, int keep_empty, int
     cut[t] = c < n ? c + 1 : n;
   }
   const char d = (char)delim;
+  const char* const text_end = text + n;
   auto work = [&](int t) {
     Table& m = tabs[t];
-    int64_t i = cut[t], e = cut[t + 1], tot = 0;
-    while (i < e) {
-      int64_t le = i;
-      while (le < e && text[le] != '\n') ++le;        // one line [i, le)
-      int64_t s = i;
-      for (int64_t j = i; j <= le; ++j) {
-        if (j == le || text[j] == d) {
-          if (keep_empty || j > s) { m.add(text + s, (size_t)(j - s), Table::hash(text + s, (size_t)(j - s)), 1); ++tot; }
-          s = j + 1;
+    int64_t e = cut[t + 1], tot = 0;
+    int64_t s = cut[t];                               // start of the current token
+    for (int64_t j = cut[t]; j < e; ++j) {            // one pass: a token ends at the delimiter or at the end of its line
+      const char ch = text[j];
+      if (ch == d || ch == '\n') {
+        if (keep_empty || j > s) {
+          const size_t len = (size_t)(j - s);
+          const uint64_t pre = load_prefix(text + s, len, text_end);
+          m.add(text + s, len, Table::hash(text + s, len, pre), pre, 1);
+          ++tot;
         }
+        s = j + 1;
       }
-      i = le + 1;
+    }
+    if (s < e || (keep_empty && s == e && e > cut[t] && text[e - 1] == d)) {   // last line without a newline
+      const size_t len = (size_t)(e - s);
+      const uint64_t pre = load_prefix(text + s, len, text_end);
+      m.add(text + s, len, Table::hash(text + s, len, pre), pre, 1);
+      ++tot;
     }
     totals[t] = tot;
   };
@@ -105,11 +131,25 @@ void* hv_split_count(const char* text, int64_t n, int delim, int keep_empty, int
   r->table = std::move(tabs[0]);
   r->total = totals[0];
   for (int t = 1; t < threads; ++t) {
-    for (const Entry& e : tabs[t].slots) if (e.h) r->table.add(e.p, e.n, e.h, e.c);
+    for (const Entry& e : tabs[t].slots) if (e.h) r->table.add(e.p, e.n, e.h, e.prefix, e.c);
     r->total += totals[t];
   }
   for (const Entry& e : r->table.slots) if (e.h) r->word_bytes += e.n;
   return r;
+}
+
+// Occurrences of one byte (line count of a text partition for the vertex statistics): memchr speed.
+int64_t hv_count_byte(const char* text, int64_t n, int byte) {
+  int64_t c = 0;
+  const char* p = text;
+  const char* end = text + n;
+  while (p < end) {
+    const char* q = (const char*)memchr(p, byte, (size_t)(end - p));
+    if (!q) break;
+    ++c;
+    p = q + 1;
+  }
+  return c;
 }
 
 int64_t hv_groups(void* h) { return (int64_t)((Result*)h)->table.used; }

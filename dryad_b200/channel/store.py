@@ -243,6 +243,13 @@ class TextPartition:
     def data(self, value):
         self._data = value
 
+    def line_count(self) -> int:
+        """Number of line terminators, counted once (natively: the vertex statistics ask several times)."""
+        if getattr(self, "_nlines", None) is None:
+            d = self.data
+            self._nlines = int(N.host().hv_count_byte(d, len(d), 10)) if d else 0
+        return self._nlines
+
     @property
     def nbytes(self) -> int:
         if self._data is None:

@@ -26,7 +26,7 @@ class HostBackend:
     @staticmethod
     def count(payload) -> int:
         if getattr(payload, "is_text_partition", False) and getattr(payload, "_lines", 1) is None:
-            return payload.data.count(b"\n")          # raw text: count lines without materialising them
+            return payload.line_count()              # raw text: count lines without materialising them
         try:
             return len(payload)
         except TypeError:

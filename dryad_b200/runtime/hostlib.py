@@ -117,6 +117,7 @@ _d("cache_get", c_int64, [P, c_char_p, c_char_p, c_int64])
 _d("cache_stats", c_int, [P] + [C.POINTER(c_int64)] * 4)
 _d("fprint64", c_uint64, [c_uint64, c_char_p, c_int64])
 _d("hv_split_count", P, [c_char_p, c_int64, c_int, c_int, c_int])
+_d("hv_count_byte", c_int64, [c_char_p, c_int64, c_int])
 _d("hv_groups", c_int64, [P])
 _d("hv_word_bytes", c_int64, [P])
 _d("hv_total", c_int64, [P])

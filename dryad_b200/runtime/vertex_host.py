@@ -94,7 +94,7 @@ def _count(payload) -> int:
     if getattr(payload, "is_text_partition", False) and getattr(payload, "_lines", 1) is None:
         if getattr(payload, "_data", b"") is None:
             return payload.nbytes // 32 + 1           # not read yet: an estimate is enough for placement weights
-        return payload.data.count(b"\n")
+        return payload.line_count()
     try:
         return len(payload)
     except TypeError:
@@ -538,9 +538,17 @@ def main(argv: Optional[List[str]] = None) -> int:
     ap.add_argument("--idle-timeout", type=float, default=300.0)
     a = ap.parse_args(argv)
     host = VertexHost(a.service, a.id, a.job_dir)
+    prof = None
+    if os.environ.get("DRYAD_HOST_PROFILE"):           # profile the vertices this host runs: <job dir>/log/host-<id>.prof
+        import cProfile
+        prof = cProfile.Profile()
+        prof.enable()
     try:
         return host.serve(a.idle_timeout)
     finally:
+        if prof is not None:
+            prof.disable()
+            prof.dump_stats(os.path.join(a.job_dir, "log", f"host-{a.id}.prof"))
         host.close()
 
 

@@ -148,6 +148,7 @@ int affinity_merge(int n, const int32_t* computer, const int64_t* weight, const 
  * SelectMany(line.Split(delim)) -> GroupBy(word) with Count(), from raw text bytes (LinqToDryad/
  * DryadLinqVertex.cs:5718-6032, samples/WordCount.cs.pp:72-75).  The handle owns the group table. */
 void* hv_split_count(const char* text, int64_t n, int delim, int keep_empty, int threads);
+int64_t hv_count_byte(const char* text, int64_t n, int byte);
 int64_t hv_groups(void* h);
 int64_t hv_word_bytes(void* h);
 int64_t hv_total(void* h);
