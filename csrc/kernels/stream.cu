@@ -68,8 +68,11 @@ __device__ __forceinline__ void run_program(const Program& P, int64_t row, Reg* 
       case DRYAD_OP_ADD_I: d.i = a.i + b.i; break;
       case DRYAD_OP_SUB_I: d.i = a.i - b.i; break;
       case DRYAD_OP_MUL_I: d.i = a.i * b.i; break;
-      case DRYAD_OP_DIV_I: d.i = b.i ? a.i / b.i : 0; break;   // C# truncating division
-      case DRYAD_OP_MOD_I: d.i = b.i ? a.i % b.i : 0; break;
+      // Python's // and %: floored quotient, remainder with the divisor's sign (same as the generated kernels)
+      case DRYAD_OP_DIV_I: { if (!b.i) { d.i = 0; break; } const long long q = a.i / b.i, r = a.i % b.i;
+                             d.i = (r != 0 && ((r < 0) != (b.i < 0))) ? q - 1 : q; break; }
+      case DRYAD_OP_MOD_I: { if (!b.i) { d.i = 0; break; } const long long r = a.i % b.i;
+                             d.i = (r != 0 && ((r < 0) != (b.i < 0))) ? r + b.i : r; break; }
       case DRYAD_OP_NEG_I: d.i = -a.i; break;
       case DRYAD_OP_ADD_F: d.f = a.f + b.f; break;
       case DRYAD_OP_SUB_F: d.f = a.f - b.f; break;

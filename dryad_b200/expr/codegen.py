@@ -26,8 +26,18 @@ _PRELUDE = r"""
 typedef long long i64; typedef unsigned long long u64;
 __device__ __forceinline__ u64 dryad_mix64(u64 x) {
   x ^= x >> 30; x *= 0xbf58476d1ce4e5b9ULL; x ^= x >> 27; x *= 0x94d049bb133111ebULL; x ^= x >> 31; return x; }
-__device__ __forceinline__ i64 dryad_div(i64 a, i64 b) { return b ? a / b : 0; }
-__device__ __forceinline__ i64 dryad_mod(i64 a, i64 b) { return b ? a % b : 0; }
+// Python's // and %: floored quotient, remainder with the divisor's sign (0 for a zero divisor)
+__device__ __forceinline__ i64 dryad_div(i64 a, i64 b) {
+  if (!b) return 0;
+  i64 q = a / b, r = a % b;
+  return (r != 0 && ((r < 0) != (b < 0))) ? q - 1 : q; }
+__device__ __forceinline__ i64 dryad_mod(i64 a, i64 b) {
+  if (!b) return 0;
+  i64 r = a % b;
+  return (r != 0 && ((r < 0) != (b < 0))) ? r + b : r; }
+__device__ __forceinline__ double dryad_fmod(double a, double b) {
+  double r = fmod(a, b);
+  return (r != 0.0 && ((r < 0.0) != (b < 0.0))) ? r + b : r; }
 // read-only probe of a finished join table (4-key buckets, csrc/kernels/hash_table.cu find_slot)
 template <bool WANT_SLOT>
 __device__ __forceinline__ i64 dryad_probe(const u64* __restrict__ keys, const int* __restrict__ head, u64 cap, u64 key) {
@@ -128,7 +138,7 @@ def emit(e: Expr, cols: Mapping[str, str], ctx: Optional[_Ctx] = None) -> str:
         return f"(({A[0]}) / ({A[1]}))" if k == "f" else f"dryad_div({A[0]}, {A[1]})"
     if op == "mod":
         if k == "f":
-            return f"fmod({A[0]}, {A[1]})"
+            return f"dryad_fmod({A[0]}, {A[1]})"
         return f"dryad_mod({A[0]}, {A[1]})"
     if op == "and":
         return f"((({A[0]}) != 0) & (({A[1]}) != 0))"

@@ -79,8 +79,12 @@ class Expr:
         if a.kind == "o" or b.kind == "o":
             # opaque operands (strings, objects, untyped aggregates): host evaluation only
             return Expr("truediv_o" if op == "truediv" else op, (a, b), "o")
-        if op == "div":
-            k = "f" if "f" in (a.kind, b.kind) else "i"   # C#: int / int truncates
+        if op == "floordiv":                              # `//`: floored, on integers and on floats
+            if "f" in (a.kind, b.kind):
+                return Expr("floor", (Expr("div", (cast(a, "f"), cast(b, "f")), "f"),), "f")
+            return Expr("div", (a, b), "i")
+        if op == "div":                                   # an existing node being rebuilt: integer = floored, float = true division
+            k = "f" if "f" in (a.kind, b.kind) else "i"
         elif op == "truediv":
             return Expr("div", (cast(a, "f"), cast(b, "f")), "f")
         else:
@@ -97,8 +101,8 @@ class Expr:
     def __rmul__(self, o): return self._bin(o, "mul", True)
     def __truediv__(self, o): return self._bin(o, "truediv")
     def __rtruediv__(self, o): return self._bin(o, "truediv", True)
-    def __floordiv__(self, o): return self._bin(o, "div")
-    def __rfloordiv__(self, o): return self._bin(o, "div", True)
+    def __floordiv__(self, o): return self._bin(o, "floordiv")
+    def __rfloordiv__(self, o): return self._bin(o, "floordiv", True)
     def __mod__(self, o): return self._bin(o, "mod")
     def __rmod__(self, o): return self._bin(o, "mod", True)
     def __neg__(self): return Expr("neg", (self,), self.kind)
@@ -268,19 +272,23 @@ def to_string(e: Expr) -> str:
 
 
 # ---- evaluation (host) ---------------------------------------------------------------------
+# The lambdas are Python: `//` and `%` keep Python's meaning on every backend (floored division, a
+# remainder with the divisor's sign), so a traced query and the same query run as opaque Python agree
+# on negative operands.  (The reference's C# truncates; its users wrote C#.)
 def _trunc_div(a, b):
     if isinstance(a, float) or isinstance(b, float):
         return a / b
     if b == 0:
         raise ZeroDivisionError("integer division by zero")
-    q = abs(a) // abs(b)
-    return q if (a >= 0) == (b >= 0) else -q
+    return a // b
 
 
 def _trunc_mod(a, b):
     if isinstance(a, float) or isinstance(b, float):
-        return math.fmod(a, b)
-    return a - b * _trunc_div(a, b)
+        return a % b if b != 0 else math.nan
+    if b == 0:
+        raise ZeroDivisionError("integer modulo by zero")
+    return a % b
 
 
 _PY = {
@@ -293,7 +301,7 @@ _PY = {
 
 
 def eval_row(e: Expr, row: Mapping[str, Any], index: int = 0) -> Any:
-    """Scalar evaluation with C# semantics (truncating integer division and remainder)."""
+    """Scalar evaluation; integer division and remainder are Python's (floored)."""
     op = e.op
     if op == "col":
         return row[e.args[0]]
@@ -348,12 +356,11 @@ def eval_numpy(e: Expr, cols: Mapping[str, np.ndarray], n: int) -> np.ndarray:
     if op == "div":
         if e.kind == "f":
             return A[0] / A[1]
-        q = np.abs(A[0]) // np.abs(np.where(A[1] == 0, 1, A[1]))
-        return np.where((A[0] >= 0) == (A[1] >= 0), q, -q)
+        return np.where(A[1] == 0, 0, np.floor_divide(A[0], np.where(A[1] == 0, 1, A[1])))
     if op == "mod":
         if e.kind == "f":
-            return np.fmod(A[0], A[1])
-        return np.fmod(A[0], np.where(A[1] == 0, 1, A[1]))
+            return np.mod(A[0], A[1])
+        return np.where(A[1] == 0, 0, np.mod(A[0], np.where(A[1] == 0, 1, A[1])))
     if op == "eq": return A[0] == A[1]
     if op == "ne": return A[0] != A[1]
     if op == "lt": return A[0] < A[1]

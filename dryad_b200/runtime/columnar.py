@@ -265,6 +265,9 @@ class ColumnBatch:
     @staticmethod
     def concat(batches: Sequence["ColumnBatch"]) -> "ColumnBatch":
         batches = [b for b in batches if b is not None]
+        if len(batches) > 1:
+            full = [b for b in batches if b.n > 0]         # empty pieces add nothing, and may lack the columns of the others
+            batches = full or batches[:1]
         if len(batches) == 1:
             return batches[0]
         names = list(batches[0].cols)

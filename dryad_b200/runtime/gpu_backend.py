@@ -957,7 +957,8 @@ def _basic_aggregate(be, node, part, inputs, env):
             return [src.slice(i, i + 1) if i >= 0 else src.slice(0, 0)]
         # sum / min / max / average over a value column or a traced selector
         if fn is not None:
-            out, _ = run_on_gpu({"v": fn.ir}, src.cols, n) if n else ({"v": torch.empty(0, dtype=torch.int64, device=be.device)}, None)
+            empty_dt = torch.float64 if getattr(fn.ir, "kind", "i") == "f" else torch.int64
+            out, _ = run_on_gpu({"v": fn.ir}, src.cols, n) if n else ({"v": torch.empty(0, dtype=empty_dt, device=be.device)}, None)
             col = out["v"]
         else:
             if "value" not in src.cols:
@@ -968,6 +969,8 @@ def _basic_aggregate(be, node, part, inputs, env):
         if n == 0:
             if kind == "sum":
                 return [ColumnBatch({"value": torch.zeros(1, dtype=col.dtype, device=be.device)}, 1)]
+            if kind == "average":                          # an empty partition's partial has the (sum, count) shape too
+                return [ColumnBatch({"item1": col[:0], "item2": torch.empty(0, dtype=torch.int64, device=be.device)}, 0, tuple_like=True)]
             return [ColumnBatch({"value": col[:0]}, 0)]
         if kind in ("sum", "average"):
             tot = _checked_sum_i64(col) if col.dtype == torch.int64 else K.reduce(col.contiguous(), "sum")

@@ -17,8 +17,9 @@ def test_trace_and_host_eval_agree_with_python():
     assert np.allclose(got, xs * 2 + ys)
     for x, y in zip(xs.tolist(), ys.tolist()):
         assert eval_row(ir["c"], {"x": x, "y": y}) == (x if x > 2 else -x)
-    # C# semantics: integer division and remainder truncate toward zero
-    assert eval_row(col("x") // 2, {"x": -7}) == -3 and eval_row(col("x") % 3, {"x": -7}) == -1
+    # the lambdas are Python: // floors and % takes the divisor's sign, on every backend
+    assert eval_row(col("x") // 2, {"x": -7}) == -4 and eval_row(col("x") % 3, {"x": -7}) == 2
+    assert eval_row(col("x") % -3, {"x": 7}) == -2 and eval_row(col("y", "f") // 2, {"y": -7.5}) == -4.0
     assert trace(lambda r: r.x if r.x > 0 else 0, {"x": "i"}) is None          # data-dependent control flow
 
 

@@ -185,7 +185,7 @@ def test_tokenize(K, keep_empty):
     assert [int(h) for h in hashes.cpu().numpy().view(np.uint64)[:20]] == [hash_bytes_py(w) for w in got[:20]]
 
 
-def test_expr_program_and_filter(K):
+def test_expr_program_and_filter(K, monkeypatch):
     from dryad_b200.expr import col, lit
     from dryad_b200.expr.compile import run_on_gpu
     n = 70_001
@@ -197,8 +197,13 @@ def test_expr_program_and_filter(K):
     assert torch.equal(out["x"], a * 3 + 1)
     assert torch.allclose(out["y"], b * 2.0 + a.to(torch.float64))
     ref = ((torch.remainder(a, 2) == 0) & (b < 0.5))
-    # C# % is a truncating remainder: even-ness is identical for negatives
     assert torch.equal(flags.bool(), ref)
+    # Python's % and // on negative operands, in the generated kernel and in the register-program interpreter
+    for codegen_on in ("1", "0"):
+        monkeypatch.setenv("DRYAD_EXPR_CODEGEN", codegen_on)
+        o, _ = run_on_gpu({"m": col("a") % 7, "q": col("a") // 7, "mn": col("a") % -7, "qn": col("a") // -7}, cols, n)
+        assert torch.equal(o["m"], torch.remainder(a, 7)) and torch.equal(o["q"], torch.div(a, 7, rounding_mode="floor"))
+        assert torch.equal(o["mn"], torch.remainder(a, -7)) and torch.equal(o["qn"], torch.div(a, -7, rounding_mode="floor"))
 
 
 def test_row_sorter_window_path_and_fallback(K):
@@ -309,7 +314,7 @@ def test_expr_interpreter_fallback_matches_codegen(K, monkeypatch):
     for k in proj:
         assert torch.equal(o1[k], o2[k]), k
     assert torch.equal(f1, f2)
-    ref_x = torch.where(torch.fmod(a, 3) == 0, torch.div(a, 2, rounding_mode="trunc"), -a)
+    ref_x = torch.where(torch.remainder(a, 3) == 0, torch.div(a, 2, rounding_mode="floor"), -a)
     assert torch.equal(o1["x"], ref_x)
 
 
