@@ -60,3 +60,42 @@ def test_cluster_mode_matches_oracle_on_random_queries(tmp_path):
             assert _norm(got[1], got[0]) == _norm(want[1], want[0]), f"{make.__name__} seed {seed}"
             checked += 1
     assert checked >= 5
+
+
+def _plain(v):
+    if isinstance(v, dict):
+        return tuple(sorted((k, _plain(x)) for k, x in v.items()))
+    if isinstance(v, (list, tuple)):
+        return tuple(_plain(x) for x in v)
+    if isinstance(v, float):
+        return round(v, 6) + 0.0
+    return v
+
+
+def _norm_typed(x, ordered):
+    if isinstance(x, tuple) and x and x[0] == "ERR":
+        return ("ERR", x[1])
+    if isinstance(x, list):
+        x = [_plain(v) for v in x]
+        return x if ordered is True else sorted(x, key=repr)
+    return _plain(x)
+
+
+def _typed_queries_match(device, seeds, tmp_path):
+    from fuzz_columnar import build_columnar
+    for seed in seeds:
+        got = _eval(build_columnar, seed, DryadLinqContext(3, device=device, work_dir=str(tmp_path)))
+        want = _eval(build_columnar, seed, DryadLinqContext(3, local_debug=True))
+        assert _norm_typed(got[1], got[0]) == _norm_typed(want[1], want[0]), f"seed {seed}"
+
+
+def test_typed_random_queries_on_the_host_backend(tmp_path):
+    """Records of int/float columns with traced lambdas (negative keys, empty partitions, ties)."""
+    _typed_queries_match("cpu", range(0, 150), tmp_path)
+
+
+@pytest.mark.gpu
+def test_typed_random_queries_on_the_gpu_backend(tmp_path):
+    """The same queries where every stage runs as kernels (this generator found the negative-modulo and
+    empty-partition Average defects of round 2)."""
+    _typed_queries_match("cuda:0", range(0, 150), tmp_path)
