@@ -164,9 +164,14 @@ class DynamicManagers:
             old = cons.partition_count
             follow = [cons]
             ok = True
+            special = (NodeType.Concat, NodeType.Zip, NodeType.Reverse, NodeType.SlidingWindow)
             for n in follow:
                 for par in n.parents:
                     pop = next(o for c, o in par.children if c is n)
+                    phead = par.members[0].type if par.type == NodeType.Super else par.type
+                    if phead in special:
+                        ok = False                                    # these read neighbouring partitions by planned position
+                        continue
                     if xp(par, n, pop):
                         continue                                      # cross product: any widths connect
                     if par.partition_count == old:

@@ -259,6 +259,10 @@ def test_cluster_runtime_range_distributor(tmp_path):
     parts = store.open_table(uri).partitions
     assert [x for p in parts for x in p] == sorted(data)          # globally sorted across the NEW partitions
     assert sum(1 for p in parts if p) >= 3
+    # operators that address their neighbours' partitions by planned position (Reverse, Zip, SlidingWindow,
+    # Concat) pin the width of the stage below them: no resize there, and the result stays right
+    assert list(ctx.from_enumerable(data, 3).order_by(lambda x: x).reverse()) == sorted(data, reverse=True)
+    assert ctx.last_cluster_status["dynamic"]["resized"] == 0
 
 
 def test_cluster_aggregation_tree_for_decomposed_group_by(tmp_path):

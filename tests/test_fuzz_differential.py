@@ -60,6 +60,14 @@ def test_cluster_mode_matches_oracle_on_random_queries(tmp_path):
             assert _norm(got[1], got[0]) == _norm(want[1], want[0]), f"{make.__name__} seed {seed}"
             checked += 1
     assert checked >= 5
+    from fuzz_columnar import build_columnar
+    for seed in (44, 93, 7):                                 # 44 / 93: a resized sort stage under Reverse / Concat (fixed in round 2)
+        ctx = DryadLinqContext(3, platform=PlatformKind.LOCAL_CLUSTER, work_dir=str(tmp_path / f"typed{seed}"))
+        ctx.job_max_nodes = 2
+        ctx.dynamic_opt_level, ctx.aggregation_tree_fan_in, ctx.dynamic_data_per_vertex = 31, 2, 2000
+        got = _eval(build_columnar, seed, ctx)
+        want = _eval(build_columnar, seed, DryadLinqContext(3, local_debug=True))
+        assert _norm_typed(got[1], got[0]) == _norm_typed(want[1], want[0]), f"typed seed {seed}"
 
 
 def _plain(v):
