@@ -50,6 +50,17 @@ class JobStatus(str, Enum):
         "NotSubmitted", "Waiting", "Running", "Success", "Failure", "Cancelled")
 
 
+def _vertex_error(text: str) -> DryadLinqException:
+    """The error a job ended with.  A vertex that failed with one of the API's own errors reports it as text
+    (`...DryadLinqException: [Code] message`) through the graph manager — possibly from another process or
+    rank; the client raises it again with the same code, as the in-process executor does."""
+    import re
+    m = re.search(r"DryadLinqException: \[(\w+)\] ?(.*)", text, re.S)
+    if m and isinstance(getattr(ErrorCode, m.group(1), None), int) and m.group(1) != "DidNotCompleteSuccessfully":
+        return DryadLinqException(getattr(ErrorCode, m.group(1)), m.group(2).strip() or text)
+    return DryadLinqException(ErrorCode.DidNotCompleteSuccessfully, text)
+
+
 class Table:
     """A materialised partitioned dataset (in memory and/or a partfile on disk)."""
 
@@ -536,6 +547,11 @@ class DryadLinqContext:
             job.status = JobStatus.Success
         except BaseException as ex:  # noqa: BLE001
             job.status = JobStatus.Cancelled if job._cancel.is_set() else JobStatus.Failure
+            if isinstance(ex, DryadLinqException) and ex.error_code == ErrorCode.DidNotCompleteSuccessfully:
+                inner = _vertex_error(ex.message)
+                if inner.error_code != ErrorCode.DidNotCompleteSuccessfully:
+                    job.error = inner                 # the API's own error (empty-sequence aggregate, user function, ...) keeps its code
+                    raise inner from ex
             job.error = ex
             raise
 
@@ -565,13 +581,7 @@ class DryadLinqContext:
         self.last_cluster_status = rec
         if st != JobStatus.Success:
             text = sub.error_text() or "job failed"
-            # a vertex that failed with one of the API's own errors (empty-sequence aggregate, user function
-            # failure, ...) keeps its error code on the client side, as in the in-process executor
-            import re
-            m = re.search(r"DryadLinqException: \[(\w+)\] ?(.*)", text, re.S)
-            if m and isinstance(getattr(ErrorCode, m.group(1), None), int) and m.group(1) != "DidNotCompleteSuccessfully":
-                raise DryadLinqException(getattr(ErrorCode, m.group(1)), m.group(2).strip() or text)
-            raise DryadLinqException(ErrorCode.DidNotCompleteSuccessfully, text)
+            raise _vertex_error(text)
         tables: Dict[int, Table] = {}
         for r in roots:
             t = rec["tables"][str(r.expr.id)]
