@@ -315,9 +315,27 @@ class SpmdExecutor(JobExecutor):
                 rep.vertex_event(node, mine, version, "completed", seconds=time.perf_counter() - t0)
 
     def _participate_only(self, node):
-        """Ranks without a vertex in a single-partition stage still take part in its gathers."""
+        """Ranks without a vertex in a single-partition stage still take part in its collectives: this
+        mirrors, edge by edge, what rank 0 does in `_spmd_inputs` (same agreement points, same
+        collectives in the same order), so no rank waits in a collective the others never enter."""
         for child, op in node.children:
-            if child.partition_count == self.world:
+            cpc = child.partition_count
+            if op == ConnOp.CrossProduct:
+                ports = self.out[child.uid][self.rank] if cpc == self.world else None
+                if ports is not None and len(ports) == 1 and getattr(ports[0], "_exchanged", False):
+                    continue
+                if cpc == 1 and _tail(child).type == NodeType.Tee and _tail(child).params.get("replicate") \
+                        and self._all_columnar([], child.schema):
+                    self._allgather_batches(None, child.schema, False)
+                    continue
+                recs = [self.backend.to_records(p) for p in ports] if ports is not None else None
+                everyone: List = [None] * self.world
+                self._sync()
+                dist.all_gather_object(everyone, recs)
+                self.object_collectives += 1
+            elif cpc == node.partition_count:
+                continue
+            elif cpc == self.world:
                 self._gather_to_zero(child)
 
     # ---- edges -----------------------------------------------------------------------------------
@@ -504,6 +522,26 @@ class SpmdExecutor(JobExecutor):
                 halo_r = list(seg[-take:]) + halo_r if take > 0 and seg else halo_r
                 s -= 1
             return [[own], [halo_r if self.rank > 0 else []]]
+        if head.type == NodeType.Reverse and node.partition_count == self.world and node.children[0][0].partition_count == self.world:
+            # partition i of the result is partition world-1-i of the input, reversed locally by the vertex
+            # (DryadLinqQueryGen.cs:2731-2810): a permutation of whole partitions between ranks
+            parts = self._gather_all(node.children[0][0])
+            return [[parts[self.world - 1 - self.rank]]] + [[self.out[c.uid][i][0]] for c, _ in node.children[1:]]
+        if head.type == NodeType.Concat and node.partition_count == self.world:
+            # partition i of the result is one whole partition of one child, by position
+            acc = 0
+            picked = None
+            for child, _ in node.children:
+                parts = self._gather_all(child)
+                if picked is None and i < acc + child.partition_count:
+                    picked = parts[i - acc]
+                acc += child.partition_count
+            return [[picked if picked is not None else []]]
+        if head.type == NodeType.Zip and node.partition_count == self.world and len(node.children) == 2 \
+                and node.children[0][0].partition_count == self.world:
+            got = self._zip_inputs(node)
+            if got is not None:
+                return got
         for child, op in node.children:
             cpc = child.partition_count
             if op == ConnOp.CrossProduct:
@@ -542,6 +580,54 @@ class SpmdExecutor(JobExecutor):
             else:
                 raise DryadLinqException(ErrorCode.Internal, "unsupported SPMD edge")
         return ins
+
+    def _gather_all(self, child) -> List:
+        """Every partition of `child` on every rank (collective): tensors when the stage is columnar on all
+        ranks, records otherwise.  For the operators that move WHOLE partitions by position (Reverse, Concat)."""
+        cpc = child.partition_count
+        own = self.out[child.uid][self.rank][0] if cpc == self.world else (self.out[child.uid][0][0] if self.rank == 0 else None)
+        if self._all_columnar([own], child.schema):
+            parts = self._allgather_batches(own, child.schema, getattr(own, "tuple_like", False) if own is not None else False)
+            return parts if cpc == self.world else [parts[0]]
+        recs = list(self.backend.to_records(own)) if own is not None else None
+        box: List = [None] * self.world
+        self._sync()
+        dist.all_gather_object(box, recs)
+        self.object_collectives += 1
+        return [b if b is not None else [] for b in box] if cpc == self.world else [box[0] or []]
+
+    def _zip_inputs(self, node) -> Optional[List[List]]:
+        """Zip pairs the i-th record of the left side with the i-th record of the right side GLOBALLY, so
+        the right side is re-aligned to the left side's partition boundaries (DryadLinqQueryGen.cs:2626-2717).
+        Every rank learns every rank's (left, right) counts (one tiny all-gather).  When the boundaries
+        already coincide nothing moves; otherwise the right side is gathered — as tensors when it is
+        columnar on every rank, as records otherwise — and each rank keeps the slice under its left range."""
+        lchild, rchild = node.children[0][0], node.children[1][0]
+        left = self.out[lchild.uid][self.rank][0]
+        rpc = rchild.partition_count
+        right = self.out[rchild.uid][self.rank][0] if rpc == self.world else (self.out[rchild.uid][0][0] if self.rank == 0 else None)
+        dev = self.backend.device if getattr(self.backend, "name", "") == "gpu" else torch.device("cpu")
+        mine = torch.tensor([self.backend.count(left), self.backend.count(right) if right is not None else 0],
+                            dtype=torch.int64, device=dev)
+        everyone = [torch.zeros(2, dtype=torch.int64, device=dev) for _ in range(self.world)]
+        self._sync()
+        dist.all_gather(everyone, mine)
+        counts = torch.stack(everyone).cpu().tolist()
+        if rpc == self.world and all(a == b for a, b in counts):
+            return [[left], [right]]                         # same boundaries on both sides: purely local
+        start = sum(c[0] for c in counts[:self.rank])
+        need = counts[self.rank][0]
+        if self._all_columnar([right], rchild.schema):
+            parts = self._allgather_batches(right, rchild.schema, getattr(right, "tuple_like", False) if right is not None else False)
+            whole = ColumnBatch.concat(parts)
+            return [[left], [whole.slice(min(start, whole.n), min(start + need, whole.n))]]
+        recs = list(self.backend.to_records(right)) if right is not None else []
+        box: List = [None] * self.world
+        self._sync()
+        dist.all_gather_object(box, recs)
+        self.object_collectives += 1
+        flat = [x for b in box for x in (b or [])]
+        return [[self.backend.to_records(left)], [flat[start:start + need]]]
 
     # ---- fused stages ----------------------------------------------------------------------------
     def _run_fused(self, node):

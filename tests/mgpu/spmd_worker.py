@@ -41,6 +41,24 @@ def cpu_checks(rank, world):
     allp = [None] * world
     dist.all_gather_object(allp, win)
     assert sum(allp, []) == [sum(seq[j:j + 4]) for j in range(len(seq) - 3)], allp
+    # Zip pairs records by GLOBAL position: sides with different partition boundaries are re-aligned
+    left = list(range(60))
+    right = [x * x for x in range(100)]
+    zq = ctx.from_enumerable(left, world).where(lambda x: x % 7 != 0).zip(ctx.from_enumerable(right, world), lambda a, b: a * 100000 + b)
+    allp = [None] * world
+    dist.all_gather_object(allp, zq.partitions()[0])
+    kept = [x for x in left if x % 7 != 0]
+    assert sum(allp, []) == [a * 100000 + b for a, b in zip(kept, right)], allp
+    # Reverse permutes whole partitions between ranks (partition i <- partition world-1-i), then reverses locally
+    rv = ctx.from_enumerable(left, world).select(lambda x: x * 3).reverse().partitions()[0]
+    allp = [None] * world
+    dist.all_gather_object(allp, rv)
+    assert sum(allp, []) == [x * 3 for x in reversed(left)], allp
+    # a single-partition stage over a cross-product edge (range partition into ONE range): every rank takes part
+    one = ctx.from_enumerable(left, world).range_partition(lambda x: x, 1).select(lambda x: x + 1).partitions()
+    allp = [None] * world
+    dist.all_gather_object(allp, one[0] if one else [])
+    assert sorted(sum(allp, [])) == [x + 1 for x in left]
     # streamed rank-to-rank channel (pointwise FIFO edge): blocks flow while the producer still produces
     from dryad_b200.channel.pipe import PipeReader, PipeWriter
     if world >= 2 and rank < 2:
