@@ -158,6 +158,18 @@ int dh_writer_end_record(void* h) {
   return 0;
 }
 
+// Bulk path for variable-length records: n records back to back in `data`, record i = data[offs[i], offs[i+1]).
+// Same effect as dh_write_bytes + dh_writer_end_record per record (records never straddle blocks).
+int dh_write_records(void* h, const void* data, const int64_t* offs, int64_t n) {
+  const char* p = (const char*)data;
+  for (int64_t i = 0; i < n; ++i) {
+    dh_write_bytes(h, p + offs[i], offs[i + 1] - offs[i]);
+    int rc = dh_writer_end_record(h);
+    if (rc) return rc;
+  }
+  return 0;
+}
+
 // Bulk path: n fixed-width records already laid out row-major.
 int dh_writer_write_rows(void* h, const void* rows, int64_t n, int32_t width) {
   Writer* w = (Writer*)h;

@@ -109,8 +109,32 @@ def build_host(force: bool = False, verbose: bool = False) -> Path | None:
     return so
 
 
+def build_pyext(force: bool = False, verbose: bool = False) -> Path | None:
+    """CPython extension modules (csrc/py/*.cpp -> dryad_b200/_lib/<name>.so): code that has to handle
+    Python objects directly, such as the record codec.  Optional: without Python headers the pure-Python
+    implementations are used."""
+    import sysconfig
+    srcs = sorted((CSRC / "py").glob("*.cpp"))
+    inc = sysconfig.get_paths().get("include")
+    if not srcs or not inc or not (Path(inc) / "Python.h").exists():
+        return None
+    LIB.mkdir(parents=True, exist_ok=True)
+    cxx = os.environ.get("CXX", "g++")
+    last = None
+    for s in srcs:
+        so = LIB / ("_dryad_" + s.stem.replace("py", "", 1) + ".so")
+        if force or _newer(so, [s]):
+            _run([cxx, *CXX_FLAGS, "-shared", "-I", inc, str(s), "-o", str(so)])
+            if verbose:
+                print("compiled", s.name)
+        last = so
+    return last
+
+
 def build_all(force: bool = False, verbose: bool = False):
-    return build_kernels(force, verbose), build_host(force, verbose)
+    k, h = build_kernels(force, verbose), build_host(force, verbose)
+    build_pyext(force, verbose)
+    return k, h
 
 
 if __name__ == "__main__":

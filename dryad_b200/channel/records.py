@@ -164,10 +164,60 @@ def _encode_extra(obj, out: List[bytes]) -> None:
             encode(obj.value, out)
 
 
-def encode_record(obj: Any) -> bytes:
+def _encode_record_py(obj: Any) -> bytes:
     out: List[bytes] = []
     encode(obj, out)
     return b"".join(out)
+
+
+def _load_native():
+    """The CPython extension csrc/py/pyrecords.cpp (built into dryad_b200/_lib by `python -m dryad_b200.build`):
+    the same wire format at C speed for the common record shapes; everything else comes back to the
+    functions of this module value by value.  Absent (no Python headers at build time): pure Python."""
+    import importlib.util
+    import os
+    if os.environ.get("DRYAD_NATIVE_RECORDS", "1") == "0":
+        return None
+    path = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "_lib", "_dryad_records.so")
+    if not os.path.exists(path):
+        return None
+    try:
+        spec = importlib.util.spec_from_file_location("_dryad_records", path)
+        mod = importlib.util.module_from_spec(spec)
+        spec.loader.exec_module(mod)
+        mod.configure(Record, Pair, LineRecord, _encode_record_py, lambda buf, pos: decode(memoryview(buf), pos))
+        return mod
+    except Exception:  # noqa: BLE001  (an extension built for another interpreter: fall back)
+        return None
+
+
+def encode_record(obj: Any) -> bytes:
+    return _native.encode_one(obj) if _native is not None else _encode_record_py(obj)
+
+
+def encode_many(records) -> Tuple[bytes, bytes, int]:
+    """-> (data, offsets, n): the records back to back, `offsets` = int64[n + 1] as bytes."""
+    if _native is not None:
+        data, offs = _native.encode_many(records)
+        return data, offs, len(offs) // 8 - 1
+    parts = [_encode_record_py(r) for r in records]
+    pos, offs = 0, [0]
+    for b in parts:
+        pos += len(b)
+        offs.append(pos)
+    return b"".join(parts), struct.pack(f"<{len(offs)}q", *offs), len(parts)
+
+
+def decode_many(buf) -> List[Any]:
+    """Every record of a buffer that holds whole records back to back."""
+    if _native is not None:
+        return _native.decode_many(buf)
+    mv = memoryview(buf)
+    out, pos, n = [], 0, len(mv)
+    while pos < n:
+        obj, pos = decode(mv, pos)
+        out.append(obj)
+    return out
 
 
 def _dec_string(buf: memoryview, pos: int) -> Tuple[str, int]:
@@ -264,3 +314,7 @@ def decode(buf: memoryview, pos: int) -> Tuple[Any, int]:
         return read(bytes(buf[pos:pos + n])), pos + n
     from ..api.errors import DryadLinqException, ErrorCode
     raise DryadLinqException(ErrorCode.FailedToDeserialize, f"unknown record tag {t}")
+
+
+_native = _load_native()
+

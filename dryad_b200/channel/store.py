@@ -87,10 +87,14 @@ def write_records_file(path: str, part, compression=None) -> int:
             raise DryadLinqException(ErrorCode.FailedToCreateStream, f"cannot create {path}")
         try:
             recs = part.to_records() if hasattr(part, "to_records") else part
-            for rec in recs:
-                b = R.encode_record(rec)
-                lib.dh_write_bytes(w, b, len(b))
-                rc = lib.dh_writer_end_record(w)
+            it = iter(recs)
+            while True:                               # encode and hand over 64 K records at a time
+                import itertools
+                chunk = list(itertools.islice(it, 65536))
+                if not chunk:
+                    break
+                data, offs, n = R.encode_many(chunk)
+                rc = lib.dh_write_records(w, data, offs, n)
                 if rc:
                     raise DryadLinqException(ErrorCode.WriteFileError, f"write failed ({rc})")
         except BaseException:
@@ -154,21 +158,7 @@ def _pf_write_table(uri: str, parts: Sequence[Sequence], schema=None, compressio
             final = _part_path(base, i)
             tmp = final + ".v0.tmp"
             tmp_paths.append((tmp, final))
-            w = lib.dh_writer_open(tmp.encode(), comp, 0)
-            if not w:
-                raise DryadLinqException(ErrorCode.FailedToCreateStream, f"cannot create {tmp}")
-            recs = part.to_records() if hasattr(part, "to_records") else part
-            for rec in recs:
-                b = R.encode_record(rec)
-                lib.dh_write_bytes(w, b, len(b))
-                rc = lib.dh_writer_end_record(w)
-                if rc:
-                    raise DryadLinqException(ErrorCode.WriteFileError, f"write failed ({rc})")
-            raw, stored, nrec = C.c_int64(), C.c_int64(), C.c_int64()
-            rc = lib.dh_writer_close(w, C.byref(raw), C.byref(stored), C.byref(nrec))
-            if rc:
-                raise DryadLinqException(ErrorCode.WriteFileError, f"close failed ({rc})")
-            sizes[i] = stored.value
+            sizes[i] = write_records_file(tmp, part, comp)
         for tmp, final in tmp_paths:                      # commit the successful part versions
             if lib.dh_commit_part(tmp.encode(), final.encode()):
                 raise DryadLinqException(ErrorCode.WriteFileError, f"cannot commit {final}")
@@ -199,12 +189,7 @@ def read_partition_file(p: str) -> List:
                 raise DryadLinqException(ErrorCode.FailedToReadFrom, f"corrupt block stream {p} ({rc})")
             if avail.value == 0:
                 break
-            buf = memoryview(C.string_at(ptr, avail.value))   # whole records only (never straddle)
-            pos = 0
-            n = len(buf)
-            while pos < n:
-                obj, pos = R.decode(buf, pos)
-                out.append(obj)
+            out.extend(R.decode_many(C.string_at(ptr, avail.value)))   # whole records only (never straddle)
             lib.dh_reader_skip(r, avail.value)
     finally:
         lib.dh_reader_close(r)

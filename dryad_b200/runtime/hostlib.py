@@ -21,6 +21,7 @@ _d("dh_write_f64", None, [P, c_double])
 _d("dh_write_compact", None, [P, c_int32])
 _d("dh_write_string", None, [P, c_char_p, c_int32, c_int32])
 _d("dh_writer_end_record", c_int, [P])
+_d("dh_write_records", c_int, [P, c_char_p, c_char_p, c_int64])
 _d("dh_writer_write_rows", c_int, [P, P, c_int64, c_int32])
 _d("dh_writer_close", c_int, [P, C.POINTER(c_int64), C.POINTER(c_int64), C.POINTER(c_int64)])
 _d("dh_reader_open", P, [c_char_p])

@@ -20,6 +20,7 @@ void dh_write_f64(void* h, double v);
 void dh_write_compact(void* h, int32_t v);
 void dh_write_string(void* h, const char* utf8, int32_t nbytes, int32_t nchars);
 int dh_writer_end_record(void* h);
+int dh_write_records(void* h, const void* data, const int64_t* offs, int64_t n);   /* n records back to back, offs[n + 1] */
 int dh_writer_write_rows(void* h, const void* rows, int64_t n, int32_t width);
 int dh_writer_close(void* h, int64_t* raw_bytes, int64_t* stored_bytes, int64_t* records);
 void* dh_reader_open(const char* path);

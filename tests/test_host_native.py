@@ -466,3 +466,64 @@ def test_gm_splice_rewrites_a_running_graph():
     while (n := g2.next_ready(0.0)) is not None:
         ready.append(n[0])
     assert sorted(ready) == [1, 2, 3]
+
+
+def test_native_record_codec_is_byte_exact_with_the_python_codec():
+    """csrc/py/pyrecords.cpp against channel/records.py: same bytes out, same objects back, for the types it
+    handles itself and for the ones it hands back (big ints, Grouping, ForkTuple, GUID, DateTime, Decimal,
+    subclasses), at any nesting depth."""
+    import datetime
+    import decimal
+    import random
+    import uuid
+    from dryad_b200.api.types import ForkTuple, ForkValue, Grouping, LineRecord, Pair, Record
+    from dryad_b200.channel import records as R
+    if R._native is None:
+        pytest.skip("native record codec not built")
+    rng = random.Random(11)
+
+    def rand(depth=0):
+        k = rng.randrange(20 if depth < 3 else 9)
+        if k == 0: return None
+        if k == 1: return rng.random() < 0.5
+        if k == 2: return rng.choice([0, 1, -1, 127, 128, -(1 << 63), (1 << 63) - 1, rng.randrange(-10**12, 10**12)])
+        if k == 3: return rng.choice([0.0, -0.0, 1.5, float("inf"), 1e-300, rng.random()])
+        if k == 4: return rng.choice(["", "a", "héllo wörld", "x" * 200, "日本語", "\\u0000z"])
+        if k == 5: return rng.choice([b"", b"\\x00\\xff", bytes(range(256))])
+        if k == 6: return LineRecord("line " + str(rng.randrange(100)))
+        if k == 7: return 1 << rng.choice([64, 70, 200])                       # big integer: Python fallback
+        if k == 8: return rng.choice([uuid.UUID(int=rng.getrandbits(128)), datetime.datetime(2024, 2, 29, 12, 30, 5, 123456),
+                                      decimal.Decimal("12.3400"), ForkValue(3), ForkValue()])
+        if k in (9, 10): return tuple(rand(depth + 1) for _ in range(rng.randrange(4)))
+        if k in (11, 12): return [rand(depth + 1) for _ in range(rng.randrange(4))]
+        if k == 13: return {rng.choice(["a", 1, 2.5, ("t", 1)]): rand(depth + 1) for _ in range(rng.randrange(3))}
+        if k in (14, 15): return Record({f"f{i}": rand(depth + 1) for i in range(rng.randrange(1, 4))})
+        if k == 16: return Pair(rand(depth + 1), rand(depth + 1))
+        if k == 17:
+            g = Grouping(rand(depth + 1))
+            g.extend(rand(depth + 1) for _ in range(rng.randrange(3)))
+            return g
+        if k == 18: return ForkTuple(rand(depth + 1), None)
+        return Record({"nested": Record({"deep": [1, (2, "x")]})})
+
+    recs = [rand() for _ in range(3000)]
+    for r in recs:
+        assert R.encode_record(r) == R._encode_record_py(r), r
+    data, offs, n = R.encode_many(recs)
+    assert n == len(recs) and data == b"".join(R._encode_record_py(r) for r in recs)
+    back = R.decode_many(data)
+    mv, pos, want = memoryview(data), 0, []
+    while pos < len(mv):
+        o, pos = R.decode(mv, pos)
+        want.append(o)
+    assert len(back) == len(want) == len(recs)
+    for a, b in zip(back, want):
+        assert type(a) is type(b) and repr(a) == repr(b)
+    # truncated and malformed streams raise instead of reading out of bounds
+    for cut in (1, 5, len(data) // 2, len(data) - 1):
+        try:
+            R.decode_many(data[:cut])
+        except Exception:  # noqa: BLE001
+            pass
+    with pytest.raises(Exception):
+        R.decode_many(bytes([7, 0xFF, 0xFF, 0xFF, 0xFF]))                          # a tuple that claims 2^31 items
