@@ -57,20 +57,21 @@ class VertexCommand:
             a = [C.c_int() for _ in range(5)]
             lib.vc_get_header(h, *[C.byref(x) for x in a])
             vc = VertexCommand(a[0].value, a[1].value, a[2].value, state=a[3].value, exit_code=a[4].value)
-            buf = C.create_string_buffer(8192)
+            cap = max(8192, len(data) + 16)            # no field is longer than the block it came in
+            buf = C.create_string_buffer(cap)
             for i in range(lib.vc_count(h, 0)):
-                lib.vc_get_item(h, 0, i, buf, 8192)
+                lib.vc_get_item(h, 0, i, buf, cap)
                 vc.args.append(buf.value.decode())
             for i in range(lib.vc_count(h, 1)):
-                n = lib.vc_get_item(h, 1, i, buf, 8192)
+                n = lib.vc_get_item(h, 1, i, buf, cap)
                 vc.inputs.append((buf.value.decode(), n))
             for i in range(lib.vc_count(h, 2)):
-                n = lib.vc_get_item(h, 2, i, buf, 8192)
+                n = lib.vc_get_item(h, 2, i, buf, cap)
                 vc.outputs.append((buf.value.decode(), n))
             for i in range(lib.vc_count(h, 3)):
-                n = lib.vc_get_item(h, 3, i, buf, 8192)
+                n = lib.vc_get_item(h, 3, i, buf, cap)
                 vc.channel_status.append((n, int(buf.value.decode() or 0)))
-            lib.vc_get_item(h, 4, 0, buf, 8192)
+            lib.vc_get_item(h, 4, 0, buf, cap)
             vc.message = buf.value.decode()
             return vc
         finally:

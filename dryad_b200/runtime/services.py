@@ -50,12 +50,19 @@ class Mailbox:
 
     def block_on_status(self, key: str, last_seen: int = 0, timeout: float = 1.0) -> Optional[Tuple[int, str, bytes]]:
         st = C.create_string_buffer(256)
-        buf = C.create_string_buffer(1 << 16)
+        cap = 1 << 16
+        buf = C.create_string_buffer(cap)
         n = C.c_int64()
-        v = self.lib.mbox_block_on_status(self.h, key.encode(), last_seen, timeout, st, 256, buf, 1 << 16, C.byref(n))
+        v = self.lib.mbox_block_on_status(self.h, key.encode(), last_seen, timeout, st, 256, buf, cap, C.byref(n))
         if v == 0:
             return None
-        return v, st.value.decode(), buf.raw[:min(n.value, 1 << 16)]
+        while n.value > cap:                           # a value larger than the buffer: read it again, whole
+            cap = int(n.value) + 1024
+            buf = C.create_string_buffer(cap)
+            v = self.lib.mbox_block_on_status(self.h, key.encode(), max(0, last_seen), 0.0, st, 256, buf, cap, C.byref(n))
+            if v == 0:
+                return None
+        return v, st.value.decode(), buf.raw[:n.value]
 
     def close(self):
         if self.h:

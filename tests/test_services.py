@@ -98,3 +98,20 @@ def test_multi_port_vertex_reader_and_writer(tmp_path):
     assert port_order(8, True, 5) == list(range(8))
     shuffled = VertexReader(uris[:3], keep_port_order=False, seed=5)
     assert sorted(shuffled.order) == [0, 1, 2] and list(shuffled) == [1, 2, 3]
+
+
+def test_commands_and_mailbox_values_have_no_size_limit():
+    """A start command with thousands of input channels (or a long substitution map) travels whole."""
+    from dryad_b200.runtime.command import CMD_START, VertexCommand
+    from dryad_b200.runtime.services import Mailbox
+    m = Mailbox()
+    big = VertexCommand(CMD_START, 7, 3, args=["name", "0", "5", "subst=" + "x" * 100000],
+                        inputs=[(f"chan://{i}/{i}/0", i) for i in range(5000)])
+    data = big.serialize()
+    assert len(data) > (1 << 16)
+    m.set("cmd", "start", data)
+    v, st, got = m.block_on_status("cmd", 0, 1.0)
+    assert got == data and st == "start"
+    back = VertexCommand.parse(got)
+    assert back.args[3] == big.args[3] and len(back.inputs) == 5000 and back.inputs[4999] == ("chan://4999/4999/0", 4999)
+    m.close()
