@@ -412,7 +412,6 @@ class VertexHost:
         return res
 
     def _is_fifo_edge(self, child, parent) -> bool:
-        from ..plan.qnodes import ConnOp
         op = next((o for c, o in parent.children if c is child), None)
         return (getattr(child.channel_type, "value", "") == "MemoryFIFO" and op is not None
                 and not self.ex.edge_is_cross_product(parent, child, op) and child.partition_count == parent.partition_count)
