@@ -397,8 +397,8 @@ class VertexHost:
                     res["part_file"] = [tmp_v, final, size]
             res["ok"] = True
         except BaseException as ex_:  # noqa: BLE001  (vertex code is user code; SystemExit must pass)
-            if isinstance(ex_, (SystemExit, KeyboardInterrupt)):
-                raise
+            if isinstance(ex_, (SystemExit, KeyboardInterrupt)) or getattr(self, "raise_errors", False):
+                raise                                              # single-vertex replay under a debugger
             for name in run.fifo_out:
                 abort_fifo(name)                                   # the consumers of the streamed edges fail fast
             res["message"] = "".join(traceback.format_exception_only(type(ex_), ex_)).strip()[:3000]

@@ -92,6 +92,7 @@ class JobManager:
         self.out_bytes: Dict[Tuple[int, int], int] = {}                       # (stage uid, part) -> channel bytes written
         self.stage_of_uid = {n.uid: st for st, n in self.nodes.items()}
         self.part_files: Dict[Tuple[int, int], Tuple[str, str, int]] = {}     # root (uid, part) -> (tmp, final, size)
+        self.sent: Dict[Tuple[int, int], bytes] = {}                          # (gm vertex, version) -> start command as sent
         self.done = threading.Event()
         self.ok = False
         self.error = ""
@@ -260,6 +261,8 @@ class JobManager:
             bad = r["bad"]
             self.reporter.vertex_event(node, part, version, "failed", error=r["message"], computer=h.index)
             rc = self.gm.failed(v, version, r["message"], bad_input=bad)
+            if rc == 1 or self.ctx.compile_for_vertex_debugging:
+                self._dump_restart(node, part, v, version, r["message"])
             if rc == 2 and bad >= 0:
                 prod = self.ex._gm_inputs[v][bad]
                 self.versions.pop(prod, None)
@@ -268,6 +271,23 @@ class JobManager:
                 self.error = r["message"]
                 if rc != 1:
                     self._finish(False, r["message"])
+
+    def _dump_restart(self, node, part: int, v: int, version: int, error: str) -> None:
+        """The start command of a finally-failed vertex, as it was sent (DumpRestartCommand,
+        dvertexpncontrol.h:72): its inputs are channel files of this job directory, so
+        `python -m dryad_b200.tools.rerun <job dir> <stage>.<partition>` can run the vertex alone."""
+        wire = self.sent.get((v, version))
+        if wire is None:
+            return
+        try:
+            d = os.path.join(self.job_dir, "restart")
+            os.makedirs(d, exist_ok=True)
+            with open(os.path.join(d, f"vertex-{node.uid}-{part}.cmd"), "wb") as f:
+                f.write(wire)
+            with open(os.path.join(d, f"vertex-{node.uid}-{part}.error.txt"), "w") as f:
+                f.write(error)
+        except OSError:
+            pass                                           # diagnostics must never mask the failure
 
     def _on_exit(self, h: _Host) -> None:
         code = h.proc.poll() if h.proc is not None else None
@@ -380,7 +400,10 @@ class JobManager:
             cmd = VertexCommand(CMD_START, node.uid, version, args=args, inputs=inputs,
                                 outputs=[(f"chan://{node.uid}/{part}/{version}", 0)])
             h.busy = (list(attempts), time.perf_counter())
-            self._mbox(h.name).set("cmd", "start", cmd.serialize())
+            wire = cmd.serialize()
+            for mv, mver in attempts:
+                self.sent[(mv, mver)] = wire
+            self._mbox(h.name).set("cmd", "start", wire)
             for mv, mver in attempts:
                 mn, mp = self._vertex(mv)
                 self.reporter.vertex_event(mn, mp, mver, "starting", computer=h.index)

@@ -476,3 +476,33 @@ def test_cluster_job_package_references_stored_tables(tmp_path):
     assert ctx.from_store(uri).select(lambda x: x % 7).sum() == sum(x % 7 for x in range(50000))
     pkg3 = os.path.join(str(tmp_path), "ClusterJobs", "3", "job.pkl")
     assert os.path.getsize(pkg3) < 100_000
+
+
+def test_cluster_failed_vertex_can_be_rerun_alone(tmp_path):
+    """A finally-failed vertex of a cluster job leaves its start command; the job directory has the vertex
+    code (package) and its inputs (channel files), so the vertex replays alone, in one process
+    (LocalDebuggingAndProfiling.cs, DumpRestartCommand)."""
+    import subprocess
+    import sys
+    from dryad_b200.tools import rerun
+    flag = str(tmp_path / "fixed")
+
+    def inject(node, part, version):
+        if "GroupBy" in node.name and "Merge" in node.name and part == 1 and not os.path.exists(flag):
+            raise ValueError("bug in the user's function")
+
+    ctx = _ctx(tmp_path, n=3, hosts=2, fault_injector=inject, max_failures_per_vertex=2)
+    with pytest.raises(DryadLinqException):
+        ctx.from_enumerable(range(300), 3).group_by(lambda x: x % 6).select(lambda g: (g.key, g.count())).to_list()
+    job_dir = os.path.join(str(tmp_path), "ClusterJobs", "1")
+    found = rerun.list_restarts(job_dir)
+    assert len(found) == 1 and found[0]["partition"] == 1 and found[0]["inputs"]
+    tag = f"{found[0]['stage']}.1"
+    res = rerun.replay_cluster(job_dir, tag)
+    assert not res["ok"] and "bug in the user's function" in res["message"]          # reproduces the failure
+    open(flag, "w").close()                                                          # "fix the bug"
+    res = rerun.replay_cluster(job_dir, tag)
+    assert res["ok"] and res["n_in"] > 0 and res["n_out"] == 2                       # keys 1 and ... of 6 land in partition 1 of 3
+    p = subprocess.run([sys.executable, "-m", "dryad_b200.tools.rerun", job_dir, tag, "--run"], capture_output=True, text=True,
+                       cwd=os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+    assert p.returncode == 0 and "completed" in p.stdout, p.stdout + p.stderr
