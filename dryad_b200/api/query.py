@@ -317,14 +317,57 @@ class Query:
         fk = self._new("fork", schema=None, fn=Lam(mapper, None, 1), n=len(keys), per_partition=False)
         return KeyedMultiQuery(self.context, fk, keys)
 
-    def broadcast(self, n: Optional[int] = None) -> "Query":
-        """BroadCast: every one of n partitions receives the whole dataset
-        (DryadLinqExtension.cs:264-281)."""
+    def broadcast(self, n=None) -> "Query":
+        """BroadCast: every one of n partitions receives the whole dataset; `n` may also be a
+        destination dataset, whose partition count is used (DryadLinqExtension.cs:264-281)."""
+        if isinstance(n, Query):
+            return n.apply_per_partition(lambda x, y: y, self, is_first_only=True)
         return self._new("broadcast", schema=self.schema, count=n)
 
-    def do_while(self, body: Callable[["Query"], "Query"], cond: Callable[["Query", "Query"], "Query"]) -> "Query":
+    # ---- the user-library operators of the reference (LinqToDryad/DryadLinqExtension.cs:152-300) --------
+    def map_reduce(self, mapper, key, reducer) -> "Query":
+        """The standard MapReduce: SelectMany(mapper).GroupBy(key, reducer) (DryadLinqExtension.cs:166-174)."""
+        return self.select_many(mapper).group_by(key, None, reducer)
+
+    def cross_product(self, other: "Query", fn) -> "Query":
+        """fn over every pair of the two datasets: `other` is broadcast to every partition of self
+        (DryadLinqExtension.cs:187-193, DryadLinqHelper.Cross)."""
+        return self.apply_per_partition(lambda xs, ys: [fn(x, y) for x in xs for y in ys], other, is_first_only=True)
+
+    def check_order_by(self, key, comparer=None, descending: bool = False) -> "Query":
+        """Pass-through that fails the job when a partition is not ordered by `key`
+        (DryadLinqExtension.cs:293-300, DryadLinqHelper.CheckSort)."""
+        kf = key.fn if isinstance(key, Lam) else key
+        import functools
+
+        def check(xs):
+            prev, have = None, False
+            for x in xs:
+                k = kf(x)
+                if have:
+                    c = comparer(prev, k) if comparer is not None else (-1 if prev < k else (1 if k < prev else 0))
+                    if (c > 0 and not descending) or (c < 0 and descending):
+                        raise DryadLinqException(ErrorCode.FailureInUserApplyFunction,
+                                                 f"partition is not ordered: {prev!r} before {k!r}")
+                prev, have = k, True
+                yield x
+        functools.update_wrapper(check, kf) if hasattr(kf, "__name__") else None
+        return self.apply_per_partition(lambda xs: list(check(xs)))
+
+    def do_while(self, body: Callable[["Query"], "Query"], cond: Callable[["Query", "Query"], "Query"], count: int = 1) -> "Query":
         """Client-side loop (DryadLinqQueryable.cs:1280-1306): each iteration submits body and
-        cond as one job; cond must produce a single bool."""
+        cond as one job; cond must produce a single bool.  `count` unrolls the body that many times per
+        job (DryadLinqExtension.cs:204-231); 0 returns the source."""
+        if count < 0:
+            raise ValueError("count")
+        if count == 0:
+            return self
+        inner = body
+        if count > 1:
+            def body(q, _inner=inner, _n=count):     # noqa: F811  (the unrolled body)
+                for _ in range(_n):
+                    q = _inner(q)
+                return q
         cur = self
         while True:
             nxt = body(cur)
@@ -461,6 +504,8 @@ class Query:
     Count, LongCount, Sum, Min, Max, Average, Any, All, Contains = count, count, sum, min, max, average, any, all, contains
     First, FirstOrDefault, Last, LastOrDefault, Single, SingleOrDefault = first, first_or_default, last, last_or_default, single, single_or_default
     Aggregate, SequenceEqual, ToStore, Submit, SubmitAndWait, DoWhile, BroadCast = aggregate, sequence_equal, to_store, submit, submit_and_wait, do_while, broadcast
+    MapReduce, CrossProduct, CheckOrderBy, ApplyWithPartitionIndex = map_reduce, cross_product, check_order_by, apply_with_partition_index
+    LongCountAsQuery, SequenceEqualAsQuery = long_count_as_query, sequence_equal_as_query
     CountAsQuery, SumAsQuery, MinAsQuery, MaxAsQuery, AverageAsQuery = count_as_query, sum_as_query, min_as_query, max_as_query, average_as_query
     AnyAsQuery, AllAsQuery, ContainsAsQuery, FirstAsQuery, LastAsQuery, SingleAsQuery, AggregateAsQuery = any_as_query, all_as_query, contains_as_query, first_as_query, last_as_query, single_as_query, aggregate_as_query
 

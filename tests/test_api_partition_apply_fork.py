@@ -195,3 +195,30 @@ def test_misc_regressions():
                .select(lambda g: (g.key, g.count())))
     check_both(lambda c, s: s(["b", "a", "c", "a"]).distinct().order_by(lambda x: x), sort=False)
     check_both(lambda c, s: s([3, 1, 2]).group_by(lambda x: x % 2, comparer=None).select(lambda g: (g.key, g.max())))
+
+
+def test_user_library_operators_of_the_reference(tmp_path):
+    """MapReduce, CrossProduct, CheckOrderBy, BroadCast(destination), DoWhile with an unrolling count
+    (LinqToDryad/DryadLinqExtension.cs:152-300)."""
+    import dryad_b200 as D
+    from dryad_b200.api.errors import DryadLinqException
+    for ld in (True, False):
+        c = D.DryadLinqContext(3, local_debug=ld, work_dir=str(tmp_path))
+        a = c.from_enumerable(list(range(6)), 3)
+        b = c.from_enumerable(["x", "y"], 2)
+        assert sorted(a.CrossProduct(b, lambda i, s: f"{s}{i}")) == sorted(f"{s}{i}" for i in range(6) for s in "xy")
+        mr = c.from_enumerable(["a b", "b c c"], 2).MapReduce(lambda l: l.split(" "), lambda w: w, lambda k, ws: (k, len(list(ws))))
+        assert sorted(mr) == [("a", 1), ("b", 2), ("c", 2)]
+        assert sorted(c.from_enumerable([3, 1, 2], 1).order_by(lambda x: x).CheckOrderBy(lambda x: x)) == [1, 2, 3]
+        assert list(c.from_enumerable([3, 2, 1], 1).check_order_by(lambda x: x, descending=True)) == [3, 2, 1]
+        with pytest.raises(DryadLinqException) as e:
+            list(c.from_enumerable([3, 1, 2], 1).check_order_by(lambda x: x))
+        assert "not ordered" in str(e.value)
+        assert sorted(b.broadcast(a)) == sorted(["x", "y"] * (1 if ld else 3))      # one copy per partition of the destination
+        r = c.from_enumerable([1], 1).DoWhile(lambda q: q.select(lambda x: x * 2),
+                                              lambda o, n: n.select(lambda x: x < 60).any_as_query(lambda t: t), count=2)
+        assert list(r) == [64]                                                       # two doublings per job
+        assert list(c.from_enumerable([5], 1).do_while(lambda q: q, lambda o, n: n.any_as_query(), count=0)) == [5]
+        assert c.from_enumerable(range(10), 2).LongCountAsQuery().to_list() == [10]
+        assert c.from_enumerable([1, 2], 1).SequenceEqualAsQuery(c.from_enumerable([1, 2], 1)).to_list() == [True]
+        assert sorted(c.from_enumerable(range(4), 2).ApplyWithPartitionIndex(lambda xs, i: [(i, len(list(xs)))]))[0][1] >= 2
