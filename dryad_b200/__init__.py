@@ -3,8 +3,9 @@
 Public API (see dryad_b200.api): DryadLinqContext, Query operators, Decomposable / Associative
 protocols, record types; column expressions in dryad_b200.expr.
 """
-from .api.context import (CompressionScheme, DryadLinqContext, DryadLinqJobInfo, JobStatus, PlatformKind,
-                          QueryLoggingLevel, Table)
+from .api.context import (CompressionScheme, DryadLinqB200Cluster, DryadLinqCluster, DryadLinqContext, DryadLinqJobInfo,
+                          DryadLinqLocalCluster, JobStatus, PlatformKind, QueryLoggingLevel, Table)
+from .channel.provider import DataProvider
 from .api.decomposable import IAssociative, IDecomposable, associative, decomposable, resource
 from .api.errors import DryadLinqException, ErrorCategory, ErrorCode
 from .api.query import KeyedMultiQuery, MultiQuery, Query
@@ -15,7 +16,7 @@ from .expr import col, lit, where
 __version__ = "0.2.1b200"
 __all__ = [
     "DryadLinqContext", "DryadLinqJobInfo", "JobStatus", "PlatformKind", "QueryLoggingLevel", "CompressionScheme",
-    "Table", "IDecomposable", "IAssociative", "decomposable", "associative", "resource", "DryadLinqException",
+    "DryadLinqCluster", "DryadLinqLocalCluster", "DryadLinqB200Cluster", "DataProvider", "Table", "IDecomposable", "IAssociative", "decomposable", "associative", "resource", "DryadLinqException",
     "ErrorCode", "ErrorCategory", "Query", "MultiQuery", "KeyedMultiQuery", "Record", "Pair", "LineRecord",
     "RowKey", "ForkTuple", "ForkValue", "Grouping", "AggregateValue", "col", "lit", "where",
 ]

@@ -61,6 +61,53 @@ def _vertex_error(text: str) -> DryadLinqException:
     return DryadLinqException(ErrorCode.DidNotCompleteSuccessfully, text)
 
 
+class DryadLinqCluster:
+    """Where jobs run (the reference's DryadLinqCluster interface with its YARN and Azure implementations,
+    DryadLinqContext.cs:56-560): kind, head node, where the cluster keeps job-internal data, and the job
+    submission a context uses.  `DryadLinqContext(cluster=...)` takes its platform and sizes from it."""
+    kind: "PlatformKind"
+    head_node = "localhost"
+
+    def make_internal_cluster_uri(self, *path: str) -> str:
+        raise NotImplementedError
+
+    def configure(self, context: "DryadLinqContext") -> None:
+        """Apply the descriptor to a context that was created with it."""
+
+    MakeInternalClusterUri = make_internal_cluster_uri
+
+
+class DryadLinqLocalCluster(DryadLinqCluster):
+    """A graph-manager process with `hosts` vertex-host processes on this box (platform LOCAL_CLUSTER)."""
+
+    def __init__(self, hosts: int = 0, work_dir: Optional[str] = None, partitions: Optional[int] = None):
+        self.kind = PlatformKind.LOCAL_CLUSTER
+        self.hosts = int(hosts or (os.cpu_count() or 1))
+        self.work_dir = work_dir
+        self.partitions = partitions or self.hosts
+
+    def make_internal_cluster_uri(self, *path: str) -> str:
+        root = self.work_dir or os.path.join(tempfile.gettempdir(), "DRYADLINQ")
+        return "partfile://" + os.path.join(root, "internal", *path)
+
+    def configure(self, context):
+        context.job_max_nodes = self.hosts
+
+
+class DryadLinqB200Cluster(DryadLinqCluster):
+    """One NVSwitch domain: one process per GPU under torchrun (platform B200).  `gpus` is informative — the
+    number of ranks comes from the launcher (WORLD_SIZE)."""
+
+    def __init__(self, gpus: int = 8, head_node: str = "127.0.0.1", work_dir: Optional[str] = None):
+        self.kind = PlatformKind.B200
+        self.gpus, self.head_node, self.work_dir = gpus, head_node, work_dir
+        self.partitions = None
+
+    def make_internal_cluster_uri(self, *path: str) -> str:
+        root = self.work_dir or os.path.join(tempfile.gettempdir(), "DRYADLINQ")
+        return "partfile://" + os.path.join(root, "internal", *path)
+
+
 class Table:
     """A materialised partitioned dataset (in memory and/or a partfile on disk)."""
 
@@ -137,7 +184,13 @@ class DryadLinqContext:
 
     def __init__(self, num_partitions: Optional[int] = None, storage_scheme: str = "partfile", *,
                  platform: PlatformKind = PlatformKind.LOCAL, device: str = "cpu", cluster_name: str = "localhost",
-                 local_debug: bool = False, work_dir: Optional[str] = None):
+                 local_debug: bool = False, work_dir: Optional[str] = None, cluster: Optional["DryadLinqCluster"] = None):
+        if cluster is not None:                       # DryadLinqContext(DryadLinqCluster), DryadLinqContext.cs:672
+            platform = cluster.kind
+            cluster_name = getattr(cluster, "head_node", cluster_name)
+            work_dir = work_dir or getattr(cluster, "work_dir", None)
+            num_partitions = num_partitions or getattr(cluster, "partitions", None)
+        self.cluster = cluster
         self.platform = PlatformKind(platform)
         self.cluster_name = cluster_name
         self.storage_scheme = storage_scheme
@@ -208,6 +261,8 @@ class DryadLinqContext:
         self._frozen = False
         self._tables: Dict[int, Table] = {}
         self._job_counter = 0
+        if cluster is not None:
+            cluster.configure(self)
         self._lock = threading.RLock()
         self.last_job_stats: List[dict] = []
         self.last_plan = None
@@ -277,6 +332,19 @@ class DryadLinqContext:
         self._azure_accounts[account] = key
 
     RegisterAzureAccount = register_azure_account
+
+    def azure_account_key(self, account: str) -> Optional[str]:
+        """The key registered for a storage account, if any (DryadLinqContext.AzureAccountKey): what a
+        registered `azureblob://` / `wasb://` DataProvider would ask the context for."""
+        return getattr(self, "_azure_accounts", {}).get(account)
+
+    AzureAccountKey = azure_account_key
+
+    def client_version(self) -> str:
+        """Version of the client library (DryadLinqContext.ClientVersion, DryadLinqContext.cs:1125)."""
+        return self.version
+
+    ClientVersion = client_version
 
     def __enter__(self):
         return self

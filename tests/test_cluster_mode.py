@@ -506,3 +506,20 @@ def test_cluster_failed_vertex_can_be_rerun_alone(tmp_path):
     p = subprocess.run([sys.executable, "-m", "dryad_b200.tools.rerun", job_dir, tag, "--run"], capture_output=True, text=True,
                        cwd=os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
     assert p.returncode == 0 and "completed" in p.stdout, p.stdout + p.stderr
+
+
+def test_context_from_a_cluster_descriptor(tmp_path):
+    """DryadLinqContext(DryadLinqCluster) (DryadLinqContext.cs:672): platform, sizes and the place for
+    job-internal data come from the descriptor."""
+    import dryad_b200 as D
+    cl = D.DryadLinqLocalCluster(hosts=2, work_dir=str(tmp_path), partitions=3)
+    ctx = D.DryadLinqContext(cluster=cl)
+    assert ctx.platform == D.PlatformKind.LOCAL_CLUSTER and ctx.num_partitions == 3 and ctx.job_max_nodes == 2
+    assert cl.MakeInternalClusterUri("staging", "x.pt") == f"partfile://{tmp_path}/internal/staging/x.pt"
+    assert sorted(ctx.from_enumerable(range(30), 3).select(lambda x: x + 1)) == list(range(1, 31))
+    assert ctx.last_cluster_status["hosts"] == 2
+    assert ctx.ClientVersion() == ctx.version
+    ctx.RegisterAzureAccount("acct", "k3y")
+    assert ctx.AzureAccountKey("acct") == "k3y" and ctx.AzureAccountKey("other") is None
+    b = D.DryadLinqB200Cluster(gpus=8)
+    assert b.kind == D.PlatformKind.B200
