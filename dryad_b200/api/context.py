@@ -74,7 +74,8 @@ class DryadLinqCluster:
     def configure(self, context: "DryadLinqContext") -> None:
         """Apply the descriptor to a context that was created with it."""
 
-    MakeInternalClusterUri = make_internal_cluster_uri
+    def MakeInternalClusterUri(self, *path: str) -> str:      # noqa: N802  (the reference's spelling)
+        return self.make_internal_cluster_uri(*path)
 
 
 class DryadLinqLocalCluster(DryadLinqCluster):
