@@ -18,6 +18,91 @@ from ..api.types import ForkTuple, Grouping, LineRecord, Pair, Record
 
 T_NONE, T_FALSE, T_TRUE, T_INT, T_FLOAT, T_STR, T_BYTES, T_TUPLE, T_LIST, T_RECORD, T_PAIR, T_GROUP, T_LINE, T_BIGINT, T_DICT, T_FORK = range(16)
 T_GUID, T_DATETIME, T_DECIMAL, T_FORKVALUE, T_CUSTOM = 16, 17, 18, 19, 20
+T_ENUM, T_OBJECT = 21, 22
+
+# ---- automatic serialization of user types (the reference generates a serializer per record type from
+#      its public fields: DryadLinqCodeGen.cs:496-1479; rules and errors DryadLinqSerialization.cs,
+#      SerializationTests.cs: nesting, arrays, enums; circular types are an error) -----------------------
+_encoding_now: set = set()
+_PUBLIC: dict = {}
+
+
+def _type_name(cls) -> str:
+    return f"{cls.__module__}:{cls.__qualname__}"
+
+
+def _resolve_type(name: str):
+    import importlib
+    from ..api.errors import DryadLinqException, ErrorCode
+    mod, _, qual = name.partition(":")
+    if "<locals>" in qual:
+        raise DryadLinqException(ErrorCode.TypeRequiredToBePublic,
+                                 f"records of type {name} cannot be read back: the class is defined inside a function")
+    try:
+        obj = importlib.import_module(mod)
+        for part in qual.split("."):
+            obj = getattr(obj, part)
+        return obj
+    except Exception as ex:  # noqa: BLE001
+        raise DryadLinqException(ErrorCode.FailedToDeserialize, f"cannot find type {name}: {ex}") from ex
+
+
+def _fields_of(obj):
+    """Field name -> value of a user object: dataclass fields, else __dict__, else __slots__."""
+    import dataclasses
+    if dataclasses.is_dataclass(obj):
+        return {f.name: getattr(obj, f.name) for f in dataclasses.fields(obj)}
+    d = getattr(obj, "__dict__", None)
+    if d is not None:
+        return dict(d)
+    names = [n for c in type(obj).__mro__ for n in getattr(c, "__slots__", ())]
+    if names:
+        return {n: getattr(obj, n) for n in names if hasattr(obj, n)}
+    return None
+
+
+def _encode_object(obj, out: List[bytes]) -> bool:
+    import enum
+    import types
+    from ..api.errors import DryadLinqException, ErrorCode
+    cls = type(obj)
+    if isinstance(obj, enum.Enum):
+        out.append(bytes((T_ENUM,)) + enc_string(_type_name(cls)))
+        encode(obj.value, out)
+        return True
+    if isinstance(obj, (types.FunctionType, types.BuiltinFunctionType, types.MethodType, types.ModuleType, type)) \
+            or cls.__module__ == "builtins":
+        return False
+    fields = _fields_of(obj)
+    if fields is None:
+        return False
+    ok = _PUBLIC.get(cls)
+    if ok is None:
+        # another process must find the class again by name (the reference requires record types to be public):
+        # it has to be reachable as module.qualname, and that name has to lead back to this very class
+        ok = False
+        if "<locals>" not in cls.__qualname__ and cls.__module__ != "__main__":
+            try:
+                ok = _resolve_type(_type_name(cls)) is cls
+            except DryadLinqException:
+                ok = False
+        _PUBLIC[cls] = ok
+    if not ok:
+        raise DryadLinqException(ErrorCode.TypeRequiredToBePublic,
+                                 f"records of type {cls.__qualname__} cannot be serialised: define the class at module level "
+                                 "of an importable module")
+    if id(obj) in _encoding_now:
+        raise DryadLinqException(ErrorCode.CannotHandleCircularTypes,
+                                 f"records of type {cls.__name__} refer to themselves: circular types cannot be serialised")
+    _encoding_now.add(id(obj))
+    try:
+        out.append(bytes((T_OBJECT,)) + enc_string(_type_name(cls)) + compact(len(fields)))
+        for k, v in fields.items():
+            out.append(enc_string(k))
+            encode(v, out)
+    finally:
+        _encoding_now.discard(id(obj))
+    return True
 
 # ---- custom serializers ([CustomDryadLinqSerializer], LinqToDryad/Attributes.cs:37-275;
 #      IDryadLinqSerializer<T>.Read/Write, DryadLinqSerialization.cs:41-789) --------------------------
@@ -128,6 +213,8 @@ def encode(obj: Any, out: List[bytes]) -> None:
             encode(float(obj), out)
         elif isinstance(obj, np.bool_):
             encode(bool(obj), out)
+        elif _encode_object(obj, out):
+            pass
         else:
             from ..api.errors import DryadLinqException, ErrorCode
             raise DryadLinqException(ErrorCode.TypeNotSerializable,
@@ -304,6 +391,20 @@ def decode(buf: memoryview, pos: int) -> Tuple[Any, int]:
             return ForkValue(), pos
         v, pos = decode(buf, pos)
         return ForkValue(v), pos
+    if t == T_ENUM:
+        name, pos = _dec_string(buf, pos)
+        v, pos = decode(buf, pos)
+        return _resolve_type(name)(v), pos
+    if t == T_OBJECT:
+        name, pos = _dec_string(buf, pos)
+        n, pos = read_compact(buf, pos)
+        cls = _resolve_type(name)
+        obj = cls.__new__(cls)
+        for _ in range(n):
+            k, pos = _dec_string(buf, pos)
+            v, pos = decode(buf, pos)
+            object.__setattr__(obj, k, v)
+        return obj, pos
     if t == T_CUSTOM:
         name, pos = _dec_string(buf, pos)
         n, pos = read_compact(buf, pos)

@@ -300,6 +300,12 @@ def test_cluster_channels_gzip_and_custom_records(tmp_path):
     assert sorted(q2) == sorted((x % 4, x) for x in range(60))
     chans2 = os.path.join(str(tmp_path), "ClusterJobs", "2", "channels")
     assert any(f.endswith(".pkl") for f in os.listdir(chans2))
+    # a user class of an importable module is serialized automatically, field by field, in the block-stream format
+    import serialization_types as T
+    q3 = ctx.from_enumerable([T.Point(i, i * 0.5) for i in range(40)], 3).hash_partition(lambda p: p.x, 2).select(lambda p: T.Point(p.x + 1, p.y))
+    assert sorted(q3, key=lambda p: p.x) == [T.Point(i + 1, i * 0.5) for i in range(40)]
+    chans3 = os.path.join(str(tmp_path), "ClusterJobs", "3", "channels")
+    assert os.listdir(chans3) and not any(f.endswith(".pkl") for f in os.listdir(chans3))
 
 
 def test_cluster_subgraph_vertex_streams_over_fifos(tmp_path):
