@@ -192,6 +192,10 @@ class DryadLinqContext:
             work_dir = work_dir or getattr(cluster, "work_dir", None)
             num_partitions = num_partitions or getattr(cluster, "partitions", None)
         self.cluster = cluster
+        if PlatformKind(platform) == PlatformKind.LOCAL_CLUSTER and str(device) != "cpu":
+            raise DryadLinqException(ErrorCode.UnsupportedExecutionKind,
+                                     "LOCAL_CLUSTER runs CPU vertices in worker processes; GPU jobs run on one GPU "
+                                     "(platform LOCAL, device='cuda') or on all of them (platform B200 under torchrun)")
         self.platform = PlatformKind(platform)
         self.cluster_name = cluster_name
         self.storage_scheme = storage_scheme
