@@ -113,6 +113,8 @@ class JobManager:
         log = open(os.path.join(self.job_dir, "log", f"host-{h.name}.txt"), "wb")
         env = dict(os.environ)
         env["DRYAD_JOB_DIR"] = self.job_dir
+        root = os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+        env["PYTHONPATH"] = os.pathsep.join([root] + [p for p in env.get("PYTHONPATH", "").split(os.pathsep) if p and p != root])
         if "DRYAD_THREADS_PER_WORKER" not in self.ctx.job_environment_variables:
             # the hosts share this box: split its cores between them (DRYAD_THREADS_PER_WORKER, VertexEnv.cs:72-86)
             env["DRYAD_THREADS_PER_WORKER"] = str(max(1, (os.cpu_count() or 1) // self.nhosts))
@@ -308,7 +310,13 @@ class JobManager:
             del self.where[key]
         h.restarts += 1
         if h.restarts > self.max_host_restarts:
-            self.error = f"vertex host slot {h.index} died {h.restarts} times"
+            tail = ""
+            try:
+                with open(os.path.join(self.job_dir, "log", f"host-{h.name}.txt"), errors="replace") as f:
+                    tail = f.read()[-1500:]
+            except OSError:
+                pass
+            self.error = f"vertex host slot {h.index} died {h.restarts} times (last exit code {code}); its log ends with:\n{tail}"
             self._finish(False, self.error)
             return
         self._launch(h)

@@ -529,3 +529,19 @@ def test_context_from_a_cluster_descriptor(tmp_path):
     assert ctx.AzureAccountKey("acct") == "k3y" and ctx.AzureAccountKey("other") is None
     b = D.DryadLinqB200Cluster(gpus=8)
     assert b.kind == D.PlatformKind.B200
+
+
+def test_cluster_hosts_that_cannot_start_fail_the_job_with_their_log(tmp_path):
+    """A vertex host that dies again and again (here: a broken environment makes it exit at start) ends the
+    job with the tail of its log, instead of restarting forever."""
+    ctx = _ctx(tmp_path, n=2, hosts=1)
+    ctx.job_environment_variables["PYTHONPATH"] = ""            # the hosts still find the framework: the manager adds its own root
+
+    def inject(node, part, version):
+        os._exit(9)                                              # every attempt takes the host down
+
+    ctx.fault_injector = inject
+    ctx.max_failures_per_vertex = 50
+    with pytest.raises(DryadLinqException) as e:
+        ctx.from_enumerable(range(10), 2).select(lambda x: x).to_list()
+    assert "died" in str(e.value) and "exit code 9" in str(e.value)
