@@ -446,6 +446,7 @@ class JobManager:
         except Exception as ex:  # noqa: BLE001
             self._finish(False, f"output commit failed: {type(ex).__name__}: {ex}")
             return
+        self._remove_uncommitted()                       # part versions of duplicate attempts that lost
         self._finish(True, "", tables)
 
     def _finish(self, ok: bool, error: str, tables: Optional[dict] = None) -> None:
