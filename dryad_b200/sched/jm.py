@@ -526,8 +526,7 @@ class JobManager:
                 h.proc.wait(max(0.05, deadline - time.monotonic()))
             except subprocess.TimeoutExpired:
                 h.proc.kill()                                                 # the exact process we started
-        if not self.ok:
-            self._remove_uncommitted()                                        # a host may have written a part after the verdict
+        self._remove_uncommitted()                                            # a host may have written a part version after the verdict
         for t in self._watchers:                                              # nobody may post to a pump that is gone
             t.join(5.0)
         self.pump.close()
