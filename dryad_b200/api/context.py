@@ -447,6 +447,9 @@ class DryadLinqContext:
         or HBM).  Each partition is a zero-copy slice; the GPU backend uploads it on first use."""
         self._check_not_disposed()
         from ..runtime.columnar import ColumnBatch
+        import torch
+        if not isinstance(rows, torch.Tensor):
+            rows = torch.as_tensor(rows)      # a numpy [n, width] uint8 array: shared, not copied
         if self.world > 1:                    # SPMD: `rows` is THIS rank's partition
             parts: List[Any] = [None] * self.world
             parts[self.rank] = ColumnBatch.rows(rows, key_off, key_len)
