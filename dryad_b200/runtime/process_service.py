@@ -238,3 +238,33 @@ class MailboxClient:
                 pass
             self._conn = None
 
+
+def main(argv=None) -> int:
+    """Daemon main (ProcessService/Program.cs): serve the mailbox, process table and file server of one node
+    until SIGTERM / SIGINT.  Prints `DRYAD_PROCESS_SERVER_URI=<uri>` on stdout once it listens.
+
+        python -m dryad_b200.runtime.process_service --root DIR [--host 127.0.0.1] [--port 0]
+    """
+    import argparse
+    import signal
+    import sys
+    ap = argparse.ArgumentParser(prog="process_service")
+    ap.add_argument("--root", required=True, help="directory served by the file server; process logs go here")
+    ap.add_argument("--host", default="127.0.0.1")
+    ap.add_argument("--port", type=int, default=0)
+    a = ap.parse_args(argv)
+    svc = ProcessService(a.root, a.host, a.port)
+    stop = threading.Event()
+    signal.signal(signal.SIGTERM, lambda *_: stop.set())
+    signal.signal(signal.SIGINT, lambda *_: stop.set())
+    print(f"DRYAD_PROCESS_SERVER_URI={svc.uri}", flush=True)
+    try:
+        while not stop.wait(0.5):
+            pass
+    finally:
+        svc.close()
+    return 0
+
+
+if __name__ == "__main__":
+    raise SystemExit(main())

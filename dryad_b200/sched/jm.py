@@ -51,6 +51,27 @@ class _Host:
         self.vertices_run = 0
 
 
+class _Watcher:
+    """IProcessWatcher of the scheduler (ClusterInterface/Interfaces.cs): queued / matched transitions of every
+    vertex process go to the event log, so the schedule view shows how long a vertex waited for a computer."""
+
+    def __init__(self, jm):
+        self.jm = jm
+
+    def on_queued(self, proc):
+        self.jm.reporter._emit("schedule", process=proc.id, what=proc.command_line, state="queued",
+                               prefer=" ".join(map(str, proc.affinity.computers)) or None, weight=proc.affinity.weight or None)
+
+    def on_matched(self, proc, computer):
+        self.jm.reporter._emit("schedule", process=proc.id, what=proc.command_line, state="matched", computer=computer.index)
+
+    def on_created(self, proc): ...
+    def on_started(self, proc): ...
+
+    def on_exited(self, proc, state, exit_code, error):
+        self.jm.reporter._emit("schedule", process=proc.id, state="cancelled", error=error)
+
+
 class JobManager:
     def __init__(self, job_dir: str, workers: int = 0, max_host_restarts: int = 8, app=None):
         from ..runtime import jobpackage
@@ -101,6 +122,7 @@ class JobManager:
         self.stats: List[dict] = []
         self.messages = 0
         self._watchers: List[threading.Thread] = []
+        self._watcher = _Watcher(self)
         from .dynamic import DynamicManagers
         self.dyn = DynamicManagers(self)
         self.pump = MessagePump(self._on_message, threads=1)                  # ONE consumer: graph changes are serialised
@@ -345,7 +367,7 @@ class JobManager:
         self.pending[pid] = list(attempts)
         node, part = self._vertex(attempts[0][0])
         label = f"{node.name}#{node.uid}[{part}]" + (f" +{len(attempts) - 1}" if len(attempts) > 1 else "")
-        self.cluster.schedule_process(Process(pid, label, Affinity(prefer, sum(votes.values()), False)))
+        self.cluster.schedule_process(Process(pid, label, Affinity(prefer, sum(votes.values()), False), self._watcher))
         for v, version in attempts:
             n_, p_ = self._vertex(v)
             self.reporter.vertex_event(n_, p_, version, "created", prefer=prefer[0] if prefer else None,

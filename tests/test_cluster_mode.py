@@ -46,6 +46,8 @@ def test_cluster_queries_match_oracle(tmp_path):
     assert any(v["cache_hits"] > 0 for v in st["vertices"])
     job_dir = os.path.join(str(tmp_path), "ClusterJobs", "1")
     assert os.path.exists(os.path.join(job_dir, "calypso.log"))
+    log = open(os.path.join(job_dir, "calypso.log")).read()
+    assert "schedule," in log and "state=queued" in log and "state=matched" in log        # IProcessWatcher transitions
     assert any(f.endswith(".chan") for f in os.listdir(os.path.join(job_dir, "channels")))
 
 

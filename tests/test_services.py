@@ -115,3 +115,29 @@ def test_commands_and_mailbox_values_have_no_size_limit():
     back = VertexCommand.parse(got)
     assert back.args[3] == big.args[3] and len(back.inputs) == 5000 and back.inputs[4999] == ("chan://4999/4999/0", 4999)
     m.close()
+
+
+def test_process_service_daemon_main(tmp_path):
+    """The node daemon as its own process: a client sets and long-polls mailbox values and fetches a file
+    range over HTTP (ProcessService/Program.cs, HttpServer.cs)."""
+    import signal
+    import subprocess
+    import sys
+    from dryad_b200.runtime.process_service import MailboxClient
+    (tmp_path / "data.bin").write_bytes(bytes(range(200)))
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    p = subprocess.Popen([sys.executable, "-m", "dryad_b200.runtime.process_service", "--root", str(tmp_path)],
+                         stdout=subprocess.PIPE, text=True, cwd=root)
+    try:
+        line = p.stdout.readline().strip()
+        assert line.startswith("DRYAD_PROCESS_SERVER_URI=http://127.0.0.1:")
+        c = MailboxClient(line.split("=", 1)[1], "test")
+        assert c.get("proc1", "k", 0, 0.1) is None
+        c.set("proc1", "k", "running", b"payload")
+        v, st, data = c.get("proc1", "k", 0, 1.0)
+        assert (st, data) == ("running", b"payload") and v >= 1
+        assert c.fetch_file("data.bin", 10, 19) == bytes(range(10, 20))
+        c.close()
+    finally:
+        p.send_signal(signal.SIGTERM)
+        assert p.wait(10) == 0
