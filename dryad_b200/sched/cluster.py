@@ -102,3 +102,8 @@ class LocalCluster(ICluster):
 
     def local_path(self, computer: Computer, name: str, compression: str = "None") -> str:
         return f"file://{computer.directory}/{name}?c={compression}"
+
+    def remote_path(self, computer: Computer, name: str, file_server: str) -> str:
+        """Where ANOTHER computer reads `name` from: through the producing node's file server
+        (ClusterInterface/HttpScheduler.cs:65-91); `file_server` is that node's process-service URI."""
+        return f"{file_server.rstrip('/')}/file/{name.lstrip('/')}"
