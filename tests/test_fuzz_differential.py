@@ -61,6 +61,15 @@ def test_cluster_mode_matches_oracle_on_random_queries(tmp_path):
             checked += 1
     assert checked >= 5
     from fuzz_columnar import build_columnar
+    from fuzz_operators import build_operators
+    for seed in (0, 4, 6, 13, 21, 27):
+        ctx = DryadLinqContext(3, platform=PlatformKind.LOCAL_CLUSTER, work_dir=str(tmp_path / f"ops{seed}"))
+        ctx.job_max_nodes = 2
+        ctx.dynamic_opt_level, ctx.aggregation_tree_fan_in, ctx.dynamic_data_per_vertex = 31, 2, 500
+        ctx.use_memory_fifo = bool(seed % 2)
+        got = _eval(build_operators, seed, ctx)
+        want = _eval(build_operators, seed, DryadLinqContext(3, local_debug=True))
+        assert _norm_typed(got[1], got[0]) == _norm_typed(want[1], want[0]), f"operators seed {seed}"
     for seed in (44, 93, 7):                                 # 44 / 93: a resized sort stage under Reverse / Concat (fixed in round 2)
         ctx = DryadLinqContext(3, platform=PlatformKind.LOCAL_CLUSTER, work_dir=str(tmp_path / f"typed{seed}"))
         ctx.job_max_nodes = 2
@@ -94,6 +103,14 @@ def _typed_queries_match(device, seeds, tmp_path):
     for seed in seeds:
         got = _eval(build_columnar, seed, DryadLinqContext(3, device=device, work_dir=str(tmp_path)))
         want = _eval(build_columnar, seed, DryadLinqContext(3, local_debug=True))
+        assert _norm_typed(got[1], got[0]) == _norm_typed(want[1], want[0]), f"seed {seed}"
+
+
+def test_less_common_operators_match_the_oracle(tmp_path):
+    from fuzz_operators import build_operators
+    for seed in range(0, 200):
+        got = _eval(build_operators, seed, DryadLinqContext(3, work_dir=str(tmp_path)))
+        want = _eval(build_operators, seed, DryadLinqContext(3, local_debug=True))
         assert _norm_typed(got[1], got[0]) == _norm_typed(want[1], want[0]), f"seed {seed}"
 
 
