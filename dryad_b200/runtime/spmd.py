@@ -522,6 +522,11 @@ class SpmdExecutor(JobExecutor):
                 halo_r = list(seg[-take:]) + halo_r if take > 0 and seg else halo_r
                 s -= 1
             return [[own], [halo_r if self.rank > 0 else []]]
+        if head.type == NodeType.ForkBranch:
+            # branch k of a Fork reads output port k of the Fork vertex of the same partition
+            child = node.children[0][0]
+            if child.partition_count == node.partition_count:
+                return [[self.out[child.uid][i][head.params["index"]]]]
         if head.type == NodeType.Reverse and node.partition_count == self.world and node.children[0][0].partition_count == self.world:
             # partition i of the result is partition world-1-i of the input, reversed locally by the vertex
             # (DryadLinqQueryGen.cs:2731-2810): a permutation of whole partitions between ranks

@@ -48,7 +48,13 @@ class ControlPlane:
         self.device = device
         self.timeout = float(getattr(context, "spmd_control_timeout", 120.0))
         self.service = None
-        self._seen = {"cmd": 0}
+        # Commands are a SEQUENCE, one mailbox key per command ("cmd/1", "cmd/2", ...).  A mailbox key holds only
+        # its latest value, so a single "cmd" key loses a command when the manager posts two before a rank has
+        # polled — which it does at job boundaries (Terminate of job k, then the first Start of job k+1): the
+        # rank then ran job k+1's stages against job k's plan.  Every rank receives every command, so both
+        # sides count in lockstep.
+        self._posted = 0
+        self._received = 0
         self._status_seen = [0] * self.world
         uri: List[Optional[str]] = [None]
         if self.rank == 0:
@@ -80,8 +86,9 @@ class ControlPlane:
     def post_command(self, cmd: VertexCommand) -> None:
         """GM side: deliver one launch descriptor to every rank's mailbox."""
         data = cmd.serialize()
+        self._posted += 1
         for r in range(self.world):
-            self._mbox(r).set("cmd", "start" if cmd.command == CMD_START else "terminate", data)
+            self._mbox(r).set(f"cmd/{self._posted}", "start" if cmd.command == CMD_START else "terminate", data)
         self.commands_delivered += 1
 
     def next_command(self) -> VertexCommand:
@@ -92,16 +99,15 @@ class ControlPlane:
             if left <= 0:
                 raise RankLost(f"rank {self.rank}: no command from the graph manager for {self.timeout:.0f} s")
             poll = min(left, 5.0)
+            key = f"cmd/{self._received + 1}"
             if self._prefetched is not None:                  # delivered together with the last status report
                 got, self._prefetched = self._prefetched, None
             elif self.rank == 0:
-                got = self._mbox(0).block_on_status("cmd", self._seen["cmd"], poll)
+                got = self._mbox(0).block_on_status(key, 0, poll)
             else:
-                got = self._http_get(f"rank-{self.rank}", "cmd", self._seen["cmd"], poll)
-            if got and got[0] <= self._seen["cmd"]:
-                got = None
+                got = self._http_get(f"rank-{self.rank}", key, 0, poll)
             if got:
-                self._seen["cmd"] = got[0]
+                self._received += 1
                 cmd = VertexCommand.parse(got[2])
                 if cmd is None:
                     raise DryadLinqException(ErrorCode.Internal, "malformed launch descriptor")
@@ -117,7 +123,7 @@ class ControlPlane:
             # report and long-poll the next command in ONE exchange
             try:
                 self._prefetched = self._client().set(f"rank-{self.rank}", "status", "completed" if ok else "failed", data,
-                                                      wait="cmd", seen=self._seen["cmd"], wait_timeout=5.0, timeout=self.timeout)
+                                                      wait=f"cmd/{self._received + 1}", seen=0, wait_timeout=5.0, timeout=self.timeout)
             except ConnectionError as ex:
                 raise RankLost(str(ex)) from ex
 

@@ -11,6 +11,7 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, os.path.dirname(os.path.dirname(HERE)))
 sys.path.insert(0, os.path.dirname(HERE))
 from fuzz_columnar import build_columnar  # noqa: E402
+from fuzz_operators import build_operators  # noqa: E402
 from fuzz_queries import build, rand_pipeline  # noqa: E402
 from test_fuzz_differential import _norm_typed  # noqa: E402
 from dryad_b200.api.context import DryadLinqContext  # noqa: E402
@@ -39,7 +40,7 @@ def main():
     ctx.from_enumerable = lambda data, n=None: plain(data, 1 if n == 1 else world)
     bad = checked = unsupported = 0
     for seed in range(first, last):
-        for make in (build_columnar, rand_pipeline, build):
+        for make in (build_columnar, rand_pipeline, build, build_operators):
             got = ev(make, seed, ctx)
             box = [None] * world
             dist.all_gather_object(box, got)
