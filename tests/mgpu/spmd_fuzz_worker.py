@@ -39,7 +39,16 @@ def main():
     plain = ctx.from_enumerable
     ctx.from_enumerable = lambda data, n=None: plain(data, 1 if n == 1 else world)
     bad = checked = unsupported = 0
+    faults = os.environ.get("FUZZ_FAULTS") == "1"
+    state = {"seed": 0}
+    if faults:
+        # a transient failure on ONE rank in the first attempt of some stages: every rank must re-run the stage
+        def inject(node, r, version):
+            if version == 0 and (state["seed"] * 31 + node.uid * 7) % 4 == 0 and r == (state["seed"] + node.uid) % world:
+                raise RuntimeError(f"injected transient failure (seed {state['seed']}, stage {node.uid}, rank {r})")
+        ctx.fault_injector = inject
     for seed in range(first, last):
+        state["seed"] = seed
         for make in (build_columnar, rand_pipeline, build, build_operators):
             got = ev(make, seed, ctx)
             box = [None] * world

@@ -19,17 +19,19 @@ def test_spmd_host_backend_over_gloo(world):
     assert "checks passed" in p.stdout
 
 
-def test_spmd_random_queries_match_the_oracle():
+@pytest.mark.parametrize("faults", ["0", "1"])
+def test_spmd_random_queries_match_the_oracle(faults):
     """The SPMD executor on random pipelines (position-dependent operators, single-partition stages over
     cross-product edges, empty partitions): no rank may wait in a collective the others never enter, and
     the gathered result must equal LocalDebug's."""
+    env = dict(os.environ, FUZZ_FAULTS=faults)              # "1": a transient failure on one rank in some stages of every job
     last = None
     for attempt in range(2):                            # a busy rendezvous port is not a property of the executor
-        port = 29650 + (os.getpid() % 300) + 311 * attempt
+        port = 29650 + (os.getpid() % 300) + 311 * attempt + 7 * int(faults)
         cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node=2",
                "--master-addr", "127.0.0.1", "--master-port", str(port),
-               os.path.join(HERE, "mgpu", "spmd_fuzz_worker.py"), "0", "45"]
-        last = subprocess.run(cmd, capture_output=True, text=True, timeout=600)
+               os.path.join(HERE, "mgpu", "spmd_fuzz_worker.py"), "0", "45" if faults == "0" else "25"]
+        last = subprocess.run(cmd, capture_output=True, text=True, timeout=600, env=env)
         if "MISMATCH" in last.stdout:
             break                                       # a wrong result is never retried
         if last.returncode == 0:
