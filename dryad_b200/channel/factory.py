@@ -177,6 +177,14 @@ class VertexWriter:
             w.close()
 
 
+def ensure_fifo(name: str, depth: int = 32) -> None:
+    """Create a named FIFO before either end touches it, so that an abort by one end is seen by the other
+    even when it comes first."""
+    with _lock:
+        if name not in _fifos:
+            _fifos[name] = Fifo(0 if depth >= 4294967295 else depth)
+
+
 def drop_fifo(name: str, abort: bool = False) -> None:
     """Forget a named FIFO once both ends are done with it (or abort it: both ends fail fast)."""
     with _lock:

@@ -470,6 +470,9 @@ class VertexHost:
                     r.fifo_in[(child.uid, r.part)] = name
                     p.fifo_out.append(name)
                     names.append(name)
+        from ..channel.factory import ensure_fifo
+        for n in names:
+            ensure_fifo(n, 32)              # exists before any member runs: a producer that fails first can still abort it
         results: List[Optional[dict]] = [None] * len(runs)
 
         def work(i):

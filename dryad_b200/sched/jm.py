@@ -140,8 +140,10 @@ class JobManager:
         if "DRYAD_THREADS_PER_WORKER" not in self.ctx.job_environment_variables:
             # the hosts share this box: split its cores between them (DRYAD_THREADS_PER_WORKER, VertexEnv.cs:72-86)
             env["DRYAD_THREADS_PER_WORKER"] = str(max(1, (os.cpu_count() or 1) // self.nhosts))
+        # hosts live as long as the job: an idle host waits (another host may run a long vertex); it leaves when it
+        # is told to, or when the manager's mailbox is gone
         cmd = [sys.executable, "-m", "dryad_b200.runtime.vertex_host", "--service", self.service.uri, "--id", h.name,
-               "--job-dir", self.job_dir]
+               "--job-dir", self.job_dir, "--idle-timeout", "604800"]
         h.proc = subprocess.Popen(cmd, stdout=log, stderr=subprocess.STDOUT, env=env, cwd=self.job_dir)
         with self.service._lock:
             self.service.procs[h.name] = h.proc

@@ -547,3 +547,21 @@ def test_cluster_hosts_that_cannot_start_fail_the_job_with_their_log(tmp_path):
     with pytest.raises(DryadLinqException) as e:
         ctx.from_enumerable(range(10), 2).select(lambda x: x).to_list()
     assert "died" in str(e.value) and "exit code 9" in str(e.value)
+
+
+def test_cluster_subgraph_member_failing_before_it_writes_does_not_hang(tmp_path):
+    """Every producer of a gang fails before it touched its FIFO: the consumer must see the abort (the FIFOs
+    exist before any member runs) and the gang restarts."""
+    import time
+
+    def inject(node, part, version):
+        if node.name == "Merge" and version == 0:
+            raise RuntimeError("producer fails first")
+
+    ctx = _ctx(tmp_path, n=3, hosts=2, use_memory_fifo=True, broadcast_join_rows=0, fault_injector=inject)
+    t0 = time.time()
+    a = ctx.from_enumerable(range(60), 3)
+    b = ctx.from_enumerable(range(0, 120, 2), 3)
+    assert sorted(a.except_(b)) == [x for x in range(60) if x % 2 == 1]
+    assert time.time() - t0 < 60
+    assert ctx.last_cluster_status["counters"]["failures"] >= 3
