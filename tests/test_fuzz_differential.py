@@ -124,3 +124,33 @@ def test_typed_random_queries_on_the_gpu_backend(tmp_path):
     """The same queries where every stage runs as kernels (this generator found the negative-modulo and
     empty-partition Average defects of round 2)."""
     _typed_queries_match("cuda:0", range(0, 150), tmp_path)
+
+
+def test_cluster_mode_with_random_failures_matches_the_oracle(tmp_path):
+    """Random queries in cluster mode while vertices fail and a vertex host dies (first attempts only): retries,
+    host restarts, gang restarts and re-execution must leave the results unchanged."""
+    import os
+    from fuzz_columnar import build_columnar
+    from fuzz_operators import build_operators
+    checked = 0
+    for seed, make in ((1, _pipeline), (3, build_columnar), (5, build_operators), (8, build), (9, _pipeline)):
+        ctx = DryadLinqContext(3, platform=PlatformKind.LOCAL_CLUSTER, work_dir=str(tmp_path / f"f{seed}"))
+        ctx.job_max_nodes = 2
+        ctx.dynamic_opt_level, ctx.aggregation_tree_fan_in, ctx.dynamic_data_per_vertex = 31, 2, 700
+        ctx.use_memory_fifo = bool(seed % 2)
+        marker = str(tmp_path / f"killed{seed}")
+
+        def inject(node, part, version, _s=seed, _m=marker):
+            if version == 0 and (_s * 13 + node.uid * 5 + part) % 5 == 0:
+                raise RuntimeError("injected vertex failure")
+            if version == 0 and (_s + node.uid + part) % 11 == 0 and not os.path.exists(_m):
+                open(_m, "w").close()
+                os._exit(5)
+        ctx.fault_injector = inject
+        got = _eval(make, seed, ctx)
+        want = _eval(make, seed, DryadLinqContext(3, local_debug=True))
+        if got is None or want is None:
+            continue
+        assert _norm_typed(got[1], got[0]) == _norm_typed(want[1], want[0]), f"{make.__name__} seed {seed}"
+        checked += 1
+    assert checked >= 3
