@@ -234,6 +234,7 @@ class DryadLinqContext:
         self.spmd_pipe = os.environ.get("DRYAD_SPMD_PIPE", "nccl")   # streamed N:1 edges: "nccl" p2p pipe or "ring" (HBM ring FIFO)
         self.schedule_vertices = True          # place every vertex through the cluster interface + delay scheduler
         self.spmd_control_timeout = 120.0      # seconds a rank waits for the graph manager / the manager for a rank
+        self.vertex_timeout_seconds = 0          # cluster mode: kill and re-run a vertex that runs longer than this (0 = never)
         self.remote_channel_reads = False        # cluster mode: read other hosts' channels through the daemon's file server (HTTP ranges)
         self.use_memory_fifo = SC.USE_MEMORY_FIFO   # stream the inputs of multi-input vertices through FIFOs (start cliques)
         self.duplicate_default_seconds = 600.0   # a vertex running longer than this (no stage model yet) gets a duplicate

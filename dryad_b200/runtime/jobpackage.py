@@ -27,7 +27,7 @@ _CTX_FIELDS = ("num_partitions", "storage_scheme", "intermediate_data_compressio
                "select_order_preserving", "max_failures_per_vertex", "fail_fast_on_deterministic_errors",
                "retain_intermediate", "sample_rate", "group_capacity_hint", "broadcast_join_rows", "fault_injector",
                "job_runtime_limit", "dynamic_opt_level", "aggregation_tree_fan_in", "broadcast_tree_min_consumers",
-               "dynamic_data_per_vertex", "duplicate_default_seconds", "duplicate_min_seconds", "use_memory_fifo", "remote_channel_reads")
+               "dynamic_data_per_vertex", "duplicate_default_seconds", "duplicate_min_seconds", "use_memory_fifo", "remote_channel_reads", "vertex_timeout_seconds")
 
 
 def write(job_dir: str, context, roots) -> str:

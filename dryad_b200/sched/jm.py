@@ -202,6 +202,15 @@ class JobManager:
                         self._on_exit(h)
                 elif listener == EV_TICK:
                     self.gm.check_duplicates(time.perf_counter() - self.t0)
+                    limit_v = float(getattr(self.ctx, "vertex_timeout_seconds", 0) or 0)
+                    if limit_v > 0:
+                        # a vertex that runs beyond the limit is treated like a dead host: its process is killed (the
+                        # watcher reports the exit, the attempt fails, the host is replaced, the vertex runs again)
+                        for h_ in self.hosts:
+                            if h_.busy is not None and h_.proc is not None and h_.proc.poll() is None \
+                                    and time.perf_counter() - h_.busy[1] > limit_v:
+                                self.reporter._emit("process", host=h_.name, state="killed", reason=f"vertex ran longer than {limit_v:g} s")
+                                h_.proc.kill()
                     limit = self.ctx.job_runtime_limit
                     if limit and time.perf_counter() - self.t0 > float(limit):
                         self._finish(False, f"job exceeded its runtime limit of {limit} s")

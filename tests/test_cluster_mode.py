@@ -565,3 +565,20 @@ def test_cluster_subgraph_member_failing_before_it_writes_does_not_hang(tmp_path
     assert sorted(a.except_(b)) == [x for x in range(60) if x % 2 == 1]
     assert time.time() - t0 < 60
     assert ctx.last_cluster_status["counters"]["failures"] >= 3
+
+
+def test_cluster_vertex_timeout_kills_and_reruns_a_hung_vertex(tmp_path):
+    import time
+
+    def hang(node, part, version):
+        if "Select" in node.name and part == 1 and version == 0:
+            time.sleep(120)
+
+    ctx = _ctx(tmp_path, n=2, hosts=2, fault_injector=hang, vertex_timeout_seconds=2, enable_speculative_duplication=False)
+    t0 = time.time()
+    assert sorted(ctx.from_enumerable(range(20), 2).select(lambda x: x * 2)) == [x * 2 for x in range(20)]
+    assert time.time() - t0 < 60
+    st = ctx.last_cluster_status
+    assert st["host_restarts"] >= 1 and st["counters"]["failures"] >= 1
+    log = open(os.path.join(str(tmp_path), "ClusterJobs", "1", "calypso.log")).read()
+    assert "state=killed" in log
