@@ -560,6 +560,12 @@ class JobManager:
             except subprocess.TimeoutExpired:
                 h.proc.kill()                                                 # the exact process we started
         self._remove_uncommitted()                                            # a host may have written a part version after the verdict
+        if self.ok and not self.ctx.retain_intermediate:
+            # intermediate channels and spill files are temporary data of the job (the reference's vertices write
+            # them as temp files of the job directory); kept by default for inspection and single-vertex replay
+            import shutil
+            for sub in ("channels", "spill"):
+                shutil.rmtree(os.path.join(self.job_dir, sub), ignore_errors=True)
         for t in self._watchers:                                              # nobody may post to a pump that is gone
             t.join(5.0)
         self.pump.close()

@@ -582,3 +582,10 @@ def test_cluster_vertex_timeout_kills_and_reruns_a_hung_vertex(tmp_path):
     assert st["host_restarts"] >= 1 and st["counters"]["failures"] >= 1
     log = open(os.path.join(str(tmp_path), "ClusterJobs", "1", "calypso.log")).read()
     assert "state=killed" in log
+
+
+def test_cluster_intermediate_data_is_removed_when_not_retained(tmp_path):
+    ctx = _ctx(tmp_path, n=3, hosts=2, retain_intermediate=False)
+    assert sorted(ctx.from_enumerable(range(90), 3).hash_partition(lambda x: x, 3).select(lambda x: x + 1)) == list(range(1, 91))
+    job_dir = os.path.join(str(tmp_path), "ClusterJobs", "1")
+    assert not os.path.exists(os.path.join(job_dir, "channels")) and os.path.exists(os.path.join(job_dir, "calypso.log"))
