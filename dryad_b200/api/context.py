@@ -649,7 +649,11 @@ class DryadLinqContext:
             raise DryadLinqException(ErrorCode.DidNotCompleteSuccessfully, "job was cancelled")
         sub.submit_job()
         limit = float(self.job_runtime_limit) + 30.0 if self.job_runtime_limit else None
-        st = sub.wait_for_completion(limit)
+        try:
+            st = sub.wait_for_completion(limit)
+        except KeyboardInterrupt:
+            sub.terminate_job()                    # Ctrl-C in the client stops the job's processes too
+            raise
         if st == JobStatus.Running:
             sub.terminate_job()
             raise DryadLinqException(ErrorCode.DidNotCompleteSuccessfully, "job exceeded its runtime limit")
