@@ -153,7 +153,11 @@ class DryadLinqJobInfo:
 
     def wait(self) -> List[Query]:
         if self._thread is not None:
-            self._thread.join()
+            try:
+                self._thread.join()
+            except KeyboardInterrupt:
+                self.cancel_job()                  # Ctrl-C while waiting: stop the job's processes, then let it propagate
+                raise
         if self.status == JobStatus.Failure and self.error is not None:
             raise self.error
         if self.status == JobStatus.Cancelled:
