@@ -47,6 +47,15 @@ class QueryGen:
         self.nodes: List[DLinqQueryNode] = []
         self._built = False
 
+    def _spmd_width(self, count):
+        """One process per GPU: a stage has one partition per rank (or a single one), so an explicit partition
+        count of a repartitioning is a hint there — any other value becomes the number of ranks.  (Explicit range
+        KEYS define their own count and are left alone.)"""
+        world = int(getattr(self.context, "world", 1) or 1)
+        if count and world > 1 and count not in (1, world):
+            return world
+        return count
+
     # ---- driver ------------------------------------------------------------------------------
     def build(self) -> "QueryGen":
         if self._built:
@@ -274,14 +283,14 @@ class QueryGen:
 
     def _visit_hash_partition(self, e: QExpr):
         child = self.visit(e.sources[0])
-        pc = e.params["count"] or child.partition_count
+        pc = self._spmd_width(e.params["count"]) or child.partition_count
         return self._hash_shuffle(child, e.params["key"], pc, e.params.get("comparer"))
 
     def _visit_range_partition(self, e: QExpr):
         child = self.visit(e.sources[0])
         p = e.params
         rk = p.get("range_keys")
-        pc = p["count"] or (len(rk) + 1 if rk is not None else child.partition_count)
+        pc = (p["count"] if rk is not None else self._spmd_width(p["count"])) or (len(rk) + 1 if rk is not None else child.partition_count)
         if rk is not None and len(rk) > pc - 1:
             raise DryadLinqException(ErrorCode.RangePartitionInputOutputMismatch,
                                      f"{len(rk)} range keys for {pc} partitions")
@@ -390,7 +399,7 @@ class QueryGen:
 
     def _visit_broadcast(self, e: QExpr):
         child = self.visit(e.sources[0])
-        return self._broadcast(child, e.params["count"] or child.partition_count)
+        return self._broadcast(child, self._spmd_width(e.params["count"]) or child.partition_count)
 
     # distinct / sets (VisitDistinct :1611, VisitSetOperation :1722)
     def _visit_distinct(self, e: QExpr):
