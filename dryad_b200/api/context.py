@@ -389,6 +389,8 @@ class DryadLinqContext:
             from .types import Record
             rows = [Record(r) if type(r) is dict else r for r in rows]
         n = int(num_partitions) if num_partitions else 1
+        if self.world > 1 and n not in (1, self.world):
+            n = self.world                          # one process per GPU: a dataset has one partition per rank (or a single one)
         parts: List[List] = [[] for _ in range(n)]
         per = (len(rows) + n - 1) // n if rows else 0
         for i in range(n):
